@@ -1,0 +1,114 @@
+"""ctypes binding to the in-tree native libraries.
+
+The CUDA library is mandatory on a GPU box: if it is missing, or a kernel call
+fails, the op raises — there is no silent PyTorch fallback.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from pathlib import Path
+
+import torch
+
+_LIB_DIR = Path(__file__).resolve().parent.parent / "lib"
+_cuda = None
+_host = None
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def _load(name: str) -> ctypes.CDLL:
+    path = _LIB_DIR / name
+    if not path.exists():
+        # Build on demand (nvcc is available on both the dev box and the GPU box).
+        from .. import build as _build
+
+        if "cuda" in name:
+            _build.build_cuda()
+        else:
+            _build.build_host()
+    if not path.exists():
+        raise NativeError(f"native library {path} is missing; run `python -m b200flow.build`")
+    return ctypes.CDLL(str(path))
+
+
+def cuda_lib() -> ctypes.CDLL:
+    global _cuda
+    if _cuda is None:
+        _cuda = _load("libb200flow_cuda.so")
+        _cuda.b2f_last_error.restype = ctypes.c_char_p
+    return _cuda
+
+
+def host_lib() -> ctypes.CDLL:
+    global _host
+    if _host is None:
+        _host = _load("libb200flow_host.so")
+    return _host
+
+
+def loaded_libraries() -> list[str]:
+    return [str(_LIB_DIR / n) for n, l in (("libb200flow_cuda.so", _cuda), ("libb200flow_host.so", _host)) if l]
+
+
+_launches = 0
+
+
+def launch_count() -> int:
+    """Number of native kernel-launching calls made through this binding."""
+    return _launches
+
+
+def reset_launch_count() -> None:
+    global _launches
+    _launches = 0
+
+
+c_void_p = ctypes.c_void_p
+c_int = ctypes.c_int
+c_ll = ctypes.c_longlong
+c_ull = ctypes.c_ulonglong
+c_float = ctypes.c_float
+
+
+def ptr(t: torch.Tensor | None) -> c_void_p:
+    if t is None:
+        return c_void_p(0)
+    return c_void_p(t.data_ptr())
+
+
+def stream_ptr() -> c_void_p:
+    return c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def call(fn_name: str, *args) -> None:
+    """Call `int fn(...)` in the CUDA library and raise with its message on failure."""
+    global _launches
+    lib = cuda_lib()
+    fn = getattr(lib, fn_name)
+    rc = fn(*args)
+    _launches += 1
+    if rc != 0:
+        msg = lib.b2f_last_error()
+        raise NativeError(f"{fn_name} failed (rc={rc}): {msg.decode() if msg else '?'}")
+
+
+def call_int(fn_name: str, *args) -> int:
+    fn = getattr(cuda_lib(), fn_name)
+    fn.restype = ctypes.c_int
+    return int(fn(*args))
+
+
+def require_cuda(*tensors: torch.Tensor) -> None:
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise NativeError("b200flow ops run on sm_100a only; got a CPU tensor "
+                              "(CPU oracles live in b200flow.ops.ref)")
+
+
+def debug_sync() -> None:
+    if os.environ.get("B2F_DEBUG_SYNC"):
+        torch.cuda.synchronize()

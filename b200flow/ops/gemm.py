@@ -1,0 +1,142 @@
+"""K0 — tcgen05 GEMM and the linear-layer autograd functions built on it.
+
+`gemm()` is the thin wrapper over ``b2f_gemm_bf16`` (csrc/kernels/gemm.cu).
+`linear()` is y = x Wᵀ (+ bias) with a backward made of two more calls of the same
+kernel: dgrad (B operand MN-major) and wgrad (both operands MN-major) — no
+transposes are materialised.  When the weight carries a ``main_grad`` fp32 buffer
+the wgrad GEMM accumulates straight into it (beta = 1 epilogue), which is what
+apex's fused_weight_gradient_mlp_cuda does for Megatron.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from ._lib import c_float, c_int, c_ll, ptr, stream_ptr
+
+EPI_GELU, EPI_OUT_F32, EPI_ACCUM, EPI_RELU, EPI_BIAS_ROW = 1, 2, 4, 8, 16
+
+
+def _ld(t: torch.Tensor) -> int:
+    assert t.stride(-1) == 1, "innermost dimension must be contiguous"
+    return t.stride(-2)
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_major: bool = False,
+         out: torch.Tensor | None = None, out_dtype: torch.dtype = torch.bfloat16,
+         bias: torch.Tensor | None = None, residual: torch.Tensor | None = None,
+         aux: torch.Tensor | None = None, gelu: bool = False, relu: bool = False,
+         accumulate: bool = False, alpha: float = 1.0) -> torch.Tensor:
+    """C = epilogue(alpha * op(A) @ op(B)ᵀ-style product), see include/b200flow.h.
+
+    a: [.., M, K] (or [.., K, M] if a_mn_major);  b: [.., N, K] (or [.., K, N] if b_mn_major).
+    """
+    _lib.require_cuda(a, b)
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    assert a.dim() == b.dim() and a.dim() in (2, 3)
+    batch = a.shape[0] if a.dim() == 3 else 1
+    if a_mn_major:
+        K, M = a.shape[-2], a.shape[-1]
+    else:
+        M, K = a.shape[-2], a.shape[-1]
+    if b_mn_major:
+        Kb, N = b.shape[-2], b.shape[-1]
+    else:
+        N, Kb = b.shape[-2], b.shape[-1]
+    assert K == Kb, f"contraction mismatch {K} vs {Kb}"
+    if out is None:
+        shape = (batch, M, N) if a.dim() == 3 else (M, N)
+        out = torch.empty(shape, dtype=out_dtype, device=a.device)
+        assert not accumulate, "accumulate needs an explicit fp32 `out`"
+    flags = 0
+    if out.dtype == torch.float32:
+        flags |= EPI_OUT_F32
+    else:
+        assert out.dtype == torch.bfloat16
+    if accumulate:
+        flags |= EPI_ACCUM
+    if gelu:
+        flags |= EPI_GELU
+    if relu:
+        flags |= EPI_RELU
+    sa = a.stride(0) if a.dim() == 3 else 0
+    sb = b.stride(0) if b.dim() == 3 else 0
+    sc = out.stride(0) if out.dim() == 3 else 0
+    sr = residual.stride(0) if (residual is not None and residual.dim() == 3) else 0
+    sx = aux.stride(0) if (aux is not None and aux.dim() == 3) else 0
+    _lib.call(
+        "b2f_gemm_bf16", ptr(a), ptr(b), ptr(out), c_int(M), c_int(N), c_int(K),
+        c_ll(_ld(a)), c_ll(_ld(b)), c_ll(_ld(out)), c_int(int(a_mn_major)), c_int(int(b_mn_major)),
+        c_int(batch), c_ll(sa), c_ll(sb), c_ll(sc), ptr(bias), ptr(residual),
+        c_ll(_ld(residual) if residual is not None else 0), c_ll(sr), ptr(aux),
+        c_ll(_ld(aux) if aux is not None else 0), c_ll(sx), c_float(alpha), c_int(flags),
+        stream_ptr())
+    _lib.debug_sync()
+    return out
+
+
+def _wgrad(x2: torch.Tensor, dy2: torch.Tensor, weight: torch.Tensor):
+    """dW[N, K] = dyᵀ x, accumulated into weight.main_grad when present."""
+    main_grad = getattr(weight, "main_grad", None)
+    if main_grad is not None:
+        gemm(dy2, x2, a_mn_major=True, b_mn_major=True, out=main_grad, accumulate=True)
+        return None
+    return gemm(dy2, x2, a_mn_major=True, b_mn_major=True)
+
+
+class _Linear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, residual):
+        x2 = x.reshape(-1, x.shape[-1])
+        r2 = residual.reshape(-1, weight.shape[0]) if residual is not None else None
+        y = gemm(x2, weight, bias=bias, residual=r2)
+        ctx.save_for_backward(x2, weight)
+        ctx.has_bias = bias is not None
+        ctx.has_res = residual is not None
+        ctx.x_shape = x.shape
+        return y.reshape(*x.shape[:-1], weight.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, weight = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1])
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dx = gemm(dy2, weight, b_mn_major=True).reshape(ctx.x_shape) if ctx.needs_input_grad[0] else None
+        dw = _wgrad(x2, dy2, weight)
+        db = dy2.sum(0) if ctx.has_bias else None
+        return dx, dw, db, (dy if ctx.has_res else None)
+
+
+def linear(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor | None = None,
+           residual: torch.Tensor | None = None) -> torch.Tensor:
+    """y = x @ weightᵀ (+ bias) (+ residual) on the tcgen05 GEMM."""
+    return _Linear.apply(x, weight, bias, residual)
+
+
+class _LinearGelu(torch.autograd.Function):
+    """y = gelu(x Wᵀ + b) with the pre-activation saved by the same GEMM epilogue."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        x2 = x.reshape(-1, x.shape[-1])
+        pre = torch.empty((x2.shape[0], weight.shape[0]), dtype=torch.bfloat16, device=x.device)
+        y = gemm(x2, weight, bias=bias, aux=pre, gelu=True)
+        ctx.save_for_backward(x2, weight, pre)
+        ctx.x_shape = x.shape
+        return y.reshape(*x.shape[:-1], weight.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        from .elementwise import gelu_bwd_raw
+
+        x2, weight, pre = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1]).contiguous()
+        dpre = gelu_bwd_raw(pre, None, dy2)
+        dx = gemm(dpre, weight, b_mn_major=True).reshape(ctx.x_shape)
+        dw = _wgrad(x2, dpre, weight)
+        return dx, dw, dpre.sum(0)
+
+
+def linear_gelu(x, weight, bias):
+    return _LinearGelu.apply(x, weight, bias)

@@ -1,0 +1,298 @@
+// b200flow K8 — LayerNorm / RMSNorm forward + backward for sm_100a.
+//
+// One CTA per row (persistent over rows in backward), 16-byte vector loads, the
+// row lives in registers between the statistics pass and the normalise pass, so
+// HBM traffic is the algorithmic minimum (read x [+residual], write y [+h]).
+// Forward optionally fuses the residual add that precedes the norm
+// (h = x + residual; y = norm(h)) — the bias-dropout-add + LN pairing of the
+// Megatron layer.  Backward produces dx and per-CTA
+// partial dgamma/dbeta rows in a scratch buffer, reduced by a second kernel
+// (the two-stage reduction apex's fused_layer_norm_cuda uses; the reference
+// pulls apex in at containers/megatron-deepspeed/Dockerfile:6-11).
+#include "../common/ptx.cuh"
+#include "../common/host.h"
+#include "../../include/b200flow.h"
+
+using namespace b2f;
+
+namespace {
+
+constexpr int NORM_THREADS = 256;
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Block-wide sum of up to two values; every thread gets the result.
+template <int NV>
+__device__ __forceinline__ void block_sum(float (&v)[NV], float* red /*[NV*8]*/) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) v[i] = warp_sum(v[i]);
+  __syncthreads();  // protect `red` from the previous use
+  if (lane == 0) {
+#pragma unroll
+    for (int i = 0; i < NV; ++i) red[i * 8 + warp] = v[i];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < NORM_THREADS / 32; ++w) s += red[i * 8 + w];
+    v[i] = s;
+  }
+}
+
+__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
+  float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z),
+         d = unpack_bf16x2(u.w);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  uint4 u;
+  u.x = pack_bf16x2(f[0], f[1]); u.y = pack_bf16x2(f[2], f[3]);
+  u.z = pack_bf16x2(f[4], f[5]); u.w = pack_bf16x2(f[6], f[7]);
+  return u;
+}
+
+// VPT = 16-byte vectors per thread; H <= VPT * 256 * 8.
+template <int VPT, bool RMS>
+__global__ void __launch_bounds__(NORM_THREADS)
+norm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ residual,
+                const __nv_bfloat16* __restrict__ gamma, const __nv_bfloat16* __restrict__ beta,
+                __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ h_out,
+                float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows, int H,
+                float eps) {
+  __shared__ float red[16];
+  const int nvec = H >> 3;
+  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+    const uint4* xr = reinterpret_cast<const uint4*>(x + (size_t)row * H);
+    const uint4* rr = residual ? reinterpret_cast<const uint4*>(residual + (size_t)row * H) : nullptr;
+    float v[VPT][8];
+    float s[2] = {0.f, 0.f};
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      const int c = threadIdx.x + i * NORM_THREADS;
+      if (c < nvec) {
+        unpack8(ld_nc_v4(xr + c), v[i]);
+        if (rr) {
+          float r[8];
+          unpack8(ld_nc_v4(rr + c), r);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[i][j] += r[j];
+          if (h_out) {
+            // round-trip through bf16 so that y is computed from exactly what is stored
+            uint4 hp = pack8(v[i]);
+            reinterpret_cast<uint4*>(h_out + (size_t)row * H)[c] = hp;
+            unpack8(hp, v[i]);
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { s[0] += v[i][j]; s[1] += v[i][j] * v[i][j]; }
+      }
+    }
+    block_sum<2>(s, red);
+    float mean = RMS ? 0.f : s[0] / H;
+    float var = RMS ? s[1] / H : fmaxf(s[1] / H - mean * mean, 0.f);
+    float rstd = rsqrtf(var + eps);
+    if (threadIdx.x == 0) {
+      if (mean_out) mean_out[row] = mean;
+      rstd_out[row] = rstd;
+    }
+    uint4* yr = reinterpret_cast<uint4*>(y + (size_t)row * H);
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      const int c = threadIdx.x + i * NORM_THREADS;
+      if (c < nvec) {
+        float g[8], o[8];
+        unpack8(__ldg(reinterpret_cast<const uint4*>(gamma) + c), g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mean) * rstd * g[j];
+        if (!RMS && beta) {
+          float bb[8];
+          unpack8(__ldg(reinterpret_cast<const uint4*>(beta) + c), bb);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] += bb[j];
+        }
+        yr[c] = pack8(o);
+      }
+    }
+  }
+}
+
+template <int VPT, bool RMS>
+__global__ void __launch_bounds__(NORM_THREADS)
+norm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                const __nv_bfloat16* __restrict__ gamma, const float* __restrict__ mean_in,
+                const float* __restrict__ rstd_in, const __nv_bfloat16* __restrict__ dres_in,
+                __nv_bfloat16* __restrict__ dx, float* __restrict__ partial /*[grid,2,H]*/,
+                int rows, int H) {
+  __shared__ float red[16];
+  const int nvec = H >> 3;
+  float dg[VPT][8], db[VPT][8];
+  float g[VPT][8];
+#pragma unroll
+  for (int i = 0; i < VPT; ++i) {
+    const int c = threadIdx.x + i * NORM_THREADS;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { dg[i][j] = 0.f; db[i][j] = 0.f; g[i][j] = 0.f; }
+    if (c < nvec) unpack8(__ldg(reinterpret_cast<const uint4*>(gamma) + c), g[i]);
+  }
+  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+    const uint4* dyr = reinterpret_cast<const uint4*>(dy + (size_t)row * H);
+    const uint4* xr = reinterpret_cast<const uint4*>(x + (size_t)row * H);
+    const float mean = RMS ? 0.f : mean_in[row];
+    const float rstd = rstd_in[row];
+    float xh[VPT][8], gy[VPT][8];
+    float s[2] = {0.f, 0.f};
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      const int c = threadIdx.x + i * NORM_THREADS;
+      if (c < nvec) {
+        float d[8], xv[8];
+        unpack8(ld_nc_v4(dyr + c), d);
+        unpack8(ld_nc_v4(xr + c), xv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          xh[i][j] = (xv[j] - mean) * rstd;
+          gy[i][j] = d[j] * g[i][j];
+          dg[i][j] += d[j] * xh[i][j];
+          db[i][j] += d[j];
+          s[0] += gy[i][j];
+          s[1] += gy[i][j] * xh[i][j];
+        }
+      }
+    }
+    block_sum<2>(s, red);
+    const float m1 = RMS ? 0.f : s[0] / H;
+    const float m2 = s[1] / H;
+    uint4* dxr = reinterpret_cast<uint4*>(dx + (size_t)row * H);
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      const int c = threadIdx.x + i * NORM_THREADS;
+      if (c < nvec) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rstd * (gy[i][j] - m1 - xh[i][j] * m2);
+        if (dres_in) {  // gradient arriving through the fused residual branch
+          float r[8];
+          unpack8(ld_nc_v4(reinterpret_cast<const uint4*>(dres_in + (size_t)row * H) + c), r);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] += r[j];
+        }
+        dxr[c] = pack8(o);
+      }
+    }
+  }
+  float* pg = partial + (size_t)blockIdx.x * 2 * H;
+  float* pb = pg + H;
+#pragma unroll
+  for (int i = 0; i < VPT; ++i) {
+    const int c = threadIdx.x + i * NORM_THREADS;
+    if (c < nvec) {
+      float4* o = reinterpret_cast<float4*>(pg + c * 8);
+      o[0] = make_float4(dg[i][0], dg[i][1], dg[i][2], dg[i][3]);
+      o[1] = make_float4(dg[i][4], dg[i][5], dg[i][6], dg[i][7]);
+      if (!RMS) {
+        float4* ob = reinterpret_cast<float4*>(pb + c * 8);
+        ob[0] = make_float4(db[i][0], db[i][1], db[i][2], db[i][3]);
+        ob[1] = make_float4(db[i][4], db[i][5], db[i][6], db[i][7]);
+      }
+    }
+  }
+}
+
+// Reduce the per-CTA partial rows: out[h] (+)= sum_p partial[p][which][h].
+__global__ void norm_bwd_reduce_kernel(const float* __restrict__ partial, int nparts, int H,
+                                       float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                       int accumulate) {
+  const int h = blockIdx.x * blockDim.x + threadIdx.x;
+  if (h >= H) return;
+  float sg = 0.f, sb = 0.f;
+  for (int p = 0; p < nparts; ++p) {
+    sg += partial[(size_t)p * 2 * H + h];
+    if (dbeta) sb += partial[(size_t)p * 2 * H + H + h];
+  }
+  dgamma[h] = accumulate ? dgamma[h] + sg : sg;
+  if (dbeta) dbeta[h] = accumulate ? dbeta[h] + sb : sb;
+}
+
+template <bool RMS>
+int launch_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* y,
+               void* h_out, float* mean, float* rstd, int rows, int H, float eps,
+               cudaStream_t st) {
+  const int vpt = (H / 8 + NORM_THREADS - 1) / NORM_THREADS;
+  const int grid = rows < 148 * 8 ? rows : 148 * 8;
+#define B2F_NORM_FWD(V)                                                                         \
+  norm_fwd_kernel<V, RMS><<<grid, NORM_THREADS, 0, st>>>(                                       \
+      (const __nv_bfloat16*)x, (const __nv_bfloat16*)residual, (const __nv_bfloat16*)gamma,     \
+      (const __nv_bfloat16*)beta, (__nv_bfloat16*)y, (__nv_bfloat16*)h_out, mean, rstd, rows, H, \
+      eps)
+  switch (vpt) {
+    case 1: B2F_NORM_FWD(1); break;
+    case 2: B2F_NORM_FWD(2); break;
+    case 3: case 4: B2F_NORM_FWD(4); break;
+    default: B2F_NORM_FWD(8); break;
+  }
+#undef B2F_NORM_FWD
+  B2F_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+template <bool RMS>
+int launch_bwd(const void* dy, const void* x, const void* gamma, const float* mean,
+               const float* rstd, const void* dres, void* dx, float* dgamma, float* dbeta,
+               float* scratch, int nparts, int rows, int H, int accumulate, cudaStream_t st) {
+  const int vpt = (H / 8 + NORM_THREADS - 1) / NORM_THREADS;
+#define B2F_NORM_BWD(V)                                                                       \
+  norm_bwd_kernel<V, RMS><<<nparts, NORM_THREADS, 0, st>>>(                                   \
+      (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (const __nv_bfloat16*)gamma, mean,   \
+      rstd, (const __nv_bfloat16*)dres, (__nv_bfloat16*)dx, scratch, rows, H)
+  switch (vpt) {
+    case 1: B2F_NORM_BWD(1); break;
+    case 2: B2F_NORM_BWD(2); break;
+    case 3: case 4: B2F_NORM_BWD(4); break;
+    default: B2F_NORM_BWD(8); break;
+  }
+#undef B2F_NORM_BWD
+  B2F_CHECK_CUDA(cudaGetLastError());
+  norm_bwd_reduce_kernel<<<(H + 255) / 256, 256, 0, st>>>(scratch, nparts, H, dgamma,
+                                                          RMS ? nullptr : dbeta, accumulate);
+  B2F_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int b2f_norm_bwd_num_partials(int rows) {
+  const int cap = b2f::sm_count() * 2;
+  return rows < cap ? rows : cap;
+}
+
+extern "C" int b2f_norm_fwd(const void* x, const void* residual, const void* gamma,
+                            const void* beta, void* y, void* h_out, float* mean, float* rstd,
+                            int rows, int H, float eps, int rms, void* stream) {
+  B2F_REQUIRE(H % 8 == 0 && H <= 8 * NORM_THREADS * 8, "norm: H must be a multiple of 8, <= 16384");
+  B2F_REQUIRE(rows > 0, "norm: rows must be positive");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return rms ? launch_fwd<true>(x, residual, gamma, beta, y, h_out, mean, rstd, rows, H, eps, st)
+             : launch_fwd<false>(x, residual, gamma, beta, y, h_out, mean, rstd, rows, H, eps, st);
+}
+
+// scratch: fp32 [b2f_norm_bwd_num_partials(rows), 2, H] owned by the caller.
+extern "C" int b2f_norm_bwd(const void* dy, const void* x, const void* gamma, const float* mean,
+                            const float* rstd, const void* dres, void* dx, float* dgamma,
+                            float* dbeta, float* scratch, int rows, int H, int rms,
+                            int accumulate, void* stream) {
+  B2F_REQUIRE(H % 8 == 0 && H <= 8 * NORM_THREADS * 8, "norm: H must be a multiple of 8, <= 16384");
+  B2F_REQUIRE(rows > 0 && scratch != nullptr, "norm bwd: rows > 0 and scratch required");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int nparts = b2f_norm_bwd_num_partials(rows);
+  return rms ? launch_bwd<true>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, scratch, nparts,
+                                rows, H, accumulate, st)
+             : launch_bwd<false>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, scratch,
+                                 nparts, rows, H, accumulate, st);
+}

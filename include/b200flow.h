@@ -1,0 +1,86 @@
+/* b200flow — C ABI of the sm_100a kernel library (libb200flow_cuda.so).
+ *
+ * Every entry point takes raw device pointers plus the CUDA stream to launch on
+ * (`void* stream` == cudaStream_t) and returns 0 on success; on failure the
+ * message is available from b2f_last_error() (thread-local).  bf16 tensors are
+ * passed as `void*`.  Nothing here allocates device memory: scratch buffers are
+ * supplied by the caller and their sizes are queried with the *_num_partials /
+ * *_scratch_bytes helpers.
+ *
+ * The reference repository contains no native code; each group
+ * below cites the upstream native component it stands in for.
+ */
+#ifndef B200FLOW_H_
+#define B200FLOW_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* b2f_last_error(void);
+
+/* ---- K0: tcgen05 GEMM ------------------------------------------------------
+ * C[b] = epilogue(alpha * op(A[b]) * op(B[b])), bf16 operands, fp32 accumulate.
+ *   a_mn_major = 0: A stored [M, K] (K contiguous);  1: A stored [K, M].
+ *   b_mn_major = 0: B stored [N, K] (K contiguous);  1: B stored [K, N].
+ * flags: 1 gelu, 2 C is fp32, 4 C += (fp32 only), 8 relu, 16 bias per row.
+ * Stands in for cuBLAS + apex fused_dense / fused_weight_gradient_mlp
+ * (containers/megatron-deepspeed/Dockerfile:6-11). */
+int b2f_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
+                  long long ldb, long long ldc, int a_mn_major, int b_mn_major, int batch,
+                  long long strideA, long long strideB, long long strideC, const void* bias,
+                  const void* residual, long long ldr, long long strideR, void* aux,
+                  long long ldaux, long long strideAux, float alpha, int flags, void* stream);
+
+/* ---- K8: LayerNorm / RMSNorm (apex fused_layer_norm_cuda) ------------------ */
+int b2f_norm_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* y,
+                 void* h_out, float* mean, float* rstd, int rows, int H, float eps, int rms,
+                 void* stream);
+int b2f_norm_bwd_num_partials(int rows);
+/* scratch: fp32 [b2f_norm_bwd_num_partials(rows) * 2 * H] */
+int b2f_norm_bwd(const void* dy, const void* x, const void* gamma, const float* mean,
+                 const float* rstd, const void* dres, void* dx, float* dgamma, float* dbeta,
+                 float* scratch, int rows, int H, int rms, int accumulate, void* stream);
+
+/* ---- K6 / K11: optimizer family (apex amp_C, DeepSpeed FusedAdam) ---------- */
+int b2f_adamw_flat(float* master, float* m, float* v, const void* grad, int grad_bf16,
+                   void* param_out, long long n, float lr, float beta1, float beta2, float eps,
+                   float weight_decay, int step, const float* grad_scale, const int* skip,
+                   void* stream);
+int b2f_adamw_multi(const void* segs, int nsegs, long long total_chunks, int grad_bf16, float lr,
+                    float beta1, float beta2, float eps, float weight_decay, int step,
+                    const float* grad_scale, const int* skip, void* stream);
+int b2f_multi_tensor_chunk(void);
+int b2f_sumsq_num_partials(long long n);
+/* scratch: fp32 [b2f_sumsq_num_partials(n)] */
+int b2f_sumsq(const void* x, long long n, int dtype_fp32, float* scratch, float* out, int* overflow,
+              int accumulate, void* stream);
+int b2f_clip_coef(const float* sumsq, float max_norm, float extra_scale, float* coef_out,
+                  float* norm_out, void* stream);
+int b2f_scale(void* x, long long n, int dtype_fp32, const float* scale_ptr, float scale,
+              void* stream);
+
+/* ---- K10 + RoPE + cross-entropy (Megatron fused_bias_gelu, bias_dropout_add,
+ *      apex fused_rotary_positional_embedding, scaled_masked_softmax) --------- */
+int b2f_swiglu_fwd(const void* gu, void* out, long long rows, int F, void* stream);
+int b2f_swiglu_bwd(const void* gu, const void* dout, void* dgu, long long rows, int F, void* stream);
+int b2f_gelu_fwd(const void* x, const void* bias, void* y, long long rows, int H, void* stream);
+int b2f_gelu_bwd(const void* x, const void* bias, const void* dy, void* dx, long long rows, int H,
+                 void* stream);
+int b2f_bias_dropout_add(const void* x, const void* bias, const void* residual, void* out,
+                         void* mask, long long rows, int H, float p, unsigned long long seed,
+                         void* stream);
+int b2f_dropout_bwd(const void* dy, const void* mask, void* dx, long long n, float p, void* stream);
+int b2f_rope(void* x, const float* cos_t, const float* sin_t, long long tokens, int seq, int nh,
+             int d, long long token_stride, int pos_offset, int backward, void* stream);
+int b2f_cross_entropy(const void* logits, const long long* targets, float* loss, void* dlogits,
+                      long long rows, int V, long long ld, float grad_scale,
+                      long long ignore_index, void* stream);
+int b2f_scaled_masked_softmax(const void* x, const void* mask, void* y, long long batch, int heads,
+                              int sq, int sk, float scale, int causal, void* stream);
+int b2f_cast_f32_bf16(const float* x, void* y, long long n, float scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200FLOW_H_ */

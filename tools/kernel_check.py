@@ -1,0 +1,320 @@
+"""Standalone kernel bring-up checks with rich diagnostics (one group per process).
+
+Used during development on the GPU box: each group runs in its own process under
+`timeout`, so a trapped kernel cannot poison the others.  The pytest suite under
+tests/ is the regression gate; this prints error maps that help debug a new
+kernel blind.   usage: python tools/kernel_check.py <group> [...]
+"""
+from __future__ import annotations
+
+import json
+import sys
+import time
+from pathlib import Path
+
+import torch
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+
+from b200flow.ops import elementwise as ew  # noqa: E402
+from b200flow.ops import gemm as G  # noqa: E402
+from b200flow.ops import norm as N  # noqa: E402
+from b200flow.ops import optim as O  # noqa: E402
+
+DEV = "cuda"
+RESULTS = []
+
+
+def report(name, got, ref, tol):
+    got = got.float()
+    ref = ref.float()
+    err = (got - ref).abs()
+    denom = ref.abs().max().item() + 1e-6
+    rel = err.max().item() / denom
+    ok = bool(rel < tol) and bool(torch.isfinite(got).all())
+    rec = {"name": name, "ok": ok, "max_abs": err.max().item(), "rel_to_max": rel,
+           "ref_absmax": denom}
+    if not ok and got.dim() == 2:
+        bad = err > tol * denom
+        rows = bad.any(1).nonzero().flatten()
+        cols = bad.any(0).nonzero().flatten()
+        rec["bad_frac"] = bad.float().mean().item()
+        rec["bad_rows_head"] = rows[:16].tolist()
+        rec["bad_rows_count"] = int(rows.numel())
+        rec["bad_cols_head"] = cols[:16].tolist()
+        rec["bad_cols_count"] = int(cols.numel())
+        rec["got_head"] = got[:2, :8].tolist()
+        rec["ref_head"] = ref[:2, :8].tolist()
+    RESULTS.append(rec)
+    print(json.dumps(rec), flush=True)
+    return ok
+
+
+def timeit(fn, iters=20, warmup=3):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=DEV)
+    ts = []
+    for _ in range(iters):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    ts.sort()
+    return ts[len(ts) // 2]
+
+
+def group_gemm(mode):
+    torch.manual_seed(0)
+    shapes = [(128, 256, 64), (256, 512, 256), (384, 768, 320), (200, 264, 136), (4096, 4096, 4096)]
+    for (M, Nn, K) in shapes:
+        a = torch.randn(M, K, device=DEV, dtype=torch.bfloat16)
+        b = torch.randn(Nn, K, device=DEV, dtype=torch.bfloat16)
+        ref = a.float() @ b.float().t()
+        if mode == "nt":
+            got = G.gemm(a, b)
+        elif mode == "nn":
+            got = G.gemm(a, b.t().contiguous(), b_mn_major=True)
+        elif mode == "tn":
+            got = G.gemm(a.t().contiguous(), b.t().contiguous(), a_mn_major=True, b_mn_major=True)
+        elif mode == "tt":
+            got = G.gemm(a.t().contiguous(), b, a_mn_major=True)
+        torch.cuda.synchronize()
+        report(f"gemm_{mode}_{M}x{Nn}x{K}", got, ref, 2e-2)
+
+
+def group_gemm_epi():
+    torch.manual_seed(1)
+    M, Nn, K = 512, 768, 256
+    a = torch.randn(M, K, device=DEV, dtype=torch.bfloat16)
+    b = torch.randn(Nn, K, device=DEV, dtype=torch.bfloat16) * 0.05
+    bias = torch.randn(Nn, device=DEV, dtype=torch.bfloat16)
+    res = torch.randn(M, Nn, device=DEV, dtype=torch.bfloat16)
+    ref = a.float() @ b.float().t()
+    report("epi_bias", G.gemm(a, b, bias=bias), ref + bias.float(), 2e-2)
+    report("epi_res", G.gemm(a, b, residual=res), ref + res.float(), 2e-2)
+    aux = torch.empty(M, Nn, device=DEV, dtype=torch.bfloat16)
+    got = G.gemm(a, b, bias=bias, gelu=True, aux=aux)
+    pre = ref + bias.float()
+    report("epi_gelu", got, torch.nn.functional.gelu(pre, approximate="tanh"), 2e-2)
+    report("epi_aux", aux, pre, 2e-2)
+    c32 = torch.ones(M, Nn, device=DEV, dtype=torch.float32)
+    G.gemm(a, b, out=c32, accumulate=True)
+    report("epi_f32_accum", c32, ref + 1.0, 2e-2)
+    c32b = torch.empty(M, Nn, device=DEV, dtype=torch.float32)
+    G.gemm(a, b, out=c32b, alpha=0.5)
+    report("epi_f32_alpha", c32b, 0.5 * ref, 2e-2)
+    # batched
+    ab = torch.randn(3, 256, 128, device=DEV, dtype=torch.bfloat16)
+    bb = torch.randn(3, 512, 128, device=DEV, dtype=torch.bfloat16)
+    report("gemm_batched", G.gemm(ab, bb).reshape(-1, 512),
+           torch.bmm(ab.float(), bb.float().transpose(1, 2)).reshape(-1, 512), 2e-2)
+
+
+def group_gemm_perf():
+    out = {}
+    for (M, Nn, K) in [(4096, 4096, 4096), (8192, 8192, 8192), (4096, 22016, 4096), (4096, 4096, 11008),
+                       (4096, 12288, 4096), (4096, 32000, 4096)]:
+        a = torch.randn(M, K, device=DEV, dtype=torch.bfloat16)
+        b = torch.randn(Nn, K, device=DEV, dtype=torch.bfloat16)
+        c = torch.empty(M, Nn, device=DEV, dtype=torch.bfloat16)
+        t_ours = timeit(lambda: G.gemm(a, b, out=c))
+        t_cublas = timeit(lambda: torch.matmul(a, b.t(), out=c))
+        fl = 2.0 * M * Nn * K
+        rec = {"name": f"perf_{M}x{Nn}x{K}", "ours_ms": t_ours, "cublas_ms": t_cublas,
+               "ours_tflops": fl / t_ours / 1e9, "cublas_tflops": fl / t_cublas / 1e9}
+        # dgrad / wgrad modes
+        bt = b.t().contiguous()
+        t_nn = timeit(lambda: G.gemm(a, bt, out=c, b_mn_major=True))
+        at = a.t().contiguous()
+        t_tn = timeit(lambda: G.gemm(at, bt, out=c, a_mn_major=True, b_mn_major=True))
+        rec["nn_tflops"] = fl / t_nn / 1e9
+        rec["tn_tflops"] = fl / t_tn / 1e9
+        print(json.dumps(rec), flush=True)
+        out[rec["name"]] = rec
+    RESULTS.append({"name": "gemm_perf", "ok": True, "detail": out})
+
+
+def group_norm():
+    torch.manual_seed(2)
+    for rms in (True, False):
+        for (rows, H) in [(64, 1024), (300, 4096), (4096, 4096), (17, 768)]:
+            x = torch.randn(rows, H, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+            r = torch.randn(rows, H, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+            g = (1 + 0.1 * torch.randn(H, device=DEV)).to(torch.bfloat16).requires_grad_()
+            bta = None if rms else (0.1 * torch.randn(H, device=DEV)).to(torch.bfloat16).requires_grad_()
+            y, h = N.norm(x, g, bta, residual=r, rms=rms, eps=1e-5)
+            dy = torch.randn_like(y)
+            dh = torch.randn_like(h)
+            (y.float() * dy.float()).sum().backward(retain_graph=True)
+            (h.float() * dh.float()).sum().backward()
+            xf = x.detach().float().requires_grad_()
+            rf = r.detach().float().requires_grad_()
+            gf = g.detach().float().requires_grad_()
+            bf = bta.detach().float().requires_grad_() if bta is not None else None
+            hf = (xf + rf).to(torch.bfloat16).float() + 0 * (xf + rf)
+            hf = xf + rf
+            if rms:
+                yf = hf * torch.rsqrt(hf.pow(2).mean(-1, keepdim=True) + 1e-5) * gf
+            else:
+                yf = torch.nn.functional.layer_norm(hf, (H,), gf, bf, 1e-5)
+            ((yf * dy.float()).sum() + (hf * dh.float()).sum()).backward()
+            tag = f"{'rms' if rms else 'ln'}_{rows}x{H}"
+            report(f"norm_y_{tag}", y, yf, 2e-2)
+            report(f"norm_dx_{tag}", x.grad, xf.grad, 3e-2)
+            report(f"norm_dres_{tag}", r.grad, rf.grad, 3e-2)
+            report(f"norm_dg_{tag}", g.grad, gf.grad, 3e-2)
+            if bta is not None:
+                report(f"norm_db_{tag}", bta.grad, bf.grad, 3e-2)
+
+
+def group_optim():
+    torch.manual_seed(3)
+    for n in (1000003, 4096, 7):
+        p = torch.randn(n, device=DEV)
+        m = torch.zeros(n, device=DEV)
+        v = torch.zeros(n, device=DEV)
+        pb = torch.empty(n, device=DEV, dtype=torch.bfloat16)
+        ref_p = torch.nn.Parameter(p.clone())
+        opt = torch.optim.AdamW([ref_p], lr=1e-2, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
+        for step in range(1, 4):
+            g = torch.randn(n, device=DEV)
+            ref_p.grad = g.clone()
+            opt.step()
+            O.adamw_flat_(p, m, v, g, pb, lr=1e-2, beta1=0.9, beta2=0.95, eps=1e-8,
+                          weight_decay=0.1, step=step)
+        report(f"adamw_flat_{n}", p, ref_p.detach(), 1e-4)
+        report(f"adamw_flat_bf16out_{n}", pb, ref_p.detach(), 1e-2)
+    x = torch.randn(3000001, device=DEV)
+    report("sumsq_f32", O.sumsq(x), (x.double() ** 2).sum().float().reshape(1), 1e-4)
+    xb = x.to(torch.bfloat16)
+    report("sumsq_bf16", O.sumsq(xb), (xb.double() ** 2).sum().float().reshape(1), 1e-4)
+    coef, nrm = O.clip_coef(O.sumsq(x), 1.0)
+    report("clip_norm", nrm, x.norm().reshape(1), 1e-4)
+    report("clip_coef", coef, (1.0 / (x.norm() + 1e-6)).reshape(1), 1e-4)
+    y = x.clone()
+    O.scale_(y, 0.5, coef)
+    report("scale", y, x * 0.5 * coef, 1e-5)
+    # multi-tensor
+    sizes = [5, 8192, 10000, 333]
+    ps = [torch.randn(s, device=DEV) for s in sizes]
+    ms = [torch.zeros_like(t) for t in ps]
+    vs = [torch.zeros_like(t) for t in ps]
+    gs = [torch.randn(s, device=DEV).to(torch.bfloat16) for s in sizes]
+    pbs = [torch.empty(s, device=DEV, dtype=torch.bfloat16) for s in sizes]
+    refs = [torch.nn.Parameter(t.clone()) for t in ps]
+    opt = torch.optim.AdamW(refs, lr=1e-2, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.01)
+    for r_, g_ in zip(refs, gs):
+        r_.grad = g_.float()
+    opt.step()
+    tab = O.MultiTensorTable(ps, ms, vs, gs, pbs)
+    O.adamw_multi_(tab, lr=1e-2, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.01, step=1)
+    report("adamw_multi", torch.cat(ps), torch.cat([r_.detach() for r_ in refs]), 1e-4)
+
+
+def group_elementwise():
+    torch.manual_seed(4)
+    rows, F = 300, 1024
+    gu = torch.randn(rows, 2 * F, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    out = ew.swiglu(gu)
+    d = torch.randn_like(out)
+    out.backward(d)
+    gf = gu.detach().float().requires_grad_()
+    of = torch.nn.functional.silu(gf[:, :F]) * gf[:, F:]
+    of.backward(d.float())
+    report("swiglu_fwd", out, of, 2e-2)
+    report("swiglu_bwd", gu.grad, gf.grad, 2e-2)
+    x = torch.randn(rows, F, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    b = torch.randn(F, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    y = ew.bias_gelu(x, b)
+    y.backward(d)
+    xf, bf = x.detach().float().requires_grad_(), b.detach().float().requires_grad_()
+    yf = torch.nn.functional.gelu(xf + bf, approximate="tanh")
+    yf.backward(d.float())
+    report("gelu_fwd", y, yf, 2e-2)
+    report("gelu_bwd", x.grad, xf.grad, 2e-2)
+    report("gelu_dbias", b.grad, bf.grad, 3e-2)
+    r = torch.randn(rows, F, device=DEV, dtype=torch.bfloat16)
+    o0 = ew.bias_dropout_add(x.detach(), b.detach(), r, 0.0)
+    report("bda_p0", o0, x.detach().float() + b.detach().float() + r.float(), 2e-2)
+    xx = torch.ones(4096, 1024, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    o1 = ew.bias_dropout_add(xx, None, None, 0.25, seed=123)
+    keep = (o1 != 0).float().mean().item()
+    RESULTS.append({"name": "bda_keep_frac", "ok": abs(keep - 0.75) < 0.01, "keep": keep})
+    print(json.dumps(RESULTS[-1]), flush=True)
+    o1.backward(torch.ones_like(o1))
+    report("bda_bwd_mask", xx.grad, o1.detach(), 1e-3)
+    # rope
+    tokens, nh, dh, seq = 256, 4, 128, 128
+    q = torch.randn(tokens, nh, dh, device=DEV, dtype=torch.bfloat16)
+    cos_t, sin_t = ew.rope_tables(seq, dh, 10000.0, DEV)
+    q2 = q.clone()
+    ew.rope_inplace_raw(q2, cos_t, sin_t, seq, False)
+    pos = torch.arange(tokens, device=DEV) % seq
+    c, s = cos_t[pos][:, None, :], sin_t[pos][:, None, :]
+    qf = q.float()
+    x1, x2 = qf[..., : dh // 2], qf[..., dh // 2:]
+    ref = torch.cat([x1 * c - x2 * s, x2 * c + x1 * s], -1)
+    report("rope_fwd", q2.reshape(tokens, -1), ref.reshape(tokens, -1), 2e-2)
+    ew.rope_inplace_raw(q2, cos_t, sin_t, seq, True)
+    report("rope_roundtrip", q2.reshape(tokens, -1), qf.reshape(tokens, -1), 3e-2)
+    # cross entropy
+    T, V = 512, 32000
+    logits = (torch.randn(T, V, device=DEV) * 2).to(torch.bfloat16).requires_grad_()
+    tg = torch.randint(0, V, (T,), device=DEV)
+    tg[:7] = -100
+    lf = logits.detach().float().requires_grad_()
+    ref_loss = torch.nn.functional.cross_entropy(lf, tg, ignore_index=-100)
+    ref_loss.backward()
+    lc = logits.detach().clone().requires_grad_()
+    loss = ew.cross_entropy(lc, tg, -100)
+    loss.backward()
+    report("ce_loss", loss.reshape(1), ref_loss.reshape(1), 1e-3)
+    report("ce_grad", lc.grad, lf.grad, 2e-2)
+    # softmax
+    xs = torch.randn(2, 3, 64, 64, device=DEV, dtype=torch.bfloat16)
+    ys = ew.scaled_masked_softmax(xs, None, 0.125, causal=True)
+    mask = torch.triu(torch.ones(64, 64, device=DEV, dtype=torch.bool), 1)
+    refs = torch.softmax((xs.float() * 0.125).masked_fill(mask, float("-inf")), -1)
+    report("softmax_causal", ys.reshape(-1, 64), refs.reshape(-1, 64), 2e-2)
+    xc = torch.randn(100003, device=DEV)
+    report("cast", ew.cast_f32_bf16(xc, scale=0.5).reshape(1, -1), (xc * 0.5).reshape(1, -1), 1e-2)
+
+
+GROUPS = {
+    "gemm_nt": lambda: group_gemm("nt"),
+    "gemm_nn": lambda: group_gemm("nn"),
+    "gemm_tn": lambda: group_gemm("tn"),
+    "gemm_tt": lambda: group_gemm("tt"),
+    "gemm_epi": group_gemm_epi,
+    "gemm_perf": group_gemm_perf,
+    "norm": group_norm,
+    "optim": group_optim,
+    "elementwise": group_elementwise,
+}
+
+try:  # optional groups registered by later modules
+    from tools import kernel_check_ext  # type: ignore  # noqa: F401
+except Exception:  # pragma: no cover
+    pass
+
+
+if __name__ == "__main__":
+    names = sys.argv[1:] or list(GROUPS)
+    t0 = time.time()
+    for n in names:
+        try:
+            GROUPS[n]()
+            torch.cuda.synchronize()
+        except Exception as e:  # noqa: BLE001
+            rec = {"name": n, "ok": False, "exception": repr(e)[:500]}
+            RESULTS.append(rec)
+            print(json.dumps(rec), flush=True)
+    nbad = sum(1 for r in RESULTS if not r.get("ok"))
+    print(json.dumps({"summary": names, "checks": len(RESULTS), "failed": nbad,
+                      "seconds": round(time.time() - t0, 1)}), flush=True)
+    sys.exit(1 if nbad else 0)
