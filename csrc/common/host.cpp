@@ -84,6 +84,41 @@ int make_tma_2d(CUtensorMap* out, const void* base, TmaDtype dt, uint64_t rows, 
   return make_tma_3d(out, base, dt, 1, rows, cols, 0, ld, box_rows, box_cols, swizzle_bytes);
 }
 
+int make_tma_4d(CUtensorMap* out, const void* base, TmaDtype dt, uint64_t d3, uint64_t d2,
+                uint64_t rows, uint64_t cols, uint64_t s3, uint64_t s2, uint64_t s1,
+                uint32_t box_rows, uint32_t box_cols, int swizzle_bytes) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) {
+    set_error("b200flow: cuTensorMapEncodeTiled driver entry point unavailable (no CUDA driver?)");
+    return -1;
+  }
+  CUtensorMapDataType cu;
+  uint32_t es;
+  if (dtype_info(dt, &cu, &es)) return -1;
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || ((s1 * es) & 15) || ((s2 * es) & 15) ||
+      ((s3 * es) & 15)) {
+    set_error("b200flow: TMA operand must be 16-byte aligned with 16-byte-multiple strides");
+    return -2;
+  }
+  // TMA wants dims ordered by increasing stride after the contiguous one; the
+  // attention layouts ([b, s, h, d] with rows = s, d2 = h) have s2 < s1, so the
+  // caller-visible coordinate order is fixed here as (col, d2, row, d3).
+  cuuint64_t dims[4] = {cols, d2, rows, d3};
+  cuuint64_t strides[3] = {s2 * es, s1 * es, s3 * es};
+  cuuint32_t box[4] = {box_cols, 1, box_rows, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUtensorMapSwizzle sw = swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                               : CU_TENSOR_MAP_SWIZZLE_NONE;
+  CUresult r = enc(out, cu, 4, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("b200flow: cuTensorMapEncodeTiled(4d) failed with CUresult " + std::to_string((int)r));
+    return -1;
+  }
+  return 0;
+}
+
 int sm_count() {
   static int cache[64] = {0};
   int dev = 0;

@@ -45,6 +45,12 @@ int make_tma_3d(CUtensorMap* out, const void* base, TmaDtype dt, uint64_t batch,
                 uint64_t cols, uint64_t batch_stride, uint64_t ld, uint32_t box_rows,
                 uint32_t box_cols, int swizzle_bytes);
 
+// 4-D variant for attention operands: element strides (s3, s2, s1, 1) over dims
+// [d3, d2, rows, cols]; box = box_rows x box_cols in the two innermost dims.
+int make_tma_4d(CUtensorMap* out, const void* base, TmaDtype dt, uint64_t d3, uint64_t d2,
+                uint64_t rows, uint64_t cols, uint64_t s3, uint64_t s2, uint64_t s1,
+                uint32_t box_rows, uint32_t box_cols, int swizzle_bytes);
+
 int sm_count();  // SMs of the current device (cached per device)
 
 }  // namespace b2f
