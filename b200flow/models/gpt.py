@@ -1,0 +1,295 @@
+"""GPT-2 / Llama decoder-only transformer on the b200flow sm_100a ops.
+
+One module covers both families the reference trains through Megatron-DeepSpeed
+(`examples/megatron-deepspeed/gpt2_345m/pretrain-ddp-zero1.yaml:39-53` for GPT-2
+345M; Llama-2 7B is BASELINE.json config 4): LayerNorm+GELU+learned positions+tied
+embeddings for GPT-2, RMSNorm+SwiGLU+RoPE+untied head for Llama.
+
+Activations are ``[tokens, hidden]`` with tokens in sequence-major ``[s, b]`` order
+(Megatron's layout) so a sequence-parallel shard is a contiguous row range.  Every
+linear goes through a :class:`~b200flow.parallel.tensor_parallel.TPContext`, which
+is the identity on one GPU and the fused all-gather→GEMM / GEMM→reduce-scatter
+kernels under tensor + sequence parallelism.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field
+
+import torch
+from torch import nn
+
+from ..ops import attention as A
+from ..ops import elementwise as E
+from ..ops import norm as N
+
+
+@dataclass
+class GPTConfig:
+    vocab_size: int = 32000
+    hidden: int = 4096
+    layers: int = 32
+    heads: int = 32
+    kv_heads: int | None = None
+    ffn: int = 11008
+    max_seq: int = 4096
+    norm: str = "rms"            # "rms" | "ln"
+    act: str = "swiglu"          # "swiglu" | "gelu"
+    rope: bool = True
+    rope_base: float = 10000.0
+    learned_pos: bool = False
+    bias: bool = False
+    tie_embeddings: bool = False
+    eps: float = 1e-5
+    init_std: float = 0.02
+    dropout: float = 0.0
+    name: str = "llama"
+
+    def __post_init__(self):
+        if self.kv_heads is None:
+            self.kv_heads = self.heads
+
+    @property
+    def head_dim(self) -> int:
+        return self.hidden // self.heads
+
+    def param_count(self) -> int:
+        d = self.head_dim
+        qkv = self.hidden * (self.heads + 2 * self.kv_heads) * d
+        proj = self.hidden * self.hidden
+        mlp = self.hidden * self.ffn * (3 if self.act == "swiglu" else 2)
+        per_layer = qkv + proj + mlp + 2 * self.hidden
+        emb = self.vocab_size * self.hidden * (1 if self.tie_embeddings else 2)
+        return self.layers * per_layer + emb + self.hidden
+
+    def flops_per_token(self, seq: int) -> float:
+        """Model FLOPs (fwd+bwd) per token, causal attention counted at half."""
+        d = self.head_dim
+        lin = 2 * (self.hidden * (self.heads + 2 * self.kv_heads) * d + self.hidden * self.hidden
+                   + self.hidden * self.ffn * (3 if self.act == "swiglu" else 2))
+        attn = 2 * 2 * seq * self.hidden * 0.5
+        head = 2 * self.hidden * self.vocab_size
+        return 3.0 * (self.layers * (lin + attn) + head)
+
+
+PRESETS = {
+    # Llama-2 7B (BASELINE.json config 4)
+    "llama2-7b": dict(vocab_size=32000, hidden=4096, layers=32, heads=32, ffn=11008, max_seq=4096),
+    # GPT-2 345M exactly as examples/megatron-deepspeed/gpt2_345m/pretrain-ddp-zero1.yaml:39-45
+    "gpt2-345m": dict(vocab_size=50304, hidden=1024, layers=24, heads=16, ffn=4096, max_seq=1024,
+                      norm="ln", act="gelu", rope=False, learned_pos=True, bias=True,
+                      tie_embeddings=True, name="gpt2"),
+    "llama-tiny": dict(vocab_size=1024, hidden=256, layers=2, heads=2, ffn=512, max_seq=256),
+    "gpt2-tiny": dict(vocab_size=1024, hidden=256, layers=2, heads=4, ffn=1024, max_seq=256,
+                      norm="ln", act="gelu", rope=False, learned_pos=True, bias=True,
+                      tie_embeddings=True, name="gpt2"),
+}
+
+
+def config_from_preset(name: str, **overrides) -> GPTConfig:
+    kw = dict(PRESETS[name])
+    kw.update(overrides)
+    return GPTConfig(**kw)
+
+
+class _QKVAttention(torch.autograd.Function):
+    """RoPE (in place on the fused QKV buffer) + flash attention, one autograd node.
+
+    qkv: [s, b, heads + 2*kv_heads, d].  Returns o: [s*b, heads*d] (sequence-major)."""
+
+    @staticmethod
+    def forward(ctx, qkv, heads, kv_heads, causal, scale, rope_tables, kv_lens):
+        s, b, nh, d = qkv.shape
+        if rope_tables is not None:
+            x = qkv.view(s * b, nh, d)[:, : heads + kv_heads]
+            E.rope_inplace_raw(x, rope_tables[0], rope_tables[1], s, False, 0, pos_div=b)
+        v = qkv.permute(1, 0, 2, 3)  # [b, s, nh, d] view
+        q, k, vv = v[:, :, :heads], v[:, :, heads:heads + kv_heads], v[:, :, heads + kv_heads:]
+        o_sb = torch.empty((s, b, heads, d), dtype=qkv.dtype, device=qkv.device)
+        o = o_sb.permute(1, 0, 2, 3)
+        lse = torch.empty((b, heads, s), dtype=torch.float32, device=qkv.device)
+        A._lib.call("b2f_attn_fwd", A.ptr(q), A.ptr(k), A.ptr(vv), A.ptr(o), A.ptr(lse), A.c_int(b),
+                    A.c_int(s), A.c_int(heads), A.c_int(kv_heads), A.c_int(d),
+                    A.c_ll(q.stride(1)), A.c_ll(q.stride(0)), A.c_ll(k.stride(1)), A.c_ll(k.stride(0)),
+                    A.c_ll(vv.stride(1)), A.c_ll(vv.stride(0)), A.c_ll(o.stride(1)), A.c_ll(o.stride(0)),
+                    A.c_float(scale), A.c_int(int(causal)), A.ptr(kv_lens), A.stream_ptr())
+        ctx.save_for_backward(qkv, o_sb, lse)
+        ctx.cfg = (heads, kv_heads, causal, scale, rope_tables, kv_lens)
+        return o_sb.view(s * b, heads * d)
+
+    @staticmethod
+    def backward(ctx, do):
+        qkv, o_sb, lse = ctx.saved_tensors
+        heads, kv_heads, causal, scale, rope_tables, kv_lens = ctx.cfg
+        s, b, nh, d = qkv.shape
+        do_sb = do.reshape(s, b, heads, d)
+        if not do_sb.is_contiguous():
+            do_sb = do_sb.contiguous()
+        dqkv = torch.empty_like(qkv)
+        v = qkv.permute(1, 0, 2, 3)
+        g = dqkv.permute(1, 0, 2, 3)
+        A.attn_bwd_raw(v[:, :, :heads], v[:, :, heads:heads + kv_heads], v[:, :, heads + kv_heads:],
+                       o_sb.permute(1, 0, 2, 3), do_sb.permute(1, 0, 2, 3), lse, causal, scale, kv_lens,
+                       dq=g[:, :, :heads], dk=g[:, :, heads:heads + kv_heads],
+                       dv=g[:, :, heads + kv_heads:])
+        if rope_tables is not None:
+            x = dqkv.view(s * b, nh, d)[:, : heads + kv_heads]
+            E.rope_inplace_raw(x, rope_tables[0], rope_tables[1], s, True, 0, pos_div=b)
+        return dqkv, None, None, None, None, None, None
+
+
+def qkv_attention(qkv, heads, kv_heads, causal, scale, rope_tables=None, kv_lens=None):
+    return _QKVAttention.apply(qkv, heads, kv_heads, causal, scale, rope_tables, kv_lens)
+
+
+class TransformerLayer(nn.Module):
+    """Pre-norm decoder block. `tp` supplies the (possibly fused-collective) linears."""
+
+    def __init__(self, cfg: GPTConfig, tp, layer_idx: int, dtype=torch.bfloat16, device=None):
+        super().__init__()
+        self.cfg, self.tp, self.layer_idx = cfg, tp, layer_idx
+        d = cfg.head_dim
+        assert cfg.heads % tp.world == 0 and cfg.kv_heads % tp.world == 0 and cfg.ffn % tp.world == 0
+        self.h_local = cfg.heads // tp.world
+        self.kv_local = cfg.kv_heads // tp.world
+        ffn_local = cfg.ffn // tp.world
+        kw = dict(dtype=dtype, device=device)
+        H = cfg.hidden
+        self.ln1_w = nn.Parameter(torch.ones(H, **kw))
+        self.ln2_w = nn.Parameter(torch.ones(H, **kw))
+        if cfg.norm == "ln":
+            self.ln1_b = nn.Parameter(torch.zeros(H, **kw))
+            self.ln2_b = nn.Parameter(torch.zeros(H, **kw))
+        else:
+            self.ln1_b = self.ln2_b = None
+        std = cfg.init_std
+        out_std = std / math.sqrt(2.0 * cfg.layers)
+        self.wqkv = nn.Parameter(torch.empty((self.h_local + 2 * self.kv_local) * d, H, **kw).normal_(0, std))
+        self.wo = nn.Parameter(torch.empty(H, self.h_local * d, **kw).normal_(0, out_std))
+        n_up = 2 * ffn_local if cfg.act == "swiglu" else ffn_local
+        self.w1 = nn.Parameter(torch.empty(n_up, H, **kw).normal_(0, std))       # gate|up or fc1
+        self.w2 = nn.Parameter(torch.empty(H, ffn_local, **kw).normal_(0, out_std))
+        if cfg.bias:
+            self.bqkv = nn.Parameter(torch.zeros(self.wqkv.shape[0], **kw))
+            self.bo = nn.Parameter(torch.zeros(H, **kw))
+            self.b1 = nn.Parameter(torch.zeros(n_up, **kw))
+            self.b2 = nn.Parameter(torch.zeros(H, **kw))
+        else:
+            self.bqkv = self.bo = self.b1 = self.b2 = None
+        # parameters replicated across the TP group need their grads all-reduced there
+        for p in (self.ln1_w, self.ln2_w, self.ln1_b, self.ln2_b, self.bo, self.b2):
+            if p is not None:
+                p.tp_replicated = True
+
+    def forward(self, h, seq: int, batch: int, rope_tables=None, kv_lens=None):
+        cfg, tp = self.cfg, self.tp
+        rms = cfg.norm == "rms"
+        d = cfg.head_dim
+        y = N.norm(h, self.ln1_w, self.ln1_b, eps=cfg.eps, rms=rms)
+        qkv = tp.column_linear(y, self.wqkv, self.bqkv)              # [s*b, (h+2kv)*d] full sequence
+        o = qkv_attention(qkv.view(seq, batch, self.h_local + 2 * self.kv_local, d), self.h_local,
+                          self.kv_local, True, 1.0 / math.sqrt(d), rope_tables, kv_lens)
+        h = tp.row_linear(o, self.wo, self.bo, residual=h)           # residual fused in the epilogue
+        y = N.norm(h, self.ln2_w, self.ln2_b, eps=cfg.eps, rms=rms)
+        if cfg.act == "swiglu":
+            a = E.swiglu(tp.column_linear(y, self.w1, self.b1))
+        else:
+            a = tp.column_linear_gelu(y, self.w1, self.b1)
+        h = tp.row_linear(a, self.w2, self.b2, residual=h)
+        return h
+
+
+class Embedding(nn.Module):
+    def __init__(self, cfg: GPTConfig, tp, dtype=torch.bfloat16, device=None):
+        super().__init__()
+        self.cfg, self.tp = cfg, tp
+        kw = dict(dtype=dtype, device=device)
+        self.wte = nn.Parameter(torch.empty(cfg.vocab_size, cfg.hidden, **kw).normal_(0, cfg.init_std))
+        self.wte.tp_replicated = True
+        if cfg.learned_pos:
+            self.wpe = nn.Parameter(torch.empty(cfg.max_seq, cfg.hidden, **kw).normal_(0, cfg.init_std))
+            self.wpe.tp_replicated = True
+        else:
+            self.wpe = None
+
+    def forward(self, tokens):
+        """tokens: [b, s] int64 -> [s*b, hidden] (sequence-major; SP shard taken by tp.scatter)."""
+        b, s = tokens.shape
+        x = torch.nn.functional.embedding(tokens.t().contiguous(), self.wte)  # [s, b, h]
+        if self.wpe is not None:
+            x = x + self.wpe[:s].unsqueeze(1)
+        return self.tp.scatter_sequence(x.view(s * b, self.cfg.hidden))
+
+
+class LMHead(nn.Module):
+    def __init__(self, cfg: GPTConfig, tp, tied_weight=None, dtype=torch.bfloat16, device=None):
+        super().__init__()
+        self.cfg, self.tp = cfg, tp
+        kw = dict(dtype=dtype, device=device)
+        self.lnf_w = nn.Parameter(torch.ones(cfg.hidden, **kw))
+        self.lnf_w.tp_replicated = True
+        if cfg.norm == "ln":
+            self.lnf_b = nn.Parameter(torch.zeros(cfg.hidden, **kw))
+            self.lnf_b.tp_replicated = True
+        else:
+            self.lnf_b = None
+        if tied_weight is not None:
+            self.weight = tied_weight
+        else:
+            assert cfg.vocab_size % tp.world == 0
+            self.weight = nn.Parameter(
+                torch.empty(cfg.vocab_size // tp.world, cfg.hidden, **kw).normal_(0, cfg.init_std))
+
+    def forward(self, h, labels):
+        """h: [tokens(_shard), hidden]; labels: [b, s] -> mean cross-entropy (scalar)."""
+        cfg = self.cfg
+        y = N.norm(h, self.lnf_w, self.lnf_b, eps=cfg.eps, rms=cfg.norm == "rms")
+        tgt = labels.t().contiguous().view(-1)  # sequence-major, matches the activations
+        return self.tp.lm_head_loss(y, self.weight, tgt)
+
+
+class GPTModel(nn.Module):
+    """Full model (or one pipeline stage of it: `layer_range`, `pre`, `post`)."""
+
+    def __init__(self, cfg: GPTConfig, tp=None, layer_range: tuple[int, int] | None = None,
+                 pre: bool = True, post: bool = True, dtype=torch.bfloat16, device=None):
+        super().__init__()
+        from ..parallel.tensor_parallel import SINGLE
+
+        self.cfg = cfg
+        self.tp = tp if tp is not None else SINGLE
+        lo, hi = layer_range if layer_range is not None else (0, cfg.layers)
+        self.layer_range = (lo, hi)
+        self.embed = Embedding(cfg, self.tp, dtype, device) if pre else None
+        self.layers = nn.ModuleList(
+            [TransformerLayer(cfg, self.tp, i, dtype, device) for i in range(lo, hi)])
+        if post:
+            tied = self.embed.wte if (cfg.tie_embeddings and pre) else None
+            self.head = LMHead(cfg, self.tp, tied, dtype, device)
+        else:
+            self.head = None
+        self.recompute = False
+
+    def _rope(self, seq, device):
+        if not self.cfg.rope:
+            return None
+        return E.rope_tables(seq, self.cfg.head_dim, self.cfg.rope_base, device)
+
+    def forward(self, tokens=None, labels=None, hidden=None, seq: int | None = None,
+                batch: int | None = None, kv_lens=None):
+        """First stage takes `tokens`; later stages take `hidden`. Last stage returns the loss."""
+        if self.embed is not None:
+            batch, seq = tokens.shape
+            h = self.embed(tokens)
+        else:
+            h = hidden
+        rope = self._rope(seq, h.device)
+        for layer in self.layers:
+            if self.recompute and torch.is_grad_enabled():
+                h = torch.utils.checkpoint.checkpoint(layer, h, seq, batch, rope, kv_lens,
+                                                      use_reentrant=False)
+            else:
+                h = layer(h, seq, batch, rope, kv_lens)
+        if self.head is not None and labels is not None:
+            return self.head(h, labels)
+        return h

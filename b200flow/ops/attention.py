@@ -1,0 +1,107 @@
+"""K7 — tcgen05 flash attention (csrc/kernels/attention.cu) as an autograd function.
+
+Tensors are ``[batch, seq, heads, head_dim]`` views whose last two dims are packed
+(any token / batch stride), e.g. slices of a fused QKV projection output.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+
+from . import _lib
+from ._lib import c_float, c_int, c_ll, ptr, stream_ptr
+
+
+def _strides(t: torch.Tensor):
+    B, S, H, D = t.shape
+    assert t.stride(3) == 1 and t.stride(2) == D, "heads must be packed: [b, s, h, d] with h*d contiguous"
+    return t.stride(1), t.stride(0)
+
+
+def attn_fwd_raw(q, k, v, causal: bool, scale: float, kv_lens=None):
+    B, S, H, D = q.shape
+    HKV = k.shape[2]
+    o = torch.empty((B, S, H, D), dtype=torch.bfloat16, device=q.device)
+    lse = torch.empty((B, H, S), dtype=torch.float32, device=q.device)
+    (q_ts, q_bs), (k_ts, k_bs), (v_ts, v_bs) = _strides(q), _strides(k), _strides(v)
+    _lib.call("b2f_attn_fwd", ptr(q), ptr(k), ptr(v), ptr(o), ptr(lse), c_int(B), c_int(S), c_int(H),
+              c_int(HKV), c_int(D), c_ll(q_ts), c_ll(q_bs), c_ll(k_ts), c_ll(k_bs), c_ll(v_ts),
+              c_ll(v_bs), c_ll(o.stride(1)), c_ll(o.stride(0)), c_float(scale), c_int(int(causal)),
+              ptr(kv_lens), stream_ptr())
+    _lib.debug_sync()
+    return o, lse
+
+
+def attn_bwd_raw(q, k, v, o, do, lse, causal: bool, scale: float, kv_lens=None, dq=None, dk=None,
+                 dv=None):
+    B, S, H, D = q.shape
+    HKV = k.shape[2]
+    if dq is None:
+        dq = torch.empty((B, S, H, D), dtype=torch.bfloat16, device=q.device)
+    if dk is None:
+        dk = torch.empty((B, S, HKV, D), dtype=torch.bfloat16, device=q.device)
+    if dv is None:
+        dv = torch.empty((B, S, HKV, D), dtype=torch.bfloat16, device=q.device)
+    delta = torch.empty((B, H, S), dtype=torch.float32, device=q.device)
+    if not (do.stride(3) == 1 and do.stride(2) == D):
+        do = do.contiguous()
+    args = []
+    for t in (q, k, v, o, do, dq, dk, dv):
+        ts, bs = _strides(t)
+        args += [c_ll(ts), c_ll(bs)]
+    _lib.call("b2f_attn_bwd", ptr(q), ptr(k), ptr(v), ptr(o), ptr(do), ptr(lse), ptr(delta), ptr(dq),
+              ptr(dk), ptr(dv), c_int(B), c_int(S), c_int(H), c_int(HKV), c_int(D), *args,
+              c_float(scale), c_int(int(causal)), ptr(kv_lens), stream_ptr())
+    _lib.debug_sync()
+    return dq, dk, dv
+
+
+class _FlashAttn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, q, k, v, causal, scale, kv_lens):
+        _lib.require_cuda(q, k, v)
+        o, lse = attn_fwd_raw(q, k, v, causal, scale, kv_lens)
+        ctx.save_for_backward(q, k, v, o, lse)
+        ctx.causal, ctx.scale, ctx.kv_lens = causal, scale, kv_lens
+        return o
+
+    @staticmethod
+    def backward(ctx, do):
+        q, k, v, o, lse = ctx.saved_tensors
+        dq, dk, dv = attn_bwd_raw(q, k, v, o, do, lse, ctx.causal, ctx.scale, ctx.kv_lens)
+        return dq, dk, dv, None, None, None
+
+
+def flash_attention(q, k, v, causal: bool = True, scale: float | None = None, kv_lens=None):
+    """softmax(scale * q kᵀ [+ causal / key-length mask]) v, O(seq) memory."""
+    if scale is None:
+        scale = 1.0 / math.sqrt(q.shape[-1])
+    return _FlashAttn.apply(q, k, v, causal, float(scale), kv_lens)
+
+
+class _FlashAttnPackedQKV(torch.autograd.Function):
+    """qkv: [b, s, 3, h, d] (one GEMM output). The backward writes dq/dk/dv straight into one
+    [b, s, 3, h, d] buffer so the QKV-projection dgrad/wgrad GEMMs consume it without a concat."""
+
+    @staticmethod
+    def forward(ctx, qkv, causal, scale, kv_lens):
+        q, k, v = qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2]
+        o, lse = attn_fwd_raw(q, k, v, causal, scale, kv_lens)
+        ctx.save_for_backward(qkv, o, lse)
+        ctx.causal, ctx.scale, ctx.kv_lens = causal, scale, kv_lens
+        return o
+
+    @staticmethod
+    def backward(ctx, do):
+        qkv, o, lse = ctx.saved_tensors
+        dqkv = torch.empty_like(qkv)
+        attn_bwd_raw(qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2], o, do, lse, ctx.causal, ctx.scale,
+                     ctx.kv_lens, dq=dqkv[:, :, 0], dk=dqkv[:, :, 1], dv=dqkv[:, :, 2])
+        return dqkv, None, None, None
+
+
+def flash_attention_qkvpacked(qkv, causal: bool = True, scale: float | None = None, kv_lens=None):
+    if scale is None:
+        scale = 1.0 / math.sqrt(qkv.shape[-1])
+    return _FlashAttnPackedQKV.apply(qkv, causal, float(scale), kv_lens)

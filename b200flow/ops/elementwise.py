@@ -122,12 +122,15 @@ def rope_tables(seq: int, dim: int, base: float, device) -> tuple[torch.Tensor, 
     return _rope_cache[key]
 
 
-def rope_inplace_raw(x: torch.Tensor, cos_t, sin_t, seq: int, backward: bool, pos_offset: int = 0):
-    """x: [tokens, heads, d] view with contiguous last two dims; rotated in place."""
+def rope_inplace_raw(x: torch.Tensor, cos_t, sin_t, seq: int, backward: bool, pos_offset: int = 0,
+                     pos_div: int = 1):
+    """x: [tokens, heads, d] view with contiguous last two dims; rotated in place.
+    Token t sits at position (t // pos_div) % seq + pos_offset."""
     tokens, nh, d = x.shape
     assert x.stride(2) == 1 and x.stride(1) == d
     _lib.call("b2f_rope", ptr(x), ptr(cos_t), ptr(sin_t), c_ll(tokens), c_int(seq), c_int(nh),
-              c_int(d), c_ll(x.stride(0)), c_int(pos_offset), c_int(int(backward)), stream_ptr())
+              c_int(d), c_ll(x.stride(0)), c_int(pos_offset), c_int(pos_div), c_int(int(backward)),
+              stream_ptr())
 
 
 class _Rope(torch.autograd.Function):

@@ -15,7 +15,19 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
+// cuTensorMapEncodeTiled needs a current driver context; threads that have only
+// ever been handed work by another thread (e.g. autograd workers) may not have
+// one yet, so bind the primary context once per thread.
+static void ensure_context() {
+  static thread_local bool ready = false;
+  if (!ready) {
+    cudaFree(nullptr);
+    ready = true;
+  }
+}
+
 static EncodeTiledFn get_encode() {
+  ensure_context();
   static EncodeTiledFn fn = nullptr;
   static std::once_flag once;
   std::call_once(once, [] {

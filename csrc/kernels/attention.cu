@@ -1,0 +1,772 @@
+// b200flow K7 — flash attention forward + backward on tcgen05 / TMEM (sm_100a).
+//
+// Layout: q/k/v/o are [batch, seq, heads, D] views (token stride and batch stride
+// free, heads packed, D in {64, 128}), so the kernels read straight out of a
+// fused QKV projection buffer.  128x128 score tiles.
+//
+// Forward (one CTA per 128 query rows of one head): warp 0 = TMA producer,
+// warp 1 = MMA issuer, warps 2-5 = softmax (one query row per thread, no
+// cross-thread reductions).  S = Q K^T lands in one of two TMEM score buffers;
+// the softmax threads turn it into bf16 probabilities *in place in TMEM* and
+// the P V product consumes them as a TMEM A-operand (tcgen05.mma TS form), so P
+// never touches shared memory.  The next tile's Q K^T is issued before the
+// current P V, which keeps the tensor core busy during the exponentials.
+//
+// Backward is two kernels that recompute P from the saved log-sum-exp:
+//   dQ  kernel (CTA per query tile):  S, dP -> dS in TMEM -> dQ += dS K
+//   dKV kernel (CTA per key tile):    S^T, dP^T -> P^T, dS^T in TMEM ->
+//                                     dV += P^T dO ; dK += dS^T Q
+// Both keep their accumulators in TMEM for the whole loop: no atomics, and the
+// result is deterministic.
+//
+// Capability parity: flash-attn v2 / Megatron scaled_(upper_triang_)masked_softmax
+// attention core.
+#include "../common/ptx.cuh"
+#include "../common/host.h"
+#include "../../include/b200flow.h"
+
+using namespace b2f;
+
+namespace {
+
+constexpr int TQ = 128;           // rows per tile (queries or keys)
+constexpr int CHUNK_B = 128 * 128;  // one 128-row x 64-col bf16 chunk, 128 B rows = 16 KB
+constexpr int ATT_THREADS = 192;
+constexpr float LOG2E = 1.4426950408889634f;
+constexpr float LN2 = 0.6931471805599453f;
+
+struct AttnParams {
+  int B, H, HKV, S;
+  float scale, scale_log2;
+  int causal;
+  const int* kv_lens;  // [B] valid key length per batch row, or null
+  // forward output / backward inputs
+  __nv_bfloat16* O;
+  long long o_ts, o_bs;
+  float* lse;    // [B, H, S] natural-log LSE (+inf for rows with no valid key)
+  float* delta;  // [B, H, S] rowsum(dO * O)
+  // backward outputs
+  __nv_bfloat16 *dQ, *dK, *dV;
+  long long dq_ts, dq_bs, dk_ts, dk_bs, dv_ts, dv_bs;
+};
+
+template <int D>
+struct Cfg {
+  static constexpr int CHUNKS = D / 64;
+  static constexpr int TILE_B = TQ * D * 2;
+};
+
+// K-major operand (rows = M/N index, contraction along the 128 B rows).
+__device__ __forceinline__ uint64_t desc_k(uint32_t tile, int k) {
+  return make_smem_desc_sw128(tile + (k >> 2) * CHUNK_B + (k & 3) * 32, 16, 1024);
+}
+// MN-major operand (rows = contraction index, 16 rows per UMMA_K step).
+__device__ __forceinline__ uint64_t desc_mn(uint32_t tile, int k) {
+  return make_smem_desc_sw128(tile + k * 2048, CHUNK_B, 1024);
+}
+
+template <int D>
+__device__ __forceinline__ void load_tile(uint8_t* dst, const CUtensorMap* m, uint64_t* bar,
+                                          int row0, int head, int batch) {
+#pragma unroll
+  for (int c = 0; c < D / 64; ++c) tma_load_4d(dst + c * CHUNK_B, m, bar, c * 64, head, row0, batch);
+}
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+__device__ __forceinline__ uint8_t* align1024(uint8_t* p) {
+  return reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(p) + 1023) &
+                                    ~static_cast<uintptr_t>(1023));
+}
+
+// ============================================================== forward
+struct FwdBars {
+  uint64_t q_full, k_full[2], v_full[2], kv_empty[2], s_full[2], p_full, o_full;
+  uint32_t tmem_base;
+};
+
+template <int D>
+__global__ void __launch_bounds__(ATT_THREADS, 1)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
+                const __grid_constant__ CUtensorMap mv, const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align1024(smem_raw);
+  constexpr int TILE_B = Cfg<D>::TILE_B;
+  uint8_t* sQ = smem;
+  uint8_t* sK = smem + TILE_B;          // 2 stages
+  uint8_t* sV = smem + 3 * TILE_B;      // 2 stages
+  FwdBars* bars = reinterpret_cast<FwdBars*>(smem + 5 * TILE_B);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nq = (p.S + TQ - 1) / TQ;
+  const int q_tile = p.causal ? nq - 1 - (int)blockIdx.x : (int)blockIdx.x;
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int hkv = h / (p.H / p.HKV);
+  const int q0 = q_tile * TQ;
+  int kv_len = p.kv_lens ? p.kv_lens[b] : p.S;
+  kv_len = kv_len < p.S ? kv_len : p.S;
+  int kv_end = p.causal ? (kv_len < q0 + TQ ? kv_len : q0 + TQ) : kv_len;
+  int n = (kv_end + TQ - 1) / TQ;
+  if (n < 1) n = 1;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&mq); tma_prefetch_desc(&mk); tma_prefetch_desc(&mv);
+    mbar_init(&bars->q_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bars->k_full[i], 1);
+      mbar_init(&bars->v_full[i], 1);
+      mbar_init(&bars->kv_empty[i], 1);
+      mbar_init(&bars->s_full[i], 1);
+    }
+    mbar_init(&bars->p_full, 128);
+    mbar_init(&bars->o_full, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(&bars->tmem_base, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = bars->tmem_base;
+  const uint32_t T_S = tmem, T_O = tmem + 256;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_arrive_expect_tx(&bars->q_full, TILE_B);
+      load_tile<D>(sQ, &mq, &bars->q_full, q0, h, b);
+      int st = 0;
+      uint32_t ph = 0;
+      for (int j = 0; j < n; ++j) {
+        mbar_wait(&bars->kv_empty[st], ph ^ 1);
+        mbar_arrive_expect_tx(&bars->k_full[st], TILE_B);
+        load_tile<D>(sK + st * TILE_B, &mk, &bars->k_full[st], j * TQ, hkv, b);
+        mbar_arrive_expect_tx(&bars->v_full[st], TILE_B);
+        load_tile<D>(sV + st * TILE_B, &mv, &bars->v_full[st], j * TQ, hkv, b);
+        st ^= 1;
+        if (st == 0) ph ^= 1;
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc_s = make_idesc(1, 1, 128, 128, 0, 0);
+      const uint32_t idesc_pv = make_idesc(1, 1, 128, D, 0, 1);
+      const uint32_t aQ = smem_u32(sQ);
+      mbar_wait(&bars->q_full, 0);
+      auto issue_s = [&](int j) {
+        const int st = j & 1;
+        mbar_wait(&bars->k_full[st], (j >> 1) & 1);
+        tc_fence_after();
+        const uint32_t aK = smem_u32(sK + st * TILE_B);
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k)
+          umma_f16_ss(T_S + st * 128, desc_k(aQ, k), desc_k(aK, k), idesc_s, k > 0);
+        umma_commit(&bars->s_full[st]);
+      };
+      issue_s(0);
+      for (int j = 0; j < n; ++j) {
+        if (j + 1 < n) issue_s(j + 1);
+        const int st = j & 1;
+        mbar_wait(&bars->p_full, j & 1);
+        mbar_wait(&bars->v_full[st], (j >> 1) & 1);
+        tc_fence_after();
+        const uint32_t aV = smem_u32(sV + st * TILE_B);
+#pragma unroll
+        for (int k = 0; k < TQ / 16; ++k)
+          umma_f16_ts(T_O, T_S + st * 128 + k * 8, desc_mn(aV, k), idesc_pv, k > 0);
+        umma_commit(&bars->kv_empty[st]);
+        umma_commit(&bars->o_full);
+      }
+    }
+    __syncwarp();
+  } else {
+    const int qw = warp & 3;
+    const int r = qw * 32 + lane;
+    const int qi = q0 + r;
+    const uint32_t lane_base = static_cast<uint32_t>(qw * 32) << 16;
+    float m = -INFINITY, l = 0.f;
+    float o[D];
+#pragma unroll
+    for (int i = 0; i < D; ++i) o[i] = 0.f;
+    for (int j = 0; j < n; ++j) {
+      const int st = j & 1;
+      const int kv0 = j * TQ;
+      mbar_wait(&bars->s_full[st], (j >> 1) & 1);
+      tc_fence_after();
+      const uint32_t sbuf = T_S + lane_base + st * 128;
+      const bool need_mask = (p.causal && kv0 + TQ - 1 > q0) || (kv0 + TQ > kv_len);
+      // limit: first masked key index for this row
+      int lim = kv_len;
+      if (p.causal && qi + 1 < lim) lim = qi + 1;
+      float mx = -INFINITY;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t acc[32];
+        tmem_ld_32x32b_x32(sbuf + c * 32, acc);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          float s = __uint_as_float(acc[i]);
+          if (need_mask && kv0 + c * 32 + i >= lim) s = -INFINITY;
+          mx = fmaxf(mx, s);
+        }
+      }
+      const float m_new = fmaxf(m, mx * p.scale_log2);
+      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+      const float alpha = ex2(m - m_use);
+      if (j > 0) {
+        mbar_wait(&bars->o_full, (j - 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < D / 32; ++c) {
+          uint32_t acc[32];
+          tmem_ld_32x32b_x32(T_O + lane_base + c * 32, acc);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) o[c * 32 + i] = (o[c * 32 + i] + __uint_as_float(acc[i])) * alpha;
+        }
+      }
+      float rowsum = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t acc[32];
+        tmem_ld_32x32b_x32(sbuf + c * 32, acc);
+        tmem_ld_wait();
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          float p0 = ex2(__uint_as_float(acc[2 * i]) * p.scale_log2 - m_use);
+          float p1 = ex2(__uint_as_float(acc[2 * i + 1]) * p.scale_log2 - m_use);
+          if (need_mask) {
+            if (kv0 + c * 32 + 2 * i >= lim) p0 = 0.f;
+            if (kv0 + c * 32 + 2 * i + 1 >= lim) p1 = 0.f;
+          }
+          rowsum += p0 + p1;
+          pk[i] = pack_bf16x2(p0, p1);
+        }
+        tmem_st_32x32b_x16(sbuf + c * 16, pk);
+      }
+      l = l * alpha + rowsum;
+      m = m_new;
+      tmem_st_wait();
+      tc_fence_before();
+      mbar_arrive(&bars->p_full);
+    }
+    mbar_wait(&bars->o_full, (n - 1) & 1);
+    tc_fence_after();
+    const float inv = l > 0.f ? 1.f / l : 0.f;
+    __nv_bfloat16* orow = p.O + (long long)b * p.o_bs + (long long)qi * p.o_ts + (long long)h * D;
+#pragma unroll
+    for (int c = 0; c < D / 32; ++c) {
+      uint32_t acc[32];
+      tmem_ld_32x32b_x32(T_O + lane_base + c * 32, acc);
+      tmem_ld_wait();
+      if (qi < p.S) {
+#pragma unroll
+        for (int q4 = 0; q4 < 4; ++q4) {
+          uint4 u;
+          float f[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            f[i] = (o[c * 32 + q4 * 8 + i] + __uint_as_float(acc[q4 * 8 + i])) * inv;
+          u.x = pack_bf16x2(f[0], f[1]); u.y = pack_bf16x2(f[2], f[3]);
+          u.z = pack_bf16x2(f[4], f[5]); u.w = pack_bf16x2(f[6], f[7]);
+          *reinterpret_cast<uint4*>(orow + c * 32 + q4 * 8) = u;
+        }
+      }
+    }
+    if (qi < p.S && p.lse)
+      p.lse[((long long)b * p.H + h) * p.S + qi] = l > 0.f ? (m * LN2 + __logf(l)) : INFINITY;
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 512);
+  }
+}
+
+// ============================================================== backward
+// delta[b,h,s] = sum_d O[b,s,h,d] * dO[b,s,h,d]
+template <int D>
+__global__ void __launch_bounds__(256)
+attn_delta_kernel(const __nv_bfloat16* __restrict__ O, long long o_ts, long long o_bs,
+                  const __nv_bfloat16* __restrict__ dO, long long do_ts, long long do_bs,
+                  float* __restrict__ delta, int B, int H, int S) {
+  constexpr int TPR = D / 8;  // threads per row
+  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long row = gid / TPR;  // over B*S*H (token-major, then head)
+  const int part = (int)(gid % TPR);
+  const long long total = (long long)B * S * H;
+  float acc = 0.f;
+  if (row < total) {
+    const int h = (int)(row % H);
+    const long long tok = row / H;
+    const int s = (int)(tok % S);
+    const int b = (int)(tok / S);
+    const uint4 a = *reinterpret_cast<const uint4*>(O + b * o_bs + (long long)s * o_ts + (long long)h * D + part * 8);
+    const uint4 g = *reinterpret_cast<const uint4*>(dO + b * do_bs + (long long)s * do_ts + (long long)h * D + part * 8);
+    float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y), a2 = unpack_bf16x2(a.z), a3 = unpack_bf16x2(a.w);
+    float2 g0 = unpack_bf16x2(g.x), g1 = unpack_bf16x2(g.y), g2 = unpack_bf16x2(g.z), g3 = unpack_bf16x2(g.w);
+    acc = a0.x * g0.x + a0.y * g0.y + a1.x * g1.x + a1.y * g1.y + a2.x * g2.x + a2.y * g2.y +
+          a3.x * g3.x + a3.y * g3.y;
+  }
+#pragma unroll
+  for (int o = TPR / 2; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if (row < total && part == 0) {
+    const int h = (int)(row % H);
+    const long long tok = row / H;
+    const int s = (int)(tok % S);
+    const int b = (int)(tok / S);
+    delta[((long long)b * H + h) * S + s] = acc;
+  }
+}
+
+struct BwdBars {
+  uint64_t fixed_full, st_full[2], st_empty[2], s_full, ds_full, acc_full;
+  uint32_t tmem_base;
+  float lse2[128];
+  float dlt[128];
+};
+
+// ---- dQ: CTA per (q tile, head, batch); loops over key tiles.
+template <int D>
+__global__ void __launch_bounds__(ATT_THREADS, 1)
+attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
+                   const __grid_constant__ CUtensorMap mv, const __grid_constant__ CUtensorMap mdo,
+                   const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align1024(smem_raw);
+  constexpr int TILE_B = Cfg<D>::TILE_B;
+  uint8_t* sQ = smem;
+  uint8_t* sdO = smem + TILE_B;
+  uint8_t* sK = smem + 2 * TILE_B;  // 2 stages
+  uint8_t* sV = smem + 4 * TILE_B;  // 2 stages
+  BwdBars* bars = reinterpret_cast<BwdBars*>(smem + 6 * TILE_B);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nq = (p.S + TQ - 1) / TQ;
+  const int q_tile = p.causal ? nq - 1 - (int)blockIdx.x : (int)blockIdx.x;
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int hkv = h / (p.H / p.HKV);
+  const int q0 = q_tile * TQ;
+  int kv_len = p.kv_lens ? p.kv_lens[b] : p.S;
+  kv_len = kv_len < p.S ? kv_len : p.S;
+  int kv_end = p.causal ? (kv_len < q0 + TQ ? kv_len : q0 + TQ) : kv_len;
+  int n = (kv_end + TQ - 1) / TQ;
+  if (n < 1) n = 1;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&mq); tma_prefetch_desc(&mk); tma_prefetch_desc(&mv); tma_prefetch_desc(&mdo);
+    mbar_init(&bars->fixed_full, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(&bars->st_full[i], 1); mbar_init(&bars->st_empty[i], 1); }
+    mbar_init(&bars->s_full, 1);
+    mbar_init(&bars->ds_full, 128);
+    mbar_init(&bars->acc_full, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) { tmem_alloc(&bars->tmem_base, 512); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = bars->tmem_base;
+  const uint32_t T_S = tmem, T_DP = tmem + 128, T_DQ = tmem + 256;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_arrive_expect_tx(&bars->fixed_full, 2 * TILE_B);
+      load_tile<D>(sQ, &mq, &bars->fixed_full, q0, h, b);
+      load_tile<D>(sdO, &mdo, &bars->fixed_full, q0, h, b);
+      int st = 0;
+      uint32_t ph = 0;
+      for (int j = 0; j < n; ++j) {
+        mbar_wait(&bars->st_empty[st], ph ^ 1);
+        mbar_arrive_expect_tx(&bars->st_full[st], 2 * TILE_B);
+        load_tile<D>(sK + st * TILE_B, &mk, &bars->st_full[st], j * TQ, hkv, b);
+        load_tile<D>(sV + st * TILE_B, &mv, &bars->st_full[st], j * TQ, hkv, b);
+        st ^= 1;
+        if (st == 0) ph ^= 1;
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc_s = make_idesc(1, 1, 128, 128, 0, 0);
+      const uint32_t idesc_dq = make_idesc(1, 1, 128, D, 0, 1);
+      const uint32_t aQ = smem_u32(sQ), adO = smem_u32(sdO);
+      mbar_wait(&bars->fixed_full, 0);
+      auto issue_sdp = [&](int j) {
+        const int st = j & 1;
+        mbar_wait(&bars->st_full[st], (j >> 1) & 1);
+        tc_fence_after();
+        const uint32_t aK = smem_u32(sK + st * TILE_B), aV = smem_u32(sV + st * TILE_B);
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k) umma_f16_ss(T_S, desc_k(aQ, k), desc_k(aK, k), idesc_s, k > 0);
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k) umma_f16_ss(T_DP, desc_k(adO, k), desc_k(aV, k), idesc_s, k > 0);
+        umma_commit(&bars->s_full);
+      };
+      issue_sdp(0);
+      for (int j = 0; j < n; ++j) {
+        const int st = j & 1;
+        mbar_wait(&bars->ds_full, j & 1);
+        tc_fence_after();
+        const uint32_t aK = smem_u32(sK + st * TILE_B);
+#pragma unroll
+        for (int k = 0; k < TQ / 16; ++k)
+          umma_f16_ts(T_DQ, T_S + k * 8, desc_mn(aK, k), idesc_dq, (j | k) != 0);
+        umma_commit(&bars->st_empty[st]);
+        if (j + 1 < n) issue_sdp(j + 1);
+      }
+      umma_commit(&bars->acc_full);
+    }
+    __syncwarp();
+  } else {
+    const int qw = warp & 3;
+    const int r = qw * 32 + lane;
+    const int qi = q0 + r;
+    const uint32_t lane_base = static_cast<uint32_t>(qw * 32) << 16;
+    const long long sidx = ((long long)b * p.H + h) * p.S + qi;
+    const float lse2 = qi < p.S ? p.lse[sidx] * LOG2E : INFINITY;
+    const float dlt = qi < p.S ? p.delta[sidx] : 0.f;
+    for (int j = 0; j < n; ++j) {
+      const int kv0 = j * TQ;
+      mbar_wait(&bars->s_full, j & 1);
+      tc_fence_after();
+      const bool need_mask = (p.causal && kv0 + TQ - 1 > q0) || (kv0 + TQ > kv_len);
+      int lim = kv_len;
+      if (p.causal && qi + 1 < lim) lim = qi + 1;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t sa[32], da[32];
+        tmem_ld_32x32b_x32(T_S + lane_base + c * 32, sa);
+        tmem_ld_32x32b_x32(T_DP + lane_base + c * 32, da);
+        tmem_ld_wait();
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          float p0 = ex2(__uint_as_float(sa[2 * i]) * p.scale_log2 - lse2);
+          float p1 = ex2(__uint_as_float(sa[2 * i + 1]) * p.scale_log2 - lse2);
+          if (need_mask) {
+            if (kv0 + c * 32 + 2 * i >= lim) p0 = 0.f;
+            if (kv0 + c * 32 + 2 * i + 1 >= lim) p1 = 0.f;
+          }
+          const float d0 = p0 * (__uint_as_float(da[2 * i]) - dlt) * p.scale;
+          const float d1 = p1 * (__uint_as_float(da[2 * i + 1]) - dlt) * p.scale;
+          pk[i] = pack_bf16x2(d0, d1);
+        }
+        tmem_st_32x32b_x16(T_S + lane_base + c * 16, pk);
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      mbar_arrive(&bars->ds_full);
+    }
+    mbar_wait(&bars->acc_full, 0);
+    tc_fence_after();
+    __nv_bfloat16* drow = p.dQ + (long long)b * p.dq_bs + (long long)qi * p.dq_ts + (long long)h * D;
+#pragma unroll
+    for (int c = 0; c < D / 32; ++c) {
+      uint32_t acc[32];
+      tmem_ld_32x32b_x32(T_DQ + lane_base + c * 32, acc);
+      tmem_ld_wait();
+      if (qi < p.S) {
+#pragma unroll
+        for (int q4 = 0; q4 < 4; ++q4) {
+          uint4 u;
+          u.x = pack_bf16x2(__uint_as_float(acc[q4 * 8 + 0]), __uint_as_float(acc[q4 * 8 + 1]));
+          u.y = pack_bf16x2(__uint_as_float(acc[q4 * 8 + 2]), __uint_as_float(acc[q4 * 8 + 3]));
+          u.z = pack_bf16x2(__uint_as_float(acc[q4 * 8 + 4]), __uint_as_float(acc[q4 * 8 + 5]));
+          u.w = pack_bf16x2(__uint_as_float(acc[q4 * 8 + 6]), __uint_as_float(acc[q4 * 8 + 7]));
+          *reinterpret_cast<uint4*>(drow + c * 32 + q4 * 8) = u;
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem, 512); }
+}
+
+// ---- dK/dV: CTA per (key tile, kv head, batch); loops over the query heads of
+// the group and over query tiles.
+template <int D>
+__global__ void __launch_bounds__(ATT_THREADS, 1)
+attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
+                    const __grid_constant__ CUtensorMap mv, const __grid_constant__ CUtensorMap mdo,
+                    const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align1024(smem_raw);
+  constexpr int TILE_B = Cfg<D>::TILE_B;
+  uint8_t* sK = smem;
+  uint8_t* sV = smem + TILE_B;
+  uint8_t* sQ = smem + 2 * TILE_B;   // 2 stages
+  uint8_t* sdO = smem + 4 * TILE_B;  // 2 stages
+  BwdBars* bars = reinterpret_cast<BwdBars*>(smem + 6 * TILE_B);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nq = (p.S + TQ - 1) / TQ;
+  const int kv_tile = blockIdx.x;
+  const int hkv = blockIdx.y, b = blockIdx.z;
+  const int G = p.H / p.HKV;
+  const int kv0 = kv_tile * TQ;
+  int kv_len = p.kv_lens ? p.kv_lens[b] : p.S;
+  kv_len = kv_len < p.S ? kv_len : p.S;
+  const int i0 = p.causal ? kv_tile : 0;
+  const int per_head = nq - i0;
+  const int n = per_head * G;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&mq); tma_prefetch_desc(&mk); tma_prefetch_desc(&mv); tma_prefetch_desc(&mdo);
+    mbar_init(&bars->fixed_full, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(&bars->st_full[i], 1); mbar_init(&bars->st_empty[i], 1); }
+    mbar_init(&bars->s_full, 1);
+    mbar_init(&bars->ds_full, 128);
+    mbar_init(&bars->acc_full, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) { tmem_alloc(&bars->tmem_base, 512); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = bars->tmem_base;
+  const uint32_t T_S = tmem, T_DP = tmem + 128, T_DV = tmem + 256, T_DK = tmem + 256 + D;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_arrive_expect_tx(&bars->fixed_full, 2 * TILE_B);
+      load_tile<D>(sK, &mk, &bars->fixed_full, kv0, hkv, b);
+      load_tile<D>(sV, &mv, &bars->fixed_full, kv0, hkv, b);
+      int st = 0;
+      uint32_t ph = 0;
+      for (int it = 0; it < n; ++it) {
+        const int g = it / per_head, i = i0 + it % per_head;
+        const int h = hkv * G + g;
+        mbar_wait(&bars->st_empty[st], ph ^ 1);
+        mbar_arrive_expect_tx(&bars->st_full[st], 2 * TILE_B);
+        load_tile<D>(sQ + st * TILE_B, &mq, &bars->st_full[st], i * TQ, h, b);
+        load_tile<D>(sdO + st * TILE_B, &mdo, &bars->st_full[st], i * TQ, h, b);
+        st ^= 1;
+        if (st == 0) ph ^= 1;
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc_s = make_idesc(1, 1, 128, 128, 0, 0);
+      const uint32_t idesc_acc = make_idesc(1, 1, 128, D, 0, 1);
+      const uint32_t aK = smem_u32(sK), aV = smem_u32(sV);
+      mbar_wait(&bars->fixed_full, 0);
+      auto issue_sdp = [&](int it) {
+        const int st = it & 1;
+        mbar_wait(&bars->st_full[st], (it >> 1) & 1);
+        tc_fence_after();
+        const uint32_t aQ = smem_u32(sQ + st * TILE_B), adO = smem_u32(sdO + st * TILE_B);
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k) umma_f16_ss(T_S, desc_k(aK, k), desc_k(aQ, k), idesc_s, k > 0);
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k) umma_f16_ss(T_DP, desc_k(aV, k), desc_k(adO, k), idesc_s, k > 0);
+        umma_commit(&bars->s_full);
+      };
+      if (n > 0) issue_sdp(0);
+      for (int it = 0; it < n; ++it) {
+        const int st = it & 1;
+        mbar_wait(&bars->ds_full, it & 1);
+        tc_fence_after();
+        const uint32_t aQ = smem_u32(sQ + st * TILE_B), adO = smem_u32(sdO + st * TILE_B);
+#pragma unroll
+        for (int k = 0; k < TQ / 16; ++k)
+          umma_f16_ts(T_DV, T_S + k * 8, desc_mn(adO, k), idesc_acc, (it | k) != 0);
+#pragma unroll
+        for (int k = 0; k < TQ / 16; ++k)
+          umma_f16_ts(T_DK, T_DP + k * 8, desc_mn(aQ, k), idesc_acc, (it | k) != 0);
+        umma_commit(&bars->st_empty[st]);
+        if (it + 1 < n) issue_sdp(it + 1);
+      }
+      umma_commit(&bars->acc_full);
+    }
+    __syncwarp();
+  } else {
+    const int qw = warp & 3;
+    const int r = qw * 32 + lane;
+    const int t = threadIdx.x - 64;  // 0..127 among the softmax threads
+    const int ki = kv0 + r;
+    const uint32_t lane_base = static_cast<uint32_t>(qw * 32) << 16;
+    for (int it = 0; it < n; ++it) {
+      const int g = it / per_head, i = i0 + it % per_head;
+      const int h = hkv * G + g;
+      const int q0 = i * TQ;
+      named_bar_sync(1, 128);
+      {
+        const int qi = q0 + t;
+        const long long sidx = ((long long)b * p.H + h) * p.S + qi;
+        bars->lse2[t] = qi < p.S ? p.lse[sidx] * LOG2E : INFINITY;
+        bars->dlt[t] = qi < p.S ? p.delta[sidx] : 0.f;
+      }
+      named_bar_sync(1, 128);
+      mbar_wait(&bars->s_full, it & 1);
+      tc_fence_after();
+      const bool row_dead = ki >= kv_len;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t sa[32], da[32];
+        tmem_ld_32x32b_x32(T_S + lane_base + c * 32, sa);
+        tmem_ld_32x32b_x32(T_DP + lane_base + c * 32, da);
+        tmem_ld_wait();
+        uint32_t pp[16], pd[16];
+#pragma unroll
+        for (int i2 = 0; i2 < 16; ++i2) {
+          const int c0 = c * 32 + 2 * i2;
+          float p0 = ex2(__uint_as_float(sa[2 * i2]) * p.scale_log2 - bars->lse2[c0]);
+          float p1 = ex2(__uint_as_float(sa[2 * i2 + 1]) * p.scale_log2 - bars->lse2[c0 + 1]);
+          if (row_dead || (p.causal && q0 + c0 < ki)) p0 = 0.f;
+          if (row_dead || (p.causal && q0 + c0 + 1 < ki)) p1 = 0.f;
+          const float d0 = p0 * (__uint_as_float(da[2 * i2]) - bars->dlt[c0]) * p.scale;
+          const float d1 = p1 * (__uint_as_float(da[2 * i2 + 1]) - bars->dlt[c0 + 1]) * p.scale;
+          pp[i2] = pack_bf16x2(p0, p1);
+          pd[i2] = pack_bf16x2(d0, d1);
+        }
+        tmem_st_32x32b_x16(T_S + lane_base + c * 16, pp);
+        tmem_st_32x32b_x16(T_DP + lane_base + c * 16, pd);
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      mbar_arrive(&bars->ds_full);
+    }
+    mbar_wait(&bars->acc_full, 0);
+    tc_fence_after();
+    __nv_bfloat16* vrow = p.dV + (long long)b * p.dv_bs + (long long)ki * p.dv_ts + (long long)hkv * D;
+    __nv_bfloat16* krow = p.dK + (long long)b * p.dk_bs + (long long)ki * p.dk_ts + (long long)hkv * D;
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {
+      __nv_bfloat16* orow = which ? krow : vrow;
+      const uint32_t tb = which ? T_DK : T_DV;
+#pragma unroll
+      for (int c = 0; c < D / 32; ++c) {
+        uint32_t acc[32];
+        if (n > 0) {
+          tmem_ld_32x32b_x32(tb + lane_base + c * 32, acc);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int i2 = 0; i2 < 32; ++i2) acc[i2] = 0u;
+        }
+        if (ki < p.S) {
+#pragma unroll
+          for (int q4 = 0; q4 < 4; ++q4) {
+            uint4 u;
+            u.x = pack_bf16x2(__uint_as_float(acc[q4 * 8 + 0]), __uint_as_float(acc[q4 * 8 + 1]));
+            u.y = pack_bf16x2(__uint_as_float(acc[q4 * 8 + 2]), __uint_as_float(acc[q4 * 8 + 3]));
+            u.z = pack_bf16x2(__uint_as_float(acc[q4 * 8 + 4]), __uint_as_float(acc[q4 * 8 + 5]));
+            u.w = pack_bf16x2(__uint_as_float(acc[q4 * 8 + 6]), __uint_as_float(acc[q4 * 8 + 7]));
+            *reinterpret_cast<uint4*>(orow + c * 32 + q4 * 8) = u;
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem, 512); }
+}
+
+int make_map(CUtensorMap* m, const void* ptr, int B, int S, int heads, int D, long long ts,
+             long long bs) {
+  return make_tma_4d(m, ptr, TmaDtype::BF16, B, heads, S, D, bs, D, ts, TQ, 64, 128);
+}
+
+template <typename K>
+int set_smem(K kernel, int bytes) {
+  B2F_CHECK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  return 0;
+}
+
+int check_common(int B, int S, int H, int HKV, int D) {
+  B2F_REQUIRE(D == 64 || D == 128, "attention: head dim must be 64 or 128");
+  B2F_REQUIRE(B > 0 && S > 0 && H > 0 && HKV > 0 && H % HKV == 0, "attention: bad shape");
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int b2f_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B,
+                            int S, int H, int HKV, int D, long long q_ts, long long q_bs,
+                            long long k_ts, long long k_bs, long long v_ts, long long v_bs,
+                            long long o_ts, long long o_bs, float scale, int causal,
+                            const int* kv_lens, void* stream) {
+  if (int rc = check_common(B, S, H, HKV, D)) return rc;
+  B2F_REQUIRE((reinterpret_cast<uintptr_t>(o) & 15) == 0 && o_ts % 8 == 0 && o_bs % 8 == 0,
+              "attention: output must be 16-byte aligned");
+  CUtensorMap mq, mk, mv;
+  if (int rc = make_map(&mq, q, B, S, H, D, q_ts, q_bs)) return rc;
+  if (int rc = make_map(&mk, k, B, S, HKV, D, k_ts, k_bs)) return rc;
+  if (int rc = make_map(&mv, v, B, S, HKV, D, v_ts, v_bs)) return rc;
+  AttnParams p{};
+  p.B = B; p.H = H; p.HKV = HKV; p.S = S;
+  p.scale = scale; p.scale_log2 = scale * LOG2E; p.causal = causal; p.kv_lens = kv_lens;
+  p.O = static_cast<__nv_bfloat16*>(o); p.o_ts = o_ts; p.o_bs = o_bs; p.lse = lse;
+  dim3 grid((S + TQ - 1) / TQ, H, B);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (D == 128) {
+    const int smem = 5 * Cfg<128>::TILE_B + 1024 + sizeof(FwdBars);
+    if (int rc = set_smem(attn_fwd_kernel<128>, smem)) return rc;
+    attn_fwd_kernel<128><<<grid, ATT_THREADS, smem, st>>>(mq, mk, mv, p);
+  } else {
+    const int smem = 5 * Cfg<64>::TILE_B + 1024 + sizeof(FwdBars);
+    if (int rc = set_smem(attn_fwd_kernel<64>, smem)) return rc;
+    attn_fwd_kernel<64><<<grid, ATT_THREADS, smem, st>>>(mq, mk, mv, p);
+  }
+  B2F_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// delta: fp32 scratch [B, H, S] supplied by the caller.
+extern "C" int b2f_attn_bwd(const void* q, const void* k, const void* v, const void* o,
+                            const void* d_o, const float* lse, float* delta, void* dq, void* dk,
+                            void* dv, int B, int S, int H, int HKV, int D, long long q_ts,
+                            long long q_bs, long long k_ts, long long k_bs, long long v_ts,
+                            long long v_bs, long long o_ts, long long o_bs, long long do_ts,
+                            long long do_bs, long long dq_ts, long long dq_bs, long long dk_ts,
+                            long long dk_bs, long long dv_ts, long long dv_bs, float scale,
+                            int causal, const int* kv_lens, void* stream) {
+  if (int rc = check_common(B, S, H, HKV, D)) return rc;
+  B2F_REQUIRE(delta != nullptr && lse != nullptr, "attention bwd: lse and delta scratch required");
+  CUtensorMap mq, mk, mv, mdo;
+  if (int rc = make_map(&mq, q, B, S, H, D, q_ts, q_bs)) return rc;
+  if (int rc = make_map(&mk, k, B, S, HKV, D, k_ts, k_bs)) return rc;
+  if (int rc = make_map(&mv, v, B, S, HKV, D, v_ts, v_bs)) return rc;
+  if (int rc = make_map(&mdo, d_o, B, S, H, D, do_ts, do_bs)) return rc;
+  AttnParams p{};
+  p.B = B; p.H = H; p.HKV = HKV; p.S = S;
+  p.scale = scale; p.scale_log2 = scale * LOG2E; p.causal = causal; p.kv_lens = kv_lens;
+  p.lse = const_cast<float*>(lse); p.delta = delta;
+  p.dQ = static_cast<__nv_bfloat16*>(dq); p.dK = static_cast<__nv_bfloat16*>(dk);
+  p.dV = static_cast<__nv_bfloat16*>(dv);
+  p.dq_ts = dq_ts; p.dq_bs = dq_bs; p.dk_ts = dk_ts; p.dk_bs = dk_bs; p.dv_ts = dv_ts; p.dv_bs = dv_bs;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int nq = (S + TQ - 1) / TQ;
+  const long long delta_threads = (long long)B * S * H * (D / 8);
+  const unsigned dgrid = (unsigned)((delta_threads + 255) / 256);
+  if (D == 128) {
+    attn_delta_kernel<128><<<dgrid, 256, 0, st>>>((const __nv_bfloat16*)o, o_ts, o_bs,
+                                                  (const __nv_bfloat16*)d_o, do_ts, do_bs, delta, B, H, S);
+    const int smem = 6 * Cfg<128>::TILE_B + 1024 + sizeof(BwdBars);
+    if (int rc = set_smem(attn_bwd_dq_kernel<128>, smem)) return rc;
+    if (int rc = set_smem(attn_bwd_dkv_kernel<128>, smem)) return rc;
+    attn_bwd_dq_kernel<128><<<dim3(nq, H, B), ATT_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+    attn_bwd_dkv_kernel<128><<<dim3(nq, HKV, B), ATT_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+  } else {
+    attn_delta_kernel<64><<<dgrid, 256, 0, st>>>((const __nv_bfloat16*)o, o_ts, o_bs,
+                                                 (const __nv_bfloat16*)d_o, do_ts, do_bs, delta, B, H, S);
+    const int smem = 6 * Cfg<64>::TILE_B + 1024 + sizeof(BwdBars);
+    if (int rc = set_smem(attn_bwd_dq_kernel<64>, smem)) return rc;
+    if (int rc = set_smem(attn_bwd_dkv_kernel<64>, smem)) return rc;
+    attn_bwd_dq_kernel<64><<<dim3(nq, H, B), ATT_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+    attn_bwd_dkv_kernel<64><<<dim3(nq, HKV, B), ATT_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+  }
+  B2F_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

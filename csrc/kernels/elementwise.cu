@@ -194,7 +194,7 @@ dropout_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restri
 __global__ void __launch_bounds__(256)
 rope_kernel(__nv_bfloat16* __restrict__ x, const float* __restrict__ cos_t,
             const float* __restrict__ sin_t, long long tokens, int seq, int nh, int d,
-            long long token_stride, int pos_offset, float sign) {
+            long long token_stride, int pos_offset, int pos_div, float sign) {
   const int half = d >> 1;
   const int hv = half >> 3;  // vectors per half head
   const long long nvec = tokens * nh * hv;
@@ -204,7 +204,7 @@ rope_kernel(__nv_bfloat16* __restrict__ x, const float* __restrict__ cos_t,
     const long long th = i / hv;
     const int head = (int)(th % nh);
     const long long tok = th / nh;
-    const int pos = (int)(tok % seq) + pos_offset;
+    const int pos = (int)((tok / pos_div) % seq) + pos_offset;
     __nv_bfloat16* base = x + tok * token_stride + (long long)head * d;
     uint4* p1 = reinterpret_cast<uint4*>(base) + c;
     uint4* p2 = reinterpret_cast<uint4*>(base + half) + c;
@@ -415,12 +415,12 @@ extern "C" int b2f_dropout_bwd(const void* dy, const void* mask, void* dx, long 
   return 0;
 }
 extern "C" int b2f_rope(void* x, const float* cos_t, const float* sin_t, long long tokens, int seq,
-                        int nh, int d, long long token_stride, int pos_offset, int backward,
-                        void* stream) {
+                        int nh, int d, long long token_stride, int pos_offset, int pos_div,
+                        int backward, void* stream) {
   B2F_REQUIRE(d % 16 == 0 && tokens > 0 && token_stride % 8 == 0, "rope: head dim must be a multiple of 16");
   rope_kernel<<<ew_grid(tokens * nh * (d / 16)), 256, 0, (cudaStream_t)stream>>>(
       (__nv_bfloat16*)x, cos_t, sin_t, tokens, seq, nh, d, token_stride, pos_offset,
-      backward ? -1.f : 1.f);
+      pos_div > 0 ? pos_div : 1, backward ? -1.f : 1.f);
   B2F_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -71,14 +71,31 @@ int b2f_bias_dropout_add(const void* x, const void* bias, const void* residual, 
                          void* mask, long long rows, int H, float p, unsigned long long seed,
                          void* stream);
 int b2f_dropout_bwd(const void* dy, const void* mask, void* dx, long long n, float p, void* stream);
+/* position of token t = (t / pos_div) % seq + pos_offset (pos_div = batch for [s, b] order) */
 int b2f_rope(void* x, const float* cos_t, const float* sin_t, long long tokens, int seq, int nh,
-             int d, long long token_stride, int pos_offset, int backward, void* stream);
+             int d, long long token_stride, int pos_offset, int pos_div, int backward,
+             void* stream);
 int b2f_cross_entropy(const void* logits, const long long* targets, float* loss, void* dlogits,
                       long long rows, int V, long long ld, float grad_scale,
                       long long ignore_index, void* stream);
 int b2f_scaled_masked_softmax(const void* x, const void* mask, void* y, long long batch, int heads,
                               int sq, int sk, float scale, int causal, void* stream);
 int b2f_cast_f32_bf16(const float* x, void* y, long long n, float scale, void* stream);
+
+/* ---- K7: flash attention fwd/bwd on tcgen05 (flash-attn v2 / Megatron fused softmax).
+ * q/k/v/o: [B, S, heads, D] views, heads packed, D in {64,128}; *_ts token stride,
+ * *_bs batch stride (elements).  lse: fp32 [B, H, S].  delta: fp32 scratch [B, H, S]. */
+int b2f_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int S,
+                 int H, int HKV, int D, long long q_ts, long long q_bs, long long k_ts,
+                 long long k_bs, long long v_ts, long long v_bs, long long o_ts, long long o_bs,
+                 float scale, int causal, const int* kv_lens, void* stream);
+int b2f_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o,
+                 const float* lse, float* delta, void* dq, void* dk, void* dv, int B, int S, int H,
+                 int HKV, int D, long long q_ts, long long q_bs, long long k_ts, long long k_bs,
+                 long long v_ts, long long v_bs, long long o_ts, long long o_bs, long long do_ts,
+                 long long do_bs, long long dq_ts, long long dq_bs, long long dk_ts, long long dk_bs,
+                 long long dv_ts, long long dv_bs, float scale, int causal, const int* kv_lens,
+                 void* stream);
 
 #ifdef __cplusplus
 }

@@ -285,7 +285,96 @@ def group_elementwise():
     report("cast", ew.cast_f32_bf16(xc, scale=0.5).reshape(1, -1), (xc * 0.5).reshape(1, -1), 1e-2)
 
 
+def _attn_ref(q, k, v, causal, scale, kv_lens=None):
+    B, S, H, D = q.shape
+    HKV = k.shape[2]
+    qf, kf, vf = q.float().transpose(1, 2), k.float().transpose(1, 2), v.float().transpose(1, 2)
+    if HKV != H:
+        kf = kf.repeat_interleave(H // HKV, 1)
+        vf = vf.repeat_interleave(H // HKV, 1)
+    s = qf @ kf.transpose(-1, -2) * scale
+    mask = torch.zeros(B, 1, S, S, dtype=torch.bool, device=q.device)
+    if causal:
+        mask |= torch.triu(torch.ones(S, S, dtype=torch.bool, device=q.device), 1)
+    if kv_lens is not None:
+        mask |= (torch.arange(S, device=q.device)[None, :] >= kv_lens[:, None])[:, None, None, :]
+    s = s.masked_fill(mask, float("-inf"))
+    p = torch.softmax(s, -1)
+    return (p @ vf).transpose(1, 2)
+
+
+def group_attn(which):
+    from b200flow.ops import attention as A
+    torch.manual_seed(5)
+    cfgs = [(1, 128, 2, 2, 128, False), (2, 256, 4, 4, 128, True), (1, 384, 2, 2, 64, True),
+            (2, 200, 4, 2, 128, True), (1, 512, 2, 2, 128, False), (1, 1024, 4, 4, 128, True)]
+    for (B, S, H, HKV, D, causal) in cfgs:
+        qkv_shape = (B, S, H + 2 * HKV, D)
+        buf = torch.randn(qkv_shape, device=DEV, dtype=torch.bfloat16)
+        q = buf[:, :, :H].detach().requires_grad_()
+        k = buf[:, :, H:H + HKV].detach().requires_grad_()
+        v = buf[:, :, H + HKV:].detach().requires_grad_()
+        scale = D ** -0.5
+        tag = f"B{B}S{S}H{H}kv{HKV}D{D}{'c' if causal else 'f'}"
+        qf, kf, vf = (t.detach().float().requires_grad_() for t in (q, k, v))
+        ref = _attn_ref(qf, kf, vf, causal, scale)
+        if which == "fwd":
+            o, lse = A.attn_fwd_raw(q.detach(), k.detach(), v.detach(), causal, scale)
+            torch.cuda.synchronize()
+            report(f"attn_fwd_{tag}", o.reshape(B * S, -1), ref.reshape(B * S, -1), 2e-2)
+        else:
+            o = A.flash_attention(q, k, v, causal, scale)
+            do = torch.randn_like(o)
+            o.backward(do)
+            ref.backward(do.float())
+            torch.cuda.synchronize()
+            report(f"attn_fwd_{tag}", o.reshape(B * S, -1), ref.reshape(B * S, -1), 2e-2)
+            report(f"attn_dq_{tag}", q.grad.reshape(B * S, -1), qf.grad.reshape(B * S, -1), 3e-2)
+            report(f"attn_dk_{tag}", k.grad.reshape(B * S, -1), kf.grad.reshape(B * S, -1), 3e-2)
+            report(f"attn_dv_{tag}", v.grad.reshape(B * S, -1), vf.grad.reshape(B * S, -1), 3e-2)
+    if which == "bwd":
+        # key-padding lengths + packed qkv path
+        B, S, H, D = 2, 256, 2, 128
+        qkv = torch.randn(B, S, 3, H, D, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+        lens = torch.tensor([256, 130], device=DEV, dtype=torch.int32)
+        o = A.flash_attention_qkvpacked(qkv, False, D ** -0.5, lens)
+        do = torch.randn_like(o)
+        o.backward(do)
+        qf = qkv.detach().float().requires_grad_()
+        ref = _attn_ref(qf[:, :, 0], qf[:, :, 1], qf[:, :, 2], False, D ** -0.5, lens)
+        ref.backward(do.float())
+        report("attn_packed_fwd", o.reshape(B * S, -1), ref.reshape(B * S, -1), 2e-2)
+        report("attn_packed_dqkv", qkv.grad.reshape(B * S, -1), qf.grad.reshape(B * S, -1), 3e-2)
+
+
+def group_attn_perf():
+    from b200flow.ops import attention as A
+    for (B, S, H, D, causal) in [(1, 4096, 32, 128, True), (8, 512, 16, 64, False)]:
+        qkv = torch.randn(B, S, 3, H, D, device=DEV, dtype=torch.bfloat16)
+        q, k, v = qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2]
+        scale = D ** -0.5
+        o, lse = A.attn_fwd_raw(q, k, v, causal, scale)
+        do = torch.randn_like(o)
+        t_f = timeit(lambda: A.attn_fwd_raw(q, k, v, causal, scale))
+        t_b = timeit(lambda: A.attn_bwd_raw(q, k, v, o, do, lse, causal, scale))
+        fl = 4.0 * B * H * S * S * D * (0.5 if causal else 1.0)
+        rec = {"name": f"attn_perf_B{B}S{S}H{H}D{D}", "fwd_ms": t_f, "bwd_ms": t_b,
+               "fwd_tflops": fl / t_f / 1e9, "bwd_tflops": 2.5 * fl / t_b / 1e9}
+        try:
+            qt, kt, vt = (t.transpose(1, 2) for t in (q, k, v))
+            t_ref = timeit(lambda: torch.nn.functional.scaled_dot_product_attention(qt, kt, vt, is_causal=causal))
+            rec["sdpa_fwd_ms"] = t_ref
+            rec["sdpa_fwd_tflops"] = fl / t_ref / 1e9
+        except Exception as e:  # noqa: BLE001
+            rec["sdpa_error"] = repr(e)[:200]
+        print(json.dumps(rec), flush=True)
+        RESULTS.append({"name": rec["name"], "ok": True})
+
+
 GROUPS = {
+    "attn_fwd": lambda: group_attn("fwd"),
+    "attn_bwd": lambda: group_attn("bwd"),
+    "attn_perf": group_attn_perf,
     "gemm_nt": lambda: group_gemm("nt"),
     "gemm_nn": lambda: group_gemm("nn"),
     "gemm_tn": lambda: group_gemm("tn"),
