@@ -1,0 +1,207 @@
+"""DeepSpeed-shaped training engine over the b200flow runtime.
+
+API surface kept from DeepSpeed so Megatron-DeepSpeed style scripts port 1:1
+(the reference drives it as `deepspeed.initialize(...)` + `engine.train_batch()`
+from `pretrain_gpt.py --deepspeed --deepspeed_config ds_config.json`,
+examples/megatron-deepspeed/gpt2_345m/pretrain-ddp-tp-pp-zero1.yaml:33-38,74-85):
+
+    engine = initialize(model_config=cfg, config=ds_config, parallel=ParallelState|None)
+    loss = engine.train_batch(data_iter)      # GAS micro-batches + optimizer step
+    engine.save_checkpoint(dir) / engine.load_checkpoint(dir)
+
+Recognised ds_config keys: train_micro_batch_size_per_gpu, gradient_accumulation_steps,
+zero_optimization.stage (0/1), bf16.enabled / fp16.enabled, gradient_clipping,
+optimizer.params.{lr,betas,eps,weight_decay}, wall_clock_breakdown.  Unknown keys warn.
+
+Internals are b200flow's own: flat bf16 params + fp32 main_grad, tcgen05 kernels,
+ZeRO-1 over the DP group, TP+SP through TPContext, 1F1B over NCCL p2p.
+"""
+from __future__ import annotations
+
+import warnings
+from typing import Iterator
+
+import torch
+import torch.distributed as dist
+
+from ..models.gpt import GPTConfig, GPTModel
+from ..parallel import pipeline as PP
+from ..parallel.groups import ParallelState
+from ..parallel.tensor_parallel import SINGLE, TPContext, allreduce_replicated_grads
+from ..parallel.zero1 import AdamConfig, Zero1Optimizer, cosine_lr
+from ..utils.flat import FlatParams
+
+_KNOWN = {"train_micro_batch_size_per_gpu", "gradient_accumulation_steps", "zero_optimization",
+          "bf16", "fp16", "gradient_clipping", "optimizer", "wall_clock_breakdown",
+          "train_batch_size", "steps_per_print", "scheduler", "fused_collectives",
+          "activation_checkpointing", "sequence_parallel"}
+
+
+def split_layers(num_layers: int, stages: int) -> list[tuple[int, int]]:
+    """Uniform layer partition (DeepSpeed `partition_method="uniform"`)."""
+    base, rem = divmod(num_layers, stages)
+    out, lo = [], 0
+    for s in range(stages):
+        hi = lo + base + (1 if s < rem else 0)
+        out.append((lo, hi))
+        lo = hi
+    return out
+
+
+class TrainEngine:
+    def __init__(self, model_config: GPTConfig, config: dict, parallel: ParallelState | None = None,
+                 device=None, seed: int = 1234):
+        for k in config:
+            if k not in _KNOWN:
+                warnings.warn(f"ds_config key {k!r} is not interpreted by b200flow (ignored)")
+        self.cfg = model_config
+        self.ds = config
+        self.ps = parallel
+        self.device = device if device is not None else (
+            torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available()
+            else torch.device("cpu"))
+        self.micro_batch = int(config.get("train_micro_batch_size_per_gpu", 1))
+        self.gas = int(config.get("gradient_accumulation_steps", 1))
+        zero_stage = int(config.get("zero_optimization", {}).get("stage", 1))
+        assert zero_stage in (0, 1), "b200flow implements ZeRO stage 0/1 (what the reference uses)"
+        dtype = torch.bfloat16 if self.device.type == "cuda" else torch.float32
+        if config.get("bf16", {}).get("enabled") and self.device.type == "cpu":
+            dtype = torch.bfloat16
+        self.dtype = dtype
+        use_fused = bool(config.get("fused_collectives", True)) and self.device.type == "cuda"
+
+        ps = parallel
+        tp_world = ps.topo.tp if ps else 1
+        pp_world = ps.topo.pp if ps else 1
+        dp_world = ps.topo.dp if ps else 1
+        self.tp_world, self.pp_world, self.dp_world = tp_world, pp_world, dp_world
+        self.stage = ps.pp_rank if ps else 0
+
+        fused_tp = None
+        if tp_world > 1 and use_fused:
+            from ..parallel.fused_tp import FusedTP
+
+            fused_tp = FusedTP.create(ps.tp_group, ps.tp_rank, tp_world, self.device)
+        self.tp = TPContext(ps.tp_group, tp_world, ps.tp_rank,
+                            sequence_parallel=bool(config.get("sequence_parallel", True)),
+                            fused=fused_tp) if tp_world > 1 else SINGLE
+
+        # same init on every TP/DP replica of a stage, different across TP shards
+        torch.manual_seed(seed + 1000 * self.stage + (ps.tp_rank if ps else 0))
+        lo, hi = split_layers(model_config.layers, pp_world)[self.stage]
+        self.model = GPTModel(model_config, self.tp, (lo, hi), pre=self.stage == 0,
+                              post=self.stage == pp_world - 1, dtype=dtype, device=self.device)
+        self.model.recompute = bool(config.get("activation_checkpointing", {}).get("enabled", False))
+        self.flat = FlatParams(self.model, pad_to_multiple=max(1, dp_world) * 128)
+        if dp_world > 1:  # replicas start identical
+            dist.broadcast(self.flat.params, src=ps.dp_ranks[0], group=ps.dp_group)
+
+        op = config.get("optimizer", {}).get("params", {})
+        betas = op.get("betas", (0.9, 0.95))
+        acfg = AdamConfig(lr=float(op.get("lr", 1.5e-4)), beta1=float(betas[0]), beta2=float(betas[1]),
+                          eps=float(op.get("eps", 1e-8)), weight_decay=float(op.get("weight_decay", 0.01)),
+                          clip_grad=float(config.get("gradient_clipping", 1.0)))
+        fused_dp = None
+        if dp_world > 1 and use_fused:
+            from ..parallel.fused_dp import FusedZero1
+
+            fused_dp = FusedZero1.create(ps.dp_group, ps.dp_rank, dp_world, self.flat, self.device)
+        norm_groups = [ps.tp_group, ps.pp_group] if ps else []
+        self.optimizer = Zero1Optimizer(self.flat, acfg, ps.dp_group if ps else None, dp_world,
+                                        ps.dp_rank if ps else 0, norm_groups, fused=fused_dp)
+        self.sched = config.get("scheduler", {}).get("params", None)
+        self.global_steps = 0
+        self.p2p = None
+        self.last_loss = None
+
+    # ------------------------------------------------------------- batch API
+    def _p2p(self, seq: int):
+        if self.p2p is None and self.pp_world > 1:
+            tokens = seq * self.micro_batch
+            if self.tp_world > 1 and self.tp.sequence_parallel:
+                tokens //= self.tp_world
+            ps = self.ps
+            self.p2p = PP.P2P(ps.prev_stage_rank() if not ps.is_first_stage else None,
+                              ps.next_stage_rank() if not ps.is_last_stage else None,
+                              (tokens, self.cfg.hidden), self.dtype, self.device)
+        return self.p2p
+
+    def _forward_micro(self, batch, act):
+        tokens, labels = batch
+        b, s = tokens.shape
+        if self.stage == 0:
+            return self.model(tokens=tokens, labels=labels if self.pp_world == 1 else None)
+        return self.model(hidden=act, labels=labels if self.stage == self.pp_world - 1 else None,
+                          seq=s, batch=b)
+
+    def train_batch(self, data_iter: Iterator) -> torch.Tensor:
+        """One optimizer step over `gradient_accumulation_steps` micro-batches.
+
+        `data_iter` yields (tokens[b, s], labels[b, s]) device tensors; every pipeline stage
+        of a DP replica must see the same micro-batches (the caller's loader guarantees it)."""
+        self.optimizer.zero_grad()
+        batches = [next(data_iter) for _ in range(self.gas)]
+        if self.pp_world == 1:
+            losses = []
+            for mb in batches:
+                loss = self._forward_micro(mb, None)
+                loss.backward()
+                losses.append(loss.detach())
+        else:
+            seq = batches[0][0].shape[1]
+            losses = PP.run_1f1b(self.stage, self.pp_world, self.gas,
+                                 lambda i, act: self._forward_micro(batches[i], act), self._p2p(seq))
+        self.flat.collect_autograd_grads()
+        allreduce_replicated_grads(self.flat, self.tp)
+        self._reduce_tied_grads()
+        self._apply_lr()
+        self.optimizer.step(grad_divisor=float(self.gas * self.dp_world))
+        self.global_steps += 1
+        loss = torch.stack(losses).mean() if losses else torch.zeros((), device=self.device)
+        if self.pp_world > 1:  # make the loss visible on every stage (for logging)
+            dist.broadcast(loss, src=self.ps.pp_ranks[-1], group=self.ps.pp_group)
+        self.last_loss = loss
+        return loss
+
+    def eval_batch(self, data_iter: Iterator) -> torch.Tensor:
+        with torch.no_grad():
+            assert self.pp_world == 1, "eval_batch under PP: use train_batch with lr=0 or pp=1"
+            tokens, labels = next(data_iter)
+            return self.model(tokens=tokens, labels=labels)
+
+    def _reduce_tied_grads(self):
+        ps = self.ps
+        if ps is None or self.pp_world == 1 or not self.cfg.tie_embeddings:
+            return
+        if ps.embedding_group is not None:
+            w = self.model.embed.wte if self.stage == 0 else self.model.head.weight
+            dist.all_reduce(w.main_grad, group=ps.embedding_group)
+
+    def _apply_lr(self):
+        if self.sched:
+            p = self.sched
+            self.optimizer.lr = cosine_lr(self.global_steps + 1, base_lr=float(p["max_lr"]),
+                                          min_lr=float(p.get("min_lr", 0.0)),
+                                          warmup_steps=int(p.get("warmup_steps", 0)),
+                                          decay_steps=int(p.get("decay_steps", 1)))
+
+    # ----------------------------------------------------------- checkpoints
+    def save_checkpoint(self, save_dir: str, tag: str | None = None, client_state: dict | None = None):
+        from ..ckpt.megatron_ds_layout import save_checkpoint
+
+        return save_checkpoint(self, save_dir, tag, client_state or {})
+
+    def load_checkpoint(self, load_dir: str, tag: str | None = None):
+        from ..ckpt.megatron_ds_layout import load_checkpoint
+
+        return load_checkpoint(self, load_dir, tag)
+
+    def grad_norm(self) -> float:
+        g = self.optimizer.last_grad_norm
+        return float(g.item()) if g is not None else float("nan")
+
+
+def initialize(model_config: GPTConfig | None = None, config: dict | None = None,
+               parallel: ParallelState | None = None, **kw) -> TrainEngine:
+    """DeepSpeed-style entry point (`deepspeed.initialize`)."""
+    return TrainEngine(model_config, config or {}, parallel, **kw)

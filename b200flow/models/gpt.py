@@ -139,6 +139,19 @@ class _QKVAttention(torch.autograd.Function):
 
 
 def qkv_attention(qkv, heads, kv_heads, causal, scale, rope_tables=None, kv_lens=None):
+    if not qkv.is_cuda:  # CPU oracle path (gloo plumbing tests)
+        from ..ops import ref
+        s, b, nh, d = qkv.shape
+        x = qkv
+        if rope_tables is not None:
+            pos = torch.arange(s * b, device=qkv.device) // b
+            rot = ref.rope(qkv.reshape(s * b, nh, d)[:, : heads + kv_heads], rope_tables[0],
+                           rope_tables[1], pos)
+            x = torch.cat([rot, qkv.reshape(s * b, nh, d)[:, heads + kv_heads:]], 1).view(s, b, nh, d)
+        v = x.permute(1, 0, 2, 3)
+        o = ref.attention(v[:, :, :heads], v[:, :, heads:heads + kv_heads], v[:, :, heads + kv_heads:],
+                          causal, scale, kv_lens)
+        return o.permute(1, 0, 2, 3).reshape(s * b, heads * d)
     return _QKVAttention.apply(qkv, heads, kv_heads, causal, scale, rope_tables, kv_lens)
 
 
@@ -205,10 +218,8 @@ class Embedding(nn.Module):
         self.cfg, self.tp = cfg, tp
         kw = dict(dtype=dtype, device=device)
         self.wte = nn.Parameter(torch.empty(cfg.vocab_size, cfg.hidden, **kw).normal_(0, cfg.init_std))
-        self.wte.tp_replicated = True
         if cfg.learned_pos:
             self.wpe = nn.Parameter(torch.empty(cfg.max_seq, cfg.hidden, **kw).normal_(0, cfg.init_std))
-            self.wpe.tp_replicated = True
         else:
             self.wpe = None
 

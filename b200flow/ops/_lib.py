@@ -55,10 +55,12 @@ def loaded_libraries() -> list[str]:
 
 
 _launches = 0
+# kernels launched per entry point (default 1)
+_KERNELS_PER_CALL = {"b2f_norm_bwd": 2, "b2f_sumsq": 2, "b2f_attn_bwd": 3}
 
 
 def launch_count() -> int:
-    """Number of native kernel-launching calls made through this binding."""
+    """Number of b200flow CUDA kernels launched through this binding."""
     return _launches
 
 
@@ -90,7 +92,7 @@ def call(fn_name: str, *args) -> None:
     lib = cuda_lib()
     fn = getattr(lib, fn_name)
     rc = fn(*args)
-    _launches += 1
+    _launches += _KERNELS_PER_CALL.get(fn_name, 1)
     if rc != 0:
         msg = lib.b2f_last_error()
         raise NativeError(f"{fn_name} failed (rc={rc}): {msg.decode() if msg else '?'}")

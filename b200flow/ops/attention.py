@@ -77,6 +77,9 @@ def flash_attention(q, k, v, causal: bool = True, scale: float | None = None, kv
     """softmax(scale * q kᵀ [+ causal / key-length mask]) v, O(seq) memory."""
     if scale is None:
         scale = 1.0 / math.sqrt(q.shape[-1])
+    if not q.is_cuda:
+        from . import ref
+        return ref.attention(q, k, v, causal, scale, kv_lens)
     return _FlashAttn.apply(q, k, v, causal, float(scale), kv_lens)
 
 
@@ -104,4 +107,7 @@ class _FlashAttnPackedQKV(torch.autograd.Function):
 def flash_attention_qkvpacked(qkv, causal: bool = True, scale: float | None = None, kv_lens=None):
     if scale is None:
         scale = 1.0 / math.sqrt(qkv.shape[-1])
+    if not qkv.is_cuda:
+        from . import ref
+        return ref.attention(qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2], causal, scale, kv_lens)
     return _FlashAttnPackedQKV.apply(qkv, causal, float(scale), kv_lens)

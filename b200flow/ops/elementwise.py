@@ -37,6 +37,9 @@ class _SwiGLU(torch.autograd.Function):
 
 def swiglu(gu: torch.Tensor) -> torch.Tensor:
     """out = silu(gu[..., :F]) * gu[..., F:]."""
+    if not gu.is_cuda:
+        from . import ref
+        return ref.swiglu(gu)
     return _SwiGLU.apply(gu)
 
 
@@ -71,6 +74,9 @@ class _BiasGelu(torch.autograd.Function):
 
 
 def bias_gelu(x, bias=None):
+    if not x.is_cuda:
+        from . import ref
+        return ref.bias_gelu(x, bias)
     return _BiasGelu.apply(x, bias)
 
 
@@ -106,6 +112,9 @@ class _BiasDropoutAdd(torch.autograd.Function):
 
 def bias_dropout_add(x, bias, residual, p: float = 0.0, seed: int = 0):
     """out = residual + dropout(x + bias, p)."""
+    if not x.is_cuda:
+        from . import ref
+        return ref.bias_dropout_add(x, bias, residual, p, seed)
     return _BiasDropoutAdd.apply(x, bias, residual, float(p), int(seed))
 
 
@@ -186,6 +195,9 @@ class _CrossEntropy(torch.autograd.Function):
 
 def cross_entropy(logits, targets, ignore_index: int = -100):
     """Fused softmax-CE (mean over non-ignored tokens). Consumes `logits` (overwritten by grad)."""
+    if not logits.is_cuda:
+        from . import ref
+        return ref.cross_entropy(logits, targets, ignore_index)
     return _CrossEntropy.apply(logits, targets, ignore_index)
 
 

@@ -111,6 +111,9 @@ class _Linear(torch.autograd.Function):
 def linear(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor | None = None,
            residual: torch.Tensor | None = None) -> torch.Tensor:
     """y = x @ weightᵀ (+ bias) (+ residual) on the tcgen05 GEMM."""
+    if not x.is_cuda:
+        from . import ref
+        return ref.linear(x, weight, bias, residual)
     return _Linear.apply(x, weight, bias, residual)
 
 
@@ -139,4 +142,7 @@ class _LinearGelu(torch.autograd.Function):
 
 
 def linear_gelu(x, weight, bias):
+    if not x.is_cuda:
+        from . import ref
+        return ref.linear_gelu(x, weight, bias)
     return _LinearGelu.apply(x, weight, bias)

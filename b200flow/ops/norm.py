@@ -87,12 +87,15 @@ class _Norm(torch.autograd.Function):
 
 
 def norm(x, gamma, beta=None, residual=None, eps: float = 1e-5, rms: bool = False):
+    if not x.is_cuda:
+        from . import ref
+        return ref.norm(x, gamma, beta, residual, eps, rms)
     return _Norm.apply(x, gamma, beta, residual, eps, rms)
 
 
 def rmsnorm(x, gamma, residual=None, eps: float = 1e-5):
-    return _Norm.apply(x, gamma, None, residual, eps, True)
+    return norm(x, gamma, None, residual, eps, True)
 
 
 def layernorm(x, gamma, beta, residual=None, eps: float = 1e-5):
-    return _Norm.apply(x, gamma, beta, residual, eps, False)
+    return norm(x, gamma, beta, residual, eps, False)
