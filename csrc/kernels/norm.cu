@@ -267,6 +267,74 @@ int launch_bwd(const void* dy, const void* x, const void* gamma, const float* me
 
 }  // namespace
 
+// ---------------------------------------------------------------------------
+// Allocation-free variant of the backward pass.
+//
+// Some hosts of this library may not allocate device memory at all once they are
+// running: a serving or training process that carved the whole GPU into its own
+// pool at start-up and hands libraries nothing but raw pointers, a process
+// confined to a fixed memory partition where a late cudaMalloc can fail, or a
+// latency-critical loop that cannot afford the device-wide synchronisation an
+// allocation may imply.  For them the partial-sum scratch of the norm backward
+// lives in this file-scope device array instead of a caller-supplied buffer.
+// The price: every GPU that loads the library keeps these bytes until the
+// process exits, and the size is a hard limit.
+constexpr int NOALLOC_MAX_H = 8192;
+constexpr long long NOALLOC_MAX_FLOATS = 296LL * 2 * 4096;  // 2,424,832 floats = 9.25 MiB
+static __device__ __align__(256) float g_norm_bwd_scratch[NOALLOC_MAX_FLOATS];
+
+// The array's name is only a host-side handle; the device address has to be asked
+// for, once per device, with that device current.
+static int noalloc_scratch_ptr(float** out) {
+  static float* cache[64] = {nullptr};
+  int dev = 0;
+  B2F_CHECK_CUDA(cudaGetDevice(&dev));
+  B2F_REQUIRE(dev >= 0 && dev < 64, "noalloc: device ordinal out of range");
+  if (!cache[dev]) {
+    float* p = nullptr;
+    B2F_CHECK_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_norm_bwd_scratch));
+    B2F_REQUIRE(p != nullptr, "noalloc: cudaGetSymbolAddress returned a null scratch address");
+    cache[dev] = p;
+  }
+  *out = cache[dev];
+  return 0;
+}
+
+extern "C" int b2f_norm_bwd_noalloc_max_h() { return NOALLOC_MAX_H; }
+
+// Same contract and same kernels as b2f_norm_bwd, minus the `scratch` argument.
+//  * Limits: H <= 8192 (b2f_norm_bwd_noalloc_max_h()); larger H is refused with an
+//    error, nothing is launched.  Any number of rows.
+//  * The first call on each device looks up the scratch address (one
+//    cudaGetSymbolAddress); make that first call outside any stream capture.
+//  * Calls no cudaMalloc / cudaFree / allocating library routine.
+//  * All calls on a device share the one array and it keeps whatever the last
+//    call left in it.  Nothing in it needs to start at zero: every partial row
+//    that the reduce step reads is first fully written by this same call.  Two
+//    calls that may overlap on the GPU (different streams, no ordering between
+//    them) race on the array — serialise them.
+extern "C" int b2f_norm_bwd_noalloc(const void* dy, const void* x, const void* gamma,
+                                    const float* mean, const float* rstd, const void* dres,
+                                    void* dx, float* dgamma, float* dbeta, int rows, int H,
+                                    int rms, int accumulate, void* stream) {
+  B2F_REQUIRE(H % 8 == 0 && H > 0, "norm bwd (noalloc): H must be a positive multiple of 8");
+  B2F_REQUIRE(H <= NOALLOC_MAX_H,
+              "norm bwd (noalloc): H exceeds the built-in scratch limit of 8192 columns; "
+              "use b2f_norm_bwd with a caller-provided scratch buffer");
+  B2F_REQUIRE(rows > 0, "norm bwd (noalloc): rows must be positive");
+  float* scratch = nullptr;
+  if (int rc = noalloc_scratch_ptr(&scratch)) return rc;
+  int nparts = b2f::sm_count() * 2;
+  if (nparts > rows) nparts = rows;
+  const long long fit = NOALLOC_MAX_FLOATS / (2LL * H);
+  if (nparts > fit) nparts = static_cast<int>(fit);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return rms ? launch_bwd<true>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, scratch, nparts,
+                                rows, H, accumulate, st)
+             : launch_bwd<false>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, scratch,
+                                 nparts, rows, H, accumulate, st);
+}
+
 extern "C" int b2f_norm_bwd_num_partials(int rows) {
   const int cap = b2f::sm_count() * 2;
   return rows < cap ? rows : cap;

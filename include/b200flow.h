@@ -42,6 +42,20 @@ int b2f_norm_bwd(const void* dy, const void* x, const void* gamma, const float* 
                  const float* rstd, const void* dres, void* dx, float* dgamma, float* dbeta,
                  float* scratch, int rows, int H, int rms, int accumulate, void* stream);
 
+/* Allocation-free norm backward.  No counterpart in the reference: it exists for callers
+ * that must not (or cannot) allocate device memory while running — a host that owns the
+ * whole GPU through its own pool and passes libraries raw pointers only, a process held to
+ * a fixed memory partition, a loop that cannot take the device synchronisation an
+ * allocation may cause.  Same arguments as b2f_norm_bwd without `scratch`: the partial
+ * sums go to a 9.25 MiB file-scope device array that every GPU loading this library holds
+ * until exit.  H <= b2f_norm_bwd_noalloc_max_h() (8192), otherwise an error is returned and
+ * nothing runs.  The first call per device resolves the array's device address; issue it
+ * before any stream capture.  Calls share the array: calls that can overlap on the GPU race. */
+int b2f_norm_bwd_noalloc_max_h(void);
+int b2f_norm_bwd_noalloc(const void* dy, const void* x, const void* gamma, const float* mean,
+                         const float* rstd, const void* dres, void* dx, float* dgamma,
+                         float* dbeta, int rows, int H, int rms, int accumulate, void* stream);
+
 /* ---- K6 / K11: optimizer family (apex amp_C, DeepSpeed FusedAdam) ---------- */
 int b2f_adamw_flat(float* master, float* m, float* v, const void* grad, int grad_bf16,
                    void* param_out, long long n, float lr, float beta1, float beta2, float eps,
