@@ -92,7 +92,14 @@ class TrainEngine:
         self.model = GPTModel(model_config, self.tp, (lo, hi), pre=self.stage == 0,
                               post=self.stage == pp_world - 1, dtype=dtype, device=self.device)
         self.model.recompute = bool(config.get("activation_checkpointing", {}).get("enabled", False))
-        self.flat = FlatParams(self.model, pad_to_multiple=max(1, dp_world) * 128)
+        self.dp_comm = None
+        allocator = None
+        if dp_world > 1 and use_fused:
+            from ..comm.arena import PeerComm
+
+            self.dp_comm = PeerComm(ps.dp_group, ps.dp_rank, dp_world, self.device)
+            allocator = self.dp_comm.allocator()
+        self.flat = FlatParams(self.model, pad_to_multiple=max(1, dp_world) * 128, allocator=allocator)
         if dp_world > 1:  # replicas start identical
             dist.broadcast(self.flat.params, src=ps.dp_ranks[0], group=ps.dp_group)
 
@@ -102,10 +109,10 @@ class TrainEngine:
                           eps=float(op.get("eps", 1e-8)), weight_decay=float(op.get("weight_decay", 0.01)),
                           clip_grad=float(config.get("gradient_clipping", 1.0)))
         fused_dp = None
-        if dp_world > 1 and use_fused:
+        if self.dp_comm is not None:
             from ..parallel.fused_dp import FusedZero1
 
-            fused_dp = FusedZero1.create(ps.dp_group, ps.dp_rank, dp_world, self.flat, self.device)
+            fused_dp = FusedZero1(self.dp_comm, self.flat.grads_handle, self.flat.params_handle)
         norm_groups = [ps.tp_group, ps.pp_group] if ps else []
         self.optimizer = Zero1Optimizer(self.flat, acfg, ps.dp_group if ps else None, dp_world,
                                         ps.dp_rank if ps else 0, norm_groups, fused=fused_dp)

@@ -29,7 +29,9 @@ class FlatParams:
     """Re-homes the parameters of `module` into flat storage (in registration order)."""
 
     def __init__(self, module: nn.Module, *, grad_dtype: torch.dtype = torch.float32,
-                 align: int = 128, pad_to_multiple: int = 1):
+                 align: int = 128, pad_to_multiple: int = 1, allocator=None):
+        """allocator(numel, dtype) -> (tensor, handle): where the flat buffers live
+        (symmetric peer memory for the fused collectives); default = ordinary tensors."""
         params = [(n, p) for n, p in module.named_parameters() if p.requires_grad]
         # de-duplicate tied parameters
         seen, uniq = set(), []
@@ -47,8 +49,13 @@ class FlatParams:
             off += (p.numel() + align - 1) // align * align
         total = (off + pad_to_multiple - 1) // pad_to_multiple * pad_to_multiple
         self.numel = total
-        self.params = torch.zeros(total, dtype=dtype, device=device)
-        self.grads = torch.zeros(total, dtype=grad_dtype, device=device)
+        self.params_handle = self.grads_handle = None
+        if allocator is not None:
+            self.params, self.params_handle = allocator(total, dtype)
+            self.grads, self.grads_handle = allocator(total, grad_dtype)
+        else:
+            self.params = torch.zeros(total, dtype=dtype, device=device)
+            self.grads = torch.zeros(total, dtype=grad_dtype, device=device)
         self.module = module
         self._by_name = dict(uniq)
         for slot, (n, p) in zip(self.slots, uniq):

@@ -41,6 +41,8 @@ def parse_args():
     ap.add_argument("--micro-batch", type=int, default=1)
     ap.add_argument("--gas", type=int, default=8)
     ap.add_argument("--no-fused", action="store_true", help="NCCL collectives instead of fused kernels")
+    ap.add_argument("--tp", type=int, default=0, help="override the tensor-parallel size")
+    ap.add_argument("--pp", type=int, default=0, help="override the pipeline-parallel size")
     return ap.parse_args()
 
 
@@ -130,6 +132,8 @@ def main():
     from b200flow.ops import _lib
 
     tp, pp = topology_for(world)
+    if args.tp or args.pp:
+        tp, pp = max(args.tp, 1), max(args.pp, 1)
     ps = ParallelState.initialize(tp=tp, pp=pp) if world > 1 else None
     dp = world // (tp * pp)
     cfg = config_from_preset(args.workload, max_seq=args.seq)

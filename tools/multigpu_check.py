@@ -1,0 +1,173 @@
+"""Multi-GPU bring-up checks (run under torchrun on N GPUs of one box).
+
+  torchrun --nproc-per-node 2 --master-addr 127.0.0.1 tools/multigpu_check.py [groups...]
+Each rank prints JSON lines; rank 0's summary line says how many checks failed.
+"""
+from __future__ import annotations
+
+import ctypes
+import itertools
+import json
+import os
+import sys
+import time
+from pathlib import Path
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+
+from b200flow.ops import _lib  # noqa: E402
+from b200flow.ops._lib import c_float, c_int, c_ll, ptr, stream_ptr  # noqa: E402
+from b200flow.parallel.groups import ParallelState, init_distributed  # noqa: E402
+
+RESULTS = []
+
+
+def report(name, ok, **kw):
+    rec = {"name": name, "ok": bool(ok), "rank": dist.get_rank(), **kw}
+    RESULTS.append(rec)
+    print(json.dumps(rec), flush=True)
+
+
+def rel(a, b):
+    return ((a.float() - b.float()).abs().max() / (b.float().abs().max() + 1e-6)).item()
+
+
+def timeit(fn, iters=10, warmup=3):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / iters], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return t.item()
+
+
+def group_arena():
+    from b200flow.comm.arena import PeerComm
+
+    rank, world = dist.get_rank(), dist.get_world_size()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    comm = PeerComm(dist.group.WORLD, rank, world, dev)
+    n = 1 << 20
+    buf = comm.alloc(n * 4)
+    x = buf.view(torch.float32, n)
+    x.copy_(torch.arange(n, device=dev, dtype=torch.float32) * (rank + 1))
+    torch.cuda.synchronize()
+    dist.barrier()
+    out = torch.empty(n, device=dev)
+    _lib.call("b2f_peer_sum_test", buf.ptr_array, comm.flag_region(0), c_int(rank), c_int(world),
+              c_ll(n), ptr(out), c_int(32), ctypes.c_uint(comm.next_epoch()), stream_ptr())
+    torch.cuda.synchronize()
+    ref = torch.arange(n, device=dev, dtype=torch.float32) * sum(range(1, world + 1))
+    report("peer_sum", rel(out, ref) < 1e-6, multicast=bool(buf.multicast_ptr))
+    return comm
+
+
+def group_allreduce():
+    from b200flow.comm.arena import PeerComm
+    from b200flow.parallel.fused_dp import FusedAllReduce
+
+    rank, world = dist.get_rank(), dist.get_world_size()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    comm = PeerComm(dist.group.WORLD, rank, world, dev)
+    n = 64 << 20
+    buf = comm.alloc(n * 4)
+    g = buf.view(torch.float32, n)
+    for use_mc in ([False, True] if buf.multicast_ptr else [False]):
+        ar = FusedAllReduce(comm, buf, blocks=32, use_multicast=use_mc)
+        torch.manual_seed(rank)
+        src = torch.randn(n, device=dev)
+        g.copy_(src)
+        ref = src.clone()
+        dist.all_reduce(ref)
+        ref /= world
+        bf = torch.empty(n, device=dev, dtype=torch.bfloat16)
+        torch.cuda.synchronize(); dist.barrier()
+        ar(0, n, 1.0 / world, bf)
+        torch.cuda.synchronize()
+        tag = "nvls" if use_mc else "p2p"
+        report(f"allreduce_{tag}", rel(g, ref) < 1e-5, err=rel(g, ref))
+        report(f"allreduce_{tag}_bf16", rel(bf, ref) < 1e-2)
+        # slice of the buffer
+        g.copy_(src)
+        torch.cuda.synchronize(); dist.barrier()
+        ar(1024, 4096, 1.0 / world)
+        torch.cuda.synchronize()
+        report(f"allreduce_{tag}_slice", rel(g[1024:5120], ref[1024:5120]) < 1e-5 and
+               torch.equal(g[:1024], src[:1024]))
+        t = timeit(lambda: ar(0, n, 1.0 / world))
+        tn = timeit(lambda: dist.all_reduce(ref))
+        bus = 2 * (world - 1) / world * n * 4 / 1e9
+        report(f"allreduce_{tag}_perf", True, ms=t, nccl_ms=tn, busbw_gbs=bus / (t / 1e3),
+               nccl_busbw_gbs=bus / (tn / 1e3))
+
+
+def _engine_curve(tp, pp, fused, steps=4, preset_kw=None):
+    from b200flow.engines.ds_engine import initialize
+    from b200flow.models.gpt import config_from_preset
+
+    ps = ParallelState.initialize(tp=tp, pp=pp)
+    cfg = config_from_preset("llama-tiny", hidden=512, heads=4, ffn=1024, layers=4, vocab_size=2048,
+                             max_seq=256, **(preset_kw or {}))
+    eng = initialize(cfg, {"train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": 4,
+                           "optimizer": {"params": {"lr": 1e-3}}, "fused_collectives": fused}, ps, seed=5)
+    g = torch.Generator().manual_seed(100 + ps.dp_rank)
+    data = [torch.randint(0, cfg.vocab_size, (2, 257), generator=g) for _ in range(4)]
+    batches = [(t[:, :-1].contiguous().cuda(), t[:, 1:].contiguous().cuda()) for t in data]
+    it = itertools.cycle(batches)
+    return [float(eng.train_batch(it)) for _ in range(steps)], eng
+
+
+def group_zero1():
+    base, _ = _engine_curve(1, 1, False)
+    fused, eng = _engine_curve(1, 1, True)
+    ok = all(abs(a - b) < 2e-2 for a, b in zip(base, fused)) and fused[-1] < fused[0]
+    report("zero1_fused_vs_nccl", ok, base=base, fused=fused,
+           fused_active=eng.optimizer.fused is not None)
+
+
+def group_tp():
+    base, _ = _engine_curve(dist.get_world_size(), 1, False)
+    report("tp_nccl_runs", base[-1] < base[0], losses=base)
+    try:
+        fused, eng = _engine_curve(dist.get_world_size(), 1, True)
+        ok = all(abs(a - b) < 3e-2 for a, b in zip(base, fused))
+        report("tp_fused_vs_nccl", ok, base=base, fused=fused, fused_active=eng.tp.fused is not None)
+    except Exception as e:  # noqa: BLE001
+        report("tp_fused_vs_nccl", False, exception=repr(e)[:400])
+
+
+def group_pp():
+    base, _ = _engine_curve(1, dist.get_world_size(), False)
+    report("pp_nccl_runs", base[-1] < base[0], losses=base)
+
+
+GROUPS = {"arena": group_arena, "allreduce": group_allreduce, "zero1": group_zero1, "tp": group_tp,
+          "pp": group_pp}
+
+if __name__ == "__main__":
+    init_distributed("nccl")
+    names = sys.argv[1:] or list(GROUPS)
+    for n in names:
+        try:
+            GROUPS[n]()
+            torch.cuda.synchronize()
+        except Exception as e:  # noqa: BLE001
+            import traceback
+
+            report(n, False, exception=repr(e)[:400], tb=traceback.format_exc()[-800:])
+    bad = sum(1 for r in RESULTS if not r["ok"])
+    if dist.get_rank() == 0:
+        print(json.dumps({"summary": names, "checks": len(RESULTS), "failed": bad}), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(1 if bad else 0)
