@@ -101,25 +101,49 @@ allreduce_f32_kernel(PeerTable grads, float* mc_base, PeerTable flags, int rank,
 
   if (MULTIMEM) {
     float* mc = mc_base + off;
-    for (long long i = r0 + threadIdx.x; i < r1; i += COMM_THREADS) {
+    long long i = r0 + threadIdx.x;
+    for (; i + 3 * COMM_THREADS < r1; i += 4 * COMM_THREADS) {  // 4 reductions in flight
+      float4 s[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) s[j] = multimem_ld_reduce_f4(mc + (i + j * COMM_THREADS) * 4);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        s[j].x *= scale; s[j].y *= scale; s[j].z *= scale; s[j].w *= scale;
+        multimem_st_f4(mc + (i + j * COMM_THREADS) * 4, s[j]);
+      }
+    }
+    for (; i < r1; i += COMM_THREADS) {
       float4 s = multimem_ld_reduce_f4(mc + i * 4);
       s.x *= scale; s.y *= scale; s.z *= scale; s.w *= scale;
       multimem_st_f4(mc + i * 4, s);
     }
   } else {
-    for (long long i = r0 + threadIdx.x; i < r1; i += COMM_THREADS) {
-      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (long long i0 = r0; i0 < r1; i0 += 2 * COMM_THREADS) {  // 2 x world loads in flight
+      float4 s[2];
 #pragma unroll
-      for (int p = 0; p < MAX_WORLD; ++p) {
-        if (p < world) {
-          const float4 v = ld_f4(static_cast<const float*>(grads.ptr[p]) + off + i * 4);
-          s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+      for (int j = 0; j < 2; ++j) {
+        const long long i = i0 + j * COMM_THREADS + threadIdx.x;
+        s[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i < r1) {
+#pragma unroll
+          for (int p = 0; p < MAX_WORLD; ++p) {
+            if (p < world) {
+              const float4 v = ld_f4(static_cast<const float*>(grads.ptr[p]) + off + i * 4);
+              s[j].x += v.x; s[j].y += v.y; s[j].z += v.z; s[j].w += v.w;
+            }
+          }
         }
       }
-      s.x *= scale; s.y *= scale; s.z *= scale; s.w *= scale;
 #pragma unroll
-      for (int p = 0; p < MAX_WORLD; ++p)
-        if (p < world) st_f4(static_cast<float*>(grads.ptr[p]) + off + i * 4, s);
+      for (int j = 0; j < 2; ++j) {
+        const long long i = i0 + j * COMM_THREADS + threadIdx.x;
+        if (i < r1) {
+          s[j].x *= scale; s[j].y *= scale; s[j].z *= scale; s[j].w *= scale;
+#pragma unroll
+          for (int p = 0; p < MAX_WORLD; ++p)
+            if (p < world) st_f4(static_cast<float*>(grads.ptr[p]) + off + i * 4, s[j]);
+        }
+      }
     }
   }
 

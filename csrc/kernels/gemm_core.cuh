@@ -88,8 +88,13 @@ struct PlainPolicy {
   }
   // Called by the producer lane before the first TMA of a tile.
   __device__ __forceinline__ void wait_operands(int, int, int) const {}
-  // Called by one epilogue lane per warp after its rows of the tile are stored.
-  __device__ __forceinline__ void tile_stored(int, int, int) const {}
+  // Called by every epilogue thread once the accumulator tile is complete in TMEM.
+  __device__ __forceinline__ void before_epilogue(int, int, int) const {}
+  // Convert/store 32 columns of one accumulator row (default: the standard epilogue).
+  __device__ __forceinline__ void store_chunk(const Params& p, int b, int mb, int nb, int m, int n0,
+                                              const uint32_t (&acc)[32]) const;
+  // Called by every epilogue thread after its rows of the tile are stored.
+  __device__ __forceinline__ void tile_done(int, int, int) const {}
 };
 
 // Store/convert one 32-column chunk of one accumulator row.
@@ -193,6 +198,11 @@ __device__ __forceinline__ void epilogue_chunk(const Params& p, int b, int m, in
         if (n0 + i < p.N) cp[i] = __float2bfloat16(v[i]);
     }
   }
+}
+
+__device__ __forceinline__ void PlainPolicy::store_chunk(const Params& p, int b, int, int, int m,
+                                                         int n0, const uint32_t (&acc)[32]) const {
+  epilogue_chunk(p, b, m, n0, acc);
 }
 
 // The whole persistent GEMM. `first_tile`/`tile_stride` let a fused kernel give
@@ -316,6 +326,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap* tma_a, const CUtens
       const uint32_t aphase = (it >> 1) & 1;
       mbar_wait(&ss->tmem_full[as], aphase);
       tc_fence_after();
+      pol.before_epilogue(b, mb, nb);
       const int m = mb * BM + q * 32 + lane;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
 #pragma unroll 1
@@ -325,14 +336,12 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap* tma_a, const CUtens
         uint32_t acc[32];
         tmem_ld_32x32b_x32(taddr + c * 32, acc);
         tmem_ld_wait();
-        epilogue_chunk(p, b, m, n0, acc);
+        pol.store_chunk(p, b, mb, nb, m, n0, acc);
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) {
-        mbar_arrive(&ss->tmem_empty[as]);
-        pol.tile_stored(b, mb, nb);
-      }
+      if (lane == 0) mbar_arrive(&ss->tmem_empty[as]);
+      pol.tile_done(b, mb, nb);
     }
   }
 

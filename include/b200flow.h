@@ -111,6 +111,36 @@ int b2f_attn_bwd(const void* q, const void* k, const void* v, const void* o, con
                  long long dv_ts, long long dv_bs, float scale, int causal, const int* kv_lens,
                  void* stream);
 
+/* ---- K1 / K2: gradient collectives over NVLink peer memory, fused with scale / Adam
+ * (torch DDP Reducer + NCCL, Horovod fusion buffer, DeepSpeed ZeRO-1 phases).
+ * *_ptrs: host arrays of `world` device addresses of the same symmetric buffer on every
+ * rank; flags: symmetric u32 region, zeroed once; epoch: monotonically increasing. */
+int b2f_comm_max_blocks(void);
+int b2f_allreduce_f32(const long long* grads_ptrs, long long multicast_ptr,
+                      const long long* flags_ptrs, int rank, int world, long long off, long long n,
+                      float scale, void* bf16_out, int blocks, unsigned epoch, void* stream);
+int b2f_zero1_reduce(const long long* grads_ptrs, const long long* flags_ptrs, int rank, int world,
+                     long long lo, long long n, float* reduced, float* partial, float* sumsq_out,
+                     int blocks, unsigned epoch, void* stream);
+int b2f_zero1_adam_gather(const float* reduced, float* master, float* m, float* v,
+                          const long long* params_ptrs, const long long* flags_ptrs, int rank,
+                          int world, long long lo, long long n, float lr, float beta1, float beta2,
+                          float eps, float weight_decay, int step, const float* grad_scale,
+                          const int* skip, int blocks, unsigned epoch, void* stream);
+int b2f_peer_sum_test(const long long* buf_ptrs, const long long* flags_ptrs, int rank, int world,
+                      long long n, float* out, int blocks, unsigned epoch, void* stream);
+
+/* ---- K3 / K4: tensor-parallel GEMMs fused with the sequence-parallel collective
+ * (Megatron Column/RowParallelLinear: NCCL all-gather + cuBLAS, cuBLAS + NCCL reduce-scatter). */
+int b2f_ag_gemm_bf16(const long long* x_shard_ptrs, void* xg, const void* B, void* Y, int T, int N,
+                     int K, long long ldb, long long ldy, int b_mn_major, const void* bias,
+                     const long long* ready_ptrs, void* tile_flags, int rank, int world,
+                     int comm_ctas, unsigned epoch, void* stream);
+int b2f_gemm_rs_bf16(const void* X, const void* B, void* Y_shard, int T, int N, int K,
+                     long long ldx, long long ldb, long long ldy, int b_mn_major, const void* bias,
+                     const void* residual, long long ldr, const long long* recv_ptrs,
+                     const long long* flag_ptrs, int rank, int world, unsigned epoch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

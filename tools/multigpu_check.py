@@ -151,7 +151,65 @@ def group_pp():
     report("pp_nccl_runs", base[-1] < base[0], losses=base)
 
 
-GROUPS = {"arena": group_arena, "allreduce": group_allreduce, "zero1": group_zero1, "tp": group_tp,
+def group_fused_gemm():
+    from b200flow.parallel.fused_tp import FusedTP
+
+    rank, world = dist.get_rank(), dist.get_world_size()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    ftp = FusedTP.create(dist.group.WORLD, rank, world, dev)
+    for (T, N, K) in [(256 * world, 512, 256), (1024 * world, 768, 1024), (4096, 6144, 4096)]:
+        ts = T // world
+        torch.manual_seed(7)
+        x_full = torch.randn(T, K, device=dev, dtype=torch.bfloat16)
+        torch.manual_seed(100 + rank)
+        w = torch.randn(N, K, device=dev, dtype=torch.bfloat16) * 0.05
+        bias = torch.randn(N, device=dev, dtype=torch.bfloat16)
+        for rep in range(3):   # repeated calls exercise slot reuse / epochs
+            y, xg = ftp.ag_gemm(x_full[rank * ts:(rank + 1) * ts].contiguous(), w, bias)
+            torch.cuda.synchronize()
+            ref = x_full.float() @ w.float().t() + bias.float()
+            report(f"ag_gemm_{T}x{N}x{K}_r{rep}", rel(y, ref) < 2e-2 and torch.equal(xg, x_full), err=rel(y, ref))
+        # MN-major B (dgrad form)
+        wt = w.t().contiguous()
+        y, _ = ftp.ag_gemm(x_full[rank * ts:(rank + 1) * ts].contiguous(), wt, None, b_mn_major=True)
+        torch.cuda.synchronize()
+        report(f"ag_gemm_mn_{T}x{N}x{K}", rel(y, x_full.float() @ w.float().t()) < 2e-2)
+        # GEMM -> RS: every rank multiplies its own K-shard; sum over ranks, scatter rows
+        torch.manual_seed(200 + rank)
+        xr = torch.randn(T, K, device=dev, dtype=torch.bfloat16)
+        wr = torch.randn(N, K, device=dev, dtype=torch.bfloat16) * 0.05
+        res = torch.randn(ts, N, device=dev, dtype=torch.bfloat16)
+        part = (xr.float() @ wr.float().t()).contiguous()
+        full = part.clone()
+        dist.all_reduce(full)
+        ref = full[rank * ts:(rank + 1) * ts] + bias.float() + res.float()
+        for rep in range(3):
+            ys = ftp.gemm_rs(xr, wr, bias, res)
+            torch.cuda.synchronize()
+            report(f"gemm_rs_{T}x{N}x{K}_r{rep}", rel(ys, ref) < 2e-2, err=rel(ys, ref))
+    T, N, K = 4096, 4096, 4096 // world * 2
+    ts = T // world
+    x = torch.randn(T, K, device=dev, dtype=torch.bfloat16)
+    w = torch.randn(N, K, device=dev, dtype=torch.bfloat16)
+    xs = x[:ts].contiguous()
+    out = torch.empty(ts, N, device=dev, dtype=torch.bfloat16)
+    xgb = torch.empty(T, K, device=dev, dtype=torch.bfloat16)
+    t_ag = timeit(lambda: ftp.ag_gemm(xs, w))
+    def nccl_ag():
+        dist.all_gather_into_tensor(xgb, xs)
+        torch.matmul(xgb, w.t())
+    t_ag_n = timeit(nccl_ag)
+    t_rs = timeit(lambda: ftp.gemm_rs(x, w))
+    def nccl_rs():
+        yp = torch.matmul(x, w.t())
+        dist.reduce_scatter_tensor(out, yp)
+    t_rs_n = timeit(nccl_rs)
+    t_plain = timeit(lambda: torch.matmul(x, w.t()))
+    report("fused_gemm_perf", True, ag_gemm_ms=t_ag, nccl_ag_cublas_ms=t_ag_n, gemm_rs_ms=t_rs,
+           cublas_nccl_rs_ms=t_rs_n, cublas_gemm_only_ms=t_plain, shape=[T, N, K])
+
+
+GROUPS = {"fused_gemm": group_fused_gemm, "arena": group_arena, "allreduce": group_allreduce, "zero1": group_zero1, "tp": group_tp,
           "pp": group_pp}
 
 if __name__ == "__main__":
