@@ -1,0 +1,82 @@
+"""`python -m b200flow.launcher` — helm-like CLI over the local job runner.
+
+    install   <release> <chart> [-f values.yaml ...] [--set k=v ...] [--root DIR] [--wait/--no-wait]
+    template  <release> <chart> [-f ...] [--set ...]        (print the rendered script + plan)
+    uninstall <release> [--root DIR]
+    status    <release> [--root DIR]
+    logs      <release> [--root DIR] [--tail N]
+
+Mirrors `helm install <release> <chart> -f <values.yaml> -n <ns>`
+(examples/accelerate/bert-glue-mrpc/README.md:23-25).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+from dataclasses import asdict
+
+from ..jobspec.render import render_job
+from . import runner as R
+
+
+def _common(p):
+    p.add_argument("--root", default=os.environ.get("B2F_ROOT", "/tmp/b200flow"))
+
+
+def main(argv=None) -> int:
+    ap = argparse.ArgumentParser(prog="b200flow")
+    sub = ap.add_subparsers(dest="cmd", required=True)
+    for name in ("install", "template"):
+        p = sub.add_parser(name)
+        p.add_argument("release")
+        p.add_argument("chart")
+        p.add_argument("-f", "--values", action="append", default=[])
+        p.add_argument("--set", action="append", default=[], dest="sets")
+        p.add_argument("-n", "--namespace", default="local")
+        p.add_argument("--strict-exit", action="store_true",
+                       help="propagate the training command's exit status (reference masks it with | tee)")
+        p.add_argument("--online", action="store_true", help="do not install the offline git/pip shims")
+        p.add_argument("--timeout", type=float, default=None)
+        p.add_argument("--inject-fault", default=None, help="rank=R,step=S,kind={exit,hang,sigkill}")
+        p.add_argument("--max-restarts", type=int, default=None)
+        _common(p)
+    for name in ("uninstall", "status", "logs"):
+        p = sub.add_parser(name)
+        p.add_argument("release")
+        p.add_argument("--tail", type=int, default=None)
+        _common(p)
+    a = ap.parse_args(argv)
+
+    if a.cmd in ("install", "template"):
+        plan = render_job(a.chart, a.release, a.values, a.sets, root=a.root, strict_exit=a.strict_exit)
+        if a.cmd == "template":
+            d = asdict(plan)
+            script = d.pop("script")
+            print(json.dumps(d, indent=1, default=str))
+            print("---")
+            print(script)
+            return 0
+        run = R.Runner(plan, a.root, offline=not a.online, fault=a.inject_fault,
+                       max_restarts=a.max_restarts)
+        rc = run.run(timeout=a.timeout)
+        print(json.dumps(R.status(a.root, a.release)))
+        return rc
+    if a.cmd == "uninstall":
+        ok = R.uninstall(a.root, a.release)
+        print(f'release "{a.release}" ' + ("uninstalled" if ok else "not found"))
+        return 0 if ok else 1
+    if a.cmd == "status":
+        print(json.dumps(R.status(a.root, a.release), indent=1))
+        return 0
+    if a.cmd == "logs":
+        for pod, txt in R.logs(a.root, a.release, a.tail).items():
+            print(f"==> {pod} <==")
+            print(txt)
+        return 0
+    return 2
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,326 @@
+"""Local job runner: what training-operator / mpi-operator / KubeRay / kubelet do for the
+reference's charts, for one box.
+
+A rendered `JobPlan` becomes a set of "pods" — process groups on this machine — with the
+environment contract the user scripts rely on:
+
+* static PyTorchJob : `PET_NNODES`, `PET_NPROC_PER_NODE`, `PET_NODE_RANK`, `PET_MASTER_ADDR`,
+  `PET_MASTER_PORT`; pod names `<release>-master-0`, `<release>-worker-<i>`
+  (charts/machine-learning/training/pytorchjob-distributed/templates/train.yaml:58-141);
+* elastic PyTorchJob : `PET_RDZV_ID` (= release), `PET_RDZV_ENDPOINT`, `PET_RDZV_BACKEND`,
+  `PET_NNODES=min:max` (…/pytorchjob-elastic/templates/train.yaml:58-71);
+* MPIJob            : `-np` ranks with `OMPI_COMM_WORLD_{RANK,SIZE,LOCAL_RANK}` (plus the
+  torch rendezvous variables so Horovod-style scripts can init NCCL);
+* RayJob            : a submitter process running the script with the worker-group size and a
+  local "cluster address"; `engines/ray_train_api.py` spawns the workers;
+* Pod / Deployment  : one process.
+
+GPUs are sliced per pod through `CUDA_VISIBLE_DEVICES`; `/efs`- and `/fsx`-style mount paths
+are remapped under `--root`; a failed pod kills the group and the group restarts up to
+`backoff_limit` times (`restartPolicy: OnFailure`); SIGINT/SIGTERM tear everything down.
+State lives under `<root>/.b200flow/releases/<release>/` (plan, script, per-pod logs, status).
+"""
+from __future__ import annotations
+
+import json
+import os
+import re
+import signal
+import socket
+import subprocess
+import sys
+import time
+from dataclasses import asdict
+from pathlib import Path
+
+from ..jobspec.render import JobPlan
+
+REPO_ROOT = Path(__file__).resolve().parent.parent.parent
+
+
+def free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def remap_paths(text: str, mounts: dict) -> str:
+    """Rewrite absolute mount paths (`/efs/...`) to their local directories."""
+    for src in sorted(mounts, key=len, reverse=True):
+        dst = mounts[src]
+        text = re.sub(r"(?<![\w./-])" + re.escape(src) + r"(?=/|\b)", dst, text)
+    return text
+
+
+def visible_gpu_count() -> int:
+    env = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if env is not None:
+        return len([x for x in env.split(",") if x.strip()])
+    try:
+        out = subprocess.run(["nvidia-smi", "-L"], capture_output=True, text=True, timeout=10).stdout
+        return len([l for l in out.splitlines() if l.startswith("GPU ")])
+    except Exception:
+        return 0
+
+
+class ReleaseState:
+    def __init__(self, root: Path, release: str):
+        self.dir = Path(root) / ".b200flow" / "releases" / release
+        self.release = release
+
+    def exists(self) -> bool:
+        return (self.dir / "plan.json").exists()
+
+    def write_status(self, **kw) -> None:
+        cur = self.read_status()
+        cur.update(kw)
+        cur["updated"] = time.time()
+        (self.dir / "status.json").write_text(json.dumps(cur, indent=1))
+
+    def read_status(self) -> dict:
+        p = self.dir / "status.json"
+        return json.loads(p.read_text()) if p.exists() else {}
+
+
+class PodSpec:
+    def __init__(self, name: str, argv: list[str], env: dict, gpus: list[int] | None):
+        self.name, self.argv, self.env, self.gpus = name, argv, env, gpus
+
+
+class Runner:
+    def __init__(self, plan: JobPlan, root: str | Path, offline: bool = True, fault=None,
+                 max_restarts: int | None = None, extra_env: dict | None = None):
+        self.plan, self.root = plan, Path(root)
+        self.state = ReleaseState(self.root, plan.release)
+        self.offline = offline
+        self.fault = fault
+        self.max_restarts = plan.backoff_limit if max_restarts is None else max_restarts
+        self.extra_env = extra_env or {}
+        self.procs: list[subprocess.Popen] = []
+        self.restarts = 0
+        self._stop = False
+
+    # ------------------------------------------------------------ preparation
+    def prepare(self) -> Path:
+        d = self.state.dir
+        (d / "pods").mkdir(parents=True, exist_ok=True)
+        for local in self.plan.mounts.values():
+            Path(local).mkdir(parents=True, exist_ok=True)
+        script = remap_paths(self.plan.script, self.plan.mounts)
+        path = d / self.plan.script_name
+        path.write_text(script)
+        path.chmod(0o555 | 0o200)      # the chart mounts it 0555 (train.yaml:80, defaultMode 365)
+        (d / "plan.json").write_text(json.dumps(asdict(self.plan), indent=1, default=str))
+        if self.offline:
+            from .offline import write_shims
+
+            write_shims(d / "shims")
+        self.state.write_status(phase="Pending", restarts=0, chart=self.plan.chart, kind=self.plan.kind)
+        return path
+
+    def _base_env(self, pod: str) -> dict:
+        env = dict(os.environ)
+        for k, v in self.plan.env.items():
+            env[k] = remap_paths(v, self.plan.mounts)
+        env.update({k: str(v) for k, v in self.extra_env.items()})
+        env["HOSTNAME"] = pod
+        env["B2F_RELEASE"] = self.plan.release
+        env["B2F_ROOT"] = str(self.root)
+        env["B2F_MOUNTS"] = json.dumps(self.plan.mounts)
+        env["PYTHONPATH"] = str(REPO_ROOT) + os.pathsep + env.get("PYTHONPATH", "")
+        env.setdefault("MASTER_ADDR", "127.0.0.1")
+        if self.offline:
+            env["PATH"] = str(self.state.dir / "shims") + os.pathsep + env.get("PATH", "")
+            env["B2F_OFFLINE"] = "1"
+        if "HOME" in env:
+            Path(env["HOME"]).mkdir(parents=True, exist_ok=True)
+        if self.fault:
+            env["B2F_INJECT_FAULT"] = self.fault
+        env["B2F_RESTART_COUNT"] = str(self.restarts)
+        return env
+
+    def _gpu_slices(self, npods: int) -> list[list[int] | None]:
+        total = visible_gpu_count()
+        per = self.plan.gpus_per_node
+        if not total or not per:
+            return [None] * npods
+        base = os.environ.get("CUDA_VISIBLE_DEVICES")
+        ids = [x.strip() for x in base.split(",")] if base else [str(i) for i in range(total)]
+        out = []
+        for i in range(npods):
+            sl = ids[(i * per) % total:(i * per) % total + per]
+            out.append(sl if len(sl) == per else ids[:min(per, total)])
+        return out
+
+    def pods(self) -> list[PodSpec]:
+        p, script = self.plan, str(self.state.dir / self.plan.script_name)
+        sh = ["bash", script]      # the data-process chart says `sh`, which is bash on its images
+        rel = p.release
+        specs: list[PodSpec] = []
+        if p.kind == "static":
+            port = free_port()
+            slices = self._gpu_slices(p.nnodes)
+            for r in range(p.nnodes):
+                name = f"{rel}-master-0" if r == 0 else f"{rel}-worker-{r - 1}"
+                env = self._base_env(name)
+                env.update(PET_NNODES=str(p.nnodes), PET_NODE_RANK=str(r), PET_MASTER_ADDR="127.0.0.1",
+                           PET_MASTER_PORT=str(port))
+                if p.nproc_per_node:
+                    env["PET_NPROC_PER_NODE"] = str(p.nproc_per_node)
+                specs.append(PodSpec(name, sh, env, slices[r]))
+        elif p.kind == "elastic":
+            port = free_port()
+            el = p.elastic or {}
+            slices = self._gpu_slices(p.nnodes)
+            lo, hi = el.get("min_replicas", 1), el.get("max_replicas", 1)
+            for r in range(p.nnodes):
+                name = f"{rel}-worker-{r}"
+                env = self._base_env(name)
+                env.update(PET_NNODES=f"{lo}:{hi}" if lo != hi else str(p.nnodes),
+                           PET_RDZV_ID=rel, PET_RDZV_BACKEND=str(el.get("rdzv_backend", "c10d")),
+                           PET_RDZV_ENDPOINT=f"127.0.0.1:{port}")
+                if p.nproc_per_node:
+                    env["PET_NPROC_PER_NODE"] = str(p.nproc_per_node)
+                specs.append(PodSpec(name, sh, env, slices[r]))
+        elif p.kind in ("mpijob", "maskrcnn"):
+            np_ = p.mpirun_np or 1
+            total = visible_gpu_count()
+            if total and np_ > total:
+                np_ = total            # one box: cap ranks at the GPUs that exist
+            port = free_port()
+            per = max(1, p.gpus_per_node or 1)
+            for r in range(np_):
+                name = f"{rel}-worker-{r // per}"
+                env = self._base_env(name)
+                env.update(OMPI_COMM_WORLD_RANK=str(r), OMPI_COMM_WORLD_SIZE=str(np_),
+                           OMPI_COMM_WORLD_LOCAL_RANK=str(r % per), OMPI_COMM_WORLD_LOCAL_SIZE=str(min(per, np_)),
+                           RANK=str(r), WORLD_SIZE=str(np_), LOCAL_RANK=str(r % per),
+                           MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port),
+                           B2F_MPIRUN_ARGS=json.dumps(p.mpirun_args))
+                pod = PodSpec(f"{name}-rank{r}", sh, env, None)
+                specs.append(pod)
+        elif p.kind == "rayjob":
+            name = f"{rel}-submitter"
+            env = self._base_env(name)
+            ray = p.ray or {}
+            env.update(RAY_ADDRESS="local", B2F_RAY_WORKERS=str(ray.get("workers", 1)),
+                       B2F_RAY_GPUS_PER_WORKER=str(p.gpus_per_node or 0),
+                       B2F_RAY_RUNTIME_ENV=str(ray.get("runtime_env_yaml") or ""))
+            specs.append(PodSpec(name, sh, env, None))
+        else:  # pod / deployment
+            name = f"{rel}-pod"
+            specs.append(PodSpec(name, sh, self._base_env(name), self._gpu_slices(1)[0]))
+        return specs
+
+    # ------------------------------------------------------------- execution
+    def _spawn(self, spec: PodSpec) -> subprocess.Popen:
+        env = dict(spec.env)
+        if spec.gpus is not None:
+            env["CUDA_VISIBLE_DEVICES"] = ",".join(spec.gpus)
+        logdir = self.state.dir / "pods" / spec.name
+        logdir.mkdir(parents=True, exist_ok=True)
+        log = open(logdir / "stdout.log", "ab")
+        log.write(f"--- start (restart {self.restarts}) {time.strftime('%F %T')}\n".encode())
+        log.flush()
+        cwd = env.get("HOME") if env.get("HOME") and Path(env["HOME"]).is_dir() else None
+        return subprocess.Popen(spec.argv, env=env, stdout=log, stderr=subprocess.STDOUT, cwd=cwd,
+                                start_new_session=True)
+
+    def _kill_all(self, sig=signal.SIGTERM) -> None:
+        for pr in self.procs:
+            if pr.poll() is None:
+                try:
+                    os.killpg(pr.pid, sig)
+                except ProcessLookupError:
+                    pass
+        deadline = time.time() + 10
+        for pr in self.procs:
+            try:
+                pr.wait(timeout=max(0.1, deadline - time.time()))
+            except subprocess.TimeoutExpired:
+                try:
+                    os.killpg(pr.pid, signal.SIGKILL)
+                except ProcessLookupError:
+                    pass
+
+    def _on_signal(self, signum, frame):
+        self._stop = True
+        self._kill_all()
+
+    def run(self, timeout: float | None = None, poll: float = 0.2) -> int:
+        """Run to completion. Returns 0 on success, the failing exit code otherwise."""
+        self.prepare()
+        old = {}
+        for s in (signal.SIGINT, signal.SIGTERM):
+            try:
+                old[s] = signal.signal(s, self._on_signal)
+            except ValueError:      # not the main thread
+                pass
+        t0 = time.time()
+        rc = 1
+        try:
+            while not self._stop:
+                specs = self.pods()
+                self.procs = [self._spawn(s) for s in specs]
+                self.state.write_status(phase="Running", restarts=self.restarts,
+                                        pods={s.name: p.pid for s, p in zip(specs, self.procs)})
+                failed = None
+                while True:
+                    codes = [p.poll() for p in self.procs]
+                    bad = [c for c in codes if c not in (None, 0)]
+                    if bad:
+                        failed = bad[0]
+                        break
+                    if all(c == 0 for c in codes):
+                        break
+                    if timeout is not None and time.time() - t0 > timeout:
+                        failed = 124
+                        self._stop = True
+                        break
+                    if self._stop:
+                        failed = 130
+                        break
+                    time.sleep(poll)
+                if failed is None:
+                    rc = 0
+                    self.state.write_status(phase="Succeeded", exit_code=0)
+                    break
+                self._kill_all()                      # cleanPodPolicy: take the whole group down
+                rc = failed
+                if self._stop or self.restarts >= self.max_restarts:
+                    self.state.write_status(phase="Failed", exit_code=failed, restarts=self.restarts)
+                    break
+                self.restarts += 1
+                self.state.write_status(phase="Restarting", restarts=self.restarts, last_exit=failed)
+        finally:
+            self._kill_all()
+            for s, h in old.items():
+                signal.signal(s, h)
+        return rc
+
+
+def uninstall(root: str | Path, release: str) -> bool:
+    """Kill whatever is left of a release and mark it uninstalled (logs are kept)."""
+    st = ReleaseState(Path(root), release)
+    if not st.exists():
+        return False
+    for name, pid in (st.read_status().get("pods") or {}).items():
+        try:
+            os.killpg(int(pid), signal.SIGTERM)
+        except (ProcessLookupError, PermissionError):
+            pass
+    st.write_status(phase="Uninstalled")
+    return True
+
+
+def status(root: str | Path, release: str) -> dict:
+    return ReleaseState(Path(root), release).read_status()
+
+
+def logs(root: str | Path, release: str, tail: int | None = None) -> dict:
+    st = ReleaseState(Path(root), release)
+    out = {}
+    for f in sorted((st.dir / "pods").glob("*/stdout.log")):
+        txt = f.read_text(errors="replace")
+        out[f.parent.name] = "\n".join(txt.splitlines()[-tail:]) if tail else txt
+    return out
