@@ -80,6 +80,9 @@ def _wgrad(x2: torch.Tensor, dy2: torch.Tensor, weight: torch.Tensor):
     main_grad = getattr(weight, "main_grad", None)
     if main_grad is not None:
         gemm(dy2, x2, a_mn_major=True, b_mn_major=True, out=main_grad, accumulate=True)
+        cb = getattr(weight, "grad_ready", None)   # DDP bucket bookkeeping
+        if cb is not None:
+            cb()
         return None
     return gemm(dy2, x2, a_mn_major=True, b_mn_major=True)
 

@@ -80,6 +80,11 @@ class _Norm(torch.autograd.Function):
         dx, dgamma, dbeta = norm_bwd_raw(dy2, inp, gamma, None if ctx.rms else mean, rstd, dres2,
                                          ctx.rms, dgamma=mg, dbeta=mb, accumulate=mg is not None)
         dx = dx.reshape(ctx.shape)
+        if mg is not None:
+            for prm in (gamma, ctx.beta_ref):
+                cb = getattr(prm, "grad_ready", None) if prm is not None else None
+                if cb is not None and getattr(prm, "main_grad", None) is not None:
+                    cb()
         dg = None if mg is not None else dgamma.to(gamma.dtype)
         has_mb = ctx.beta_ref is not None and getattr(ctx.beta_ref, "main_grad", None) is not None
         db = dbeta.to(gamma.dtype) if (ctx.has_beta and dbeta is not None and not has_mb) else None

@@ -1,0 +1,98 @@
+"""torch.optim-shaped front-ends over the fused optimizer kernels (K11) and LR schedules.
+
+`AdamW` keeps fp32 master weights + moments for (bf16 or fp32) parameters and updates every
+tensor of every group in ONE multi-tensor launch (`b2f_adamw_multi`); gradients are taken
+from `p.main_grad` (flat fp32 buffer, when the model was flattened) or `p.grad`.  On CPU it
+runs the fp32 oracle.  Stands in for apex `FusedAdam` / `torch.optim.AdamW(fused=True)`
+(SURVEY.md §2H C23).
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+
+from .ops import optim as O
+from .ops import ref
+
+
+class AdamW(torch.optim.Optimizer):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.01):
+        super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay))
+        self._tables = {}
+        self._step = 0
+        self.grad_scale = None      # optional device scalar multiplied into every gradient
+        self.skip = None            # optional device int flag: skip the step (fp16 overflow)
+
+    def _grad(self, p):
+        g = getattr(p, "main_grad", None)
+        return g if g is not None else p.grad
+
+    def _init_state(self, p):
+        st = self.state[p]
+        if "master" not in st:
+            st["master"] = p.detach().float().clone()
+            st["exp_avg"] = torch.zeros_like(st["master"])
+            st["exp_avg_sq"] = torch.zeros_like(st["master"])
+        return st
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        self._step += 1
+        for gi, group in enumerate(self.param_groups):
+            ps = [p for p in group["params"] if self._grad(p) is not None]
+            if not ps:
+                continue
+            b1, b2 = group["betas"]
+            if ps[0].is_cuda:
+                key = (gi, tuple(id(p) for p in ps), tuple(self._grad(p).data_ptr() for p in ps))
+                tab = self._tables.get(key)
+                if tab is None:
+                    sts = [self._init_state(p) for p in ps]
+                    outs = [p.data if p.dtype == torch.bfloat16 else None for p in ps]
+                    tab = O.MultiTensorTable([s["master"] for s in sts], [s["exp_avg"] for s in sts],
+                                             [s["exp_avg_sq"] for s in sts],
+                                             [self._grad(p).contiguous() for p in ps], outs)
+                    self._tables = {key: tab} if len(self._tables) > 8 else {**self._tables, key: tab}
+                O.adamw_multi_(tab, lr=group["lr"], beta1=b1, beta2=b2, eps=group["eps"],
+                               weight_decay=group["weight_decay"], step=self._step,
+                               grad_scale=self.grad_scale, skip=self.skip)
+                for p in ps:
+                    if p.dtype != torch.bfloat16:   # fp32 params: master is the truth
+                        p.data.copy_(self.state[p]["master"])
+            else:
+                for p in ps:
+                    st = self._init_state(p)
+                    g = self._grad(p).float()
+                    if self.grad_scale is not None:
+                        g = g * float(self.grad_scale)
+                    ref.adamw_step(st["master"], st["exp_avg"], st["exp_avg_sq"], g, lr=group["lr"],
+                                   beta1=b1, beta2=b2, eps=group["eps"],
+                                   weight_decay=group["weight_decay"], step=self._step)
+                    p.data.copy_(st["master"].to(p.dtype))
+
+    def zero_grad(self, set_to_none: bool = True):
+        for group in self.param_groups:
+            for p in group["params"]:
+                p.grad = None
+                mg = getattr(p, "main_grad", None)
+                if mg is not None:
+                    mg.zero_()
+
+
+def get_linear_schedule_with_warmup(optimizer, num_warmup_steps: int, num_training_steps: int):
+    """HF `get_linear_schedule_with_warmup` (used by the Accelerate example)."""
+    def f(step):
+        if step < num_warmup_steps:
+            return step / max(1, num_warmup_steps)
+        return max(0.0, (num_training_steps - step) / max(1, num_training_steps - num_warmup_steps))
+    return torch.optim.lr_scheduler.LambdaLR(optimizer, f)
+
+
+def get_cosine_schedule(optimizer, num_warmup_steps: int, num_training_steps: int, min_ratio: float = 0.0):
+    def f(step):
+        if step < num_warmup_steps:
+            return step / max(1, num_warmup_steps)
+        t = (step - num_warmup_steps) / max(1, num_training_steps - num_warmup_steps)
+        return min_ratio + (1 - min_ratio) * 0.5 * (1 + math.cos(math.pi * min(1.0, t)))
+    return torch.optim.lr_scheduler.LambdaLR(optimizer, f)

@@ -1,0 +1,175 @@
+"""Data-parallel wrapper with a bucketed gradient reducer (K1).
+
+What torch's C++ `Reducer` (25 MB buckets in reverse registration order, one all-reduce per
+bucket as soon as its gradients exist, overlapped with the rest of backward) and Horovod's
+fusion buffer do for the reference's DDP / Horovod workloads (SURVEY.md §2F "DP", §2H C1/C2),
+re-designed around flat storage:
+
+* gradients live in ONE flat fp32 buffer (symmetric peer memory on GPUs), so a bucket is a
+  slice and needs no copy-in / copy-out;
+* the bucket plan comes from the host C++ planner (`csrc/host/bucket_plan.cpp`);
+* a bucket is reduced by the K1 kernel (`csrc/comm/collectives.cu`): in-place NVLS /
+  peer-memory all-reduce with the 1/N averaging fused, launched on a side stream using a
+  few SMs while backward keeps the rest;
+* readiness is tracked per parameter: autograd post-accumulate hooks for gradients autograd
+  produces, and the `grad_ready` callback that the wgrad GEMM / norm kernels fire after
+  accumulating straight into `main_grad`.
+
+On CPU (gloo) the same bookkeeping drives `dist.all_reduce` on the slice.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+import torch
+import torch.distributed as dist
+from torch import nn
+
+from ..utils.flat import FlatParams
+
+
+def plan_buckets(flat: FlatParams, cap_mb: float = 25.0, first_cap_mb: float = 1.0) -> list[tuple]:
+    """[(first_slot, last_slot_excl, elem_begin, elem_end)] in backward-fill order."""
+    from ..ops._lib import host_lib
+
+    lib = host_lib()
+    n = len(flat.slots)
+    offs = np.array([s.offset for s in flat.slots], dtype=np.int64)
+    nums = np.array([s.numel for s in flat.slots], dtype=np.int64)
+    out = np.zeros((n + 1) * 4, dtype=np.int64)
+    lib.b2f_plan_buckets.restype = ctypes.c_int
+    nb = lib.b2f_plan_buckets(offs.ctypes.data_as(ctypes.c_void_p), nums.ctypes.data_as(ctypes.c_void_p),
+                              ctypes.c_int(n), ctypes.c_longlong(flat.numel),
+                              ctypes.c_longlong(flat.grads.element_size()),
+                              ctypes.c_longlong(int(cap_mb * (1 << 20))),
+                              ctypes.c_longlong(int(first_cap_mb * (1 << 20))),
+                              out.ctypes.data_as(ctypes.c_void_p), ctypes.c_int(n + 1))
+    assert nb > 0, "bucket planner failed"
+    return [tuple(int(v) for v in out[4 * i:4 * i + 4]) for i in range(nb)]
+
+
+class DistributedDataParallel(nn.Module):
+    def __init__(self, module: nn.Module, process_group=None, bucket_cap_mb: float = 25.0,
+                 fused: bool = True, comm_blocks: int = 32):
+        super().__init__()
+        self.module = module
+        self.group = process_group if process_group is not None else dist.group.WORLD
+        self.world = dist.get_world_size(self.group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(self.group) if dist.is_initialized() else 0
+        p0 = next(module.parameters())
+        self.on_gpu = p0.is_cuda
+        self.comm = None
+        allocator = None
+        if self.on_gpu and fused and self.world > 1:
+            from ..comm.arena import PeerComm
+
+            self.comm = PeerComm(self.group, self.rank, self.world, p0.device)
+            allocator = self.comm.allocator()
+        self.flat = FlatParams(module, allocator=allocator, pad_to_multiple=128)
+        if self.world > 1:
+            dist.broadcast(self.flat.params, src=dist.get_global_rank(self.group, 0) if hasattr(
+                dist, "get_global_rank") else 0, group=self.group)
+        self.buckets = plan_buckets(self.flat, bucket_cap_mb)
+        self._slot_bucket = {}
+        for bi, (s0, s1, _, _) in enumerate(self.buckets):
+            for s in range(s0, s1):
+                self._slot_bucket[s] = bi
+        self._pending = [0] * len(self.buckets)
+        self._launched = [False] * len(self.buckets)
+        self.require_sync = True
+        self.reducer = None
+        self.side = None
+        if self.comm is not None:
+            from .fused_dp import FusedAllReduce
+
+            self.reducer = FusedAllReduce(self.comm, self.flat.grads_handle, blocks=comm_blocks)
+            self.side = torch.cuda.Stream(device=p0.device)
+        self._works = []
+        params = dict(self.flat.named_parameters())
+        self._params_by_slot = [params[slot.name] for slot in self.flat.slots]
+        for si, slot in enumerate(self.flat.slots):
+            p = params[slot.name]
+            p.grad_ready = self._make_ready(si)
+            p.register_post_accumulate_grad_hook(self._make_hook(si))
+        self._reset()
+
+    # ------------------------------------------------------------- bookkeeping
+    def _reset(self):
+        for bi, (s0, s1, _, _) in enumerate(self.buckets):
+            self._pending[bi] = s1 - s0
+            self._launched[bi] = False
+        self._uses = [int(getattr(self._params_by_slot[si], "ddp_uses", 1)) for si in range(len(self.flat.slots))]
+
+    def _make_hook(self, si):
+        def hook(p):
+            if p.grad is not None:
+                p.main_grad.add_(p.grad.to(p.main_grad.dtype))
+                p.grad = None
+            self._mark(si)
+        return hook
+
+    def _make_ready(self, si):
+        return lambda: self._mark(si)
+
+    def _mark(self, si):
+        if not self.require_sync or self._uses[si] <= 0:
+            return
+        self._uses[si] -= 1
+        if self._uses[si] > 0:      # parameter used more than once (tied weights): wait for all
+            return
+        bi = self._slot_bucket[si]
+        self._pending[bi] -= 1
+        if self._pending[bi] == 0:
+            self._launch(bi)
+
+    def _launch(self, bi):
+        if self._launched[bi] or self.world == 1:
+            self._launched[bi] = True
+            return
+        self._launched[bi] = True
+        _, _, e0, e1 = self.buckets[bi]
+        if self.reducer is not None:
+            self.side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(self.side):
+                self.reducer(e0, e1 - e0, 1.0 / self.world)
+        else:
+            g = self.flat.grads[e0:e1]
+            if g.is_cuda:
+                self._works.append((dist.all_reduce(g, group=self.group, async_op=True), g))
+            else:
+                dist.all_reduce(g, group=self.group)
+                g.div_(self.world)
+
+    # ----------------------------------------------------------------- public
+    def forward(self, *a, **kw):
+        return self.module(*a, **kw)
+
+    def no_sync(self):
+        ddp = self
+
+        class _Ctx:
+            def __enter__(self):
+                ddp.require_sync = False
+
+            def __exit__(self, *exc):
+                ddp.require_sync = True
+        return _Ctx()
+
+    def finish_reduction(self):
+        """Call after backward: reduce any bucket whose parameters received no gradient this
+        step, wait for the side stream, re-arm the bookkeeping."""
+        if self.require_sync:
+            for bi in range(len(self.buckets)):
+                if not self._launched[bi]:
+                    self._launch(bi)
+            if self.side is not None:
+                torch.cuda.current_stream().wait_stream(self.side)
+            for w, g in self._works:
+                w.wait()
+                g.div_(self.world)
+            self._works = []
+        self._reset()
+
+    def zero_grad(self, set_to_none: bool = True):
+        self.flat.zero_grad()
