@@ -1,0 +1,94 @@
+"""Local launcher: env contract per job kind, path remap, restart budget, pipeline semantics."""
+import json
+import os
+import sys
+from pathlib import Path
+
+import pytest
+
+from b200flow.jobspec.render import render_job
+from b200flow.launcher import runner as R
+from b200flow.pipeline.runner import run_pipeline
+
+
+def _vals(cmd, **extra):
+    v = {"train": {"env": [{"name": "HOME", "value": "/efs/home/{{ .Release.Name }}"}],
+                   "command": ["bash -c"], "args": [json.dumps(cmd)]}}
+    v.update(extra)
+    return v
+
+
+def _run(chart, rel, vals, tmp_root, sets=(), **kw):
+    plan = render_job(chart, rel, [vals], sets, root=tmp_root)
+    rc = R.Runner(plan, tmp_root, **kw).run(timeout=120)
+    return rc, R.logs(tmp_root, rel), R.status(tmp_root, rel)
+
+
+def test_static_env_contract_and_path_remap(tmp_root):
+    cmd = "echo N=$PET_NNODES R=$PET_NODE_RANK P=$PET_NPROC_PER_NODE H=$HOSTNAME M=$PET_MASTER_ADDR; echo hi > /fsx/out.$PET_NODE_RANK; echo $HOME"
+    rc, logs, st = _run("pytorchjob-distributed", "s1", _vals(cmd, resources={"nnodes": 2, "nproc_per_node": 3}), tmp_root)
+    assert rc == 0 and st["phase"] == "Succeeded"
+    assert "N=2 R=0 P=3 H=s1-master-0 M=127.0.0.1" in logs["s1-master-0"]
+    assert "N=2 R=1 P=3 H=s1-worker-0" in logs["s1-worker-0"]
+    assert (tmp_root / "fsx" / "out.0").exists() and (tmp_root / "fsx" / "out.1").exists()
+    assert str(tmp_root / "efs" / "home" / "s1") in logs["s1-master-0"]
+    assert "Training script done" in logs["s1-master-0"]
+
+
+def test_elastic_and_mpirun_and_ray_env(tmp_root):
+    rc, logs, _ = _run("pytorchjob-elastic", "e1", _vals("echo ID=$PET_RDZV_ID EP=$PET_RDZV_ENDPOINT B=$PET_RDZV_BACKEND"),
+                       tmp_root)
+    assert rc == 0 and "ID=e1 EP=127.0.0.1:" in logs["e1-worker-0"] and "B=c10d" in logs["e1-worker-0"]
+    v = {"train": {"command": ["bash -c"], "args": [json.dumps("echo RANK=$OMPI_COMM_WORLD_RANK/$OMPI_COMM_WORLD_SIZE L=$OMPI_COMM_WORLD_LOCAL_RANK A=$HOROVOD_AUTOTUNE")]},
+         "resources": {"gpu_nodes": 1, "gpus_per_node": 3}}
+    rc, logs, _ = _run("mpijob-horovod-tensorflow-gpu", "m1", v, tmp_root)
+    assert rc == 0 and len(logs) == 3
+    assert any("RANK=2/3 L=2 A=1" in t for t in logs.values())
+    rc, logs, _ = _run("raytrain", "r1", _vals("echo W=$B2F_RAY_WORKERS A=$RAY_ADDRESS", resources={"nnodes": 2}), tmp_root)
+    assert rc == 0 and "W=2 A=local" in logs["r1-submitter"]
+
+
+def test_restart_budget_and_strict_exit(tmp_root):
+    # fails on the first incarnation only -> one restart, then success
+    cmd = "if [ $B2F_RESTART_COUNT = 0 ]; then exit 3; fi; echo recovered"
+    plan = render_job("pytorchjob-distributed", "f1", [_vals(cmd, resources={"nnodes": 1})], root=tmp_root,
+                      strict_exit=True)
+    run = R.Runner(plan, tmp_root)
+    assert run.run(timeout=60) == 0 and run.restarts == 1
+    assert "recovered" in R.logs(tmp_root, "f1")["f1-master-0"]
+    # budget exhausted -> failure with the command's status
+    plan = render_job("pytorchjob-distributed", "f2", [_vals("exit 5", resources={"nnodes": 1}, backoff_limit=1)],
+                      root=tmp_root, strict_exit=True)
+    run = R.Runner(plan, tmp_root)
+    assert run.run(timeout=60) == 5 and run.restarts == 1
+    assert R.status(tmp_root, "f2")["phase"] == "Failed"
+    # reference semantics (no strict_exit): a failing command is masked, the pod "succeeds"
+    plan = render_job("pytorchjob-distributed", "f3", [_vals("false | tee /dev/null", resources={"nnodes": 1})], root=tmp_root)
+    assert R.Runner(plan, tmp_root).run(timeout=60) == 0
+
+
+def test_offline_git_and_pip_shims(tmp_root):
+    v = _vals("ls examples/complete_nlp_example.py && pwd",
+              git={"repo_url": "https://github.com/huggingface/accelerate.git", "branch": "main", "commit": "abc"},
+              pre_script=["pip3 install transformers==4.38.1"], resources={"nnodes": 1})
+    rc, logs, _ = _run("pytorchjob-distributed", "g1", v, tmp_root)
+    txt = logs["g1-master-0"]
+    assert rc == 0 and "examples/complete_nlp_example.py" in txt and "skipped: pip3 install" in txt
+    assert "/tmp/g1-master-0" in txt          # cwd is $HOME/tmp/$HOSTNAME
+    assert not (tmp_root / "efs/home/g1/tmp/g1-master-0").exists()   # clone dir removed at the end
+
+
+def test_pipeline_stops_at_first_failure_and_always_uninstalls(tmp_root):
+    ok = {"release_name": "p-ok", "chart": "data-process",
+          "values": {"process": {"command": ["echo"], "args": ["step1"]}}}
+    bad = {"release_name": "p-bad", "chart": "data-process", "strict_exit": True, "max_restarts": 0,
+           "values": {"process": {"command": ["bash -c"], "args": ["'exit 9'"]}}}
+    never = {"release_name": "p-never", "chart": "data-process",
+             "values": {"process": {"command": ["echo"], "args": ["nope"]}}}
+    msgs = []
+    assert run_pipeline([ok, bad, never], root=str(tmp_root), log=msgs.append) == "Failure"
+    assert R.status(tmp_root, "p-ok")["phase"] == "Uninstalled"
+    assert R.status(tmp_root, "p-bad")["phase"] == "Uninstalled"
+    assert R.status(tmp_root, "p-never") == {}
+    assert any("uninstalled p-bad" in m for m in msgs)
+    assert run_pipeline([ok], root=str(tmp_root), log=msgs.append) == "Success"
