@@ -1,0 +1,181 @@
+"""Megatron-DeepSpeed checkpoint directory layout.
+
+The reference saves with `--save $CKPT_ROOT/$PET_NODE_RANK --save-interval 10000`
+(examples/megatron-deepspeed/gpt2_345m/pretrain-ddp-zero1.yaml:26,55,83).  File names kept
+([UP] Megatron-DeepSpeed `save_checkpoint`):
+
+    <save>/latest                                  text: global_step<N>
+    <save>/latest_checkpointed_iteration.txt       text: <N>
+    <save>/global_step<N>/
+        mp_rank_<TP:02d>_model_states.pt                       module (non-pipeline) + client state
+        layer_<idx:02d>-model_<TP:02d>-model_states.pt         per layer (pipeline parallel)
+        zero_pp_rank_<DP>_mp_rank_<TP:02d>_optim_states.pt     ZeRO-1 shard (fp16)
+        bf16_zero_pp_rank_<DP>_mp_rank_<TP:02d>_optim_states.pt   … under bf16
+        layer_<L>_expert_<E>_mp_rank_<TP:02d>_model_states.pt  MoE expert weights
+        expp_rank_<EP>_mp_rank_<TP:02d>_optim_states.pt        MoE expert optimizer shard
+
+Pipeline layer indices follow the PipelineModule convention: embedding = 00, transformer
+layer i = i + 1, final norm + head = layers + 1.  Saves run on a background thread
+(`async_save=True`) once tensors are staged to host, since a 7B model with optimizer state
+is ~100 GB.
+"""
+from __future__ import annotations
+
+import threading
+from pathlib import Path
+
+import torch
+import torch.distributed as dist
+
+_pending: list[threading.Thread] = []
+
+
+def _cpu(sd):
+    return {k: (v.detach().to("cpu", copy=True) if isinstance(v, torch.Tensor) else v) for k, v in sd.items()}
+
+
+def _write(obj, path: Path, async_save: bool):
+    if async_save:
+        t = threading.Thread(target=torch.save, args=(obj, path), daemon=False)
+        t.start()
+        _pending.append(t)
+    else:
+        torch.save(obj, path)
+
+
+def wait_for_pending_saves() -> None:
+    while _pending:
+        _pending.pop().join()
+
+
+def tag_for(step: int) -> str:
+    return f"global_step{step}"
+
+
+def layer_file(idx: int, tp: int) -> str:
+    return f"layer_{idx:02d}-model_{tp:02d}-model_states.pt"
+
+
+def model_states_file(tp: int) -> str:
+    return f"mp_rank_{tp:02d}_model_states.pt"
+
+
+def optim_file(dp: int, tp: int, bf16: bool) -> str:
+    return ("bf16_" if bf16 else "") + f"zero_pp_rank_{dp}_mp_rank_{tp:02d}_optim_states.pt"
+
+
+def expert_file(layer: int, expert: int, tp: int) -> str:
+    return f"layer_{layer}_expert_{expert}_mp_rank_{tp:02d}_model_states.pt"
+
+
+def expert_optim_file(ep: int, tp: int) -> str:
+    return f"expp_rank_{ep}_mp_rank_{tp:02d}_optim_states.pt"
+
+
+def _split_expert_state(sd: dict):
+    dense, experts = {}, {}
+    for k, v in sd.items():
+        if ".experts." in k:
+            experts[k] = v
+        else:
+            dense[k] = v
+    return dense, experts
+
+
+def save_checkpoint(engine, save_dir: str, tag: str | None = None, client_state: dict | None = None,
+                    async_save: bool = False) -> str:
+    ps = engine.ps
+    tp = ps.tp_rank if ps else 0
+    dp = ps.dp_rank if ps else 0
+    pp_world = engine.pp_world
+    step = engine.global_steps
+    tag = tag or tag_for(step)
+    d = Path(save_dir) / tag
+    d.mkdir(parents=True, exist_ok=True)
+    bf16 = engine.dtype == torch.bfloat16
+    model = engine.model
+    client = {"iteration": step, "global_steps": step, "args": getattr(engine, "args", None),
+              "rng_state": torch.get_rng_state(), "lr": engine.optimizer.lr,
+              "parallel": {"tp": engine.tp_world, "pp": pp_world, "dp": engine.dp_world},
+              **(client_state or {})}
+    if dp == 0:      # one DP replica writes the module
+        if pp_world > 1:
+            lo, hi = model.layer_range
+            if model.embed is not None:
+                _write(_cpu(model.embed.state_dict()), d / layer_file(0, tp), async_save)
+            for i, layer in zip(range(lo, hi), model.layers):
+                _write(_cpu(layer.state_dict()), d / layer_file(i + 1, tp), async_save)
+            if model.head is not None:
+                _write(_cpu(model.head.state_dict()), d / layer_file(engine.cfg.layers + 1, tp), async_save)
+            if engine.stage == 0:
+                _write({"module": None, **client}, d / model_states_file(tp), async_save)
+        else:
+            dense, experts = _split_expert_state(_cpu(model.state_dict()))
+            _write({"module": dense, **client}, d / model_states_file(tp), async_save)
+            by = {}
+            for k, v in experts.items():     # "...layers.<L>....experts.<E>...."
+                parts = k.split(".")
+                L = int(parts[parts.index("layers") + 1]) if "layers" in parts else 0
+                E = int(parts[parts.index("experts") + 1])
+                by.setdefault((L, E), {})[k] = v
+            for (L, E), sd in by.items():
+                _write(sd, d / expert_file(L, E, tp), async_save)
+    osd = engine.optimizer.state_dict()
+    osd = {k: (v.detach().cpu() if isinstance(v, torch.Tensor) else v) for k, v in osd.items()}
+    osd["stage"] = engine.stage
+    name = optim_file(dp, tp, bf16)
+    if pp_world > 1:   # one file per (stage, dp, tp): stage goes into the DeepSpeed "pp_rank" slot
+        name = ("bf16_" if bf16 else "") + f"zero_pp_rank_{dp + engine.dp_world * engine.stage}_mp_rank_{tp:02d}_optim_states.pt"
+    _write({"optimizer_state_dict": osd, "ds_version": "b200flow"}, d / name, async_save)
+    if dist.is_initialized():
+        dist.barrier()
+    if (not dist.is_initialized()) or dist.get_rank() == 0:
+        wait_for_pending_saves() if not async_save else None
+        (Path(save_dir) / "latest").write_text(tag)
+        (Path(save_dir) / "latest_checkpointed_iteration.txt").write_text(str(step))
+    return str(d)
+
+
+def load_checkpoint(engine, load_dir: str, tag: str | None = None):
+    wait_for_pending_saves()
+    root = Path(load_dir)
+    if tag is None:
+        latest = root / "latest"
+        if not latest.exists():
+            return None, {}
+        tag = latest.read_text().strip()
+    d = root / tag
+    ps = engine.ps
+    tp = ps.tp_rank if ps else 0
+    dp = ps.dp_rank if ps else 0
+    model = engine.model
+    bf16 = engine.dtype == torch.bfloat16
+    client = {}
+    if engine.pp_world > 1:
+        lo, hi = model.layer_range
+        if model.embed is not None:
+            model.embed.load_state_dict(torch.load(d / layer_file(0, tp), map_location="cpu"))
+        for i, layer in zip(range(lo, hi), model.layers):
+            layer.load_state_dict(torch.load(d / layer_file(i + 1, tp), map_location="cpu"))
+        if model.head is not None:
+            model.head.load_state_dict(torch.load(d / layer_file(engine.cfg.layers + 1, tp), map_location="cpu"),
+                                       strict=False)
+        ms = d / model_states_file(tp)
+        if ms.exists():
+            client = torch.load(ms, map_location="cpu", weights_only=False)
+        name = ("bf16_" if bf16 else "") + f"zero_pp_rank_{dp + engine.dp_world * engine.stage}_mp_rank_{tp:02d}_optim_states.pt"
+    else:
+        client = torch.load(d / model_states_file(tp), map_location="cpu", weights_only=False)
+        sd = dict(client.pop("module"))
+        for f in d.glob(f"layer_*_expert_*_mp_rank_{tp:02d}_model_states.pt"):
+            sd.update(torch.load(f, map_location="cpu"))
+        model.load_state_dict(sd, strict=False)
+        name = optim_file(dp, tp, bf16)
+    osd = torch.load(d / name, map_location="cpu", weights_only=False)["optimizer_state_dict"]
+    dev = engine.flat.params.device
+    osd = {k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in osd.items()}
+    engine.optimizer.load_state_dict(osd)
+    engine.global_steps = int(client.get("global_steps", osd.get("step", 0)))
+    if "rng_state" in client:
+        torch.set_rng_state(client["rng_state"])
+    return str(d), client

@@ -116,6 +116,10 @@ class TrainEngine:
         norm_groups = [ps.tp_group, ps.pp_group] if ps else []
         self.optimizer = Zero1Optimizer(self.flat, acfg, ps.dp_group if ps else None, dp_world,
                                         ps.dp_rank if ps else 0, norm_groups, fused=fused_dp)
+        self._sync_tied_weights()
+        if self.pp_world > 1 and self.cfg.tie_embeddings and self.stage == pp_world - 1:
+            o = self.optimizer      # master copy of the re-tied head rows
+            o.master.copy_(self.flat.params[o.lo:o.hi].float())
         self.sched = config.get("scheduler", {}).get("params", None)
         self.global_steps = 0
         self.p2p = None
@@ -176,13 +180,42 @@ class TrainEngine:
             tokens, labels = next(data_iter)
             return self.model(tokens=tokens, labels=labels)
 
+    def _tied_slice(self, t):
+        """Stage 0 keeps the whole (replicated) embedding table, the last stage a vocab-parallel
+        head: this TP rank's rows of the table are the ones tied to its head shard."""
+        if self.stage != 0 or self.tp_world == 1:
+            return t
+        n = t.shape[0] // self.tp_world
+        return t[self.ps.tp_rank * n:(self.ps.tp_rank + 1) * n]
+
+    def _sync_tied_weights(self):
+        """Make the last stage's head start as a copy of the first stage's embedding rows."""
+        ps = self.ps
+        if ps is None or self.pp_world == 1 or not self.cfg.tie_embeddings or ps.embedding_group is None:
+            return
+        w = self.model.embed.wte if self.stage == 0 else self.model.head.weight
+        buf = self._tied_slice(w.data).contiguous()
+        dist.broadcast(buf, src=ps.pp_ranks[0], group=ps.embedding_group)
+        if self.stage != 0:
+            w.data.copy_(buf)
+
     def _reduce_tied_grads(self):
         ps = self.ps
         if ps is None or self.pp_world == 1 or not self.cfg.tie_embeddings:
             return
         if ps.embedding_group is not None:
             w = self.model.embed.wte if self.stage == 0 else self.model.head.weight
-            dist.all_reduce(w.main_grad, group=ps.embedding_group)
+            g = self._tied_slice(w.main_grad)
+            dist.all_reduce(g, group=ps.embedding_group)
+            if self.stage == 0 and self.tp_world > 1:
+                # every TP replica of the table needs every slice's tied gradient
+                dist.all_gather_into_tensor(w.main_grad, g.clone(), group=ps.tp_group) if g.is_cuda else \
+                    self._cpu_gather_rows(w.main_grad, g)
+
+    def _cpu_gather_rows(self, full, mine):
+        parts = [torch.empty_like(mine) for _ in range(self.tp_world)]
+        dist.all_gather(parts, mine.contiguous(), group=self.ps.tp_group)
+        full.copy_(torch.cat(parts, 0))
 
     def _apply_lr(self):
         if self.sched:

@@ -292,6 +292,7 @@ class Runner:
                     break
                 self.restarts += 1
                 self.state.write_status(phase="Restarting", restarts=self.restarts, last_exit=failed)
+                time.sleep(min(10.0, 0.05 * (2 ** min(self.restarts, 8))))   # crash-loop back-off
         finally:
             self._kill_all()
             for s, h in old.items():
