@@ -1,0 +1,89 @@
+"""The slice of PyTorch-Lightning the reference's Ray workload uses (`LightningModule`,
+`Trainer.fit`, callbacks, `self.log`), on the b200flow DDP (RayDDPStrategy's role) — see
+examples/ray/lightning-bert/fine-tune.yaml:17 (pytorch-lightning==2.2.1 pinned there)."""
+from __future__ import annotations
+
+import os
+import tempfile
+
+import torch
+import torch.distributed as dist
+from torch import nn
+
+from ..parallel.ddp import DistributedDataParallel
+
+
+class LightningModule(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self._logged: dict = {}
+        self.trainer = None
+
+    def log(self, name, value, sync_dist: bool = False, **kw):
+        v = float(value.detach()) if isinstance(value, torch.Tensor) else float(value)
+        if sync_dist and dist.is_initialized() and dist.get_world_size() > 1:
+            dev = next(self.parameters()).device
+            t = torch.tensor([v], device=dev if dist.get_backend() == "nccl" else "cpu")
+            dist.all_reduce(t)
+            v = float(t) / dist.get_world_size()
+        self._logged[name] = v
+
+
+class Callback:
+    def on_train_epoch_end(self, trainer, module):
+        pass
+
+
+class RayTrainReportCallback(Callback):
+    """Report the logged metrics and a checkpoint of the module at the end of every epoch."""
+
+    def on_train_epoch_end(self, trainer, module):
+        from . import ray_train_api as train
+
+        metrics = dict(module._logged, epoch=trainer.current_epoch, step=trainer.global_step)
+        tmp = tempfile.mkdtemp(prefix="b2f_ckpt_")
+        if train.get_context().get_world_rank() == 0:
+            torch.save({"state_dict": trainer.unwrapped.state_dict(), "epoch": trainer.current_epoch},
+                       os.path.join(tmp, "checkpoint.ckpt"))
+        train.report(metrics, checkpoint=train.Checkpoint.from_directory(tmp))
+
+
+class Trainer:
+    def __init__(self, max_epochs: int = 1, accelerator: str = "auto", devices="auto", strategy=None,
+                 plugins=None, callbacks=None, enable_progress_bar: bool = False, **kw):
+        self.max_epochs, self.callbacks = max_epochs, list(callbacks or [])
+        self.current_epoch = 0
+        self.global_step = 0
+        self.unwrapped = None
+
+    def fit(self, model: LightningModule, train_dataloaders=None, val_dataloaders=None):
+        use_cuda = torch.cuda.is_available() and dist.is_initialized() and dist.get_backend() == "nccl"
+        dev = torch.device("cuda", torch.cuda.current_device()) if use_cuda else torch.device("cpu")
+        model.to(dev)
+        if use_cuda:
+            model.to(torch.bfloat16)
+        model.trainer = self
+        self.unwrapped = model
+        ddp = DistributedDataParallel(model) if dist.is_initialized() else None
+        opt = model.configure_optimizers()
+        to_dev = lambda b: {k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in b.items()}  # noqa: E731
+        for epoch in range(self.max_epochs):
+            self.current_epoch = epoch
+            model.train()
+            for i, batch in enumerate(train_dataloaders() if callable(train_dataloaders) else train_dataloaders):
+                loss = model.training_step(to_dev(batch), i)
+                loss.backward()
+                if ddp is not None:
+                    ddp.finish_reduction()
+                opt.step()
+                opt.zero_grad()
+                self.global_step += 1
+            if val_dataloaders is not None:
+                model.eval()
+                with torch.no_grad():
+                    for i, batch in enumerate(val_dataloaders() if callable(val_dataloaders) else val_dataloaders):
+                        model.validation_step(to_dev(batch), i)
+                if hasattr(model, "on_validation_epoch_end"):
+                    model.on_validation_epoch_end()
+            for cb in self.callbacks:
+                cb.on_train_epoch_end(self, model)

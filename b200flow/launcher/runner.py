@@ -132,6 +132,8 @@ class Runner:
         if self.offline:
             env["PATH"] = str(self.state.dir / "shims") + os.pathsep + env.get("PATH", "")
             env["B2F_OFFLINE"] = "1"
+            env["PYTHONPATH"] = str(REPO_ROOT / "b200flow" / "workloads" / "offline_site") + os.pathsep + \
+                env["PYTHONPATH"]
         if "HOME" in env:
             Path(env["HOME"]).mkdir(parents=True, exist_ok=True)
         if self.fault:
