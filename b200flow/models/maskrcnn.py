@@ -1,0 +1,334 @@
+"""Mask R-CNN ResNet-50-FPN on the b200flow detection kernels.
+
+The reference trains tensorpack's and aws-samples' TensorFlow Mask R-CNN under Horovod
+(examples/maskrcnn/train-maskrcnn-tensorpack.yaml:17-35, train-maskrcnn-aws.yaml:17-37;
+graph in SURVEY.md §3.4): ResNet-50 backbone with frozen BN, FPN, RPN head, proposal
+generation (decode + per-level top-k + NMS), fg/bg sampling, multilevel RoIAlign, 2-fc box
+head, 4-conv + deconv mask head.  Same architecture here in PyTorch: convolutions stay on
+cuDNN (channels_last, bf16), everything the survey lists as a kernel —
+RoIAlign (K12), box decode + batched NMS (K13), matcher / IoU (K14), mask crop / paste (K15),
+the fc layers (K0) — runs on b200flow kernels.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field
+
+import torch
+import torch.nn.functional as F
+from torch import nn
+
+from ..ops import detection as D
+from ..ops import gemm as G
+
+
+@dataclass
+class MaskRCNNConfig:
+    num_classes: int = 81                 # COCO 80 + background
+    mode_mask: bool = True
+    mode_fpn: bool = True
+    backbone: str = "resnet50"
+    anchor_sizes: tuple = (32, 64, 128, 256, 512)
+    anchor_ratios: tuple = (0.5, 1.0, 2.0)
+    rpn_pre_nms_train: int = 2000
+    rpn_pre_nms_test: int = 1000
+    rpn_post_nms_train: int = 2000
+    rpn_post_nms_test: int = 1000
+    rpn_nms_thresh: float = 0.7
+    rpn_fg_iou: float = 0.7
+    rpn_bg_iou: float = 0.3
+    rpn_batch: int = 256
+    roi_batch: int = 512
+    roi_fg_fraction: float = 0.25
+    roi_fg_iou: float = 0.5
+    box_weights: tuple = (10.0, 10.0, 5.0, 5.0)
+    det_score_thresh: float = 0.05
+    det_nms_thresh: float = 0.5
+    det_per_image: int = 100
+    fc_dim: int = 1024
+    mask_res: int = 28
+    width: float = 1.0                    # channel multiplier for test-size models
+
+
+def make_anchors(feat_hw: list[tuple[int, int]], strides, sizes, ratios, device) -> list[torch.Tensor]:
+    out = []
+    for (h, w), s, size in zip(feat_hw, strides, sizes):
+        r = torch.tensor(ratios, device=device, dtype=torch.float32)
+        hs = size * torch.sqrt(r)
+        ws = size / torch.sqrt(r)
+        base = torch.stack([-ws, -hs, ws, hs], 1) / 2
+        sx = (torch.arange(w, device=device, dtype=torch.float32) + 0.5) * s
+        sy = (torch.arange(h, device=device, dtype=torch.float32) + 0.5) * s
+        cy, cx = torch.meshgrid(sy, sx, indexing="ij")
+        shifts = torch.stack([cx, cy, cx, cy], -1).reshape(-1, 1, 4)
+        out.append((shifts + base[None]).reshape(-1, 4))
+    return out
+
+
+def encode_boxes(gt, anchors, weights):
+    wx, wy, ww, wh = weights
+    aw, ah = anchors[:, 2] - anchors[:, 0], anchors[:, 3] - anchors[:, 1]
+    ax, ay = anchors[:, 0] + 0.5 * aw, anchors[:, 1] + 0.5 * ah
+    gw, gh = (gt[:, 2] - gt[:, 0]).clamp(min=1), (gt[:, 3] - gt[:, 1]).clamp(min=1)
+    gx, gy = gt[:, 0] + 0.5 * gw, gt[:, 1] + 0.5 * gh
+    return torch.stack([wx * (gx - ax) / aw, wy * (gy - ay) / ah, ww * torch.log(gw / aw),
+                        wh * torch.log(gh / ah)], 1)
+
+
+def _sample(pos_mask, neg_mask, batch, pos_frac):
+    pos, neg = pos_mask.nonzero().flatten(), neg_mask.nonzero().flatten()
+    npos = min(int(batch * pos_frac), pos.numel())
+    nneg = min(batch - npos, neg.numel())
+    pos = pos[torch.randperm(pos.numel(), device=pos.device)[:npos]]
+    neg = neg[torch.randperm(neg.numel(), device=neg.device)[:nneg]]
+    return pos, neg
+
+
+class RPNHead(nn.Module):
+    def __init__(self, c, a):
+        super().__init__()
+        self.conv = nn.Conv2d(c, c, 3, padding=1)
+        self.cls = nn.Conv2d(c, a, 1)
+        self.box = nn.Conv2d(c, a * 4, 1)
+        for m in (self.conv, self.cls, self.box):
+            nn.init.normal_(m.weight, std=0.01)
+            nn.init.zeros_(m.bias)
+
+    def forward(self, feats):
+        logits, deltas = [], []
+        for f in feats:
+            t = F.relu(self.conv(f))
+            logits.append(self.cls(t).permute(0, 2, 3, 1).flatten(1))               # [N, H*W*A]
+            n, _, h, w = f.shape
+            deltas.append(self.box(t).view(n, -1, 4, h, w).permute(0, 3, 4, 1, 2).reshape(n, -1, 4))
+        return logits, deltas
+
+
+class FCHead(nn.Module):
+    """2-fc box head + class / box predictors on the tcgen05 GEMM."""
+
+    def __init__(self, in_dim, fc, ncls):
+        super().__init__()
+        mk = lambda o, i, std: nn.Parameter(torch.empty(o, i).normal_(0, std))  # noqa: E731
+        self.w6, self.b6 = mk(fc, in_dim, math.sqrt(2.0 / in_dim)), nn.Parameter(torch.zeros(fc))
+        self.w7, self.b7 = mk(fc, fc, math.sqrt(2.0 / fc)), nn.Parameter(torch.zeros(fc))
+        self.wc, self.bc = mk(ncls, fc, 0.01), nn.Parameter(torch.zeros(ncls))
+        self.wb, self.bb = mk(ncls * 4, fc, 0.001), nn.Parameter(torch.zeros(ncls * 4))
+
+    def forward(self, x):
+        x = F.relu(G.linear(x, self.w6, self.b6))
+        x = F.relu(G.linear(x, self.w7, self.b7))
+        return G.linear(x, self.wc, self.bc).float(), G.linear(x, self.wb, self.bb).float()
+
+
+class MaskHead(nn.Module):
+    def __init__(self, c, ncls, dim=256):
+        super().__init__()
+        self.convs = nn.ModuleList([nn.Conv2d(c if i == 0 else dim, dim, 3, padding=1) for i in range(4)])
+        self.deconv = nn.ConvTranspose2d(dim, dim, 2, stride=2)
+        self.pred = nn.Conv2d(dim, ncls, 1)
+        for m in [*self.convs, self.deconv, self.pred]:
+            nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
+            nn.init.zeros_(m.bias)
+
+    def forward(self, x):
+        for c in self.convs:
+            x = F.relu(c(x))
+        return self.pred(F.relu(self.deconv(x)))
+
+
+class MaskRCNN(nn.Module):
+    def __init__(self, cfg: MaskRCNNConfig | None = None):
+        super().__init__()
+        import torchvision
+        from torchvision.models.detection.backbone_utils import BackboneWithFPN
+        from torchvision.ops import FrozenBatchNorm2d
+
+        self.cfg = cfg = cfg or MaskRCNNConfig()
+        c = max(16, int(256 * cfg.width) // 8 * 8)
+        if cfg.width >= 1.0:
+            body = torchvision.models.resnet50(weights=None, norm_layer=FrozenBatchNorm2d)   # BACKBONE.NORM=FreezeBN
+            chans = [256, 512, 1024, 2048]
+        else:
+            body = torchvision.models.resnet18(weights=None, norm_layer=FrozenBatchNorm2d)
+            chans = [64, 128, 256, 512]
+        for name, p in body.named_parameters():          # tensorpack freezes the stem + res2
+            if name.startswith(("conv1", "layer1")):
+                p.requires_grad_(False)
+        self.backbone = BackboneWithFPN(body, {"layer1": "0", "layer2": "1", "layer3": "2", "layer4": "3"},
+                                        chans, c)
+        self.strides = (4, 8, 16, 32, 64)
+        self.rpn = RPNHead(c, len(cfg.anchor_ratios))
+        self.box_head = FCHead(c * 7 * 7, max(64, int(cfg.fc_dim * cfg.width)), cfg.num_classes)
+        self.mask_head = MaskHead(c, cfg.num_classes, c) if cfg.mode_mask else None
+
+    # ------------------------------------------------------------------ RPN
+    def _proposals(self, logits, deltas, anchors, img_hw, training):
+        cfg = self.cfg
+        n = logits[0].shape[0]
+        pre = cfg.rpn_pre_nms_train if training else cfg.rpn_pre_nms_test
+        post = cfg.rpn_post_nms_train if training else cfg.rpn_post_nms_test
+        boxes_all, scores_all, seg_sizes = [], [], []
+        for lg, dl, an in zip(logits, deltas, anchors):
+            k = min(pre, lg.shape[1])
+            sc, idx = lg.detach().float().topk(k, dim=1)                     # sorted descending
+            d = torch.gather(dl.detach().float(), 1, idx[..., None].expand(-1, -1, 4))
+            a = an[idx]
+            b = D.box_decode(a.reshape(-1, 4), d.reshape(-1, 4), (1.0, 1.0, 1.0, 1.0), img_hw[1], img_hw[0])
+            boxes_all.append(b.view(n, k, 4))
+            scores_all.append(sc)
+            seg_sizes.append(k)
+        # segments ordered (image, level): each is already sorted by score
+        boxes = torch.cat([torch.cat([b[i] for b in boxes_all], 0) for i in range(n)], 0)
+        scores = torch.cat([torch.cat([s[i] for s in scores_all], 0) for i in range(n)], 0)
+        sizes = torch.tensor(seg_sizes * n, device=boxes.device)
+        seg_off = torch.cat([sizes.new_zeros(1), sizes.cumsum(0)]).int()
+        keep = D.nms_batched(boxes, seg_off, cfg.rpn_nms_thresh, max_seg=max(seg_sizes))
+        wh_ok = ((boxes[:, 2] - boxes[:, 0]) > 1e-3) & ((boxes[:, 3] - boxes[:, 1]) > 1e-3)
+        scores = torch.where(keep & wh_ok, scores, scores.new_full((), -1e9))
+        per_img = sum(seg_sizes)
+        out = []
+        for i in range(n):
+            s = scores[i * per_img:(i + 1) * per_img]
+            k = min(post, s.numel())
+            top, idx = s.topk(k)
+            sel = idx[top > -1e8]
+            out.append(boxes[i * per_img:(i + 1) * per_img][sel])
+        return out
+
+    def _rpn_loss(self, logits, deltas, anchors, targets):
+        cfg = self.cfg
+        lg = torch.cat(logits, 1).float()
+        dl = torch.cat(deltas, 1).float()
+        an = torch.cat(anchors, 0)
+        cls_loss, box_loss = lg.new_zeros(()), lg.new_zeros(())
+        for i, t in enumerate(targets):
+            gt = t["boxes"].float()
+            if gt.numel() == 0:
+                labels = torch.zeros(an.shape[0], device=an.device)
+                pos, neg = _sample(labels > 1, labels == 0, cfg.rpn_batch, 0.5)
+            else:
+                iou = D.pairwise_iou(an, gt)
+                best, arg = iou.max(1)
+                labels = torch.full_like(best, -1)
+                labels[best < cfg.rpn_bg_iou] = 0
+                labels[best >= cfg.rpn_fg_iou] = 1
+                labels[iou.argmax(0)] = 1                                   # every gt gets an anchor
+                pos, neg = _sample(labels == 1, labels == 0, cfg.rpn_batch, 0.5)
+                if pos.numel():
+                    tgt = encode_boxes(gt[arg[pos]], an[pos], (1.0, 1.0, 1.0, 1.0))
+                    box_loss = box_loss + F.smooth_l1_loss(dl[i, pos], tgt, beta=1.0 / 9, reduction="sum") / cfg.rpn_batch
+            sel = torch.cat([pos, neg])
+            y = torch.cat([torch.ones_like(pos, dtype=torch.float32), torch.zeros_like(neg, dtype=torch.float32)])
+            cls_loss = cls_loss + F.binary_cross_entropy_with_logits(lg[i, sel], y, reduction="sum") / cfg.rpn_batch
+        n = max(1, len(targets))
+        return cls_loss / n, box_loss / n
+
+    # ------------------------------------------------------------- ROI heads
+    def _roi_feats(self, feats_nhwc, rois, P):
+        scales = [1.0 / s for s in self.strides[:4]]
+        return D.roi_align(feats_nhwc[:4], scales, rois, P, sampling=2, aligned=True)   # [R, P, P, C]
+
+    def forward(self, images: torch.Tensor, targets: list[dict] | None = None):
+        """images: [N, 3, H, W]; targets: per image {"boxes" [n,4], "labels" [n], "masks" u8 [n,H,W]}.
+        Training returns a loss dict; eval returns per-image detections."""
+        cfg = self.cfg
+        training = self.training and targets is not None
+        x = images.contiguous(memory_format=torch.channels_last)
+        fmap = self.backbone(x)
+        feats = [fmap[k] for k in ("0", "1", "2", "3", "pool")]
+        img_hw = images.shape[-2:]
+        anchors = make_anchors([f.shape[-2:] for f in feats], self.strides, cfg.anchor_sizes,
+                               cfg.anchor_ratios, images.device)
+        logits, deltas = self.rpn(feats)
+        proposals = self._proposals(logits, deltas, anchors, img_hw, training)
+        feats_nhwc = [f.permute(0, 2, 3, 1).contiguous() if not f.permute(0, 2, 3, 1).is_contiguous()
+                      else f.permute(0, 2, 3, 1) for f in feats]
+        feats_nhwc = [f.to(torch.bfloat16) if f.is_cuda else f for f in feats_nhwc]
+        dt = feats[0].dtype
+        if training:
+            rpn_cls, rpn_box = self._rpn_loss(logits, deltas, anchors, targets)
+            rois, labels, reg_t, mask_rois, mask_gt, mask_lbl = [], [], [], [], [], []
+            gt_all = torch.cat([t["boxes"].float() for t in targets], 0)
+            gt_off = torch.tensor([0] + [t["boxes"].shape[0] for t in targets], device=images.device).cumsum(0).int()
+            for i, (p, t) in enumerate(zip(proposals, targets)):
+                p = torch.cat([p, t["boxes"].float()], 0)                     # gt boxes join the proposals
+                pb = torch.full((p.shape[0],), i, device=p.device, dtype=torch.int32)
+                iou, idx = D.match_proposals(p, pb, gt_all, gt_off)
+                fg, bg = _sample(iou >= cfg.roi_fg_iou, iou < cfg.roi_fg_iou, cfg.roi_batch, cfg.roi_fg_fraction)
+                sel = torch.cat([fg, bg])
+                lab = torch.zeros(sel.numel(), dtype=torch.long, device=p.device)
+                gidx = idx[fg].long()
+                all_labels = torch.cat([tt["labels"] for tt in targets])
+                lab[:fg.numel()] = all_labels[gidx]
+                rois.append(torch.cat([pb[sel].float()[:, None], p[sel]], 1))
+                labels.append(lab)
+                reg = torch.zeros(sel.numel(), 4, device=p.device)
+                if fg.numel():
+                    reg[:fg.numel()] = encode_boxes(gt_all[gidx], p[fg], cfg.box_weights)
+                reg_t.append(reg)
+                if cfg.mode_mask and fg.numel():
+                    mask_rois.append(torch.cat([pb[fg].float()[:, None], p[fg]], 1))
+                    mask_gt.append((i, gidx - gt_off[i].long()))
+                    mask_lbl.append(all_labels[gidx])
+            rois, labels, reg_t = torch.cat(rois), torch.cat(labels), torch.cat(reg_t)
+            box_feat = self._roi_feats(feats_nhwc, rois, 7).permute(0, 3, 1, 2).flatten(1).to(dt)
+            cls_logits, box_reg = self.box_head(box_feat)
+            loss_cls = F.cross_entropy(cls_logits, labels)
+            fg = (labels > 0).nonzero().flatten()
+            br = box_reg.view(-1, cfg.num_classes, 4)[fg, labels[fg]]
+            loss_box = F.smooth_l1_loss(br, reg_t[fg], beta=1.0, reduction="sum") / max(1, labels.numel())
+            losses = {"rpn_cls": rpn_cls, "rpn_box": rpn_box, "frcnn_cls": loss_cls, "frcnn_box": loss_box}
+            if cfg.mode_mask and mask_rois:
+                mr = torch.cat(mask_rois)
+                mfeat = self._roi_feats(feats_nhwc, mr, 14).permute(0, 3, 1, 2).to(dt)
+                mlogits = self.mask_head(mfeat.contiguous(memory_format=torch.channels_last)).float()
+                tgt, off = [], 0
+                for (i, gi), r in zip(mask_gt, mask_rois):
+                    tgt.append(D.mask_crop(targets[i]["masks"], r[:, 1:], gi.int(), cfg.mask_res))
+                ml = torch.cat(mask_lbl)
+                sel_logits = mlogits[torch.arange(ml.numel(), device=ml.device), ml]
+                losses["mrcnn"] = F.binary_cross_entropy_with_logits(sel_logits, torch.cat(tgt))
+            losses["total"] = sum(losses.values())
+            return losses
+        # ---------------------------------------------------------- inference
+        results = []
+        for i, p in enumerate(proposals):
+            if p.numel() == 0:
+                results.append({"boxes": p.new_zeros(0, 4), "scores": p.new_zeros(0), "labels": p.new_zeros(0).long()})
+                continue
+            rois = torch.cat([p.new_full((p.shape[0], 1), i), p], 1)
+            feat = self._roi_feats(feats_nhwc, rois, 7).permute(0, 3, 1, 2).flatten(1).to(dt)
+            cls_logits, box_reg = self.box_head(feat)
+            prob = cls_logits.softmax(-1)[:, 1:]                              # drop background
+            R, K = prob.shape
+            boxes = D.box_decode(p[:, None].expand(-1, K, -1).reshape(-1, 4),
+                                 box_reg.view(R, cfg.num_classes, 4)[:, 1:].reshape(-1, 4),
+                                 cfg.box_weights, img_hw[1], img_hw[0]).view(R, K, 4)
+            sc, cl = prob.flatten(), torch.arange(1, K + 1, device=p.device).repeat(R)
+            bx = boxes.reshape(-1, 4)
+            ok = (sc > cfg.det_score_thresh).nonzero().flatten()
+            sc, cl, bx = sc[ok], cl[ok], bx[ok]
+            # per-class NMS: sort by (class, -score) and cut one segment per class
+            order = torch.argsort(cl.float() * 2 - sc)       # class ascending, score descending inside
+            sc, cl, bx = sc[order], cl[order], bx[order]
+            counts = torch.bincount(cl, minlength=K + 1)
+            seg_off = torch.cat([counts.new_zeros(1), counts.cumsum(0)]).int()
+            keep = D.nms_batched(bx, seg_off, cfg.det_nms_thresh) if bx.numel() else torch.zeros(0, dtype=torch.bool, device=p.device)
+            sc, cl, bx = sc[keep], cl[keep], bx[keep]
+            top = sc.argsort(descending=True)[:cfg.det_per_image]
+            det = {"boxes": bx[top], "scores": sc[top], "labels": cl[top], "fastrcnn_all_scores": prob}
+            if cfg.mode_mask and top.numel():
+                mr = torch.cat([bx.new_full((top.numel(), 1), i), bx[top]], 1)
+                mfeat = self._roi_feats(feats_nhwc, mr, 14).permute(0, 3, 1, 2).to(dt)
+                ml = self.mask_head(mfeat.contiguous(memory_format=torch.channels_last)).float().sigmoid()
+                det["masks"] = ml[torch.arange(top.numel(), device=ml.device), cl[top]]   # [n, 28, 28]
+            results.append(det)
+        return results
+
+
+def paste_masks(det: dict, H: int, W: int) -> torch.Tensor:
+    """28x28 probabilities -> full-image binary masks (the notebook's `get_mask` step)."""
+    if "masks" not in det or det["masks"].numel() == 0:
+        return torch.zeros(0, H, W, dtype=torch.uint8)
+    return D.mask_paste(det["masks"], det["boxes"], H, W, 0.5)

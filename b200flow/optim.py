@@ -96,3 +96,46 @@ def get_cosine_schedule(optimizer, num_warmup_steps: int, num_training_steps: in
         t = (step - num_warmup_steps) / max(1, num_training_steps - num_warmup_steps)
         return min_ratio + (1 - min_ratio) * 0.5 * (1 + math.cos(math.pi * min(1.0, t)))
     return torch.optim.lr_scheduler.LambdaLR(optimizer, f)
+
+
+class FlatMomentumSGD:
+    """Momentum SGD over a `FlatParams` buffer (one fused launch): the optimizer of the
+    reference's Mask R-CNN workloads (tensorpack `MomentumOptimizer(0.9)`)."""
+
+    def __init__(self, flat, lr: float = 0.01, momentum: float = 0.9, weight_decay: float = 1e-4):
+        self.flat, self.lr, self.momentum, self.weight_decay = flat, lr, momentum, weight_decay
+        self.master = flat.params.float().clone()
+        self.buf = torch.zeros_like(self.master)
+        self.grad_scale = None
+        self.param_groups = [{"lr": lr}]
+
+    @torch.no_grad()
+    def step(self):
+        from .ops import _lib
+        from .ops._lib import c_float, c_int, c_ll, ptr, stream_ptr
+
+        lr = self.param_groups[0]["lr"]
+        f = self.flat
+        if f.params.is_cuda:
+            out = f.params if f.params.dtype == torch.bfloat16 else None
+            _lib.call("b2f_sgd_momentum_flat", ptr(self.master), ptr(self.buf), ptr(f.grads),
+                      c_int(int(f.grads.dtype == torch.bfloat16)), ptr(out), c_ll(f.numel), c_float(lr),
+                      c_float(self.momentum), c_float(self.weight_decay), ptr(self.grad_scale), stream_ptr())
+            if out is None:
+                f.params.copy_(self.master)
+        else:
+            g = f.grads.float() * (float(self.grad_scale) if self.grad_scale is not None else 1.0)
+            self.buf.mul_(self.momentum).add_(g + self.weight_decay * self.master)
+            self.master.add_(self.buf, alpha=-lr)
+            f.params.copy_(self.master.to(f.params.dtype))
+
+    def zero_grad(self, set_to_none: bool = True):
+        self.flat.zero_grad()
+
+    def state_dict(self):
+        return {"master": self.master, "momentum_buffer": self.buf, "lr": self.param_groups[0]["lr"]}
+
+    def load_state_dict(self, sd):
+        self.master.copy_(sd["master"])
+        self.buf.copy_(sd["momentum_buffer"])
+        self.flat.params.copy_(self.master.to(self.flat.params.dtype))

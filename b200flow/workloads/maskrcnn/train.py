@@ -1,0 +1,223 @@
+"""Mask R-CNN trainer with the command line of the reference's training scripts:
+
+    python3 train.py --logdir <dir> [--images_per_epoch N] --config KEY=VALUE ...
+
+(charts/machine-learning/training/maskrcnn/templates/maskrcnn.yaml:114-132 for tensorpack's
+`examples/FasterRCNN/train.py`; maskrcnn-optimized/templates/maskrcnn.yaml:117-136 for
+aws-samples' `MaskRCNN/train.py`; launched by mpirun with TRAINER=horovod).  Recognised
+config keys: MODE_MASK, MODE_FPN, DATA.BASEDIR, DATA.TRAIN, DATA.VAL, TRAIN.EVAL_PERIOD,
+TRAIN.STEPS_PER_EPOCH, TRAIN.LR_SCHEDULE, TRAIN.LR_EPOCH_SCHEDULE, TRAIN.BASE_LR,
+TRAIN.BATCH_SIZE_PER_GPU, TRAIN.CHECKPOINT_PERIOD, TRAIN.GRADIENT_CLIP, TRAIN.WARMUP,
+BACKBONE.WEIGHTS, BACKBONE.NORM, PREPROC.PREDEFINED_PADDING, TRAINER (others are stored
+and ignored).  Ranks come from the launcher's mpirun mode (OMPI_COMM_WORLD_* / RANK).
+
+Callbacks mirror tensorpack's: periodic model saver (`model-<step>.pt` + `model-<step>.index`
+marker + `checkpoint` file under `<logdir>`, auto-resume from the newest), LR schedule with
+linear warm-up, throughput tracker, evaluation every EVAL_PERIOD epochs (box AP@0.5 on the
+synthetic validation split), TensorBoard scalars.  COCO-shaped synthetic images.
+
+Test-size knobs: B2F_MRCNN_WIDTH, B2F_MRCNN_IMAGE (HxW), B2F_MRCNN_EPOCHS, B2F_MRCNN_STEPS.
+"""
+from __future__ import annotations
+
+import argparse
+import ast
+import json
+import os
+import time
+from pathlib import Path
+
+import torch
+import torch.distributed as dist
+
+from b200flow.data.synthetic import coco_like
+from b200flow.models.maskrcnn import MaskRCNN, MaskRCNNConfig
+from b200flow.obs.tracking import Tracker, maybe_inject_fault
+from b200flow.optim import FlatMomentumSGD
+from b200flow.parallel.ddp import DistributedDataParallel
+from b200flow.parallel.groups import init_distributed
+
+
+def parse_config(items):
+    cfg = {}
+    for it in items or []:
+        k, _, v = it.partition("=")
+        try:
+            cfg[k] = ast.literal_eval(v)
+        except (ValueError, SyntaxError):
+            cfg[k] = v
+    return cfg
+
+
+def lr_at(step, base_lr, world, batch, warmup, boundaries):
+    """tensorpack scales BASE_LR by total batch / 8 and decays 10x at each boundary (given for
+    a total batch of 8); linear warm-up from lr/3."""
+    lr = base_lr * (world * batch) / 8.0
+    scale = 8.0 / (world * batch)
+    if step < warmup:
+        return lr * (1 / 3 + (2 / 3) * step / max(1, warmup))
+    for i, b in enumerate(boundaries):
+        if step < b * scale:
+            return lr * (0.1 ** i)
+    return lr * (0.1 ** len(boundaries))
+
+
+def ap50(dets, gts):
+    """Class-aware box AP at IoU 0.5 over a list of images (simple all-point interpolation)."""
+    import torchvision
+
+    recs, npos = [], 0
+    for d, g in zip(dets, gts):
+        npos += g["boxes"].shape[0]
+        used = torch.zeros(g["boxes"].shape[0], dtype=torch.bool)
+        for b, s, l in zip(d["boxes"].cpu(), d["scores"].cpu(), d["labels"].cpu()):
+            ok = False
+            if g["boxes"].numel():
+                iou = torchvision.ops.box_iou(b[None], g["boxes"].cpu().float())[0]
+                iou[(g["labels"].cpu() != l) | used] = 0
+                j = int(iou.argmax())
+                if iou[j] >= 0.5:
+                    used[j] = ok = True
+            recs.append((float(s), ok))
+    if not recs or npos == 0:
+        return 0.0
+    recs.sort(key=lambda t: -t[0])
+    tp = torch.tensor([r[1] for r in recs], dtype=torch.float32).cumsum(0)
+    prec = tp / torch.arange(1, len(recs) + 1)
+    rec = tp / npos
+    ap, prev = 0.0, 0.0
+    for i in range(len(recs)):
+        ap += float(prec[i:].max()) * (float(rec[i]) - prev)
+        prev = float(rec[i])
+    return ap
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--logdir", required=True)
+    ap.add_argument("--images_per_epoch", type=int, default=None)
+    ap.add_argument("--config", nargs="*", default=[])
+    ap.add_argument("--load", default=None)
+    args, unknown = ap.parse_known_args()
+    cfgd = parse_config(args.config)
+    use_cuda = torch.cuda.is_available()
+    rank, local_rank, world = init_distributed("nccl" if use_cuda else "gloo") if "RANK" in os.environ else (0, 0, 1)
+    dev = torch.device("cuda", torch.cuda.current_device()) if use_cuda else torch.device("cpu")
+    batch = int(cfgd.get("TRAIN.BATCH_SIZE_PER_GPU", 1))
+    ipe = args.images_per_epoch
+    steps_per_epoch = int(os.environ.get("B2F_MRCNN_STEPS", 0)) or (
+        ipe // (world * batch) if ipe else int(cfgd.get("TRAIN.STEPS_PER_EPOCH", 7500)))
+    if "TRAIN.LR_EPOCH_SCHEDULE" in cfgd:      # [(16, 0.1), (20, 0.01), (24, None)] in epochs
+        sched = cfgd["TRAIN.LR_EPOCH_SCHEDULE"]
+        total_epochs = sched[-1][0]
+        boundaries = [e * 120000 // 8 for e, _ in sched[:-1]]
+    else:
+        boundaries = list(cfgd.get("TRAIN.LR_SCHEDULE", [240000, 320000, 360000]))
+        total_epochs = max(1, int(boundaries[-1] * 8 / (world * batch)) // max(1, steps_per_epoch))
+        boundaries = boundaries[:-1]
+    total_epochs = int(os.environ.get("B2F_MRCNN_EPOCHS", total_epochs))
+    H, W = (int(v) for v in os.environ.get("B2F_MRCNN_IMAGE", "800x1344").split("x"))
+    width = float(os.environ.get("B2F_MRCNN_WIDTH", 1.0))
+    mcfg = MaskRCNNConfig(mode_mask=bool(cfgd.get("MODE_MASK", True)), mode_fpn=bool(cfgd.get("MODE_FPN", True)),
+                          width=width)
+    if width < 1.0:
+        mcfg.rpn_pre_nms_train = mcfg.rpn_post_nms_train = 300
+        mcfg.rpn_pre_nms_test = mcfg.rpn_post_nms_test = 200
+        mcfg.roi_batch = 128
+    torch.manual_seed(1234)
+    model = MaskRCNN(mcfg).to(dev)
+    if use_cuda:
+        model = model.to(torch.bfloat16).to(memory_format=torch.channels_last)
+    ddp = DistributedDataParallel(model) if world > 1 else None
+    if ddp is None:
+        from b200flow.utils.flat import FlatParams
+
+        flat = FlatParams(model)
+    else:
+        flat = ddp.flat
+    opt = FlatMomentumSGD(flat, lr=float(cfgd.get("TRAIN.BASE_LR", 0.01)), momentum=0.9, weight_decay=1e-4)
+    clip = float(cfgd.get("TRAIN.GRADIENT_CLIP", 0) or 0)
+    logdir = Path(args.logdir)
+    if rank == 0:
+        logdir.mkdir(parents=True, exist_ok=True)
+        (logdir / "config.json").write_text(json.dumps({"config": cfgd, "world": world}, default=str, indent=1))
+    tracker = Tracker(logdir, ".") if rank == 0 else None
+    # ---- auto-resume from <logdir>/checkpoint (tensorpack behaviour)
+    step = 0
+    ckfile = logdir / "checkpoint"
+    if ckfile.exists():
+        name = json.loads(ckfile.read_text())["model_checkpoint_path"]
+        sd = torch.load(logdir / (name + ".pt"), map_location="cpu", weights_only=False)
+        model.load_state_dict(sd["model"])
+        opt.load_state_dict({k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in sd["optimizer"].items()})
+        step = sd["global_step"]
+        if rank == 0:
+            print(f"[b200flow] resumed from {name} (step {step})", flush=True)
+    warmup = int(cfgd.get("TRAIN.WARMUP", min(1000, steps_per_epoch)))
+    ckpt_period = int(cfgd.get("TRAIN.CHECKPOINT_PERIOD", 1))
+    eval_period = int(cfgd.get("TRAIN.EVAL_PERIOD", 1))
+    data = coco_like(10 ** 9, H, W, seed=1000 + rank, device="cpu")
+    start_epoch = step // max(1, steps_per_epoch)
+    for epoch in range(start_epoch + 1, total_epochs + 1):
+        model.train()
+        t0, seen, agg = time.time(), 0, {}
+        for _ in range(steps_per_epoch):
+            maybe_inject_fault(step)
+            samples = [next(data) for _ in range(batch)]
+            imgs = torch.stack([s["image"] for s in samples]).to(dev)
+            if use_cuda:
+                imgs = imgs.to(torch.bfloat16)
+            tg = [{k: s[k].to(dev) for k in ("boxes", "labels", "masks")} for s in samples]
+            opt.param_groups[0]["lr"] = lr_at(step, float(cfgd.get("TRAIN.BASE_LR", 0.01)), world, batch,
+                                              warmup, boundaries)
+            opt.zero_grad()
+            losses = model(imgs, tg)
+            losses["total"].backward()
+            flat.collect_autograd_grads()
+            if ddp is not None:
+                ddp.finish_reduction()
+            if clip > 0:
+                gn = flat.grads.norm()
+                opt.grad_scale = (clip / (gn + 1e-6)).clamp(max=1.0).reshape(1)
+            opt.step()
+            step += 1
+            seen += batch * world
+            for k, v in losses.items():
+                agg[k] = agg.get(k, 0.0) + float(v.detach())
+        dt = time.time() - t0
+        if rank == 0:
+            msg = {k: v / steps_per_epoch for k, v in agg.items()}
+            print(f"[epoch {epoch}] step {step} | " + " ".join(f"{k}={v:.4f}" for k, v in msg.items()) +
+                  f" | lr={opt.param_groups[0]['lr']:.5f} | throughput={seen / dt:.2f} images/s", flush=True)
+            tracker.log({**{f"loss/{k}": v for k, v in msg.items()}, "learning_rate": opt.param_groups[0]["lr"],
+                         "throughput/images_per_sec": seen / dt}, step)
+        if epoch % eval_period == 0:
+            model.eval()
+            val = list(coco_like(4, H, W, seed=77 + rank, device="cpu"))
+            with torch.no_grad():
+                vi = torch.stack([s["image"] for s in val]).to(dev)
+                dets = model(vi.to(torch.bfloat16) if use_cuda else vi)
+            score = ap50(dets, val)
+            if world > 1:
+                t = torch.tensor([score], device=dev)
+                dist.all_reduce(t)
+                score = float(t) / world
+            if rank == 0:
+                print(f"[epoch {epoch}] val box AP@0.5 = {score:.4f}", flush=True)
+                tracker.log({"val/box_AP50": score}, step)
+        if epoch % ckpt_period == 0 and rank == 0:
+            name = f"model-{step}"
+            torch.save({"model": model.state_dict(), "optimizer": opt.state_dict(), "global_step": step,
+                        "config": cfgd, "model_config": mcfg.__dict__}, logdir / (name + ".pt"))
+            (logdir / (name + ".index")).write_text(name + ".pt\n")
+            ckfile.write_text(json.dumps({"model_checkpoint_path": name}))
+        if world > 1:
+            dist.barrier()
+    if tracker:
+        tracker.finish()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -214,6 +214,28 @@ scale_kernel(void* __restrict__ x, long long n, const float* __restrict__ scale_
   }
 }
 
+// Momentum SGD on a flat buffer (tensorpack's MomentumOptimizer(0.9) of the Mask R-CNN
+// workloads): buf = mu * buf + (g * scale + wd * p); p -= lr * buf; bf16 working copy out.
+template <bool GRAD_BF16>
+__global__ void __launch_bounds__(256)
+sgd_momentum_flat_kernel(float* __restrict__ master, float* __restrict__ buf,
+                         const void* __restrict__ grad, __nv_bfloat16* __restrict__ param_out,
+                         long long n, float lr, float mu, float wd,
+                         const float* __restrict__ grad_scale) {
+  const float gs = grad_scale ? *grad_scale : 1.f;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const float g = (GRAD_BF16 ? __bfloat162float(static_cast<const __nv_bfloat16*>(grad)[i])
+                               : static_cast<const float*>(grad)[i]) * gs;
+    float p = master[i];
+    const float b = mu * buf[i] + g + wd * p;
+    p -= lr * b;
+    buf[i] = b;
+    master[i] = p;
+    if (param_out) param_out[i] = __float2bfloat16(p);
+  }
+}
+
 inline int grid_for(long long n, int per_thread) {
   long long blocks = (n / per_thread + 255) / 256;
   const long long cap = (long long)b2f::sm_count() * 8;
@@ -259,6 +281,22 @@ extern "C" int b2f_adamw_multi(const void* segs, int nsegs, long long total_chun
   else
     adamw_multi_kernel<false><<<(unsigned)total_chunks, 256, 0, st>>>((const Segment*)segs, nsegs,
                                                                       h, grad_scale, skip);
+  B2F_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b2f_sgd_momentum_flat(float* master, float* buf, const void* grad, int grad_bf16,
+                                     void* param_out, long long n, float lr, float momentum,
+                                     float weight_decay, const float* grad_scale, void* stream) {
+  if (n <= 0) return 0;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int grid = grid_for(n, 1);
+  if (grad_bf16)
+    sgd_momentum_flat_kernel<true><<<grid, 256, 0, st>>>(master, buf, grad, (__nv_bfloat16*)param_out, n,
+                                                         lr, momentum, weight_decay, grad_scale);
+  else
+    sgd_momentum_flat_kernel<false><<<grid, 256, 0, st>>>(master, buf, grad, (__nv_bfloat16*)param_out,
+                                                          n, lr, momentum, weight_decay, grad_scale);
   B2F_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -64,6 +64,9 @@ int b2f_adamw_flat(float* master, float* m, float* v, const void* grad, int grad
 int b2f_adamw_multi(const void* segs, int nsegs, long long total_chunks, int grad_bf16, float lr,
                     float beta1, float beta2, float eps, float weight_decay, int step,
                     const float* grad_scale, const int* skip, void* stream);
+int b2f_sgd_momentum_flat(float* master, float* buf, const void* grad, int grad_bf16, void* param_out,
+                          long long n, float lr, float momentum, float weight_decay,
+                          const float* grad_scale, void* stream);
 int b2f_multi_tensor_chunk(void);
 int b2f_sumsq_num_partials(long long n);
 /* scratch: fp32 [b2f_sumsq_num_partials(n)] */
@@ -140,6 +143,28 @@ int b2f_gemm_rs_bf16(const void* X, const void* B, void* Y_shard, int T, int N, 
                      long long ldx, long long ldb, long long ldy, int b_mn_major, const void* bias,
                      const void* residual, long long ldr, const long long* recv_ptrs,
                      const long long* flag_ptrs, int rank, int world, unsigned epoch, void* stream);
+
+/* ---- K12-K15: Mask R-CNN detection kernels (tf.image.crop_and_resize / non_max_suppression,
+ * tensorpack model_box / model_frcnn / model_mrcnn).  Features are NHWC bf16, one pointer per
+ * FPN level (P2..P5); rois: fp32 [R, 5] = (image, x1, y1, x2, y2). */
+int b2f_roi_align_fwd(const void* const* feats, const int* H, const int* W, const float* scales,
+                      int levels, int C, const float* rois, int R, int P, int sampling, int aligned,
+                      void* out, void* stream);
+int b2f_roi_align_bwd(const void* const* feats, float* const* grads, const int* H, const int* W,
+                      const float* scales, int levels, int C, const float* rois, int R, int P,
+                      int sampling, int aligned, const void* dout, void* stream);
+int b2f_box_decode(const float* anchors, const float* deltas, float* out, long long n, float wx,
+                   float wy, float ww, float wh, float img_w, float img_h, void* stream);
+/* mask_scratch: u64 [total_boxes * ceil(max_seg / 64)] */
+int b2f_nms_batched(const float* boxes, const int* seg_off, int num_segs, int max_seg, float iou_thr,
+                    unsigned long long* mask_scratch, unsigned char* keep, void* stream);
+int b2f_match_proposals(const float* props, const int* prop_batch, long long n, const float* gts,
+                        const int* gt_off, float* best_iou, int* best_idx, void* stream);
+int b2f_pairwise_iou(const float* a, long long na, const float* b, int nb, float* out, void* stream);
+int b2f_mask_crop(const unsigned char* masks, int H, int W, const float* rois, const int* gt_index,
+                  int R, int M, float* out, void* stream);
+int b2f_mask_paste(const float* probs, int M, const float* boxes, int R, int H, int W, float thr,
+                   unsigned char* out, void* stream);
 
 #ifdef __cplusplus
 }
