@@ -112,13 +112,17 @@ class FCHead(nn.Module):
         mk = lambda o, i, std: nn.Parameter(torch.empty(o, i).normal_(0, std))  # noqa: E731
         self.w6, self.b6 = mk(fc, in_dim, math.sqrt(2.0 / in_dim)), nn.Parameter(torch.zeros(fc))
         self.w7, self.b7 = mk(fc, fc, math.sqrt(2.0 / fc)), nn.Parameter(torch.zeros(fc))
-        self.wc, self.bc = mk(ncls, fc, 0.01), nn.Parameter(torch.zeros(ncls))
-        self.wb, self.bb = mk(ncls * 4, fc, 0.001), nn.Parameter(torch.zeros(ncls * 4))
+        # predictor widths are padded to a multiple of 8 (16-byte rows for the TMA-fed GEMMs)
+        self.ncls = ncls
+        pc, pb = (ncls + 7) // 8 * 8, (ncls * 4 + 7) // 8 * 8
+        self.wc, self.bc = mk(pc, fc, 0.01), nn.Parameter(torch.zeros(pc))
+        self.wb, self.bb = mk(pb, fc, 0.001), nn.Parameter(torch.zeros(pb))
 
     def forward(self, x):
         x = F.relu(G.linear(x, self.w6, self.b6))
         x = F.relu(G.linear(x, self.w7, self.b7))
-        return G.linear(x, self.wc, self.bc).float(), G.linear(x, self.wb, self.bb).float()
+        return (G.linear(x, self.wc, self.bc)[:, :self.ncls].float(),
+                G.linear(x, self.wb, self.bb)[:, :self.ncls * 4].float())
 
 
 class MaskHead(nn.Module):

@@ -50,6 +50,10 @@ def test_attention_backward():
     _run("attn_bwd")
 
 
+def test_detection_kernels():
+    _run("detection")
+
+
 def test_native_library_is_loaded():
     from b200flow.ops import _lib
 

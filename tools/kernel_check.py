@@ -27,7 +27,7 @@ RESULTS = []
 
 def report(name, got, ref, tol):
     got = got.float()
-    ref = ref.float()
+    ref = ref.float().to(got.device)
     err = (got - ref).abs()
     denom = ref.abs().max().item() + 1e-6
     rel = err.max().item() / denom
@@ -371,7 +371,123 @@ def group_attn_perf():
         RESULTS.append({"name": rec["name"], "ok": True})
 
 
+def group_detection():
+    import torchvision
+    from b200flow.ops import detection as Dt
+    torch.manual_seed(6)
+    # --- K12 RoIAlign fwd/bwd vs torchvision CPU (fp32), multilevel
+    C = 64
+    shapes = [(2, 200, 336), (2, 100, 168), (2, 50, 84), (2, 25, 42)]
+    scales = [0.25, 0.125, 0.0625, 0.03125]
+    feats = [torch.randn(n, h, w, C, device=DEV).to(torch.bfloat16).requires_grad_() for n, h, w in shapes]
+    R = 300
+    xy = torch.rand(R, 2, device=DEV) * torch.tensor([1000.0, 600.0], device=DEV)
+    wh = torch.rand(R, 2, device=DEV) * 500 + 8
+    rois = torch.cat([torch.randint(0, 2, (R, 1), device=DEV).float(), xy, xy + wh], 1)
+    for P in (7, 14):
+        out = Dt.roi_align(feats, scales, rois, P)
+        dout = torch.randn_like(out)
+        for f in feats:
+            f.grad = None
+        out.backward(dout)
+        lv = Dt.fpn_level_of(rois.cpu())
+        ref = torch.zeros(R, P, P, C)
+        cf = [f.detach().float().cpu().permute(0, 3, 1, 2).requires_grad_() for f in feats]
+        parts = []
+        for i in range(4):
+            idx = (lv == i).nonzero().flatten()
+            if idx.numel():
+                o = torchvision.ops.roi_align(cf[i], rois.cpu()[idx], P, scales[i], 2, True)
+                ref[idx] = o.permute(0, 2, 3, 1)
+                parts.append((o * dout.float().cpu()[idx].permute(0, 3, 1, 2)).sum())
+        sum(parts).backward()
+        report(f"roi_align_fwd_P{P}", out.reshape(R, -1), ref.reshape(R, -1), 2e-2)
+        for i in range(4):
+            if cf[i].grad is not None:
+                report(f"roi_align_bwd_P{P}_L{i}", feats[i].grad.permute(0, 3, 1, 2).reshape(2, -1),
+                       cf[i].grad.reshape(2, -1), 3e-2)
+    # --- K13 decode + NMS
+    n = 5000
+    anchors = torch.rand(n, 2, device=DEV) * 800
+    anchors = torch.cat([anchors, anchors + torch.rand(n, 2, device=DEV) * 200 + 4], 1)
+    deltas = torch.randn(n, 4, device=DEV) * 0.3
+    got = Dt.box_decode(anchors, deltas, (10.0, 10.0, 5.0, 5.0), 1344.0, 800.0)
+    report("box_decode", got, Dt.box_decode(anchors.cpu(), deltas.cpu(), (10.0, 10.0, 5.0, 5.0), 1344.0, 800.0), 1e-4)
+    segs = [2000, 1333, 64, 1, 700]
+    boxes = []
+    for m in segs:
+        c = torch.rand(m, 2, device=DEV) * 600
+        boxes.append(torch.cat([c, c + torch.rand(m, 2, device=DEV) * 150 + 10], 1))
+    boxes = torch.cat(boxes)
+    off = torch.tensor([0] + segs, device=DEV).cumsum(0).int()
+    keep = Dt.nms_batched(boxes, off, 0.7)
+    ref_keep = Dt.nms_batched(boxes.cpu(), off.cpu(), 0.7)
+    report("nms_batched", keep.float().reshape(1, -1), ref_keep.float().reshape(1, -1), 1e-6)
+    # --- K14 matcher / IoU
+    gts = boxes[:40].clone()
+    gt_off = torch.tensor([0, 25, 40], device=DEV).int()
+    pb = torch.randint(0, 2, (3000,), device=DEV).int()
+    bi, bj = Dt.match_proposals(boxes[:3000], pb, gts, gt_off)
+    rbi, rbj = Dt.match_proposals(boxes[:3000].cpu(), pb.cpu(), gts.cpu(), gt_off.cpu())
+    report("match_iou", bi.reshape(1, -1), rbi.reshape(1, -1), 1e-4)
+    agree = ((bj.cpu() == rbj) | (rbi < 1e-6)).float().mean().item()
+    RESULTS.append({"name": "match_idx", "ok": agree > 0.999, "agree": agree}); print(json.dumps(RESULTS[-1]), flush=True)
+    report("pairwise_iou", Dt.pairwise_iou(boxes[:500], gts), torchvision.ops.box_iou(boxes[:500].cpu(), gts.cpu()), 1e-4)
+    # --- K15 mask crop / paste
+    H, W = 200, 300
+    masks = (torch.rand(6, H, W, device=DEV) > 0.5).to(torch.uint8)
+    masks[:, 50:150, 80:220] = 1
+    rois4 = torch.tensor([[60.0, 40, 250, 170], [0, 0, 299, 199], [100, 90, 130, 120], [10.5, 20.25, 80.75, 99.5]], device=DEV)
+    gi = torch.tensor([0, 3, 5, 2], device=DEV).int()
+    got = Dt.mask_crop(masks, rois4, gi, 28)
+    ref = Dt.mask_crop_ref(masks.cpu(), rois4.cpu(), gi.cpu(), 28)
+    frac = (got.cpu() == ref).float().mean().item()
+    RESULTS.append({"name": "mask_crop", "ok": frac > 0.99, "agree": frac}); print(json.dumps(RESULTS[-1]), flush=True)
+    probs = torch.rand(4, 28, 28, device=DEV)
+    got = Dt.mask_paste(probs, rois4, H, W)
+    ref = Dt.mask_paste_ref(probs.cpu(), rois4.cpu(), H, W)
+    frac = (got.cpu() == ref).float().mean().item()
+    RESULTS.append({"name": "mask_paste", "ok": frac > 0.995, "agree": frac}); print(json.dumps(RESULTS[-1]), flush=True)
+
+
+def group_maskrcnn_step():
+    from b200flow.data.synthetic import coco_like
+    from b200flow.models.maskrcnn import MaskRCNN, MaskRCNNConfig, paste_masks
+    from b200flow.optim import FlatMomentumSGD
+    from b200flow.utils.flat import FlatParams
+    torch.manual_seed(0)
+    model = MaskRCNN(MaskRCNNConfig()).to(DEV).to(torch.bfloat16).to(memory_format=torch.channels_last)
+    flat = FlatParams(model)
+    opt = FlatMomentumSGD(flat, lr=0.005)
+    data = list(coco_like(2, 800, 1344, seed=3))
+    imgs = torch.stack([s["image"] for s in data]).to(DEV).to(torch.bfloat16)
+    tg = [{k: s[k].to(DEV) for k in ("boxes", "labels", "masks")} for s in data]
+    model.train()
+    ls = []
+    for _ in range(4):
+        opt.zero_grad()
+        l = model(imgs, tg)
+        l["total"].backward()
+        flat.collect_autograd_grads()
+        opt.step()
+        ls.append(float(l["total"]))
+    RESULTS.append({"name": "maskrcnn_r50fpn_train", "ok": ls[-1] < ls[0] and all(x == x for x in ls), "losses": ls})
+    print(json.dumps(RESULTS[-1]), flush=True)
+    def step():
+        opt.zero_grad(); l = model(imgs, tg); l["total"].backward(); flat.collect_autograd_grads(); opt.step()
+    t = timeit(step, iters=5, warmup=2)
+    model.eval()
+    with torch.no_grad():
+        det = model(imgs)
+    pm = paste_masks(det[0], 800, 1344)
+    RESULTS.append({"name": "maskrcnn_r50fpn_perf", "ok": True, "ms_per_step_bs2": t, "images_per_s": 2 / (t / 1e3),
+                    "dets": int(det[0]["boxes"].shape[0]), "pasted": list(pm.shape)})
+    print(json.dumps(RESULTS[-1]), flush=True)
+
+
 GROUPS = {
+    "detection": group_detection,
+    "maskrcnn_step": group_maskrcnn_step,
     "attn_fwd": lambda: group_attn("fwd"),
     "attn_bwd": lambda: group_attn("bwd"),
     "attn_perf": group_attn_perf,
