@@ -34,7 +34,7 @@ from ..utils.flat import FlatParams
 _KNOWN = {"train_micro_batch_size_per_gpu", "gradient_accumulation_steps", "zero_optimization",
           "bf16", "fp16", "gradient_clipping", "optimizer", "wall_clock_breakdown",
           "train_batch_size", "steps_per_print", "scheduler", "fused_collectives",
-          "activation_checkpointing", "sequence_parallel"}
+          "activation_checkpointing", "sequence_parallel", "expert_parallel_size"}
 
 
 def split_layers(num_layers: int, stages: int) -> list[tuple[int, int]]:
@@ -86,11 +86,31 @@ class TrainEngine:
                             sequence_parallel=bool(config.get("sequence_parallel", True)),
                             fused=fused_tp) if tp_world > 1 else SINGLE
 
+        # expert parallelism: EP groups are carved out of the DP dimension
+        self.ep_world = ps.topo.ep if ps else 1
+        self.ep_ctx = None
+        if model_config.num_experts and self.ep_world > 1:
+            from ..parallel.moe import EPContext
+
+            ep_rank = ps.ep_ranks.index(ps.rank)
+            comm = None
+            if use_fused:
+                from ..comm.arena import PeerComm
+
+                comm = PeerComm(ps.ep_group, ep_rank, self.ep_world, self.device)
+            self.ep_ctx = EPContext(ps.ep_group, self.ep_world, ep_rank, comm)
         # same init on every TP/DP replica of a stage, different across TP shards
         torch.manual_seed(seed + 1000 * self.stage + (ps.tp_rank if ps else 0))
         lo, hi = split_layers(model_config.layers, pp_world)[self.stage]
         self.model = GPTModel(model_config, self.tp, (lo, hi), pre=self.stage == 0,
-                              post=self.stage == pp_world - 1, dtype=dtype, device=self.device)
+                              post=self.stage == pp_world - 1, dtype=dtype, device=self.device,
+                              ep=self.ep_ctx, fused_moe=use_fused)
+        if model_config.num_experts and self.ep_world > 1:
+            # every EP rank holds different experts: re-draw them with a rank-dependent seed
+            g = torch.Generator(device=self.device).manual_seed(seed + 7919 * (self.ep_ctx.rank + 1))
+            for n, p in self.model.named_parameters():
+                if getattr(p, "is_expert", False) and p.dim() > 2:
+                    p.data.normal_(0, model_config.init_std, generator=g)
         self.model.recompute = bool(config.get("activation_checkpointing", {}).get("enabled", False))
         self.dp_comm = None
         allocator = None
@@ -99,7 +119,14 @@ class TrainEngine:
 
             self.dp_comm = PeerComm(ps.dp_group, ps.dp_rank, dp_world, self.device)
             allocator = self.dp_comm.allocator()
-        self.flat = FlatParams(self.model, pad_to_multiple=max(1, dp_world) * 128, allocator=allocator)
+        is_exp = lambda n, p: getattr(p, "is_expert", False)          # noqa: E731
+        self.flat = FlatParams(self.model, pad_to_multiple=max(1, dp_world) * 128, allocator=allocator,
+                               param_filter=lambda n, p: not is_exp(n, p))
+        has_experts = any(is_exp(n, p) for n, p in self.model.named_parameters())
+        self.flat_expert = None
+        if has_experts:
+            edp = dp_world // self.ep_world
+            self.flat_expert = FlatParams(self.model, pad_to_multiple=max(1, edp) * 128, param_filter=is_exp)
         if dp_world > 1:  # replicas start identical
             dist.broadcast(self.flat.params, src=ps.dp_ranks[0], group=ps.dp_group)
 
@@ -116,6 +143,14 @@ class TrainEngine:
         norm_groups = [ps.tp_group, ps.pp_group] if ps else []
         self.optimizer = Zero1Optimizer(self.flat, acfg, ps.dp_group if ps else None, dp_world,
                                         ps.dp_rank if ps else 0, norm_groups, fused=fused_dp)
+        self.expert_optimizer = None
+        if self.flat_expert is not None:
+            edp = dp_world // self.ep_world
+            eg = ps.expert_dp_group if (ps and self.ep_world > 1) else (ps.dp_group if ps else None)
+            er = (ps.dp_rank // self.ep_world) if ps else 0
+            extra = [ps.ep_group] if (ps and self.ep_world > 1) else []
+            self.expert_optimizer = Zero1Optimizer(self.flat_expert, acfg, eg if edp > 1 else None, edp,
+                                                   er if edp > 1 else 0, norm_groups + extra)
         self._sync_tied_weights()
         if self.pp_world > 1 and self.cfg.tie_embeddings and self.stage == pp_world - 1:
             o = self.optimizer      # master copy of the re-tied head rows
@@ -151,6 +186,8 @@ class TrainEngine:
         `data_iter` yields (tokens[b, s], labels[b, s]) device tensors; every pipeline stage
         of a DP replica must see the same micro-batches (the caller's loader guarantees it)."""
         self.optimizer.zero_grad()
+        if self.expert_optimizer is not None:
+            self.expert_optimizer.zero_grad()
         batches = [next(data_iter) for _ in range(self.gas)]
         if self.pp_world == 1:
             losses = []
@@ -163,10 +200,15 @@ class TrainEngine:
             losses = PP.run_1f1b(self.stage, self.pp_world, self.gas,
                                  lambda i, act: self._forward_micro(batches[i], act), self._p2p(seq))
         self.flat.collect_autograd_grads()
+        if self.flat_expert is not None:
+            self.flat_expert.collect_autograd_grads()
         allreduce_replicated_grads(self.flat, self.tp)
         self._reduce_tied_grads()
         self._apply_lr()
         self.optimizer.step(grad_divisor=float(self.gas * self.dp_world))
+        if self.expert_optimizer is not None:
+            self.expert_optimizer.lr = self.optimizer.lr
+            self.expert_optimizer.step(grad_divisor=float(self.gas * self.dp_world))
         self.global_steps += 1
         loss = torch.stack(losses).mean() if losses else torch.zeros((), device=self.device)
         if self.pp_world > 1:  # make the loss visible on every stage (for logging)

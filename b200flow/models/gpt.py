@@ -44,6 +44,10 @@ class GPTConfig:
     init_std: float = 0.02
     dropout: float = 0.0
     name: str = "llama"
+    num_experts: int = 0          # > 0: MoE FFN every `moe_every`-th layer (DeepSpeed --num-experts)
+    moe_every: int = 2            # --expert-interval
+    capacity_factor: float = 1.0
+    aux_loss_coeff: float = 0.01
 
     def __post_init__(self):
         if self.kv_heads is None:
@@ -60,7 +64,10 @@ class GPTConfig:
         mlp = self.hidden * self.ffn * (3 if self.act == "swiglu" else 2)
         per_layer = qkv + proj + mlp + 2 * self.hidden
         emb = self.vocab_size * self.hidden * (1 if self.tie_embeddings else 2)
-        return self.layers * per_layer + emb + self.hidden
+        total = self.layers * per_layer + emb + self.hidden
+        if self.num_experts:
+            total += (self.layers // self.moe_every) * (self.num_experts - 1) * mlp
+        return total
 
     def flops_per_token(self, seq: int) -> float:
         """Model FLOPs (fwd+bwd) per token, causal attention counted at half."""
@@ -79,6 +86,13 @@ PRESETS = {
     "gpt2-345m": dict(vocab_size=50304, hidden=1024, layers=24, heads=16, ffn=4096, max_seq=1024,
                       norm="ln", act="gelu", rope=False, learned_pos=True, bias=True,
                       tie_embeddings=True, name="gpt2"),
+    # GPT-MoE 1.3B, 8 experts (BASELINE.json config 5; [UP] ds_pretrain_gpt_1.3B_MoE*.sh)
+    "gpt-moe-1.3b": dict(vocab_size=50304, hidden=2048, layers=24, heads=16, ffn=8192, max_seq=2048,
+                         norm="ln", act="gelu", rope=False, learned_pos=True, bias=True,
+                         tie_embeddings=True, name="gpt-moe", num_experts=8, moe_every=2),
+    "gpt-moe-tiny": dict(vocab_size=1024, hidden=128, layers=4, heads=4, ffn=256, max_seq=128,
+                         norm="ln", act="gelu", rope=False, learned_pos=True, bias=True,
+                         tie_embeddings=True, name="gpt-moe", num_experts=4, moe_every=2),
     "llama-tiny": dict(vocab_size=1024, hidden=256, layers=2, heads=2, ffn=512, max_seq=256),
     "gpt2-tiny": dict(vocab_size=1024, hidden=256, layers=2, heads=4, ffn=1024, max_seq=256,
                       norm="ln", act="gelu", rope=False, learned_pos=True, bias=True,
@@ -158,9 +172,11 @@ def qkv_attention(qkv, heads, kv_heads, causal, scale, rope_tables=None, kv_lens
 class TransformerLayer(nn.Module):
     """Pre-norm decoder block. `tp` supplies the (possibly fused-collective) linears."""
 
-    def __init__(self, cfg: GPTConfig, tp, layer_idx: int, dtype=torch.bfloat16, device=None):
+    def __init__(self, cfg: GPTConfig, tp, layer_idx: int, dtype=torch.bfloat16, device=None, ep=None,
+                 fused_moe: bool = True):
         super().__init__()
         self.cfg, self.tp, self.layer_idx = cfg, tp, layer_idx
+        self.is_moe = cfg.num_experts > 0 and (layer_idx + 1) % cfg.moe_every == 0
         d = cfg.head_dim
         assert cfg.heads % tp.world == 0 and cfg.kv_heads % tp.world == 0 and cfg.ffn % tp.world == 0
         self.h_local = cfg.heads // tp.world
@@ -180,13 +196,23 @@ class TransformerLayer(nn.Module):
         self.wqkv = nn.Parameter(torch.empty((self.h_local + 2 * self.kv_local) * d, H, **kw).normal_(0, std))
         self.wo = nn.Parameter(torch.empty(H, self.h_local * d, **kw).normal_(0, out_std))
         n_up = 2 * ffn_local if cfg.act == "swiglu" else ffn_local
-        self.w1 = nn.Parameter(torch.empty(n_up, H, **kw).normal_(0, std))       # gate|up or fc1
-        self.w2 = nn.Parameter(torch.empty(H, ffn_local, **kw).normal_(0, out_std))
+        self.moe = None
+        if self.is_moe:
+            from ..parallel.moe import MoELayer
+
+            assert tp.world == 1 and cfg.act == "gelu", "MoE layers: TP=1, GELU experts (GPT-MoE recipe)"
+            self.moe = MoELayer(H, cfg.ffn, cfg.num_experts, ep, cfg.capacity_factor, act="gelu",
+                                aux_loss_coeff=cfg.aux_loss_coeff, init_std=std, dtype=dtype, device=device,
+                                fused=fused_moe)
+            self.w1 = self.w2 = None
+        else:
+            self.w1 = nn.Parameter(torch.empty(n_up, H, **kw).normal_(0, std))       # gate|up or fc1
+            self.w2 = nn.Parameter(torch.empty(H, ffn_local, **kw).normal_(0, out_std))
         if cfg.bias:
             self.bqkv = nn.Parameter(torch.zeros(self.wqkv.shape[0], **kw))
             self.bo = nn.Parameter(torch.zeros(H, **kw))
-            self.b1 = nn.Parameter(torch.zeros(n_up, **kw))
-            self.b2 = nn.Parameter(torch.zeros(H, **kw))
+            self.b1 = None if self.is_moe else nn.Parameter(torch.zeros(n_up, **kw))
+            self.b2 = None if self.is_moe else nn.Parameter(torch.zeros(H, **kw))
         else:
             self.bqkv = self.bo = self.b1 = self.b2 = None
         # parameters replicated across the TP group need their grads all-reduced there
@@ -204,6 +230,8 @@ class TransformerLayer(nn.Module):
                           self.kv_local, True, 1.0 / math.sqrt(d), rope_tables, kv_lens)
         h = tp.row_linear(o, self.wo, self.bo, residual=h)           # residual fused in the epilogue
         y = N.norm(h, self.ln2_w, self.ln2_b, eps=cfg.eps, rms=rms)
+        if self.moe is not None:
+            return h + self.moe(y)
         if cfg.act == "swiglu":
             a = E.swiglu(tp.column_linear(y, self.w1, self.b1))
         else:
@@ -263,7 +291,8 @@ class GPTModel(nn.Module):
     """Full model (or one pipeline stage of it: `layer_range`, `pre`, `post`)."""
 
     def __init__(self, cfg: GPTConfig, tp=None, layer_range: tuple[int, int] | None = None,
-                 pre: bool = True, post: bool = True, dtype=torch.bfloat16, device=None):
+                 pre: bool = True, post: bool = True, dtype=torch.bfloat16, device=None, ep=None,
+                 fused_moe: bool = True):
         super().__init__()
         from ..parallel.tensor_parallel import SINGLE
 
@@ -273,7 +302,7 @@ class GPTModel(nn.Module):
         self.layer_range = (lo, hi)
         self.embed = Embedding(cfg, self.tp, dtype, device) if pre else None
         self.layers = nn.ModuleList(
-            [TransformerLayer(cfg, self.tp, i, dtype, device) for i in range(lo, hi)])
+            [TransformerLayer(cfg, self.tp, i, dtype, device, ep, fused_moe) for i in range(lo, hi)])
         if post:
             tied = self.embed.wte if (cfg.tie_embeddings and pre) else None
             self.head = LMHead(cfg, self.tp, tied, dtype, device)
@@ -302,5 +331,11 @@ class GPTModel(nn.Module):
             else:
                 h = layer(h, seq, batch, rope, kv_lens)
         if self.head is not None and labels is not None:
-            return self.head(h, labels)
+            loss = self.head(h, labels)
+            if self.cfg.num_experts:
+                aux = [l.moe.last_aux for l in self.layers if l.moe is not None and l.moe.last_aux is not None]
+                if aux:
+                    self.last_lm_loss = loss.detach()
+                    loss = loss + self.cfg.aux_loss_coeff * torch.stack(aux).sum()
+            return loss
         return h

@@ -29,10 +29,11 @@ class FlatParams:
     """Re-homes the parameters of `module` into flat storage (in registration order)."""
 
     def __init__(self, module: nn.Module, *, grad_dtype: torch.dtype = torch.float32,
-                 align: int = 128, pad_to_multiple: int = 1, allocator=None):
+                 align: int = 128, pad_to_multiple: int = 1, allocator=None, param_filter=None):
         """allocator(numel, dtype) -> (tensor, handle): where the flat buffers live
         (symmetric peer memory for the fused collectives); default = ordinary tensors."""
-        params = [(n, p) for n, p in module.named_parameters() if p.requires_grad]
+        params = [(n, p) for n, p in module.named_parameters()
+                  if p.requires_grad and (param_filter is None or param_filter(n, p))]
         # de-duplicate tied parameters
         seen, uniq = set(), []
         for n, p in params:

@@ -268,6 +268,10 @@ peer_sum_test_kernel(PeerTable bufs, PeerTable flags, int rank, int world, long 
   }
 }
 
+__global__ void peer_barrier_kernel(PeerTable flags, int rank, int world, uint32_t epoch) {
+  cross_rank_block_barrier(flags, rank, world, 0, epoch);
+}
+
 int fill_table(PeerTable* t, const long long* ptrs, int world) {
   B2F_REQUIRE(world >= 1 && world <= MAX_WORLD, "peer group size must be 1..8");
   for (int i = 0; i < MAX_WORLD; ++i) t->ptr[i] = i < world ? reinterpret_cast<void*>(ptrs[i]) : nullptr;
@@ -338,6 +342,17 @@ extern "C" int b2f_zero1_adam_gather(const float* reduced, float* master, float*
               1.f - powf(beta2, (float)step)};
   zero1_adam_gather_kernel<<<blocks, COMM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
       reduced, master, m, v, p, f, rank, world, lo, n, h, grad_scale, skip, epoch);
+  B2F_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Stream-ordered barrier across the ranks of a peer group: everything every rank enqueued
+// before it (including stores into peers' memory) is complete and visible after it.
+extern "C" int b2f_peer_barrier(const long long* flags_ptrs, int rank, int world, unsigned epoch,
+                                void* stream) {
+  PeerTable f;
+  if (int rc = fill_table(&f, flags_ptrs, world)) return rc;
+  peer_barrier_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(f, rank, world, epoch);
   B2F_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -130,6 +130,7 @@ int b2f_zero1_adam_gather(const float* reduced, float* master, float* m, float* 
                           int world, long long lo, long long n, float lr, float beta1, float beta2,
                           float eps, float weight_decay, int step, const float* grad_scale,
                           const int* skip, int blocks, unsigned epoch, void* stream);
+int b2f_peer_barrier(const long long* flags_ptrs, int rank, int world, unsigned epoch, void* stream);
 int b2f_peer_sum_test(const long long* buf_ptrs, const long long* flags_ptrs, int rank, int world,
                       long long n, float* out, int blocks, unsigned epoch, void* stream);
 
@@ -165,6 +166,21 @@ int b2f_mask_crop(const unsigned char* masks, int H, int W, const float* rois, c
                   int R, int M, float* out, void* stream);
 int b2f_mask_paste(const float* probs, int M, const float* boxes, int R, int H, int W, float thr,
                    unsigned char* out, void* stream);
+
+/* ---- K5a + MoE token movement (DeepSpeed top1gating + einsum dispatch/combine + all_to_all).
+ * With peer_ptrs the dispatch stores rows straight into the expert owner's buffer
+ * [src_rank, local_expert, capacity, H] and the combine pulls them back: the all-to-alls are
+ * done by these kernels over NVLink. */
+int b2f_moe_router_top1(const float* logits, int T, int E, int capacity, int* expert, int* slot,
+                        float* gate, float* probs, int* counts, float* me, float* ce, void* stream);
+int b2f_moe_dispatch(const void* x, const int* expert, const int* slot, int T, int H, int capacity,
+                     void* dst_local, const long long* peer_ptrs, int world, int experts_per_rank,
+                     int src_rank, void* stream);
+int b2f_moe_combine(const void* src_local, const long long* peer_ptrs, int world,
+                    int experts_per_rank, int src_rank, const int* expert, const int* slot,
+                    const float* gate, int T, int H, int capacity, void* y, void* stream);
+int b2f_moe_gate_grad(const void* rows, const int* expert, const int* slot, const void* dy, int T,
+                      int H, int capacity, float* dgate, void* stream);
 
 #ifdef __cplusplus
 }

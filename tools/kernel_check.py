@@ -485,7 +485,37 @@ def group_maskrcnn_step():
     print(json.dumps(RESULTS[-1]), flush=True)
 
 
+def group_moe():
+    from b200flow.parallel.moe import MoELayer, route_top1
+    torch.manual_seed(8)
+    T, E, C = 3000, 8, 384
+    logits = torch.randn(T, E, device=DEV)
+    r = route_top1(logits, C)
+    rc = route_top1(logits.cpu(), C)
+    for k in ("expert", "slot", "counts"):
+        RESULTS.append({"name": f"router_{k}", "ok": bool(torch.equal(r[k].cpu(), rc[k]))}); print(json.dumps(RESULTS[-1]), flush=True)
+    report("router_gate", r["gate"].reshape(1, -1), rc["gate"].reshape(1, -1), 1e-5)
+    report("router_me", r["me"].reshape(1, -1), rc["me"].reshape(1, -1), 1e-4)
+    report("router_ce", r["ce"].reshape(1, -1), rc["ce"].reshape(1, -1), 1e-6)
+    layer = MoELayer(256, 512, 8, dtype=torch.bfloat16, device=DEV)
+    x = (torch.randn(1024, 256, device=DEV) * 0.5).to(torch.bfloat16).requires_grad_()
+    y = layer(x)
+    (y.float().square().sum() + layer.last_aux).backward()
+    ref_layer = MoELayer(256, 512, 8, dtype=torch.float32)
+    ref_layer.load_state_dict({k: v.float().cpu() for k, v in layer.state_dict().items()})
+    xr = x.detach().float().cpu().requires_grad_()
+    yr = ref_layer(xr)
+    (yr.square().sum() + ref_layer.last_aux).backward()
+    same_route = float((layer.last_counts.cpu() == ref_layer.last_counts).float().mean())
+    RESULTS.append({"name": "moe_route_agree", "ok": same_route > 0.5, "agree": same_route}); print(json.dumps(RESULTS[-1]), flush=True)
+    report("moe_fwd", y, yr, 4e-2)
+    report("moe_dx", x.grad, xr.grad, 6e-2)
+    report("moe_dw1", layer.w1.grad.reshape(8, -1), ref_layer.w1.grad.reshape(8, -1), 6e-2)
+    report("moe_dwg", layer.wg.grad[:8], ref_layer.wg.grad[:8], 8e-2)
+
+
 GROUPS = {
+    "moe": group_moe,
     "detection": group_detection,
     "maskrcnn_step": group_maskrcnn_step,
     "attn_fwd": lambda: group_attn("fwd"),

@@ -209,7 +209,40 @@ def group_fused_gemm():
            cublas_nccl_rs_ms=t_rs_n, cublas_gemm_only_ms=t_plain, shape=[T, N, K])
 
 
-GROUPS = {"fused_gemm": group_fused_gemm, "arena": group_arena, "allreduce": group_allreduce, "zero1": group_zero1, "tp": group_tp,
+def group_moe_ep():
+    """Expert parallel: fused peer-memory dispatch/combine vs the all_to_all_single baseline."""
+    from b200flow.comm.arena import PeerComm
+    from b200flow.parallel.moe import EPContext, MoELayer
+
+    rank, world = dist.get_rank(), dist.get_world_size()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    comm = PeerComm(dist.group.WORLD, rank, world, dev)
+    ep = EPContext(dist.group.WORLD, world, rank, comm)
+    E = 2 * world
+    torch.manual_seed(31)
+    base = MoELayer(512, 1024, E, ep=ep, dtype=torch.bfloat16, device=dev, fused=False)
+    fused = MoELayer(512, 1024, E, ep=ep, dtype=torch.bfloat16, device=dev, fused=True)
+    fused.load_state_dict(base.state_dict())
+    torch.manual_seed(50 + rank)
+    x = (torch.randn(2048, 512, device=dev) * 0.5).to(torch.bfloat16)
+    for rep in range(2):
+        xa, xb = x.clone().requires_grad_(), x.clone().requires_grad_()
+        ya, yb = base(xa), fused(xb)
+        ya.float().square().sum().backward()
+        yb.float().square().sum().backward()
+        torch.cuda.synchronize()
+        report(f"moe_ep_fwd_r{rep}", rel(yb, ya) < 1e-2, err=rel(yb, ya))
+        report(f"moe_ep_dx_r{rep}", rel(xb.grad, xa.grad) < 2e-2, err=rel(xb.grad, xa.grad))
+        report(f"moe_ep_dw1_r{rep}", rel(fused.w1.grad, base.w1.grad) < 2e-2)
+        base.zero_grad(); fused.zero_grad()
+    def run(layer):
+        xx = x.clone().requires_grad_()
+        layer(xx).float().sum().backward()
+    tb, tf = timeit(lambda: run(base)), timeit(lambda: run(fused))
+    report("moe_ep_perf", True, baseline_a2a_ms=tb, fused_peer_ms=tf)
+
+
+GROUPS = {"moe_ep": group_moe_ep, "fused_gemm": group_fused_gemm, "arena": group_arena, "allreduce": group_allreduce, "zero1": group_zero1, "tp": group_tp,
           "pp": group_pp}
 
 if __name__ == "__main__":
