@@ -253,8 +253,9 @@ class MoELayer(nn.Module):
     def __init__(self, hidden: int, ffn: int, num_experts: int, ep: EPContext | None = None,
                  capacity_factor: float = 1.0, min_capacity: int = 4, act: str = "gelu",
                  aux_loss_coeff: float = 0.01, init_std: float = 0.02, dtype=torch.bfloat16, device=None,
-                 fused: bool = True):
+                 fused: bool = True, fp8: bool = False):
         super().__init__()
+        self.fp8 = fp8
         self.ep = ep or LOCAL
         assert num_experts % self.ep.world == 0
         self.E, self.El = num_experts, num_experts // self.ep.world
@@ -287,9 +288,13 @@ class MoELayer(nn.Module):
         self.last_aux, self.last_counts = aux, counts
         xin = _Dispatch.apply(x, expert, slot, self.E, C, self.ep, self.fused)       # [El, ep*C, H]
         outs = []
+        if self.fp8 and x.is_cuda:
+            from ..ops.gemm_fp8 import linear_fp8 as lin, linear_gelu_fp8 as lin_gelu
+        else:
+            lin, lin_gelu = G.linear, G.linear_gelu
         for e in range(self.El):
-            h1 = G.linear_gelu(xin[e], self.w1[e], self.b1[e])
-            outs.append(G.linear(h1, self.w2[e], self.b2[e]))
+            h1 = lin_gelu(xin[e], self.w1[e], self.b1[e])
+            outs.append(lin(h1, self.w2[e], self.b2[e]))
         out = torch.stack(outs, 0)
         y = _Combine.apply(out, gate, expert, slot, self.E, C, self.ep, self.fused)
         return y

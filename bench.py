@@ -134,9 +134,17 @@ def main():
     tp, pp = topology_for(world)
     if args.tp or args.pp:
         tp, pp = max(args.tp, 1), max(args.pp, 1)
-    ps = ParallelState.initialize(tp=tp, pp=pp) if world > 1 else None
-    dp = world // (tp * pp)
+    is_moe = "moe" in args.workload
+    if is_moe:       # BASELINE.json config 5: experts spread over all GPUs (EP = #GPUs), fp8 expert GEMMs
+        tp = pp = 1
+        if args.seq == 4096:
+            args.seq = 2048
     cfg = config_from_preset(args.workload, max_seq=args.seq)
+    ep = min(world, cfg.num_experts) if is_moe else 1
+    if is_moe:
+        cfg.moe_fp8 = True
+    ps = ParallelState.initialize(tp=tp, pp=pp, ep=ep) if world > 1 else None
+    dp = world // (tp * pp)
     ds_config = {
         "train_micro_batch_size_per_gpu": args.micro_batch,
         "gradient_accumulation_steps": args.gas,
@@ -209,7 +217,8 @@ def main():
         model_tflops = cfg.flops_per_token(S) * val / 1e12
         out = {
             "metric": "Llama-2 7B Megatron-DS tokens/s" if args.workload == "llama2-7b"
-            else f"{args.workload} tokens/s",
+            else ("GPT-MoE 1.3B (8 experts) tokens/s" if args.workload == "gpt-moe-1.3b"
+                  else f"{args.workload} tokens/s"),
             "value": val, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",

@@ -58,6 +58,9 @@ struct Params {
   long long ldaux, strideAux;
   float alpha;
   int flags;
+  // fp8 path: dequantisation scales, v = acc * row_scale[m] * col_scale[n]
+  const float* row_scale;
+  const float* col_scale;
 };
 
 struct SharedStorage {
@@ -106,6 +109,15 @@ __device__ __forceinline__ void epilogue_chunk(const Params& p, int b, int m, in
 #pragma unroll
   for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(acc[i]) * p.alpha;
   const bool full = (n0 + 32 <= p.N);
+  if (p.row_scale) {
+    const float rs = p.row_scale[m];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] *= rs;
+  }
+  if (p.col_scale) {
+    for (int i = 0; i < 32; ++i)
+      if (n0 + i < p.N) v[i] *= p.col_scale[n0 + i];
+  }
   if (p.bias) {
     if (flags & EPI_BIAS_ROW) {
       float bv = __bfloat162float(p.bias[m]);
@@ -207,7 +219,9 @@ __device__ __forceinline__ void PlainPolicy::store_chunk(const Params& p, int b,
 
 // The whole persistent GEMM. `first_tile`/`tile_stride` let a fused kernel give
 // only a subset of its CTAs to the GEMM role (the rest move data between GPUs).
-template <class Policy>
+// KIND: 0 = bf16 operands (kind::f16, 64 elements per 128 B row), 1 = fp8 e4m3 operands
+// (kind::f8f6f4, 128 elements per row, K-major only).
+template <class Policy, int KIND = 0>
 __device__ __forceinline__ void gemm_body(const CUtensorMap* tma_a, const CUtensorMap* tma_b,
                                           const Params& p, const Policy& pol, int first_tile,
                                           int tile_stride, uint8_t* smem_raw) {
@@ -219,7 +233,8 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap* tma_a, const CUtens
   const int num_m = (p.M + BM - 1) / BM;
   const int num_n = (p.N + BN - 1) / BN;
   const int num_tiles = num_m * num_n * p.batch;
-  const int num_kb = (p.K + BK - 1) / BK;
+  constexpr int BKE = KIND == 1 ? 2 * BK : BK;      // elements per k-block (one 128 B row)
+  const int num_kb = (p.K + BKE - 1) / BKE;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(tma_a);
@@ -259,7 +274,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap* tma_a, const CUtens
           uint8_t* sa = smem + stage * STAGE_BYTES;
           uint8_t* sb = sa + A_STAGE_BYTES;
           mbar_arrive_expect_tx(&ss->full[stage], STAGE_BYTES);
-          const int k0 = kb * BK;
+          const int k0 = kb * BKE;
           if (!p.a_mn_major) {
             tma_load_3d(sa, tma_a, &ss->full[stage], k0, m0, b);
           } else {
@@ -282,7 +297,8 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap* tma_a, const CUtens
   } else if (warp == 1) {
     if (lane == 0) {
       // ------------------------------------------------------------ MMA issuer
-      const uint32_t idesc = make_idesc(1, 1, BM, BN, p.a_mn_major, p.b_mn_major);
+      const uint32_t idesc = KIND == 1 ? make_idesc(0, 0, BM, BN, 0, 0)
+                                       : make_idesc(1, 1, BM, BN, p.a_mn_major, p.b_mn_major);
       // K-major: +32 B per UMMA_K inside the swizzle atom; MN-major: +16 rows * 128 B.
       const uint32_t a_kstep = p.a_mn_major ? 2048u : 32u;
       const uint32_t b_kstep = p.b_mn_major ? 2048u : 32u;
@@ -306,7 +322,8 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap* tma_a, const CUtens
           for (int k = 0; k < BK / 16; ++k) {
             uint64_t da = make_smem_desc_sw128(sa + k * a_kstep, a_lbo, 1024);
             uint64_t db = make_smem_desc_sw128(sb + k * b_kstep, b_lbo, 1024);
-            umma_f16_ss(d_tmem, da, db, idesc, (kb | k) != 0);
+            if (KIND == 1) umma_f8_ss(d_tmem, da, db, idesc, (kb | k) != 0);
+            else umma_f16_ss(d_tmem, da, db, idesc, (kb | k) != 0);
           }
           umma_commit(&ss->empty[stage]);  // frees the smem slot when these MMAs retire
           if (kb == num_kb - 1) umma_commit(&ss->tmem_full[as]);

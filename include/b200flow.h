@@ -32,6 +32,15 @@ int b2f_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, lo
                   const void* residual, long long ldr, long long strideR, void* aux,
                   long long ldaux, long long strideAux, float alpha, int flags, void* stream);
 
+/* fp8 (e4m3) GEMM for the MoE experts: C = (Aq Bq^T) * row_scale[m] * col_scale[n] with the usual
+ * epilogue; operands quantised row-wise by b2f_quantize_rows_e4m3 (scale = amax / 448). */
+int b2f_gemm_fp8(const void* Aq, const void* Bq, void* C, int M, int N, int K, long long lda,
+                 long long ldb, long long ldc, const float* row_scale, const float* col_scale,
+                 const void* bias, const void* residual, long long ldr, void* aux, long long ldaux,
+                 int flags, void* stream);
+int b2f_quantize_rows_e4m3(const void* x, void* q, float* scale, long long rows, int K, long long ldx,
+                           void* stream);
+
 /* ---- K8: LayerNorm / RMSNorm (apex fused_layer_norm_cuda) ------------------ */
 int b2f_norm_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* y,
                  void* h_out, float* mean, float* rstd, int rows, int H, float eps, int rms,

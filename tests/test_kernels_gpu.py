@@ -50,6 +50,14 @@ def test_attention_backward():
     _run("attn_bwd")
 
 
+def test_fp8_gemm_and_linear():
+    _run("fp8")
+
+
+def test_moe_router_and_layer():
+    _run("moe")
+
+
 def test_detection_kernels():
     _run("detection")
 

@@ -514,7 +514,44 @@ def group_moe():
     report("moe_dwg", layer.wg.grad[:8], ref_layer.wg.grad[:8], 8e-2)
 
 
+def group_fp8():
+    from b200flow.ops import gemm_fp8 as F8
+    torch.manual_seed(9)
+    for (M, Nn, K) in [(256, 512, 256), (1000, 2048, 1024), (4096, 8192, 2048)]:
+        a = (torch.randn(M, K, device=DEV) * torch.rand(M, 1, device=DEV) * 3).to(torch.bfloat16)
+        b = (torch.randn(Nn, K, device=DEV) * 0.05).to(torch.bfloat16)
+        aq, sa = F8.quantize_rows(a)
+        bq, sb = F8.quantize_rows(b)
+        deq = aq.view(torch.float8_e4m3fn).float() * sa[:, None]
+        report(f"fp8_quant_{M}x{K}", deq, a.float(), 0.07)
+        exact = (aq.view(torch.float8_e4m3fn).float() @ bq.view(torch.float8_e4m3fn).float().t()) * sa[:, None] * sb[None, :]
+        got = F8.gemm_fp8(aq, sa, bq, sb)
+        report(f"fp8_gemm_exact_{M}x{Nn}x{K}", got, exact, 1e-2)       # vs the same quantised operands
+        report(f"fp8_gemm_vs_bf16_{M}x{Nn}x{K}", got, a.float() @ b.float().t(), 6e-2)
+    x = (torch.randn(2048, 2048, device=DEV)).to(torch.bfloat16).requires_grad_()
+    w = (torch.randn(8192, 2048, device=DEV) * 0.02).to(torch.bfloat16).requires_grad_()
+    bias = torch.zeros(8192, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    y = F8.linear_gelu_fp8(x, w, bias)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xf, wf = x.detach().float().requires_grad_(), w.detach().float().requires_grad_()
+    yf = torch.nn.functional.gelu(xf @ wf.t(), approximate="tanh")
+    yf.backward(dy.float())
+    report("fp8_linear_gelu_fwd", y, yf, 6e-2)
+    report("fp8_linear_gelu_dx", x.grad, xf.grad, 8e-2)
+    report("fp8_linear_gelu_dw", w.grad, wf.grad, 4e-2)
+    a = torch.randn(4096, 4096, device=DEV, dtype=torch.bfloat16)
+    b = torch.randn(8192, 4096, device=DEV, dtype=torch.bfloat16)
+    aq, sa = F8.quantize_rows(a); bq, sb = F8.quantize_rows(b)
+    t8 = timeit(lambda: F8.gemm_fp8(aq, sa, bq, sb))
+    t16 = timeit(lambda: G.gemm(a, b))
+    fl = 2.0 * 4096 * 8192 * 4096
+    RESULTS.append({"name": "fp8_perf", "ok": True, "fp8_tflops": fl / t8 / 1e9, "bf16_tflops": fl / t16 / 1e9})
+    print(json.dumps(RESULTS[-1]), flush=True)
+
+
 GROUPS = {
+    "fp8": group_fp8,
     "moe": group_moe,
     "detection": group_detection,
     "maskrcnn_step": group_maskrcnn_step,
