@@ -207,7 +207,8 @@ def _dispatch_fwd(x, expert, slot, E, capacity, ep: EPContext, fused):
         _lib.call("b2f_moe_dispatch", ptr(x), ptr(expert), ptr(slot), c_int(T), c_int(H), c_int(capacity),
                   ptr(None), recv.ptr_array, c_int(ep.world), c_int(El), c_int(ep.rank), stream_ptr())
         ep.barrier()                      # every peer's rows have landed
-        got = view.view(ep.world, El, capacity, H)
+        # copy out of the (reused) symmetric buffer: the expert GEMMs save their input for backward
+        got = view.view(ep.world, El, capacity, H).clone()
     else:
         buf = _dispatch_local(x, expert, slot, E, capacity)            # [E*C, H] = [ep, El, C, H]
         got = _a2a(buf, ep).view(ep.world, El, capacity, H)

@@ -218,7 +218,7 @@ def group_moe_ep():
     dev = torch.device("cuda", torch.cuda.current_device())
     comm = PeerComm(dist.group.WORLD, rank, world, dev)
     ep = EPContext(dist.group.WORLD, world, rank, comm)
-    E = 2 * world
+    E = int(os.environ.get("B2F_CHECK_EXPERTS_PER_RANK", 2)) * world
     torch.manual_seed(31)
     base = MoELayer(512, 1024, E, ep=ep, dtype=torch.bfloat16, device=dev, fused=False)
     fused = MoELayer(512, 1024, E, ep=ep, dtype=torch.bfloat16, device=dev, fused=True)
