@@ -14,7 +14,17 @@ import torch
 from . import _lib
 from ._lib import c_float, c_int, c_ll, ptr, stream_ptr
 
+import os
+
 EPI_GELU, EPI_OUT_F32, EPI_ACCUM, EPI_RELU, EPI_BIAS_ROW = 1, 2, 4, 8, 16
+# "2cta": CTA-pair kernel (cta_group::2) for tiles that fill it; "1cta": always the 128x256 kernel
+GEMM_IMPL = os.environ.get("B2F_GEMM", "2cta")
+
+
+def _entry(M: int, N: int) -> str:
+    if GEMM_IMPL == "2cta" and M >= 256 and N >= 256:
+        return "b2f_gemm_bf16_2cta"
+    return "b2f_gemm_bf16"
 
 
 def _ld(t: torch.Tensor) -> int:
@@ -65,7 +75,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_maj
     sr = residual.stride(0) if (residual is not None and residual.dim() == 3) else 0
     sx = aux.stride(0) if (aux is not None and aux.dim() == 3) else 0
     _lib.call(
-        "b2f_gemm_bf16", ptr(a), ptr(b), ptr(out), c_int(M), c_int(N), c_int(K),
+        _entry(M, N), ptr(a), ptr(b), ptr(out), c_int(M), c_int(N), c_int(K),
         c_ll(_ld(a)), c_ll(_ld(b)), c_ll(_ld(out)), c_int(int(a_mn_major)), c_int(int(b_mn_major)),
         c_int(batch), c_ll(sa), c_ll(sb), c_ll(sc), ptr(bias), ptr(residual),
         c_ll(_ld(residual) if residual is not None else 0), c_ll(sr), ptr(aux),

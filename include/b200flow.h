@@ -32,6 +32,13 @@ int b2f_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, lo
                   const void* residual, long long ldr, long long strideR, void* aux,
                   long long ldaux, long long strideAux, float alpha, int flags, void* stream);
 
+/* Same contract on CTA pairs (cta_group::2, 256x256 tile per pair, 6 stages). */
+int b2f_gemm_bf16_2cta(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
+                       long long ldb, long long ldc, int a_mn_major, int b_mn_major, int batch,
+                       long long strideA, long long strideB, long long strideC, const void* bias,
+                       const void* residual, long long ldr, long long strideR, void* aux,
+                       long long ldaux, long long strideAux, float alpha, int flags, void* stream);
+
 /* fp8 (e4m3) GEMM for the MoE experts: C = (Aq Bq^T) * row_scale[m] * col_scale[n] with the usual
  * epilogue; operands quantised row-wise by b2f_quantize_rows_e4m3 (scale = amax / 448). */
 int b2f_gemm_fp8(const void* Aq, const void* Bq, void* C, int M, int N, int K, long long lda,

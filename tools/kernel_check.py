@@ -550,7 +550,36 @@ def group_fp8():
     print(json.dumps(RESULTS[-1]), flush=True)
 
 
+def group_gemm2():
+    """2-CTA kernel: all layouts + epilogues vs fp32, then perf vs the 1-CTA kernel and cuBLAS."""
+    G.GEMM_IMPL = "2cta"
+    for mode in ("nt", "nn", "tn", "tt"):
+        group_gemm(mode)
+    group_gemm_epi()
+    out = {}
+    for (M, Nn, K) in [(4096, 4096, 4096), (8192, 8192, 8192), (4096, 22016, 4096), (4096, 4096, 11008),
+                       (4096, 12288, 4096), (4096, 32000, 4096)]:
+        a = torch.randn(M, K, device=DEV, dtype=torch.bfloat16)
+        b = torch.randn(Nn, K, device=DEV, dtype=torch.bfloat16)
+        c = torch.empty(M, Nn, device=DEV, dtype=torch.bfloat16)
+        fl = 2.0 * M * Nn * K
+        G.GEMM_IMPL = "2cta"
+        t2 = timeit(lambda: G.gemm(a, b, out=c))
+        bt, at = b.t().contiguous(), a.t().contiguous()
+        t2nn = timeit(lambda: G.gemm(a, bt, out=c, b_mn_major=True))
+        t2tn = timeit(lambda: G.gemm(at, bt, out=c, a_mn_major=True, b_mn_major=True))
+        G.GEMM_IMPL = "1cta"
+        t1 = timeit(lambda: G.gemm(a, b, out=c))
+        tc = timeit(lambda: torch.matmul(a, b.t(), out=c))
+        rec = {"name": f"perf2_{M}x{Nn}x{K}", "cta2_tflops": fl / t2 / 1e9, "cta2_nn": fl / t2nn / 1e9,
+               "cta2_tn": fl / t2tn / 1e9, "cta1_tflops": fl / t1 / 1e9, "cublas_tflops": fl / tc / 1e9}
+        print(json.dumps(rec), flush=True)
+    G.GEMM_IMPL = "2cta"
+    RESULTS.append({"name": "gemm2_perf", "ok": True})
+
+
 GROUPS = {
+    "gemm2": group_gemm2,
     "fp8": group_fp8,
     "moe": group_moe,
     "detection": group_detection,
