@@ -21,6 +21,8 @@
 //
 // Capability parity: flash-attn v2 / Megatron scaled_(upper_triang_)masked_softmax
 // attention core.
+#include <stdlib.h>
+
 #include "../common/ptx.cuh"
 #include "../common/host.h"
 #include "../../include/b200flow.h"
@@ -281,6 +283,256 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ 
     }
     if (qi < p.S && p.lse)
       p.lse[((long long)b * p.H + h) * p.S + qi] = l > 0.f ? (m * LN2 + __logf(l)) : INFINITY;
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 512);
+  }
+}
+
+// ---- forward v2: two query tiles per CTA, ping-ponged on the tensor core.
+// warp 0 = TMA, warp 1 = MMA issuer, warps 4-7 = softmax of query tile A,
+// warps 8-11 = softmax of tile B (registers moved to them with setmaxnreg).
+// While one group exponentiates its scores the MMA pipe runs the other tile's Q K^T / P V.  Each softmax thread owns one query
+// row and holds all 128 scores in registers (one TMEM read).  O accumulates in TMEM
+// across key tiles; the running max is only raised when it grows by more than 2^8
+// (then that warp rescales its O rows in TMEM), so most tiles skip the rescale.
+constexpr int FWD2_THREADS = 384;  // warpgroup 0: TMA + MMA (+2 idle warps); 1, 2: softmax A, B
+constexpr float RESCALE_THRESHOLD = 8.f;
+
+struct Fwd2Bars {
+  uint64_t q_full[2], k_full[2], v_full[2], k_empty[2], v_empty[2], s_full[2], p_full[2], o_full[2];
+  uint32_t tmem_base;
+};
+
+template <int D>
+__global__ void __launch_bounds__(FWD2_THREADS, 1)
+attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
+                 const __grid_constant__ CUtensorMap mv, const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align1024(smem_raw);
+  constexpr int TILE_B = Cfg<D>::TILE_B;
+  uint8_t* sQ = smem;                   // 2 query tiles
+  uint8_t* sK = smem + 2 * TILE_B;      // 2 stages
+  uint8_t* sV = smem + 4 * TILE_B;      // 2 stages
+  Fwd2Bars* bars = reinterpret_cast<Fwd2Bars*>(smem + 6 * TILE_B);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nblk = (p.S + 2 * TQ - 1) / (2 * TQ);
+  const int q_blk = p.causal ? nblk - 1 - (int)blockIdx.x : (int)blockIdx.x;
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int hkv = h / (p.H / p.HKV);
+  const int q0 = q_blk * 2 * TQ;
+  int kv_len = p.kv_lens ? p.kv_lens[b] : p.S;
+  kv_len = kv_len < p.S ? kv_len : p.S;
+  // key tiles needed by each query tile (tile B may lie wholly past the sequence end)
+  int n_w[2];
+#pragma unroll
+  for (int w = 0; w < 2; ++w) {
+    const int qs = q0 + w * TQ;
+    int kv_end = p.causal ? (kv_len < qs + TQ ? kv_len : qs + TQ) : kv_len;
+    int nn = (kv_end + TQ - 1) / TQ;
+    if (nn < 1) nn = 1;
+    n_w[w] = qs < p.S ? nn : 0;
+  }
+  const int nA = n_w[0], nB = n_w[1];
+  const int n = nA > nB ? nA : nB;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&mq); tma_prefetch_desc(&mk); tma_prefetch_desc(&mv);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bars->q_full[i], 1);
+      mbar_init(&bars->k_full[i], 1);
+      mbar_init(&bars->v_full[i], 1);
+      mbar_init(&bars->k_empty[i], 1);
+      mbar_init(&bars->v_empty[i], 1);
+      mbar_init(&bars->s_full[i], 1);
+      mbar_init(&bars->p_full[i], 128);
+      mbar_init(&bars->o_full[i], 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(&bars->tmem_base, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = bars->tmem_base;
+  // columns: S_A [0,128) S_B [128,256) O_A [256,256+D) O_B [384,384+D)
+
+  if (warp < 4) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
+    if (warp == 0 && lane == 0) {
+      for (int w = 0; w < 2; ++w)
+        if (n_w[w] > 0) {
+          mbar_arrive_expect_tx(&bars->q_full[w], TILE_B);
+          load_tile<D>(sQ + w * TILE_B, &mq, &bars->q_full[w], q0 + w * TQ, h, b);
+        }
+      for (int j = 0; j < n; ++j) {
+        const int st = j & 1;
+        const uint32_t ph = (j >> 1) & 1;
+        mbar_wait(&bars->k_empty[st], ph ^ 1);
+        mbar_arrive_expect_tx(&bars->k_full[st], TILE_B);
+        load_tile<D>(sK + st * TILE_B, &mk, &bars->k_full[st], j * TQ, hkv, b);
+        mbar_wait(&bars->v_empty[st], ph ^ 1);
+        mbar_arrive_expect_tx(&bars->v_full[st], TILE_B);
+        load_tile<D>(sV + st * TILE_B, &mv, &bars->v_full[st], j * TQ, hkv, b);
+      }
+    } else if (warp == 1 && lane == 0) {
+      const uint32_t idesc_s = make_idesc(1, 1, 128, 128, 0, 0);
+      const uint32_t idesc_pv = make_idesc(1, 1, 128, D, 0, 1);
+      // S_w(j) = Q_w K_j^T ; the last reader of K_j releases its stage.
+      auto issue_s = [&](int w, int j) {
+        const int st = j & 1;
+        const uint32_t aQ = smem_u32(sQ + w * TILE_B), aK = smem_u32(sK + st * TILE_B);
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k)
+          umma_f16_ss(tmem + w * 128, desc_k(aQ, k), desc_k(aK, k), idesc_s, k > 0);
+        umma_commit(&bars->s_full[w]);
+        const bool last_reader = (w == 1) || j >= nB;
+        if (last_reader) umma_commit(&bars->k_empty[st]);
+      };
+      auto issue_pv = [&](int w, int j) {
+        const int st = j & 1;
+        const uint32_t aV = smem_u32(sV + st * TILE_B);
+#pragma unroll
+        for (int k = 0; k < TQ / 16; ++k)
+          umma_f16_ts(tmem + 256 + w * 128, tmem + w * 128 + k * 8, desc_mn(aV, k), idesc_pv,
+                      (j | k) != 0);
+        const bool last_reader = (w == 1) || j >= nB;
+        if (last_reader) umma_commit(&bars->v_empty[st]);
+        if (j + 1 == n_w[w]) umma_commit(&bars->o_full[w]);
+      };
+      mbar_wait(&bars->k_full[0], 0);
+      tc_fence_after();
+      if (nA > 0) { mbar_wait(&bars->q_full[0], 0); tc_fence_after(); issue_s(0, 0); }
+      if (nB > 0) { mbar_wait(&bars->q_full[1], 0); tc_fence_after(); issue_s(1, 0); }
+      for (int j = 0; j < n; ++j) {
+        const int st = j & 1;
+        const uint32_t ph = (j >> 1) & 1;
+#pragma unroll
+        for (int w = 0; w < 2; ++w) {
+          if (j >= n_w[w]) continue;
+          mbar_wait(&bars->p_full[w], j & 1);
+          mbar_wait(&bars->v_full[st], ph);
+          tc_fence_after();
+          issue_pv(w, j);
+          if (j + 1 < n_w[w]) {
+            mbar_wait(&bars->k_full[st ^ 1], ((j + 1) >> 1) & 1);
+            tc_fence_after();
+            issue_s(w, j + 1);
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
+    const int w = (warp - 4) >> 2;   // 0: tile A, 1: tile B
+    const int qw = warp & 3;         // TMEM lane quadrant this warp may touch
+    const int r = qw * 32 + lane;
+    const int qs = q0 + w * TQ;
+    const int qi = qs + r;
+    const int nw = n_w[w];
+    const uint32_t lane_base = static_cast<uint32_t>(qw * 32) << 16;
+    const uint32_t T_S = tmem + lane_base + w * 128;
+    const uint32_t T_O = tmem + lane_base + 256 + w * 128;
+    float m = 0.f, l = 0.f;
+    for (int j = 0; j < nw; ++j) {
+      const int kv0 = j * TQ;
+      mbar_wait(&bars->s_full[w], j & 1);
+      tc_fence_after();
+      uint32_t s[128];
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        tmem_ld_32x32b_x32(T_S + c * 32, *reinterpret_cast<uint32_t(*)[32]>(s + c * 32));
+      tmem_ld_wait();
+      const bool need_mask = (p.causal && kv0 + TQ - 1 > qs) || (kv0 + TQ > kv_len);
+      if (need_mask) {
+        int lim = kv_len;
+        if (p.causal && qi + 1 < lim) lim = qi + 1;
+        lim -= kv0;
+#pragma unroll
+        for (int i = 0; i < 128; ++i)
+          if (i >= lim) s[i] = 0xff800000u;  // -inf
+      }
+      float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+#pragma unroll
+      for (int i = 0; i < 128; i += 4) {
+        mx0 = fmaxf(mx0, __uint_as_float(s[i]));
+        mx1 = fmaxf(mx1, __uint_as_float(s[i + 1]));
+        mx2 = fmaxf(mx2, __uint_as_float(s[i + 2]));
+        mx3 = fmaxf(mx3, __uint_as_float(s[i + 3]));
+      }
+      const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * p.scale_log2;
+      if (j == 0) {
+        m = (mx == -INFINITY) ? 0.f : mx;
+      } else {
+        const bool grow = mx > m + RESCALE_THRESHOLD;
+        if (__any_sync(0xffffffffu, grow)) {
+          const float alpha = grow ? ex2(m - mx) : 1.f;
+          if (grow) m = mx;
+          l *= alpha;
+#pragma unroll
+          for (int c = 0; c < D / 32; ++c) {
+            uint32_t acc[32];
+            tmem_ld_32x32b_x32(T_O + c * 32, acc);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) acc[i] = __float_as_uint(__uint_as_float(acc[i]) * alpha);
+            tmem_st_32x32b_x32(T_O + c * 32, acc);
+          }
+        }
+      }
+      float sum0 = 0.f, sum1 = 0.f;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const float p0 = ex2(fmaf(__uint_as_float(s[c * 32 + 2 * i]), p.scale_log2, -m));
+          const float p1 = ex2(fmaf(__uint_as_float(s[c * 32 + 2 * i + 1]), p.scale_log2, -m));
+          sum0 += p0;
+          sum1 += p1;
+          pk[i] = pack_bf16x2(p0, p1);
+        }
+        tmem_st_32x32b_x16(T_S + c * 16, pk);
+      }
+      l += sum0 + sum1;
+      tmem_st_wait();
+      tc_fence_before();
+      mbar_arrive(&bars->p_full[w]);
+    }
+    if (nw > 0) {
+      mbar_wait(&bars->o_full[w], 0);
+      tc_fence_after();
+      const float inv = l > 0.f ? 1.f / l : 0.f;
+      __nv_bfloat16* orow = p.O + (long long)b * p.o_bs + (long long)qi * p.o_ts + (long long)h * D;
+#pragma unroll
+      for (int c = 0; c < D / 32; ++c) {
+        uint32_t acc[32];
+        tmem_ld_32x32b_x32(T_O + c * 32, acc);
+        tmem_ld_wait();
+        if (qi < p.S) {
+#pragma unroll
+          for (int q4 = 0; q4 < 4; ++q4) {
+            uint4 u;
+            float f[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) f[i] = __uint_as_float(acc[q4 * 8 + i]) * inv;
+            u.x = pack_bf16x2(f[0], f[1]); u.y = pack_bf16x2(f[2], f[3]);
+            u.z = pack_bf16x2(f[4], f[5]); u.w = pack_bf16x2(f[6], f[7]);
+            *reinterpret_cast<uint4*>(orow + c * 32 + q4 * 8) = u;
+          }
+        }
+      }
+      if (qi < p.S && p.lse)
+        p.lse[((long long)b * p.H + h) * p.S + qi] = l > 0.f ? (m * LN2 + __logf(l)) : INFINITY;
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -710,6 +962,21 @@ extern "C" int b2f_attn_fwd(const void* q, const void* k, const void* v, void* o
   p.O = static_cast<__nv_bfloat16*>(o); p.o_ts = o_ts; p.o_bs = o_bs; p.lse = lse;
   dim3 grid((S + TQ - 1) / TQ, H, B);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  static const bool use_v1 = [] { const char* e = getenv("B2F_ATTN_FWD"); return e && e[0] == '1'; }();
+  if (!use_v1) {
+    dim3 grid2((S + 2 * TQ - 1) / (2 * TQ), H, B);
+    if (D == 128) {
+      const int smem = 6 * Cfg<128>::TILE_B + 1024 + sizeof(Fwd2Bars);
+      if (int rc = set_smem(attn_fwd2_kernel<128>, smem)) return rc;
+      attn_fwd2_kernel<128><<<grid2, FWD2_THREADS, smem, st>>>(mq, mk, mv, p);
+    } else {
+      const int smem = 6 * Cfg<64>::TILE_B + 1024 + sizeof(Fwd2Bars);
+      if (int rc = set_smem(attn_fwd2_kernel<64>, smem)) return rc;
+      attn_fwd2_kernel<64><<<grid2, FWD2_THREADS, smem, st>>>(mq, mk, mv, p);
+    }
+    B2F_CHECK_CUDA(cudaGetLastError());
+    return 0;
+  }
   if (D == 128) {
     const int smem = 5 * Cfg<128>::TILE_B + 1024 + sizeof(FwdBars);
     if (int rc = set_smem(attn_fwd_kernel<128>, smem)) return rc;

@@ -307,15 +307,18 @@ def group_attn(which):
     from b200flow.ops import attention as A
     torch.manual_seed(5)
     cfgs = [(1, 128, 2, 2, 128, False), (2, 256, 4, 4, 128, True), (1, 384, 2, 2, 64, True),
-            (2, 200, 4, 2, 128, True), (1, 512, 2, 2, 128, False), (1, 1024, 4, 4, 128, True)]
-    for (B, S, H, HKV, D, causal) in cfgs:
+            (2, 200, 4, 2, 128, True), (1, 512, 2, 2, 128, False), (1, 1024, 4, 4, 128, True),
+            (1, 896, 2, 1, 128, True, 3.0), (1, 640, 2, 2, 64, False, 3.0)]
+    for cfg in cfgs:
+        (B, S, H, HKV, D, causal), amp = cfg[:6], (cfg[6] if len(cfg) > 6 else 1.0)
         qkv_shape = (B, S, H + 2 * HKV, D)
-        buf = torch.randn(qkv_shape, device=DEV, dtype=torch.bfloat16)
+        # amp > 1 makes the row max jump between key tiles (exercises the lazy O rescale)
+        buf = (torch.randn(qkv_shape, device=DEV) * amp).to(torch.bfloat16)
         q = buf[:, :, :H].detach().requires_grad_()
         k = buf[:, :, H:H + HKV].detach().requires_grad_()
         v = buf[:, :, H + HKV:].detach().requires_grad_()
         scale = D ** -0.5
-        tag = f"B{B}S{S}H{H}kv{HKV}D{D}{'c' if causal else 'f'}"
+        tag = f"B{B}S{S}H{H}kv{HKV}D{D}{'c' if causal else 'f'}" + ("amp" if amp != 1.0 else "")
         qf, kf, vf = (t.detach().float().requires_grad_() for t in (q, k, v))
         ref = _attn_ref(qf, kf, vf, causal, scale)
         if which == "fwd":
