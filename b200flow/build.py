@@ -31,6 +31,7 @@ NVCC_FLAGS = [
     "--expt-relaxed-constexpr",
     "-Xptxas", "-v",
     "-I", str(ROOT / "include"),
+    *os.environ.get("B2F_NVCC_EXTRA", "").split(),  # e.g. -DB2F_ATTN_DEBUG for the timing counters
 ]
 CXX_FLAGS = ["-O3", "-std=c++17", "-fPIC", "-Wall", "-pthread", "-I", str(ROOT / "include")]
 

@@ -50,6 +50,7 @@ struct AttnParams {
   // backward outputs
   __nv_bfloat16 *dQ, *dK, *dV;
   long long dq_ts, dq_bs, dk_ts, dk_bs, dv_ts, dv_bs;
+  int dbg_mode;  // B2F_ATTN_DEBUG builds only: 1 = softmax does no math, 2 = also no P V, 3 = also no Q K^T
 };
 
 template <int D>
@@ -58,13 +59,33 @@ struct Cfg {
   static constexpr int TILE_B = TQ * D * 2;
 };
 
-// K-major operand (rows = M/N index, contraction along the 128 B rows).
-__device__ __forceinline__ uint64_t desc_k(uint32_t tile, int k) {
-  return make_smem_desc_sw128(tile + (k >> 2) * CHUNK_B + (k & 3) * 32, 16, 1024);
+// UMMA shared-memory descriptors, split so the MMA-issuing thread only adds a constant to the
+// low word per K step (a 128x128x16 MMA lasts 64 cycles: the issue loop has to be shorter).
+//   high word: SBO = 1024 B, descriptor version 1, SWIZZLE_128B;  low word: address >> 4 | LBO << 16
+constexpr uint32_t DESC_HI = (1024u >> 4) | (1u << 14) | (2u << 29);
+__device__ __forceinline__ uint64_t mk_desc(uint32_t lo) {
+  uint64_t d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(DESC_HI));
+  return d;
 }
-// MN-major operand (rows = contraction index, 16 rows per UMMA_K step).
-__device__ __forceinline__ uint64_t desc_mn(uint32_t tile, int k) {
-  return make_smem_desc_sw128(tile + k * 2048, CHUNK_B, 1024);
+// K-major operand (rows = M/N index, contraction along the 128 B rows): LBO unused (16 B).
+__device__ __forceinline__ uint32_t lo_k(uint32_t tile) { return ((tile & 0x3FFFF) >> 4) | (1u << 16); }
+__device__ __forceinline__ uint64_t desc_k(uint32_t lo, int k) {
+  return mk_desc(lo + (k >> 2) * (CHUNK_B >> 4) + (k & 3) * 2);
+}
+// MN-major operand (rows = contraction index, 16 rows per UMMA_K step): LBO = chunk stride.
+__device__ __forceinline__ uint32_t lo_mn(uint32_t tile) {
+  return ((tile & 0x3FFFF) >> 4) | (static_cast<uint32_t>(CHUNK_B >> 4) << 16);
+}
+__device__ __forceinline__ uint64_t desc_mn(uint32_t lo, int k) { return mk_desc(lo + k * (2048 >> 4)); }
+
+// Every kernel here allocates all 512 TMEM columns, so the allocation starts at column 0; the
+// kernels check that once and then use literal TMEM addresses (keeps them in uniform registers).
+__device__ __forceinline__ void require_tmem_base0(uint32_t base) {
+  if (base != 0) {
+    if (threadIdx.x == 0) printf("b200flow: attention expects TMEM base 0, got %u\n", base);
+    __trap();
+  }
 }
 
 template <int D>
@@ -84,221 +105,24 @@ __device__ __forceinline__ uint8_t* align1024(uint8_t* p) {
 }
 
 // ============================================================== forward
-struct FwdBars {
-  uint64_t q_full, k_full[2], v_full[2], kv_empty[2], s_full[2], p_full, o_full;
-  uint32_t tmem_base;
-};
-
-template <int D>
-__global__ void __launch_bounds__(ATT_THREADS, 1)
-attn_fwd_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
-                const __grid_constant__ CUtensorMap mv, const AttnParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = align1024(smem_raw);
-  constexpr int TILE_B = Cfg<D>::TILE_B;
-  uint8_t* sQ = smem;
-  uint8_t* sK = smem + TILE_B;          // 2 stages
-  uint8_t* sV = smem + 3 * TILE_B;      // 2 stages
-  FwdBars* bars = reinterpret_cast<FwdBars*>(smem + 5 * TILE_B);
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nq = (p.S + TQ - 1) / TQ;
-  const int q_tile = p.causal ? nq - 1 - (int)blockIdx.x : (int)blockIdx.x;
-  const int h = blockIdx.y, b = blockIdx.z;
-  const int hkv = h / (p.H / p.HKV);
-  const int q0 = q_tile * TQ;
-  int kv_len = p.kv_lens ? p.kv_lens[b] : p.S;
-  kv_len = kv_len < p.S ? kv_len : p.S;
-  int kv_end = p.causal ? (kv_len < q0 + TQ ? kv_len : q0 + TQ) : kv_len;
-  int n = (kv_end + TQ - 1) / TQ;
-  if (n < 1) n = 1;
-
-  if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&mq); tma_prefetch_desc(&mk); tma_prefetch_desc(&mv);
-    mbar_init(&bars->q_full, 1);
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(&bars->k_full[i], 1);
-      mbar_init(&bars->v_full[i], 1);
-      mbar_init(&bars->kv_empty[i], 1);
-      mbar_init(&bars->s_full[i], 1);
-    }
-    mbar_init(&bars->p_full, 128);
-    mbar_init(&bars->o_full, 1);
-    fence_mbar_init();
-  }
-  if (warp == 1) {
-    tmem_alloc(&bars->tmem_base, 512);
-    tmem_relinquish();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem = bars->tmem_base;
-  const uint32_t T_S = tmem, T_O = tmem + 256;
-
-  if (warp == 0) {
-    if (lane == 0) {
-      mbar_arrive_expect_tx(&bars->q_full, TILE_B);
-      load_tile<D>(sQ, &mq, &bars->q_full, q0, h, b);
-      int st = 0;
-      uint32_t ph = 0;
-      for (int j = 0; j < n; ++j) {
-        mbar_wait(&bars->kv_empty[st], ph ^ 1);
-        mbar_arrive_expect_tx(&bars->k_full[st], TILE_B);
-        load_tile<D>(sK + st * TILE_B, &mk, &bars->k_full[st], j * TQ, hkv, b);
-        mbar_arrive_expect_tx(&bars->v_full[st], TILE_B);
-        load_tile<D>(sV + st * TILE_B, &mv, &bars->v_full[st], j * TQ, hkv, b);
-        st ^= 1;
-        if (st == 0) ph ^= 1;
-      }
-    }
-    __syncwarp();
-  } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc_s = make_idesc(1, 1, 128, 128, 0, 0);
-      const uint32_t idesc_pv = make_idesc(1, 1, 128, D, 0, 1);
-      const uint32_t aQ = smem_u32(sQ);
-      mbar_wait(&bars->q_full, 0);
-      auto issue_s = [&](int j) {
-        const int st = j & 1;
-        mbar_wait(&bars->k_full[st], (j >> 1) & 1);
-        tc_fence_after();
-        const uint32_t aK = smem_u32(sK + st * TILE_B);
-#pragma unroll
-        for (int k = 0; k < D / 16; ++k)
-          umma_f16_ss(T_S + st * 128, desc_k(aQ, k), desc_k(aK, k), idesc_s, k > 0);
-        umma_commit(&bars->s_full[st]);
-      };
-      issue_s(0);
-      for (int j = 0; j < n; ++j) {
-        if (j + 1 < n) issue_s(j + 1);
-        const int st = j & 1;
-        mbar_wait(&bars->p_full, j & 1);
-        mbar_wait(&bars->v_full[st], (j >> 1) & 1);
-        tc_fence_after();
-        const uint32_t aV = smem_u32(sV + st * TILE_B);
-#pragma unroll
-        for (int k = 0; k < TQ / 16; ++k)
-          umma_f16_ts(T_O, T_S + st * 128 + k * 8, desc_mn(aV, k), idesc_pv, k > 0);
-        umma_commit(&bars->kv_empty[st]);
-        umma_commit(&bars->o_full);
-      }
-    }
-    __syncwarp();
-  } else {
-    const int qw = warp & 3;
-    const int r = qw * 32 + lane;
-    const int qi = q0 + r;
-    const uint32_t lane_base = static_cast<uint32_t>(qw * 32) << 16;
-    float m = -INFINITY, l = 0.f;
-    float o[D];
-#pragma unroll
-    for (int i = 0; i < D; ++i) o[i] = 0.f;
-    for (int j = 0; j < n; ++j) {
-      const int st = j & 1;
-      const int kv0 = j * TQ;
-      mbar_wait(&bars->s_full[st], (j >> 1) & 1);
-      tc_fence_after();
-      const uint32_t sbuf = T_S + lane_base + st * 128;
-      const bool need_mask = (p.causal && kv0 + TQ - 1 > q0) || (kv0 + TQ > kv_len);
-      // limit: first masked key index for this row
-      int lim = kv_len;
-      if (p.causal && qi + 1 < lim) lim = qi + 1;
-      float mx = -INFINITY;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t acc[32];
-        tmem_ld_32x32b_x32(sbuf + c * 32, acc);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float s = __uint_as_float(acc[i]);
-          if (need_mask && kv0 + c * 32 + i >= lim) s = -INFINITY;
-          mx = fmaxf(mx, s);
-        }
-      }
-      const float m_new = fmaxf(m, mx * p.scale_log2);
-      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
-      const float alpha = ex2(m - m_use);
-      if (j > 0) {
-        mbar_wait(&bars->o_full, (j - 1) & 1);
-        tc_fence_after();
-#pragma unroll
-        for (int c = 0; c < D / 32; ++c) {
-          uint32_t acc[32];
-          tmem_ld_32x32b_x32(T_O + lane_base + c * 32, acc);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 32; ++i) o[c * 32 + i] = (o[c * 32 + i] + __uint_as_float(acc[i])) * alpha;
-        }
-      }
-      float rowsum = 0.f;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t acc[32];
-        tmem_ld_32x32b_x32(sbuf + c * 32, acc);
-        tmem_ld_wait();
-        uint32_t pk[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          float p0 = ex2(__uint_as_float(acc[2 * i]) * p.scale_log2 - m_use);
-          float p1 = ex2(__uint_as_float(acc[2 * i + 1]) * p.scale_log2 - m_use);
-          if (need_mask) {
-            if (kv0 + c * 32 + 2 * i >= lim) p0 = 0.f;
-            if (kv0 + c * 32 + 2 * i + 1 >= lim) p1 = 0.f;
-          }
-          rowsum += p0 + p1;
-          pk[i] = pack_bf16x2(p0, p1);
-        }
-        tmem_st_32x32b_x16(sbuf + c * 16, pk);
-      }
-      l = l * alpha + rowsum;
-      m = m_new;
-      tmem_st_wait();
-      tc_fence_before();
-      mbar_arrive(&bars->p_full);
-    }
-    mbar_wait(&bars->o_full, (n - 1) & 1);
-    tc_fence_after();
-    const float inv = l > 0.f ? 1.f / l : 0.f;
-    __nv_bfloat16* orow = p.O + (long long)b * p.o_bs + (long long)qi * p.o_ts + (long long)h * D;
-#pragma unroll
-    for (int c = 0; c < D / 32; ++c) {
-      uint32_t acc[32];
-      tmem_ld_32x32b_x32(T_O + lane_base + c * 32, acc);
-      tmem_ld_wait();
-      if (qi < p.S) {
-#pragma unroll
-        for (int q4 = 0; q4 < 4; ++q4) {
-          uint4 u;
-          float f[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i)
-            f[i] = (o[c * 32 + q4 * 8 + i] + __uint_as_float(acc[q4 * 8 + i])) * inv;
-          u.x = pack_bf16x2(f[0], f[1]); u.y = pack_bf16x2(f[2], f[3]);
-          u.z = pack_bf16x2(f[4], f[5]); u.w = pack_bf16x2(f[6], f[7]);
-          *reinterpret_cast<uint4*>(orow + c * 32 + q4 * 8) = u;
-        }
-      }
-    }
-    if (qi < p.S && p.lse)
-      p.lse[((long long)b * p.H + h) * p.S + qi] = l > 0.f ? (m * LN2 + __logf(l)) : INFINITY;
-  }
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 1) {
-    tc_fence_after();
-    tmem_dealloc(tmem, 512);
-  }
-}
-
-// ---- forward v2: two query tiles per CTA, ping-ponged on the tensor core.
+// Two query tiles per CTA, ping-ponged on the tensor core.
 // warp 0 = TMA, warp 1 = MMA issuer, warps 4-7 = softmax of query tile A,
 // warps 8-11 = softmax of tile B (registers moved to them with setmaxnreg).
 // While one group exponentiates its scores the MMA pipe runs the other tile's Q K^T / P V.  Each softmax thread owns one query
 // row and holds all 128 scores in registers (one TMEM read).  O accumulates in TMEM
 // across key tiles; the running max is only raised when it grows by more than 2^8
 // (then that warp rescales its O rows in TMEM), so most tiles skip the rescale.
+#ifdef B2F_ATTN_DEBUG
+// cycle counters summed over CTAs (read with b2f_attn_debug): softmax-A lane 0: [0] loop total,
+// [1] waiting for scores, [2] TMEM read + max, [3] exp + P store, [4] tiles; MMA thread: [5] loop total,
+// [6] waiting for P, [7] waiting for K/V.
+__device__ unsigned long long g_attn_dbg[16];
+#define DBG_T(var) const long long var = clock64()
+#define DBG_ADD(i, v) do { if ((threadIdx.x & 31) == 0) atomicAdd(&g_attn_dbg[i], (unsigned long long)(v)); } while (0)
+#else
+#define DBG_T(var)
+#define DBG_ADD(i, v)
+#endif
 constexpr int FWD2_THREADS = 384;  // warpgroup 0: TMA + MMA (+2 idle warps); 1, 2: softmax A, B
 constexpr float RESCALE_THRESHOLD = 8.f;
 
@@ -311,6 +135,11 @@ template <int D>
 __global__ void __launch_bounds__(FWD2_THREADS, 1)
 attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
                  const __grid_constant__ CUtensorMap mv, const AttnParams p) {
+  DBG_T(t_cta0);
+#ifdef B2F_ATTN_DEBUG
+  unsigned long long ns0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns0));
+#endif
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align1024(smem_raw);
   constexpr int TILE_B = Cfg<D>::TILE_B;
@@ -321,8 +150,10 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nblk = (p.S + 2 * TQ - 1) / (2 * TQ);
-  const int q_blk = p.causal ? nblk - 1 - (int)blockIdx.x : (int)blockIdx.x;
-  const int h = blockIdx.y, b = blockIdx.z;
+  // grid: x = (head, batch) fastest, y = query block, longest (last) causal blocks first, so
+  // CTAs are handed out longest-job-first across the whole launch
+  const int q_blk = p.causal ? nblk - 1 - (int)blockIdx.y : (int)blockIdx.y;
+  const int h = blockIdx.x % p.H, b = blockIdx.x / p.H;
   const int hkv = h / (p.H / p.HKV);
   const int q0 = q_blk * 2 * TQ;
   int kv_len = p.kv_lens ? p.kv_lens[b] : p.S;
@@ -361,7 +192,11 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem = bars->tmem_base;
+  require_tmem_base0(bars->tmem_base);
+  constexpr uint32_t tmem = 0;
+#ifdef B2F_ATTN_DEBUG
+  if (threadIdx.x == 0) { DBG_T(t_pro); DBG_ADD(9, t_pro - t_cta0); }
+#endif
   // columns: S_A [0,128) S_B [128,256) O_A [256,256+D) O_B [384,384+D)
 
   if (warp < 4) {
@@ -382,52 +217,77 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
         mbar_arrive_expect_tx(&bars->v_full[st], TILE_B);
         load_tile<D>(sV + st * TILE_B, &mv, &bars->v_full[st], j * TQ, hkv, b);
       }
-    } else if (warp == 1 && lane == 0) {
+    } else if (warp == 1) {
+      // all 32 lanes walk the loop (uniform control flow keeps the issue sequence in uniform
+      // registers); one elected lane issues the MMAs and commits
       const uint32_t idesc_s = make_idesc(1, 1, 128, 128, 0, 0);
       const uint32_t idesc_pv = make_idesc(1, 1, 128, D, 0, 1);
       // S_w(j) = Q_w K_j^T ; the last reader of K_j releases its stage.
       auto issue_s = [&](int w, int j) {
         const int st = j & 1;
-        const uint32_t aQ = smem_u32(sQ + w * TILE_B), aK = smem_u32(sK + st * TILE_B);
-#pragma unroll
-        for (int k = 0; k < D / 16; ++k)
-          umma_f16_ss(tmem + w * 128, desc_k(aQ, k), desc_k(aK, k), idesc_s, k > 0);
-        umma_commit(&bars->s_full[w]);
+        const uint32_t aQ = lo_k(smem_u32(sQ + w * TILE_B)), aK = lo_k(smem_u32(sK + st * TILE_B));
         const bool last_reader = (w == 1) || j >= nB;
-        if (last_reader) umma_commit(&bars->k_empty[st]);
+        if (elect_one()) {
+#ifdef B2F_ATTN_DEBUG
+          if (p.dbg_mode != 3)
+#endif
+#pragma unroll
+          for (int k = 0; k < D / 16; ++k)
+            umma_f16_ss(tmem + w * 128, desc_k(aQ, k), desc_k(aK, k), idesc_s, k > 0);
+          umma_commit(&bars->s_full[w]);
+          if (last_reader) umma_commit(&bars->k_empty[st]);
+        }
+        __syncwarp();
       };
       auto issue_pv = [&](int w, int j) {
         const int st = j & 1;
-        const uint32_t aV = smem_u32(sV + st * TILE_B);
-#pragma unroll
-        for (int k = 0; k < TQ / 16; ++k)
-          umma_f16_ts(tmem + 256 + w * 128, tmem + w * 128 + k * 8, desc_mn(aV, k), idesc_pv,
-                      (j | k) != 0);
+        const uint32_t aV = lo_mn(smem_u32(sV + st * TILE_B));
         const bool last_reader = (w == 1) || j >= nB;
-        if (last_reader) umma_commit(&bars->v_empty[st]);
-        if (j + 1 == n_w[w]) umma_commit(&bars->o_full[w]);
+        if (elect_one()) {
+#ifdef B2F_ATTN_DEBUG
+          if (p.dbg_mode != 2)
+#endif
+#pragma unroll
+          for (int k = 0; k < TQ / 16; ++k)
+            umma_f16_ts(tmem + 256 + w * 128, tmem + w * 128 + k * 8, desc_mn(aV, k), idesc_pv,
+                        (j | k) != 0);
+          if (last_reader) umma_commit(&bars->v_empty[st]);
+          if (j + 1 == n_w[w]) umma_commit(&bars->o_full[w]);
+        }
+        __syncwarp();
       };
       mbar_wait(&bars->k_full[0], 0);
       tc_fence_after();
       if (nA > 0) { mbar_wait(&bars->q_full[0], 0); tc_fence_after(); issue_s(0, 0); }
       if (nB > 0) { mbar_wait(&bars->q_full[1], 0); tc_fence_after(); issue_s(1, 0); }
+      DBG_T(t_loop0);
       for (int j = 0; j < n; ++j) {
         const int st = j & 1;
         const uint32_t ph = (j >> 1) & 1;
 #pragma unroll
         for (int w = 0; w < 2; ++w) {
           if (j >= n_w[w]) continue;
+          DBG_T(t0);
           mbar_wait(&bars->p_full[w], j & 1);
+          DBG_T(t1);
           mbar_wait(&bars->v_full[st], ph);
           tc_fence_after();
+          DBG_T(t2);
           issue_pv(w, j);
+          DBG_T(t3);
           if (j + 1 < n_w[w]) {
             mbar_wait(&bars->k_full[st ^ 1], ((j + 1) >> 1) & 1);
             tc_fence_after();
+            DBG_T(t4);
             issue_s(w, j + 1);
+            DBG_ADD(7, t4 - t3);
           }
+          DBG_ADD(6, t1 - t0);
+          DBG_ADD(7, t2 - t1);
         }
       }
+      DBG_T(t_loop1);
+      DBG_ADD(5, t_loop1 - t_loop0);
     }
     __syncwarp();
   } else {
@@ -442,10 +302,20 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
     const uint32_t T_S = tmem + lane_base + w * 128;
     const uint32_t T_O = tmem + lane_base + 256 + w * 128;
     float m = 0.f, l = 0.f;
+    DBG_T(t_sm0);
     for (int j = 0; j < nw; ++j) {
       const int kv0 = j * TQ;
+      DBG_T(ts0);
       mbar_wait(&bars->s_full[w], j & 1);
       tc_fence_after();
+      DBG_T(ts1);
+#ifdef B2F_ATTN_DEBUG
+      if (p.dbg_mode >= 1) {
+        tc_fence_before();
+        mbar_arrive(&bars->p_full[w]);
+        continue;
+      }
+#endif
       uint32_t s[128];
 #pragma unroll
       for (int c = 0; c < 4; ++c)
@@ -488,6 +358,7 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
           }
         }
       }
+      DBG_T(ts2);
       float sum0 = 0.f, sum1 = 0.f;
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
@@ -506,7 +377,17 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(&bars->p_full[w]);
+#ifdef B2F_ATTN_DEBUG
+      if (threadIdx.x == 128) {
+        DBG_T(ts3);
+        DBG_ADD(1, ts1 - ts0); DBG_ADD(2, ts2 - ts1); DBG_ADD(3, ts3 - ts2); DBG_ADD(4, 1);
+      }
+#endif
     }
+#ifdef B2F_ATTN_DEBUG
+    DBG_T(t_sm1);
+    if (threadIdx.x == 128) { DBG_ADD(0, t_sm1 - t_sm0); }
+#endif
     if (nw > 0) {
       mbar_wait(&bars->o_full[w], 0);
       tc_fence_after();
@@ -533,6 +414,9 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
       if (qi < p.S && p.lse)
         p.lse[((long long)b * p.H + h) * p.S + qi] = l > 0.f ? (m * LN2 + __logf(l)) : INFINITY;
     }
+#ifdef B2F_ATTN_DEBUG
+    if (threadIdx.x == 128) { DBG_T(t_ep); DBG_ADD(10, t_ep - t_sm1); }
+#endif
   }
   tc_fence_before();
   __syncthreads();
@@ -540,6 +424,16 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
     tc_fence_after();
     tmem_dealloc(tmem, 512);
   }
+#ifdef B2F_ATTN_DEBUG
+  if (threadIdx.x == 0) {
+    DBG_T(t_cta1);
+    unsigned long long ns1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns1));
+    DBG_ADD(8, t_cta1 - t_cta0);
+    DBG_ADD(11, ns1 - ns0);
+    DBG_ADD(12, 1);
+  }
+#endif
 }
 
 // ============================================================== backward
@@ -602,8 +496,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = (p.S + TQ - 1) / TQ;
-  const int q_tile = p.causal ? nq - 1 - (int)blockIdx.x : (int)blockIdx.x;
-  const int h = blockIdx.y, b = blockIdx.z;
+  const int q_tile = p.causal ? nq - 1 - (int)blockIdx.y : (int)blockIdx.y;
+  const int h = blockIdx.x % p.H, b = blockIdx.x / p.H;
   const int hkv = h / (p.H / p.HKV);
   const int q0 = q_tile * TQ;
   int kv_len = p.kv_lens ? p.kv_lens[b] : p.S;
@@ -625,7 +519,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem = bars->tmem_base;
+  require_tmem_base0(bars->tmem_base);
+  constexpr uint32_t tmem = 0;
   const uint32_t T_S = tmem, T_DP = tmem + 128, T_DQ = tmem + 256;
 
   if (warp == 0) {
@@ -649,13 +544,13 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant
     if (lane == 0) {
       const uint32_t idesc_s = make_idesc(1, 1, 128, 128, 0, 0);
       const uint32_t idesc_dq = make_idesc(1, 1, 128, D, 0, 1);
-      const uint32_t aQ = smem_u32(sQ), adO = smem_u32(sdO);
+      const uint32_t aQ = lo_k(smem_u32(sQ)), adO = lo_k(smem_u32(sdO));
       mbar_wait(&bars->fixed_full, 0);
       auto issue_sdp = [&](int j) {
         const int st = j & 1;
         mbar_wait(&bars->st_full[st], (j >> 1) & 1);
         tc_fence_after();
-        const uint32_t aK = smem_u32(sK + st * TILE_B), aV = smem_u32(sV + st * TILE_B);
+        const uint32_t aK = lo_k(smem_u32(sK + st * TILE_B)), aV = lo_k(smem_u32(sV + st * TILE_B));
 #pragma unroll
         for (int k = 0; k < D / 16; ++k) umma_f16_ss(T_S, desc_k(aQ, k), desc_k(aK, k), idesc_s, k > 0);
 #pragma unroll
@@ -667,7 +562,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant
         const int st = j & 1;
         mbar_wait(&bars->ds_full, j & 1);
         tc_fence_after();
-        const uint32_t aK = smem_u32(sK + st * TILE_B);
+        const uint32_t aK = lo_mn(smem_u32(sK + st * TILE_B));
 #pragma unroll
         for (int k = 0; k < TQ / 16; ++k)
           umma_f16_ts(T_DQ, T_S + k * 8, desc_mn(aK, k), idesc_dq, (j | k) != 0);
@@ -761,8 +656,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constan
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = (p.S + TQ - 1) / TQ;
-  const int kv_tile = blockIdx.x;
-  const int hkv = blockIdx.y, b = blockIdx.z;
+  const int kv_tile = blockIdx.y;  // causal: key tile 0 sees every query tile, so ascending = longest first
+  const int hkv = blockIdx.x % p.HKV, b = blockIdx.x / p.HKV;
   const int G = p.H / p.HKV;
   const int kv0 = kv_tile * TQ;
   int kv_len = p.kv_lens ? p.kv_lens[b] : p.S;
@@ -784,7 +679,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constan
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem = bars->tmem_base;
+  require_tmem_base0(bars->tmem_base);
+  constexpr uint32_t tmem = 0;
   const uint32_t T_S = tmem, T_DP = tmem + 128, T_DV = tmem + 256, T_DK = tmem + 256 + D;
 
   if (warp == 0) {
@@ -810,13 +706,13 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constan
     if (lane == 0) {
       const uint32_t idesc_s = make_idesc(1, 1, 128, 128, 0, 0);
       const uint32_t idesc_acc = make_idesc(1, 1, 128, D, 0, 1);
-      const uint32_t aK = smem_u32(sK), aV = smem_u32(sV);
+      const uint32_t aK = lo_k(smem_u32(sK)), aV = lo_k(smem_u32(sV));
       mbar_wait(&bars->fixed_full, 0);
       auto issue_sdp = [&](int it) {
         const int st = it & 1;
         mbar_wait(&bars->st_full[st], (it >> 1) & 1);
         tc_fence_after();
-        const uint32_t aQ = smem_u32(sQ + st * TILE_B), adO = smem_u32(sdO + st * TILE_B);
+        const uint32_t aQ = lo_k(smem_u32(sQ + st * TILE_B)), adO = lo_k(smem_u32(sdO + st * TILE_B));
 #pragma unroll
         for (int k = 0; k < D / 16; ++k) umma_f16_ss(T_S, desc_k(aK, k), desc_k(aQ, k), idesc_s, k > 0);
 #pragma unroll
@@ -828,7 +724,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constan
         const int st = it & 1;
         mbar_wait(&bars->ds_full, it & 1);
         tc_fence_after();
-        const uint32_t aQ = smem_u32(sQ + st * TILE_B), adO = smem_u32(sdO + st * TILE_B);
+        const uint32_t aQ = lo_mn(smem_u32(sQ + st * TILE_B)), adO = lo_mn(smem_u32(sdO + st * TILE_B));
 #pragma unroll
         for (int k = 0; k < TQ / 16; ++k)
           umma_f16_ts(T_DV, T_S + k * 8, desc_mn(adO, k), idesc_acc, (it | k) != 0);
@@ -944,6 +840,18 @@ int check_common(int B, int S, int H, int HKV, int D) {
 
 }  // namespace
 
+#ifdef B2F_ATTN_DEBUG
+extern "C" int b2f_attn_debug(unsigned long long* out, int reset) {
+  if (reset) {
+    unsigned long long z[16] = {0};
+    B2F_CHECK_CUDA(cudaMemcpyToSymbol(g_attn_dbg, z, sizeof(z)));
+  } else {
+    B2F_CHECK_CUDA(cudaMemcpyFromSymbol(out, g_attn_dbg, sizeof(unsigned long long) * 16));
+  }
+  return 0;
+}
+#endif
+
 extern "C" int b2f_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B,
                             int S, int H, int HKV, int D, long long q_ts, long long q_bs,
                             long long k_ts, long long k_bs, long long v_ts, long long v_bs,
@@ -960,31 +868,19 @@ extern "C" int b2f_attn_fwd(const void* q, const void* k, const void* v, void* o
   p.B = B; p.H = H; p.HKV = HKV; p.S = S;
   p.scale = scale; p.scale_log2 = scale * LOG2E; p.causal = causal; p.kv_lens = kv_lens;
   p.O = static_cast<__nv_bfloat16*>(o); p.o_ts = o_ts; p.o_bs = o_bs; p.lse = lse;
-  dim3 grid((S + TQ - 1) / TQ, H, B);
+#ifdef B2F_ATTN_DEBUG
+  if (const char* e = getenv("B2F_ATTN_DBG_MODE")) p.dbg_mode = atoi(e);
+#endif
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  static const bool use_v1 = [] { const char* e = getenv("B2F_ATTN_FWD"); return e && e[0] == '1'; }();
-  if (!use_v1) {
-    dim3 grid2((S + 2 * TQ - 1) / (2 * TQ), H, B);
-    if (D == 128) {
-      const int smem = 6 * Cfg<128>::TILE_B + 1024 + sizeof(Fwd2Bars);
-      if (int rc = set_smem(attn_fwd2_kernel<128>, smem)) return rc;
-      attn_fwd2_kernel<128><<<grid2, FWD2_THREADS, smem, st>>>(mq, mk, mv, p);
-    } else {
-      const int smem = 6 * Cfg<64>::TILE_B + 1024 + sizeof(Fwd2Bars);
-      if (int rc = set_smem(attn_fwd2_kernel<64>, smem)) return rc;
-      attn_fwd2_kernel<64><<<grid2, FWD2_THREADS, smem, st>>>(mq, mk, mv, p);
-    }
-    B2F_CHECK_CUDA(cudaGetLastError());
-    return 0;
-  }
+  dim3 grid2(H * B, (S + 2 * TQ - 1) / (2 * TQ), 1);
   if (D == 128) {
-    const int smem = 5 * Cfg<128>::TILE_B + 1024 + sizeof(FwdBars);
-    if (int rc = set_smem(attn_fwd_kernel<128>, smem)) return rc;
-    attn_fwd_kernel<128><<<grid, ATT_THREADS, smem, st>>>(mq, mk, mv, p);
+    const int smem = 6 * Cfg<128>::TILE_B + 1024 + sizeof(Fwd2Bars);
+    if (int rc = set_smem(attn_fwd2_kernel<128>, smem)) return rc;
+    attn_fwd2_kernel<128><<<grid2, FWD2_THREADS, smem, st>>>(mq, mk, mv, p);
   } else {
-    const int smem = 5 * Cfg<64>::TILE_B + 1024 + sizeof(FwdBars);
-    if (int rc = set_smem(attn_fwd_kernel<64>, smem)) return rc;
-    attn_fwd_kernel<64><<<grid, ATT_THREADS, smem, st>>>(mq, mk, mv, p);
+    const int smem = 6 * Cfg<64>::TILE_B + 1024 + sizeof(Fwd2Bars);
+    if (int rc = set_smem(attn_fwd2_kernel<64>, smem)) return rc;
+    attn_fwd2_kernel<64><<<grid2, FWD2_THREADS, smem, st>>>(mq, mk, mv, p);
   }
   B2F_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -1023,16 +919,16 @@ extern "C" int b2f_attn_bwd(const void* q, const void* k, const void* v, const v
     const int smem = 6 * Cfg<128>::TILE_B + 1024 + sizeof(BwdBars);
     if (int rc = set_smem(attn_bwd_dq_kernel<128>, smem)) return rc;
     if (int rc = set_smem(attn_bwd_dkv_kernel<128>, smem)) return rc;
-    attn_bwd_dq_kernel<128><<<dim3(nq, H, B), ATT_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
-    attn_bwd_dkv_kernel<128><<<dim3(nq, HKV, B), ATT_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+    attn_bwd_dq_kernel<128><<<dim3(H * B, nq, 1), ATT_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+    attn_bwd_dkv_kernel<128><<<dim3(HKV * B, nq, 1), ATT_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
   } else {
     attn_delta_kernel<64><<<dgrid, 256, 0, st>>>((const __nv_bfloat16*)o, o_ts, o_bs,
                                                  (const __nv_bfloat16*)d_o, do_ts, do_bs, delta, B, H, S);
     const int smem = 6 * Cfg<64>::TILE_B + 1024 + sizeof(BwdBars);
     if (int rc = set_smem(attn_bwd_dq_kernel<64>, smem)) return rc;
     if (int rc = set_smem(attn_bwd_dkv_kernel<64>, smem)) return rc;
-    attn_bwd_dq_kernel<64><<<dim3(nq, H, B), ATT_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
-    attn_bwd_dkv_kernel<64><<<dim3(nq, HKV, B), ATT_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+    attn_bwd_dq_kernel<64><<<dim3(H * B, nq, 1), ATT_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+    attn_bwd_dkv_kernel<64><<<dim3(HKV * B, nq, 1), ATT_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
   }
   B2F_CHECK_CUDA(cudaGetLastError());
   return 0;
