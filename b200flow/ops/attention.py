@@ -43,7 +43,9 @@ def attn_bwd_raw(q, k, v, o, do, lse, causal: bool, scale: float, kv_lens=None, 
         dk = torch.empty((B, S, HKV, D), dtype=torch.bfloat16, device=q.device)
     if dv is None:
         dv = torch.empty((B, S, HKV, D), dtype=torch.bfloat16, device=q.device)
-    delta = torch.empty((B, H, S), dtype=torch.float32, device=q.device)
+    s_pad = (S + 127) // 128 * 128
+    # scratch for the pre-pass: [lse * log2e | rowsum(o * do)], query rows padded to whole tiles
+    delta = torch.empty((2, B, H, s_pad), dtype=torch.float32, device=q.device)
     if not (do.stride(3) == 1 and do.stride(2) == D):
         do = do.contiguous()
     args = []

@@ -33,7 +33,6 @@ namespace {
 
 constexpr int TQ = 128;           // rows per tile (queries or keys)
 constexpr int CHUNK_B = 128 * 128;  // one 128-row x 64-col bf16 chunk, 128 B rows = 16 KB
-constexpr int ATT_THREADS = 192;
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
 
@@ -437,23 +436,27 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
 }
 
 // ============================================================== backward
-// delta[b,h,s] = sum_d O[b,s,h,d] * dO[b,s,h,d]
+// Pre-pass over every (padded) query row: dlt = rowsum(O * dO) and lse2 = lse * log2(e), written to
+// the fp32 scratch [2][B*H][S_pad] (S_pad = S rounded up to 128).  Padding rows get lse2 = +inf and
+// dlt = 0, so the main kernels can bulk-copy whole 128-row slices and see P = 0 there.
 template <int D>
 __global__ void __launch_bounds__(256)
 attn_delta_kernel(const __nv_bfloat16* __restrict__ O, long long o_ts, long long o_bs,
                   const __nv_bfloat16* __restrict__ dO, long long do_ts, long long do_bs,
-                  float* __restrict__ delta, int B, int H, int S) {
+                  const float* __restrict__ lse, float* __restrict__ scr, int B, int H, int S,
+                  int S_pad) {
   constexpr int TPR = D / 8;  // threads per row
   const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  const long long row = gid / TPR;  // over B*S*H (token-major, then head)
+  const long long row = gid / TPR;  // over B*S_pad*H (token-major, then head)
   const int part = (int)(gid % TPR);
-  const long long total = (long long)B * S * H;
+  const long long total = (long long)B * S_pad * H;
+  const int h = (int)(row % H);
+  const long long tok = row / H;
+  const int s = (int)(tok % S_pad);
+  const int b = (int)(tok / S_pad);
+  const bool live = row < total && s < S;
   float acc = 0.f;
-  if (row < total) {
-    const int h = (int)(row % H);
-    const long long tok = row / H;
-    const int s = (int)(tok % S);
-    const int b = (int)(tok / S);
+  if (live) {
     const uint4 a = *reinterpret_cast<const uint4*>(O + b * o_bs + (long long)s * o_ts + (long long)h * D + part * 8);
     const uint4 g = *reinterpret_cast<const uint4*>(dO + b * do_bs + (long long)s * do_ts + (long long)h * D + part * 8);
     float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y), a2 = unpack_bf16x2(a.z), a3 = unpack_bf16x2(a.w);
@@ -464,24 +467,62 @@ attn_delta_kernel(const __nv_bfloat16* __restrict__ O, long long o_ts, long long
 #pragma unroll
   for (int o = TPR / 2; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
   if (row < total && part == 0) {
-    const int h = (int)(row % H);
-    const long long tok = row / H;
-    const int s = (int)(tok % S);
-    const int b = (int)(tok / S);
-    delta[((long long)b * H + h) * S + s] = acc;
+    const long long idx = ((long long)b * H + h) * S_pad + s;
+    scr[idx] = live ? lse[((long long)b * H + h) * S + s] * LOG2E : INFINITY;
+    scr[(long long)B * H * S_pad + idx] = acc;
   }
 }
 
+// Backward kernels: 384 threads.  Warpgroup 0 = TMA warp + MMA warp; warpgroups 1 and 2 each take
+// 64 of the 128 columns of the score tile (one tile row per thread).  Both groups read their fp32
+// columns of S / dP into registers, meet at a named barrier, and only then overwrite the front of
+// those TMEM regions with the bf16 P / dS operands.  The softmax scale is folded into the epilogue.
+constexpr int BWD_THREADS = 384;
+
 struct BwdBars {
-  uint64_t fixed_full, st_full[2], st_empty[2], s_full, ds_full, acc_full;
+  uint64_t fixed_full, st_full[2], st_empty[2], s_full[2], dp_full, ds_full, acc_full;
   uint32_t tmem_base;
-  float lse2[128];
-  float dlt[128];
+  alignas(128) float lse2[2][128];  // dkv kernel: per-stage statistics of the staged query tile
+  alignas(128) float dlt[2][128];
 };
 
-// ---- dQ: CTA per (q tile, head, batch); loops over key tiles.
+__device__ __forceinline__ void load_cols64(uint32_t taddr, uint32_t (&r)[64]) {
+  tmem_ld_32x32b_x32(taddr, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
+  tmem_ld_32x32b_x32(taddr + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+}
+__device__ __forceinline__ void store_cols32(uint32_t taddr, const uint32_t (&r)[32]) {
+  tmem_st_32x32b_x16(taddr, *reinterpret_cast<const uint32_t(*)[16]>(&r[0]));
+  tmem_st_32x32b_x16(taddr + 16, *reinterpret_cast<const uint32_t(*)[16]>(&r[16]));
+}
+
+// Accumulator rows -> bf16 global rows; the two compute warpgroups split the D columns.
 template <int D>
-__global__ void __launch_bounds__(ATT_THREADS, 1)
+__device__ __forceinline__ void store_acc_half(uint32_t taddr, __nv_bfloat16* row, int cg, bool ok, float mul) {
+#pragma unroll
+  for (int c = 0; c < D / 64; ++c) {
+    uint32_t acc[32];
+    const int col = cg * (D / 2) + c * 32;
+    tmem_ld_32x32b_x32(taddr + col, acc);
+    tmem_ld_wait();
+    if (ok) {
+#pragma unroll
+      for (int q4 = 0; q4 < 4; ++q4) {
+        uint4 u;
+        u.x = pack_bf16x2(__uint_as_float(acc[q4 * 8 + 0]) * mul, __uint_as_float(acc[q4 * 8 + 1]) * mul);
+        u.y = pack_bf16x2(__uint_as_float(acc[q4 * 8 + 2]) * mul, __uint_as_float(acc[q4 * 8 + 3]) * mul);
+        u.z = pack_bf16x2(__uint_as_float(acc[q4 * 8 + 4]) * mul, __uint_as_float(acc[q4 * 8 + 5]) * mul);
+        u.w = pack_bf16x2(__uint_as_float(acc[q4 * 8 + 6]) * mul, __uint_as_float(acc[q4 * 8 + 7]) * mul);
+        *reinterpret_cast<uint4*>(row + col + q4 * 8) = u;
+      }
+    }
+  }
+}
+
+// ---- dQ: CTA per (q tile, head, batch); loops over key tiles.  TMEM: S double-buffered
+// [0,256), dP / dS [256,384), dQ [384,384+D): S(j+1) = Q K^T runs while the compute groups are
+// still busy with tile j.
+template <int D>
+__global__ void __launch_bounds__(BWD_THREADS, 1)
 attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
                    const __grid_constant__ CUtensorMap mv, const __grid_constant__ CUtensorMap mdo,
                    const AttnParams p) {
@@ -509,9 +550,13 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&mq); tma_prefetch_desc(&mk); tma_prefetch_desc(&mv); tma_prefetch_desc(&mdo);
     mbar_init(&bars->fixed_full, 1);
-    for (int i = 0; i < 2; ++i) { mbar_init(&bars->st_full[i], 1); mbar_init(&bars->st_empty[i], 1); }
-    mbar_init(&bars->s_full, 1);
-    mbar_init(&bars->ds_full, 128);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bars->st_full[i], 1);
+      mbar_init(&bars->st_empty[i], 1);
+      mbar_init(&bars->s_full[i], 1);
+    }
+    mbar_init(&bars->dp_full, 1);
+    mbar_init(&bars->ds_full, 256);
     mbar_init(&bars->acc_full, 1);
     fence_mbar_init();
   }
@@ -520,128 +565,140 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant
   __syncthreads();
   tc_fence_after();
   require_tmem_base0(bars->tmem_base);
-  constexpr uint32_t tmem = 0;
-  const uint32_t T_S = tmem, T_DP = tmem + 128, T_DQ = tmem + 256;
+  constexpr uint32_t T_S = 0, T_DP = 256, T_DQ = 384;
 
-  if (warp == 0) {
-    if (lane == 0) {
+  if (warp < 4) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
+    if (warp == 0 && lane == 0) {
       mbar_arrive_expect_tx(&bars->fixed_full, 2 * TILE_B);
       load_tile<D>(sQ, &mq, &bars->fixed_full, q0, h, b);
       load_tile<D>(sdO, &mdo, &bars->fixed_full, q0, h, b);
-      int st = 0;
-      uint32_t ph = 0;
       for (int j = 0; j < n; ++j) {
-        mbar_wait(&bars->st_empty[st], ph ^ 1);
+        const int st = j & 1;
+        mbar_wait(&bars->st_empty[st], ((j >> 1) & 1) ^ 1);
         mbar_arrive_expect_tx(&bars->st_full[st], 2 * TILE_B);
         load_tile<D>(sK + st * TILE_B, &mk, &bars->st_full[st], j * TQ, hkv, b);
         load_tile<D>(sV + st * TILE_B, &mv, &bars->st_full[st], j * TQ, hkv, b);
-        st ^= 1;
-        if (st == 0) ph ^= 1;
       }
-    }
-    __syncwarp();
-  } else if (warp == 1) {
-    if (lane == 0) {
+    } else if (warp == 1) {
       const uint32_t idesc_s = make_idesc(1, 1, 128, 128, 0, 0);
       const uint32_t idesc_dq = make_idesc(1, 1, 128, D, 0, 1);
       const uint32_t aQ = lo_k(smem_u32(sQ)), adO = lo_k(smem_u32(sdO));
-      mbar_wait(&bars->fixed_full, 0);
-      auto issue_sdp = [&](int j) {
+      auto issue_s = [&](int j) {
         const int st = j & 1;
-        mbar_wait(&bars->st_full[st], (j >> 1) & 1);
-        tc_fence_after();
-        const uint32_t aK = lo_k(smem_u32(sK + st * TILE_B)), aV = lo_k(smem_u32(sV + st * TILE_B));
+        const uint32_t aK = lo_k(smem_u32(sK + st * TILE_B));
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < D / 16; ++k) umma_f16_ss(T_S, desc_k(aQ, k), desc_k(aK, k), idesc_s, k > 0);
-#pragma unroll
-        for (int k = 0; k < D / 16; ++k) umma_f16_ss(T_DP, desc_k(adO, k), desc_k(aV, k), idesc_s, k > 0);
-        umma_commit(&bars->s_full);
+          for (int k = 0; k < D / 16; ++k)
+            umma_f16_ss(T_S + st * 128, desc_k(aQ, k), desc_k(aK, k), idesc_s, k > 0);
+          umma_commit(&bars->s_full[st]);
+        }
+        __syncwarp();
       };
-      issue_sdp(0);
+      auto issue_dp = [&](int j) {
+        const uint32_t aV = lo_k(smem_u32(sV + (j & 1) * TILE_B));
+        if (elect_one()) {
+#pragma unroll
+          for (int k = 0; k < D / 16; ++k)
+            umma_f16_ss(T_DP, desc_k(adO, k), desc_k(aV, k), idesc_s, k > 0);
+          umma_commit(&bars->dp_full);
+        }
+        __syncwarp();
+      };
+      mbar_wait(&bars->fixed_full, 0);
+      mbar_wait(&bars->st_full[0], 0);
+      tc_fence_after();
+      issue_s(0);
+      issue_dp(0);
       for (int j = 0; j < n; ++j) {
         const int st = j & 1;
+        if (j + 1 < n) {
+          mbar_wait(&bars->st_full[st ^ 1], ((j + 1) >> 1) & 1);
+          tc_fence_after();
+          issue_s(j + 1);
+        }
         mbar_wait(&bars->ds_full, j & 1);
         tc_fence_after();
         const uint32_t aK = lo_mn(smem_u32(sK + st * TILE_B));
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < TQ / 16; ++k)
-          umma_f16_ts(T_DQ, T_S + k * 8, desc_mn(aK, k), idesc_dq, (j | k) != 0);
-        umma_commit(&bars->st_empty[st]);
-        if (j + 1 < n) issue_sdp(j + 1);
+          for (int k = 0; k < TQ / 16; ++k)
+            umma_f16_ts(T_DQ, T_DP + k * 8, desc_mn(aK, k), idesc_dq, (j | k) != 0);
+          umma_commit(&bars->st_empty[st]);
+          if (j + 1 == n) umma_commit(&bars->acc_full);
+        }
+        __syncwarp();
+        if (j + 1 < n) issue_dp(j + 1);
       }
-      umma_commit(&bars->acc_full);
     }
-    __syncwarp();
   } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
+    const int cg = (warp - 4) >> 2;  // column group: score columns [cg*64, cg*64+64)
     const int qw = warp & 3;
     const int r = qw * 32 + lane;
     const int qi = q0 + r;
     const uint32_t lane_base = static_cast<uint32_t>(qw * 32) << 16;
-    const long long sidx = ((long long)b * p.H + h) * p.S + qi;
-    const float lse2 = qi < p.S ? p.lse[sidx] * LOG2E : INFINITY;
-    const float dlt = qi < p.S ? p.delta[sidx] : 0.f;
+    const int S_pad = nq * TQ;
+    const long long sidx = ((long long)b * p.H + h) * S_pad + qi;
+    const float lse2 = p.delta[sidx];
+    const float dlt = p.delta[(long long)p.B * p.H * S_pad + sidx];
     for (int j = 0; j < n; ++j) {
       const int kv0 = j * TQ;
-      mbar_wait(&bars->s_full, j & 1);
+      DBG_T(tq0);
+      mbar_wait(&bars->s_full[j & 1], (j >> 1) & 1);
+      mbar_wait(&bars->dp_full, j & 1);
       tc_fence_after();
+      DBG_T(tq1);
+      uint32_t sa[64], da[64];
+      load_cols64(T_S + lane_base + (j & 1) * 128 + cg * 64, sa);
+      load_cols64(T_DP + lane_base + cg * 64, da);
+      tmem_ld_wait();
+      tc_fence_before();
+      named_bar_sync(2, 256);  // every fp32 dP column is in registers: dS may now overwrite them
+      tc_fence_after();
+      DBG_T(tq2);
       const bool need_mask = (p.causal && kv0 + TQ - 1 > q0) || (kv0 + TQ > kv_len);
       int lim = kv_len;
       if (p.causal && qi + 1 < lim) lim = qi + 1;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t sa[32], da[32];
-        tmem_ld_32x32b_x32(T_S + lane_base + c * 32, sa);
-        tmem_ld_32x32b_x32(T_DP + lane_base + c * 32, da);
-        tmem_ld_wait();
-        uint32_t pk[16];
+      lim -= kv0 + cg * 64;  // first masked column among this thread's 64
+      uint32_t pk[32];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          float p0 = ex2(__uint_as_float(sa[2 * i]) * p.scale_log2 - lse2);
-          float p1 = ex2(__uint_as_float(sa[2 * i + 1]) * p.scale_log2 - lse2);
-          if (need_mask) {
-            if (kv0 + c * 32 + 2 * i >= lim) p0 = 0.f;
-            if (kv0 + c * 32 + 2 * i + 1 >= lim) p1 = 0.f;
-          }
-          const float d0 = p0 * (__uint_as_float(da[2 * i]) - dlt) * p.scale;
-          const float d1 = p1 * (__uint_as_float(da[2 * i + 1]) - dlt) * p.scale;
-          pk[i] = pack_bf16x2(d0, d1);
+      for (int i = 0; i < 32; ++i) {
+        float p0 = ex2(fmaf(__uint_as_float(sa[2 * i]), p.scale_log2, -lse2));
+        float p1 = ex2(fmaf(__uint_as_float(sa[2 * i + 1]), p.scale_log2, -lse2));
+        if (need_mask) {
+          if (2 * i >= lim) p0 = 0.f;
+          if (2 * i + 1 >= lim) p1 = 0.f;
         }
-        tmem_st_32x32b_x16(T_S + lane_base + c * 16, pk);
+        pk[i] = pack_bf16x2(p0 * (__uint_as_float(da[2 * i]) - dlt),
+                            p1 * (__uint_as_float(da[2 * i + 1]) - dlt));
       }
+      store_cols32(T_DP + lane_base + cg * 32, pk);
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(&bars->ds_full);
+#ifdef B2F_ATTN_DEBUG
+      if (threadIdx.x == 128) {
+        DBG_T(tq3);
+        DBG_ADD(5, tq1 - tq0); DBG_ADD(6, tq2 - tq1); DBG_ADD(7, tq3 - tq2); DBG_ADD(8, 1);
+      }
+#endif
     }
     mbar_wait(&bars->acc_full, 0);
     tc_fence_after();
     __nv_bfloat16* drow = p.dQ + (long long)b * p.dq_bs + (long long)qi * p.dq_ts + (long long)h * D;
-#pragma unroll
-    for (int c = 0; c < D / 32; ++c) {
-      uint32_t acc[32];
-      tmem_ld_32x32b_x32(T_DQ + lane_base + c * 32, acc);
-      tmem_ld_wait();
-      if (qi < p.S) {
-#pragma unroll
-        for (int q4 = 0; q4 < 4; ++q4) {
-          uint4 u;
-          u.x = pack_bf16x2(__uint_as_float(acc[q4 * 8 + 0]), __uint_as_float(acc[q4 * 8 + 1]));
-          u.y = pack_bf16x2(__uint_as_float(acc[q4 * 8 + 2]), __uint_as_float(acc[q4 * 8 + 3]));
-          u.z = pack_bf16x2(__uint_as_float(acc[q4 * 8 + 4]), __uint_as_float(acc[q4 * 8 + 5]));
-          u.w = pack_bf16x2(__uint_as_float(acc[q4 * 8 + 6]), __uint_as_float(acc[q4 * 8 + 7]));
-          *reinterpret_cast<uint4*>(drow + c * 32 + q4 * 8) = u;
-        }
-      }
-    }
+    store_acc_half<D>(T_DQ + lane_base, drow, cg, qi < p.S, p.scale);
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem, 512); }
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(0, 512); }
 }
 
-// ---- dK/dV: CTA per (key tile, kv head, batch); loops over the query heads of
-// the group and over query tiles.
+// ---- dK/dV: CTA per (key tile, kv head, batch); loops over the query heads of the group and
+// over query tiles.  TMEM: S^T [0,128) -> P^T, dP^T [128,256) -> dS^T, dV [256,..), dK [384,..).
+// The TMA warp also stages each query tile's lse2 / dlt rows (two 512 B bulk copies).
 template <int D>
-__global__ void __launch_bounds__(ATT_THREADS, 1)
+__global__ void __launch_bounds__(BWD_THREADS, 1)
 attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
                     const __grid_constant__ CUtensorMap mv, const __grid_constant__ CUtensorMap mdo,
                     const AttnParams p) {
@@ -665,13 +722,14 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constan
   const int i0 = p.causal ? kv_tile : 0;
   const int per_head = nq - i0;
   const int n = per_head * G;
+  const int S_pad = nq * TQ;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&mq); tma_prefetch_desc(&mk); tma_prefetch_desc(&mv); tma_prefetch_desc(&mdo);
     mbar_init(&bars->fixed_full, 1);
     for (int i = 0; i < 2; ++i) { mbar_init(&bars->st_full[i], 1); mbar_init(&bars->st_empty[i], 1); }
-    mbar_init(&bars->s_full, 1);
-    mbar_init(&bars->ds_full, 128);
+    mbar_init(&bars->s_full[0], 1);
+    mbar_init(&bars->ds_full, 256);
     mbar_init(&bars->acc_full, 1);
     fence_mbar_init();
   }
@@ -680,145 +738,144 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constan
   __syncthreads();
   tc_fence_after();
   require_tmem_base0(bars->tmem_base);
-  constexpr uint32_t tmem = 0;
-  const uint32_t T_S = tmem, T_DP = tmem + 128, T_DV = tmem + 256, T_DK = tmem + 256 + D;
+  constexpr uint32_t T_S = 0, T_DP = 128, T_DV = 256, T_DK = 384;
 
-  if (warp == 0) {
-    if (lane == 0) {
+  if (warp < 4) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
+    if (warp == 0 && lane == 0) {
       mbar_arrive_expect_tx(&bars->fixed_full, 2 * TILE_B);
       load_tile<D>(sK, &mk, &bars->fixed_full, kv0, hkv, b);
       load_tile<D>(sV, &mv, &bars->fixed_full, kv0, hkv, b);
-      int st = 0;
-      uint32_t ph = 0;
       for (int it = 0; it < n; ++it) {
+        const int st = it & 1;
         const int g = it / per_head, i = i0 + it % per_head;
         const int h = hkv * G + g;
-        mbar_wait(&bars->st_empty[st], ph ^ 1);
-        mbar_arrive_expect_tx(&bars->st_full[st], 2 * TILE_B);
+        mbar_wait(&bars->st_empty[st], ((it >> 1) & 1) ^ 1);
+        mbar_arrive_expect_tx(&bars->st_full[st], 2 * TILE_B + 2 * TQ * 4);
         load_tile<D>(sQ + st * TILE_B, &mq, &bars->st_full[st], i * TQ, h, b);
         load_tile<D>(sdO + st * TILE_B, &mdo, &bars->st_full[st], i * TQ, h, b);
-        st ^= 1;
-        if (st == 0) ph ^= 1;
+        const float* stats = p.delta + ((long long)b * p.H + h) * S_pad + i * TQ;
+        bulk_load_1d(bars->lse2[st], stats, TQ * 4, &bars->st_full[st]);
+        bulk_load_1d(bars->dlt[st], stats + (long long)p.B * p.H * S_pad, TQ * 4, &bars->st_full[st]);
       }
-    }
-    __syncwarp();
-  } else if (warp == 1) {
-    if (lane == 0) {
+    } else if (warp == 1) {
       const uint32_t idesc_s = make_idesc(1, 1, 128, 128, 0, 0);
       const uint32_t idesc_acc = make_idesc(1, 1, 128, D, 0, 1);
       const uint32_t aK = lo_k(smem_u32(sK)), aV = lo_k(smem_u32(sV));
-      mbar_wait(&bars->fixed_full, 0);
       auto issue_sdp = [&](int it) {
         const int st = it & 1;
         mbar_wait(&bars->st_full[st], (it >> 1) & 1);
         tc_fence_after();
         const uint32_t aQ = lo_k(smem_u32(sQ + st * TILE_B)), adO = lo_k(smem_u32(sdO + st * TILE_B));
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < D / 16; ++k) umma_f16_ss(T_S, desc_k(aK, k), desc_k(aQ, k), idesc_s, k > 0);
+          for (int k = 0; k < D / 16; ++k) umma_f16_ss(T_S, desc_k(aK, k), desc_k(aQ, k), idesc_s, k > 0);
 #pragma unroll
-        for (int k = 0; k < D / 16; ++k) umma_f16_ss(T_DP, desc_k(aV, k), desc_k(adO, k), idesc_s, k > 0);
-        umma_commit(&bars->s_full);
+          for (int k = 0; k < D / 16; ++k) umma_f16_ss(T_DP, desc_k(aV, k), desc_k(adO, k), idesc_s, k > 0);
+          umma_commit(&bars->s_full[0]);
+        }
+        __syncwarp();
       };
+      mbar_wait(&bars->fixed_full, 0);
       if (n > 0) issue_sdp(0);
       for (int it = 0; it < n; ++it) {
         const int st = it & 1;
         mbar_wait(&bars->ds_full, it & 1);
         tc_fence_after();
         const uint32_t aQ = lo_mn(smem_u32(sQ + st * TILE_B)), adO = lo_mn(smem_u32(sdO + st * TILE_B));
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < TQ / 16; ++k)
-          umma_f16_ts(T_DV, T_S + k * 8, desc_mn(adO, k), idesc_acc, (it | k) != 0);
+          for (int k = 0; k < TQ / 16; ++k)
+            umma_f16_ts(T_DV, T_S + k * 8, desc_mn(adO, k), idesc_acc, (it | k) != 0);
 #pragma unroll
-        for (int k = 0; k < TQ / 16; ++k)
-          umma_f16_ts(T_DK, T_DP + k * 8, desc_mn(aQ, k), idesc_acc, (it | k) != 0);
-        umma_commit(&bars->st_empty[st]);
+          for (int k = 0; k < TQ / 16; ++k)
+            umma_f16_ts(T_DK, T_DP + k * 8, desc_mn(aQ, k), idesc_acc, (it | k) != 0);
+          umma_commit(&bars->st_empty[st]);
+          if (it + 1 == n) umma_commit(&bars->acc_full);
+        }
+        __syncwarp();
         if (it + 1 < n) issue_sdp(it + 1);
       }
-      umma_commit(&bars->acc_full);
     }
-    __syncwarp();
   } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
+    const int cg = (warp - 4) >> 2;  // column group: query columns [cg*64, cg*64+64) of the S^T tile
     const int qw = warp & 3;
     const int r = qw * 32 + lane;
-    const int t = threadIdx.x - 64;  // 0..127 among the softmax threads
     const int ki = kv0 + r;
     const uint32_t lane_base = static_cast<uint32_t>(qw * 32) << 16;
+    const bool row_dead = ki >= kv_len;
     for (int it = 0; it < n; ++it) {
-      const int g = it / per_head, i = i0 + it % per_head;
-      const int h = hkv * G + g;
+      const int st = it & 1;
+      const int i = i0 + it % per_head;
       const int q0 = i * TQ;
-      named_bar_sync(1, 128);
-      {
-        const int qi = q0 + t;
-        const long long sidx = ((long long)b * p.H + h) * p.S + qi;
-        bars->lse2[t] = qi < p.S ? p.lse[sidx] * LOG2E : INFINITY;
-        bars->dlt[t] = qi < p.S ? p.delta[sidx] : 0.f;
-      }
-      named_bar_sync(1, 128);
-      mbar_wait(&bars->s_full, it & 1);
+      DBG_T(tk0);
+      mbar_wait(&bars->st_full[st], (it >> 1) & 1);  // lse2 / dlt rows of this query tile are staged
+      mbar_wait(&bars->s_full[0], it & 1);
       tc_fence_after();
-      const bool row_dead = ki >= kv_len;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t sa[32], da[32];
-        tmem_ld_32x32b_x32(T_S + lane_base + c * 32, sa);
-        tmem_ld_32x32b_x32(T_DP + lane_base + c * 32, da);
-        tmem_ld_wait();
-        uint32_t pp[16], pd[16];
+      DBG_T(tk1);
+      uint32_t sa[64], da[64];
+      load_cols64(T_S + lane_base + cg * 64, sa);
+      load_cols64(T_DP + lane_base + cg * 64, da);
+      tmem_ld_wait();
+      tc_fence_before();
+      named_bar_sync(2, 256);
+      tc_fence_after();
+      DBG_T(tk2);
+      const bool need_mask = (p.causal && q0 < kv0 + TQ - 1) || (kv0 + TQ > kv_len);
+      // causal: query column c is visible to key row ki iff q0 + c >= ki
+      const int first_ok = row_dead ? 128 : (p.causal ? ki - q0 - cg * 64 : 0);
+      const float4* l4 = reinterpret_cast<const float4*>(&bars->lse2[st][cg * 64]);
+      const float4* d4 = reinterpret_cast<const float4*>(&bars->dlt[st][cg * 64]);
+      uint32_t pp[32], pd[32];
 #pragma unroll
-        for (int i2 = 0; i2 < 16; ++i2) {
-          const int c0 = c * 32 + 2 * i2;
-          float p0 = ex2(__uint_as_float(sa[2 * i2]) * p.scale_log2 - bars->lse2[c0]);
-          float p1 = ex2(__uint_as_float(sa[2 * i2 + 1]) * p.scale_log2 - bars->lse2[c0 + 1]);
-          if (row_dead || (p.causal && q0 + c0 < ki)) p0 = 0.f;
-          if (row_dead || (p.causal && q0 + c0 + 1 < ki)) p1 = 0.f;
-          const float d0 = p0 * (__uint_as_float(da[2 * i2]) - bars->dlt[c0]) * p.scale;
-          const float d1 = p1 * (__uint_as_float(da[2 * i2 + 1]) - bars->dlt[c0 + 1]) * p.scale;
-          pp[i2] = pack_bf16x2(p0, p1);
-          pd[i2] = pack_bf16x2(d0, d1);
+      for (int i4 = 0; i4 < 16; ++i4) {
+        const float4 lv = l4[i4], dv = d4[i4];
+        const float ls[4] = {lv.x, lv.y, lv.z, lv.w};
+        const float ds_[4] = {dv.x, dv.y, dv.z, dv.w};
+        float pv[4], dsv[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int c = i4 * 4 + e;
+          float pe = ex2(fmaf(__uint_as_float(sa[c]), p.scale_log2, -ls[e]));
+          if (need_mask && c < first_ok) pe = 0.f;
+          pv[e] = pe;
+          dsv[e] = pe * (__uint_as_float(da[c]) - ds_[e]);
         }
-        tmem_st_32x32b_x16(T_S + lane_base + c * 16, pp);
-        tmem_st_32x32b_x16(T_DP + lane_base + c * 16, pd);
+        pp[i4 * 2] = pack_bf16x2(pv[0], pv[1]);
+        pp[i4 * 2 + 1] = pack_bf16x2(pv[2], pv[3]);
+        pd[i4 * 2] = pack_bf16x2(dsv[0], dsv[1]);
+        pd[i4 * 2 + 1] = pack_bf16x2(dsv[2], dsv[3]);
       }
+      store_cols32(T_S + lane_base + cg * 32, pp);
+      store_cols32(T_DP + lane_base + cg * 32, pd);
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(&bars->ds_full);
+#ifdef B2F_ATTN_DEBUG
+      if (threadIdx.x == 128) {
+        DBG_T(tk3);
+        DBG_ADD(1, tk1 - tk0); DBG_ADD(2, tk2 - tk1); DBG_ADD(3, tk3 - tk2); DBG_ADD(4, 1);
+      }
+#endif
     }
-    mbar_wait(&bars->acc_full, 0);
-    tc_fence_after();
     __nv_bfloat16* vrow = p.dV + (long long)b * p.dv_bs + (long long)ki * p.dv_ts + (long long)hkv * D;
     __nv_bfloat16* krow = p.dK + (long long)b * p.dk_bs + (long long)ki * p.dk_ts + (long long)hkv * D;
-#pragma unroll
-    for (int which = 0; which < 2; ++which) {
-      __nv_bfloat16* orow = which ? krow : vrow;
-      const uint32_t tb = which ? T_DK : T_DV;
-#pragma unroll
-      for (int c = 0; c < D / 32; ++c) {
-        uint32_t acc[32];
-        if (n > 0) {
-          tmem_ld_32x32b_x32(tb + lane_base + c * 32, acc);
-          tmem_ld_wait();
-        } else {
-#pragma unroll
-          for (int i2 = 0; i2 < 32; ++i2) acc[i2] = 0u;
-        }
-        if (ki < p.S) {
-#pragma unroll
-          for (int q4 = 0; q4 < 4; ++q4) {
-            uint4 u;
-            u.x = pack_bf16x2(__uint_as_float(acc[q4 * 8 + 0]), __uint_as_float(acc[q4 * 8 + 1]));
-            u.y = pack_bf16x2(__uint_as_float(acc[q4 * 8 + 2]), __uint_as_float(acc[q4 * 8 + 3]));
-            u.z = pack_bf16x2(__uint_as_float(acc[q4 * 8 + 4]), __uint_as_float(acc[q4 * 8 + 5]));
-            u.w = pack_bf16x2(__uint_as_float(acc[q4 * 8 + 6]), __uint_as_float(acc[q4 * 8 + 7]));
-            *reinterpret_cast<uint4*>(orow + c * 32 + q4 * 8) = u;
-          }
-        }
+    if (n > 0) {
+      mbar_wait(&bars->acc_full, 0);
+      tc_fence_after();
+      store_acc_half<D>(T_DV + lane_base, vrow, cg, ki < p.S, 1.f);
+      store_acc_half<D>(T_DK + lane_base, krow, cg, ki < p.S, p.scale);
+    } else if (ki < p.S) {
+      for (int c = cg * (D / 2); c < (cg + 1) * (D / 2); c += 8) {
+        *reinterpret_cast<uint4*>(vrow + c) = make_uint4(0, 0, 0, 0);
+        *reinterpret_cast<uint4*>(krow + c) = make_uint4(0, 0, 0, 0);
       }
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem, 512); }
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(0, 512); }
 }
 
 int make_map(CUtensorMap* m, const void* ptr, int B, int S, int heads, int D, long long ts,
@@ -886,7 +943,8 @@ extern "C" int b2f_attn_fwd(const void* q, const void* k, const void* v, void* o
   return 0;
 }
 
-// delta: fp32 scratch [B, H, S] supplied by the caller.
+// delta: fp32 scratch of 2 * B * H * S_pad floats supplied by the caller (S_pad = S rounded up to
+// 128); the pre-pass fills it with lse * log2(e) and rowsum(O * dO) for the two main kernels.
 extern "C" int b2f_attn_bwd(const void* q, const void* k, const void* v, const void* o,
                             const void* d_o, const float* lse, float* delta, void* dq, void* dk,
                             void* dv, int B, int S, int H, int HKV, int D, long long q_ts,
@@ -897,6 +955,7 @@ extern "C" int b2f_attn_bwd(const void* q, const void* k, const void* v, const v
                             int causal, const int* kv_lens, void* stream) {
   if (int rc = check_common(B, S, H, HKV, D)) return rc;
   B2F_REQUIRE(delta != nullptr && lse != nullptr, "attention bwd: lse and delta scratch required");
+  B2F_REQUIRE((reinterpret_cast<uintptr_t>(delta) & 15) == 0, "attention bwd: scratch must be 16-byte aligned");
   CUtensorMap mq, mk, mv, mdo;
   if (int rc = make_map(&mq, q, B, S, H, D, q_ts, q_bs)) return rc;
   if (int rc = make_map(&mk, k, B, S, HKV, D, k_ts, k_bs)) return rc;
@@ -911,24 +970,27 @@ extern "C" int b2f_attn_bwd(const void* q, const void* k, const void* v, const v
   p.dq_ts = dq_ts; p.dq_bs = dq_bs; p.dk_ts = dk_ts; p.dk_bs = dk_bs; p.dv_ts = dv_ts; p.dv_bs = dv_bs;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int nq = (S + TQ - 1) / TQ;
-  const long long delta_threads = (long long)B * S * H * (D / 8);
+  const int S_pad = nq * TQ;
+  const long long delta_threads = (long long)B * S_pad * H * (D / 8);
   const unsigned dgrid = (unsigned)((delta_threads + 255) / 256);
   if (D == 128) {
     attn_delta_kernel<128><<<dgrid, 256, 0, st>>>((const __nv_bfloat16*)o, o_ts, o_bs,
-                                                  (const __nv_bfloat16*)d_o, do_ts, do_bs, delta, B, H, S);
+                                                  (const __nv_bfloat16*)d_o, do_ts, do_bs, lse, delta,
+                                                  B, H, S, S_pad);
     const int smem = 6 * Cfg<128>::TILE_B + 1024 + sizeof(BwdBars);
     if (int rc = set_smem(attn_bwd_dq_kernel<128>, smem)) return rc;
     if (int rc = set_smem(attn_bwd_dkv_kernel<128>, smem)) return rc;
-    attn_bwd_dq_kernel<128><<<dim3(H * B, nq, 1), ATT_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
-    attn_bwd_dkv_kernel<128><<<dim3(HKV * B, nq, 1), ATT_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+    attn_bwd_dq_kernel<128><<<dim3(H * B, nq, 1), BWD_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+    attn_bwd_dkv_kernel<128><<<dim3(HKV * B, nq, 1), BWD_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
   } else {
     attn_delta_kernel<64><<<dgrid, 256, 0, st>>>((const __nv_bfloat16*)o, o_ts, o_bs,
-                                                 (const __nv_bfloat16*)d_o, do_ts, do_bs, delta, B, H, S);
+                                                 (const __nv_bfloat16*)d_o, do_ts, do_bs, lse, delta,
+                                                 B, H, S, S_pad);
     const int smem = 6 * Cfg<64>::TILE_B + 1024 + sizeof(BwdBars);
     if (int rc = set_smem(attn_bwd_dq_kernel<64>, smem)) return rc;
     if (int rc = set_smem(attn_bwd_dkv_kernel<64>, smem)) return rc;
-    attn_bwd_dq_kernel<64><<<dim3(H * B, nq, 1), ATT_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
-    attn_bwd_dkv_kernel<64><<<dim3(HKV * B, nq, 1), ATT_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+    attn_bwd_dq_kernel<64><<<dim3(H * B, nq, 1), BWD_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+    attn_bwd_dkv_kernel<64><<<dim3(HKV * B, nq, 1), BWD_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
   }
   B2F_CHECK_CUDA(cudaGetLastError());
   return 0;

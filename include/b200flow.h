@@ -117,7 +117,8 @@ int b2f_cast_f32_bf16(const float* x, void* y, long long n, float scale, void* s
 
 /* ---- K7: flash attention fwd/bwd on tcgen05 (flash-attn v2 / Megatron fused softmax).
  * q/k/v/o: [B, S, heads, D] views, heads packed, D in {64,128}; *_ts token stride,
- * *_bs batch stride (elements).  lse: fp32 [B, H, S].  delta: fp32 scratch [B, H, S]. */
+ * *_bs batch stride (elements).  lse: fp32 [B, H, S].  delta: fp32 scratch of
+ * 2 * B * H * S_pad floats (S_pad = S rounded up to 128), 16-byte aligned. */
 int b2f_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int S,
                  int H, int HKV, int D, long long q_ts, long long q_bs, long long k_ts,
                  long long k_bs, long long v_ts, long long v_bs, long long o_ts, long long o_bs,
