@@ -358,20 +358,24 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
         }
       }
       DBG_T(ts2);
-      float sum0 = 0.f, sum1 = 0.f;
+      const uint64_t sc2 = f2pack(p.scale_log2, p.scale_log2), nm2 = f2pack(-m, -m);
+      uint64_t sum2 = f2pack(0.f, 0.f);
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
-          const float p0 = ex2(fmaf(__uint_as_float(s[c * 32 + 2 * i]), p.scale_log2, -m));
-          const float p1 = ex2(fmaf(__uint_as_float(s[c * 32 + 2 * i + 1]), p.scale_log2, -m));
-          sum0 += p0;
-          sum1 += p1;
+          const uint64_t t = fma2(f2pack(__uint_as_float(s[c * 32 + 2 * i]), __uint_as_float(s[c * 32 + 2 * i + 1])), sc2, nm2);
+          float t0, t1;
+          f2unpack(t, t0, t1);
+          const float p0 = ex2(t0), p1 = ex2(t1);
+          sum2 = add2(sum2, f2pack(p0, p1));
           pk[i] = pack_bf16x2(p0, p1);
         }
         tmem_st_32x32b_x16(T_S + c * 16, pk);
       }
+      float sum0, sum1;
+      f2unpack(sum2, sum0, sum1);
       l += sum0 + sum1;
       tmem_st_wait();
       tc_fence_before();
@@ -436,9 +440,10 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
 }
 
 // ============================================================== backward
-// Pre-pass over every (padded) query row: dlt = rowsum(O * dO) and lse2 = lse * log2(e), written to
-// the fp32 scratch [2][B*H][S_pad] (S_pad = S rounded up to 128).  Padding rows get lse2 = +inf and
-// dlt = 0, so the main kernels can bulk-copy whole 128-row slices and see P = 0 there.
+// Pre-pass over every (padded) query row: nlse2 = -lse * log2(e) and ndlt = -rowsum(O * dO) (negated
+// so the main kernels feed them straight into packed FMA / ADD), written to the fp32 scratch
+// [2][B*H][S_pad] (S_pad = S rounded up to 128).  Padding rows get nlse2 = -inf and ndlt = 0, so the
+// main kernels can bulk-copy whole 128-row slices and see P = 0 there.
 template <int D>
 __global__ void __launch_bounds__(256)
 attn_delta_kernel(const __nv_bfloat16* __restrict__ O, long long o_ts, long long o_bs,
@@ -468,8 +473,8 @@ attn_delta_kernel(const __nv_bfloat16* __restrict__ O, long long o_ts, long long
   for (int o = TPR / 2; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
   if (row < total && part == 0) {
     const long long idx = ((long long)b * H + h) * S_pad + s;
-    scr[idx] = live ? lse[((long long)b * H + h) * S + s] * LOG2E : INFINITY;
-    scr[(long long)B * H * S_pad + idx] = acc;
+    scr[idx] = live ? -lse[((long long)b * H + h) * S + s] * LOG2E : -INFINITY;
+    scr[(long long)B * H * S_pad + idx] = -acc;
   }
 }
 
@@ -640,8 +645,9 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant
     const uint32_t lane_base = static_cast<uint32_t>(qw * 32) << 16;
     const int S_pad = nq * TQ;
     const long long sidx = ((long long)b * p.H + h) * S_pad + qi;
-    const float lse2 = p.delta[sidx];
-    const float dlt = p.delta[(long long)p.B * p.H * S_pad + sidx];
+    const float nlse2 = p.delta[sidx];
+    const float ndlt = p.delta[(long long)p.B * p.H * S_pad + sidx];
+    const uint64_t sc2 = f2pack(p.scale_log2, p.scale_log2), nl2 = f2pack(nlse2, nlse2), nd2 = f2pack(ndlt, ndlt);
     for (int j = 0; j < n; ++j) {
       const int kv0 = j * TQ;
       DBG_T(tq0);
@@ -658,20 +664,34 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant
       tc_fence_after();
       DBG_T(tq2);
       const bool need_mask = (p.causal && kv0 + TQ - 1 > q0) || (kv0 + TQ > kv_len);
-      int lim = kv_len;
-      if (p.causal && qi + 1 < lim) lim = qi + 1;
-      lim -= kv0 + cg * 64;  // first masked column among this thread's 64
       uint32_t pk[32];
+      if (!need_mask) {
 #pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        float p0 = ex2(fmaf(__uint_as_float(sa[2 * i]), p.scale_log2, -lse2));
-        float p1 = ex2(fmaf(__uint_as_float(sa[2 * i + 1]), p.scale_log2, -lse2));
-        if (need_mask) {
-          if (2 * i >= lim) p0 = 0.f;
-          if (2 * i + 1 >= lim) p1 = 0.f;
+        for (int i = 0; i < 32; ++i) {
+          const uint64_t t = fma2(f2pack(__uint_as_float(sa[2 * i]), __uint_as_float(sa[2 * i + 1])), sc2, nl2);
+          float t0, t1;
+          f2unpack(t, t0, t1);
+          const uint64_t d = add2(f2pack(__uint_as_float(da[2 * i]), __uint_as_float(da[2 * i + 1])), nd2);
+          float d0, d1;
+          f2unpack(mul2(f2pack(ex2(t0), ex2(t1)), d), d0, d1);
+          pk[i] = pack_bf16x2(d0, d1);
         }
-        pk[i] = pack_bf16x2(p0 * (__uint_as_float(da[2 * i]) - dlt),
-                            p1 * (__uint_as_float(da[2 * i + 1]) - dlt));
+      } else {
+        int lim = kv_len;
+        if (p.causal && qi + 1 < lim) lim = qi + 1;
+        lim -= kv0 + cg * 64;  // first masked column among this thread's 64
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const uint64_t t = fma2(f2pack(__uint_as_float(sa[2 * i]), __uint_as_float(sa[2 * i + 1])), sc2, nl2);
+          float t0, t1;
+          f2unpack(t, t0, t1);
+          const float p0 = 2 * i < lim ? ex2(t0) : 0.f;
+          const float p1 = 2 * i + 1 < lim ? ex2(t1) : 0.f;
+          const uint64_t d = add2(f2pack(__uint_as_float(da[2 * i]), __uint_as_float(da[2 * i + 1])), nd2);
+          float d0, d1;
+          f2unpack(mul2(f2pack(p0, p1), d), d0, d1);
+          pk[i] = pack_bf16x2(d0, d1);
+        }
       }
       store_cols32(T_DP + lane_base + cg * 32, pk);
       tmem_st_wait();
@@ -805,6 +825,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constan
     const int ki = kv0 + r;
     const uint32_t lane_base = static_cast<uint32_t>(qw * 32) << 16;
     const bool row_dead = ki >= kv_len;
+    const uint64_t sc2 = f2pack(p.scale_log2, p.scale_log2);
     for (int it = 0; it < n; ++it) {
       const int st = it & 1;
       const int i = i0 + it % per_head;
@@ -825,27 +846,45 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constan
       const bool need_mask = (p.causal && q0 < kv0 + TQ - 1) || (kv0 + TQ > kv_len);
       // causal: query column c is visible to key row ki iff q0 + c >= ki
       const int first_ok = row_dead ? 128 : (p.causal ? ki - q0 - cg * 64 : 0);
-      const float4* l4 = reinterpret_cast<const float4*>(&bars->lse2[st][cg * 64]);
-      const float4* d4 = reinterpret_cast<const float4*>(&bars->dlt[st][cg * 64]);
+      const uint32_t l_addr = smem_u32(&bars->lse2[st][cg * 64]), d_addr = smem_u32(&bars->dlt[st][cg * 64]);
       uint32_t pp[32], pd[32];
+      if (!need_mask) {
 #pragma unroll
-      for (int i4 = 0; i4 < 16; ++i4) {
-        const float4 lv = l4[i4], dv = d4[i4];
-        const float ls[4] = {lv.x, lv.y, lv.z, lv.w};
-        const float ds_[4] = {dv.x, dv.y, dv.z, dv.w};
-        float pv[4], dsv[4];
+        for (int i4 = 0; i4 < 16; ++i4) {
+          const ulonglong2 nl = lds_v2_u64(l_addr + i4 * 16), nd = lds_v2_u64(d_addr + i4 * 16);
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const int c = i4 * 4 + e;
-          float pe = ex2(fmaf(__uint_as_float(sa[c]), p.scale_log2, -ls[e]));
-          if (need_mask && c < first_ok) pe = 0.f;
-          pv[e] = pe;
-          dsv[e] = pe * (__uint_as_float(da[c]) - ds_[e]);
+          for (int e = 0; e < 2; ++e) {
+            const int c = i4 * 4 + e * 2;
+            const uint64_t t = fma2(f2pack(__uint_as_float(sa[c]), __uint_as_float(sa[c + 1])), sc2, e ? nl.y : nl.x);
+            float t0, t1;
+            f2unpack(t, t0, t1);
+            const float p0 = ex2(t0), p1 = ex2(t1);
+            const uint64_t d = add2(f2pack(__uint_as_float(da[c]), __uint_as_float(da[c + 1])), e ? nd.y : nd.x);
+            float d0, d1;
+            f2unpack(mul2(f2pack(p0, p1), d), d0, d1);
+            pp[i4 * 2 + e] = pack_bf16x2(p0, p1);
+            pd[i4 * 2 + e] = pack_bf16x2(d0, d1);
+          }
         }
-        pp[i4 * 2] = pack_bf16x2(pv[0], pv[1]);
-        pp[i4 * 2 + 1] = pack_bf16x2(pv[2], pv[3]);
-        pd[i4 * 2] = pack_bf16x2(dsv[0], dsv[1]);
-        pd[i4 * 2 + 1] = pack_bf16x2(dsv[2], dsv[3]);
+      } else {
+#pragma unroll
+        for (int i4 = 0; i4 < 16; ++i4) {
+          const ulonglong2 nl = lds_v2_u64(l_addr + i4 * 16), nd = lds_v2_u64(d_addr + i4 * 16);
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const int c = i4 * 4 + e * 2;
+            const uint64_t t = fma2(f2pack(__uint_as_float(sa[c]), __uint_as_float(sa[c + 1])), sc2, e ? nl.y : nl.x);
+            float t0, t1;
+            f2unpack(t, t0, t1);
+            const float p0 = c >= first_ok ? ex2(t0) : 0.f;
+            const float p1 = c + 1 >= first_ok ? ex2(t1) : 0.f;
+            const uint64_t d = add2(f2pack(__uint_as_float(da[c]), __uint_as_float(da[c + 1])), e ? nd.y : nd.x);
+            float d0, d1;
+            f2unpack(mul2(f2pack(p0, p1), d), d0, d1);
+            pp[i4 * 2 + e] = pack_bf16x2(p0, p1);
+            pd[i4 * 2 + e] = pack_bf16x2(d0, d1);
+          }
+        }
       }
       store_cols32(T_S + lane_base + cg * 32, pp);
       store_cols32(T_DP + lane_base + cg * 32, pd);
