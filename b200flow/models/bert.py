@@ -90,7 +90,7 @@ class BertLayer(nn.Module):
         if p > 0:
             a = E.bias_dropout_add(a, None, None, p, seed)
         x = _post_ln(a, x, self.ln1_w, self.ln1_b, cfg.eps)
-        f = G.linear(G.linear_gelu(x, self.w1, self.b1), self.w2, self.b2)
+        f = G.mlp_gelu(x, self.w1, self.b1, self.w2, self.b2)
         if p > 0:
             f = E.bias_dropout_add(f, None, None, p, seed + 1)
         return _post_ln(f, x, self.ln2_w, self.ln2_b, cfg.eps)
@@ -162,16 +162,35 @@ class BertForPreTraining(nn.Module):
         self.bert.word.ddp_uses = 2     # embedding lookup + tied decoder
         self.pool_w, self.pool_b = _p(H, H, std=cfg.init_std, **kw), _p(H, **kw)
         self.nsp_w, self.nsp_b = _p(2, H, std=cfg.init_std, **kw), _p(2, **kw)
+        self.gather_masked = True
 
     def forward(self, input_ids, token_type_ids=None, attention_mask=None, labels=None,
-                next_sentence_label=None):
+                next_sentence_label=None, masked_lm_positions=None):
+        """`masked_lm_positions` (optional, int64 [n_masked]): flat indices into [batch*seq] of the
+        positions whose label is not -100, prepared by the collator.  The MLM transform, the tied
+        decoder GEMM and the loss then run on those rows only (same loss; the other rows have zero
+        gradient anyway).  Without it the positions are found on the device (one host sync)."""
         cfg = self.cfg
         x = self.bert(input_ids, token_type_ids, attention_mask)
         b, s, H = x.shape
-        h = G.linear_gelu(x, self.tr_w, self.tr_b)
+        flat_labels = labels.reshape(-1)
+        if masked_lm_positions is None and x.is_cuda and self.gather_masked:
+            masked_lm_positions = (flat_labels != -100).nonzero().squeeze(-1)
+        xm = x.reshape(b * s, H)
+        if masked_lm_positions is not None:
+            n_m = masked_lm_positions.numel()
+            pad = (-n_m) % 8          # keep GEMM rows a multiple of 8; padded rows carry label -100
+            if pad:
+                masked_lm_positions = torch.cat([masked_lm_positions, masked_lm_positions.new_zeros(pad)])
+            xm = xm.index_select(0, masked_lm_positions)
+            flat_labels = flat_labels.index_select(0, masked_lm_positions)
+            if pad:
+                flat_labels = flat_labels.clone()
+                flat_labels[n_m:] = -100
+        h = G.linear_gelu(xm, self.tr_w, self.tr_b)
         h = N.norm(h, self.tr_ln_w, self.tr_ln_b, eps=cfg.eps, rms=False)
-        logits = G.linear(h.reshape(b * s, H), self.bert.word, self.dec_b)   # tied decoder
-        mlm = E.cross_entropy(logits, labels.reshape(-1), ignore_index=-100)
+        logits = G.linear(h, self.bert.word, self.dec_b)   # tied decoder
+        mlm = E.cross_entropy(logits, flat_labels, ignore_index=-100)
         pooled = torch.tanh(torch.nn.functional.linear(x[:, 0], self.pool_w, self.pool_b))
         nsp_logits = torch.nn.functional.linear(pooled, self.nsp_w, self.nsp_b).float()
         loss = mlm

@@ -16,7 +16,7 @@ from ._lib import c_float, c_int, c_ll, ptr, stream_ptr
 
 import os
 
-EPI_GELU, EPI_OUT_F32, EPI_ACCUM, EPI_RELU, EPI_BIAS_ROW = 1, 2, 4, 8, 16
+EPI_GELU, EPI_OUT_F32, EPI_ACCUM, EPI_RELU, EPI_BIAS_ROW, EPI_DGELU = 1, 2, 4, 8, 16, 32
 # "2cta": CTA-pair kernel (cta_group::2) for tiles that fill it; "1cta": always the 128x256 kernel
 GEMM_IMPL = os.environ.get("B2F_GEMM", "2cta")
 
@@ -36,7 +36,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_maj
          out: torch.Tensor | None = None, out_dtype: torch.dtype = torch.bfloat16,
          bias: torch.Tensor | None = None, residual: torch.Tensor | None = None,
          aux: torch.Tensor | None = None, gelu: bool = False, relu: bool = False,
-         accumulate: bool = False, alpha: float = 1.0) -> torch.Tensor:
+         accumulate: bool = False, alpha: float = 1.0, dgelu: bool = False) -> torch.Tensor:
     """C = epilogue(alpha * op(A) @ op(B)ᵀ-style product), see include/b200flow.h.
 
     a: [.., M, K] (or [.., K, M] if a_mn_major);  b: [.., N, K] (or [.., K, N] if b_mn_major).
@@ -69,6 +69,9 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_maj
         flags |= EPI_GELU
     if relu:
         flags |= EPI_RELU
+    if dgelu:   # `residual` is a saved pre-activation z: C = (A B) * gelu'(z)
+        assert residual is not None
+        flags |= EPI_DGELU
     sa = a.stride(0) if a.dim() == 3 else 0
     sb = b.stride(0) if b.dim() == 3 else 0
     sc = out.stride(0) if out.dim() == 3 else 0
@@ -152,6 +155,44 @@ class _LinearGelu(torch.autograd.Function):
         dx = gemm(dpre, weight, b_mn_major=True).reshape(ctx.x_shape)
         dw = _wgrad(x2, dpre, weight)
         return dx, dw, dpre.sum(0)
+
+
+class _MlpGelu(torch.autograd.Function):
+    """y = gelu(x W1ᵀ + b1) W2ᵀ + b2 as one autograd node, so the backward can fold gelu' into the
+    epilogue of the dgrad GEMM through W2 (no separate activation-gradient pass over [tokens, ffn])."""
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, w2, b2):
+        x2 = x.reshape(-1, x.shape[-1])
+        pre = torch.empty((x2.shape[0], w1.shape[0]), dtype=torch.bfloat16, device=x.device)
+        h = gemm(x2, w1, bias=b1, aux=pre, gelu=True)
+        y = gemm(h, w2, bias=b2)
+        ctx.save_for_backward(x2, w1, w2, pre, h)
+        ctx.x_shape = x.shape
+        ctx.has_b = (b1 is not None, b2 is not None)
+        return y.reshape(*x.shape[:-1], w2.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w1, w2, pre, h = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1])
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dpre = gemm(dy2, w2, b_mn_major=True, residual=pre, dgelu=True)
+        dw2 = _wgrad(h, dy2, w2)
+        db2 = dy2.sum(0) if ctx.has_b[1] else None
+        dx = gemm(dpre, w1, b_mn_major=True).reshape(ctx.x_shape) if ctx.needs_input_grad[0] else None
+        dw1 = _wgrad(x2, dpre, w1)
+        db1 = dpre.sum(0) if ctx.has_b[0] else None
+        return dx, dw1, db1, dw2, db2
+
+
+def mlp_gelu(x, w1, b1, w2, b2):
+    """Transformer FFN with GELU: two tcgen05 GEMMs forward, four backward, no elementwise pass."""
+    if not x.is_cuda:
+        from . import ref
+        return ref.linear(ref.linear_gelu(x, w1, b1), w2, b2, None)
+    return _MlpGelu.apply(x, w1, b1, w2, b2)
 
 
 def linear_gelu(x, weight, bias):

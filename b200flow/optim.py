@@ -72,12 +72,19 @@ class AdamW(torch.optim.Optimizer):
                     p.data.copy_(st["master"].to(p.dtype))
 
     def zero_grad(self, set_to_none: bool = True):
+        owners = {}
         for group in self.param_groups:
             for p in group["params"]:
                 p.grad = None
+                owner = getattr(p, "_flat_owner", None)
+                if owner is not None:
+                    owners[id(owner)] = owner      # flat storage: one fill for every gradient
+                    continue
                 mg = getattr(p, "main_grad", None)
                 if mg is not None:
                     mg.zero_()
+        for owner in owners.values():
+            owner.grads.zero_()
 
 
 def get_linear_schedule_with_warmup(optimizer, num_warmup_steps: int, num_training_steps: int):

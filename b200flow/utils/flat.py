@@ -64,6 +64,7 @@ class FlatParams:
             view.copy_(p.data)
             p.data = view
             p.main_grad = self.grads[slot.offset: slot.offset + slot.numel].view(slot.shape)
+            p._flat_owner = self   # lets optimizers clear all gradients with one fill
 
     def named_parameters(self):
         for slot in self.slots:

@@ -22,7 +22,9 @@ def _batches(cfg, n, batch, seq, gen):
         ids[m] = 103
         out.append({"input_ids": ids, "token_type_ids": torch.zeros_like(ids),
                     "attention_mask": torch.ones_like(ids), "labels": labels,
-                    "next_sentence_label": torch.randint(0, 2, (batch,), generator=gen)})
+                    "next_sentence_label": torch.randint(0, 2, (batch,), generator=gen),
+                    # collator-side list of the masked positions (NVIDIA-style masked_lm_positions)
+                    "masked_lm_positions": (labels.reshape(-1) != -100).nonzero().squeeze(-1)})
     return out
 
 
@@ -35,7 +37,7 @@ def run_bert_bench(args, rank, world, dev, ClockSampler):
     name = "bert-large" if args.workload in ("bert", "bert-large") else args.workload
     cfg = bert_config(name, dropout=0.1)
     seq = min(args.seq, cfg.max_pos)
-    batch = args.micro_batch if args.micro_batch > 1 else 16
+    batch = args.micro_batch if args.micro_batch > 1 else 64
     acc = Accelerator(mixed_precision="bf16", fused_collectives=not args.no_fused)
     torch.manual_seed(1234)
     model = BertForPreTraining(cfg, dtype=torch.bfloat16, device=dev)

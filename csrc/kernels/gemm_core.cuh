@@ -42,6 +42,7 @@ enum EpiFlags : int {
   EPI_ACCUM = 4,       // C += v (fp32 C only; wgrad main_grad accumulate)
   EPI_RELU = 8,        // v = max(v, 0)
   EPI_BIAS_ROW = 16,   // bias indexed by row (m) instead of column (n)
+  EPI_DGELU = 32,      // `residual` holds a saved pre-activation z: v *= gelu'(z) instead of v += z
 };
 
 struct Params {
@@ -77,6 +78,14 @@ __device__ __forceinline__ float gelu_tanh(float x) {
   float t;
   asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
   return 0.5f * x * (1.0f + t);
+}
+
+__device__ __forceinline__ float gelu_tanh_grad(float x) {
+  const float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
+  const float du = 0.7978845608028654f * (1.f + 3.f * 0.044715f * x * x);
+  return 0.5f * (1.f + t) + 0.5f * x * (1.f - t * t) * du;
 }
 
 // Default policy: plain GEMM, row-major tile order (m fastest), no cross-GPU hooks.
@@ -164,18 +173,25 @@ __device__ __forceinline__ void epilogue_chunk(const Params& p, int b, int m, in
   if (p.residual) {
     const __nv_bfloat16* rp =
         p.residual + (long long)b * p.strideR + (long long)m * p.ldr + n0;
+    float r[32];
     if (full && ((p.ldr & 7) == 0)) {
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         uint4 u = *reinterpret_cast<const uint4*>(rp + q * 8);
         float2 f0 = unpack_bf16x2(u.x), f1 = unpack_bf16x2(u.y), f2 = unpack_bf16x2(u.z),
                f3 = unpack_bf16x2(u.w);
-        v[q * 8 + 0] += f0.x; v[q * 8 + 1] += f0.y; v[q * 8 + 2] += f1.x; v[q * 8 + 3] += f1.y;
-        v[q * 8 + 4] += f2.x; v[q * 8 + 5] += f2.y; v[q * 8 + 6] += f3.x; v[q * 8 + 7] += f3.y;
+        r[q * 8 + 0] = f0.x; r[q * 8 + 1] = f0.y; r[q * 8 + 2] = f1.x; r[q * 8 + 3] = f1.y;
+        r[q * 8 + 4] = f2.x; r[q * 8 + 5] = f2.y; r[q * 8 + 6] = f3.x; r[q * 8 + 7] = f3.y;
       }
     } else {
-      for (int i = 0; i < 32; ++i)
-        if (n0 + i < p.N) v[i] += __bfloat162float(rp[i]);
+      for (int i = 0; i < 32; ++i) r[i] = (n0 + i < p.N) ? __bfloat162float(rp[i]) : 0.f;
+    }
+    if (flags & EPI_DGELU) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] *= gelu_tanh_grad(r[i]);
+    } else {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] += r[i];
     }
   }
   if (flags & EPI_OUT_F32) {

@@ -108,6 +108,28 @@ def group_gemm_epi():
     c32b = torch.empty(M, Nn, device=DEV, dtype=torch.float32)
     G.gemm(a, b, out=c32b, alpha=0.5)
     report("epi_f32_alpha", c32b, 0.5 * ref, 2e-2)
+    # dgelu epilogue: C = (A B^T) * gelu'(z), z passed through the residual pointer
+    z = torch.randn(M, Nn, device=DEV, dtype=torch.bfloat16)
+    zf = z.float().requires_grad_()
+    torch.nn.functional.gelu(zf, approximate="tanh").sum().backward()
+    report("epi_dgelu", G.gemm(a, b, residual=z, dgelu=True), ref * zf.grad, 2e-2)
+    # fused FFN (two GEMMs forward, four backward) against fp32 autograd
+    H_, F_ = 256, 1024
+    x = torch.randn(384, H_, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    w1 = (torch.randn(F_, H_, device=DEV) * 0.05).to(torch.bfloat16).requires_grad_()
+    b1 = (torch.randn(F_, device=DEV) * 0.1).to(torch.bfloat16).requires_grad_()
+    w2 = (torch.randn(H_, F_, device=DEV) * 0.05).to(torch.bfloat16).requires_grad_()
+    b2 = (torch.randn(H_, device=DEV) * 0.1).to(torch.bfloat16).requires_grad_()
+    y = G.mlp_gelu(x, w1, b1, w2, b2)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    fx, fw1, fb1, fw2, fb2 = (t.detach().float().requires_grad_() for t in (x, w1, b1, w2, b2))
+    yr = torch.nn.functional.gelu(fx @ fw1.t() + fb1, approximate="tanh") @ fw2.t() + fb2
+    yr.backward(dy.float())
+    report("mlp_fwd", y, yr, 2e-2)
+    for nm, got, want in (("dx", x.grad, fx.grad), ("dw1", w1.grad, fw1.grad), ("db1", b1.grad, fb1.grad),
+                          ("dw2", w2.grad, fw2.grad), ("db2", b2.grad, fb2.grad)):
+        report(f"mlp_{nm}", got.reshape(-1, got.shape[-1]), want.reshape(-1, want.shape[-1]), 3e-2)
     # batched
     ab = torch.randn(3, 256, 128, device=DEV, dtype=torch.bfloat16)
     bb = torch.randn(3, 512, 128, device=DEV, dtype=torch.bfloat16)
