@@ -206,24 +206,259 @@ norm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __res
 }
 
 // Reduce the per-CTA partial rows: out[h] (+)= sum_p partial[p][which][h].
-__global__ void norm_bwd_reduce_kernel(const float* __restrict__ partial, int nparts, int H,
-                                       float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                       int accumulate) {
-  const int h = blockIdx.x * blockDim.x + threadIdx.x;
-  if (h >= H) return;
-  float sg = 0.f, sb = 0.f;
-  for (int p = 0; p < nparts; ++p) {
-    sg += partial[(size_t)p * 2 * H + h];
-    if (dbeta) sb += partial[(size_t)p * 2 * H + H + h];
+// Block = 32 columns x 8 row slices (coalesced 128 B reads, 8 independent partial sums per column).
+__global__ void __launch_bounds__(256)
+norm_bwd_reduce_kernel(const float* __restrict__ partial, int nparts, int H,
+                       float* __restrict__ dgamma, float* __restrict__ dbeta, int accumulate) {
+  __shared__ float sg[8][33], sb[8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int h = blockIdx.x * 32 + tx;
+  float ag = 0.f, ab = 0.f;
+  if (h < H) {
+    for (int p = ty; p < nparts; p += 8) {
+      ag += partial[(size_t)p * 2 * H + h];
+      if (dbeta) ab += partial[(size_t)p * 2 * H + H + h];
+    }
   }
-  dgamma[h] = accumulate ? dgamma[h] + sg : sg;
-  if (dbeta) dbeta[h] = accumulate ? dbeta[h] + sb : sb;
+  sg[ty][tx] = ag;
+  sb[ty][tx] = ab;
+  __syncthreads();
+  if (ty == 0 && h < H) {
+    float g = 0.f, b = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { g += sg[i][tx]; b += sb[i][tx]; }
+    dgamma[h] = accumulate ? dgamma[h] + g : g;
+    if (dbeta) dbeta[h] = accumulate ? dbeta[h] + b : b;
+  }
+}
+
+// ---- group-per-row kernels (H <= 8192).  A row is owned by G threads (G = 32 for H <= 1024, so a
+// warp per row and shuffle-only reductions; up to 256 for H = 8192), every thread holds at most
+// four 16-byte vectors, and a 256-thread CTA works on 256/G rows at once.  Compared with one CTA
+// per row this keeps 4-8x more rows in flight per SM, which is what HBM needs at small H.
+constexpr int GVPT = 4;
+
+template <int G>
+__device__ __forceinline__ void group_sum2(float& a, float& b, float (*red)[8][2], int grp, int t) {
+  a = warp_sum(a);
+  b = warp_sum(b);
+  if (G > 32) {
+    const int w = t >> 5;
+    __syncthreads();  // previous use of `red` is over
+    if ((t & 31) == 0) { red[grp][w][0] = a; red[grp][w][1] = b; }
+    __syncthreads();
+    a = 0.f; b = 0.f;
+#pragma unroll
+    for (int i = 0; i < G / 32; ++i) { a += red[grp][i][0]; b += red[grp][i][1]; }
+  }
+}
+
+template <int G, bool RMS>
+__global__ void __launch_bounds__(NORM_THREADS)
+norm_fwd_g_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ residual,
+                  const __nv_bfloat16* __restrict__ gamma, const __nv_bfloat16* __restrict__ beta,
+                  __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ h_out,
+                  float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows, int H,
+                  float eps) {
+  constexpr int RPC = NORM_THREADS / G;
+  __shared__ float red[RPC][8][2];
+  const int grp = threadIdx.x / G, t = threadIdx.x % G;
+  const int nvec = H >> 3;
+  const float inv_h = 1.f / H;
+  for (int base = blockIdx.x * RPC; base < rows; base += gridDim.x * RPC) {
+    const int row = base + grp;
+    const bool active = row < rows;
+    const uint4* xr = reinterpret_cast<const uint4*>(x + (size_t)row * H);
+    const uint4* rr = reinterpret_cast<const uint4*>(residual + (size_t)row * H);
+    uint4 raw[GVPT];
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int i = 0; i < GVPT; ++i) {
+      const int c = t + i * G;
+      raw[i] = make_uint4(0, 0, 0, 0);
+      if (active && c < nvec) {
+        raw[i] = ld_nc_v4(xr + c);
+        if (residual) {
+          float v[8], r[8];
+          unpack8(raw[i], v);
+          unpack8(ld_nc_v4(rr + c), r);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] += r[j];
+          raw[i] = pack8(v);  // y is computed from exactly the bf16 sum that is stored
+          if (h_out) reinterpret_cast<uint4*>(h_out + (size_t)row * H)[c] = raw[i];
+        }
+        float v[8];
+        unpack8(raw[i], v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { s0 += v[j]; s1 += v[j] * v[j]; }
+      }
+    }
+    group_sum2<G>(s0, s1, red, grp, t);
+    const float mean = RMS ? 0.f : s0 * inv_h;
+    const float var = RMS ? s1 * inv_h : fmaxf(s1 * inv_h - mean * mean, 0.f);
+    const float rstd = rsqrtf(var + eps);
+    if (active && t == 0) {
+      if (mean_out) mean_out[row] = mean;
+      rstd_out[row] = rstd;
+    }
+    uint4* yr = reinterpret_cast<uint4*>(y + (size_t)row * H);
+#pragma unroll
+    for (int i = 0; i < GVPT; ++i) {
+      const int c = t + i * G;
+      if (active && c < nvec) {
+        float v[8], g[8], o[8];
+        unpack8(raw[i], v);
+        unpack8(__ldg(reinterpret_cast<const uint4*>(gamma) + c), g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = (v[j] - mean) * rstd * g[j];
+        if (!RMS && beta) {
+          float bb[8];
+          unpack8(__ldg(reinterpret_cast<const uint4*>(beta) + c), bb);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] += bb[j];
+        }
+        yr[c] = pack8(o);
+      }
+    }
+  }
+}
+
+template <int G, bool RMS>
+__global__ void __launch_bounds__(NORM_THREADS, 2)
+norm_bwd_g_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                  const __nv_bfloat16* __restrict__ gamma, const float* __restrict__ mean_in,
+                  const float* __restrict__ rstd_in, const __nv_bfloat16* __restrict__ dres_in,
+                  __nv_bfloat16* __restrict__ dx, float* __restrict__ partial /*[grid,2,H]*/,
+                  int rows, int H) {
+  constexpr int RPC = NORM_THREADS / G;
+  __shared__ float red[RPC][8][2];
+  __shared__ float part[8192];  // cross-group reduction of the dgamma / dbeta partials
+  const int grp = threadIdx.x / G, t = threadIdx.x % G;
+  const int nvec = H >> 3;
+  const float inv_h = 1.f / H;
+  float dg[GVPT][8], db[GVPT][8];
+#pragma unroll
+  for (int i = 0; i < GVPT; ++i) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { dg[i][j] = 0.f; db[i][j] = 0.f; }
+  }
+  const uint4* gvec = reinterpret_cast<const uint4*>(gamma);  // re-read per use: stays in L1
+  for (int base = blockIdx.x * RPC; base < rows; base += gridDim.x * RPC) {
+    const int row = base + grp;
+    const bool active = row < rows;
+    const uint4* dyr = reinterpret_cast<const uint4*>(dy + (size_t)row * H);
+    const uint4* xr = reinterpret_cast<const uint4*>(x + (size_t)row * H);
+    const float mean = (RMS || !active) ? 0.f : mean_in[row];
+    const float rstd = active ? rstd_in[row] : 0.f;
+    uint4 draw[GVPT], xraw[GVPT];
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int i = 0; i < GVPT; ++i) {
+      const int c = t + i * G;
+      draw[i] = make_uint4(0, 0, 0, 0);
+      xraw[i] = make_uint4(0, 0, 0, 0);
+      if (active && c < nvec) {
+        draw[i] = ld_nc_v4(dyr + c);
+        xraw[i] = ld_nc_v4(xr + c);
+        float d[8], xv[8], g[8];
+        unpack8(draw[i], d);
+        unpack8(xraw[i], xv);
+        unpack8(__ldg(gvec + c), g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float xh = (xv[j] - mean) * rstd;
+          const float gy = d[j] * g[j];
+          dg[i][j] += d[j] * xh;
+          db[i][j] += d[j];
+          s0 += gy;
+          s1 += gy * xh;
+        }
+      }
+    }
+    group_sum2<G>(s0, s1, red, grp, t);
+    const float m1 = RMS ? 0.f : s0 * inv_h;
+    const float m2 = s1 * inv_h;
+    uint4* dxr = reinterpret_cast<uint4*>(dx + (size_t)row * H);
+#pragma unroll
+    for (int i = 0; i < GVPT; ++i) {
+      const int c = t + i * G;
+      if (active && c < nvec) {
+        float d[8], xv[8], g[8], o[8];
+        unpack8(draw[i], d);
+        unpack8(xraw[i], xv);
+        unpack8(__ldg(gvec + c), g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float xh = (xv[j] - mean) * rstd;
+          o[j] = rstd * (d[j] * g[j] - m1 - xh * m2);
+        }
+        if (dres_in) {  // gradient arriving through the fused residual branch
+          float r[8];
+          unpack8(ld_nc_v4(reinterpret_cast<const uint4*>(dres_in + (size_t)row * H) + c), r);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] += r[j];
+        }
+        dxr[c] = pack8(o);
+      }
+    }
+  }
+  // CTA partial = sum over its row groups, through shared memory (RPC * H <= 8192 floats)
+#pragma unroll
+  for (int which = 0; which < (RMS ? 1 : 2); ++which) {
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < GVPT; ++i) {
+      const int c = t + i * G;
+      if (c < nvec) {
+        float4* o = reinterpret_cast<float4*>(part + grp * H + c * 8);
+        const float(&src)[8] = which ? db[i] : dg[i];
+        o[0] = make_float4(src[0], src[1], src[2], src[3]);
+        o[1] = make_float4(src[4], src[5], src[6], src[7]);
+      }
+    }
+    __syncthreads();
+    float* dst = partial + (size_t)blockIdx.x * 2 * H + which * H;
+    for (int h = threadIdx.x; h < H; h += NORM_THREADS) {
+      float acc = 0.f;
+#pragma unroll
+      for (int g2 = 0; g2 < RPC; ++g2) acc += part[g2 * H + h];
+      dst[h] = acc;
+    }
+  }
+}
+
+// Threads per row for the group kernels, 0 = use the CTA-per-row fallback.
+static int group_size(int H) {
+  const int nvec = H / 8;
+  for (int g = 32; g <= 256; g *= 2)
+    if (nvec <= GVPT * g) return g;
+  return 0;
 }
 
 template <bool RMS>
 int launch_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* y,
                void* h_out, float* mean, float* rstd, int rows, int H, float eps,
                cudaStream_t st) {
+  if (const int G = group_size(H)) {
+    const int rpc = NORM_THREADS / G;
+    const int want = (rows + rpc - 1) / rpc;
+    const int cap = sm_count() * 8;
+    const int ggrid = want < cap ? want : cap;
+#define B2F_NORM_FWD_G(GG)                                                                      \
+  norm_fwd_g_kernel<GG, RMS><<<ggrid, NORM_THREADS, 0, st>>>(                                    \
+      (const __nv_bfloat16*)x, (const __nv_bfloat16*)residual, (const __nv_bfloat16*)gamma,     \
+      (const __nv_bfloat16*)beta, (__nv_bfloat16*)y, (__nv_bfloat16*)h_out, mean, rstd, rows, H, \
+      eps)
+    switch (G) {
+      case 32: B2F_NORM_FWD_G(32); break;
+      case 64: B2F_NORM_FWD_G(64); break;
+      case 128: B2F_NORM_FWD_G(128); break;
+      default: B2F_NORM_FWD_G(256); break;
+    }
+#undef B2F_NORM_FWD_G
+    B2F_CHECK_CUDA(cudaGetLastError());
+    return 0;
+  }
   const int vpt = (H / 8 + NORM_THREADS - 1) / NORM_THREADS;
   const int grid = rows < 148 * 8 ? rows : 148 * 8;
 #define B2F_NORM_FWD(V)                                                                         \
@@ -246,6 +481,24 @@ template <bool RMS>
 int launch_bwd(const void* dy, const void* x, const void* gamma, const float* mean,
                const float* rstd, const void* dres, void* dx, float* dgamma, float* dbeta,
                float* scratch, int nparts, int rows, int H, int accumulate, cudaStream_t st) {
+  if (const int G = group_size(H)) {
+#define B2F_NORM_BWD_G(GG)                                                                    \
+  norm_bwd_g_kernel<GG, RMS><<<nparts, NORM_THREADS, 0, st>>>(                                 \
+      (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (const __nv_bfloat16*)gamma, mean,   \
+      rstd, (const __nv_bfloat16*)dres, (__nv_bfloat16*)dx, scratch, rows, H)
+    switch (G) {
+      case 32: B2F_NORM_BWD_G(32); break;
+      case 64: B2F_NORM_BWD_G(64); break;
+      case 128: B2F_NORM_BWD_G(128); break;
+      default: B2F_NORM_BWD_G(256); break;
+    }
+#undef B2F_NORM_BWD_G
+    B2F_CHECK_CUDA(cudaGetLastError());
+    norm_bwd_reduce_kernel<<<(H + 31) / 32, 256, 0, st>>>(scratch, nparts, H, dgamma,
+                                                            RMS ? nullptr : dbeta, accumulate);
+    B2F_CHECK_CUDA(cudaGetLastError());
+    return 0;
+  }
   const int vpt = (H / 8 + NORM_THREADS - 1) / NORM_THREADS;
 #define B2F_NORM_BWD(V)                                                                       \
   norm_bwd_kernel<V, RMS><<<nparts, NORM_THREADS, 0, st>>>(                                   \
@@ -259,7 +512,7 @@ int launch_bwd(const void* dy, const void* x, const void* gamma, const float* me
   }
 #undef B2F_NORM_BWD
   B2F_CHECK_CUDA(cudaGetLastError());
-  norm_bwd_reduce_kernel<<<(H + 255) / 256, 256, 0, st>>>(scratch, nparts, H, dgamma,
+  norm_bwd_reduce_kernel<<<(H + 31) / 32, 256, 0, st>>>(scratch, nparts, H, dgamma,
                                                           RMS ? nullptr : dbeta, accumulate);
   B2F_CHECK_CUDA(cudaGetLastError());
   return 0;

@@ -164,7 +164,7 @@ def group_gemm_perf():
 def group_norm():
     torch.manual_seed(2)
     for rms in (True, False):
-        for (rows, H) in [(64, 1024), (300, 4096), (4096, 4096), (17, 768)]:
+        for (rows, H) in [(64, 1024), (300, 4096), (4096, 4096), (17, 768), (33, 2048), (9, 8192), (70, 5120), (5, 16384)]:
             x = torch.randn(rows, H, device=DEV, dtype=torch.bfloat16, requires_grad=True)
             r = torch.randn(rows, H, device=DEV, dtype=torch.bfloat16, requires_grad=True)
             g = (1 + 0.1 * torch.randn(H, device=DEV)).to(torch.bfloat16).requires_grad_()
@@ -192,6 +192,24 @@ def group_norm():
             report(f"norm_dg_{tag}", g.grad, gf.grad, 3e-2)
             if bta is not None:
                 report(f"norm_db_{tag}", bta.grad, bf.grad, 3e-2)
+
+
+def group_norm_perf():
+    """Bandwidth of the norm kernels (bytes = algorithmic minimum) against the measured HBM peak."""
+    for (rows, H, rms) in [(32768, 1024, False), (4096, 4096, True), (16384, 4096, True), (8192, 8192, True)]:
+        x = torch.randn(rows, H, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+        r = torch.randn(rows, H, device=DEV, dtype=torch.bfloat16)
+        g = torch.ones(H, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+        b = None if rms else torch.zeros(H, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+        y, h = N.norm(x, g, b, residual=r, rms=rms, eps=1e-5)
+        dy = torch.randn_like(y)
+        t_f = timeit(lambda: N.norm(x.detach(), g.detach(), None if b is None else b.detach(), residual=r, rms=rms, eps=1e-5))
+        t_b = timeit(lambda: torch.autograd.grad(y, (x, g), dy, retain_graph=True))
+        nb = rows * H * 2
+        rec = {"name": f"norm_perf_{rows}x{H}_{'rms' if rms else 'ln'}", "fwd_ms": t_f, "bwd_ms": t_b,
+               "fwd_GBps": 4 * nb / t_f / 1e6, "bwd_GBps": 3 * nb / t_b / 1e6}
+        print(json.dumps(rec), flush=True)
+        RESULTS.append({"name": rec["name"], "ok": True})
 
 
 def group_optim():
@@ -619,6 +637,7 @@ GROUPS = {
     "gemm_epi": group_gemm_epi,
     "gemm_perf": group_gemm_perf,
     "norm": group_norm,
+    "norm_perf": group_norm_perf,
     "optim": group_optim,
     "elementwise": group_elementwise,
 }
