@@ -190,13 +190,16 @@ b2f_gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0 && leader) {
-      // ------------------------------------------- MMA issuer (leader CTA only)
+    if (leader) {
+      // ------------------------------------------- MMA issuer (leader CTA only).  The whole warp
+      // walks the loop (uniform control flow, operands stay in uniform registers) and one elected
+      // lane issues; descriptors are a precomputed low word plus a constant per K step.
       const uint32_t idesc = make_idesc(1, 1, T2_BM, T2_BN, p.a_mn_major, p.b_mn_major);
       const uint32_t a_kstep = p.a_mn_major ? 2048u : 32u;
       const uint32_t b_kstep = p.b_mn_major ? 2048u : 32u;
       const uint32_t a_lbo = p.a_mn_major ? (uint32_t)CHUNK_BYTES : 16u;
       const uint32_t b_lbo = p.b_mn_major ? (uint32_t)CHUNK_BYTES : 16u;
+      constexpr uint32_t DHI = desc_hi_sw128(1024);
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
@@ -226,20 +229,21 @@ b2f_gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
 #endif
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + stage * ST2_BYTES);
-          const uint32_t sb = sa + A2_BYTES;
+          const uint32_t la = desc_lo_sw128(sa, a_lbo), lb = desc_lo_sw128(sa + A2_BYTES, b_lbo);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k) {
-            const uint64_t da = make_smem_desc_sw128(sa + k * a_kstep, a_lbo, 1024);
-            const uint64_t db = make_smem_desc_sw128(sb + k * b_kstep, b_lbo, 1024);
-            umma_f16_ss_2sm(d_tmem, da, db, idesc, (kb | k) != 0);
+            for (int k = 0; k < BK / 16; ++k)
+              umma_f16_ss_2sm(d_tmem, desc_from(la + k * (a_kstep >> 4), DHI),
+                              desc_from(lb + k * (b_kstep >> 4), DHI), idesc, (kb | k) != 0);
+            umma_commit_2sm(&ss->empty[stage]);
+            if (kb == num_kb - 1) umma_commit_2sm(&ss->tmem_full[as]);
           }
-          umma_commit_2sm(&ss->empty[stage]);
-          if (kb == num_kb - 1) umma_commit_2sm(&ss->tmem_full[as]);
+          __syncwarp();
           if (++stage == S2) { stage = 0; phase ^= 1; }
         }
       }
 #ifdef B2F_GEMM2_DEBUG
-      if (pair == 0) {
+      if (pair == 0 && lane == 0) {
         g_gemm2_dbg[0] = clock64() - t_begin;
         g_gemm2_dbg[1] = t_full;
         g_gemm2_dbg[2] = t_acc;

@@ -311,8 +311,9 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap* tma_a, const CUtens
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0) {
-      // ------------------------------------------------------------ MMA issuer
+    {
+      // ------------------------------------------------------------ MMA issuer: the whole warp
+      // walks the loop, one elected lane issues (keeps descriptors in uniform registers)
       const uint32_t idesc = KIND == 1 ? make_idesc(0, 0, BM, BN, 0, 0)
                                        : make_idesc(1, 1, BM, BN, p.a_mn_major, p.b_mn_major);
       // K-major: +32 B per UMMA_K inside the swizzle atom; MN-major: +16 rows * 128 B.
@@ -320,6 +321,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap* tma_a, const CUtens
       const uint32_t b_kstep = p.b_mn_major ? 2048u : 32u;
       const uint32_t a_lbo = p.a_mn_major ? (uint32_t)CHUNK_BYTES : 16u;
       const uint32_t b_lbo = p.b_mn_major ? (uint32_t)CHUNK_BYTES : 16u;
+      constexpr uint32_t DHI = desc_hi_sw128(1024);
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
@@ -333,16 +335,19 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap* tma_a, const CUtens
           mbar_wait(&ss->full[stage], phase);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
-          const uint32_t sb = sa + A_STAGE_BYTES;
+          const uint32_t la = desc_lo_sw128(sa, a_lbo), lb = desc_lo_sw128(sa + A_STAGE_BYTES, b_lbo);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k) {
-            uint64_t da = make_smem_desc_sw128(sa + k * a_kstep, a_lbo, 1024);
-            uint64_t db = make_smem_desc_sw128(sb + k * b_kstep, b_lbo, 1024);
-            if (KIND == 1) umma_f8_ss(d_tmem, da, db, idesc, (kb | k) != 0);
-            else umma_f16_ss(d_tmem, da, db, idesc, (kb | k) != 0);
+            for (int k = 0; k < BK / 16; ++k) {
+              const uint64_t da = desc_from(la + k * (a_kstep >> 4), DHI);
+              const uint64_t db = desc_from(lb + k * (b_kstep >> 4), DHI);
+              if (KIND == 1) umma_f8_ss(d_tmem, da, db, idesc, (kb | k) != 0);
+              else umma_f16_ss(d_tmem, da, db, idesc, (kb | k) != 0);
+            }
+            umma_commit(&ss->empty[stage]);  // frees the smem slot when these MMAs retire
+            if (kb == num_kb - 1) umma_commit(&ss->tmem_full[as]);
           }
-          umma_commit(&ss->empty[stage]);  // frees the smem slot when these MMAs retire
-          if (kb == num_kb - 1) umma_commit(&ss->tmem_full[as]);
+          __syncwarp();
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
