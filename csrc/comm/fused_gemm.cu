@@ -22,7 +22,10 @@
 //
 // Replaces NCCL all-gather + cuBLAS and cuBLAS + NCCL reduce-scatter of Megatron's
 // sequence-parallel Column/RowParallelLinear.
+#include <stdlib.h>
+
 #include "../kernels/gemm_core.cuh"
+#include "../kernels/gemm2_core.cuh"
 #include "../common/host.h"
 #include "../../include/b200flow.h"
 
@@ -81,6 +84,7 @@ struct AGArgs {
   int rows_per_rank, K;
   int comm_ctas;
   uint32_t epoch;
+  int own_last;
 };
 
 struct AGPolicy {
@@ -106,45 +110,102 @@ struct AGPolicy {
     epilogue_chunk(p, b, m, n0, acc);
   }
   __device__ __forceinline__ void tile_done(int, int, int) const {}
+  __device__ __forceinline__ void finish() const {}
 };
 
-__device__ void ag_comm_role(const AGArgs& a) {
+// Gather role: one thread per comm CTA drives the copy engine.  A 128-row block of a shard
+// (128 x K bf16, contiguous) is moved in 32 KB chunks: bulk load (peer or local global -> this
+// CTA's shared memory, completion on an mbarrier), then bulk store (shared -> local gathered
+// buffer).  Six 32 KB slots, five loads in flight per CTA, so a handful of CTAs keeps enough
+// bytes in flight to cover NVLink latency; no registers or LSU instructions touch the data.
+constexpr int AG_CHUNK = 32 * 1024;
+constexpr int AG_SLOTS = 6;
+constexpr int AG_AHEAD = 5;
+
+__device__ void ag_comm_role(const AGArgs& a, uint8_t* smem_raw) {
+  if (threadIdx.x != 0) return;
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + AG_SLOTS * AG_CHUNK);
+  for (int i = 0; i < AG_SLOTS; ++i) mbar_init(&full[i], 1);
+  fence_mbar_init();
   const int blocks_per_rank = a.rows_per_rank / BM;
   const int units = blocks_per_rank * a.world;
-  const long long row_vecs = (long long)a.K / 8;          // uint4 per row
-  const long long unit_vecs = row_vecs * BM;
-  if (blockIdx.x == 0 && (int)threadIdx.x < a.world) {
+  const long long unit_bytes = (long long)BM * a.K * 2;
+  const int chunks_per_unit = (int)((unit_bytes + AG_CHUNK - 1) / AG_CHUNK);
+  if (blockIdx.x == 0) {
     // announce: this rank's shard for `epoch` is complete (stream order guarantees it)
     __threadfence_system();
-    st_release_sys(static_cast<uint32_t*>(a.ready.ptr[threadIdx.x]) + a.rank, a.epoch);
+    for (int r = 0; r < a.world; ++r)
+      st_release_sys(static_cast<uint32_t*>(a.ready.ptr[r]) + a.rank, a.epoch);
   }
-  for (int u = blockIdx.x; u < units; u += a.comm_ctas) {
-    // own shard first, then peers in ring order
-    const int src = (a.rank + u / blocks_per_rank) % a.world;
+  // this CTA's chunk sequence: units blockIdx.x, +comm_ctas, ... each split into chunks
+  int my_units = 0;
+  for (int u = blockIdx.x; u < units; u += a.comm_ctas) ++my_units;
+  const long long total = (long long)my_units * chunks_per_unit;
+  auto locate = [&](long long c, const uint8_t*& src, uint8_t*& dst, uint32_t& bytes, int& unit_idx) {
+    const int ui = (int)(c / chunks_per_unit), ci = (int)(c % chunks_per_unit);
+    const int u = blockIdx.x + ui * a.comm_ctas;
+    // ring order; `own_last` (CTA-pair kernel: the GEMM reads own rows from the shard) moves the
+    // local copy behind the remote pulls
+    const int srank = (a.rank + u / blocks_per_rank + (a.own_last ? 1 : 0)) % a.world;
     const int blk = u % blocks_per_rank;
-    if (src != a.rank) {
-      if (threadIdx.x == 0)
-        wait_flag_ge(static_cast<const uint32_t*>(a.ready.ptr[a.rank]) + src, a.epoch);
-      __syncthreads();
+    const long long off = (long long)ci * AG_CHUNK;
+    const long long rem = unit_bytes - off;
+    bytes = (uint32_t)(rem < AG_CHUNK ? rem : AG_CHUNK);
+    src = static_cast<const uint8_t*>(a.x_shards.ptr[srank]) + (long long)blk * unit_bytes + off;
+    dst = reinterpret_cast<uint8_t*>(a.xg) + ((long long)srank * blocks_per_rank + blk) * unit_bytes + off;
+    unit_idx = srank * blocks_per_rank + blk;
+    return srank;
+  };
+  int ready_seen = -1;  // ranks are visited in ring order, so one "last checked" value suffices
+  auto issue_load = [&](long long c) {
+    const uint8_t* src; uint8_t* dst; uint32_t bytes; int ui;
+    const int srank = locate(c, src, dst, bytes, ui);
+    if (srank != a.rank && srank != ready_seen) {
+      wait_flag_ge(static_cast<const uint32_t*>(a.ready.ptr[a.rank]) + srank, a.epoch);
+      ready_seen = srank;
     }
-    const uint4* s = reinterpret_cast<const uint4*>(
-        static_cast<const __nv_bfloat16*>(a.x_shards.ptr[src]) + (long long)blk * BM * a.K);
-    uint4* d = reinterpret_cast<uint4*>(a.xg + ((long long)src * a.rows_per_rank + (long long)blk * BM) * a.K);
-    long long i = threadIdx.x;
-    const long long step = blockDim.x;
-    for (; i + 7 * step < unit_vecs; i += 8 * step) {   // 8 independent 16 B loads in flight
-      uint4 v[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] = ld_v4(s + i + j * step);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) d[i + j * step] = v[j];
-    }
-    for (; i < unit_vecs; i += step) d[i] = ld_v4(s + i);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      __threadfence();
+    const int slot = (int)(c % AG_SLOTS);
+    mbar_arrive_expect_tx(&full[slot], bytes);
+    bulk_load_1d(smem + slot * AG_CHUNK, src, bytes, &full[slot]);
+  };
+  long long next_load = 0;
+  for (; next_load < total && next_load < AG_AHEAD; ++next_load) issue_load(next_load);
+  int pending_flag = -1;        // unit whose stores are all issued but not yet known complete
+  int since_pending = 0;        // store groups committed after that unit's last one
+  for (long long c = 0; c < total; ++c) {
+    const uint8_t* src; uint8_t* dst; uint32_t bytes; int ui;
+    locate(c, src, dst, bytes, ui);
+    const int slot = (int)(c % AG_SLOTS);
+    mbar_wait(&full[slot], (uint32_t)((c / AG_SLOTS) & 1));
+    bulk_store_1d(dst, smem + slot * AG_CHUNK, bytes);
+    tma_store_commit();
+    if (pending_flag >= 0) ++since_pending;
+    // slot of chunk c+AG_AHEAD was last read by the store of chunk c-1: allow only the newest
+    // group (this one) to still be reading
+    tma_store_wait_read<1>();
+    if (next_load < total) issue_load(next_load++);
+    if (pending_flag >= 0 && since_pending == 2) {
+      tma_store_wait<2>();      // everything older than the two newest groups has landed
       asm volatile("fence.proxy.async;" ::: "memory");
-      st_release_gpu(a.tile_flags + src * blocks_per_rank + blk, a.epoch);
+      __threadfence();
+      st_release_gpu(a.tile_flags + pending_flag, a.epoch);
+      pending_flag = -1;
+    }
+    if ((c + 1) % chunks_per_unit == 0) {
+      if (pending_flag >= 0 || chunks_per_unit < 3 || c + 1 == total) {
+        // short units or the tail: drain and publish directly
+        tma_store_wait<0>();
+        asm volatile("fence.proxy.async;" ::: "memory");
+        __threadfence();
+        if (pending_flag >= 0) st_release_gpu(a.tile_flags + pending_flag, a.epoch);
+        st_release_gpu(a.tile_flags + ui, a.epoch);
+        pending_flag = -1;
+      } else {
+        pending_flag = ui;
+        since_pending = 0;
+      }
     }
   }
 }
@@ -154,12 +215,58 @@ b2f_ag_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_const
                    const Params p, const AGArgs a) {
   extern __shared__ uint8_t smem_raw[];
   if ((int)blockIdx.x < a.comm_ctas) {
-    ag_comm_role(a);
+    ag_comm_role(a, smem_raw);
     return;
   }
   AGPolicy pol{a.tile_flags, a.epoch, a.rank, a.rows_per_rank / BM};
   gemm_body(&tma_a, &tma_b, p, pol, (int)blockIdx.x - a.comm_ctas, (int)gridDim.x - a.comm_ctas,
             smem_raw);
+}
+
+// ---- K3 on the CTA-pair core: 256x256 pair tiles, each CTA of a pair waits for (and loads) its own
+// 128-row block.  Rows of this rank's own shard are read straight from the shard (second tensor
+// map), so the GEMM starts at once and the gather role copies the own shard last.
+struct AG2Policy {
+  const uint32_t* tile_flags;
+  const CUtensorMap* own_map;   // tensor map over this rank's [Ts, K] shard
+  uint32_t epoch;
+  int rank, blocks_per_rank;    // 128-row blocks per rank
+  __device__ __forceinline__ void map_tile(int t, int num_m, int num_n, int& b, int& mb, int& nb) const {
+    b = 0;
+    const int mi = t / num_n;
+    nb = t - mi * num_n;
+    mb = (mi + rank * (blocks_per_rank >> 1)) % num_m;   // pair-tile rows, own shard first
+  }
+  __device__ __forceinline__ void wait_operands(int, int mb128, int) const {
+    if (mb128 / blocks_per_rank == rank) return;           // own rows come from the shard itself
+    wait_ge_gpu(tile_flags + mb128, epoch);
+    asm volatile("fence.proxy.async;" ::: "memory");
+  }
+  __device__ __forceinline__ const CUtensorMap* select_a(const CUtensorMap* def, int mb128, int& m0) const {
+    if (mb128 / blocks_per_rank != rank) return def;
+    m0 -= rank * blocks_per_rank * BM;
+    return own_map;
+  }
+  __device__ __forceinline__ void before_epilogue(int, int, int) const {}
+  __device__ __forceinline__ void store_chunk(const Params& p, int b, int, int, int m, int n0,
+                                              const uint32_t (&acc)[32]) const {
+    epilogue_chunk(p, b, m, n0, acc);
+  }
+  __device__ __forceinline__ void tile_done(int, int, int) const {}
+  __device__ __forceinline__ void finish() const {}
+};
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+b2f_ag_gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_own,
+                    const __grid_constant__ CUtensorMap tma_b, const Params p, const AGArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  if ((int)blockIdx.x < a.comm_ctas) {   // comm_ctas is even: whole clusters
+    ag_comm_role(a, smem_raw);
+    return;
+  }
+  AG2Policy pol{a.tile_flags, &tma_own, a.epoch, a.rank, a.rows_per_rank / BM};
+  gemm2::gemm2_body<AG2Policy, gemm2::S2>(&tma_a, &tma_b, p, pol, ((int)blockIdx.x - a.comm_ctas) >> 1,
+                                          ((int)gridDim.x - a.comm_ctas) >> 1, smem_raw);
 }
 
 // ------------------------------------------------------------------ K4
@@ -170,11 +277,41 @@ struct RSArgs {
   int rows_per_rank;        // Ts
   int N;
   uint32_t epoch;
+  int dbg;                  // timing experiments only (B2F_RS_DEBUG): 1 = no sends, no receives; 2 = sends only
 };
+
+// Partial tiles bound for a peer are staged in shared memory as bf16 rows (528 B pitch: 512 B of
+// data + 16 B so the one-row-per-thread 16 B writes spread over the banks) and leave as one bulk
+// copy per row, i.e. 512 B NVLink writes instead of scattered 16 B stores.
+constexpr int RS_STAGES = 3;
+constexpr int RS_PITCH = BN * 2 + 16;
+constexpr int RS_SMEM_BYTES = RS_STAGES * STAGE_BYTES + 1024 /*barriers*/ + BM * RS_PITCH + 16 /*rx barrier*/ + 1024 /*align*/;
 
 struct RSPolicy {
   RSArgs a;
   int blocks_per_rank, num_n;
+  uint8_t* staging;
+  // the flag of a shipped tile is published one tile later (its bulk copies have long landed by
+  // then), so the epilogue never sits out an NVLink round trip
+  mutable int pend_owner = -1, pend_mb_local = 0, pend_nb = 0;
+  mutable uint32_t rx_phase = 0;
+  __device__ __forceinline__ uint64_t* rx_bar() const {
+    return reinterpret_cast<uint64_t*>(staging + BM * RS_PITCH);
+  }
+  // kernel prologue (one thread, before the CTA-wide sync): barrier for the partial-row prefetch
+  __device__ __forceinline__ void init_smem() const { mbar_init(rx_bar(), 128); fence_mbar_init(); }
+  __device__ __forceinline__ void flush() const {
+    if (pend_owner < 0) return;
+    tma_store_wait<0>();  // this thread's row of the pending tile is in the peer's memory
+    asm volatile("fence.proxy.async;" ::: "memory");
+    asm volatile("bar.sync 1, 128;" ::: "memory");  // ... and so is everyone else's
+    if (threadIdx.x == 64) {
+      __threadfence_system();
+      st_release_sys(flag_at(pend_owner, a.rank, pend_mb_local, pend_nb), a.epoch);
+    }
+    pend_owner = -1;
+  }
+  __device__ __forceinline__ void finish() const { flush(); }
   __device__ __forceinline__ int owner_of(int mb) const { return mb / blocks_per_rank; }
   __device__ __forceinline__ void map_tile(int t, int num_m, int nn, int& b, int& mb, int& nb) const {
     // peers' row blocks first (ring order after this rank), own blocks last
@@ -192,13 +329,32 @@ struct RSPolicy {
            ((size_t)src * blocks_per_rank + mb_local) * num_n + nb;
   }
   __device__ __forceinline__ void before_epilogue(int, int mb, int nb) const {
-    if (owner_of(mb) != a.rank) return;
+    if (owner_of(mb) != a.rank) {
+      tma_store_wait_read<0>();  // the staging rows of the previous shipped tile have been read out
+      return;
+    }
+    flush();  // publish before waiting on the peers, or two ranks could wait on each other
+    if (a.dbg) return;
     const int mb_local = mb - a.rank * blocks_per_rank;
     if ((threadIdx.x & 31) == 0) {
       for (int s = 0; s < a.world; ++s)
         if (s != a.rank) wait_flag_ge(flag_at(a.rank, s, mb_local, nb), a.epoch);
     }
     __syncwarp();
+    if (a.world == 2) {
+      // one bulk copy per row pulls the peer's 512 B partial row into the (idle) staging buffer
+      const int r = (int)threadIdx.x - 64;
+      const int row_in_tile = (((r >> 5) + 2) & 3) * 32 + (r & 31);
+      const int n0 = nb * BN;
+      const int cols = a.N - n0 < BN ? a.N - n0 : BN;
+      const __nv_bfloat16* src = static_cast<const __nv_bfloat16*>(a.recv.ptr[a.rank]) +
+                                 ((size_t)(a.rank ^ 1) * a.rows_per_rank + (size_t)mb_local * BM + row_in_tile) * a.N + n0;
+      asm volatile("fence.proxy.async;" ::: "memory");
+      mbar_arrive_expect_tx(rx_bar(), (uint32_t)cols * 2);
+      bulk_load_1d(staging + (size_t)row_in_tile * RS_PITCH, src, (uint32_t)cols * 2, rx_bar());
+      mbar_wait(rx_bar(), rx_phase);
+      rx_phase ^= 1;
+    }
   }
   __device__ __forceinline__ void store_chunk(const Params& p, int b, int mb, int nb, int m, int n0,
                                               const uint32_t (&acc)[32]) const {
@@ -206,9 +362,8 @@ struct RSPolicy {
     const int row_local = m - owner * a.rows_per_rank;
     if (m >= p.M || n0 >= p.N) return;
     if (owner != a.rank) {
-      // partial tile -> owner's receive slot for this source rank
-      __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(a.recv.ptr[owner]) +
-                           ((size_t)a.rank * a.rows_per_rank + row_local) * a.N + n0;
+      // partial tile -> bf16 row in the staging buffer; tile_done ships the rows
+      uint8_t* dst = staging + (size_t)(m - mb * BM) * RS_PITCH + (size_t)(n0 - nb * BN) * 2;
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         uint4 u;
@@ -216,7 +371,7 @@ struct RSPolicy {
         u.y = pack_bf16x2(__uint_as_float(acc[q * 8 + 2]), __uint_as_float(acc[q * 8 + 3]));
         u.z = pack_bf16x2(__uint_as_float(acc[q * 8 + 4]), __uint_as_float(acc[q * 8 + 5]));
         u.w = pack_bf16x2(__uint_as_float(acc[q * 8 + 6]), __uint_as_float(acc[q * 8 + 7]));
-        st_v4(dst + q * 8, u);
+        *reinterpret_cast<uint4*>(dst + q * 16) = u;
       }
       return;
     }
@@ -225,12 +380,13 @@ struct RSPolicy {
 #pragma unroll
     for (int i = 0; i < 32; ++i) sum[i] = acc[i];
     for (int s = 0; s < a.world; ++s) {
-      if (s == a.rank) continue;
+      if (s == a.rank || a.dbg) continue;
       const __nv_bfloat16* src = static_cast<const __nv_bfloat16*>(a.recv.ptr[a.rank]) +
                                  ((size_t)s * a.rows_per_rank + row_local) * a.N + n0;
+      const uint8_t* staged = staging + (size_t)(m - mb * BM) * RS_PITCH + (size_t)(n0 - nb * BN) * 2;
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
-        const uint4 u = ld_cv_v4(src + q * 8);
+        const uint4 u = a.world == 2 ? *reinterpret_cast<const uint4*>(staged + q * 16) : ld_cv_v4(src + q * 8);
         const float2 f0 = unpack_bf16x2(u.x), f1 = unpack_bf16x2(u.y), f2 = unpack_bf16x2(u.z),
                      f3 = unpack_bf16x2(u.w);
         sum[q * 8 + 0] = __float_as_uint(__uint_as_float(sum[q * 8 + 0]) + f0.x);
@@ -250,13 +406,23 @@ struct RSPolicy {
   }
   __device__ __forceinline__ void tile_done(int, int mb, int nb) const {
     const int owner = owner_of(mb);
-    if (owner == a.rank) return;
-    // all 128 epilogue threads' peer stores must be out before the flag
-    asm volatile("bar.sync 1, 128;" ::: "memory");
-    if (threadIdx.x == 64) {  // first epilogue thread
-      __threadfence_system();
-      st_release_sys(flag_at(owner, a.rank, mb - owner * blocks_per_rank, nb), a.epoch);
-    }
+    if (owner == a.rank) return;   // (before_epilogue already flushed)
+    // this thread's row: staging -> owner's receive slot for this source rank, one bulk copy
+    const int r = (int)threadIdx.x - 64;  // epilogue threads are 64..191, TMEM quarter = warp & 3
+    const int row_in_tile = (((r >> 5) + 2) & 3) * 32 + (r & 31);
+    const int row_local = mb * BM + row_in_tile - owner * a.rows_per_rank;
+    const int n0 = nb * BN;
+    const int cols = a.N - n0 < BN ? a.N - n0 : BN;
+    __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(a.recv.ptr[owner]) +
+                         ((size_t)a.rank * a.rows_per_rank + row_local) * a.N + n0;
+    flush();
+    if (a.dbg == 1) return;
+    asm volatile("fence.proxy.async;" ::: "memory");  // generic-proxy staging writes -> bulk copy reads
+    bulk_store_1d(dst, staging + (size_t)row_in_tile * RS_PITCH, (uint32_t)cols * 2);
+    tma_store_commit();
+    pend_owner = owner;
+    pend_mb_local = mb - owner * blocks_per_rank;
+    pend_nb = nb;
   }
 };
 
@@ -264,8 +430,50 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 b2f_gemm_rs_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                    const Params p, const RSArgs a) {
   extern __shared__ uint8_t smem_raw[];
-  RSPolicy pol{a, a.rows_per_rank / BM, (p.N + BN - 1) / BN};
-  gemm_body(&tma_a, &tma_b, p, pol, blockIdx.x, gridDim.x, smem_raw);
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  RSPolicy pol{a, a.rows_per_rank / BM, (p.N + BN - 1) / BN, smem + RS_STAGES * STAGE_BYTES + 1024};
+  if (threadIdx.x == 0) pol.init_smem();
+  gemm_body<RSPolicy, 0, RS_STAGES>(&tma_a, &tma_b, p, pol, blockIdx.x, gridDim.x, smem_raw);
+}
+
+// ---- K4 on the CTA-pair core: same protocol, each CTA of a pair handles its own 128-row block.
+constexpr int RS2_STAGES = 4;
+constexpr int RS2_SMEM_BYTES = gemm2::smem2_bytes(RS2_STAGES, BM * RS_PITCH + 16);
+
+struct RS2Policy {
+  RSPolicy in;   // 128-row-block logic is identical; only the tile order differs
+  __device__ __forceinline__ void map_tile(int t, int num_m, int nn, int& b, int& mb, int& nb) const {
+    b = 0;
+    const int pairs_per_rank = in.blocks_per_rank >> 1;
+    const int per_owner = pairs_per_rank * nn;
+    const int oi = t / per_owner;
+    const int owner = (in.a.rank + 1 + oi) % in.a.world;
+    const int r = t - oi * per_owner;
+    nb = r / pairs_per_rank;
+    mb = owner * pairs_per_rank + (r - nb * pairs_per_rank);
+  }
+  __device__ __forceinline__ void wait_operands(int, int, int) const {}
+  __device__ __forceinline__ const CUtensorMap* select_a(const CUtensorMap* def, int, int&) const { return def; }
+  __device__ __forceinline__ void before_epilogue(int b, int mb128, int nb) const { in.before_epilogue(b, mb128, nb); }
+  __device__ __forceinline__ void store_chunk(const Params& p, int b, int mb128, int nb, int m, int n0,
+                                              const uint32_t (&acc)[32]) const {
+    in.store_chunk(p, b, mb128, nb, m, n0, acc);
+  }
+  __device__ __forceinline__ void tile_done(int b, int mb128, int nb) const { in.tile_done(b, mb128, nb); }
+  __device__ __forceinline__ void finish() const { in.finish(); }
+};
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+b2f_gemm_rs2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                    const Params p, const RSArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  RS2Policy pol{RSPolicy{a, a.rows_per_rank / BM, (p.N + BN - 1) / BN,
+                         smem + RS2_STAGES * gemm2::ST2_BYTES + 1024}};
+  if (threadIdx.x == 0) pol.in.init_smem();
+  gemm2::gemm2_body<RS2Policy, RS2_STAGES>(&tma_a, &tma_b, p, pol, blockIdx.x >> 1, gridDim.x >> 1, smem_raw);
 }
 
 int fill(PeerPtrs* t, const long long* ptrs, int world) {
@@ -304,9 +512,28 @@ extern "C" int b2f_ag_gemm_bf16(const long long* x_shard_ptrs, void* xg, const v
   a.tile_flags = static_cast<uint32_t*>(tile_flags);
   a.rank = rank; a.world = world; a.rows_per_rank = T / world; a.K = K; a.epoch = epoch;
   const int sms = sm_count();
-  if (comm_ctas < 1) comm_ctas = 16;
+  if (comm_ctas < 1) comm_ctas = 8;
   if (comm_ctas > sms / 2) comm_ctas = sms / 2;
   a.comm_ctas = comm_ctas;
+  static const bool force_1cta = [] { const char* e = getenv("B2F_FUSED_TP_CORE"); return e && e[0] == '1'; }();
+  if (!force_1cta && (T / world) % 256 == 0 && N >= 256) {
+    // CTA-pair core: per-CTA boxes of 128 rows of A / 128 rows of B
+    a.own_last = 1;
+    if (a.comm_ctas & 1) ++a.comm_ctas;
+    CUtensorMap ma2, mown, mb2;
+    if (int rc = make_operand_map(&ma2, xg, T, K, K, 1, 0, 0, BM)) return rc;
+    if (int rc = make_operand_map(&mown, reinterpret_cast<const void*>(x_shard_ptrs[rank]), T / world, K, K, 1, 0, 0, BM)) return rc;
+    if (int rc = make_operand_map(&mb2, B, N, K, ldb, 1, 0, b_mn_major, BM)) return rc;
+    B2F_CHECK_CUDA(cudaFuncSetAttribute(b2f_ag_gemm2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        gemm2::SMEM2_BYTES));
+    const int tiles2 = (T / 256) * ((N + 255) / 256);
+    int pairs = (sms - a.comm_ctas) / 2;
+    if (pairs > tiles2) pairs = tiles2;
+    b2f_ag_gemm2_kernel<<<a.comm_ctas + 2 * pairs, NUM_THREADS, gemm2::SMEM2_BYTES, static_cast<cudaStream_t>(stream)>>>(
+        ma2, mown, mb2, p, a);
+    B2F_CHECK_CUDA(cudaGetLastError());
+    return 0;
+  }
   CUtensorMap ma, mb;
   if (int rc = make_operand_map(&ma, xg, T, K, K, 1, 0, 0, BM)) return rc;
   if (int rc = make_operand_map(&mb, B, N, K, ldb, 1, 0, b_mn_major, BN)) return rc;
@@ -343,13 +570,29 @@ extern "C" int b2f_gemm_rs_bf16(const void* X, const void* B, void* Y_shard, int
   if (int rc = fill(&a.recv, recv_ptrs, world)) return rc;
   if (int rc = fill(&a.flags, flag_ptrs, world)) return rc;
   a.rank = rank; a.world = world; a.rows_per_rank = T / world; a.N = N; a.epoch = epoch;
+  if (const char* e = getenv("B2F_RS_DEBUG")) a.dbg = atoi(e);
+  static const bool force_1cta = [] { const char* e = getenv("B2F_FUSED_TP_CORE"); return e && e[0] == '1'; }();
+  if (!force_1cta && (T / world) % 256 == 0 && N >= 256) {
+    CUtensorMap ma2, mb2;
+    if (int rc = make_operand_map(&ma2, X, T, K, ldx, 1, 0, 0, BM)) return rc;
+    if (int rc = make_operand_map(&mb2, B, N, K, ldb, 1, 0, b_mn_major, BM)) return rc;
+    B2F_CHECK_CUDA(cudaFuncSetAttribute(b2f_gemm_rs2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        RS2_SMEM_BYTES));
+    const int tiles2 = (T / 256) * ((N + 255) / 256);
+    int pairs = sm_count() / 2;
+    if (pairs > tiles2) pairs = tiles2;
+    b2f_gemm_rs2_kernel<<<2 * pairs, NUM_THREADS, RS2_SMEM_BYTES, static_cast<cudaStream_t>(stream)>>>(ma2, mb2, p, a);
+    B2F_CHECK_CUDA(cudaGetLastError());
+    return 0;
+  }
   CUtensorMap ma, mb;
   if (int rc = make_operand_map(&ma, X, T, K, ldx, 1, 0, 0, BM)) return rc;
   if (int rc = make_operand_map(&mb, B, N, K, ldb, 1, 0, b_mn_major, BN)) return rc;
-  if (int rc = ensure_smem(b2f_gemm_rs_kernel)) return rc;
+  B2F_CHECK_CUDA(cudaFuncSetAttribute(b2f_gemm_rs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      RS_SMEM_BYTES));
   const int tiles = (T / BM) * ((N + BN - 1) / BN);
   const int sms = sm_count();
-  b2f_gemm_rs_kernel<<<tiles < sms ? tiles : sms, NUM_THREADS, SMEM_BYTES, static_cast<cudaStream_t>(stream)>>>(
+  b2f_gemm_rs_kernel<<<tiles < sms ? tiles : sms, NUM_THREADS, RS_SMEM_BYTES, static_cast<cudaStream_t>(stream)>>>(
       ma, mb, p, a);
   B2F_CHECK_CUDA(cudaGetLastError());
   return 0;

@@ -122,6 +122,13 @@ __device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, u
       "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
       : "memory");
 }
+// 1-D bulk copy shared -> global (may be a peer GPU's mapped memory); completion is tracked by
+// the issuing thread's bulk async-group (tma_store_commit / tma_store_wait*).
+__device__ __forceinline__ void bulk_store_1d(void* gdst, const void* smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst),
+               "r"(smem_u32(smem_src)), "r"(bytes)
+               : "memory");
+}
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* smem_src,
                                              int32_t c0, int32_t c1) {
   asm volatile(

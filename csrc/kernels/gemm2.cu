@@ -13,12 +13,15 @@
 //   tmem_empty[a] leader's: 8 arrivals = 4 epilogue warps x 2 CTAs (remote mbarrier.arrive)
 //
 // Same operand-majorness options and epilogue as the 1-CTA core (gemm_core.cuh).
-#include "gemm_core.cuh"
+#include <stdlib.h>
+
+#include "gemm2_core.cuh"
 #include "../common/host.h"
 #include "../../include/b200flow.h"
 
 using namespace b2f;
 using namespace b2f::gemm;
+using namespace b2f::gemm2;
 
 namespace b2f {
 namespace gemm {
@@ -30,263 +33,22 @@ int check_params(const Params& p);
 
 namespace {
 
-constexpr int T2_BM = 256, T2_BN = 256;     // tile of the CTA pair
-constexpr int HALF = 128;                   // rows of A / rows of B staged per CTA
-constexpr int S2 = 6;                       // stages
-constexpr int A2_BYTES = HALF * BK * 2;     // 16 KB
-constexpr int B2_BYTES = HALF * BK * 2;     // 16 KB
-constexpr int ST2_BYTES = A2_BYTES + B2_BYTES;
-constexpr int SMEM2_BYTES = S2 * ST2_BYTES + 1024 + 256;
-
-struct Shared2 {
-  uint64_t full[S2];
-  uint64_t empty[S2];
-  uint64_t tmem_full[2];
-  uint64_t tmem_empty[2];
-  uint32_t tmem_base;
-};
-
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-  uint32_t r;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-  return r;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-// shared::cluster address of `local` in CTA `rank` of the cluster
-__device__ __forceinline__ uint32_t map_to_cta(uint32_t local, uint32_t rank) {
-  uint32_t r;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(rank));
-  return r;
-}
-__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  // default semantics (no cluster-scope membar): a .release.cluster arrive made the producer wait for
-  // its previous TMA round trip every k-block and halved the kernel's throughput
-  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
-}
-__device__ __forceinline__ void tma_load_3d_2sm(void* smem_dst, const CUtensorMap* m, uint32_t bar_cluster_addr,
-                                                int32_t c0, int32_t c1, int32_t c2) {
-  asm volatile(
-      "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
-      " [%0], [%1, {%3, %4, %5}], [%2];"
-      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_cluster_addr), "r"(c0), "r"(c1),
-      "r"(c2)
-      : "memory");
-}
-__device__ __forceinline__ void tmem_alloc_2sm(uint32_t* smem_dst, uint32_t ncols) {
-  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)),
-               "r"(ncols)
-               : "memory");
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc_2sm(uint32_t taddr, uint32_t ncols) {
-  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
-}
-__device__ __forceinline__ void umma_f16_ss_2sm(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
-                                                uint32_t idesc, uint32_t accumulate) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
-      "}\n" ::"r"(d_tmem),
-      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-// arrive on the barrier at this smem offset in BOTH CTAs once all prior MMAs have retired
-__device__ __forceinline__ void umma_commit_2sm(uint64_t* bar) {
-  const uint16_t mask = 0x3;
-  asm volatile(
-      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
-          smem_u32(bar)),
-      "h"(mask)
-      : "memory");
-}
-
-// Cycle accounting of the leader's MMA thread in pair 0 (development aid, read with
-// b2f_gemm2_debug; compiled in with -DB2F_GEMM2_DEBUG): [0] total loop, [1] waiting for operands, [2] waiting for a free accumulator,
-// [3] k-blocks issued.
-__device__ long long g_gemm2_dbg[8];
-
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 b2f_gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                       const Params p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~static_cast<uintptr_t>(1023));
-  Shared2* ss = reinterpret_cast<Shared2*>(smem + S2 * ST2_BYTES);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t cta = cluster_ctarank();
-  const bool leader = cta == 0;
-  const int num_m = (p.M + T2_BM - 1) / T2_BM;
-  const int num_n = (p.N + T2_BN - 1) / T2_BN;
-  const int num_tiles = num_m * num_n * p.batch;
-  const int num_kb = (p.K + BK - 1) / BK;
-  const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+  Plain2 pol;
+  gemm2_body<Plain2, S2>(&tma_a, &tma_b, p, pol, blockIdx.x >> 1, gridDim.x >> 1, smem_raw);
+}
 
-  if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tma_a);
-    tma_prefetch_desc(&tma_b);
-    for (int s = 0; s < S2; ++s) {
-      mbar_init(&ss->full[s], 2);
-      mbar_init(&ss->empty[s], 1);
-    }
-    mbar_init(&ss->tmem_full[0], 1);
-    mbar_init(&ss->tmem_full[1], 1);
-    mbar_init(&ss->tmem_empty[0], 8);
-    mbar_init(&ss->tmem_empty[1], 8);
-    fence_mbar_init();
-  }
-  if (warp == 1) tmem_alloc_2sm(&ss->tmem_base, TMEM_COLS);
-  tc_fence_before();
-  __syncthreads();
-  cluster_sync_all();            // peer's barriers are initialised before anyone signals them
-  tc_fence_after();
-  const uint32_t tmem_base = ss->tmem_base;
-
-  auto map_tile = [&](int t, int& b, int& mb, int& nb) {
-    const int per_batch = num_m * num_n;
-    b = t / per_batch;
-    const int r = t - b * per_batch;
-    nb = r / num_m;
-    mb = r - nb * num_m;
-  };
-
-  if (warp == 0) {
-    if (lane == 0) {
-      // ------------------------------------------------ TMA producer (one per CTA)
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int t = pair; t < num_tiles; t += npairs) {
-        int b, mb, nb;
-        map_tile(t, b, mb, nb);
-        const int m0 = mb * T2_BM + (int)cta * HALF;     // this CTA's accumulator rows
-        const int n0 = nb * T2_BN + (int)cta * HALF;     // this CTA's half of the B tile
-        for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait(&ss->empty[stage], phase ^ 1);
-          uint8_t* sa = smem + stage * ST2_BYTES;
-          uint8_t* sb = sa + A2_BYTES;
-          const uint32_t full_leader = map_to_cta(smem_u32(&ss->full[stage]), 0);
-          if (leader) mbar_arrive_expect_tx(&ss->full[stage], 2 * ST2_BYTES);
-          else mbar_arrive_cluster(full_leader);
-          const int k0 = kb * BK;
-          if (!p.a_mn_major) {
-            tma_load_3d_2sm(sa, &tma_a, full_leader, k0, m0, b);
-          } else {
-            tma_load_3d_2sm(sa, &tma_a, full_leader, m0, k0, b);
-            tma_load_3d_2sm(sa + CHUNK_BYTES, &tma_a, full_leader, m0 + 64, k0, b);
-          }
-          if (!p.b_mn_major) {
-            tma_load_3d_2sm(sb, &tma_b, full_leader, k0, n0, b);
-          } else {
-            tma_load_3d_2sm(sb, &tma_b, full_leader, n0, k0, b);
-            tma_load_3d_2sm(sb + CHUNK_BYTES, &tma_b, full_leader, n0 + 64, k0, b);
-          }
-          if (++stage == S2) { stage = 0; phase ^= 1; }
-        }
-      }
-    }
-    __syncwarp();
-  } else if (warp == 1) {
-    if (leader) {
-      // ------------------------------------------- MMA issuer (leader CTA only).  The whole warp
-      // walks the loop (uniform control flow, operands stay in uniform registers) and one elected
-      // lane issues; descriptors are a precomputed low word plus a constant per K step.
-      const uint32_t idesc = make_idesc(1, 1, T2_BM, T2_BN, p.a_mn_major, p.b_mn_major);
-      const uint32_t a_kstep = p.a_mn_major ? 2048u : 32u;
-      const uint32_t b_kstep = p.b_mn_major ? 2048u : 32u;
-      const uint32_t a_lbo = p.a_mn_major ? (uint32_t)CHUNK_BYTES : 16u;
-      const uint32_t b_lbo = p.b_mn_major ? (uint32_t)CHUNK_BYTES : 16u;
-      constexpr uint32_t DHI = desc_hi_sw128(1024);
-      int stage = 0;
-      uint32_t phase = 0;
-      int it = 0;
-#ifdef B2F_GEMM2_DEBUG
-      long long t_full = 0, t_acc = 0, nkb = 0;
-      const long long t_begin = clock64();
-#endif
-      for (int t = pair; t < num_tiles; t += npairs, ++it) {
-        const int as = it & 1;
-#ifdef B2F_GEMM2_DEBUG
-        long long c0 = clock64();
-#endif
-        mbar_wait(&ss->tmem_empty[as], ((it >> 1) & 1) ^ 1);
-#ifdef B2F_GEMM2_DEBUG
-        t_acc += clock64() - c0;
-#endif
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + as * T2_BN;
-        for (int kb = 0; kb < num_kb; ++kb) {
-#ifdef B2F_GEMM2_DEBUG
-          c0 = clock64();
-#endif
-          mbar_wait(&ss->full[stage], phase);
-#ifdef B2F_GEMM2_DEBUG
-          t_full += clock64() - c0;
-          ++nkb;
-#endif
-          tc_fence_after();
-          const uint32_t sa = smem_u32(smem + stage * ST2_BYTES);
-          const uint32_t la = desc_lo_sw128(sa, a_lbo), lb = desc_lo_sw128(sa + A2_BYTES, b_lbo);
-          if (elect_one()) {
-#pragma unroll
-            for (int k = 0; k < BK / 16; ++k)
-              umma_f16_ss_2sm(d_tmem, desc_from(la + k * (a_kstep >> 4), DHI),
-                              desc_from(lb + k * (b_kstep >> 4), DHI), idesc, (kb | k) != 0);
-            umma_commit_2sm(&ss->empty[stage]);
-            if (kb == num_kb - 1) umma_commit_2sm(&ss->tmem_full[as]);
-          }
-          __syncwarp();
-          if (++stage == S2) { stage = 0; phase ^= 1; }
-        }
-      }
-#ifdef B2F_GEMM2_DEBUG
-      if (pair == 0 && lane == 0) {
-        g_gemm2_dbg[0] = clock64() - t_begin;
-        g_gemm2_dbg[1] = t_full;
-        g_gemm2_dbg[2] = t_acc;
-        g_gemm2_dbg[3] = nkb;
-      }
-#endif
-    }
-    __syncwarp();
-  } else {
-    // -------------------------------------------- epilogue (both CTAs, own rows)
-    const int q = warp & 3;
-    PlainPolicy pol;
-    int it = 0;
-    for (int t = pair; t < num_tiles; t += npairs, ++it) {
-      int b, mb, nb;
-      map_tile(t, b, mb, nb);
-      const int as = it & 1;
-      mbar_wait(&ss->tmem_full[as], (it >> 1) & 1);
-      tc_fence_after();
-      const int m = mb * T2_BM + (int)cta * HALF + q * 32 + lane;
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * T2_BN;
-#pragma unroll 1
-      for (int c = 0; c < T2_BN / 32; ++c) {
-        const int n0 = nb * T2_BN + c * 32;
-        if (n0 >= p.N) break;
-        uint32_t acc[32];
-        tmem_ld_32x32b_x32(taddr + c * 32, acc);
-        tmem_ld_wait();
-        pol.store_chunk(p, b, mb, nb, m, n0, acc);
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(map_to_cta(smem_u32(&ss->tmem_empty[as]), 0));
-    }
-  }
-
-  tc_fence_before();
-  __syncthreads();
-  cluster_sync_all();            // neither CTA frees TMEM / exits while the peer still uses the pair
-  if (warp == 1) {
-    tc_fence_after();
-    tmem_dealloc_2sm(tmem_base, TMEM_COLS);
-  }
+// Same kernel with a 4-deep ring (what the fused GEMM->reduce-scatter kernel can afford next to its
+// staging buffer); exposed so its cost can be measured in isolation (B2F_GEMM2_STAGES=4).
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+b2f_gemm2_bf16_s4_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                         const Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  Plain2 pol;
+  gemm2_body<Plain2, 4>(&tma_a, &tma_b, p, pol, blockIdx.x >> 1, gridDim.x >> 1, smem_raw);
 }
 
 }  // namespace
@@ -323,13 +85,22 @@ extern "C" int b2f_gemm_bf16_2cta(const void* A, const void* B, void* C, int M, 
   const int tiles = ((M + T2_BM - 1) / T2_BM) * ((N + T2_BN - 1) / T2_BN) * batch;
   int pairs = sm_count() / 2;
   if (pairs > tiles) pairs = tiles;
-  b2f_gemm2_bf16_kernel<<<pairs * 2, NUM_THREADS, SMEM2_BYTES, static_cast<cudaStream_t>(stream)>>>(ma, mb, p);
+  static const bool s4 = [] { const char* e = getenv("B2F_GEMM2_STAGES"); return e && e[0] == '4'; }();
+  if (s4) {
+    B2F_CHECK_CUDA(cudaFuncSetAttribute(b2f_gemm2_bf16_s4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        SMEM2_BYTES));
+    b2f_gemm2_bf16_s4_kernel<<<pairs * 2, NUM_THREADS, SMEM2_BYTES, static_cast<cudaStream_t>(stream)>>>(ma, mb, p);
+  } else {
+    b2f_gemm2_bf16_kernel<<<pairs * 2, NUM_THREADS, SMEM2_BYTES, static_cast<cudaStream_t>(stream)>>>(ma, mb, p);
+  }
   B2F_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
 
+#ifdef B2F_GEMM2_DEBUG
 extern "C" int b2f_gemm2_debug(long long* out8) {
   B2F_CHECK_CUDA(cudaDeviceSynchronize());
   B2F_CHECK_CUDA(cudaMemcpyFromSymbol(out8, g_gemm2_dbg, sizeof(long long) * 8));
   return 0;
 }
+#endif

@@ -107,6 +107,7 @@ struct PlainPolicy {
                                               const uint32_t (&acc)[32]) const;
   // Called by every epilogue thread after its rows of the tile are stored.
   __device__ __forceinline__ void tile_done(int, int, int) const {}
+  __device__ __forceinline__ void finish() const {}
 };
 
 // Store/convert one 32-column chunk of one accumulator row.
@@ -237,13 +238,15 @@ __device__ __forceinline__ void PlainPolicy::store_chunk(const Params& p, int b,
 // only a subset of its CTAs to the GEMM role (the rest move data between GPUs).
 // KIND: 0 = bf16 operands (kind::f16, 64 elements per 128 B row), 1 = fp8 e4m3 operands
 // (kind::f8f6f4, 128 elements per row, K-major only).
-template <class Policy, int KIND = 0>
+// NSTAGES: depth of the operand ring (a fused kernel may trade a stage for epilogue staging space;
+// the shared-memory layout is [NSTAGES x 48 KB ring][SharedStorage, 1 KB][policy-owned tail]).
+template <class Policy, int KIND = 0, int NSTAGES = STAGES>
 __device__ __forceinline__ void gemm_body(const CUtensorMap* tma_a, const CUtensorMap* tma_b,
                                           const Params& p, const Policy& pol, int first_tile,
                                           int tile_stride, uint8_t* smem_raw) {
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
-  SharedStorage* ss = reinterpret_cast<SharedStorage*>(smem + STAGES * STAGE_BYTES);
+  SharedStorage* ss = reinterpret_cast<SharedStorage*>(smem + NSTAGES * STAGE_BYTES);
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int num_m = (p.M + BM - 1) / BM;
@@ -256,7 +259,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap* tma_a, const CUtens
     tma_prefetch_desc(tma_a);
     tma_prefetch_desc(tma_b);
 #pragma unroll
-    for (int s = 0; s < STAGES; ++s) {
+    for (int s = 0; s < NSTAGES; ++s) {
       mbar_init(&ss->full[s], 1);
       mbar_init(&ss->empty[s], 1);
     }
@@ -305,7 +308,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap* tma_a, const CUtens
             for (int j = 0; j < BN / 64; ++j)
               tma_load_3d(sb + j * CHUNK_BYTES, tma_b, &ss->full[stage], n0 + j * 64, k0, b);
           }
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          if (++stage == NSTAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
@@ -348,7 +351,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap* tma_a, const CUtens
             if (kb == num_kb - 1) umma_commit(&ss->tmem_full[as]);
           }
           __syncwarp();
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          if (++stage == NSTAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
@@ -381,6 +384,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap* tma_a, const CUtens
       if (lane == 0) mbar_arrive(&ss->tmem_empty[as]);
       pol.tile_done(b, mb, nb);
     }
+    pol.finish();
   }
 
   tc_fence_before();
