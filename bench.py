@@ -122,6 +122,11 @@ def main():
         torch.cuda.set_device(0)
     dev = torch.device("cuda", torch.cuda.current_device())
 
+    if args.impl == "twin":
+        from b200flow.workloads.twin import run_twin
+
+        return run_twin(args, rank, world, dev, ClockSampler)
+
     if args.workload.startswith("bert"):
         from b200flow.workloads.bench_bert import run_bert_bench
 

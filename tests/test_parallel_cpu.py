@@ -179,3 +179,48 @@ def test_1f1b_schedule_shape():
                 assert peak <= min(stages - s, m)
     assert abs(bubble_fraction(2, 1) - 0.5) < 1e-9   # the reference's W3 config: 50 % bubble
     assert abs(bubble_fraction(2, 8) - 1 / 9) < 1e-9
+
+
+def _ulysses_worker(rank, world, port, q_out):
+    import torch.distributed as dist
+    from b200flow.ops import ref
+    from b200flow.parallel.ulysses import ulysses_attention
+
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    torch.manual_seed(0)
+    b, s, h, hkv, d = 2, 16, 4, 2, 8
+    q = torch.randn(b, s, h, d)
+    k = torch.randn(b, s, hkv, d)
+    v = torch.randn(b, s, hkv, d)
+    sl = s // world
+    qs = q[:, rank * sl:(rank + 1) * sl].clone().requires_grad_()
+    ks = k[:, rank * sl:(rank + 1) * sl].clone().requires_grad_()
+    vs = v[:, rank * sl:(rank + 1) * sl].clone().requires_grad_()
+    out = ulysses_attention(qs, ks, vs, dist.group.WORLD, causal=True)
+    qf, kf, vf = q.clone().requires_grad_(), k.clone().requires_grad_(), v.clone().requires_grad_()
+    full = ref.attention(qf, kf, vf, True)
+    w = torch.randn(b, s, h, d, generator=torch.Generator().manual_seed(3))
+    (out * w[:, rank * sl:(rank + 1) * sl]).sum().backward()
+    (full * w).sum().backward()
+    err_o = (out - full[:, rank * sl:(rank + 1) * sl]).abs().max().item()
+    err_q = (qs.grad - qf.grad[:, rank * sl:(rank + 1) * sl]).abs().max().item()
+    err_k = (ks.grad - kf.grad[:, rank * sl:(rank + 1) * sl]).abs().max().item()
+    q_out.put((rank, err_o, err_q, err_k))
+    dist.destroy_process_group()
+
+
+def test_ulysses_attention_matches_full_attention_gloo():
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q_out = ctx.Queue()
+    port = 29600 + (os.getpid() % 300)
+    procs = [ctx.Process(target=_ulysses_worker, args=(r, 2, port, q_out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q_out.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, eo, eq, ek in res:
+        assert eo < 1e-4 and eq < 1e-4 and ek < 1e-4, (rank, eo, eq, ek)
