@@ -99,6 +99,18 @@ static __device__ long long g_gemm2_dbg[8];
 //   wait_operands(b, mb128, nb)                     producer: rows of A for this block are ready
 //   select_a(def, mb128, m0) -> map                 producer: tensor map / row origin for A
 //   before_epilogue / store_chunk / tile_done       epilogue, as in the 1-CTA core
+// tile_done may take the Params (policies that store C themselves) or not
+template <class Policy>
+__device__ __forceinline__ auto tile_done_hook(const Policy& pol, const Params& p, int b, int mb128, int nb)
+    -> decltype(pol.tile_done(p, b, mb128, nb)) {
+  return pol.tile_done(p, b, mb128, nb);
+}
+template <class Policy>
+__device__ __forceinline__ auto tile_done_hook(const Policy& pol, const Params&, int b, int mb128, int nb)
+    -> decltype(pol.tile_done(b, mb128, nb)) {
+  return pol.tile_done(b, mb128, nb);
+}
+
 template <class Policy, int NST>
 __device__ __forceinline__ void gemm2_body(const CUtensorMap* tma_a_p, const CUtensorMap* tma_b_p,
                                            const Params& p, const Policy& pol, int first_pair,
@@ -265,7 +277,7 @@ __device__ __forceinline__ void gemm2_body(const CUtensorMap* tma_a_p, const CUt
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(map_to_cta(smem_u32(&ss->tmem_empty[as]), 0));
-      pol.tile_done(b, mb128, nb);
+      tile_done_hook(pol, p, b, mb128, nb);
     }
     pol.finish();
   }
@@ -279,14 +291,22 @@ __device__ __forceinline__ void gemm2_body(const CUtensorMap* tma_a_p, const CUt
   }
 }
 
-// Default policy: m-fastest tile order, operands always ready, ordinary epilogue.
+// Default policy: operands always ready, ordinary epilogue.  Tile order: m-fastest inside groups
+// of GROUP_M pair-tile rows, n next, groups last — the A rows of a group (GROUP_M x 256 x K) stay in
+// L2 while B streams past once per group, so neither operand is re-read from HBM when M is large.
 struct Plain2 {
+  static constexpr int GROUP_M = 8;
   __device__ __forceinline__ void map_tile(int t, int num_m, int num_n, int& b, int& mb, int& nb) const {
     const int per_batch = num_m * num_n;
     b = t / per_batch;
     const int r = t - b * per_batch;
-    nb = r / num_m;
-    mb = r - nb * num_m;
+    const int per_group = GROUP_M * num_n;
+    const int g = r / per_group;
+    const int m0 = g * GROUP_M;
+    const int gm = num_m - m0 < GROUP_M ? num_m - m0 : GROUP_M;   // rows in this (maybe last) group
+    const int rr = r - g * per_group;
+    nb = rr / gm;
+    mb = m0 + (rr - nb * gm);
   }
   __device__ __forceinline__ void wait_operands(int, int, int) const {}
   __device__ __forceinline__ const CUtensorMap* select_a(const CUtensorMap* def, int, int&) const { return def; }
@@ -297,6 +317,66 @@ struct Plain2 {
   }
   __device__ __forceinline__ void tile_done(int, int, int) const {}
   __device__ __forceinline__ void finish() const {}
+};
+
+// Same as Plain2, but a bf16 C tile leaves through shared memory and the TMA store path.  The
+// staging buffer is two 64-column blocks of [128 rows x 128 B] in the 128B-swizzle pattern
+// (conflict-free 16 B writes).  Each epilogue warp works on its own 32 rows: two 32-column chunks
+// fill a block, lane 0 issues one `cp.async.bulk.tensor` store for the warp's 32 x 64 box, and the
+// block is reused two chunks later once that store has read it (`wait_group.read 1`).  L2 then sees
+// whole-line writes instead of eight 16-byte partial-sector stores per row and chunk (ncu: half the
+// write sectors, an eighth of the write requests); partial tiles are clipped by the tensor map; and
+// 32 KB of staging leaves room for the full 6-stage operand ring.
+constexpr int STAGE_BLOCK = HALF * 128;           // one 64-column block: 128 rows x 128 B = 16 KB
+constexpr int STAGE_BYTES_2 = 2 * STAGE_BLOCK;    // 32 KB
+
+struct Staged2 : Plain2 {
+  uint8_t* staging;             // 1024-byte aligned
+  const CUtensorMap* map_c;     // [batch, M, N] bf16, box 64 cols x 32 rows, SWIZZLE_128B
+  __device__ __forceinline__ void issue_block(const Params& p, int b, int mb128, int n0_block, int blk) const {
+    asm volatile("fence.proxy.async;" ::: "memory");   // generic-proxy staging writes -> TMA reads
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) {
+      const int row0 = ((threadIdx.x >> 5) & 3) * 32;            // this warp's TMEM quarter
+      const int m0 = mb128 * HALF + row0;
+      if (m0 < p.M) tma_store_3d(map_c, staging + blk * STAGE_BLOCK + row0 * 128, n0_block, m0, b);
+      tma_store_commit();
+    }
+  }
+  __device__ __forceinline__ void before_epilogue(int, int, int) const {
+    if ((threadIdx.x & 31) == 0) tma_store_wait_read<0>();  // previous tile's blocks have left the buffer
+    __syncwarp();
+  }
+  __device__ __forceinline__ void store_chunk(const Params& p, int b, int mb128, int nb, int m, int n0,
+                                              const uint32_t (&acc)[32]) const {
+    const int c = (n0 - nb * T2_BN) >> 5;                       // 32-column chunk inside the tile
+    const int blk = (c >> 1) & 1;
+    if (c >= 4 && (c & 1) == 0) {
+      // this block was shipped two chunks ago: only the newer store may still be reading
+      if ((threadIdx.x & 31) == 0) tma_store_wait_read<1>();
+      __syncwarp();
+    }
+    if (m < p.M) {   // rows past M: whatever is in the staging buffer is clipped by the store
+      float v[32];
+      epilogue_values(p, b, m, n0, acc, v);
+      const int row = m - mb128 * HALF;
+      uint8_t* base = staging + blk * STAGE_BLOCK + row * 128;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        uint4 u;
+        u.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]); u.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
+        u.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]); u.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
+        const int j = ((c & 1) * 4 + q) ^ (row & 7);            // 128B swizzle: 16 B chunk ^= row % 8
+        *reinterpret_cast<uint4*>(base + j * 16) = u;
+      }
+    }
+    // second half of a block (or the last chunk of a tile whose width is an odd number of chunks)
+    if ((c & 1) == 1 || n0 + 32 >= p.N) issue_block(p, b, mb128, nb * T2_BN + (c >> 1) * 64, blk);
+  }
+  __device__ __forceinline__ void tile_done(int, int, int) const {}
+  __device__ __forceinline__ void finish() const {
+    if ((threadIdx.x & 31) == 0) tma_store_wait<0>();
+  }
 };
 
 }  // namespace gemm2

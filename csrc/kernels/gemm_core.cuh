@@ -90,13 +90,19 @@ __device__ __forceinline__ float gelu_tanh_grad(float x) {
 
 // Default policy: plain GEMM, row-major tile order (m fastest), no cross-GPU hooks.
 struct PlainPolicy {
+  static constexpr int GROUP_M = 16;  // 2048 rows of A stay in L2 while B streams past (see gemm2_core.cuh)
   __device__ __forceinline__ void map_tile(int t, int num_m, int num_n, int& b, int& mb,
                                            int& nb) const {
-    int per_batch = num_m * num_n;
+    const int per_batch = num_m * num_n;
     b = t / per_batch;
-    int r = t - b * per_batch;
-    nb = r / num_m;
-    mb = r - nb * num_m;
+    const int r = t - b * per_batch;
+    const int per_group = GROUP_M * num_n;
+    const int g = r / per_group;
+    const int m0 = g * GROUP_M;
+    const int gm = num_m - m0 < GROUP_M ? num_m - m0 : GROUP_M;
+    const int rr = r - g * per_group;
+    nb = rr / gm;
+    mb = m0 + (rr - nb * gm);
   }
   // Called by the producer lane before the first TMA of a tile.
   __device__ __forceinline__ void wait_operands(int, int, int) const {}
@@ -110,12 +116,10 @@ struct PlainPolicy {
   __device__ __forceinline__ void finish() const {}
 };
 
-// Store/convert one 32-column chunk of one accumulator row.
-__device__ __forceinline__ void epilogue_chunk(const Params& p, int b, int m, int n0,
-                                               const uint32_t (&acc)[32]) {
-  if (m >= p.M) return;
+// Epilogue arithmetic of one 32-column chunk of one accumulator row (everything but the C store).
+__device__ __forceinline__ void epilogue_values(const Params& p, int b, int m, int n0,
+                                                const uint32_t (&acc)[32], float (&v)[32]) {
   const int flags = p.flags;
-  float v[32];
 #pragma unroll
   for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(acc[i]) * p.alpha;
   const bool full = (n0 + 32 <= p.N);
@@ -195,6 +199,12 @@ __device__ __forceinline__ void epilogue_chunk(const Params& p, int b, int m, in
       for (int i = 0; i < 32; ++i) v[i] += r[i];
     }
   }
+}
+
+// C store of one chunk (bf16 or fp32, optional fp32 accumulate).
+__device__ __forceinline__ void epilogue_store(const Params& p, int b, int m, int n0, const float (&v)[32]) {
+  const int flags = p.flags;
+  const bool full = (n0 + 32 <= p.N);
   if (flags & EPI_OUT_F32) {
     float* cp = reinterpret_cast<float*>(p.C) + (long long)b * p.strideC + (long long)m * p.ldc + n0;
     if (full && ((p.ldc & 3) == 0)) {
@@ -227,6 +237,15 @@ __device__ __forceinline__ void epilogue_chunk(const Params& p, int b, int m, in
         if (n0 + i < p.N) cp[i] = __float2bfloat16(v[i]);
     }
   }
+}
+
+// Store/convert one 32-column chunk of one accumulator row.
+__device__ __forceinline__ void epilogue_chunk(const Params& p, int b, int m, int n0,
+                                               const uint32_t (&acc)[32]) {
+  if (m >= p.M) return;
+  float v[32];
+  epilogue_values(p, b, m, n0, acc, v);
+  epilogue_store(p, b, m, n0, v);
 }
 
 __device__ __forceinline__ void PlainPolicy::store_chunk(const Params& p, int b, int, int, int m,
