@@ -54,7 +54,6 @@ struct AttnParams {
 
 template <int D>
 struct Cfg {
-  static constexpr int CHUNKS = D / 64;
   static constexpr int TILE_B = TQ * D * 2;
 };
 
@@ -479,7 +478,7 @@ attn_delta_kernel(const __nv_bfloat16* __restrict__ O, long long o_ts, long long
 }
 
 // Backward kernels: 384 threads.  Warpgroup 0 = TMA warp + MMA warp; warpgroups 1 and 2 each take
-// 64 of the 128 columns of the score tile (one tile row per thread).  Both groups read their fp32
+// half of the columns of a score (half) tile, one tile row per thread.  Both groups read their fp32
 // columns of S / dP into registers, meet at a named barrier, and only then overwrite the front of
 // those TMEM regions with the bf16 P / dS operands.  The softmax scale is folded into the epilogue.
 constexpr int BWD_THREADS = 384;
@@ -490,15 +489,6 @@ struct BwdBars {
   alignas(128) float lse2[2][128];  // dkv kernel: per-stage statistics of the staged query tile
   alignas(128) float dlt[2][128];
 };
-
-__device__ __forceinline__ void load_cols64(uint32_t taddr, uint32_t (&r)[64]) {
-  tmem_ld_32x32b_x32(taddr, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
-  tmem_ld_32x32b_x32(taddr + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
-}
-__device__ __forceinline__ void store_cols32(uint32_t taddr, const uint32_t (&r)[32]) {
-  tmem_st_32x32b_x16(taddr, *reinterpret_cast<const uint32_t(*)[16]>(&r[0]));
-  tmem_st_32x32b_x16(taddr + 16, *reinterpret_cast<const uint32_t(*)[16]>(&r[16]));
-}
 
 // Accumulator rows -> bf16 global rows; the two compute warpgroups split the D columns.
 template <int D>
@@ -523,9 +513,14 @@ __device__ __forceinline__ void store_acc_half(uint32_t taddr, __nv_bfloat16* ro
   }
 }
 
-// ---- dQ: CTA per (q tile, head, batch); loops over key tiles.  TMEM: S double-buffered
-// [0,256), dP / dS [256,384), dQ [384,384+D): S(j+1) = Q K^T runs while the compute groups are
-// still busy with tile j.
+// Both backward kernels work on half score tiles (128 rows x 64 columns) so that two of them fit
+// next to the accumulators and the loop is software-pipelined: while the compute groups turn half h
+// into its bf16 operands, the tensor core already produces S / dP of half h+1 in the other buffer,
+// and the accumulate MMAs of half h follow as soon as its operands are stored.
+//   TMEM: buffer b = columns [128 b, 128 b + 128): S half at +0, dP half at +64; the bf16 operands
+//   overwrite the front of S / dP (32 columns each).
+
+// ---- dQ: CTA per (q tile, head, batch); loops over key half-tiles.  dQ accumulates at [256, 256+D).
 template <int D>
 __global__ void __launch_bounds__(BWD_THREADS, 1)
 attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
@@ -551,6 +546,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant
   int kv_end = p.causal ? (kv_len < q0 + TQ ? kv_len : q0 + TQ) : kv_len;
   int n = (kv_end + TQ - 1) / TQ;
   if (n < 1) n = 1;
+  const int H2 = 2 * n;  // half tiles
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&mq); tma_prefetch_desc(&mk); tma_prefetch_desc(&mv); tma_prefetch_desc(&mdo);
@@ -560,7 +556,6 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant
       mbar_init(&bars->st_empty[i], 1);
       mbar_init(&bars->s_full[i], 1);
     }
-    mbar_init(&bars->dp_full, 1);
     mbar_init(&bars->ds_full, 256);
     mbar_init(&bars->acc_full, 1);
     fence_mbar_init();
@@ -570,7 +565,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant
   __syncthreads();
   tc_fence_after();
   require_tmem_base0(bars->tmem_base);
-  constexpr uint32_t T_S = 0, T_DP = 256, T_DQ = 384;
+  constexpr uint32_t T_DQ = 256;
 
   if (warp < 4) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
@@ -586,59 +581,50 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant
         load_tile<D>(sV + st * TILE_B, &mv, &bars->st_full[st], j * TQ, hkv, b);
       }
     } else if (warp == 1) {
-      const uint32_t idesc_s = make_idesc(1, 1, 128, 128, 0, 0);
+      const uint32_t idesc_s = make_idesc(1, 1, 128, 64, 0, 0);
       const uint32_t idesc_dq = make_idesc(1, 1, 128, D, 0, 1);
       const uint32_t aQ = lo_k(smem_u32(sQ)), adO = lo_k(smem_u32(sdO));
-      auto issue_s = [&](int j) {
-        const int st = j & 1;
-        const uint32_t aK = lo_k(smem_u32(sK + st * TILE_B));
-        if (elect_one()) {
-#pragma unroll
-          for (int k = 0; k < D / 16; ++k)
-            umma_f16_ss(T_S + st * 128, desc_k(aQ, k), desc_k(aK, k), idesc_s, k > 0);
-          umma_commit(&bars->s_full[st]);
+      // S_h = Q K_h^T and dP_h = dO V_h^T for key half hh (64 keys = rows [64 half, +64) of the stage)
+      auto issue_sdp = [&](int hh) {
+        const int j = hh >> 1, half = hh & 1, st = j & 1;
+        if (half == 0) {
+          mbar_wait(&bars->st_full[st], (j >> 1) & 1);
+          tc_fence_after();
         }
-        __syncwarp();
-      };
-      auto issue_dp = [&](int j) {
-        const uint32_t aV = lo_k(smem_u32(sV + (j & 1) * TILE_B));
+        const uint32_t aK = lo_k(smem_u32(sK + st * TILE_B + half * 8192));
+        const uint32_t aV = lo_k(smem_u32(sV + st * TILE_B + half * 8192));
+        const uint32_t tb = (hh & 1) * 128;
         if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < D / 16; ++k)
-            umma_f16_ss(T_DP, desc_k(adO, k), desc_k(aV, k), idesc_s, k > 0);
-          umma_commit(&bars->dp_full);
+          for (int k = 0; k < D / 16; ++k) umma_f16_ss(tb, desc_k(aQ, k), desc_k(aK, k), idesc_s, k > 0);
+#pragma unroll
+          for (int k = 0; k < D / 16; ++k) umma_f16_ss(tb + 64, desc_k(adO, k), desc_k(aV, k), idesc_s, k > 0);
+          umma_commit(&bars->s_full[hh & 1]);
         }
         __syncwarp();
       };
       mbar_wait(&bars->fixed_full, 0);
-      mbar_wait(&bars->st_full[0], 0);
-      tc_fence_after();
-      issue_s(0);
-      issue_dp(0);
-      for (int j = 0; j < n; ++j) {
-        const int st = j & 1;
-        if (j + 1 < n) {
-          mbar_wait(&bars->st_full[st ^ 1], ((j + 1) >> 1) & 1);
-          tc_fence_after();
-          issue_s(j + 1);
-        }
-        mbar_wait(&bars->ds_full, j & 1);
+      issue_sdp(0);
+      for (int hh = 0; hh < H2; ++hh) {
+        const int j = hh >> 1, half = hh & 1, st = j & 1;
+        if (hh + 1 < H2) issue_sdp(hh + 1);
+        mbar_wait(&bars->ds_full, hh & 1);
         tc_fence_after();
         const uint32_t aK = lo_mn(smem_u32(sK + st * TILE_B));
+        const uint32_t tds = (hh & 1) * 128 + 64;
         if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < TQ / 16; ++k)
-            umma_f16_ts(T_DQ, T_DP + k * 8, desc_mn(aK, k), idesc_dq, (j | k) != 0);
-          umma_commit(&bars->st_empty[st]);
-          if (j + 1 == n) umma_commit(&bars->acc_full);
+          for (int k = 0; k < 4; ++k)
+            umma_f16_ts(T_DQ, tds + k * 8, desc_mn(aK, half * 4 + k), idesc_dq, (hh | k) != 0);
+          if (half == 1) umma_commit(&bars->st_empty[st]);
+          if (hh + 1 == H2) umma_commit(&bars->acc_full);
         }
         __syncwarp();
-        if (j + 1 < n) issue_dp(j + 1);
       }
     }
   } else {
     asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
-    const int cg = (warp - 4) >> 2;  // column group: score columns [cg*64, cg*64+64)
+    const int cg = (warp - 4) >> 2;  // column group: 32 of the 64 key columns of a half tile
     const int qw = warp & 3;
     const int r = qw * 32 + lane;
     const int qi = q0 + r;
@@ -648,26 +634,27 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant
     const float nlse2 = p.delta[sidx];
     const float ndlt = p.delta[(long long)p.B * p.H * S_pad + sidx];
     const uint64_t sc2 = f2pack(p.scale_log2, p.scale_log2), nl2 = f2pack(nlse2, nlse2), nd2 = f2pack(ndlt, ndlt);
-    for (int j = 0; j < n; ++j) {
-      const int kv0 = j * TQ;
+    for (int hh = 0; hh < H2; ++hh) {
+      const int kv0 = hh * 64 + cg * 32;  // first key column of this thread's 32
+      const uint32_t tb = lane_base + (hh & 1) * 128;
       DBG_T(tq0);
-      mbar_wait(&bars->s_full[j & 1], (j >> 1) & 1);
-      mbar_wait(&bars->dp_full, j & 1);
+      mbar_wait(&bars->s_full[hh & 1], (hh >> 1) & 1);
       tc_fence_after();
       DBG_T(tq1);
-      uint32_t sa[64], da[64];
-      load_cols64(T_S + lane_base + (j & 1) * 128 + cg * 64, sa);
-      load_cols64(T_DP + lane_base + cg * 64, da);
+      uint32_t sa[32], da[32];
+      tmem_ld_32x32b_x32(tb + cg * 32, sa);
+      tmem_ld_32x32b_x32(tb + 64 + cg * 32, da);
       tmem_ld_wait();
       tc_fence_before();
       named_bar_sync(2, 256);  // every fp32 dP column is in registers: dS may now overwrite them
       tc_fence_after();
       DBG_T(tq2);
-      const bool need_mask = (p.causal && kv0 + TQ - 1 > q0) || (kv0 + TQ > kv_len);
-      uint32_t pk[32];
+      const int kvh0 = hh * 64;
+      const bool need_mask = (p.causal && kvh0 + 63 > q0) || (kvh0 + 64 > kv_len);
+      uint32_t pk[16];
       if (!need_mask) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
+        for (int i = 0; i < 16; ++i) {
           const uint64_t t = fma2(f2pack(__uint_as_float(sa[2 * i]), __uint_as_float(sa[2 * i + 1])), sc2, nl2);
           float t0, t1;
           f2unpack(t, t0, t1);
@@ -679,9 +666,9 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant
       } else {
         int lim = kv_len;
         if (p.causal && qi + 1 < lim) lim = qi + 1;
-        lim -= kv0 + cg * 64;  // first masked column among this thread's 64
+        lim -= kv0;  // first masked column among this thread's 32
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
+        for (int i = 0; i < 16; ++i) {
           const uint64_t t = fma2(f2pack(__uint_as_float(sa[2 * i]), __uint_as_float(sa[2 * i + 1])), sc2, nl2);
           float t0, t1;
           f2unpack(t, t0, t1);
@@ -693,7 +680,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant
           pk[i] = pack_bf16x2(d0, d1);
         }
       }
-      store_cols32(T_DP + lane_base + cg * 32, pk);
+      tmem_st_32x32b_x16(tb + 64 + cg * 16, pk);
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(&bars->ds_full);
@@ -714,9 +701,10 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant
   if (warp == 1) { tc_fence_after(); tmem_dealloc(0, 512); }
 }
 
-// ---- dK/dV: CTA per (key tile, kv head, batch); loops over the query heads of the group and
-// over query tiles.  TMEM: S^T [0,128) -> P^T, dP^T [128,256) -> dS^T, dV [256,..), dK [384,..).
-// The TMA warp also stages each query tile's lse2 / dlt rows (two 512 B bulk copies).
+// ---- dK/dV: CTA per (key tile, kv head, batch); loops over the query heads of the group and over
+// query half-tiles (S^T formulation: rows = keys, columns = 64 queries, so P^T / dS^T are TMEM
+// A-operands).  dV accumulates at [256, 256+D), dK at [384, 384+D).  The TMA warp also stages each
+// query tile's -lse2 / -delta rows (two 512 B bulk copies).
 template <int D>
 __global__ void __launch_bounds__(BWD_THREADS, 1)
 attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
@@ -742,13 +730,17 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constan
   const int i0 = p.causal ? kv_tile : 0;
   const int per_head = nq - i0;
   const int n = per_head * G;
+  const int H2 = 2 * n;
   const int S_pad = nq * TQ;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&mq); tma_prefetch_desc(&mk); tma_prefetch_desc(&mv); tma_prefetch_desc(&mdo);
     mbar_init(&bars->fixed_full, 1);
-    for (int i = 0; i < 2; ++i) { mbar_init(&bars->st_full[i], 1); mbar_init(&bars->st_empty[i], 1); }
-    mbar_init(&bars->s_full[0], 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bars->st_full[i], 1);
+      mbar_init(&bars->st_empty[i], 1);
+      mbar_init(&bars->s_full[i], 1);
+    }
     mbar_init(&bars->ds_full, 256);
     mbar_init(&bars->acc_full, 1);
     fence_mbar_init();
@@ -758,7 +750,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constan
   __syncthreads();
   tc_fence_after();
   require_tmem_base0(bars->tmem_base);
-  constexpr uint32_t T_S = 0, T_DP = 128, T_DV = 256, T_DK = 384;
+  constexpr uint32_t T_DV = 256, T_DK = 384;
 
   if (warp < 4) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
@@ -779,78 +771,86 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constan
         bulk_load_1d(bars->dlt[st], stats + (long long)p.B * p.H * S_pad, TQ * 4, &bars->st_full[st]);
       }
     } else if (warp == 1) {
-      const uint32_t idesc_s = make_idesc(1, 1, 128, 128, 0, 0);
+      const uint32_t idesc_s = make_idesc(1, 1, 128, 64, 0, 0);
       const uint32_t idesc_acc = make_idesc(1, 1, 128, D, 0, 1);
       const uint32_t aK = lo_k(smem_u32(sK)), aV = lo_k(smem_u32(sV));
-      auto issue_sdp = [&](int it) {
-        const int st = it & 1;
-        mbar_wait(&bars->st_full[st], (it >> 1) & 1);
-        tc_fence_after();
-        const uint32_t aQ = lo_k(smem_u32(sQ + st * TILE_B)), adO = lo_k(smem_u32(sdO + st * TILE_B));
+      // S^T_h = K Q_h^T and dP^T_h = V dO_h^T for query half hh (rows [64 half, +64) of the stage)
+      auto issue_sdp = [&](int hh) {
+        const int it = hh >> 1, half = hh & 1, st = it & 1;
+        if (half == 0) {
+          mbar_wait(&bars->st_full[st], (it >> 1) & 1);
+          tc_fence_after();
+        }
+        const uint32_t aQ = lo_k(smem_u32(sQ + st * TILE_B + half * 8192));
+        const uint32_t adO = lo_k(smem_u32(sdO + st * TILE_B + half * 8192));
+        const uint32_t tb = (hh & 1) * 128;
         if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < D / 16; ++k) umma_f16_ss(T_S, desc_k(aK, k), desc_k(aQ, k), idesc_s, k > 0);
+          for (int k = 0; k < D / 16; ++k) umma_f16_ss(tb, desc_k(aK, k), desc_k(aQ, k), idesc_s, k > 0);
 #pragma unroll
-          for (int k = 0; k < D / 16; ++k) umma_f16_ss(T_DP, desc_k(aV, k), desc_k(adO, k), idesc_s, k > 0);
-          umma_commit(&bars->s_full[0]);
+          for (int k = 0; k < D / 16; ++k) umma_f16_ss(tb + 64, desc_k(aV, k), desc_k(adO, k), idesc_s, k > 0);
+          umma_commit(&bars->s_full[hh & 1]);
         }
         __syncwarp();
       };
       mbar_wait(&bars->fixed_full, 0);
-      if (n > 0) issue_sdp(0);
-      for (int it = 0; it < n; ++it) {
-        const int st = it & 1;
-        mbar_wait(&bars->ds_full, it & 1);
+      if (H2 > 0) issue_sdp(0);
+      for (int hh = 0; hh < H2; ++hh) {
+        const int it = hh >> 1, half = hh & 1, st = it & 1;
+        if (hh + 1 < H2) issue_sdp(hh + 1);
+        mbar_wait(&bars->ds_full, hh & 1);
         tc_fence_after();
         const uint32_t aQ = lo_mn(smem_u32(sQ + st * TILE_B)), adO = lo_mn(smem_u32(sdO + st * TILE_B));
+        const uint32_t tb = (hh & 1) * 128;
         if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < TQ / 16; ++k)
-            umma_f16_ts(T_DV, T_S + k * 8, desc_mn(adO, k), idesc_acc, (it | k) != 0);
+          for (int k = 0; k < 4; ++k)
+            umma_f16_ts(T_DV, tb + k * 8, desc_mn(adO, half * 4 + k), idesc_acc, (hh | k) != 0);
 #pragma unroll
-          for (int k = 0; k < TQ / 16; ++k)
-            umma_f16_ts(T_DK, T_DP + k * 8, desc_mn(aQ, k), idesc_acc, (it | k) != 0);
-          umma_commit(&bars->st_empty[st]);
-          if (it + 1 == n) umma_commit(&bars->acc_full);
+          for (int k = 0; k < 4; ++k)
+            umma_f16_ts(T_DK, tb + 64 + k * 8, desc_mn(aQ, half * 4 + k), idesc_acc, (hh | k) != 0);
+          if (half == 1) umma_commit(&bars->st_empty[st]);
+          if (hh + 1 == H2) umma_commit(&bars->acc_full);
         }
         __syncwarp();
-        if (it + 1 < n) issue_sdp(it + 1);
       }
     }
   } else {
     asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
-    const int cg = (warp - 4) >> 2;  // column group: query columns [cg*64, cg*64+64) of the S^T tile
+    const int cg = (warp - 4) >> 2;  // column group: 32 of the 64 query columns of a half tile
     const int qw = warp & 3;
     const int r = qw * 32 + lane;
     const int ki = kv0 + r;
     const uint32_t lane_base = static_cast<uint32_t>(qw * 32) << 16;
     const bool row_dead = ki >= kv_len;
     const uint64_t sc2 = f2pack(p.scale_log2, p.scale_log2);
-    for (int it = 0; it < n; ++it) {
-      const int st = it & 1;
+    for (int hh = 0; hh < H2; ++hh) {
+      const int it = hh >> 1, half = hh & 1, st = it & 1;
       const int i = i0 + it % per_head;
-      const int q0 = i * TQ;
+      const int qh0 = i * TQ + half * 64;      // first query of this half tile
+      const uint32_t tb = lane_base + (hh & 1) * 128;
       DBG_T(tk0);
-      mbar_wait(&bars->st_full[st], (it >> 1) & 1);  // lse2 / dlt rows of this query tile are staged
-      mbar_wait(&bars->s_full[0], it & 1);
+      if (half == 0) mbar_wait(&bars->st_full[st], (it >> 1) & 1);  // statistics of this query tile are staged
+      mbar_wait(&bars->s_full[hh & 1], (hh >> 1) & 1);
       tc_fence_after();
       DBG_T(tk1);
-      uint32_t sa[64], da[64];
-      load_cols64(T_S + lane_base + cg * 64, sa);
-      load_cols64(T_DP + lane_base + cg * 64, da);
+      uint32_t sa[32], da[32];
+      tmem_ld_32x32b_x32(tb + cg * 32, sa);
+      tmem_ld_32x32b_x32(tb + 64 + cg * 32, da);
       tmem_ld_wait();
       tc_fence_before();
       named_bar_sync(2, 256);
       tc_fence_after();
       DBG_T(tk2);
-      const bool need_mask = (p.causal && q0 < kv0 + TQ - 1) || (kv0 + TQ > kv_len);
-      // causal: query column c is visible to key row ki iff q0 + c >= ki
-      const int first_ok = row_dead ? 128 : (p.causal ? ki - q0 - cg * 64 : 0);
-      const uint32_t l_addr = smem_u32(&bars->lse2[st][cg * 64]), d_addr = smem_u32(&bars->dlt[st][cg * 64]);
-      uint32_t pp[32], pd[32];
+      const bool need_mask = (p.causal && qh0 < kv0 + TQ - 1) || (kv0 + TQ > kv_len);
+      // causal: query column c is visible to key row ki iff qh0 + cg*32 + c >= ki
+      const int first_ok = row_dead ? 64 : (p.causal ? ki - qh0 - cg * 32 : 0);
+      const uint32_t l_addr = smem_u32(&bars->lse2[st][half * 64 + cg * 32]);
+      const uint32_t d_addr = smem_u32(&bars->dlt[st][half * 64 + cg * 32]);
+      uint32_t pp[16], pd[16];
       if (!need_mask) {
 #pragma unroll
-        for (int i4 = 0; i4 < 16; ++i4) {
+        for (int i4 = 0; i4 < 8; ++i4) {
           const ulonglong2 nl = lds_v2_u64(l_addr + i4 * 16), nd = lds_v2_u64(d_addr + i4 * 16);
 #pragma unroll
           for (int e = 0; e < 2; ++e) {
@@ -868,7 +868,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constan
         }
       } else {
 #pragma unroll
-        for (int i4 = 0; i4 < 16; ++i4) {
+        for (int i4 = 0; i4 < 8; ++i4) {
           const ulonglong2 nl = lds_v2_u64(l_addr + i4 * 16), nd = lds_v2_u64(d_addr + i4 * 16);
 #pragma unroll
           for (int e = 0; e < 2; ++e) {
@@ -886,8 +886,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constan
           }
         }
       }
-      store_cols32(T_S + lane_base + cg * 32, pp);
-      store_cols32(T_DP + lane_base + cg * 32, pd);
+      tmem_st_32x32b_x16(tb + cg * 16, pp);
+      tmem_st_32x32b_x16(tb + 64 + cg * 16, pd);
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(&bars->ds_full);
