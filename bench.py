@@ -5,7 +5,9 @@ BASELINE.json config 4: Llama-2 7B, bf16, ZeRO-1, tensor + sequence + pipeline
 parallelism — TP=2 x PP=2 x DP=2 on 8 GPUs; the 1/2/4-GPU points use the largest
 sub-topology (tp1 -> tp2 -> tp2.pp2), as BASELINE.md §3 specifies.  Synthetic token
 streams, random-init weights (no network here).  `--workload bert-large` measures
-BASELINE.json config 2 (BERT-large pre-training samples/s, DDP) instead.
+BASELINE.json config 2 (BERT-large pre-training samples/s, DDP), `--workload maskrcnn` config 3
+(Mask R-CNN R50-FPN images/s, DDP), `--workload gpt-moe-1.3b` config 5 (fp8 experts, EP = #GPUs);
+`--impl twin` runs the stock-library arm (torch nn + cuBLAS + SDPA + torch DDP).
 
 Contract (see the task statement): W untimed warm-up steps, then exactly K steps
 timed on the device with CUDA events between barrier+synchronize pairs, max over
@@ -126,6 +128,11 @@ def main():
         from b200flow.workloads.twin import run_twin
 
         return run_twin(args, rank, world, dev, ClockSampler)
+
+    if args.workload.startswith("maskrcnn"):
+        from b200flow.workloads.bench_maskrcnn import run_maskrcnn_bench
+
+        return run_maskrcnn_bench(args, rank, world, dev, ClockSampler)
 
     if args.workload.startswith("bert"):
         from b200flow.workloads.bench_bert import run_bert_bench

@@ -82,3 +82,7 @@ def test_smoke_entry():
     import __graft_entry__ as g
 
     g.smoke()
+
+
+def test_gemm_cta_pair_kernel():
+    _run("gemm2")
