@@ -41,10 +41,11 @@ def parse_args():
     ap.add_argument("--workload", default="llama2-7b")
     ap.add_argument("--seq", type=int, default=4096)
     ap.add_argument("--micro-batch", type=int, default=1)
-    ap.add_argument("--gas", type=int, default=8)
+    ap.add_argument("--gas", type=int, default=16)
     ap.add_argument("--no-fused", action="store_true", help="NCCL collectives instead of fused kernels")
     ap.add_argument("--tp", type=int, default=0, help="override the tensor-parallel size")
     ap.add_argument("--pp", type=int, default=0, help="override the pipeline-parallel size")
+    ap.add_argument("--profile", default="", help="write a torch.profiler kernel table of one extra step to this file")
     return ap.parse_args()
 
 
@@ -223,6 +224,16 @@ def main():
 
     e2e_step()
     ms_e2e = timed(e2e_step, args.steps)
+    if args.profile:   # after the timed regions: per-kernel device time of one step (rank 0's view)
+        from torch.profiler import ProfilerActivity, profile
+
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            engine.train_batch(it_dev)
+            torch.cuda.synchronize()
+        if rank == 0:
+            Path(args.profile).parent.mkdir(parents=True, exist_ok=True)
+            Path(args.profile).write_text(prof.key_averages().table(sort_by="cuda_time_total", row_limit=40,
+                                                                     max_name_column_width=90))
     if rank == 0:
         val = tokens_per_step * args.steps / (ms / 1e3)
         val_e2e = tokens_per_step * args.steps / (ms_e2e / 1e3)

@@ -56,6 +56,18 @@ b2f_gemm2_bf16_staged_kernel(const __grid_constant__ CUtensorMap tma_a, const __
   gemm2_body<Staged2, STAGED_STAGES>(&tma_a, &tma_b, p, pol, blockIdx.x >> 1, gridDim.x >> 1, smem_raw);
 }
 
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+b2f_gemm2_f32_staged_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                            const __grid_constant__ CUtensorMap tma_c, const Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  StagedF32 pol;
+  pol.staging = smem + STAGED_STAGES * ST2_BYTES + 1024;
+  pol.map_c = &tma_c;
+  gemm2_body<StagedF32, STAGED_STAGES>(&tma_a, &tma_b, p, pol, blockIdx.x >> 1, gridDim.x >> 1, smem_raw);
+}
+
 // Same kernel with a 4-deep ring (what the fused GEMM->reduce-scatter kernel can afford next to its
 // staging buffer); exposed so its cost can be measured in isolation (B2F_GEMM2_STAGES=4).
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
@@ -103,7 +115,20 @@ extern "C" int b2f_gemm_bf16_2cta(const void* A, const void* B, void* C, int M, 
   static const bool s4 = [] { const char* e = getenv("B2F_GEMM2_STAGES"); return e && e[0] == '4'; }();
   static const bool direct = [] { const char* e = getenv("B2F_GEMM2_EPI"); return e && e[0] == 'd'; }();
   const bool can_stage = !(flags & EPI_OUT_F32) && (ldc % 8 == 0) && (N % 8 == 0) && (strideC % 8 == 0);
-  if (can_stage && !direct && !s4) {
+  const bool can_stage_f32 = (flags & EPI_OUT_F32) && (ldc % 4 == 0) && (N % 4 == 0) && (strideC % 4 == 0);
+  if (can_stage_f32 && !direct && !s4) {
+    static bool f32_attr[64] = {false};
+    if (!f32_attr[dev & 63]) {
+      B2F_CHECK_CUDA(cudaFuncSetAttribute(b2f_gemm2_f32_staged_kernel,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, STAGED_SMEM));
+      f32_attr[dev & 63] = true;
+    }
+    CUtensorMap mc;
+    if (int rc = make_tma_3d(&mc, C, TmaDtype::F32, batch, M, N, batch > 1 ? strideC : (long long)M * ldc, ldc,
+                             32, 32, 128)) return rc;
+    // the reducing store needs the accumulate flag out of the per-element epilogue: values only
+    b2f_gemm2_f32_staged_kernel<<<pairs * 2, NUM_THREADS, STAGED_SMEM, static_cast<cudaStream_t>(stream)>>>(ma, mb, mc, p);
+  } else if (can_stage && !direct && !s4) {
     static bool staged_attr[64] = {false};
     if (!staged_attr[dev & 63]) {
       B2F_CHECK_CUDA(cudaFuncSetAttribute(b2f_gemm2_bf16_staged_kernel,

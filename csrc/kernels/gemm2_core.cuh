@@ -379,5 +379,51 @@ struct Staged2 : Plain2 {
   }
 };
 
+// fp32 C through the same staging buffer: one 32-column chunk (128 B of fp32 per row) is one
+// staging block, shipped per warp as a 32 x 32 box with a plain tensor store or — for the wgrad
+// `C +=` — a reducing tensor store (`cp.reduce.async.bulk.tensor ... .add`), so main_grad is never
+// read by the SM and L2 sees whole-line updates.
+struct StagedF32 : Plain2 {
+  uint8_t* staging;             // 1024-byte aligned, 2 blocks of [128 rows x 128 B]
+  const CUtensorMap* map_c;     // [batch, M, N] fp32, box 32 cols x 32 rows, SWIZZLE_128B
+  __device__ __forceinline__ void before_epilogue(int, int, int) const {
+    if ((threadIdx.x & 31) == 0) tma_store_wait_read<0>();
+    __syncwarp();
+  }
+  __device__ __forceinline__ void store_chunk(const Params& p, int b, int mb128, int nb, int m, int n0,
+                                              const uint32_t (&acc)[32]) const {
+    const int c = (n0 - nb * T2_BN) >> 5;
+    const int blk = c & 1;
+    if (c >= 2) {   // this block was shipped two chunks ago: only the newer store may still be reading
+      if ((threadIdx.x & 31) == 0) tma_store_wait_read<1>();
+      __syncwarp();
+    }
+    if (m < p.M) {
+      float v[32];
+      epilogue_values(p, b, m, n0, acc, v);
+      const int row = m - mb128 * HALF;
+      uint8_t* base = staging + blk * STAGE_BLOCK + row * 128;
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+        *reinterpret_cast<float4*>(base + ((q ^ (row & 7)) * 16)) = make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
+    }
+    asm volatile("fence.proxy.async;" ::: "memory");
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) {
+      const int row0 = ((threadIdx.x >> 5) & 3) * 32;
+      const int m0 = mb128 * HALF + row0;
+      if (m0 < p.M) {
+        if (p.flags & EPI_ACCUM) tma_reduce_add_3d(map_c, staging + blk * STAGE_BLOCK + row0 * 128, n0, m0, b);
+        else tma_store_3d(map_c, staging + blk * STAGE_BLOCK + row0 * 128, n0, m0, b);
+      }
+      tma_store_commit();
+    }
+  }
+  __device__ __forceinline__ void tile_done(int, int, int) const {}
+  __device__ __forceinline__ void finish() const {
+    if ((threadIdx.x & 31) == 0) tma_store_wait<0>();
+  }
+};
+
 }  // namespace gemm2
 }  // namespace b2f

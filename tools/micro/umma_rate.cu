@@ -11,6 +11,7 @@ __device__ __forceinline__ uint64_t mk_desc(uint32_t lo) {
 }
 extern __shared__ uint8_t sm_raw[];
 // MODE 0: SS K-major A,B.  MODE 1: TS (A in TMEM), B MN-major.  MODE 2: SS with A K-major, B MN-major
+// MODE 3: SS with A and B MN-major (the wgrad form)
 template <int MODE, int N>
 __global__ void __launch_bounds__(128, 1) rate_kernel(int iters, long long* out) {
   __shared__ uint64_t bar;
@@ -25,6 +26,8 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(int iters, long long* out)
     const uint32_t b = ((smem_u32(sm + 65536) & 0x3FFFF) >> 4) | (1u << 16);
     const uint32_t bmn = ((smem_u32(sm + 65536) & 0x3FFFF) >> 4) | (1024u << 16);
     const uint32_t idesc_kk = make_idesc(1, 1, 128, N, 0, 0), idesc_kmn = make_idesc(1, 1, 128, N, 0, 1);
+    const uint32_t idesc_mnmn = make_idesc(1, 1, 128, N, 1, 1);
+    const uint32_t amn = ((smem_u32(sm) & 0x3FFFF) >> 4) | (512u << 16);   // LBO = 8 KB chunk stride
     long long t0 = clock64();
     for (int it = 0; it < iters; ++it) {
       if (elect_one()) {
@@ -33,6 +36,7 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(int iters, long long* out)
           if (MODE == 0) umma_f16_ss(256 * (it & 1), mk_desc(a + (k >> 2) * 1024 + (k & 3) * 2), mk_desc(b + (k >> 2) * 1024 * (N / 128 > 0 ? N / 128 : 1) + (k & 3) * 2), idesc_kk, k > 0);
           if (MODE == 1) umma_f16_ts(256, 0 + k * 8, mk_desc(bmn + k * 128), idesc_kmn, k > 0);
           if (MODE == 2) umma_f16_ss(256 * (it & 1), mk_desc(a + (k >> 2) * 1024 + (k & 3) * 2), mk_desc(bmn + k * 128), idesc_kmn, k > 0);
+          if (MODE == 3) umma_f16_ss(256 * (it & 1), mk_desc(amn + (k & 3) * 128), mk_desc(bmn + (k & 3) * 128), idesc_mnmn, k > 0);
         }
       }
       __syncwarp();
@@ -65,6 +69,8 @@ int main() {
   run<0, 256>("SS  A,B K-major", d_out);
   run<2, 128>("SS  A K-major, B MN-major", d_out);
   run<2, 256>("SS  A K-major, B MN-major", d_out);
+  run<3, 128>("SS  A,B MN-major", d_out);
+  run<3, 256>("SS  A,B MN-major", d_out);
   run<1, 64>("TS  A in TMEM, B MN-major", d_out);
   run<1, 128>("TS  A in TMEM, B MN-major", d_out);
   run<1, 256>("TS  A in TMEM, B MN-major", d_out);
