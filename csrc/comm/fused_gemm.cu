@@ -104,13 +104,15 @@ struct AGPolicy {
     wait_ge_gpu(tile_flags + mb, epoch);
     asm volatile("fence.proxy.async;" ::: "memory");  // generic-proxy copy -> TMA (async proxy) read
   }
-  __device__ __forceinline__ void before_epilogue(int, int, int) const {}
-  __device__ __forceinline__ void store_chunk(const Params& p, int b, int, int, int m, int n0,
+  // C leaves through the swizzled staging buffer and TMA tensor stores (see gemm2::Staged2)
+  gemm2::Staged2 out;
+  __device__ __forceinline__ void before_epilogue(int b, int mb128, int nb) const { out.before_epilogue(b, mb128, nb); }
+  __device__ __forceinline__ void store_chunk(const Params& p, int b, int mb128, int nb, int m, int n0,
                                               const uint32_t (&acc)[32]) const {
-    epilogue_chunk(p, b, m, n0, acc);
+    out.store_chunk(p, b, mb128, nb, m, n0, acc);
   }
   __device__ __forceinline__ void tile_done(int, int, int) const {}
-  __device__ __forceinline__ void finish() const {}
+  __device__ __forceinline__ void finish() const { out.finish(); }
 };
 
 // Gather role: one thread per comm CTA drives the copy engine.  A 128-row block of a shard
@@ -247,24 +249,31 @@ struct AG2Policy {
     m0 -= rank * blocks_per_rank * BM;
     return own_map;
   }
-  __device__ __forceinline__ void before_epilogue(int, int, int) const {}
-  __device__ __forceinline__ void store_chunk(const Params& p, int b, int, int, int m, int n0,
+  // C leaves through the swizzled staging buffer and TMA tensor stores (see gemm2::Staged2)
+  gemm2::Staged2 out;
+  __device__ __forceinline__ void before_epilogue(int b, int mb128, int nb) const { out.before_epilogue(b, mb128, nb); }
+  __device__ __forceinline__ void store_chunk(const Params& p, int b, int mb128, int nb, int m, int n0,
                                               const uint32_t (&acc)[32]) const {
-    epilogue_chunk(p, b, m, n0, acc);
+    out.store_chunk(p, b, mb128, nb, m, n0, acc);
   }
   __device__ __forceinline__ void tile_done(int, int, int) const {}
-  __device__ __forceinline__ void finish() const {}
+  __device__ __forceinline__ void finish() const { out.finish(); }
 };
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 b2f_ag_gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_own,
-                    const __grid_constant__ CUtensorMap tma_b, const Params p, const AGArgs a) {
+                    const __grid_constant__ CUtensorMap tma_b, const __grid_constant__ CUtensorMap tma_c,
+                    const Params p, const AGArgs a) {
   extern __shared__ uint8_t smem_raw[];
   if ((int)blockIdx.x < a.comm_ctas) {   // comm_ctas is even: whole clusters
     ag_comm_role(a, smem_raw);
     return;
   }
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
   AG2Policy pol{a.tile_flags, &tma_own, a.epoch, a.rank, a.rows_per_rank / BM};
+  pol.out.staging = smem + gemm2::S2 * gemm2::ST2_BYTES + 1024;
+  pol.out.map_c = &tma_c;
   gemm2::gemm2_body<AG2Policy, gemm2::S2>(&tma_a, &tma_b, p, pol, ((int)blockIdx.x - a.comm_ctas) >> 1,
                                           ((int)gridDim.x - a.comm_ctas) >> 1, smem_raw);
 }
@@ -291,6 +300,8 @@ struct RSPolicy {
   RSArgs a;
   int blocks_per_rank, num_n;
   uint8_t* staging;
+  __nv_bfloat16* out;   // local output shard [Ts, N] and its row pitch (elements)
+  long long ldo;
   // the flag of a shipped tile is published one tile later (its bulk copies have long landed by
   // then), so the epilogue never sits out an NVLink round trip
   mutable int pend_owner = -1, pend_mb_local = 0, pend_nb = 0;
@@ -311,7 +322,10 @@ struct RSPolicy {
     }
     pend_owner = -1;
   }
-  __device__ __forceinline__ void finish() const { flush(); }
+  __device__ __forceinline__ void finish() const {
+    flush();
+    tma_store_wait<0>();
+  }
   __device__ __forceinline__ int owner_of(int mb) const { return mb / blocks_per_rank; }
   __device__ __forceinline__ void map_tile(int t, int num_m, int nn, int& b, int& mb, int& nb) const {
     // peers' row blocks first (ring order after this rank), own blocks last
@@ -329,10 +343,8 @@ struct RSPolicy {
            ((size_t)src * blocks_per_rank + mb_local) * num_n + nb;
   }
   __device__ __forceinline__ void before_epilogue(int, int mb, int nb) const {
-    if (owner_of(mb) != a.rank) {
-      tma_store_wait_read<0>();  // the staging rows of the previous shipped tile have been read out
-      return;
-    }
+    tma_store_wait_read<0>();    // the staging rows of the previous tile have been read out
+    if (owner_of(mb) != a.rank) return;
     flush();  // publish before waiting on the peers, or two ranks could wait on each other
     if (a.dbg) return;
     const int mb_local = mb - a.rank * blocks_per_rank;
@@ -399,14 +411,35 @@ struct RSPolicy {
         sum[q * 8 + 7] = __float_as_uint(__uint_as_float(sum[q * 8 + 7]) + f3.y);
       }
     }
-    // Params describe the *shard* output: C/residual are [Ts, N], indexed by the local row
+    // Params describe the *shard* output: C/residual are [Ts, N], indexed by the local row.  The
+    // finished bf16 row chunk goes back into this thread's staging row (over the partial it just
+    // consumed) and leaves with one bulk copy per row in tile_done.
     Params q = p;
     q.M = a.rows_per_rank;
-    epilogue_chunk(q, b, row_local, n0, sum);
+    float v[32];
+    epilogue_values(q, b, row_local, n0, sum, v);
+    uint8_t* dst = staging + (size_t)(m - mb * BM) * RS_PITCH + (size_t)(n0 - nb * BN) * 2;
+#pragma unroll
+    for (int qq = 0; qq < 4; ++qq) {
+      uint4 u;
+      u.x = pack_bf16x2(v[qq * 8 + 0], v[qq * 8 + 1]); u.y = pack_bf16x2(v[qq * 8 + 2], v[qq * 8 + 3]);
+      u.z = pack_bf16x2(v[qq * 8 + 4], v[qq * 8 + 5]); u.w = pack_bf16x2(v[qq * 8 + 6], v[qq * 8 + 7]);
+      *reinterpret_cast<uint4*>(dst + qq * 16) = u;
+    }
   }
   __device__ __forceinline__ void tile_done(int, int mb, int nb) const {
     const int owner = owner_of(mb);
-    if (owner == a.rank) return;   // (before_epilogue already flushed)
+    if (owner == a.rank) {   // (before_epilogue already flushed) finished rows -> the local output shard
+      const int r = (int)threadIdx.x - 64;
+      const int row_in_tile = (((r >> 5) + 2) & 3) * 32 + (r & 31);
+      const int row_local = mb * BM + row_in_tile - owner * a.rows_per_rank;
+      const int n0 = nb * BN;
+      const int cols = a.N - n0 < BN ? a.N - n0 : BN;
+      asm volatile("fence.proxy.async;" ::: "memory");
+      bulk_store_1d(out + (size_t)row_local * ldo + n0, staging + (size_t)row_in_tile * RS_PITCH, (uint32_t)cols * 2);
+      tma_store_commit();
+      return;
+    }
     // this thread's row: staging -> owner's receive slot for this source rank, one bulk copy
     const int r = (int)threadIdx.x - 64;  // epilogue threads are 64..191, TMEM quarter = warp & 3
     const int row_in_tile = (((r >> 5) + 2) & 3) * 32 + (r & 31);
@@ -432,7 +465,8 @@ b2f_gemm_rs_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_const
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
-  RSPolicy pol{a, a.rows_per_rank / BM, (p.N + BN - 1) / BN, smem + RS_STAGES * STAGE_BYTES + 1024};
+  RSPolicy pol{a, a.rows_per_rank / BM, (p.N + BN - 1) / BN, smem + RS_STAGES * STAGE_BYTES + 1024,
+               reinterpret_cast<__nv_bfloat16*>(p.C), p.ldc};
   if (threadIdx.x == 0) pol.init_smem();
   gemm_body<RSPolicy, 0, RS_STAGES>(&tma_a, &tma_b, p, pol, blockIdx.x, gridDim.x, smem_raw);
 }
@@ -471,7 +505,7 @@ b2f_gemm_rs2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
   RS2Policy pol{RSPolicy{a, a.rows_per_rank / BM, (p.N + BN - 1) / BN,
-                         smem + RS2_STAGES * gemm2::ST2_BYTES + 1024}};
+                         smem + RS2_STAGES * gemm2::ST2_BYTES + 1024, reinterpret_cast<__nv_bfloat16*>(p.C), p.ldc}};
   if (threadIdx.x == 0) pol.in.init_smem();
   gemm2::gemm2_body<RS2Policy, RS2_STAGES>(&tma_a, &tma_b, p, pol, blockIdx.x >> 1, gridDim.x >> 1, smem_raw);
 }
@@ -516,7 +550,7 @@ extern "C" int b2f_ag_gemm_bf16(const long long* x_shard_ptrs, void* xg, const v
   if (comm_ctas > sms / 2) comm_ctas = sms / 2;
   a.comm_ctas = comm_ctas;
   static const bool force_1cta = [] { const char* e = getenv("B2F_FUSED_TP_CORE"); return e && e[0] == '1'; }();
-  if (!force_1cta && (T / world) % 256 == 0 && N >= 256) {
+  if (!force_1cta && (T / world) % 256 == 0 && N >= 256 && N % 8 == 0 && ldy % 8 == 0) {
     // CTA-pair core: per-CTA boxes of 128 rows of A / 128 rows of B
     a.own_last = 1;
     if (a.comm_ctas & 1) ++a.comm_ctas;
@@ -524,13 +558,15 @@ extern "C" int b2f_ag_gemm_bf16(const long long* x_shard_ptrs, void* xg, const v
     if (int rc = make_operand_map(&ma2, xg, T, K, K, 1, 0, 0, BM)) return rc;
     if (int rc = make_operand_map(&mown, reinterpret_cast<const void*>(x_shard_ptrs[rank]), T / world, K, K, 1, 0, 0, BM)) return rc;
     if (int rc = make_operand_map(&mb2, B, N, K, ldb, 1, 0, b_mn_major, BM)) return rc;
-    B2F_CHECK_CUDA(cudaFuncSetAttribute(b2f_ag_gemm2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        gemm2::SMEM2_BYTES));
+    CUtensorMap mc;
+    if (int rc = make_tma_3d(&mc, Y, TmaDtype::BF16, 1, T, N, (long long)T * ldy, ldy, 32, 64, 128)) return rc;
+    constexpr int AG2_SMEM = gemm2::smem2_bytes(gemm2::S2, gemm2::STAGE_BYTES_2);
+    B2F_CHECK_CUDA(cudaFuncSetAttribute(b2f_ag_gemm2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AG2_SMEM));
     const int tiles2 = (T / 256) * ((N + 255) / 256);
     int pairs = (sms - a.comm_ctas) / 2;
     if (pairs > tiles2) pairs = tiles2;
-    b2f_ag_gemm2_kernel<<<a.comm_ctas + 2 * pairs, NUM_THREADS, gemm2::SMEM2_BYTES, static_cast<cudaStream_t>(stream)>>>(
-        ma2, mown, mb2, p, a);
+    b2f_ag_gemm2_kernel<<<a.comm_ctas + 2 * pairs, NUM_THREADS, AG2_SMEM, static_cast<cudaStream_t>(stream)>>>(
+        ma2, mown, mb2, mc, p, a);
     B2F_CHECK_CUDA(cudaGetLastError());
     return 0;
   }
@@ -557,6 +593,7 @@ extern "C" int b2f_gemm_rs_bf16(const void* X, const void* B, void* Y_shard, int
                                 int world, unsigned epoch, void* stream) {
   B2F_REQUIRE(T % (world * BM) == 0, "gemm_rs: rows per rank must be a multiple of 128");
   B2F_REQUIRE(N % 32 == 0, "gemm_rs: N must be a multiple of 32");
+  B2F_REQUIRE(ldy % 8 == 0 && (reinterpret_cast<uintptr_t>(Y_shard) & 15) == 0, "gemm_rs: output rows must be 16-byte aligned");
   Params p{};
   p.M = T; p.N = N; p.K = K; p.batch = 1;
   p.a_mn_major = 0; p.b_mn_major = b_mn_major;
