@@ -104,15 +104,13 @@ struct AGPolicy {
     wait_ge_gpu(tile_flags + mb, epoch);
     asm volatile("fence.proxy.async;" ::: "memory");  // generic-proxy copy -> TMA (async proxy) read
   }
-  // C leaves through the swizzled staging buffer and TMA tensor stores (see gemm2::Staged2)
-  gemm2::Staged2 out;
-  __device__ __forceinline__ void before_epilogue(int b, int mb128, int nb) const { out.before_epilogue(b, mb128, nb); }
-  __device__ __forceinline__ void store_chunk(const Params& p, int b, int mb128, int nb, int m, int n0,
+  __device__ __forceinline__ void before_epilogue(int, int, int) const {}
+  __device__ __forceinline__ void store_chunk(const Params& p, int b, int, int, int m, int n0,
                                               const uint32_t (&acc)[32]) const {
-    out.store_chunk(p, b, mb128, nb, m, n0, acc);
+    epilogue_chunk(p, b, m, n0, acc);
   }
   __device__ __forceinline__ void tile_done(int, int, int) const {}
-  __device__ __forceinline__ void finish() const { out.finish(); }
+  __device__ __forceinline__ void finish() const {}
 };
 
 // Gather role: one thread per comm CTA drives the copy engine.  A 128-row block of a shard
