@@ -1,0 +1,162 @@
+"""Horovod-shaped facade (`import b200flow.engines.horovod_api as hvd`).
+
+The reference's Mask R-CNN workloads run under Horovod 0.28.1 with NCCL GPU operations, launched
+by `mpirun` (charts/machine-learning/training/mpijob-horovod-tensorflow-gpu/values.yaml:18-60,
+containers/aws-samples-maskrcnn/Dockerfile:57).  What a training script touches is small: `init`,
+`rank / size / local_rank`, `allreduce`, `broadcast_parameters`, `DistributedOptimizer` — and
+underneath, the tensor-fusion buffer that batches many small gradients into few collectives.
+
+Here the ranks come from the launcher's mpirun mode (`OMPI_COMM_WORLD_*`, or torchrun's variables),
+collectives are `torch.distributed` (NCCL on GPUs, gloo on CPU), and the fusion buffer is the flat
+gradient storage + bucketed K1 reducer of `parallel/ddp.py` (gradients are *born* inside one
+contiguous buffer, so "fusion" needs no copy-in / copy-out).
+"""
+from __future__ import annotations
+
+import os
+
+import torch
+import torch.distributed as dist
+
+Average, Sum = "average", "sum"
+
+
+def init(backend: str | None = None) -> None:
+    if dist.is_initialized():
+        return
+    env = os.environ
+    rank = int(env.get("OMPI_COMM_WORLD_RANK", env.get("RANK", 0)))
+    world = int(env.get("OMPI_COMM_WORLD_SIZE", env.get("WORLD_SIZE", 1)))
+    local = int(env.get("OMPI_COMM_WORLD_LOCAL_RANK", env.get("LOCAL_RANK", 0)))
+    env.setdefault("RANK", str(rank))
+    env.setdefault("WORLD_SIZE", str(world))
+    env.setdefault("LOCAL_RANK", str(local))
+    env.setdefault("MASTER_ADDR", "127.0.0.1")
+    env.setdefault("MASTER_PORT", "29500")
+    if backend is None:
+        backend = "nccl" if torch.cuda.is_available() else "gloo"
+    if torch.cuda.is_available():
+        torch.cuda.set_device(local % torch.cuda.device_count())
+    if world > 1:
+        dist.init_process_group(backend, rank=rank, world_size=world)
+
+
+def shutdown() -> None:
+    if dist.is_initialized():
+        dist.destroy_process_group()
+
+
+def is_initialized() -> bool:
+    return dist.is_initialized() or int(os.environ.get("WORLD_SIZE", os.environ.get("OMPI_COMM_WORLD_SIZE", 1))) == 1
+
+
+def size() -> int:
+    return dist.get_world_size() if dist.is_initialized() else 1
+
+
+def rank() -> int:
+    return dist.get_rank() if dist.is_initialized() else 0
+
+
+def local_rank() -> int:
+    return int(os.environ.get("OMPI_COMM_WORLD_LOCAL_RANK", os.environ.get("LOCAL_RANK", 0)))
+
+
+def local_size() -> int:
+    return int(os.environ.get("OMPI_COMM_WORLD_LOCAL_SIZE", os.environ.get("LOCAL_WORLD_SIZE", size())))
+
+
+def allreduce(tensor: torch.Tensor, op: str = Average, name: str | None = None) -> torch.Tensor:
+    out = tensor.clone()
+    if size() > 1:
+        dist.all_reduce(out)
+        if op == Average:
+            out = out / size() if out.is_floating_point() else out // size()
+    return out
+
+
+def allgather(tensor: torch.Tensor, name: str | None = None) -> torch.Tensor:
+    if size() == 1:
+        return tensor.clone()
+    outs = [torch.empty_like(tensor) for _ in range(size())]
+    dist.all_gather(outs, tensor.contiguous())
+    return torch.cat(outs, 0)
+
+
+def broadcast(tensor: torch.Tensor, root_rank: int = 0, name: str | None = None) -> torch.Tensor:
+    out = tensor.clone()
+    if size() > 1:
+        dist.broadcast(out, src=root_rank)
+    return out
+
+
+def broadcast_parameters(params, root_rank: int = 0) -> None:
+    """`hvd.broadcast_parameters(model.state_dict(), root_rank=0)` — start every rank from rank 0's weights."""
+    if size() == 1:
+        return
+    items = params.items() if hasattr(params, "items") else params
+    for _, p in items:
+        if isinstance(p, torch.Tensor):
+            dist.broadcast(p.data if isinstance(p, torch.nn.Parameter) else p, src=root_rank)
+
+
+def broadcast_optimizer_state(optimizer, root_rank: int = 0) -> None:
+    if size() == 1:
+        return
+    for st in optimizer.state.values():
+        for v in st.values():
+            if isinstance(v, torch.Tensor):
+                dist.broadcast(v, src=root_rank)
+
+
+class _DistributedOptimizer:
+    """Wraps an optimizer: gradients are averaged across ranks before `step()`.  With a model wrapped by
+    `b200flow.parallel.ddp.DistributedDataParallel` the bucketed reducer has already done it during
+    backward (pass `ddp=`); otherwise every gradient is all-reduced here (one flat collective per dtype:
+    the fusion buffer)."""
+
+    def __init__(self, optimizer, named_parameters=None, ddp=None, op: str = Average):
+        self.optimizer, self.ddp, self.op = optimizer, ddp, op
+        self.params = [p for _, p in named_parameters] if named_parameters is not None else [
+            p for g in optimizer.param_groups for p in g["params"]]
+
+    @property
+    def param_groups(self):
+        return self.optimizer.param_groups
+
+    def synchronize(self) -> None:
+        if size() == 1:
+            return
+        if self.ddp is not None:
+            self.ddp.finish_reduction()
+            return
+        by_dtype: dict = {}
+        for p in self.params:
+            if p.grad is not None:
+                by_dtype.setdefault(p.grad.dtype, []).append(p.grad)
+        for grads in by_dtype.values():
+            flat = torch.cat([g.reshape(-1) for g in grads])
+            dist.all_reduce(flat)
+            if self.op == Average:
+                flat /= size()
+            off = 0
+            for g in grads:
+                g.copy_(flat[off:off + g.numel()].view_as(g))
+                off += g.numel()
+
+    def step(self, closure=None):
+        self.synchronize()
+        return self.optimizer.step(closure) if closure is not None else self.optimizer.step()
+
+    def zero_grad(self, *a, **kw):
+        return self.optimizer.zero_grad(*a, **kw)
+
+    def state_dict(self):
+        return self.optimizer.state_dict()
+
+    def load_state_dict(self, sd):
+        return self.optimizer.load_state_dict(sd)
+
+
+def DistributedOptimizer(optimizer, named_parameters=None, ddp=None, op: str = Average, **_ignored):
+    return _DistributedOptimizer(optimizer, named_parameters, ddp, op)

@@ -224,3 +224,41 @@ def test_ulysses_attention_matches_full_attention_gloo():
         assert p.exitcode == 0
     for rank, eo, eq, ek in res:
         assert eo < 1e-4 and eq < 1e-4 and ek < 1e-4, (rank, eo, eq, ek)
+
+
+def _hvd_worker(rank, world, port, q_out):
+    os.environ.update({"OMPI_COMM_WORLD_RANK": str(rank), "OMPI_COMM_WORLD_SIZE": str(world),
+                       "OMPI_COMM_WORLD_LOCAL_RANK": str(rank), "MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port)})
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        os.environ.pop(k, None)
+    import b200flow.engines.horovod_api as hvd
+
+    hvd.init("gloo")
+    torch.manual_seed(rank)
+    model = torch.nn.Linear(4, 3)
+    hvd.broadcast_parameters(model.state_dict(), root_rank=0)
+    w0 = model.weight.detach().clone()
+    opt = hvd.DistributedOptimizer(torch.optim.SGD(model.parameters(), lr=0.1), named_parameters=model.named_parameters())
+    x = torch.full((2, 4), float(rank + 1))
+    model(x).sum().backward()
+    g_local = model.weight.grad.clone()
+    opt.step()
+    avg = hvd.allreduce(g_local)                     # what every rank should have applied
+    ok = torch.allclose(model.weight.detach(), w0 - 0.1 * avg, atol=1e-6)
+    q_out.put((rank, hvd.size(), bool(ok), float(hvd.allreduce(torch.tensor([float(rank)]), op=hvd.Sum))))
+    hvd.shutdown()
+
+
+def test_horovod_facade_over_gloo():
+    ctx = mp.get_context("spawn")
+    q_out = ctx.Queue()
+    port = 29650 + (os.getpid() % 300)
+    procs = [ctx.Process(target=_hvd_worker, args=(r, 2, port, q_out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q_out.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, sz, ok, s in res:
+        assert sz == 2 and ok and s == 1.0, (rank, sz, ok, s)
