@@ -56,7 +56,8 @@ def loaded_libraries() -> list[str]:
 
 _launches = 0
 # kernels launched per entry point (default 1)
-_KERNELS_PER_CALL = {"b2f_norm_bwd": 2, "b2f_sumsq": 2, "b2f_attn_bwd": 3}
+_KERNELS_PER_CALL = {"b2f_norm_bwd": 2, "b2f_norm_bwd_noalloc": 2, "b2f_sumsq": 2, "b2f_attn_bwd": 3,
+                     "b2f_moe_router_top1": 2}
 
 
 def launch_count() -> int:

@@ -62,9 +62,10 @@ def route_top1(logits: torch.Tensor, capacity: int):
                    gate=torch.empty(T, dtype=torch.float32, device=dev), probs=torch.empty(T, E, dtype=torch.float32, device=dev),
                    counts=torch.empty(E, dtype=torch.int32, device=dev), me=torch.empty(E, dtype=torch.float32, device=dev),
                    ce=torch.empty(E, dtype=torch.float32, device=dev))
+        scratch = torch.empty(((T + 511) // 512) * E * 2, dtype=torch.int32, device=dev)   # per-block partials
         _lib.call("b2f_moe_router_top1", ptr(logits.contiguous()), c_int(T), c_int(E), c_int(capacity),
                   ptr(out["expert"]), ptr(out["slot"]), ptr(out["gate"]), ptr(out["probs"]), ptr(out["counts"]),
-                  ptr(out["me"]), ptr(out["ce"]), stream_ptr())
+                  ptr(out["me"]), ptr(out["ce"]), ptr(scratch), stream_ptr())
         return out
     probs = logits.float().softmax(-1)
     gate, best = probs.max(-1)

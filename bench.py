@@ -152,6 +152,8 @@ def main():
         tp = pp = 1
         if args.seq == 4096:
             args.seq = 2048
+        if args.micro_batch == 1 and args.gas == 16:   # defaults: 8 x 2048 tokens per micro-batch, 4 of them
+            args.micro_batch, args.gas = 8, 4
     cfg = config_from_preset(args.workload, max_seq=args.seq)
     ep = min(world, cfg.num_experts) if is_moe else 1
     if is_moe:

@@ -18,75 +18,106 @@ using namespace b2f;
 namespace {
 
 constexpr int MAX_E = 64;
-constexpr int RT = 1024;   // router threads (single block: T per GPU is a few thousand tokens)
+constexpr int RT = 512;    // tokens (= threads) per router block
 
-// logits fp32 [T, E]. Outputs: expert[T] (-1 = dropped), slot[T], gate[T], probs [T, E] (saved for
-// backward), counts[E] (kept tokens), me[E] = sum_t p[t, e], ce[E] = #tokens whose arg-max is e.
+// The router runs as two kernels over ceil(T / RT) blocks, with a small caller-provided scratch
+// ([blocks][E] ints + [blocks][E] floats) between them:
+//   pass 1  softmax, arg-max, gate probability; per-block token count and probability mass per expert
+//   pass 2  a token's slot = tokens of its expert in earlier blocks (summed from the scratch)
+//           + earlier tokens of its expert in this block (ballot ranks); capacity dropping;
+//           block 0 also reduces the per-block partials into counts / me / ce in a fixed order.
+// Slots follow token order, so routing is deterministic.
+
+// logits fp32 [T, E]. Outputs of the pair: expert[T] (-1 = dropped), slot[T], gate[T], probs [T, E]
+// (saved for backward), counts[E] (kept tokens), me[E] = sum_t p[t, e], ce[E] = #tokens whose
+// arg-max is e.
 __global__ void __launch_bounds__(RT)
-router_top1_kernel(const float* __restrict__ logits, int T, int E, int capacity,
-                   int* __restrict__ expert, int* __restrict__ slot, float* __restrict__ gate,
-                   float* __restrict__ probs, int* __restrict__ counts, float* __restrict__ me,
-                   float* __restrict__ ce) {
-  __shared__ int warp_cnt[RT / 32][MAX_E / 8];   // E <= 8 per pass keeps smem small; looped below
-  __shared__ int base[MAX_E];
+router_pass1_kernel(const float* __restrict__ logits, int T, int E, int* __restrict__ expert,
+                    float* __restrict__ gate, float* __restrict__ probs, int* __restrict__ blk_cnt,
+                    float* __restrict__ blk_me) {
   __shared__ float me_s[MAX_E];
   __shared__ int ce_s[MAX_E];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int e = threadIdx.x; e < E; e += RT) { base[e] = 0; me_s[e] = 0.f; ce_s[e] = 0; }
+  const int lane = threadIdx.x & 31;
+  for (int e = threadIdx.x; e < E; e += RT) { me_s[e] = 0.f; ce_s[e] = 0; }
   __syncthreads();
-  for (int t0 = 0; t0 < T; t0 += RT) {
-    const int t = t0 + threadIdx.x;
-    int best = -1;
-    float bp = 0.f;
+  const int t = blockIdx.x * RT + threadIdx.x;
+  int best = -1;
+  float bp = 0.f;
+  const float* z = logits + (long long)t * E;
+  float mx = -INFINITY, inv = 0.f;
+  if (t < T) {
+    for (int e = 0; e < E; ++e) mx = fmaxf(mx, z[e]);
+    float sum = 0.f;
+    for (int e = 0; e < E; ++e) sum += __expf(z[e] - mx);
+    inv = 1.f / sum;
+  }
+  for (int e = 0; e < E; ++e) {
+    float p = 0.f;
     if (t < T) {
-      const float* z = logits + (long long)t * E;
-      float mx = z[0];
-      for (int e = 1; e < E; ++e) mx = fmaxf(mx, z[e]);
-      float sum = 0.f;
-      for (int e = 0; e < E; ++e) sum += __expf(z[e] - mx);
-      const float inv = 1.f / sum;
-      for (int e = 0; e < E; ++e) {
-        const float p = __expf(z[e] - mx) * inv;
-        probs[(long long)t * E + e] = p;
-        atomicAdd(&me_s[e], p);
-        if (p > bp) { bp = p; best = e; }
-      }
-      atomicAdd(&ce_s[best], 1);
+      p = __expf(z[e] - mx) * inv;
+      probs[(long long)t * E + e] = p;
+      if (p > bp) { bp = p; best = e; }
     }
-    // ordered slot inside the expert: tokens are ranked by index (deterministic)
-    int my_slot = -1;
-    for (int e0 = 0; e0 < E; e0 += MAX_E / 8) {
-      const int ne = E - e0 < MAX_E / 8 ? E - e0 : MAX_E / 8;
-      for (int k = 0; k < ne; ++k) {
-        const unsigned m = __ballot_sync(0xffffffffu, best == e0 + k);
-        if (lane == 0) warp_cnt[warp][k] = __popc(m);
-        if (best == e0 + k) my_slot = __popc(m & ((1u << lane) - 1));
-      }
-      __syncthreads();
-      if (best >= e0 && best < e0 + ne) {
-        int before = base[best];
-        for (int w = 0; w < warp; ++w) before += warp_cnt[w][best - e0];
-        my_slot += before;
-      }
-      __syncthreads();
-      if ((int)threadIdx.x < ne) {
-        int tot = 0;
-        for (int w = 0; w < RT / 32; ++w) tot += warp_cnt[w][threadIdx.x];
-        base[e0 + threadIdx.x] += tot;
-      }
-      __syncthreads();
-    }
-    if (t < T) {
-      const bool keep = my_slot < capacity;
-      expert[t] = keep ? best : -1;
-      slot[t] = keep ? my_slot : -1;
-      gate[t] = keep ? bp : 0.f;
+    // warp-level sum first: one shared-memory atomic per warp and expert
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) p += __shfl_xor_sync(0xffffffffu, p, o);
+    if (lane == 0) atomicAdd(&me_s[e], p);
+  }
+  for (int e = 0; e < E; ++e) {
+    const unsigned m = __ballot_sync(0xffffffffu, best == e);
+    if (lane == 0 && m) atomicAdd(&ce_s[e], __popc(m));
+  }
+  if (t < T) {
+    expert[t] = best;   // provisional: pass 2 applies the capacity
+    gate[t] = bp;
+  }
+  __syncthreads();
+  for (int e = threadIdx.x; e < E; e += RT) {
+    blk_cnt[blockIdx.x * E + e] = ce_s[e];
+    blk_me[blockIdx.x * E + e] = me_s[e];
+  }
+}
+
+__global__ void __launch_bounds__(RT)
+router_pass2_kernel(int T, int E, int capacity, int nblk, int* __restrict__ expert, int* __restrict__ slot,
+                    float* __restrict__ gate, const int* __restrict__ blk_cnt,
+                    const float* __restrict__ blk_me, int* __restrict__ counts, float* __restrict__ me,
+                    float* __restrict__ ce) {
+  __shared__ int base[MAX_E];
+  __shared__ int warp_cnt[RT / 32][MAX_E];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // tokens of each expert in earlier blocks
+  for (int e = threadIdx.x; e < E; e += RT) {
+    int acc = 0;
+    for (int bI = 0; bI < (int)blockIdx.x; ++bI) acc += blk_cnt[bI * E + e];
+    base[e] = acc;
+  }
+  if (blockIdx.x == 0) {
+    for (int e = threadIdx.x; e < E; e += RT) {
+      int tot = 0;
+      float m = 0.f;
+      for (int bI = 0; bI < nblk; ++bI) { tot += blk_cnt[bI * E + e]; m += blk_me[bI * E + e]; }
+      counts[e] = tot < capacity ? tot : capacity;
+      ce[e] = (float)tot;
+      me[e] = m;
     }
   }
-  for (int e = threadIdx.x; e < E; e += RT) {
-    counts[e] = base[e] < capacity ? base[e] : capacity;
-    me[e] = me_s[e];
-    ce[e] = (float)ce_s[e];
+  const int t = blockIdx.x * RT + threadIdx.x;
+  const int best = t < T ? expert[t] : -1;
+  int rank_in_warp = 0;
+  for (int e = 0; e < E; ++e) {
+    const unsigned m = __ballot_sync(0xffffffffu, best == e);
+    if (lane == 0) warp_cnt[warp][e] = __popc(m);
+    if (best == e) rank_in_warp = __popc(m & ((1u << lane) - 1));
+  }
+  __syncthreads();
+  if (t < T) {
+    int my_slot = base[best] + rank_in_warp;
+    for (int w = 0; w < warp; ++w) my_slot += warp_cnt[w][best];
+    const bool keep = my_slot < capacity;
+    expert[t] = keep ? best : -1;
+    slot[t] = keep ? my_slot : -1;
+    if (!keep) gate[t] = 0.f;
   }
 }
 
@@ -202,12 +233,24 @@ inline int row_grid(int T) {
 
 }  // namespace
 
+extern "C" long long b2f_moe_router_scratch_bytes(int T, int E) {
+  const long long nblk = (T + RT - 1) / RT;
+  return nblk * E * 8;
+}
+
+// scratch: b2f_moe_router_scratch_bytes(T, E) bytes of device memory (contents irrelevant).
 extern "C" int b2f_moe_router_top1(const float* logits, int T, int E, int capacity, int* expert,
                                    int* slot, float* gate, float* probs, int* counts, float* me,
-                                   float* ce, void* stream) {
+                                   float* ce, void* scratch, void* stream) {
   B2F_REQUIRE(T > 0 && E >= 1 && E <= MAX_E && capacity > 0, "router: need 1 <= E <= 64, capacity > 0");
-  router_top1_kernel<<<1, RT, 0, (cudaStream_t)stream>>>(logits, T, E, capacity, expert, slot, gate, probs,
-                                                         counts, me, ce);
+  B2F_REQUIRE(scratch != nullptr, "router: scratch buffer required (b2f_moe_router_scratch_bytes)");
+  const int nblk = (T + RT - 1) / RT;
+  int* blk_cnt = static_cast<int*>(scratch);
+  float* blk_me = reinterpret_cast<float*>(blk_cnt + (long long)nblk * E);
+  router_pass1_kernel<<<nblk, RT, 0, (cudaStream_t)stream>>>(logits, T, E, expert, gate, probs, blk_cnt, blk_me);
+  B2F_CHECK_CUDA(cudaGetLastError());
+  router_pass2_kernel<<<nblk, RT, 0, (cudaStream_t)stream>>>(T, E, capacity, nblk, expert, slot, gate, blk_cnt,
+                                                             blk_me, counts, me, ce);
   B2F_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -188,8 +188,10 @@ int b2f_mask_paste(const float* probs, int M, const float* boxes, int R, int H, 
  * With peer_ptrs the dispatch stores rows straight into the expert owner's buffer
  * [src_rank, local_expert, capacity, H] and the combine pulls them back: the all-to-alls are
  * done by these kernels over NVLink. */
+long long b2f_moe_router_scratch_bytes(int T, int E);
 int b2f_moe_router_top1(const float* logits, int T, int E, int capacity, int* expert, int* slot,
-                        float* gate, float* probs, int* counts, float* me, float* ce, void* stream);
+                        float* gate, float* probs, int* counts, float* me, float* ce, void* scratch,
+                        void* stream);
 int b2f_moe_dispatch(const void* x, const int* expert, const int* slot, int T, int H, int capacity,
                      void* dst_local, const long long* peer_ptrs, int world, int experts_per_rank,
                      int src_rank, void* stream);
