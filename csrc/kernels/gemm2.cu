@@ -68,16 +68,6 @@ b2f_gemm2_f32_staged_kernel(const __grid_constant__ CUtensorMap tma_a, const __g
   gemm2_body<StagedF32, STAGED_STAGES>(&tma_a, &tma_b, p, pol, blockIdx.x >> 1, gridDim.x >> 1, smem_raw);
 }
 
-// Same kernel with a 4-deep ring (what the fused GEMM->reduce-scatter kernel can afford next to its
-// staging buffer); exposed so its cost can be measured in isolation (B2F_GEMM2_STAGES=4).
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
-b2f_gemm2_bf16_s4_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
-                         const Params p) {
-  extern __shared__ uint8_t smem_raw[];
-  Plain2 pol;
-  gemm2_body<Plain2, 4>(&tma_a, &tma_b, p, pol, blockIdx.x >> 1, gridDim.x >> 1, smem_raw);
-}
-
 }  // namespace
 
 extern "C" int b2f_gemm_bf16_2cta(const void* A, const void* B, void* C, int M, int N, int K,
@@ -112,11 +102,10 @@ extern "C" int b2f_gemm_bf16_2cta(const void* A, const void* B, void* C, int M, 
   const int tiles = ((M + T2_BM - 1) / T2_BM) * ((N + T2_BN - 1) / T2_BN) * batch;
   int pairs = sm_count() / 2;
   if (pairs > tiles) pairs = tiles;
-  static const bool s4 = [] { const char* e = getenv("B2F_GEMM2_STAGES"); return e && e[0] == '4'; }();
   static const bool direct = [] { const char* e = getenv("B2F_GEMM2_EPI"); return e && e[0] == 'd'; }();
   const bool can_stage = !(flags & EPI_OUT_F32) && (ldc % 8 == 0) && (N % 8 == 0) && (strideC % 8 == 0);
   const bool can_stage_f32 = (flags & EPI_OUT_F32) && (ldc % 4 == 0) && (N % 4 == 0) && (strideC % 4 == 0);
-  if (can_stage_f32 && !direct && !s4) {
+  if (can_stage_f32 && !direct) {
     static bool f32_attr[64] = {false};
     if (!f32_attr[dev & 63]) {
       B2F_CHECK_CUDA(cudaFuncSetAttribute(b2f_gemm2_f32_staged_kernel,
@@ -126,9 +115,8 @@ extern "C" int b2f_gemm_bf16_2cta(const void* A, const void* B, void* C, int M, 
     CUtensorMap mc;
     if (int rc = make_tma_3d(&mc, C, TmaDtype::F32, batch, M, N, batch > 1 ? strideC : (long long)M * ldc, ldc,
                              32, 32, 128)) return rc;
-    // the reducing store needs the accumulate flag out of the per-element epilogue: values only
     b2f_gemm2_f32_staged_kernel<<<pairs * 2, NUM_THREADS, STAGED_SMEM, static_cast<cudaStream_t>(stream)>>>(ma, mb, mc, p);
-  } else if (can_stage && !direct && !s4) {
+  } else if (can_stage && !direct) {
     static bool staged_attr[64] = {false};
     if (!staged_attr[dev & 63]) {
       B2F_CHECK_CUDA(cudaFuncSetAttribute(b2f_gemm2_bf16_staged_kernel,
@@ -139,10 +127,6 @@ extern "C" int b2f_gemm_bf16_2cta(const void* A, const void* B, void* C, int M, 
     if (int rc = make_tma_3d(&mc, C, TmaDtype::BF16, batch, M, N, batch > 1 ? strideC : (long long)M * ldc, ldc,
                              32, 64, 128)) return rc;
     b2f_gemm2_bf16_staged_kernel<<<pairs * 2, NUM_THREADS, STAGED_SMEM, static_cast<cudaStream_t>(stream)>>>(ma, mb, mc, p);
-  } else if (s4) {
-    B2F_CHECK_CUDA(cudaFuncSetAttribute(b2f_gemm2_bf16_s4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        SMEM2_BYTES));
-    b2f_gemm2_bf16_s4_kernel<<<pairs * 2, NUM_THREADS, SMEM2_BYTES, static_cast<cudaStream_t>(stream)>>>(ma, mb, p);
   } else {
     b2f_gemm2_bf16_kernel<<<pairs * 2, NUM_THREADS, SMEM2_BYTES, static_cast<cudaStream_t>(stream)>>>(ma, mb, p);
   }
