@@ -4,20 +4,25 @@
 // free, heads packed, D in {64, 128}), so the kernels read straight out of a
 // fused QKV projection buffer.  128x128 score tiles.
 //
-// Forward (one CTA per 128 query rows of one head): warp 0 = TMA producer,
-// warp 1 = MMA issuer, warps 2-5 = softmax (one query row per thread, no
-// cross-thread reductions).  S = Q K^T lands in one of two TMEM score buffers;
-// the softmax threads turn it into bf16 probabilities *in place in TMEM* and
-// the P V product consumes them as a TMEM A-operand (tcgen05.mma TS form), so P
-// never touches shared memory.  The next tile's Q K^T is issued before the
-// current P V, which keeps the tensor core busy during the exponentials.
+// Forward (one CTA per 256 query rows of one head, 384 threads): warpgroup 0 = TMA
+// warp + MMA warp, warpgroups 1 and 2 = softmax of the two 128-row query tiles,
+// which ping-pong on the tensor core.  One query row per thread with all 128
+// scores in registers (no cross-thread reductions); the bf16 probabilities are
+// written back over S in TMEM and the P V product consumes them as a TMEM
+// A-operand (tcgen05.mma TS form), so P never touches shared memory.  O
+// accumulates in TMEM; the running max is raised lazily (see the kernel).
 //
-// Backward is two kernels that recompute P from the saved log-sum-exp:
+// Backward is a statistics pre-pass plus two kernels that recompute P from the
+// saved log-sum-exp, software-pipelined over half score tiles (128 x 64):
 //   dQ  kernel (CTA per query tile):  S, dP -> dS in TMEM -> dQ += dS K
 //   dKV kernel (CTA per key tile):    S^T, dP^T -> P^T, dS^T in TMEM ->
 //                                     dV += P^T dO ; dK += dS^T Q
 // Both keep their accumulators in TMEM for the whole loop: no atomics, and the
 // result is deterministic.
+//
+// The MMA warp walks its loop as a whole and one elect.sync lane issues, with
+// descriptors built as a constant high word + an incremented low word: a
+// 128x128x16 MMA lasts 64 cycles, so the issue sequence must be shorter than that.
 //
 // Capability parity: flash-attn v2 / Megatron scaled_(upper_triang_)masked_softmax
 // attention core.
