@@ -84,6 +84,22 @@ class FusedTP:
                   ctypes.c_uint(self.rs_calls), stream_ptr())
         return y
 
+    def vocab_ce_exchange(self, logits: torch.Tensor, targets: torch.Tensor, lo: int) -> torch.Tensor:
+        """K9 statistics pass with the exchange done by the kernel's stores: every rank writes its
+        per-row {max, sum-exp, target logit} into slot `rank` of all peers' [world, T, 3] buffer;
+        one flag barrier later each rank holds every shard's statistics.  Returns that buffer."""
+        comm = self.comm
+        T, vl = logits.shape
+        self.ce_calls = getattr(self, "ce_calls", 0) + 1
+        buf = self._slots(self.__dict__.setdefault("_ce_slots", {}), comm.world * T * 3 * 4)[self.ce_calls & 1]
+        _lib.call("b2f_vocab_ce_stats", ptr(logits), ptr(targets), c_ll(T), c_int(vl), c_ll(logits.stride(0)),
+                  c_ll(lo), c_int(comm.rank), c_int(comm.world), buf.ptr_array, stream_ptr())
+        if not hasattr(self, "_ce_flags"):
+            self._ce_flags = comm.flag_region(3)
+        _lib.call("b2f_peer_barrier", self._ce_flags, c_int(comm.rank), c_int(comm.world),
+                  ctypes.c_uint(comm.next_epoch()), stream_ptr())
+        return buf.view(torch.float32, comm.world * T * 3)
+
     # ------------------------------------------------------- layer interface
     def column_linear(self, x, w, bias=None):
         return _FusedColumn.apply(x, w, bias, self)

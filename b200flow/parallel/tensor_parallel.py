@@ -159,6 +159,10 @@ class _VocabParallelCE(torch.autograd.Function):
     def forward(ctx, logits, targets, tp, ignore_index):
         T, Vl = logits.shape
         lo = tp.rank * Vl
+        if logits.is_cuda and logits.dtype == torch.bfloat16 and Vl % 8 == 0 and logits.stride(1) == 1 \
+                and logits.stride(0) % 8 == 0:
+            return _VocabParallelCE._forward_native(ctx, logits, targets.reshape(-1).to(torch.int64).contiguous(),
+                                                    tp, ignore_index, lo)
         lf = logits.float()
         local_max = lf.max(-1).values
         gmax = local_max.clone()
@@ -180,6 +184,33 @@ class _VocabParallelCE(torch.autograd.Function):
         p[torch.arange(T, device=logits.device)[mine], idx[mine]] -= 1.0
         p = p * valid[:, None]
         logits.copy_(p.to(logits.dtype))
+        ctx.save_for_backward(logits, nvalid)
+        return loss.sum() / nvalid
+
+    @staticmethod
+    def _forward_native(ctx, logits, targets, tp, ignore_index, lo):
+        """K9 (csrc/kernels/elementwise.cu): statistics kernel -> one exchange -> loss + in-place gradient."""
+        import ctypes
+
+        from ..ops import _lib
+        from ..ops._lib import c_float, c_int, c_ll, ptr, stream_ptr
+
+        T, Vl = logits.shape
+        dev = logits.device
+        if tp.fused is not None:
+            stats = tp.fused.vocab_ce_exchange(logits, targets, lo)      # peers stored into our buffer
+        else:
+            stats = torch.empty(tp.world * T * 3, dtype=torch.float32, device=dev)
+            ptrs = (ctypes.c_longlong * tp.world)(*[stats.data_ptr() if r == tp.rank else 0 for r in range(tp.world)])
+            _lib.call("b2f_vocab_ce_stats", ptr(logits), ptr(targets), c_ll(T), c_int(Vl), c_ll(logits.stride(0)),
+                      c_ll(lo), c_int(tp.rank), c_int(tp.world), ptrs, stream_ptr())
+            if tp.world > 1:
+                mine = stats[tp.rank * T * 3:(tp.rank + 1) * T * 3].clone()
+                dist.all_gather_into_tensor(stats, mine, group=tp.group)
+        loss = torch.empty(T, dtype=torch.float32, device=dev)
+        _lib.call("b2f_vocab_ce_finish", ptr(logits), ptr(targets), c_ll(T), c_int(Vl), c_ll(logits.stride(0)),
+                  c_ll(lo), c_int(tp.world), ptr(stats), c_ll(ignore_index), c_float(1.0), ptr(loss), stream_ptr())
+        nvalid = (targets != ignore_index).sum().clamp(min=1).float()
         ctx.save_for_backward(logits, nvalid)
         return loss.sum() / nvalid
 

@@ -300,6 +300,102 @@ cross_entropy_kernel(const __nv_bfloat16* __restrict__ logits, const long long* 
   }
 }
 
+// ---- K9: cross-entropy over vocab-sharded logits (Megatron vocab_parallel_cross_entropy, SURVEY.md
+// §2H C10) as two kernels around ONE exchange of per-row statistics.
+//   stats  : per row {local max, sum exp(z - local max), z[target] if the target is in this shard}
+//            written to slot `rank` of the statistics buffer [world][T][3] — of this GPU, or of
+//            every peer (mapped symmetric memory), which makes the exchange a store pattern.
+//   finish : combines the `world` slots (global max / sum / target logit), writes the loss and the
+//            gradient (softmax - onehot) * scale over the logits in place.
+struct CEPeers {
+  float* ptr[8];
+};
+
+__global__ void __launch_bounds__(512)
+vocab_ce_stats_kernel(const __nv_bfloat16* __restrict__ logits, const long long* __restrict__ targets,
+                      int Vl, long long ld, long long lo, long long T, int rank, int world,
+                      CEPeers out) {
+  __shared__ float red_m[16], red_s[16];
+  const long long row = blockIdx.x;
+  const __nv_bfloat16* lr = logits + row * ld;
+  const int vv = Vl >> 3;
+  float mx = -INFINITY, sm = 0.f;
+  for (int c = threadIdx.x; c < vv; c += blockDim.x) {
+    float f[8];
+    unpack8(ld_v4(reinterpret_cast<const uint4*>(lr) + c), f);
+    float cm = f[0];
+#pragma unroll
+    for (int j = 1; j < 8; ++j) cm = fmaxf(cm, f[j]);
+    const float nm = fmaxf(mx, cm);
+    float add = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) add += __expf(f[j] - nm);
+    sm = sm * __expf(mx - nm) + add;
+    mx = nm;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+    const float os = __shfl_xor_sync(0xffffffffu, sm, o);
+    const float nm = fmaxf(mx, om);
+    sm = (mx == -INFINITY ? 0.f : sm * __expf(mx - nm)) + (om == -INFINITY ? 0.f : os * __expf(om - nm));
+    mx = nm;
+  }
+  if ((threadIdx.x & 31) == 0) { red_m[threadIdx.x >> 5] = mx; red_s[threadIdx.x >> 5] = sm; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float gm = -INFINITY, gs = 0.f;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) {
+      const float om = red_m[w], os = red_s[w];
+      const float nm = fmaxf(gm, om);
+      gs = (gm == -INFINITY ? 0.f : gs * __expf(gm - nm)) + (om == -INFINITY ? 0.f : os * __expf(om - nm));
+      gm = nm;
+    }
+    const long long tgt = targets[row] - lo;
+    const float tl = (tgt >= 0 && tgt < Vl) ? __bfloat162float(lr[tgt]) : 0.f;
+    for (int r = 0; r < world; ++r) {
+      if (!out.ptr[r]) continue;
+      float* dst = out.ptr[r] + ((long long)rank * T + row) * 3;
+      dst[0] = gm; dst[1] = gs; dst[2] = tl;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(512)
+vocab_ce_finish_kernel(__nv_bfloat16* __restrict__ logits, const long long* __restrict__ targets,
+                       int Vl, long long ld, long long lo, long long T, int world,
+                       const float* __restrict__ stats /*[world][T][3]*/, long long ignore_index,
+                       float grad_scale, float* __restrict__ loss) {
+  const long long row = blockIdx.x;
+  float gm = -INFINITY;
+  for (int r = 0; r < world; ++r) gm = fmaxf(gm, stats[((long long)r * T + row) * 3]);
+  float gs = 0.f, tl = 0.f;
+  for (int r = 0; r < world; ++r) {
+    const float* st = stats + ((long long)r * T + row) * 3;
+    gs += st[1] * __expf(st[0] - gm);
+    tl += st[2];
+  }
+  const long long tgt_g = targets[row];
+  const bool ignored = tgt_g == ignore_index;
+  if (threadIdx.x == 0) loss[row] = ignored ? 0.f : gm + __logf(gs) - tl;
+  const long long tgt = tgt_g - lo;
+  const float inv = 1.f / gs;
+  const float scale = ignored ? 0.f : grad_scale;
+  __nv_bfloat16* lr = logits + row * ld;
+  const int vv = Vl >> 3;
+  for (int c = threadIdx.x; c < vv; c += blockDim.x) {
+    float f[8];
+    unpack8(ld_v4(reinterpret_cast<const uint4*>(lr) + c), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float pj = __expf(f[j] - gm) * inv;
+      if ((long long)(c * 8 + j) == tgt) pj -= 1.f;
+      f[j] = pj * scale;
+    }
+    reinterpret_cast<uint4*>(lr)[c] = pack8(f);
+  }
+}
+
 // Row softmax with optional causal / additive mask — the standalone
 // scaled_(upper_triang_)masked_softmax of Megatron; the
 // training path uses the fused attention kernel, this is kept for parity.
@@ -431,6 +527,29 @@ extern "C" int b2f_cross_entropy(const void* logits, const long long* targets, f
   cross_entropy_kernel<<<(unsigned)rows, 512, 0, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)logits, targets, loss, (__nv_bfloat16*)dlogits, V, ld, grad_scale,
       ignore_index);
+  B2F_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+// stats_ptrs: `world` device addresses of the [world][T][3] fp32 statistics buffer on every rank
+// (symmetric memory), or only entry `rank` non-zero when the exchange is done by a collective.
+extern "C" int b2f_vocab_ce_stats(const void* logits, const long long* targets, long long T, int Vl,
+                                  long long ld, long long lo, int rank, int world,
+                                  const long long* stats_ptrs, void* stream) {
+  B2F_REQUIRE(T > 0 && Vl > 0 && Vl % 8 == 0 && ld % 8 == 0, "vocab CE: shard width and ld must be multiples of 8");
+  B2F_REQUIRE(world >= 1 && world <= 8 && rank >= 0 && rank < world, "vocab CE: world must be 1..8");
+  CEPeers out;
+  for (int r = 0; r < 8; ++r) out.ptr[r] = r < world ? reinterpret_cast<float*>(stats_ptrs[r]) : nullptr;
+  vocab_ce_stats_kernel<<<(unsigned)T, 512, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)logits, targets, Vl, ld, lo, T, rank, world, out);
+  B2F_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int b2f_vocab_ce_finish(void* logits, const long long* targets, long long T, int Vl, long long ld,
+                                   long long lo, int world, const float* stats, long long ignore_index,
+                                   float grad_scale, float* loss, void* stream) {
+  B2F_REQUIRE(T > 0 && Vl > 0 && Vl % 8 == 0 && ld % 8 == 0, "vocab CE: shard width and ld must be multiples of 8");
+  vocab_ce_finish_kernel<<<(unsigned)T, 512, 0, (cudaStream_t)stream>>>(
+      (__nv_bfloat16*)logits, targets, Vl, ld, lo, T, world, stats, ignore_index, grad_scale, loss);
   B2F_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -111,6 +111,14 @@ int b2f_rope(void* x, const float* cos_t, const float* sin_t, long long tokens, 
 int b2f_cross_entropy(const void* logits, const long long* targets, float* loss, void* dlogits,
                       long long rows, int V, long long ld, float grad_scale,
                       long long ignore_index, void* stream);
+/* K9: cross-entropy over vocab-sharded logits (Megatron vocab_parallel_cross_entropy): per-row
+ * statistics {max, sum-exp, target logit} stored into slot `rank` of a [world][T][3] fp32 buffer on
+ * this GPU and (through mapped symmetric memory) on every peer, then loss + in-place gradient. */
+int b2f_vocab_ce_stats(const void* logits, const long long* targets, long long T, int Vl, long long ld,
+                       long long lo, int rank, int world, const long long* stats_ptrs, void* stream);
+int b2f_vocab_ce_finish(void* logits, const long long* targets, long long T, int Vl, long long ld,
+                        long long lo, int world, const float* stats, long long ignore_index,
+                        float grad_scale, float* loss, void* stream);
 int b2f_scaled_masked_softmax(const void* x, const void* mask, void* y, long long batch, int heads,
                               int sq, int sk, float scale, int causal, void* stream);
 int b2f_cast_f32_bf16(const float* x, void* y, long long n, float scale, void* stream);

@@ -84,5 +84,9 @@ def test_smoke_entry():
     g.smoke()
 
 
+def test_vocab_parallel_cross_entropy_kernels():
+    _run("vocab_ce")
+
+
 def test_gemm_cta_pair_kernel():
     _run("gemm2")

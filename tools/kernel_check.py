@@ -212,6 +212,38 @@ def group_norm_perf():
         RESULTS.append({"name": rec["name"], "ok": True})
 
 
+def group_vocab_ce():
+    """K9 on one GPU: two vocab shards of the same logits play the two ranks."""
+    import ctypes
+    from b200flow.ops import _lib
+    from b200flow.ops._lib import c_float, c_int, c_ll, ptr, stream_ptr
+    torch.manual_seed(11)
+    T, V, world = 300, 2048, 2
+    Vl = V // world
+    logits = (torch.randn(T, V, device=DEV) * 3).to(torch.bfloat16)
+    targets = torch.randint(0, V, (T,), device=DEV)
+    targets[::7] = -100
+    lf = logits.float().requires_grad_()
+    ref = torch.nn.functional.cross_entropy(lf, targets, ignore_index=-100, reduction="sum")
+    ref.backward()
+    shards = [logits[:, r * Vl:(r + 1) * Vl].contiguous() for r in range(world)]
+    stats = torch.zeros(world * T * 3, device=DEV)
+    both = (ctypes.c_longlong * world)(*[stats.data_ptr()] * world)
+    for r in range(world):
+        _lib.call("b2f_vocab_ce_stats", ptr(shards[r]), ptr(targets), c_ll(T), c_int(Vl), c_ll(Vl), c_ll(r * Vl),
+                  c_int(r), c_int(world), both, stream_ptr())
+    losses = []
+    for r in range(world):
+        loss = torch.empty(T, device=DEV)
+        _lib.call("b2f_vocab_ce_finish", ptr(shards[r]), ptr(targets), c_ll(T), c_int(Vl), c_ll(Vl), c_ll(r * Vl),
+                  c_int(world), ptr(stats), c_ll(-100), c_float(1.0), ptr(loss), stream_ptr())
+        losses.append(loss)
+    torch.cuda.synchronize()
+    report("vocab_ce_loss", losses[0].sum().reshape(1, 1), ref.detach().reshape(1, 1), 5e-3)
+    report("vocab_ce_loss_ranks_agree", losses[0].reshape(1, -1), losses[1].reshape(1, -1), 1e-6)
+    report("vocab_ce_grad", torch.cat(shards, 1), lf.grad, 2e-2)
+
+
 def group_optim():
     torch.manual_seed(3)
     for n in (1000003, 4096, 7):
@@ -636,6 +668,7 @@ GROUPS = {
     "gemm_tt": lambda: group_gemm("tt"),
     "gemm_epi": group_gemm_epi,
     "gemm_perf": group_gemm_perf,
+    "vocab_ce": group_vocab_ce,
     "norm": group_norm,
     "norm_perf": group_norm_perf,
     "optim": group_optim,
