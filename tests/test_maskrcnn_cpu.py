@@ -1,0 +1,46 @@
+"""Mask R-CNN through the launcher on CPU/gloo at test size: the `maskrcnn` chart (mpirun mode, two
+ranks, tensorpack command line: charts/machine-learning/training/maskrcnn/templates/maskrcnn.yaml:54-132)
+followed by the `maskrcnn-jupyter` chart (charts/machine-learning/testing/maskrcnn-jupyter), which finds
+the newest `model-*.index`, predicts and renders boxes + pasted masks headlessly."""
+import json
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+REPO = Path(__file__).resolve().parent.parent
+TINY = {"B2F_MRCNN_WIDTH": "0.125", "B2F_MRCNN_IMAGE": "128x128", "CUDA_VISIBLE_DEVICES": ""}
+
+
+def _install(release, chart, values, root, env):
+    cmd = [sys.executable, "-m", "b200flow.launcher", "install", release, chart, "-f", str(values),
+           "--root", str(root), "--max-restarts", "0"]
+    res = subprocess.run(cmd, cwd=REPO, env=dict(os.environ, **env), capture_output=True, text=True, timeout=900)
+    return res.returncode, json.loads(res.stdout.strip().splitlines()[-1]), res.stdout[-2000:] + res.stderr[-2000:]
+
+
+def test_maskrcnn_chart_then_jupyter_chart(tmp_root):
+    v = tmp_root / "train.yaml"
+    v.write_text("maskrcnn:\n  gpus: 2\n  gpu_nodes: 1\n  gpus_per_node: 2\n  steps_per_epoch: 2\n"
+                 "  lr_schedule: \"[4,6,8]\"\n")
+    rc, st, out = _install("mrcnn", "maskrcnn", v, tmp_root, dict(TINY, B2F_MRCNN_EPOCHS="2"))
+    assert rc == 0 and st["phase"] == "Succeeded" and len(st["pods"]) == 2, out
+    logdirs = list((tmp_root / "fsx/logs").iterdir())
+    assert len(logdirs) == 1
+    ck = logdirs[0] / "train_log/maskrcnn"
+    names = {p.name for p in ck.iterdir()}
+    # tensorpack ModelSaver layout + TensorBoard events + config dump (TRAIN.CHECKPOINT_PERIOD=2 from the chart)
+    assert {"checkpoint", "model-4.index", "model-4.pt", "config.json", "metrics.jsonl"} <= names
+    assert any(n.startswith("events.out.tfevents") for n in names)
+    cfg = json.loads((ck / "config.json").read_text())
+    assert cfg["world"] == 2 and cfg["config"]["MODE_MASK"] is True and cfg["config"]["TRAIN.CHECKPOINT_PERIOD"] == 2
+
+    j = tmp_root / "viz.yaml"
+    j.write_text(f"global:\n  log_dir: logs/{logdirs[0].name}\n")
+    rc, st, out = _install("viz", "maskrcnn-jupyter", j, tmp_root, TINY)
+    assert rc == 0 and st["phase"] == "Succeeded", out
+    viz = logdirs[0] / "visualization"
+    pngs = sorted(viz.glob("detections_*.png"))
+    assert pngs and pngs[0].read_bytes()[:8] == b"\x89PNG\r\n\x1a\n"
+    dets = json.loads((viz / "detections.json").read_text())
+    assert isinstance(dets, (list, dict)) and len(dets) > 0
