@@ -39,6 +39,7 @@ struct PeerTable {
 // Block-level barrier across ranks. flags: symmetric u32 array, layout [slot][world].
 __device__ __forceinline__ void cross_rank_block_barrier(const PeerTable& flags, int rank,
                                                          int world, int slot, uint32_t epoch) {
+  if (threadIdx.x == 0) race_delay();
   __syncthreads();
   if ((int)threadIdx.x < world) {
     const int p = threadIdx.x;

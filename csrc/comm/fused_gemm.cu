@@ -167,6 +167,7 @@ __device__ void ag_comm_role(const AGArgs& a, uint8_t* smem_raw) {
       ready_seen = srank;
     }
     const int slot = (int)(c % AG_SLOTS);
+    if (c % chunks_per_unit == 0) race_delay();
     mbar_arrive_expect_tx(&full[slot], bytes);
     bulk_load_1d(smem + slot * AG_CHUNK, src, bytes, &full[slot]);
   };
@@ -341,6 +342,8 @@ struct RSPolicy {
            ((size_t)src * blocks_per_rank + mb_local) * num_n + nb;
   }
   __device__ __forceinline__ void before_epilogue(int, int mb, int nb) const {
+    if ((threadIdx.x & 31) == 0) race_delay();
+    __syncwarp();
     tma_store_wait_read<0>();    // the staging rows of the previous tile have been read out
     if (owner_of(mb) != a.rank) return;
     flush();  // publish before waiting on the peers, or two ranks could wait on each other

@@ -368,6 +368,17 @@ __device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
 __device__ __forceinline__ void red_add_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+// Race-hunting build (-DB2F_RACE_DELAYS, tools/race_check.sh): pseudo-random pauses of up to ~30 us at
+// the hand-rolled synchronisation points (before a CTA joins a cross-GPU barrier, before a gather unit,
+// before a fused epilogue), so ranks and CTAs drift apart and a missing wait or fence shows up as a
+// wrong result instead of hiding behind lock-step timing.  Compiles to nothing otherwise.
+__device__ __forceinline__ void race_delay() {
+#ifdef B2F_RACE_DELAYS
+  unsigned h = (unsigned)clock64() * 2654435761u + blockIdx.x * 40503u + threadIdx.x;
+  h ^= h >> 15;
+  __nanosleep((h & 0x7fffu));
+#endif
+}
 // Spin until *p >= target (monotonic epoch counters). Traps on timeout.
 __device__ __forceinline__ void wait_flag_ge(const uint32_t* p, uint32_t target) {
   long long t0 = clock64();

@@ -136,6 +136,8 @@ moe_dispatch_kernel(const __nv_bfloat16* __restrict__ x, const int* __restrict__
   const int warps_per_block = blockDim.x >> 5;
   const int lane = threadIdx.x & 31;
   const int hv = H >> 3;
+  if (lane == 0) race_delay();
+  __syncwarp();
   for (int t = blockIdx.x * warps_per_block + (threadIdx.x >> 5); t < T; t += gridDim.x * warps_per_block) {
     const int e = expert[t];
     if (e < 0) continue;
