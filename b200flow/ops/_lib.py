@@ -56,6 +56,7 @@ def loaded_libraries() -> list[str]:
 
 _launches = 0
 # kernels launched per entry point (default 1)
+_NVTX = os.environ.get("B2F_NVTX", "0") == "1"
 _KERNELS_PER_CALL = {"b2f_norm_bwd": 2, "b2f_norm_bwd_noalloc": 2, "b2f_sumsq": 2, "b2f_attn_bwd": 3,
                      "b2f_moe_router_top1": 2}
 
@@ -92,7 +93,14 @@ def call(fn_name: str, *args) -> None:
     global _launches
     lib = cuda_lib()
     fn = getattr(lib, fn_name)
-    rc = fn(*args)
+    if _NVTX:       # B2F_NVTX=1: one NVTX range per native entry point (shows up in nsys / torch.profiler)
+        torch.cuda.nvtx.range_push(fn_name)
+        try:
+            rc = fn(*args)
+        finally:
+            torch.cuda.nvtx.range_pop()
+    else:
+        rc = fn(*args)
     _launches += _KERNELS_PER_CALL.get(fn_name, 1)
     if rc != 0:
         msg = lib.b2f_last_error()

@@ -234,8 +234,11 @@ def main():
             torch.cuda.synchronize()
         if rank == 0:
             Path(args.profile).parent.mkdir(parents=True, exist_ok=True)
-            Path(args.profile).write_text(prof.key_averages().table(sort_by="cuda_time_total", row_limit=40,
-                                                                     max_name_column_width=90))
+            if args.profile.endswith(".json"):     # chrome://tracing / Perfetto timeline
+                prof.export_chrome_trace(args.profile)
+            else:
+                Path(args.profile).write_text(prof.key_averages().table(sort_by="cuda_time_total", row_limit=40,
+                                                                         max_name_column_width=90))
     if rank == 0:
         val = tokens_per_step * args.steps / (ms / 1e3)
         val_e2e = tokens_per_step * args.steps / (ms_e2e / 1e3)
