@@ -35,10 +35,10 @@ __global__ void __launch_bounds__(RT)
 router_pass1_kernel(const float* __restrict__ logits, int T, int E, int* __restrict__ expert,
                     float* __restrict__ gate, float* __restrict__ probs, int* __restrict__ blk_cnt,
                     float* __restrict__ blk_me) {
-  __shared__ float me_s[MAX_E];
+  __shared__ float me_w[RT / 32][MAX_E];   // per-warp partial sums, added in warp order (deterministic)
   __shared__ int ce_s[MAX_E];
-  const int lane = threadIdx.x & 31;
-  for (int e = threadIdx.x; e < E; e += RT) { me_s[e] = 0.f; ce_s[e] = 0; }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int e = threadIdx.x; e < E; e += RT) ce_s[e] = 0;
   __syncthreads();
   const int t = blockIdx.x * RT + threadIdx.x;
   int best = -1;
@@ -58,10 +58,9 @@ router_pass1_kernel(const float* __restrict__ logits, int T, int E, int* __restr
       probs[(long long)t * E + e] = p;
       if (p > bp) { bp = p; best = e; }
     }
-    // warp-level sum first: one shared-memory atomic per warp and expert
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) p += __shfl_xor_sync(0xffffffffu, p, o);
-    if (lane == 0) atomicAdd(&me_s[e], p);
+    if (lane == 0) me_w[warp][e] = p;
   }
   for (int e = 0; e < E; ++e) {
     const unsigned m = __ballot_sync(0xffffffffu, best == e);
@@ -73,8 +72,10 @@ router_pass1_kernel(const float* __restrict__ logits, int T, int E, int* __restr
   }
   __syncthreads();
   for (int e = threadIdx.x; e < E; e += RT) {
+    float m = 0.f;
+    for (int w = 0; w < RT / 32; ++w) m += me_w[w][e];
     blk_cnt[blockIdx.x * E + e] = ce_s[e];
-    blk_me[blockIdx.x * E + e] = me_s[e];
+    blk_me[blockIdx.x * E + e] = m;
   }
 }
 

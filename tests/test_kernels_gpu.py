@@ -90,3 +90,49 @@ def test_vocab_parallel_cross_entropy_kernels():
 
 def test_gemm_cta_pair_kernel():
     _run("gemm2")
+
+
+def test_kernels_are_deterministic():
+    """Same inputs twice -> bit-identical outputs (no atomics in the GEMM / attention / norm / router paths;
+    the wgrad accumulate is one reducing store per output element per call)."""
+    from b200flow.ops import attention as A
+    from b200flow.ops import gemm as G
+    from b200flow.ops import norm as N
+    from b200flow.parallel.moe import route_top1
+
+    torch.manual_seed(0)
+    dev = "cuda"
+    a = torch.randn(1024, 512, device=dev, dtype=torch.bfloat16)
+    b = torch.randn(768, 512, device=dev, dtype=torch.bfloat16)
+    assert torch.equal(G.gemm(a, b), G.gemm(a, b))
+    acc1 = torch.zeros(512, 512, device=dev)
+    acc2 = torch.zeros(512, 512, device=dev)
+    x = torch.randn(1024, 512, device=dev, dtype=torch.bfloat16)
+    for acc in (acc1, acc2):
+        for _ in range(3):
+            G.gemm(a, x, a_mn_major=True, b_mn_major=True, out=acc, accumulate=True)
+    assert torch.equal(acc1, acc2)
+
+    qkv = torch.randn(2, 384, 3, 4, 128, device=dev, dtype=torch.bfloat16)
+    outs = []
+    for _ in range(2):
+        t = qkv.clone().requires_grad_()
+        o = A.flash_attention_qkvpacked(t, causal=True)
+        o.backward(torch.ones_like(o))
+        outs.append((o.detach().clone(), t.grad.clone()))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+
+    h = torch.randn(300, 1024, device=dev, dtype=torch.bfloat16)
+    grads = []
+    for _ in range(2):
+        xi = h.clone().requires_grad_()
+        g = torch.ones(1024, device=dev, dtype=torch.bfloat16, requires_grad=True)
+        y = N.norm(xi, g, None, rms=True, eps=1e-5)
+        y = y[0] if isinstance(y, tuple) else y
+        y.backward(torch.ones_like(y))
+        grads.append((xi.grad.clone(), g.grad.clone()))
+    assert torch.equal(grads[0][0], grads[1][0]) and torch.equal(grads[0][1], grads[1][1])
+
+    logits = torch.randn(5000, 8, device=dev)
+    r1, r2 = route_top1(logits, 700), route_top1(logits, 700)
+    assert all(torch.equal(r1[k], r2[k]) for k in ("expert", "slot", "gate", "counts", "me", "ce"))
