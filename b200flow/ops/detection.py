@@ -216,3 +216,85 @@ def mask_paste(probs, boxes, H: int, W: int, thr: float = 0.5):
     _lib.call("b2f_mask_paste", ptr(probs), c_int(probs.shape[-1]), ptr(boxes), c_int(probs.shape[0]),
               c_int(H), c_int(W), c_float(thr), ptr(out), stream_ptr())
     return out
+
+
+# --------------------------------------------------- K16: polygons and RLE (pycocotools maskApi)
+def _flatten_polys(objects):
+    """objects: list (per object) of lists of polygons, each [x0, y0, x1, y1, ...] (COCO `segmentation`)."""
+    xy, poly_off, obj_poly = [], [0], [0]
+    for polys in objects:
+        for p in polys:
+            pts = torch.as_tensor(p, dtype=torch.float32).reshape(-1, 2)
+            xy.append(pts)
+            poly_off.append(poly_off[-1] + pts.shape[0])
+        obj_poly.append(len(poly_off) - 1)
+    return torch.cat(xy) if xy else torch.zeros(0, 2), poly_off, obj_poly
+
+
+def poly_to_mask_ref(objects, H: int, W: int) -> torch.Tensor:
+    """CPU oracle: even-odd test at pixel centres, parts OR-ed.  uint8 [N, H, W]."""
+    out = torch.zeros(len(objects), H, W, dtype=torch.uint8)
+    px = torch.arange(W, dtype=torch.float32)[None, :] + 0.5
+    py = torch.arange(H, dtype=torch.float32)[:, None] + 0.5
+    for o, polys in enumerate(objects):
+        inside = torch.zeros(H, W, dtype=torch.bool)
+        for p in polys:
+            pts = torch.as_tensor(p, dtype=torch.float32).reshape(-1, 2)
+            odd = torch.zeros(H, W, dtype=torch.bool)
+            n = pts.shape[0]
+            for i in range(n):
+                xi, yi = pts[i]
+                xj, yj = pts[i - 1]
+                cond = (yi > py) != (yj > py)
+                if yj != yi:
+                    xc = (xj - xi) * (py - yi) / (yj - yi) + xi
+                    odd ^= cond & (px < xc)
+            inside |= odd
+        out[o] = inside.to(torch.uint8)
+    return out
+
+
+def poly_to_mask(objects, H: int, W: int, device=None) -> torch.Tensor:
+    """COCO polygon annotations -> uint8 masks [N, H, W] (K16 on a GPU, the oracle on CPU)."""
+    device = torch.device(device) if device is not None else torch.device("cuda" if torch.cuda.is_available() else "cpu")
+    if device.type != "cuda":
+        return poly_to_mask_ref(objects, H, W)
+    xy, poly_off, obj_poly = _flatten_polys(objects)
+    xy = xy.to(device).contiguous()
+    po = torch.tensor(poly_off, dtype=torch.int32, device=device)
+    op = torch.tensor(obj_poly, dtype=torch.int32, device=device)
+    out = torch.empty(len(objects), H, W, dtype=torch.uint8, device=device)
+    _lib.call("b2f_poly_to_mask", ptr(xy), ptr(po), ptr(op), c_int(len(objects)), c_int(H), c_int(W), ptr(out),
+              stream_ptr())
+    return out
+
+
+def rle_encode(mask: torch.Tensor) -> dict:
+    """COCO run-length encoding of one binary mask [H, W]: column-major runs, starting with a zero run."""
+    h, w = mask.shape
+    flat = mask.t().reshape(-1).to(torch.uint8).cpu()
+    change = torch.nonzero(flat[1:] != flat[:-1]).squeeze(-1) + 1
+    bounds = torch.cat([torch.tensor([0]), change, torch.tensor([flat.numel()])])
+    counts = (bounds[1:] - bounds[:-1]).tolist()
+    if flat.numel() and int(flat[0]) == 1:
+        counts = [0] + counts
+    return {"size": [h, w], "counts": counts}
+
+
+def rle_decode(rle: dict) -> torch.Tensor:
+    h, w = rle["size"]
+    vals = torch.zeros(len(rle["counts"]), dtype=torch.uint8)
+    vals[1::2] = 1
+    flat = torch.repeat_interleave(vals, torch.tensor(rle["counts"]))
+    return flat.reshape(w, h).t().contiguous()
+
+
+def rle_area(rle: dict) -> int:
+    return int(sum(rle["counts"][1::2]))
+
+
+def rle_iou(a: dict, b: dict) -> float:
+    ma, mb = rle_decode(a).bool(), rle_decode(b).bool()
+    inter = int((ma & mb).sum())
+    union = int((ma | mb).sum())
+    return inter / union if union else 0.0

@@ -312,6 +312,36 @@ int fill_pyramid(Pyramid* p, const void* const* feats, float* const* grads, cons
   return 0;
 }
 
+// ---- K16: polygon -> binary mask (pycocotools maskApi frPoly): one thread per pixel of
+// one object; even-odd crossing count at the pixel centre over all edges of the object's polygons
+// (a COCO object may have several parts; a pixel inside any part is set).
+//   xy          float [sum(points), 2] vertices of all polygons, object after object
+//   poly_off    int [P + 1]  first vertex of each polygon
+//   obj_poly    int [N + 1]  first polygon of each object
+__global__ void __launch_bounds__(256)
+poly_to_mask_kernel(const float* __restrict__ xy, const int* __restrict__ poly_off,
+                    const int* __restrict__ obj_poly, int H, int W, unsigned char* __restrict__ out) {
+  const int obj = blockIdx.y;
+  const long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (pix >= (long long)H * W) return;
+  const float px = (float)(pix % W) + 0.5f, py = (float)(pix / W) + 0.5f;
+  bool inside = false;
+  for (int pl = obj_poly[obj]; pl < obj_poly[obj + 1] && !inside; ++pl) {
+    const int v0 = poly_off[pl], n = poly_off[pl + 1] - v0;
+    bool odd = false;
+    for (int i = 0, j = n - 1; i < n; j = i++) {
+      const float xi = xy[2 * (v0 + i)], yi = xy[2 * (v0 + i) + 1];
+      const float xj = xy[2 * (v0 + j)], yj = xy[2 * (v0 + j) + 1];
+      if ((yi > py) != (yj > py)) {
+        const float xc = (xj - xi) * (py - yi) / (yj - yi) + xi;
+        if (px < xc) odd = !odd;
+      }
+    }
+    inside = odd;
+  }
+  out[(long long)obj * H * W + pix] = inside ? 1 : 0;
+}
+
 }  // namespace
 
 extern "C" int b2f_roi_align_fwd(const void* const* feats, const int* H, const int* W,
@@ -398,6 +428,16 @@ extern "C" int b2f_mask_paste(const float* probs, int M, const float* boxes, int
   if (R == 0) return 0;
   mask_paste_kernel<<<grid1d((long long)R * H * W), 256, 0, (cudaStream_t)stream>>>(probs, M, boxes, R, H,
                                                                                   W, thr, out);
+  B2F_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// masks: uint8 [N, H, W].  Vertices in pixel coordinates (x right, y down), as in COCO annotations.
+extern "C" int b2f_poly_to_mask(const float* xy, const int* poly_off, const int* obj_poly, int N, int H,
+                                int W, unsigned char* masks, void* stream) {
+  B2F_REQUIRE(N > 0 && H > 0 && W > 0, "poly_to_mask: bad shape");
+  const unsigned gx = (unsigned)(((long long)H * W + 255) / 256);
+  poly_to_mask_kernel<<<dim3(gx, (unsigned)N), 256, 0, (cudaStream_t)stream>>>(xy, poly_off, obj_poly, H, W, masks);
   B2F_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -192,6 +192,10 @@ int b2f_mask_crop(const unsigned char* masks, int H, int W, const float* rois, c
 int b2f_mask_paste(const float* probs, int M, const float* boxes, int R, int H, int W, float thr,
                    unsigned char* out, void* stream);
 
+/* K16: polygons -> binary masks (pycocotools frPoly): even-odd test at pixel centres, parts OR-ed. */
+int b2f_poly_to_mask(const float* xy, const int* poly_off, const int* obj_poly, int N, int H, int W,
+                     unsigned char* masks, void* stream);
+
 /* ---- K5a + MoE token movement (DeepSpeed top1gating + einsum dispatch/combine + all_to_all).
  * With peer_ptrs the dispatch stores rows straight into the expert owner's buffer
  * [src_rank, local_expert, capacity, H] and the combine pulls them back: the all-to-alls are

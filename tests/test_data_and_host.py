@@ -155,3 +155,24 @@ def test_shared_memory_mailbox_between_processes():
             ch.recv(timeout_ms=10)
     finally:
         ch.free()
+
+
+def test_polygon_rasteriser_oracle_and_rle_round_trip():
+    from b200flow.ops.detection import poly_to_mask_ref, rle_area, rle_decode, rle_encode, rle_iou
+
+    objects = [[[2, 2, 12, 2, 12, 9, 2, 9]],                              # axis-aligned box
+               [[1, 1, 6, 1, 6, 6, 1, 6], [10, 10, 15, 10, 15, 15, 10, 15]],   # two parts
+               [[8.0, 1.0, 15.0, 15.0, 1.0, 15.0]]]                         # triangle
+    m = poly_to_mask_ref(objects, 16, 16)
+    assert m.shape == (3, 16, 16) and m.dtype == torch.uint8
+    assert int(m[0].sum()) == 10 * 7 and bool(m[0, 2, 2]) and not bool(m[0, 9, 2])
+    assert int(m[1].sum()) == 25 + 25
+    assert 0 < int(m[2].sum()) < 14 * 14 // 2 + 14
+    for k in range(3):
+        r = rle_encode(m[k])
+        assert r["size"] == [16, 16] and sum(r["counts"]) == 256
+        assert torch.equal(rle_decode(r), m[k]) and rle_area(r) == int(m[k].sum())
+    full = rle_encode(torch.ones(4, 5, dtype=torch.uint8))
+    assert full["counts"] == [0, 20]
+    assert rle_iou(rle_encode(m[0]), rle_encode(m[0])) == 1.0
+    assert 0.0 < rle_iou(rle_encode(m[0]), rle_encode(m[2])) < 1.0

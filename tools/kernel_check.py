@@ -525,6 +525,27 @@ def group_detection():
     RESULTS.append({"name": "mask_paste", "ok": frac > 0.995, "agree": frac}); print(json.dumps(RESULTS[-1]), flush=True)
 
 
+    # K16 polygon rasteriser against the pixel-centre even-odd oracle
+    from b200flow.ops import detection as Dm
+    g = torch.Generator().manual_seed(5)
+    objs = []
+    for o in range(6):
+        parts = []
+        for _ in range(1 + o % 2):
+            n = 3 + int(torch.randint(0, 6, (1,), generator=g))
+            cx, cy = (torch.rand(2, generator=g) * 100 + 30).tolist()
+            ang = torch.sort(torch.rand(n, generator=g) * 6.2831853)[0]
+            rad = torch.rand(n, generator=g) * 25 + 8
+            pts = torch.stack([cx + rad * torch.cos(ang), cy + rad * torch.sin(ang)], 1).reshape(-1)
+            parts.append(pts.tolist())
+        objs.append(parts)
+    got = Dm.poly_to_mask(objs, 160, 200, device=DEV)
+    want = Dm.poly_to_mask_ref(objs, 160, 200)
+    diff = int((got.cpu() != want).sum())       # fp contraction may move a pixel lying exactly on an edge
+    RESULTS.append({"name": "poly_to_mask", "ok": diff <= 4 and int(want.sum()) > 1000, "mismatched_pixels": diff,
+                    "set_pixels": int(want.sum())})
+    print(json.dumps(RESULTS[-1]), flush=True)
+
 def group_maskrcnn_step():
     from b200flow.data.synthetic import coco_like
     from b200flow.models.maskrcnn import MaskRCNN, MaskRCNNConfig, paste_masks
