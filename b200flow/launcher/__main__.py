@@ -41,6 +41,9 @@ def main(argv=None) -> int:
         p.add_argument("--timeout", type=float, default=None)
         p.add_argument("--inject-fault", default=None, help="rank=R,step=S,kind={exit,hang,sigkill}")
         p.add_argument("--max-restarts", type=int, default=None)
+        p.add_argument("--auto-resume", action="store_true",
+                       help="restarted (or re-installed) workloads continue from their newest checkpoint even though the "
+                            "values file passes no --load / --resume_from_checkpoint (the reference's examples do not)")
         _common(p)
     for name in ("uninstall", "status", "logs"):
         p = sub.add_parser(name)
@@ -59,7 +62,8 @@ def main(argv=None) -> int:
             print(script)
             return 0
         run = R.Runner(plan, a.root, offline=not a.online, fault=a.inject_fault,
-                       max_restarts=a.max_restarts)
+                       max_restarts=a.max_restarts,
+                       extra_env={"B2F_AUTO_RESUME": "1"} if a.auto_resume else None)
         rc = run.run(timeout=a.timeout)
         print(json.dumps(R.status(a.root, a.release)))
         return rc

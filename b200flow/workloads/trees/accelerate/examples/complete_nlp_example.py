@@ -81,6 +81,10 @@ def training_function(config, args):
         model, optimizer, train_dl, eval_dl, lr_scheduler)
 
     overall_step, starting_epoch, resume_step = 0, 0, None
+    if not args.resume_from_checkpoint and os.environ.get("B2F_AUTO_RESUME") == "1" and args.output_dir and \
+            os.path.isdir(args.output_dir) and any(d.is_dir() and d.name.startswith(("epoch_", "step_"))
+                                                   for d in os.scandir(args.output_dir)):
+        args.resume_from_checkpoint = "latest"     # launcher --auto-resume
     if args.resume_from_checkpoint:
         path = args.resume_from_checkpoint
         if path in ("", "latest", True):

@@ -157,6 +157,8 @@ def main():
             step += 1
 
     start = 0
+    if not args.load and args.save and os.environ.get("B2F_AUTO_RESUME") == "1":
+        args.load = args.save          # launcher --auto-resume: continue from what this job saved before
     if args.load and os.path.exists(os.path.join(args.load, "latest")):
         path, client = engine.load_checkpoint(args.load)
         start = engine.global_steps
