@@ -41,6 +41,8 @@ def main(argv=None) -> int:
         p.add_argument("--timeout", type=float, default=None)
         p.add_argument("--inject-fault", default=None, help="rank=R,step=S,kind={exit,hang,sigkill}")
         p.add_argument("--max-restarts", type=int, default=None)
+        p.add_argument("--hang-timeout", type=float, default=None,
+                       help="seconds of total log silence after which the process group is killed and restarted")
         p.add_argument("--auto-resume", action="store_true",
                        help="restarted (or re-installed) workloads continue from their newest checkpoint even though the "
                             "values file passes no --load / --resume_from_checkpoint (the reference's examples do not)")
@@ -64,7 +66,7 @@ def main(argv=None) -> int:
         run = R.Runner(plan, a.root, offline=not a.online, fault=a.inject_fault,
                        max_restarts=a.max_restarts,
                        extra_env={"B2F_AUTO_RESUME": "1"} if a.auto_resume else None)
-        rc = run.run(timeout=a.timeout)
+        rc = run.run(timeout=a.timeout, hang_timeout=a.hang_timeout)
         print(json.dumps(R.status(a.root, a.release)))
         return rc
     if a.cmd == "uninstall":

@@ -249,8 +249,22 @@ class Runner:
         self._stop = True
         self._kill_all()
 
-    def run(self, timeout: float | None = None, poll: float = 0.2) -> int:
-        """Run to completion. Returns 0 on success, the failing exit code otherwise."""
+    def _log_progress(self) -> int:
+        """Total bytes the pods have logged so far: the job's heartbeat."""
+        total = 0
+        for f in (self.state.dir / "pods").glob("*/stdout.log"):
+            try:
+                total += f.stat().st_size
+            except OSError:
+                pass
+        return total
+
+    def run(self, timeout: float | None = None, poll: float = 0.2, hang_timeout: float | None = None) -> int:
+        """Run to completion. Returns 0 on success, the failing exit code otherwise.
+
+        `hang_timeout`: seconds without a single new log byte from any pod after which the group is declared
+        hung (exit code 125), killed and restarted like any other failure — the local stand-in for the NCCL
+        watchdog / lost-heartbeat detection a cluster would provide."""
         self.prepare()
         old = {}
         for s in (signal.SIGINT, signal.SIGTERM):
@@ -267,6 +281,7 @@ class Runner:
                 self.state.write_status(phase="Running", restarts=self.restarts,
                                         pods={s.name: p.pid for s, p in zip(specs, self.procs)})
                 failed = None
+                seen, seen_at = self._log_progress(), time.time()
                 while True:
                     codes = [p.poll() for p in self.procs]
                     bad = [c for c in codes if c not in (None, 0)]
@@ -279,6 +294,13 @@ class Runner:
                         failed = 124
                         self._stop = True
                         break
+                    if hang_timeout is not None:
+                        now_bytes = self._log_progress()
+                        if now_bytes != seen:
+                            seen, seen_at = now_bytes, time.time()
+                        elif time.time() - seen_at > hang_timeout:
+                            failed = 125
+                            break
                     if self._stop:
                         failed = 130
                         break

@@ -141,3 +141,16 @@ def test_auto_resume_continues_from_checkpoint_after_a_fault(tmp_root):
     assert "injected fault exit at rank 0 step 3" in logs
     assert "successfully loaded checkpoint" in logs and "at iteration 2" in logs      # saved at 2, died at 3
     assert "iteration        5/       5" in logs
+
+
+def test_hang_is_detected_and_the_group_restarted(tmp_root):
+    values = EX / "megatron-deepspeed/gpt2_345m/pretrain-ddp-zero1.yaml"
+    cmd = [sys.executable, "-m", "b200flow.launcher", "install", "hng", "pytorchjob-distributed", "-f", str(values),
+           "--root", str(tmp_root), "--max-restarts", "2", "--strict-exit", "--hang-timeout", "12", "--inject-fault",
+           "rank=1,step=2,kind=hang", "--set", "resources.nnodes=1", "--set", "resources.nproc_per_node=2"]
+    env = dict(os.environ, B2F_TRAIN_ITERS="3", B2F_OVERRIDE_ARGS=TINY_GPT, CUDA_VISIBLE_DEVICES="")
+    res = subprocess.run(cmd, cwd=REPO, env=env, capture_output=True, text=True, timeout=900)
+    st = json.loads(res.stdout.strip().splitlines()[-1])
+    assert res.returncode == 0 and st["phase"] == "Succeeded" and st["restarts"] == 1, res.stdout[-2000:]
+    logs = (tmp_root / ".b200flow/releases/hng/pods/hng-master-0/stdout.log").read_text()
+    assert "injected fault hang at rank 1 step 2" in logs and "iteration        3/       3" in logs
