@@ -72,14 +72,26 @@ def expert_optim_file(ep: int, tp: int) -> str:
     return f"expp_rank_{ep}_mp_rank_{tp:02d}_optim_states.pt"
 
 
-def _split_expert_state(sd: dict):
+_EXPERT_TENSORS = ("w1", "b1", "w2", "b2")     # MoELayer keeps its local experts batched: [E_local, ...]
+
+
+def _split_expert_state(sd: dict, ep_rank: int = 0):
+    """dense state dict + {(layer, global expert id): {key: that expert's slice}}."""
     dense, experts = {}, {}
     for k, v in sd.items():
-        if ".experts." in k:
-            experts[k] = v
+        parts = k.split(".")
+        if len(parts) >= 2 and parts[-2] == "moe" and parts[-1] in _EXPERT_TENSORS and v.dim() >= 2:
+            L = int(parts[parts.index("layers") + 1]) if "layers" in parts else 0
+            for e in range(v.shape[0]):
+                experts.setdefault((L, ep_rank * v.shape[0] + e), {})[k] = v[e].clone()
         else:
             dense[k] = v
     return dense, experts
+
+
+def _ep_rank(engine) -> int:
+    ctx = getattr(engine, "ep_ctx", None)
+    return int(getattr(ctx, "rank", 0)) if ctx is not None else 0
 
 
 def save_checkpoint(engine, save_dir: str, tag: str | None = None, client_state: dict | None = None,
@@ -110,15 +122,9 @@ def save_checkpoint(engine, save_dir: str, tag: str | None = None, client_state:
             if engine.stage == 0:
                 _write({"module": None, **client}, d / model_states_file(tp), async_save)
         else:
-            dense, experts = _split_expert_state(_cpu(model.state_dict()))
+            dense, experts = _split_expert_state(_cpu(model.state_dict()), _ep_rank(engine))
             _write({"module": dense, **client}, d / model_states_file(tp), async_save)
-            by = {}
-            for k, v in experts.items():     # "...layers.<L>....experts.<E>...."
-                parts = k.split(".")
-                L = int(parts[parts.index("layers") + 1]) if "layers" in parts else 0
-                E = int(parts[parts.index("experts") + 1])
-                by.setdefault((L, E), {})[k] = v
-            for (L, E), sd in by.items():
+            for (L, E), sd in experts.items():     # one file per (layer, global expert), as DeepSpeed MoE does
                 _write(sd, d / expert_file(L, E, tp), async_save)
     osd = engine.optimizer.state_dict()
     osd = {k: (v.detach().cpu() if isinstance(v, torch.Tensor) else v) for k, v in osd.items()}
@@ -127,6 +133,11 @@ def save_checkpoint(engine, save_dir: str, tag: str | None = None, client_state:
     if pp_world > 1:   # one file per (stage, dp, tp): stage goes into the DeepSpeed "pp_rank" slot
         name = ("bf16_" if bf16 else "") + f"zero_pp_rank_{dp + engine.dp_world * engine.stage}_mp_rank_{tp:02d}_optim_states.pt"
     _write({"optimizer_state_dict": osd, "ds_version": "b200flow"}, d / name, async_save)
+    eopt = getattr(engine, "expert_optimizer", None)
+    if eopt is not None:        # expert parameters have their own (expert-data-parallel) optimizer shard
+        esd = {k: (v.detach().cpu() if isinstance(v, torch.Tensor) else v) for k, v in eopt.state_dict().items()}
+        _write({"optimizer_state_dict": esd, "ds_version": "b200flow"}, d / expert_optim_file(_ep_rank(engine), tp),
+               async_save)
     if dist.is_initialized():
         dist.barrier()
     if (not dist.is_initialized()) or dist.get_rank() == 0:
@@ -167,14 +178,26 @@ def load_checkpoint(engine, load_dir: str, tag: str | None = None):
     else:
         client = torch.load(d / model_states_file(tp), map_location="cpu", weights_only=False)
         sd = dict(client.pop("module"))
-        for f in d.glob(f"layer_*_expert_*_mp_rank_{tp:02d}_model_states.pt"):
-            sd.update(torch.load(f, map_location="cpu"))
+        own = model.state_dict()
+        ep_rank = _ep_rank(engine)
+        for k, v in own.items():     # restack this rank's experts from the per-expert files
+            parts = k.split(".")
+            if len(parts) >= 2 and parts[-2] == "moe" and parts[-1] in _EXPERT_TENSORS and v.dim() >= 2:
+                L = int(parts[parts.index("layers") + 1]) if "layers" in parts else 0
+                rows = [torch.load(d / expert_file(L, ep_rank * v.shape[0] + e, tp), map_location="cpu")[k]
+                        for e in range(v.shape[0])]
+                sd[k] = torch.stack(rows)
         model.load_state_dict(sd, strict=False)
         name = optim_file(dp, tp, bf16)
     osd = torch.load(d / name, map_location="cpu", weights_only=False)["optimizer_state_dict"]
     dev = engine.flat.params.device
     osd = {k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in osd.items()}
     engine.optimizer.load_state_dict(osd)
+    eopt = getattr(engine, "expert_optimizer", None)
+    ef = d / expert_optim_file(_ep_rank(engine), tp)
+    if eopt is not None and ef.exists():
+        esd = torch.load(ef, map_location="cpu", weights_only=False)["optimizer_state_dict"]
+        eopt.load_state_dict({k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in esd.items()})
     engine.global_steps = int(client.get("global_steps", osd.get("step", 0)))
     if "rng_state" in client:
         torch.set_rng_state(client["rng_state"])
