@@ -154,3 +154,20 @@ def test_hang_is_detected_and_the_group_restarted(tmp_root):
     assert res.returncode == 0 and st["phase"] == "Succeeded" and st["restarts"] == 1, res.stdout[-2000:]
     logs = (tmp_root / ".b200flow/releases/hng/pods/hng-master-0/stdout.log").read_text()
     assert "injected fault hang at rank 1 step 2" in logs and "iteration        3/       3" in logs
+
+
+def test_accelerate_auto_resume_from_epoch_checkpoint(tmp_root):
+    values = EX / "accelerate/bert-glue-mrpc/pretrain.yaml"
+    env = {"B2F_MODEL": "bert-tiny", "B2F_TRAIN_SAMPLES": "64", "B2F_EVAL_SAMPLES": "32"}
+    rc, st, logs = _install("acr", "pytorchjob-elastic", values, tmp_root, sets=["resources.nproc_per_node=2"],
+                            env=dict(env, B2F_EPOCHS="1"))
+    assert rc == 0 and st["phase"] == "Succeeded", logs[-2000:]
+    ck = tmp_root / "efs/home/acr/checkpoints/acr-worker-0"
+    assert (ck / "epoch_0").is_dir()
+    # second install of the same release: with --auto-resume it loads epoch_0 and only trains epoch 1
+    rc, st, logs = _install("acr", "pytorchjob-elastic", values, tmp_root, sets=["resources.nproc_per_node=2"],
+                            env=dict(env, B2F_EPOCHS="2"), extra=["--auto-resume"])
+    assert rc == 0 and st["phase"] == "Succeeded", logs[-2000:]
+    assert "Resumed from checkpoint" in logs and (ck / "epoch_1").is_dir()
+    log = (tmp_root / "efs/home/acr/logs/acr-worker-0/pretrain.log").read_text()
+    assert "epoch 1:" in log
