@@ -16,7 +16,6 @@ from __future__ import annotations
 import contextlib
 import math
 import os
-from pathlib import Path
 
 import torch
 import torch.distributed as dist

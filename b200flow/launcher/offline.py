@@ -15,7 +15,6 @@ is no network, so the launcher prepends a directory of tiny executables to `PATH
 """
 from __future__ import annotations
 
-import os
 import stat
 import sys
 from pathlib import Path

@@ -28,7 +28,6 @@ import re
 import signal
 import socket
 import subprocess
-import sys
 import time
 from dataclasses import asdict
 from pathlib import Path

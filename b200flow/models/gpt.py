@@ -14,7 +14,7 @@ kernels under tensor + sequence parallelism.
 from __future__ import annotations
 
 import math
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 
 import torch
 from torch import nn

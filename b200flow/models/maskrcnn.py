@@ -12,7 +12,7 @@ the fc layers (K0) — runs on b200flow kernels.
 from __future__ import annotations
 
 import math
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 
 import torch
 import torch.nn.functional as F

@@ -14,7 +14,6 @@ replicated 7B model, not TP2·PP2·DP2.
 from __future__ import annotations
 
 import json
-import math
 
 import torch
 import torch.distributed as dist

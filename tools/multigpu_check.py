@@ -10,7 +10,6 @@ import itertools
 import json
 import os
 import sys
-import time
 from pathlib import Path
 
 import torch

@@ -10,7 +10,6 @@ from __future__ import annotations
 
 import re
 import subprocess
-import sys
 from collections import Counter, OrderedDict
 from pathlib import Path
 

@@ -1,6 +1,6 @@
 """Sustained (power-capped) GEMM throughput: each kernel runs back-to-back for ~3 s while nvidia-smi
 clocks and power are sampled.  Burst numbers hide this: the end-to-end step runs at the power cap."""
-import json, os, subprocess, sys, threading, time
+import json, subprocess, sys, threading, time
 import torch
 sys.path.insert(0, "/root/repo")
 from b200flow.ops import gemm as G
