@@ -121,7 +121,11 @@ def main():
                                  "eps": args.adam_eps, "weight_decay": args.weight_decay}},
         "scheduler": {"params": {"max_lr": args.lr, "min_lr": args.min_lr, "warmup_steps": warm,
                                  "decay_steps": decay_iters}},
-        "sequence_parallel": bool(args.sequence_parallel) or tp == 1,
+        # Megatron's --sequence-parallel only changes where activations live between the TP linears; the
+        # numerics are the same.  The engine therefore shards the sequence whenever TP > 1 (that is the form
+        # the fused all-gather->GEMM / GEMM->reduce-scatter kernels implement) unless B2F_AUTO_SP=0 asks for
+        # the replicated-activation + all-reduce form of a run without the flag.
+        "sequence_parallel": bool(args.sequence_parallel) or tp == 1 or os.environ.get("B2F_AUTO_SP", "1") != "0",
         "activation_checkpointing": {"enabled": args.checkpoint_activations},
         "fused_collectives": os.environ.get("B2F_FUSED", "1") == "1",
     }
