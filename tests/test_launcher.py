@@ -92,3 +92,37 @@ def test_pipeline_stops_at_first_failure_and_always_uninstalls(tmp_root):
     assert R.status(tmp_root, "p-never") == {}
     assert any("uninstalled p-bad" in m for m in msgs)
     assert run_pipeline([ok], root=str(tmp_root), log=msgs.append) == "Success"
+
+
+def test_data_charts_run_offline_and_are_idempotent(tmp_root):
+    """`coco-data` and `redpajama-data` (charts/machine-learning/data-prep/*): offline they write synthetic
+    stand-ins in the layout the training charts expect; like the reference's pod, a second run leaves an
+    existing data directory alone (coco-data.yaml:13 exits when the directory exists)."""
+    import json
+    import subprocess
+    import sys
+
+    v = tmp_root / "empty.yaml"
+    v.write_text("{}\n")
+
+    def install(release, chart):
+        cmd = [sys.executable, "-m", "b200flow.launcher", "install", release, chart, "-f", str(v),
+               "--root", str(tmp_root), "--max-restarts", "0"]
+        res = subprocess.run(cmd, cwd=Path(__file__).resolve().parent.parent, capture_output=True, text=True,
+                             timeout=600, env=dict(os.environ, CUDA_VISIBLE_DEVICES=""))
+        return res.returncode, json.loads(res.stdout.strip().splitlines()[-1])
+
+    rc, st = install("d-coco", "coco-data")
+    assert rc == 0 and st["phase"] == "Succeeded" and st["kind"] == "pod"
+    coco = tmp_root / "fsx/data/coco2017"
+    assert {"train2017", "val2017", "annotations", "pretrained-models"} <= {p.name for p in coco.iterdir()}
+    marker = coco / "annotations" / "keep.me"
+    marker.write_text("x")
+    rc, st = install("d-coco", "coco-data")
+    assert rc == 0 and marker.exists()            # untouched on the second run
+
+    rc, st = install("d-rp", "redpajama-data")
+    assert rc == 0 and st["phase"] == "Succeeded"
+    jl = tmp_root / "fsx/data/redpajama/data.jsonl"
+    first = json.loads(jl.read_text().splitlines()[0])
+    assert isinstance(first.get("text"), str) and len(first["text"]) > 0
