@@ -126,9 +126,18 @@ def save_checkpoint(engine, save_dir: str, tag: str | None = None, client_state:
             _write({"module": dense, **client}, d / model_states_file(tp), async_save)
             for (L, E), sd in experts.items():     # one file per (layer, global expert), as DeepSpeed MoE does
                 _write(sd, d / expert_file(L, E, tp), async_save)
+    elif getattr(engine, "ep_world", 1) > 1 and dp < engine.ep_world and pp_world == 1:
+        # the other EP ranks of the first expert-data-parallel replica own the remaining experts
+        _, experts = _split_expert_state(_cpu(model.state_dict()), _ep_rank(engine))
+        for (L, E), sd in experts.items():
+            _write(sd, d / expert_file(L, E, tp), async_save)
     osd = engine.optimizer.state_dict()
     osd = {k: (v.detach().cpu() if isinstance(v, torch.Tensor) else v) for k, v in osd.items()}
     osd["stage"] = engine.stage
+    scaler = getattr(engine, "loss_scaler", None)
+    if scaler is not None:     # DeepSpeed keeps the fp16 loss-scale state with the optimizer state
+        osd["loss_scaler"] = scaler.state_dict()
+        osd["skipped_steps"] = engine.skipped_steps
     name = optim_file(dp, tp, bf16)
     if pp_world > 1:   # one file per (stage, dp, tp): stage goes into the DeepSpeed "pp_rank" slot
         name = ("bf16_" if bf16 else "") + f"zero_pp_rank_{dp + engine.dp_world * engine.stage}_mp_rank_{tp:02d}_optim_states.pt"
@@ -193,6 +202,9 @@ def load_checkpoint(engine, load_dir: str, tag: str | None = None):
     dev = engine.flat.params.device
     osd = {k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in osd.items()}
     engine.optimizer.load_state_dict(osd)
+    if getattr(engine, "loss_scaler", None) is not None and "loss_scaler" in osd:
+        engine.loss_scaler.load_state_dict(osd["loss_scaler"])
+        engine.skipped_steps = int(osd.get("skipped_steps", 0))
     eopt = getattr(engine, "expert_optimizer", None)
     ef = d / expert_optim_file(_ep_rank(engine), tp)
     if eopt is not None and ef.exists():

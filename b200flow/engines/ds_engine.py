@@ -10,7 +10,9 @@ examples/megatron-deepspeed/gpt2_345m/pretrain-ddp-tp-pp-zero1.yaml:33-38,74-85)
     engine.save_checkpoint(dir) / engine.load_checkpoint(dir)
 
 Recognised ds_config keys: train_micro_batch_size_per_gpu, gradient_accumulation_steps,
-zero_optimization.stage (0/1), bf16.enabled / fp16.enabled, gradient_clipping,
+zero_optimization.stage (0/1), bf16.enabled, fp16.{enabled, loss_scale, initial_scale_power,
+loss_scale_window, hysteresis, min_loss_scale} (dynamic loss scaling with skipped steps; the
+compute dtype stays bf16), gradient_clipping,
 optimizer.params.{lr,betas,eps,weight_decay}, wall_clock_breakdown.  Unknown keys warn.
 
 Internals are b200flow's own: flat bf16 params + fp32 main_grad, tcgen05 kernels,
@@ -27,6 +29,7 @@ import torch.distributed as dist
 from ..models.gpt import GPTConfig, GPTModel
 from ..parallel import pipeline as PP
 from ..parallel.groups import ParallelState
+from ..parallel.loss_scaler import make_loss_scaler
 from ..parallel.tensor_parallel import SINGLE, TPContext, allreduce_replicated_grads
 from ..parallel.zero1 import AdamConfig, Zero1Optimizer, cosine_lr
 from ..utils.flat import FlatParams
@@ -156,6 +159,10 @@ class TrainEngine:
             o = self.optimizer      # master copy of the re-tied head rows
             o.master.copy_(self.flat.params[o.lo:o.hi].float())
         self.sched = config.get("scheduler", {}).get("params", None)
+        # "fp16": {"enabled": true} keeps DeepSpeed's loss-scale state machine (parallel/loss_scaler.py)
+        self.loss_scaler = make_loss_scaler(config.get("fp16"))
+        self.skipped_steps = 0
+        self._overflow = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.global_steps = 0
         self.p2p = None
         self.last_loss = None
@@ -175,10 +182,14 @@ class TrainEngine:
     def _forward_micro(self, batch, act):
         tokens, labels = batch
         b, s = tokens.shape
+        last = self.stage == self.pp_world - 1
         if self.stage == 0:
-            return self.model(tokens=tokens, labels=labels if self.pp_world == 1 else None)
-        return self.model(hidden=act, labels=labels if self.stage == self.pp_world - 1 else None,
-                          seq=s, batch=b)
+            out = self.model(tokens=tokens, labels=labels if self.pp_world == 1 else None)
+        else:
+            out = self.model(hidden=act, labels=labels if last else None, seq=s, batch=b)
+        if last and self.loss_scaler is not None and torch.is_grad_enabled():
+            out = out * self.loss_scaler.scale     # backward sees the scaled loss
+        return out
 
     def train_batch(self, data_iter: Iterator) -> torch.Tensor:
         """One optimizer step over `gradient_accumulation_steps` micro-batches.
@@ -204,23 +215,46 @@ class TrainEngine:
             self.flat_expert.collect_autograd_grads()
         allreduce_replicated_grads(self.flat, self.tp)
         self._reduce_tied_grads()
-        self._apply_lr()
-        self.optimizer.step(grad_divisor=float(self.gas * self.dp_world))
-        if self.expert_optimizer is not None:
-            self.expert_optimizer.lr = self.optimizer.lr
-            self.expert_optimizer.step(grad_divisor=float(self.gas * self.dp_world))
+        div, scale = float(self.gas * self.dp_world), 1.0
+        overflow = False
+        if self.loss_scaler is not None:
+            scale = self.loss_scaler.scale
+            div *= scale                            # the unscale rides on the gradient divisor
+            overflow = self._grads_overflowed()
+            self.loss_scaler.update(overflow)
+        if overflow:                                # DeepSpeed: skip the update and the lr step
+            self.skipped_steps += 1
+        else:
+            self._apply_lr()
+            self.optimizer.step(grad_divisor=div)
+            if self.expert_optimizer is not None:
+                self.expert_optimizer.lr = self.optimizer.lr
+                self.expert_optimizer.step(grad_divisor=div)
         self.global_steps += 1
         loss = torch.stack(losses).mean() if losses else torch.zeros((), device=self.device)
+        if scale != 1.0:
+            loss = loss / scale
         if self.pp_world > 1:  # make the loss visible on every stage (for logging)
             dist.broadcast(loss, src=self.ps.pp_ranks[-1], group=self.ps.pp_group)
         self.last_loss = loss
         return loss
 
-    def eval_batch(self, data_iter: Iterator) -> torch.Tensor:
+    def eval_batch(self, data_iter: Iterator, num_micro_batches: int = 1) -> torch.Tensor:
+        """Forward-only loss over `num_micro_batches` micro-batches (Megatron's `--eval-iters` loop calls
+        this; examples/megatron-deepspeed/gpt2_345m/pretrain-ddp-tp-pp-zero1.yaml:57).  Under pipeline
+        parallelism the micro-batches stream through the stages and every stage returns the loss."""
+        batches = [next(data_iter) for _ in range(num_micro_batches)]
         with torch.no_grad():
-            assert self.pp_world == 1, "eval_batch under PP: use train_batch with lr=0 or pp=1"
-            tokens, labels = next(data_iter)
-            return self.model(tokens=tokens, labels=labels)
+            if self.pp_world == 1:
+                losses = [self.model(tokens=t, labels=l) for t, l in batches]
+            else:
+                seq = batches[0][0].shape[1]
+                losses = PP.run_forward_only(self.stage, self.pp_world, num_micro_batches,
+                                             lambda i, act: self._forward_micro(batches[i], act), self._p2p(seq))
+            loss = torch.stack(losses).mean() if losses else torch.zeros((), device=self.device)
+            if self.pp_world > 1:
+                dist.broadcast(loss, src=self.ps.pp_ranks[-1], group=self.ps.pp_group)
+        return loss
 
     def _tied_slice(self, t):
         """Stage 0 keeps the whole (replicated) embedding table, the last stage a vocab-parallel
@@ -259,10 +293,32 @@ class TrainEngine:
         dist.all_gather(parts, mine.contiguous(), group=self.ps.tp_group)
         full.copy_(torch.cat(parts, 0))
 
+    def _grads_overflowed(self) -> bool:
+        """inf/nan anywhere in this rank's gradients, agreed on by every rank (MAX all-reduce:
+        SURVEY.md §2H C6).  Costs one pass over the gradients and a host sync, fp16 mode only."""
+        from ..ops import optim as O
+
+        self._overflow.zero_()
+        for flat in (self.flat, self.flat_expert):
+            if flat is None:
+                continue
+            if flat.grads.is_cuda:
+                O.sumsq(flat.grads, overflow=self._overflow)
+            elif not bool(torch.isfinite(flat.grads).all()):
+                self._overflow.fill_(1)
+        if self.ps is not None and dist.is_initialized() and dist.get_world_size() > 1:
+            dist.all_reduce(self._overflow, op=dist.ReduceOp.MAX)
+        return bool(self._overflow.item())
+
+    @property
+    def loss_scale(self) -> float:
+        return self.loss_scaler.scale if self.loss_scaler is not None else 1.0
+
     def _apply_lr(self):
         if self.sched:
             p = self.sched
-            self.optimizer.lr = cosine_lr(self.global_steps + 1, base_lr=float(p["max_lr"]),
+            self.optimizer.lr = cosine_lr(self.global_steps - self.skipped_steps + 1,
+                                          base_lr=float(p["max_lr"]),
                                           min_lr=float(p.get("min_lr", 0.0)),
                                           warmup_steps=int(p.get("warmup_steps", 0)),
                                           decay_steps=int(p.get("decay_steps", 1)))

@@ -48,6 +48,8 @@ class GPTConfig:
     moe_every: int = 2            # --expert-interval
     capacity_factor: float = 1.0
     aux_loss_coeff: float = 0.01
+    moe_top_k: int = 1            # --topk (DeepSpeed TopKGate: 1 or 2)
+    moe_min_capacity: int = 4     # --moe-min-capacity
     moe_fp8: bool = False         # expert GEMMs (forward + dgrad) in e4m3
 
     def __post_init__(self):
@@ -204,7 +206,8 @@ class TransformerLayer(nn.Module):
             assert tp.world == 1 and cfg.act == "gelu", "MoE layers: TP=1, GELU experts (GPT-MoE recipe)"
             self.moe = MoELayer(H, cfg.ffn, cfg.num_experts, ep, cfg.capacity_factor, act="gelu",
                                 aux_loss_coeff=cfg.aux_loss_coeff, init_std=std, dtype=dtype, device=device,
-                                fused=fused_moe, fp8=cfg.moe_fp8)
+                                fused=fused_moe, fp8=cfg.moe_fp8, top_k=cfg.moe_top_k,
+                                min_capacity=cfg.moe_min_capacity)
             self.w1 = self.w2 = None
         else:
             self.w1 = nn.Parameter(torch.empty(n_up, H, **kw).normal_(0, std))       # gate|up or fc1

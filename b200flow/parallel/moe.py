@@ -77,6 +77,46 @@ def route_top1(logits: torch.Tensor, capacity: int):
                 me=probs.sum(0), ce=onehot.sum(0).float())
 
 
+def route_top2(logits: torch.Tensor, capacity: int):
+    """DeepSpeed `top2gating` without noise: every token goes to its two most probable experts.
+
+    Second choices queue up behind *all* first choices of an expert (their slot starts at that
+    expert's first-choice count), then the capacity cut is applied to both.  Built from two
+    launches of the top-1 router (K5a) — the second on logits with the first choice masked out —
+    plus a few [T]-sized index ops, so CUDA and CPU share the routing order.
+    Returns dict(expert [2, T], slot [2, T] (-1 = dropped), probs [T, E], first_counts [E])."""
+    T, E = logits.shape
+    assert E >= 2, "top-2 routing needs at least two experts"
+    r1 = route_top1(logits, T)                      # capacity T: nothing dropped, raw slots
+    e1 = r1["expert"].long()
+    masked = logits.masked_fill(F.one_hot(e1, E).bool(), torch.finfo(torch.float32).min)
+    r2 = route_top1(masked, T)
+    e2 = r2["expert"].long()
+    first = r1["counts"].long()                     # first-choice tokens per expert (uncut)
+    s1, s2 = r1["slot"].long(), r2["slot"].long() + first[e2]
+    k1, k2 = s1 < capacity, s2 < capacity
+    neg = torch.full_like(s1, -1)
+    expert = torch.stack([torch.where(k1, e1, neg), torch.where(k2, e2, neg)]).int()
+    slot = torch.stack([torch.where(k1, s1, neg), torch.where(k2, s2, neg)]).int()
+    return dict(expert=expert, slot=slot, probs=r1["probs"], first_counts=first)
+
+
+def gate_top2(logits: torch.Tensor, capacity: int):
+    """(gates [2, T], aux, expert [2, T], slot [2, T]).  Routing is constant; the gate values
+    g_k / (g_1 + g_2) (dropped choices count as 0) and the load-balancing loss
+    E * sum_e mean_t(p_te) * frac_first_e are plain differentiable torch expressions of the
+    softmax — [T, E] is tiny next to the expert GEMMs."""
+    T, E = logits.shape
+    with torch.no_grad():
+        r = route_top2(logits.detach().float().contiguous(), capacity)
+    probs = logits.float().softmax(-1)
+    kept = r["expert"] >= 0
+    g = probs.gather(1, r["expert"].clamp(min=0).long().t()).t() * kept       # [2, T]
+    gates = g / g.sum(0, keepdim=True).clamp(min=torch.finfo(torch.float32).eps)
+    aux = (probs.mean(0) * (r["first_counts"].float() / T)).sum() * E
+    return gates, aux, r["expert"], r["slot"]
+
+
 class _Gate(torch.autograd.Function):
     """Routing decisions are constants; gradients reach the logits through the chosen gate
     probability and the auxiliary loss  l_aux = E * sum_e mean_t(p_te) * frac_e."""
@@ -255,9 +295,10 @@ class MoELayer(nn.Module):
     def __init__(self, hidden: int, ffn: int, num_experts: int, ep: EPContext | None = None,
                  capacity_factor: float = 1.0, min_capacity: int = 4, act: str = "gelu",
                  aux_loss_coeff: float = 0.01, init_std: float = 0.02, dtype=torch.bfloat16, device=None,
-                 fused: bool = True, fp8: bool = False):
+                 fused: bool = True, fp8: bool = False, top_k: int = 1):
         super().__init__()
-        self.fp8 = fp8
+        assert top_k in (1, 2), "DeepSpeed's TopKGate supports k = 1 or 2"
+        self.fp8, self.top_k = fp8, top_k
         self.ep = ep or LOCAL
         assert num_experts % self.ep.world == 0
         self.E, self.El = num_experts, num_experts // self.ep.world
@@ -276,7 +317,7 @@ class MoELayer(nn.Module):
         self.last_counts = None
 
     def capacity(self, tokens: int) -> int:
-        c = max(self.min_cap, math.ceil(tokens / self.E * self.cf))
+        c = max(self.min_cap, math.ceil(tokens / self.E * self.cf * self.top_k))
         return (c + 7) // 8 * 8
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
@@ -286,7 +327,15 @@ class MoELayer(nn.Module):
             logits = _GateLogits.apply(x, self.wg, self.E)
         else:
             logits = G.linear(x, self.wg)[:, :self.E]
-        gate, aux, expert, slot, counts = _Gate.apply(logits.float(), C)
+        if self.top_k == 2:
+            # both choices ride through the top-1 row movers as a token list of length 2T
+            gates, aux, expert2, slot2 = gate_top2(logits, C)
+            gate, expert, slot = gates.reshape(-1), expert2.reshape(-1).contiguous(), slot2.reshape(-1).contiguous()
+            counts = torch.bincount(expert.clamp(min=0).long(), weights=(expert >= 0).float(),
+                                    minlength=self.E).int()
+            x = torch.cat([x, x], 0)
+        else:
+            gate, aux, expert, slot, counts = _Gate.apply(logits.float(), C)
         self.last_aux, self.last_counts = aux, counts
         xin = _Dispatch.apply(x, expert, slot, self.E, C, self.ep, self.fused)       # [El, ep*C, H]
         outs = []
@@ -299,6 +348,8 @@ class MoELayer(nn.Module):
             outs.append(lin(h1, self.w2[e], self.b2[e]))
         out = torch.stack(outs, 0)
         y = _Combine.apply(out, gate, expert, slot, self.E, C, self.ep, self.fused)
+        if self.top_k == 2:
+            y = y[:T] + y[T:]
         return y
 
 

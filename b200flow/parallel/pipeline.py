@@ -131,3 +131,21 @@ def run_1f1b(stage: int, stages: int, micro_batches: int, forward_fn, p2p: P2P):
             if g is not None:
                 pending_grad = g
     return losses
+
+
+def run_forward_only(stage: int, stages: int, micro_batches: int, forward_fn, p2p: P2P):
+    """Evaluation schedule (DeepSpeed `InferenceSchedule` in spirit): every micro-batch flows
+    through the stages once, no backward and nothing kept.  Returns the last stage's losses."""
+    first, last = stage == 0, stage == stages - 1
+    losses = []
+    with torch.no_grad():
+        for mb in range(micro_batches):
+            act = None
+            if not first:
+                act, _ = p2p.exchange(recv_fwd=True)
+            out = forward_fn(mb, act)
+            if last:
+                losses.append(out.detach())
+            else:
+                p2p.exchange(send_fwd=out.detach())
+    return losses

@@ -72,6 +72,13 @@ def parse_args():
     a("--deepspeed", action="store_true"); a("--deepspeed_config", default=None)
     a("--zero-stage", type=int, default=None); a("--no-pipeline-parallel", action="store_true")
     a("--local_rank", "--local-rank", type=int, default=None)
+    # DeepSpeed-MoE flags of the pinned commit (examples_deepspeed/MoE/ds_pretrain_gpt_*_MoE*.sh upstream)
+    a("--num-experts", type=int, nargs="+", default=[0]); a("--topk", type=int, default=1)
+    a("--expert-interval", type=int, default=2); a("--moe-expert-parallel-size", type=int, default=1)
+    a("--moe-loss-coeff", type=float, default=0.01); a("--moe-train-capacity-factor", type=float, default=1.0)
+    a("--moe-eval-capacity-factor", type=float, default=1.0); a("--moe-min-capacity", type=int, default=4)
+    a("--mlp-type", default="standard"); a("--create-moe-param-group", action="store_true")
+    a("--disable-moe-token-dropping", action="store_true")
     import shlex
     argv = sys.argv[1:] + shlex.split(os.environ.get("B2F_OVERRIDE_ARGS", ""))  # test-size overrides
     args, unknown = p.parse_known_args(argv)
@@ -90,7 +97,9 @@ def main():
     backend = args.distributed_backend if torch.cuda.is_available() else "gloo"
     rank, local_rank, world = init_distributed(backend)
     tp, pp = args.tensor_model_parallel_size, args.pipeline_model_parallel_size
-    ps = ParallelState.initialize(tp=tp, pp=pp) if world > 1 else None
+    n_experts = max(args.num_experts)
+    ep = min(args.moe_expert_parallel_size, world // (tp * pp)) if n_experts > 1 else 1
+    ps = ParallelState.initialize(tp=tp, pp=pp, ep=ep) if world > 1 else None
     dp = world // (tp * pp)
     ds = json.load(open(args.deepspeed_config)) if args.deepspeed_config else {}
     micro = int(ds.get("train_micro_batch_size_per_gpu", args.micro_batch_size))
@@ -111,6 +120,12 @@ def main():
         act="swiglu" if args.swiglu else "gelu", rope=args.use_rotary_position_embeddings,
         learned_pos=not args.use_rotary_position_embeddings, bias=not args.disable_bias_linear,
         tie_embeddings=not args.untie_embeddings_and_output_weights, name="llama" if llama else "gpt2")
+    if n_experts > 1:
+        cfg.num_experts, cfg.moe_every, cfg.moe_top_k = n_experts, args.expert_interval, args.topk
+        cfg.aux_loss_coeff, cfg.moe_min_capacity = args.moe_loss_coeff, args.moe_min_capacity
+        # without token dropping every token must fit even if all of them pick one expert
+        cfg.capacity_factor = float(n_experts) if args.disable_moe_token_dropping else args.moe_train_capacity_factor
+        cfg.name = "gpt-moe"
     decay_iters = args.lr_decay_iters or args.train_iters
     warm = args.lr_warmup_iters if args.lr_warmup_iters is not None else int(args.lr_warmup_fraction * decay_iters)
     ds_cfg = {
@@ -129,6 +144,8 @@ def main():
         "activation_checkpointing": {"enabled": args.checkpoint_activations},
         "fused_collectives": os.environ.get("B2F_FUSED", "1") == "1",
     }
+    if ds.get("fp16", {}).get("enabled") or (args.fp16 and not ds.get("bf16", {}).get("enabled")):
+        ds_cfg["fp16"] = {**ds.get("fp16", {}), "enabled": True}    # loss-scale state machine (skipped steps)
     engine = initialize(cfg, ds_cfg, ps, seed=args.seed)
     engine.args = vars(args)
     dev = engine.device
@@ -183,7 +200,11 @@ def main():
             tok_s = gbs * args.seq_length / dt
             line = (f" iteration {iteration:8d}/{train_iters:8d} | consumed samples: {iteration * gbs:12d} | "
                     f"elapsed time per iteration (ms): {dt * 1e3:.1f} | learning rate: {engine.optimizer.lr:.3E} | "
-                    f"global batch size: {gbs:5d} | lm loss: {loss_acc / n_acc:.6E} | grad norm: {engine.grad_norm():.3f} | "
+                    f"global batch size: {gbs:5d} | lm loss: {loss_acc / n_acc:.6E} | "
+                    + (f"loss scale: {engine.loss_scale:.1f} | " if engine.loss_scaler is not None else "")
+                    + f"grad norm: {engine.grad_norm():.3f} | "
+                    + (f"number of skipped iterations: {engine.skipped_steps:3d} | "
+                       if engine.loss_scaler is not None else "") +
                     f"samples per second: {gbs / dt:.3f} | tokens per second: {tok_s:.1f} | "
                     f"TFLOPs: {flops_tok * tok_s / world / 1e12:.2f} |")
             if rank == 0:
@@ -192,7 +213,7 @@ def main():
                     tracker.log({"lm loss": loss_acc / n_acc, "learning-rate": engine.optimizer.lr,
                                  "grad-norm": engine.grad_norm(), "tokens-per-second": tok_s}, iteration)
             t_last, loss_acc, n_acc = time.time(), 0.0, 0
-        if valid_ds is not None and args.eval_interval and iteration % args.eval_interval == 0 and pp == 1:
+        if valid_ds is not None and args.eval_interval and iteration % args.eval_interval == 0:
             vit = batches(valid_ds, iteration // args.eval_interval)
             with torch.no_grad():
                 vl = sum(float(engine.eval_batch(vit)) for _ in range(args.eval_iters)) / args.eval_iters

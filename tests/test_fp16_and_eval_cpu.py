@@ -1,0 +1,146 @@
+"""fp16 loss scaling (DeepSpeed's dynamic scaler semantics, skipped steps, checkpointed state) and
+forward-only evaluation under pipeline parallelism, on CPU/gloo.
+
+The reference's Megatron-DeepSpeed values files train with `--fp16` + `"fp16": {"enabled": true}` and
+evaluate every `--eval-interval` on a TP2 x PP2 topology
+(examples/megatron-deepspeed/gpt2_345m/pretrain-ddp-tp-pp-zero1.yaml:33-57)."""
+import itertools
+import os
+import sys
+from pathlib import Path
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+
+from b200flow.parallel.loss_scaler import (DynamicLossScaler, LossScaler, LossScalerConfig,  # noqa: E402
+                                           make_loss_scaler)
+
+
+def test_dynamic_scaler_follows_deepspeed_state_machine():
+    s = DynamicLossScaler(LossScalerConfig(initial_scale_power=4, scale_window=3, hysteresis=2, min_scale=1))
+    assert s.scale == 16
+    s.update(True)                      # first overflow only uses up hysteresis
+    assert s.scale == 16 and s.cur_hysteresis == 1 and s.skipped == 1
+    s.update(True)                      # second one halves
+    assert s.scale == 8
+    s.update(True)
+    assert s.scale == 4
+    for _ in range(2):
+        s.update(False)
+    assert s.scale == 4
+    s.update(False)                     # third clean step since the last overflow: grow, hysteresis restored
+    assert s.scale == 8 and s.cur_hysteresis == 2
+    for _ in range(20):
+        s.update(True)
+    assert s.scale == 1                 # floor
+    t = DynamicLossScaler(LossScalerConfig(initial_scale_power=4, scale_window=3))
+    t.load_state_dict(s.state_dict())
+    assert (t.scale, t.cur_iter, t.last_overflow_iter, t.skipped) == (s.scale, s.cur_iter, s.last_overflow_iter, s.skipped)
+
+
+def test_scaler_factory_reads_ds_config_keys():
+    assert make_loss_scaler(None) is None and make_loss_scaler({"enabled": False}) is None
+    st = make_loss_scaler({"enabled": True, "loss_scale": 128})
+    assert isinstance(st, LossScaler) and not st.dynamic and st.scale == 128
+    dy = make_loss_scaler({"enabled": True, "loss_scale": 0, "initial_scale_power": 12, "loss_scale_window": 50,
+                           "hysteresis": 1, "min_loss_scale": 2})
+    assert dy.dynamic and dy.scale == 4096 and dy.cfg.scale_window == 50 and dy.cfg.min_scale == 2
+    dy.update(True)
+    assert dy.scale == 2048             # hysteresis 1: every overflow lowers the scale
+
+
+def _engine(extra, ps=None, seed=5):
+    from b200flow.engines.ds_engine import initialize
+    from b200flow.models.gpt import config_from_preset
+
+    cfg = config_from_preset("llama-tiny", hidden=64, heads=4, ffn=128, layers=4, vocab_size=128, max_seq=32)
+    ds = {"train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": 2,
+          "optimizer": {"params": {"lr": 2e-3, "weight_decay": 0.0}}, "gradient_clipping": 1.0, **extra}
+    return cfg, initialize(cfg, ds, ps, device=torch.device("cpu"), seed=seed)
+
+
+def _batches(cfg, n=4, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    mbs = [torch.randint(0, cfg.vocab_size, (2, 33), generator=g) for _ in range(n)]
+    return [(t[:, :-1].contiguous(), t[:, 1:].contiguous()) for t in mbs]
+
+
+def test_fp16_run_matches_unscaled_run_and_skips_overflowing_steps(tmp_path):
+    cfg, plain = _engine({})
+    _, scaled = _engine({"fp16": {"enabled": True, "initial_scale_power": 10, "hysteresis": 1,
+                                  "loss_scale_window": 2}})
+    assert scaled.loss_scaler is not None and scaled.loss_scale == 1024
+    it_a, it_b = itertools.cycle(_batches(cfg)), itertools.cycle(_batches(cfg))
+    for _ in range(3):
+        la, lb = float(plain.train_batch(it_a)), float(scaled.train_batch(it_b))
+        assert abs(la - lb) < 1e-4, (la, lb)         # the reported loss is unscaled, updates identical
+    assert scaled.loss_scale == 2048 and scaled.skipped_steps == 0   # window of 2 clean steps passed once
+    # poison one gradient: the step is skipped, parameters and Adam state stay as they were
+    before = scaled.flat.params.clone()
+    steps_before = scaled.optimizer.step_count
+    orig = scaled.flat.collect_autograd_grads
+
+    def poisoned():
+        orig()
+        scaled.flat.grads[3] = float("inf")
+
+    scaled.flat.collect_autograd_grads = poisoned
+    scaled.train_batch(it_b)
+    scaled.flat.collect_autograd_grads = orig
+    assert scaled.skipped_steps == 1 and scaled.loss_scale == 1024
+    assert torch.equal(before, scaled.flat.params) and scaled.optimizer.step_count == steps_before
+    assert scaled.global_steps == 4
+    # the scaler state travels with the optimizer state of a checkpoint
+    scaled.save_checkpoint(str(tmp_path))
+    _, fresh = _engine({"fp16": {"enabled": True, "initial_scale_power": 10, "hysteresis": 1,
+                                 "loss_scale_window": 2}})
+    fresh.load_checkpoint(str(tmp_path))
+    assert fresh.loss_scale == 1024 and fresh.skipped_steps == 1
+    assert fresh.loss_scaler.cur_iter == scaled.loss_scaler.cur_iter
+    l1, l2 = float(scaled.train_batch(it_b)), float(fresh.train_batch(itertools.cycle(_batches(cfg))))
+    assert abs(l1 - l2) < 1e-5
+
+
+def _pp_eval_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.set_num_threads(1)
+    from b200flow.parallel.groups import ParallelState
+    from test_parallel_cpu import _sync_weights_from_reference
+
+    ps = ParallelState.initialize(tp=1, pp=2)
+    cfg, eng = _engine({}, ps)
+    _sync_weights_from_reference(eng, ps, cfg)
+    it = itertools.cycle(_batches(cfg))
+    ev = [float(eng.eval_batch(it, num_micro_batches=3)), float(eng.eval_batch(it))]
+    tr = float(eng.train_batch(it))     # training after evaluation still works (p2p buffers reused)
+    q.put((rank, ev, tr))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_eval_batch_under_pipeline_parallelism_matches_single_process():
+    from test_parallel_cpu import _sync_weights_from_reference
+
+    cfg, eng = _engine({})
+    _sync_weights_from_reference(eng, None, cfg)
+    it = itertools.cycle(_batches(cfg))
+    want = [float(eng.eval_batch(it, num_micro_batches=3)), float(eng.eval_batch(it))]
+    want_train = float(eng.train_batch(it))
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_pp_eval_worker, args=(r, 2, 29641, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = [q.get(timeout=300) for _ in range(2)]
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    for rank, ev, tr in got:            # every stage reports the same loss
+        for a, b in zip(ev, want):
+            assert abs(a - b) < 2e-3, (rank, ev, want)
+        assert abs(tr - want_train) < 2e-3

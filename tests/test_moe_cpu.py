@@ -95,3 +95,67 @@ def test_expert_parallel_all_to_all_matches_local():
     for p in procs:
         p.join(timeout=60)
     assert all(ok for _, ok, _ in res), res
+
+
+def _top2_reference(logits, C):
+    """DeepSpeed `top2gating` (no noise) written the dense way: one-hot masks, cumsum locations,
+    second choices placed after every first choice of the expert, capacity cut, renormalised gates."""
+    T, E = logits.shape
+    gates = logits.softmax(-1)
+    i1 = gates.argmax(-1)
+    m1 = torch.nn.functional.one_hot(i1, E)
+    i2 = logits.masked_fill(m1.bool(), float("-inf")).argmax(-1)
+    m2 = torch.nn.functional.one_hot(i2, E)
+    loc1 = m1.cumsum(0) - 1
+    loc2 = m2.cumsum(0) - 1 + m1.sum(0, keepdim=True)
+    aux = (gates.mean(0) * m1.float().mean(0)).sum() * E
+    m1, m2 = m1 * (loc1 < C), m2 * (loc2 < C)
+    s1, s2 = (loc1 * m1).sum(1), (loc2 * m2).sum(1)
+    g1, g2 = (gates * m1).sum(1), (gates * m2).sum(1)
+    den = (g1 + g2).clamp(min=torch.finfo(torch.float32).eps)
+    return (i1, i2), (m1.sum(1) > 0, m2.sum(1) > 0), (s1, s2), (g1 / den, g2 / den), aux
+
+
+def test_top2_routing_matches_deepspeed_formulation():
+    from b200flow.parallel.moe import gate_top2
+
+    torch.manual_seed(3)
+    T, E, C = 96, 4, 40            # 2T/E = 48 > C: some second choices are cut
+    logits = torch.randn(T, E, requires_grad=True)
+    gates, aux, expert, slot = gate_top2(logits, C)
+    (i1, i2), (k1, k2), (s1, s2), (g1, g2), aux_ref = _top2_reference(logits.detach(), C)
+    assert not bool(k2.all()) and bool(k1.all())
+    for k, (i, keep, s, g) in enumerate(((i1, k1, s1, g1), (i2, k2, s2, g2))):
+        assert torch.equal(expert[k][keep].long(), i[keep]) and (expert[k][~keep] == -1).all()
+        assert torch.equal(slot[k][keep].long(), s[keep])
+        assert torch.allclose(gates[k], g, atol=1e-6)
+    assert abs(float(aux) - float(aux_ref)) < 1e-6
+    # no (expert, slot) pair is handed out twice
+    rows = (expert.long() * C + slot.long())[expert >= 0]
+    assert rows.unique().numel() == rows.numel()
+    (gates.sum() + aux).backward()
+    assert logits.grad is not None and torch.isfinite(logits.grad).all()
+
+
+def test_top2_layer_matches_dense_oracle_and_trains():
+    from b200flow.parallel.moe import gate_top2
+
+    torch.manual_seed(4)
+    layer = MoELayer(32, 64, 4, dtype=torch.float32, capacity_factor=0.75, top_k=2)
+    x = torch.randn(40, 32, requires_grad=True)
+    y = layer(x)
+    T = x.shape[0]
+    with torch.no_grad():
+        logits = torch.nn.functional.linear(x, layer.wg)[:, :layer.E].float()
+        gates, _, expert, _ = gate_top2(logits, layer.capacity(T))
+        ref = torch.zeros_like(x)
+        for t in range(T):
+            for k in range(2):
+                e = int(expert[k, t])
+                if e >= 0:
+                    h = torch.nn.functional.gelu(torch.nn.functional.linear(x[t], layer.w1[e], layer.b1[e]),
+                                                 approximate="tanh")
+                    ref[t] += gates[k, t] * torch.nn.functional.linear(h, layer.w2[e], layer.b2[e])
+    assert torch.allclose(y, ref, atol=1e-5)
+    (y.square().sum() + layer.last_aux).backward()
+    assert x.grad is not None and layer.wg.grad.abs().sum() > 0 and layer.w2.grad.abs().sum() > 0

@@ -52,11 +52,16 @@ def test_accelerate_bert_mrpc_gloo_ws2(tmp_root):
 def test_megatron_tp2_pp2_zero1_and_resume(tmp_root):
     """W3: the TP=2 x PP=2 values file (test-size model), Megatron-DS checkpoint layout, resume."""
     values = EX / "megatron-deepspeed/gpt2_345m/pretrain-ddp-tp-pp-zero1.yaml"
-    env = {"B2F_TRAIN_ITERS": "4", "B2F_OVERRIDE_ARGS": TINY_GPT + " --save-interval 2"}
+    env = {"B2F_TRAIN_ITERS": "4",
+           "B2F_OVERRIDE_ARGS": TINY_GPT + " --save-interval 2 --eval-interval 2 --eval-iters 2"}
     sets = ["resources.nnodes=1", "resources.nproc_per_node=4"]
     rc, st, logs = _install("mds", "pytorchjob-distributed", values, tmp_root, sets, env)
     assert rc == 0 and st["phase"] == "Succeeded", logs[-3000:]
     assert "iteration        4/       4" in logs and "lm loss" in logs
+    # the values file trains in fp16: DeepSpeed's loss-scale state and skipped-step count are logged
+    assert "loss scale: 65536.0" in logs and "number of skipped iterations:   0" in logs
+    # --eval-interval under PP=2: forward-only pipeline schedule
+    assert "validation loss at iteration 2" in logs and "validation loss at iteration 4" in logs
     ck = tmp_root / "fsx/home/mds/checkpoints/0"
     assert (ck / "latest").read_text() == "global_step4"
     names = {p.name for p in (ck / "global_step4").iterdir()}
@@ -70,6 +75,24 @@ def test_megatron_tp2_pp2_zero1_and_resume(tmp_root):
     assert rc == 0, logs[-3000:]
     assert "successfully loaded checkpoint" in logs and "at iteration 4" in logs
     assert "iteration        6/       6" in logs
+
+
+def test_megatron_moe_flags_top2_expert_parallel(tmp_root):
+    """DeepSpeed-MoE flags of the pinned Megatron-DeepSpeed (--num-experts / --topk /
+    --moe-expert-parallel-size) on the DP + ZeRO-1 values file: 4 experts over EP=2, top-2 gating,
+    per-expert checkpoint files."""
+    values = EX / "megatron-deepspeed/gpt2_345m/pretrain-ddp-zero1.yaml"
+    moe = (" --num-experts 4 --topk 2 --moe-expert-parallel-size 2 --moe-loss-coeff 0.01 "
+           "--moe-train-capacity-factor 1.0 --moe-min-capacity 4 --create-moe-param-group")
+    env = {"B2F_TRAIN_ITERS": "4", "B2F_OVERRIDE_ARGS": TINY_GPT + moe}
+    rc, st, logs = _install("mds-moe", "pytorchjob-distributed", values, tmp_root,
+                            ["resources.nnodes=1", "resources.nproc_per_node=2"], env)
+    assert rc == 0 and st["phase"] == "Succeeded", logs[-3000:]
+    assert "iteration        4/       4" in logs and "unknown arguments" not in logs
+    ck = tmp_root / "fsx/home/mds-moe/checkpoints/0/global_step4"
+    names = {p.name for p in ck.iterdir()}
+    assert {f"layer_1_expert_{e}_mp_rank_00_model_states.pt" for e in range(4)} <= names, names
+    assert "expp_rank_0_mp_rank_00_optim_states.pt" in names and "expp_rank_1_mp_rank_00_optim_states.pt" in names
 
 
 def test_wikicorpus_preprocess_then_ddp_zero1_pipeline(tmp_root):
