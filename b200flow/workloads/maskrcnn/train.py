@@ -13,8 +13,8 @@ and ignored).  Ranks come from the launcher's mpirun mode (OMPI_COMM_WORLD_* / R
 
 Callbacks mirror tensorpack's: periodic model saver (`model-<step>.pt` + `model-<step>.index`
 marker + `checkpoint` file under `<logdir>`, auto-resume from the newest), LR schedule with
-linear warm-up, throughput tracker, evaluation every EVAL_PERIOD epochs (box AP@0.5 on the
-synthetic validation split), TensorBoard scalars.  COCO-shaped synthetic images.
+linear warm-up, throughput tracker, evaluation every EVAL_PERIOD epochs (COCO bbox / segm mAP on the
+synthetic validation split, coco_eval.py), TensorBoard scalars.  COCO-shaped synthetic images.
 
 Test-size knobs: B2F_MRCNN_WIDTH, B2F_MRCNN_IMAGE (HxW), B2F_MRCNN_EPOCHS, B2F_MRCNN_STEPS.
 """
@@ -62,34 +62,31 @@ def lr_at(step, base_lr, world, batch, warmup, boundaries):
     return lr * (0.1 ** len(boundaries))
 
 
-def ap50(dets, gts):
-    """Class-aware box AP at IoU 0.5 over a list of images (simple all-point interpolation)."""
-    import torchvision
+def evaluate_coco(model, val, dev, use_cuda, mode_mask):
+    """COCO protocol on this rank's validation shard, merged over ranks: tensorpack's
+    `mAP(bbox)/...` and `mAP(segm)/...` scalars (coco_eval.py)."""
+    from b200flow.models.maskrcnn import paste_masks
+    from b200flow.workloads.maskrcnn.coco_eval import COCOEvaluator
 
-    recs, npos = [], 0
-    for d, g in zip(dets, gts):
-        npos += g["boxes"].shape[0]
-        used = torch.zeros(g["boxes"].shape[0], dtype=torch.bool)
-        for b, s, l in zip(d["boxes"].cpu(), d["scores"].cpu(), d["labels"].cpu()):
-            ok = False
-            if g["boxes"].numel():
-                iou = torchvision.ops.box_iou(b[None], g["boxes"].cpu().float())[0]
-                iou[(g["labels"].cpu() != l) | used] = 0
-                j = int(iou.argmax())
-                if iou[j] >= 0.5:
-                    used[j] = ok = True
-            recs.append((float(s), ok))
-    if not recs or npos == 0:
-        return 0.0
-    recs.sort(key=lambda t: -t[0])
-    tp = torch.tensor([r[1] for r in recs], dtype=torch.float32).cumsum(0)
-    prec = tp / torch.arange(1, len(recs) + 1)
-    rec = tp / npos
-    ap, prev = 0.0, 0.0
-    for i in range(len(recs)):
-        ap += float(prec[i:].max()) * (float(rec[i]) - prev)
-        prev = float(rec[i])
-    return ap
+    evs = {"bbox": COCOEvaluator("bbox")}
+    if mode_mask:
+        evs["segm"] = COCOEvaluator("segm")
+    with torch.no_grad():
+        vi = torch.stack([s["image"] for s in val]).to(dev)
+        dets = model(vi.to(torch.bfloat16) if use_cuda else vi)
+    H, W = vi.shape[-2:]
+    for d, g in zip(dets, val):
+        d = {k: v for k, v in d.items() if k != "fastrcnn_all_scores"}
+        evs["bbox"].add({"boxes": d["boxes"].float().cpu(), "labels": d["labels"].cpu(), "scores": d["scores"].float().cpu()},
+                        {"boxes": g["boxes"].float().cpu(), "labels": g["labels"].cpu()})
+        if mode_mask:
+            pm = paste_masks(d, H, W).cpu() if d["labels"].numel() else torch.zeros(0, H, W, dtype=torch.uint8)
+            evs["segm"].add({"masks": pm, "labels": d["labels"].cpu(), "scores": d["scores"].float().cpu()},
+                            {"masks": g["masks"].cpu(), "labels": g["labels"].cpu()})
+    out = {}
+    for ev in evs.values():
+        out.update(ev.gather().tensorpack_names())
+    return out
 
 
 def main():
@@ -194,17 +191,10 @@ def main():
         if epoch % eval_period == 0:
             model.eval()
             val = list(coco_like(4, H, W, seed=77 + rank, device="cpu"))
-            with torch.no_grad():
-                vi = torch.stack([s["image"] for s in val]).to(dev)
-                dets = model(vi.to(torch.bfloat16) if use_cuda else vi)
-            score = ap50(dets, val)
-            if world > 1:
-                t = torch.tensor([score], device=dev)
-                dist.all_reduce(t)
-                score = float(t) / world
+            scores = evaluate_coco(model, val, dev, use_cuda, mcfg.mode_mask)
             if rank == 0:
-                print(f"[epoch {epoch}] val box AP@0.5 = {score:.4f}", flush=True)
-                tracker.log({"val/box_AP50": score}, step)
+                print(f"[epoch {epoch}] " + " | ".join(f"{k}: {v:.4f}" for k, v in scores.items()), flush=True)
+                tracker.log(scores, step)
         if epoch % ckpt_period == 0 and rank == 0:
             name = f"model-{step}"
             torch.save({"model": model.state_dict(), "optimizer": opt.state_dict(), "global_step": step,

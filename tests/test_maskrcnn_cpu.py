@@ -32,6 +32,10 @@ def test_maskrcnn_chart_then_jupyter_chart(tmp_root):
     # tensorpack ModelSaver layout + TensorBoard events + config dump (TRAIN.CHECKPOINT_PERIOD=2 from the chart)
     assert {"checkpoint", "model-4.index", "model-4.pt", "config.json", "metrics.jsonl"} <= names
     assert any(n.startswith("events.out.tfevents") for n in names)
+    # TRAIN.EVAL_PERIOD=1: COCO bbox and segm mAP (tensorpack's scalar names) after every epoch, gathered over ranks
+    metrics = [json.loads(l) for l in (ck / "metrics.jsonl").read_text().splitlines()]
+    evals = [m for m in metrics if "mAP(bbox)/IoU=0.5:0.95" in m]
+    assert len(evals) == 2 and all("mAP(segm)/IoU=0.5" in m and -1.0 <= m["mAP(bbox)/IoU=0.5"] <= 1.0 for m in evals)
     cfg = json.loads((ck / "config.json").read_text())
     assert cfg["world"] == 2 and cfg["config"]["MODE_MASK"] is True and cfg["config"]["TRAIN.CHECKPOINT_PERIOD"] == 2
 
