@@ -158,5 +158,43 @@ class _DistributedOptimizer:
         return self.optimizer.load_state_dict(sd)
 
 
+def ddp_options_from_env(env=None) -> dict:
+    """Horovod's tuning knobs as the chart exports them (`mpirun -x HOROVOD_AUTOTUNE ...`,
+    charts/machine-learning/training/mpijob-horovod-tensorflow-gpu/values.yaml:22-24,38-41,79-82):
+
+    HOROVOD_FUSION_THRESHOLD  bytes of the fusion buffer   -> bucket cap of the reducer (default 64 MiB)
+    HOROVOD_AUTOTUNE          "1": pick the cap by measurement (parallel/ddp.py BucketAutotuner)
+    HOROVOD_AUTOTUNE_LOG      CSV of the candidates tried
+    HOROVOD_AUTOTUNE_WARMUP_SAMPLES / HOROVOD_AUTOTUNE_STEPS_PER_SAMPLE
+    HOROVOD_TIMELINE          chrome-trace file of the bucket reductions (rank 0)
+    HOROVOD_CYCLE_TIME, HOROVOD_HIERARCHICAL_*, HOROVOD_TORUS_ALLREDUCE have no meaning without a
+    background negotiation thread / multi-node topology and are accepted silently."""
+    env = os.environ if env is None else env
+    return {"bucket_cap_mb": int(env.get("HOROVOD_FUSION_THRESHOLD", 64 << 20)) / float(1 << 20),
+            "autotune": env.get("HOROVOD_AUTOTUNE", "0") not in ("0", "", "false", "False"),
+            "autotune_log": env.get("HOROVOD_AUTOTUNE_LOG") or None,
+            "autotune_warmup": int(env.get("HOROVOD_AUTOTUNE_WARMUP_SAMPLES", 3)),
+            "autotune_steps": int(env.get("HOROVOD_AUTOTUNE_STEPS_PER_SAMPLE", 10)),
+            "timeline": env.get("HOROVOD_TIMELINE") or None}
+
+
+def make_ddp(module, env=None, **kw):
+    """(ddp, autotuner | None): the bucketed reducer configured from the Horovod environment."""
+    from ..obs.tracking import Timeline
+    from ..parallel.ddp import BucketAutotuner, DistributedDataParallel
+
+    o = ddp_options_from_env(env)
+    ddp = DistributedDataParallel(module, bucket_cap_mb=max(o["bucket_cap_mb"], 1.0 / 1024), **kw)
+    if o["timeline"] and ddp.rank == 0:
+        ddp.timeline = Timeline(o["timeline"], ddp.rank)
+    tuner = None
+    if o["autotune"] and ddp.world > 1:
+        tuner = BucketAutotuner(ddp, warmup=o["autotune_warmup"], steps_per_sample=o["autotune_steps"],
+                                log_path=o["autotune_log"])
+        if ddp.rank == 0 and os.environ.get("HOROVOD_LOG_LEVEL", "").upper() in ("INFO", "DEBUG", "TRACE"):
+            print(f"[b200flow] HOROVOD_AUTOTUNE: trying bucket caps {tuner.cands} MB", flush=True)
+    return ddp, tuner
+
+
 def DistributedOptimizer(optimizer, named_parameters=None, ddp=None, op: str = Average, **_ignored):
     return _DistributedOptimizer(optimizer, named_parameters, ddp, op)

@@ -57,6 +57,37 @@ def _num(v):
     return v
 
 
+class Timeline:
+    """Chrome-trace event log (`chrome://tracing` / Perfetto), the `HOROVOD_TIMELINE=<file>` facility of the
+    reference's Horovod stack: host-side instants and spans, one process row per rank."""
+
+    def __init__(self, path: str | os.PathLike, rank: int = 0):
+        self.path, self.rank, self.events, self._t0 = Path(path), rank, [], time.perf_counter()
+
+    def _us(self) -> float:
+        return (time.perf_counter() - self._t0) * 1e6
+
+    def instant(self, name: str, **args) -> None:
+        self.events.append({"name": name, "ph": "i", "s": "t", "ts": self._us(), "pid": self.rank, "tid": 0,
+                            "args": args})
+
+    def span(self, name: str, **args):
+        tl = self
+
+        class _Span:
+            def __enter__(self):
+                self.t = tl._us()
+
+            def __exit__(self, *exc):
+                tl.events.append({"name": name, "ph": "X", "ts": self.t, "dur": tl._us() - self.t,
+                                  "pid": tl.rank, "tid": 0, "args": args})
+        return _Span()
+
+    def flush(self) -> None:
+        self.path.parent.mkdir(parents=True, exist_ok=True)
+        self.path.write_text(json.dumps({"traceEvents": self.events, "displayTimeUnit": "ms"}))
+
+
 class Timers:
     """Named CUDA-event timers (wall-clock on CPU); `summary(group)` reduces max over ranks —
     the Megatron `Timers` / DeepSpeed `wall_clock_breakdown` equivalent."""

@@ -70,14 +70,8 @@ class DistributedDataParallel(nn.Module):
         if self.world > 1:
             dist.broadcast(self.flat.params, src=dist.get_global_rank(self.group, 0) if hasattr(
                 dist, "get_global_rank") else 0, group=self.group)
-        self.buckets = plan_buckets(self.flat, bucket_cap_mb)
-        self._slot_bucket = {}
-        for bi, (s0, s1, _, _) in enumerate(self.buckets):
-            for s in range(s0, s1):
-                self._slot_bucket[s] = bi
-        self._pending = [0] * len(self.buckets)
-        self._launched = [False] * len(self.buckets)
         self.require_sync = True
+        self.timeline = None          # optional obs.tracking.Timeline: one event per bucket reduction
         self.reducer = None
         self.side = None
         if self.comm is not None:
@@ -92,9 +86,22 @@ class DistributedDataParallel(nn.Module):
             p = params[slot.name]
             p.grad_ready = self._make_ready(si)
             p.register_post_accumulate_grad_hook(self._make_hook(si))
-        self._reset()
+        self.set_bucket_cap(bucket_cap_mb)
 
     # ------------------------------------------------------------- bookkeeping
+    def set_bucket_cap(self, cap_mb: float) -> None:
+        """(Re)plan the buckets.  Only between steps (after `finish_reduction`); every rank must pass the
+        same value — the plan is a pure function of the parameter layout and the cap."""
+        self.bucket_cap_mb = float(cap_mb)
+        self.buckets = plan_buckets(self.flat, cap_mb, first_cap_mb=min(1.0, cap_mb))
+        self._slot_bucket = {}
+        for bi, (s0, s1, _, _) in enumerate(self.buckets):
+            for s in range(s0, s1):
+                self._slot_bucket[s] = bi
+        self._pending = [0] * len(self.buckets)
+        self._launched = [False] * len(self.buckets)
+        self._reset()
+
     def _reset(self):
         for bi, (s0, s1, _, _) in enumerate(self.buckets):
             self._pending[bi] = s1 - s0
@@ -129,6 +136,8 @@ class DistributedDataParallel(nn.Module):
             return
         self._launched[bi] = True
         _, _, e0, e1 = self.buckets[bi]
+        if self.timeline is not None:
+            self.timeline.instant("allreduce", bucket=bi, bytes=(e1 - e0) * self.flat.grads.element_size())
         if self.reducer is not None:
             self.side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(self.side):
@@ -173,3 +182,64 @@ class DistributedDataParallel(nn.Module):
 
     def zero_grad(self, set_to_none: bool = True):
         self.flat.zero_grad()
+
+
+class BucketAutotuner:
+    """Picks the bucket (fusion-buffer) size by measurement, in the spirit of `HOROVOD_AUTOTUNE=1`
+    — which the reference's MPI chart switches on by default
+    (charts/machine-learning/training/mpijob-horovod-tensorflow-gpu/values.yaml:22-24,38-39).
+
+    Horovod scores (fusion threshold, cycle time) pairs by bytes reduced per second; here the only
+    knob is the bucket cap, and the score is the step time itself.  After `warmup` steps each
+    candidate runs for `steps_per_sample` steps; the per-candidate time is the MAX over ranks (one
+    tiny all-reduce per sample), so every rank takes the same decision; the fastest cap is then kept.
+    Call `step_done()` once per training step, after `finish_reduction()` / the optimizer step."""
+
+    def __init__(self, ddp: DistributedDataParallel, candidates_mb=(1.0, 4.0, 8.0, 16.0, 25.0, 64.0, 128.0),
+                 warmup: int = 3, steps_per_sample: int = 10, log_path: str | None = None, clock=None):
+        import time
+
+        self.ddp, self.cands = ddp, [float(c) for c in candidates_mb]
+        self.warmup, self.sps, self.log_path = warmup, max(1, steps_per_sample), log_path
+        self.clock = clock or time.perf_counter
+        self.results: list[tuple[float, float]] = []     # (cap_mb, seconds per step)
+        self.done = ddp.world == 1 or not self.cands
+        self.best_mb = ddp.bucket_cap_mb
+        self._i, self._n, self._t0 = -1, 0, None          # candidate index (-1 = warm-up), steps seen, start
+
+    def _sync_time(self) -> float:
+        if self.ddp.on_gpu:
+            torch.cuda.synchronize()
+        return self.clock()
+
+    def step_done(self) -> None:
+        if self.done:
+            return
+        self._n += 1
+        if self._i < 0:
+            if self._n >= self.warmup:
+                self._start(0)
+            return
+        if self._n < self.sps:
+            return
+        dt = (self._sync_time() - self._t0) / self.sps
+        t = torch.tensor([dt], dtype=torch.float64, device=self.ddp.flat.grads.device if self.ddp.on_gpu else "cpu")
+        if self.ddp.world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.ddp.group)
+        self.results.append((self.cands[self._i], float(t)))
+        if self._i + 1 < len(self.cands):
+            self._start(self._i + 1)
+            return
+        self.best_mb = min(self.results, key=lambda r: r[1])[0]
+        self.ddp.set_bucket_cap(self.best_mb)
+        self.done = True
+        if self.log_path and self.ddp.rank == 0:
+            with open(self.log_path, "w") as f:        # Horovod's HOROVOD_AUTOTUNE_LOG is a CSV too
+                f.write("bucket_cap_mb,seconds_per_step,chosen\n")
+                for cap, sec in self.results:
+                    f.write(f"{cap},{sec:.6f},{int(cap == self.best_mb)}\n")
+
+    def _start(self, i: int) -> None:
+        self._i, self._n = i, 0
+        self.ddp.set_bucket_cap(self.cands[i])
+        self._t0 = self._sync_time()

@@ -34,7 +34,6 @@ from b200flow.data.synthetic import coco_like
 from b200flow.models.maskrcnn import MaskRCNN, MaskRCNNConfig
 from b200flow.obs.tracking import Tracker, maybe_inject_fault
 from b200flow.optim import FlatMomentumSGD
-from b200flow.parallel.ddp import DistributedDataParallel
 from b200flow.parallel.groups import init_distributed
 
 
@@ -125,7 +124,11 @@ def main():
     model = MaskRCNN(mcfg).to(dev)
     if use_cuda:
         model = model.to(torch.bfloat16).to(memory_format=torch.channels_last)
-    ddp = DistributedDataParallel(model) if world > 1 else None
+    ddp, tuner = None, None
+    if world > 1:      # TRAINER=horovod: fusion-buffer size / autotune / timeline come from the HOROVOD_* variables
+        from b200flow.engines.horovod_api import make_ddp
+
+        ddp, tuner = make_ddp(model)
     if ddp is None:
         from b200flow.utils.flat import FlatParams
 
@@ -177,6 +180,8 @@ def main():
                 gn = flat.grads.norm()
                 opt.grad_scale = (clip / (gn + 1e-6)).clamp(max=1.0).reshape(1)
             opt.step()
+            if tuner is not None:
+                tuner.step_done()
             step += 1
             seen += batch * world
             for k, v in losses.items():
@@ -205,6 +210,10 @@ def main():
             dist.barrier()
     if tracker:
         tracker.finish()
+    if ddp is not None and ddp.timeline is not None:
+        ddp.timeline.flush()
+    if tuner is not None and tuner.done and rank == 0:
+        print(f"[b200flow] HOROVOD_AUTOTUNE: bucket cap {tuner.best_mb} MB", flush=True)
     if world > 1:
         dist.destroy_process_group()
 

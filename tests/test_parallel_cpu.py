@@ -262,3 +262,67 @@ def test_horovod_facade_over_gloo():
         assert p.exitcode == 0
     for rank, sz, ok, s in res:
         assert sz == 2 and ok and s == 1.0, (rank, sz, ok, s)
+
+
+def _autotune_worker(rank, world, port, tmp, q_out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), OMPI_COMM_WORLD_RANK=str(rank),
+                      OMPI_COMM_WORLD_SIZE=str(world), OMPI_COMM_WORLD_LOCAL_RANK=str(rank),
+                      HOROVOD_AUTOTUNE="1", HOROVOD_AUTOTUNE_LOG=f"{tmp}/autotune.csv",
+                      HOROVOD_AUTOTUNE_WARMUP_SAMPLES="1", HOROVOD_AUTOTUNE_STEPS_PER_SAMPLE="2",
+                      HOROVOD_FUSION_THRESHOLD=str(8 << 10), HOROVOD_TIMELINE=f"{tmp}/timeline.json")
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        os.environ.pop(k, None)
+    import b200flow.engines.horovod_api as hvd
+
+    hvd.init("gloo")
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(*[torch.nn.Linear(64, 64) for _ in range(6)])      # 6 x 16.6 KB of fp32 gradients
+    torch.manual_seed(0)
+    oracle = torch.nn.Sequential(*[torch.nn.Linear(64, 64) for _ in range(6)])
+    ddp, tuner = hvd.make_ddp(model)
+    tuner.cands = [0.008, 0.03, 1.0]                                              # MB: 6+ buckets, 3-4 buckets, 1-2
+    caps_seen, nb_seen, ok = [], set(), True
+    for step in range(1 + 3 * 2 + 2):
+        ddp.zero_grad()
+        x = torch.full((4, 64), float(rank + 1 + step))
+        ddp(x).sum().backward()
+        ddp.finish_reduction()
+        # oracle: an unwrapped copy of the model on both ranks' inputs, averaged
+        want = []
+        for r in range(world):
+            oracle.zero_grad()
+            oracle(torch.full((4, 64), float(r + 1 + step))).sum().backward()
+            want.append(torch.cat([p.grad.reshape(-1) for p in oracle.parameters()]))
+        have = torch.cat([p.main_grad.reshape(-1) for p in model.parameters()])
+        ok = ok and torch.allclose(have, (want[0] + want[1]) / 2, rtol=1e-5, atol=1e-5)
+        caps_seen.append(ddp.bucket_cap_mb)
+        nb_seen.add(len(ddp.buckets))
+        tuner.step_done()
+    if ddp.timeline is not None:
+        ddp.timeline.flush()
+    q_out.put((rank, bool(ok), tuner.done, tuner.best_mb, [c for c, _ in tuner.results], sorted(nb_seen)))
+    hvd.shutdown()
+
+
+def test_horovod_autotune_replans_buckets_and_keeps_gradients_right(tmp_path):
+    import json
+
+    ctx = mp.get_context("spawn")
+    q_out = ctx.Queue()
+    port = 29950 + (os.getpid() % 40)
+    procs = [ctx.Process(target=_autotune_worker, args=(r, 2, port, str(tmp_path), q_out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q_out.get(timeout=180) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    (r0, ok0, done0, best0, cands0, nb0), (r1, ok1, done1, best1, cands1, nb1) = res
+    assert ok0 and ok1, "averaged gradients wrong after a bucket re-plan"
+    assert done0 and done1 and best0 == best1 and best0 in (0.008, 0.03, 1.0)     # same decision on every rank
+    assert cands0 == [0.008, 0.03, 1.0] and len(nb0) >= 2                          # the plan really changed
+    rows = (tmp_path / "autotune.csv").read_text().strip().splitlines()
+    assert rows[0] == "bucket_cap_mb,seconds_per_step,chosen" and len(rows) == 4
+    assert sum(int(r.split(",")[2]) for r in rows[1:]) == 1
+    ev = json.loads((tmp_path / "timeline.json").read_text())["traceEvents"]
+    assert ev and all(e["name"] == "allreduce" and e["args"]["bytes"] > 0 for e in ev)
