@@ -5,6 +5,9 @@
     uninstall <release> [--root DIR]
     status    <release> [--root DIR]
     logs      <release> [--root DIR] [--tail N]
+    smoke     [--gpus N] [--root DIR]            (GPU / mounts / native libraries / collective check)
+    stage-data <src> <dst under /efs or /fsx> [--root DIR]
+    attach    [release] [--root DIR]             (where /efs and /fsx live locally and what is in them)
 
 Mirrors `helm install <release> <chart> -f <values.yaml> -n <ns>`
 (examples/accelerate/bert-glue-mrpc/README.md:23-25).
@@ -52,7 +55,27 @@ def main(argv=None) -> int:
         p.add_argument("release")
         p.add_argument("--tail", type=int, default=None)
         _common(p)
+    p = sub.add_parser("smoke")
+    p.add_argument("--gpus", type=int, default=0)
+    _common(p)
+    p = sub.add_parser("stage-data")
+    p.add_argument("src")
+    p.add_argument("dst")
+    _common(p)
+    p = sub.add_parser("attach")
+    p.add_argument("release", nargs="?", default=None)
+    _common(p)
     a = ap.parse_args(argv)
+    if a.cmd in ("smoke", "stage-data", "attach"):
+        from . import tools as T
+
+        if a.cmd == "smoke":
+            rep = T.smoke(a.root, a.gpus)
+            print(json.dumps(rep, indent=1))
+            return 0 if rep.get("ok") else 1
+        print(json.dumps(T.stage_data(a.root, a.src, a.dst) if a.cmd == "stage-data" else T.attach(a.root, a.release),
+                         indent=1))
+        return 0
 
     if a.cmd in ("install", "template"):
         plan = render_job(a.chart, a.release, a.values, a.sets, root=a.root, strict_exit=a.strict_exit)

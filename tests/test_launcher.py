@@ -126,3 +126,35 @@ def test_data_charts_run_offline_and_are_idempotent(tmp_root):
     jl = tmp_root / "fsx/data/redpajama/data.jsonl"
     first = json.loads(jl.read_text().splitlines()[0])
     assert isinstance(first.get("text"), str) and len(first["text"]) > 0
+
+
+def test_smoke_stage_data_attach_commands(tmp_path):
+    """The reference's manual cluster checks (eks-cluster/tests/test-gpu*.yaml) and volume utilities
+    (eks-cluster/utils/stage-data.yaml, attach-pvc.yaml) as launcher commands."""
+    import json
+    import subprocess
+    import sys
+    from pathlib import Path
+
+    repo = Path(__file__).resolve().parent.parent
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="")
+    run = lambda *a: subprocess.run([sys.executable, "-m", "b200flow.launcher", *a, "--root", str(tmp_path)],  # noqa: E731
+                                    cwd=repo, env=env, capture_output=True, text=True, timeout=300)
+    r = run("smoke", "--gpus", "2")
+    rep = json.loads(r.stdout)
+    assert r.returncode == 0 and rep["ok"], r.stdout + r.stderr
+    assert rep["collective"]["backend"] == "gloo" and all(x["allreduce_ok"] for x in rep["collective"]["ranks"])
+    assert rep["mounts"]["/fsx"]["writable"] and rep["mounts"]["/efs"]["writable"]
+    src = tmp_path / "bucket" / "my-bucket" / "ml-platform" / "data"
+    src.mkdir(parents=True)
+    (src / "a.txt").write_text("hello")
+    (src / "sub").mkdir()
+    (src / "sub" / "b.bin").write_bytes(b"\\0" * 10)
+    env["B2F_S3_ROOT"] = str(tmp_path / "bucket")
+    r = run("stage-data", "s3://my-bucket/ml-platform/data", "/efs/data/coco2017")
+    out = json.loads(r.stdout)
+    assert r.returncode == 0 and out["files"] == 2 and (tmp_path / "efs/data/coco2017/sub/b.bin").exists()
+    assert run("stage-data", str(src), "/tmp/elsewhere").returncode != 0       # only the shared mounts
+    r = run("attach")
+    listing = json.loads(r.stdout)
+    assert "/efs/data/coco2017/a.txt" in listing["/efs"]["entries"]
