@@ -20,12 +20,17 @@ all-reduce-forward after row linears.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
 import torch.nn.functional as F
 
 from ..ops import elementwise as E
 from ..ops import gemm as G
+
+
+_FUSED_AR = os.environ.get("B2F_FUSED_AR", "0") == "1"   # opt-in until measured on two GPUs
 
 
 # ---------------------------------------------------------------- primitives
@@ -235,6 +240,12 @@ class TPContext:
         return _reduce_scatter_rows(x, self.group, self.world)
 
     # -- layer interface ------------------------------------------------------
+    def _fused_replicated(self, x, n_allreduced: int) -> bool:
+        """Replicated-activation (no sequence parallelism) layers can use K4' when the all-reduced matrix
+        [tokens, n] fits its tiling; B2F_FUSED_AR=0 keeps the NCCL all-reduce."""
+        return (self.fused is not None and x.is_cuda and x.dim() == 2 and _FUSED_AR
+                and self.fused.ar_supported(x.shape[0], n_allreduced))
+
     def column_linear(self, x, w, bias=None):
         if self.world == 1:
             return G.linear(x, w, bias)
@@ -242,6 +253,8 @@ class TPContext:
             if self.fused is not None and x.is_cuda:
                 return self.fused.column_linear(x, w, bias)
             return _ColumnSP.apply(x, w, bias, self)
+        if self._fused_replicated(x, w.shape[1]):    # dgrad + all-reduce in one kernel (K4')
+            return self.fused.column_linear_replicated(x, w, bias)
         return G.linear(_CopyToTP.apply(x, self), w, bias)
 
     def column_linear_gelu(self, x, w, bias=None):
@@ -256,6 +269,8 @@ class TPContext:
             if self.fused is not None and x.is_cuda:
                 return self.fused.row_linear(x, w, bias, residual)
             return _RowSP.apply(x, w, bias, residual, self)
+        if self._fused_replicated(x, w.shape[0]):    # GEMM + all-reduce in one kernel (K4')
+            return self.fused.row_linear_replicated(x, w, bias, residual)
         y = _ReduceFromTP.apply(G.linear(x, w), self)
         if bias is not None:
             y = y + bias
@@ -276,8 +291,7 @@ class TPContext:
         if self.world == 1:
             logits = G.linear(y, weight)
             return E.cross_entropy(logits, targets, ignore_index)
-        logits = self.column_linear(y, weight) if self.sequence_parallel else \
-            G.linear(_CopyToTP.apply(y, self), weight)
+        logits = self.column_linear(y, weight)
         return _VocabParallelCE.apply(logits, targets, self, ignore_index)
 
 

@@ -286,6 +286,13 @@ struct RSArgs {
   int N;
   uint32_t epoch;
   int dbg;                  // timing experiments only (B2F_RS_DEBUG): 1 = no sends, no receives; 2 = sends only
+  // K4' (GEMM -> all-reduce): finished rows also go to every peer's full output, then one
+  // "all my rows have landed" flag per peer closes the call
+  int allreduce;
+  PeerPtrs bcast;           // symmetric: each rank's full output [T, N] bf16, row pitch ld_bcast
+  long long ld_bcast;
+  PeerPtrs done;            // symmetric u32[world]
+  uint32_t* cta_counter;    // local u32, zero between calls
 };
 
 // Partial tiles bound for a peer are staged in shared memory as bf16 rows (528 B pitch: 512 B of
@@ -324,6 +331,24 @@ struct RSPolicy {
   __device__ __forceinline__ void finish() const {
     flush();
     tma_store_wait<0>();
+    if (!a.allreduce) return;
+    // K4': this CTA's rows are in every peer's output.  The last CTA of the grid to get here tells the
+    // peers and then holds the kernel open until every peer has said the same, so that whatever follows
+    // on this stream reads a complete matrix.
+    asm volatile("fence.proxy.async;" ::: "memory");
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    if (threadIdx.x == 64) {
+      __threadfence_system();
+      const unsigned arrived = atomicAdd(a.cta_counter, 1u);
+      if (arrived == gridDim.x - 1) {
+        atomicExch(a.cta_counter, 0u);
+        __threadfence_system();
+        for (int s = 0; s < a.world; ++s)
+          if (s != a.rank) st_release_sys(static_cast<uint32_t*>(a.done.ptr[s]) + a.rank, a.epoch);
+        for (int s = 0; s < a.world; ++s)
+          if (s != a.rank) wait_flag_ge(static_cast<uint32_t*>(a.done.ptr[a.rank]) + s, a.epoch);
+      }
+    }
   }
   __device__ __forceinline__ int owner_of(int mb) const { return mb / blocks_per_rank; }
   __device__ __forceinline__ void map_tile(int t, int num_m, int nn, int& b, int& mb, int& nb) const {
@@ -438,6 +463,13 @@ struct RSPolicy {
       const int cols = a.N - n0 < BN ? a.N - n0 : BN;
       asm volatile("fence.proxy.async;" ::: "memory");
       bulk_store_1d(out + (size_t)row_local * ldo + n0, staging + (size_t)row_in_tile * RS_PITCH, (uint32_t)cols * 2);
+      if (a.allreduce) {   // K4': the same finished row into every peer's full output
+        const size_t row_global = (size_t)mb * BM + row_in_tile;
+        for (int s = 0; s < a.world; ++s)
+          if (s != a.rank)
+            bulk_store_1d(static_cast<__nv_bfloat16*>(a.bcast.ptr[s]) + row_global * a.ld_bcast + n0,
+                          staging + (size_t)row_in_tile * RS_PITCH, (uint32_t)cols * 2);
+      }
       tma_store_commit();
       return;
     }
@@ -587,11 +619,17 @@ extern "C" int b2f_ag_gemm_bf16(const long long* x_shard_ptrs, void* xg, const v
 // Y_shard[T/world, N] = RS(X[T, K] * B) (+bias) (+residual_shard).
 // recv_ptrs: each rank's symmetric receive buffer [world][T/world, N] bf16;
 // flag_ptrs: symmetric u32 [world][(T/world/128) * ceil(N/256)].
-extern "C" int b2f_gemm_rs_bf16(const void* X, const void* B, void* Y_shard, int T, int N, int K,
-                                long long ldx, long long ldb, long long ldy, int b_mn_major,
-                                const void* bias, const void* residual, long long ldr,
-                                const long long* recv_ptrs, const long long* flag_ptrs, int rank,
-                                int world, unsigned epoch, void* stream) {
+struct ARExtra {
+  const long long* out_ptrs;   // each rank's full output [T, N]
+  const long long* done_ptrs;
+  void* cta_counter;
+};
+
+static int gemm_rs_launch(const void* X, const void* B, void* Y_shard, int T, int N, int K,
+                          long long ldx, long long ldb, long long ldy, int b_mn_major,
+                          const void* bias, const void* residual, long long ldr,
+                          const long long* recv_ptrs, const long long* flag_ptrs, int rank,
+                          int world, unsigned epoch, void* stream, const ARExtra* ar) {
   B2F_REQUIRE(T % (world * BM) == 0, "gemm_rs: rows per rank must be a multiple of 128");
   B2F_REQUIRE(N % 32 == 0, "gemm_rs: N must be a multiple of 32");
   B2F_REQUIRE(ldy % 8 == 0 && (reinterpret_cast<uintptr_t>(Y_shard) & 15) == 0, "gemm_rs: output rows must be 16-byte aligned");
@@ -609,6 +647,14 @@ extern "C" int b2f_gemm_rs_bf16(const void* X, const void* B, void* Y_shard, int
   if (int rc = fill(&a.flags, flag_ptrs, world)) return rc;
   a.rank = rank; a.world = world; a.rows_per_rank = T / world; a.N = N; a.epoch = epoch;
   if (const char* e = getenv("B2F_RS_DEBUG")) a.dbg = atoi(e);
+  if (ar) {
+    a.allreduce = 1;
+    a.dbg = 0;
+    if (int rc = fill(&a.bcast, ar->out_ptrs, world)) return rc;
+    if (int rc = fill(&a.done, ar->done_ptrs, world)) return rc;
+    a.ld_bcast = ldy;
+    a.cta_counter = static_cast<uint32_t*>(ar->cta_counter);
+  }
   static const bool force_1cta = [] { const char* e = getenv("B2F_FUSED_TP_CORE"); return e && e[0] == '1'; }();
   if (!force_1cta && (T / world) % 256 == 0 && N >= 256) {
     CUtensorMap ma2, mb2;
@@ -634,4 +680,35 @@ extern "C" int b2f_gemm_rs_bf16(const void* X, const void* B, void* Y_shard, int
       ma, mb, p, a);
   B2F_CHECK_CUDA(cudaGetLastError());
   return 0;
+}
+
+extern "C" int b2f_gemm_rs_bf16(const void* X, const void* B, void* Y_shard, int T, int N, int K,
+                                long long ldx, long long ldb, long long ldy, int b_mn_major,
+                                const void* bias, const void* residual, long long ldr,
+                                const long long* recv_ptrs, const long long* flag_ptrs, int rank,
+                                int world, unsigned epoch, void* stream) {
+  return gemm_rs_launch(X, B, Y_shard, T, N, K, ldx, ldb, ldy, b_mn_major, bias, residual, ldr, recv_ptrs,
+                        flag_ptrs, rank, world, epoch, stream, nullptr);
+}
+
+// K4': Y[T, N] = all-reduce(X[T, K] * B) (+bias) (+residual) on every rank — Megatron's row-parallel
+// linear (and the dgrad of a column-parallel one) without sequence parallelism.
+// The reduce-scatter half is K4 unchanged; a rank's finished rows then go into its own output and,
+// with one 512-byte bulk copy per row and peer, into every peer's, and the kernel ends only when every
+// peer has reported that all of its rows have landed.
+// out_ptrs: each rank's [T, N] bf16 output in symmetric memory (row pitch ldy); residual: this rank's
+// own rows [T/world, N]; done_ptrs: symmetric u32[world]; cta_counter: local u32, zero at first use.
+extern "C" int b2f_gemm_ar_bf16(const void* X, const void* B, const long long* out_ptrs, int T, int N, int K,
+                                long long ldx, long long ldb, long long ldy, int b_mn_major,
+                                const void* bias, const void* residual, long long ldr,
+                                const long long* recv_ptrs, const long long* flag_ptrs,
+                                const long long* done_ptrs, void* cta_counter, int rank, int world,
+                                unsigned epoch, void* stream) {
+  B2F_REQUIRE(out_ptrs && done_ptrs && cta_counter, "gemm_ar: output, done-flag and counter buffers required");
+  B2F_REQUIRE(world >= 2 && world <= MAX_WORLD && rank >= 0 && rank < world, "gemm_ar: bad rank / group size");
+  B2F_REQUIRE(T % world == 0, "gemm_ar: rows must divide by the group size");
+  ARExtra ar{out_ptrs, done_ptrs, cta_counter};
+  void* own_rows = reinterpret_cast<__nv_bfloat16*>(out_ptrs[rank]) + (size_t)rank * (T / world) * ldy;
+  return gemm_rs_launch(X, B, own_rows, T, N, K, ldx, ldb, ldy, b_mn_major, bias, residual, ldr, recv_ptrs,
+                        flag_ptrs, rank, world, epoch, stream, &ar);
 }

@@ -169,6 +169,15 @@ int b2f_gemm_rs_bf16(const void* X, const void* B, void* Y_shard, int T, int N, 
                      long long ldx, long long ldb, long long ldy, int b_mn_major, const void* bias,
                      const void* residual, long long ldr, const long long* recv_ptrs,
                      const long long* flag_ptrs, int rank, int world, unsigned epoch, void* stream);
+/* K4': GEMM -> all-reduce, Y[T, N] complete on every rank (Megatron RowParallelLinear without
+ * sequence parallelism and the dgrad of ColumnParallelLinear: cuBLAS + NCCL all-reduce).
+ * out_ptrs: every rank's [T, N] bf16 output in symmetric memory; residual: this rank's own rows
+ * [T/world, N]; done_ptrs: symmetric u32[world]; cta_counter: local u32 that is zero between calls. */
+int b2f_gemm_ar_bf16(const void* X, const void* B, const long long* out_ptrs, int T, int N, int K,
+                     long long ldx, long long ldb, long long ldy, int b_mn_major, const void* bias,
+                     const void* residual, long long ldr, const long long* recv_ptrs,
+                     const long long* flag_ptrs, const long long* done_ptrs, void* cta_counter,
+                     int rank, int world, unsigned epoch, void* stream);
 
 /* ---- K12-K15: Mask R-CNN detection kernels (tf.image.crop_and_resize / non_max_suppression,
  * tensorpack model_box / model_frcnn / model_mrcnn).  Features are NHWC bf16, one pointer per

@@ -23,6 +23,8 @@ def _run(env_extra):
     errs = {m.group(1): float(m.group(2)) for m in re.finditer(r"(K3|K4) loopback rel err ([0-9.e+-]+)", out)}
     assert set(errs) == {"K3", "K4"}, out[-800:]
     assert all(v < 2e-2 for v in errs.values()), errs
+    ar = [float(m.group(1)) for m in re.finditer(r"K4AR loopback rel err ([0-9.e+-]+)", out)]
+    assert len(ar) == 2 and all(v < 2e-2 for v in ar), out[-800:]
     assert "K1/K2 loopback done" in out
     m = re.search(r"K5 loopback max \|combine\(dispatch\(x\)\) - x\| ([0-9.e+-]+)", out)
     assert m and float(m.group(1)) == 0.0, out[-400:]

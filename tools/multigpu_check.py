@@ -186,6 +186,17 @@ def group_fused_gemm():
             ys = ftp.gemm_rs(xr, wr, bias, res)
             torch.cuda.synchronize()
             report(f"gemm_rs_{T}x{N}x{K}_r{rep}", rel(ys, ref) < 2e-2, err=rel(ys, ref))
+        # K4': GEMM -> all-reduce, the complete matrix on every rank (bias once, residual on top)
+        res_full = torch.randn(T, N, device=dev, dtype=torch.bfloat16)
+        dist.broadcast(res_full, src=0)
+        ref_ar = full + bias.float() + res_full.float()
+        for rep in range(3):
+            ya = ftp.gemm_ar(xr, wr, bias, res_full)
+            torch.cuda.synchronize()
+            report(f"gemm_ar_{T}x{N}x{K}_r{rep}", rel(ya, ref_ar) < 2e-2, err=rel(ya, ref_ar))
+        ya = ftp.gemm_ar(xr, wr.t().contiguous(), None, None, b_mn_major=True)      # dgrad form
+        torch.cuda.synchronize()
+        report(f"gemm_ar_mn_{T}x{N}x{K}", rel(ya, full) < 2e-2, err=rel(ya, full))
     T, N, K = 4096, 4096, 4096 // world * 2
     ts = T // world
     x = torch.randn(T, K, device=dev, dtype=torch.bfloat16)
@@ -204,8 +215,14 @@ def group_fused_gemm():
         dist.reduce_scatter_tensor(out, yp)
     t_rs_n = timeit(nccl_rs)
     t_plain = timeit(lambda: torch.matmul(x, w.t()))
+    t_ar = timeit(lambda: ftp.gemm_ar(x, w))
+    def nccl_ar():
+        yp = torch.matmul(x, w.t())
+        dist.all_reduce(yp)
+    t_ar_n = timeit(nccl_ar)
     report("fused_gemm_perf", True, ag_gemm_ms=t_ag, nccl_ag_cublas_ms=t_ag_n, gemm_rs_ms=t_rs,
-           cublas_nccl_rs_ms=t_rs_n, cublas_gemm_only_ms=t_plain, shape=[T, N, K])
+           cublas_nccl_rs_ms=t_rs_n, gemm_ar_ms=t_ar, cublas_nccl_ar_ms=t_ar_n, cublas_gemm_only_ms=t_plain,
+           shape=[T, N, K])
 
 
 def group_moe_ep():

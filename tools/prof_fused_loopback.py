@@ -53,6 +53,23 @@ def k3_k4():
     torch.cuda.synchronize()
     ref = x[:ts].float() @ w.float().t()          # the absent peer's partial is zero
     print("K4 loopback rel err", float((ysh.float() - ref).abs().max() / ref.abs().max()))
+    # K4' (GEMM -> all-reduce): rank 0's finished rows must appear in its own and in the peer's full output
+    outs = [torch.zeros(T, N, device=dev, dtype=torch.bfloat16) for _ in range(world)]
+    done = [flags(64) for _ in range(world)]
+    counter = torch.zeros(1, dtype=torch.int32, device=dev)
+    bias = torch.randn(N, device=dev, dtype=torch.bfloat16)
+    res = torch.randn(ts, N, device=dev, dtype=torch.bfloat16)
+    for epoch in (2, 3):     # twice: the CTA counter must be back at zero for the second call
+        _lib.call("b2f_gemm_ar_bf16", ptr(x), ptr(w), ptrs(*outs), c_int(T), c_int(N), c_int(K), c_ll(K), c_ll(K),
+                  c_ll(N), c_int(0), ptr(bias), ptr(res), c_ll(N), ptrs(*recv), ptrs(*fl), ptrs(*done), ptr(counter),
+                  c_int(0), c_int(world), ctypes.c_uint(epoch), stream_ptr())
+        torch.cuda.synchronize()
+        ref = ref_rows = x[:ts].float() @ w.float().t() + bias.float() + res.float()
+        err = max(float((o[:ts].float() - ref_rows).abs().max() / ref.abs().max()) for o in outs)
+        untouched = all(float(o[ts:].abs().max()) == 0.0 for o in outs)      # peer rows are the peer's to write
+        print("K4AR loopback rel err", err if untouched and int(counter.item()) == 0 else 1.0)
+        for o in outs:
+            o.zero_()
 
 
 def k1_k2():
