@@ -9,14 +9,15 @@
 On one GPU these are plain tcgen05 GEMMs.  Across a TP group there are two
 implementations behind the same interface: the *baseline* path (NCCL/gloo
 collective followed by / preceded by the GEMM — what Megatron does, SURVEY.md
-§2F/§2H C7-C10) and the *fused* path (`parallel/fused_tp.py`: K3 all-gather→GEMM
-and K4 GEMM→reduce-scatter kernels over NVLink peer memory).  The baseline path
+§2F/§2H C7-C10) and the *fused* path (`parallel/fused_tp.py`: K3 all-gather→GEMM,
+K4 GEMM→reduce-scatter and K4′ GEMM→all-reduce kernels over NVLink peer memory).  The baseline path
 also runs on CPU/gloo, which is how the sharding math is unit-tested.
 
 With ``sequence_parallel=False`` the context reproduces W3's non-SP layout
 (`examples/megatron-deepspeed/gpt2_345m/pretrain-ddp-tp-pp-zero1.yaml:39-55`):
 identity-forward/all-reduce-backward before column linears and
-all-reduce-forward after row linears.
+all-reduce-forward after row linears; on GPUs both all-reduces are fused into the
+producing GEMM (K4′) when the token count is a multiple of 128 x TP.
 """
 from __future__ import annotations
 
@@ -30,7 +31,7 @@ from ..ops import elementwise as E
 from ..ops import gemm as G
 
 
-_FUSED_AR = os.environ.get("B2F_FUSED_AR", "0") == "1"   # opt-in until measured on two GPUs
+_FUSED_AR = os.environ.get("B2F_FUSED_AR", "1") == "1"   # B2F_FUSED_AR=0: NCCL all-reduce around the GEMM
 
 
 # ---------------------------------------------------------------- primitives

@@ -34,5 +34,9 @@ def test_fused_tensor_parallel_gemms():
     _run(["fused_gemm"])
 
 
+def test_tensor_parallel_without_sequence_parallel_uses_gemm_allreduce():
+    _run(["tp_replicated"])
+
+
 def test_tp_pp_engines_and_moe_expert_parallel():
     _run(["tp", "pp", "moe_ep"])

@@ -40,6 +40,7 @@ def _build(tp, pp, world, rank):
     eng = initialize(cfg, {"train_micro_batch_size_per_gpu": 2,
                            "gradient_accumulation_steps": GAS if world > 1 else GAS * 1,
                            "optimizer": {"params": {"lr": 2e-3, "weight_decay": 0.0}},
+                           "sequence_parallel": os.environ.get("B2F_TEST_NOSP") != "1",
                            "gradient_clipping": 1.0}, ps, device=torch.device("cpu"), seed=11)
     return cfg, ps, dp, eng
 
@@ -146,6 +147,16 @@ def test_topology_matches_single_process(single, world, tp, pp, port):
         # DP changes the global batch (GAS*dp micro-batches), so compare against itself:
         # the loss must fall and stay finite; exact parity is covered by the dp=1 cases
         assert all(map(lambda v: v == v, got)) and got[-1] < got[0]
+
+
+def test_tp_without_sequence_parallel_matches_single_process(single, monkeypatch):
+    """Replicated activations + all-reduces (the reference's GPT-2 345M TP2 x PP2 example passes no
+    --sequence-parallel): same loss curve as one process."""
+    monkeypatch.setenv("B2F_TEST_NOSP", "1")
+    for world, tp, pp, port in ((2, 2, 1, 29617), (4, 2, 2, 29618)):
+        got = _run(world, tp, pp, port)
+        for a, b in zip(got, single):
+            assert abs(a - b) < 2e-3, (world, got, single)
 
 
 def test_topology_rank_order_tp_fastest():

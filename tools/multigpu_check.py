@@ -110,7 +110,7 @@ def group_allreduce():
                nccl_busbw_gbs=bus / (tn / 1e3))
 
 
-def _engine_curve(tp, pp, fused, steps=4, preset_kw=None):
+def _engine_curve(tp, pp, fused, steps=4, preset_kw=None, ds_extra=None):
     from b200flow.engines.ds_engine import initialize
     from b200flow.models.gpt import config_from_preset
 
@@ -118,7 +118,8 @@ def _engine_curve(tp, pp, fused, steps=4, preset_kw=None):
     cfg = config_from_preset("llama-tiny", hidden=512, heads=4, ffn=1024, layers=4, vocab_size=2048,
                              max_seq=256, **(preset_kw or {}))
     eng = initialize(cfg, {"train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": 4,
-                           "optimizer": {"params": {"lr": 1e-3}}, "fused_collectives": fused}, ps, seed=5)
+                           "optimizer": {"params": {"lr": 1e-3}}, "fused_collectives": fused,
+                           **(ds_extra or {})}, ps, seed=5)
     g = torch.Generator().manual_seed(100 + ps.dp_rank)
     data = [torch.randint(0, cfg.vocab_size, (2, 257), generator=g) for _ in range(4)]
     batches = [(t[:, :-1].contiguous().cuda(), t[:, 1:].contiguous().cuda()) for t in data]
@@ -143,6 +144,28 @@ def group_tp():
         report("tp_fused_vs_nccl", ok, base=base, fused=fused, fused_active=eng.tp.fused is not None)
     except Exception as e:  # noqa: BLE001
         report("tp_fused_vs_nccl", False, exception=repr(e)[:400])
+
+
+def group_tp_replicated():
+    """Tensor parallelism without sequence parallelism (the reference's GPT-2 345M TP2 x PP2 example passes no
+    --sequence-parallel): NCCL all-reduces vs the K4' kernels."""
+    import b200flow.parallel.tensor_parallel as TPM
+
+    nosp = {"sequence_parallel": False}
+    TPM._FUSED_AR = False
+    base, _ = _engine_curve(dist.get_world_size(), 1, False, ds_extra=nosp)
+    report("tp_replicated_nccl_runs", base[-1] < base[0], losses=base)
+    try:
+        TPM._FUSED_AR = True
+        calls0 = 0
+        fused, eng = _engine_curve(dist.get_world_size(), 1, True, ds_extra=nosp)
+        ok = all(abs(a - b) < 3e-2 for a, b in zip(base, fused))
+        report("tp_replicated_fused_vs_nccl", ok and eng.tp.fused.rs_calls > calls0, base=base, fused=fused,
+               k4ar_calls=eng.tp.fused.rs_calls)
+    except Exception as e:  # noqa: BLE001
+        report("tp_replicated_fused_vs_nccl", False, exception=repr(e)[:400])
+    finally:
+        TPM._FUSED_AR = False
 
 
 def group_pp():
@@ -189,9 +212,11 @@ def group_fused_gemm():
         # K4': GEMM -> all-reduce, the complete matrix on every rank (bias once, residual on top)
         res_full = torch.randn(T, N, device=dev, dtype=torch.bfloat16)
         dist.broadcast(res_full, src=0)
-        ref_ar = full + bias.float() + res_full.float()
+        bias_rep = bias.clone()                      # a row-parallel bias is the same on every rank
+        dist.broadcast(bias_rep, src=0)
+        ref_ar = full + bias_rep.float() + res_full.float()
         for rep in range(3):
-            ya = ftp.gemm_ar(xr, wr, bias, res_full)
+            ya = ftp.gemm_ar(xr, wr, bias_rep, res_full)
             torch.cuda.synchronize()
             report(f"gemm_ar_{T}x{N}x{K}_r{rep}", rel(ya, ref_ar) < 2e-2, err=rel(ya, ref_ar))
         ya = ftp.gemm_ar(xr, wr.t().contiguous(), None, None, b_mn_major=True)      # dgrad form
@@ -259,7 +284,7 @@ def group_moe_ep():
 
 
 GROUPS = {"moe_ep": group_moe_ep, "fused_gemm": group_fused_gemm, "arena": group_arena, "allreduce": group_allreduce, "zero1": group_zero1, "tp": group_tp,
-          "pp": group_pp}
+          "pp": group_pp, "tp_replicated": group_tp_replicated}
 
 if __name__ == "__main__":
     init_distributed("nccl")
