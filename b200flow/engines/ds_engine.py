@@ -164,6 +164,7 @@ class TrainEngine:
         self.skipped_steps = 0
         self._overflow = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.global_steps = 0
+        self._micro_steps, self._stepped_at = 0, -1
         self.p2p = None
         self.last_loss = None
 
@@ -210,6 +211,18 @@ class TrainEngine:
             seq = batches[0][0].shape[1]
             losses = PP.run_1f1b(self.stage, self.pp_world, self.gas,
                                  lambda i, act: self._forward_micro(batches[i], act), self._p2p(seq))
+        scale = self._optimizer_step()
+        loss = torch.stack(losses).mean() if losses else torch.zeros((), device=self.device)
+        if scale != 1.0:
+            loss = loss / scale
+        if self.pp_world > 1:  # make the loss visible on every stage (for logging)
+            dist.broadcast(loss, src=self.ps.pp_ranks[-1], group=self.ps.pp_group)
+        self.last_loss = loss
+        return loss
+
+    def _optimizer_step(self) -> float:
+        """Everything after the last backward of a step: gradient collection, TP / tied-weight reductions,
+        fp16 overflow check, ZeRO-1 update.  Returns the loss scale the step ran with."""
         self.flat.collect_autograd_grads()
         if self.flat_expert is not None:
             self.flat_expert.collect_autograd_grads()
@@ -231,13 +244,37 @@ class TrainEngine:
                 self.expert_optimizer.lr = self.optimizer.lr
                 self.expert_optimizer.step(grad_divisor=div)
         self.global_steps += 1
-        loss = torch.stack(losses).mean() if losses else torch.zeros((), device=self.device)
-        if scale != 1.0:
-            loss = loss / scale
-        if self.pp_world > 1:  # make the loss visible on every stage (for logging)
-            dist.broadcast(loss, src=self.ps.pp_ranks[-1], group=self.ps.pp_group)
-        self.last_loss = loss
+        return scale
+
+    # ------------------------------------------- DeepSpeed's forward / backward / step triple
+    def __call__(self, tokens: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        return self.forward(tokens, labels)
+
+    def forward(self, tokens: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        """`loss = engine(batch)` of a DeepSpeed training loop without pipeline parallelism (Megatron-DeepSpeed
+        takes this route when `--pipeline-model-parallel-size 1`: `model[0](...)`, `model[0].backward(loss)`,
+        `model[0].step()`).  Returns the unscaled loss of one micro-batch."""
+        assert self.pp_world == 1, "forward/backward/step is the non-pipeline API; use train_batch under PP"
+        if self._micro_steps % self.gas == 0:
+            self.optimizer.zero_grad()
+            if self.expert_optimizer is not None:
+                self.expert_optimizer.zero_grad()
+        return self.model(tokens=tokens, labels=labels)
+
+    def backward(self, loss: torch.Tensor) -> torch.Tensor:
+        (loss * self.loss_scaler.scale if self.loss_scaler is not None else loss).backward()
+        self._micro_steps += 1
         return loss
+
+    def is_gradient_accumulation_boundary(self) -> bool:
+        return self._micro_steps % self.gas == 0 and self._micro_steps > 0
+
+    def step(self) -> None:
+        """Optimizer step at a gradient-accumulation boundary, a no-op otherwise (DeepSpeed semantics)."""
+        if not self.is_gradient_accumulation_boundary() or self._stepped_at == self._micro_steps:
+            return
+        self._stepped_at = self._micro_steps
+        self._optimizer_step()
 
     def eval_batch(self, data_iter: Iterator, num_micro_batches: int = 1) -> torch.Tensor:
         """Forward-only loss over `num_micro_batches` micro-batches (Megatron's `--eval-iters` loop calls

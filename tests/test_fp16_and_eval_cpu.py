@@ -144,3 +144,29 @@ def test_eval_batch_under_pipeline_parallelism_matches_single_process():
         for a, b in zip(ev, want):
             assert abs(a - b) < 2e-3, (rank, ev, want)
         assert abs(tr - want_train) < 2e-3
+
+
+def test_forward_backward_step_triple_equals_train_batch():
+    """DeepSpeed's non-pipeline loop (`loss = engine(x, y); engine.backward(loss); engine.step()`) makes the
+    same updates as `train_batch`, with `step()` acting only at accumulation boundaries."""
+    cfg, a = _engine({"fp16": {"enabled": True, "initial_scale_power": 8}})
+    _, b = _engine({"fp16": {"enabled": True, "initial_scale_power": 8}})
+    data = _batches(cfg)
+    it = itertools.cycle(data)
+    la = [float(a.train_batch(it)) for _ in range(3)]            # gas = 2 -> 6 micro-batches
+    lb, k = [], 0
+    for _ in range(3):
+        acc = 0.0
+        for _ in range(2):
+            tok, lab = data[k % len(data)]
+            k += 1
+            loss = b(tok, lab)
+            b.backward(loss)
+            assert b.is_gradient_accumulation_boundary() == (k % 2 == 0)
+            b.step()                                              # no-op in the middle of an accumulation window
+            acc += float(loss)
+        lb.append(acc / 2)
+    assert b.global_steps == 3 and a.global_steps == 3
+    for x, y in zip(la, lb):
+        assert abs(x - y) < 1e-5, (la, lb)
+    assert torch.allclose(a.flat.params, b.flat.params, atol=1e-6)
