@@ -7,7 +7,9 @@ re-designed around flat storage:
 
 * gradients live in ONE flat fp32 buffer (symmetric peer memory on GPUs), so a bucket is a
   slice and needs no copy-in / copy-out;
-* the bucket plan comes from the host C++ planner (`csrc/host/bucket_plan.cpp`);
+* the bucket plan comes from the host C++ planner (`csrc/host/bucket_plan.cpp`) and the per-event
+  readiness bookkeeping runs in the host C++ reducer (`csrc/host/reducer.cpp`): a gradient-ready event is
+  one call that answers "which bucket, if any, is now complete";
 * a bucket is reduced by the K1 kernel (`csrc/comm/collectives.cu`): in-place NVLS /
   peer-memory all-reduce with the 1/N averaging fused, launched on a side stream using a
   few SMs while backward keeps the rest;
@@ -92,21 +94,42 @@ class DistributedDataParallel(nn.Module):
     def set_bucket_cap(self, cap_mb: float) -> None:
         """(Re)plan the buckets.  Only between steps (after `finish_reduction`); every rank must pass the
         same value — the plan is a pure function of the parameter layout and the cap."""
+        from ..ops._lib import host_lib
+
         self.bucket_cap_mb = float(cap_mb)
         self.buckets = plan_buckets(self.flat, cap_mb, first_cap_mb=min(1.0, cap_mb))
-        self._slot_bucket = {}
-        for bi, (s0, s1, _, _) in enumerate(self.buckets):
-            for s in range(s0, s1):
-                self._slot_bucket[s] = bi
-        self._pending = [0] * len(self.buckets)
-        self._launched = [False] * len(self.buckets)
-        self._reset()
+        lib = host_lib()
+        lib.b2f_reducer_create.restype = ctypes.c_void_p
+        lib.b2f_reducer_mark.restype = lib.b2f_reducer_next_unlaunched.restype = ctypes.c_int
+        lib.b2f_reducer_mark.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        lib.b2f_reducer_next_unlaunched.argtypes = lib.b2f_reducer_reset.argtypes = [ctypes.c_void_p]
+        lib.b2f_reducer_destroy.argtypes = [ctypes.c_void_p]
+        self._free_reducer()
+        plan = np.array(self.buckets, dtype=np.int64).reshape(-1)
+        uses = np.array([int(getattr(p, "ddp_uses", 1)) for p in self._params_by_slot], dtype=np.int32)
+        self._lib = lib
+        self._state = lib.b2f_reducer_create(plan.ctypes.data_as(ctypes.c_void_p), ctypes.c_int(len(self.buckets)),
+                                             ctypes.c_int(len(self.flat.slots)), uses.ctypes.data_as(ctypes.c_void_p))
+        assert self._state, "bucket plan does not cover every parameter exactly once"
+        self._uses_seen = uses.tolist()
+
+    def _free_reducer(self):
+        if getattr(self, "_state", None):
+            self._lib.b2f_reducer_destroy(self._state)
+            self._state = None
+
+    def __del__(self):
+        try:
+            self._free_reducer()
+        except Exception:       # noqa: BLE001 - interpreter shutdown
+            pass
 
     def _reset(self):
-        for bi, (s0, s1, _, _) in enumerate(self.buckets):
-            self._pending[bi] = s1 - s0
-            self._launched[bi] = False
-        self._uses = [int(getattr(self._params_by_slot[si], "ddp_uses", 1)) for si in range(len(self.flat.slots))]
+        uses = [int(getattr(p, "ddp_uses", 1)) for p in self._params_by_slot]
+        if uses != self._uses_seen:          # a model changed how often it uses a parameter: rebuild
+            self.set_bucket_cap(self.bucket_cap_mb)
+        else:
+            self._lib.b2f_reducer_reset(self._state)
 
     def _make_hook(self, si):
         def hook(p):
@@ -120,21 +143,15 @@ class DistributedDataParallel(nn.Module):
         return lambda: self._mark(si)
 
     def _mark(self, si):
-        if not self.require_sync or self._uses[si] <= 0:
+        if not self.require_sync:
             return
-        self._uses[si] -= 1
-        if self._uses[si] > 0:      # parameter used more than once (tied weights): wait for all
-            return
-        bi = self._slot_bucket[si]
-        self._pending[bi] -= 1
-        if self._pending[bi] == 0:
+        bi = self._lib.b2f_reducer_mark(self._state, si)
+        if bi >= 0:
             self._launch(bi)
 
     def _launch(self, bi):
-        if self._launched[bi] or self.world == 1:
-            self._launched[bi] = True
+        if self.world == 1:
             return
-        self._launched[bi] = True
         _, _, e0, e1 = self.buckets[bi]
         if self.timeline is not None:
             self.timeline.instant("allreduce", bucket=bi, bytes=(e1 - e0) * self.flat.grads.element_size())
@@ -169,9 +186,8 @@ class DistributedDataParallel(nn.Module):
         """Call after backward: reduce any bucket whose parameters received no gradient this
         step, wait for the side stream, re-arm the bookkeeping."""
         if self.require_sync:
-            for bi in range(len(self.buckets)):
-                if not self._launched[bi]:
-                    self._launch(bi)
+            while (bi := self._lib.b2f_reducer_next_unlaunched(self._state)) >= 0:
+                self._launch(bi)
             if self.side is not None:
                 torch.cuda.current_stream().wait_stream(self.side)
             for w, g in self._works:

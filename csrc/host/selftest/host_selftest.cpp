@@ -26,6 +26,12 @@ void b2f_build_doc_idx(int32_t* out, const int32_t* documents, long long num_doc
 int b2f_plan_buckets(const int64_t* offsets, const int64_t* numels, int nslots, int64_t total_elems,
                      int64_t elem_bytes, int64_t cap_bytes, int64_t first_cap_bytes, int64_t* out,
                      int max_buckets);
+void* b2f_reducer_create(const int64_t* plan, int nb, int nslots, const int32_t* uses);
+void b2f_reducer_destroy(void* h);
+void b2f_reducer_reset(void* h);
+int b2f_reducer_mark(void* h, int slot);
+int b2f_reducer_next_unlaunched(void* h);
+int b2f_reducer_num_buckets(void* h);
 void* b2f_chan_create(const char* name, uint64_t capacity);
 void* b2f_chan_open(const char* name);
 int b2f_chan_send(void* ch, const void* buf, uint32_t len, long timeout_ms);
@@ -105,6 +111,36 @@ static void test_buckets() {
   CHECK(b2f_plan_buckets(offs.data(), nums.data(), n, total, 4, 4000, 4000, out.data(), 2) == -1);  // too few rows
 }
 
+static void test_reducer() {
+  // 3 buckets over 7 slots, backward order: {5,6} {2,3,4} {0,1}; slot 3 is used twice (tied weight)
+  const int64_t plan[12] = {5, 7, 50, 70, 2, 5, 20, 50, 0, 2, 0, 20};
+  const int32_t uses[7] = {1, 1, 1, 2, 1, 1, 1};
+  void* r = b2f_reducer_create(plan, 3, 7, uses);
+  CHECK(r != nullptr);
+  if (!r) return;
+  CHECK(b2f_reducer_num_buckets(r) == 3);
+  for (int step = 0; step < 2; ++step) {
+    CHECK(b2f_reducer_mark(r, 6) == -1);
+    CHECK(b2f_reducer_mark(r, 5) == 0);          // bucket 0 complete
+    CHECK(b2f_reducer_mark(r, 5) == -1);         // surplus event ignored
+    CHECK(b2f_reducer_mark(r, 4) == -1);
+    CHECK(b2f_reducer_mark(r, 3) == -1);         // first of two uses
+    CHECK(b2f_reducer_mark(r, 2) == -1);
+    CHECK(b2f_reducer_mark(r, 3) == 1);          // last use completes bucket 1
+    CHECK(b2f_reducer_mark(r, 1) == -1);         // slot 0 never gets a gradient this step
+    CHECK(b2f_reducer_next_unlaunched(r) == 2);  // the sweep hands out what is left, once
+    CHECK(b2f_reducer_next_unlaunched(r) == -1);
+    CHECK(b2f_reducer_mark(r, 0) == -1);         // a late event cannot hand bucket 2 out again
+    b2f_reducer_reset(r);
+  }
+  CHECK(b2f_reducer_mark(r, 99) == -1 && b2f_reducer_mark(r, -1) == -1);
+  b2f_reducer_destroy(r);
+  const int64_t overlap[8] = {0, 3, 0, 30, 2, 4, 20, 40};   // slot 2 in two buckets
+  CHECK(b2f_reducer_create(overlap, 2, 4, nullptr) == nullptr);
+  const int64_t gap[4] = {1, 4, 10, 40};                    // slot 0 in no bucket
+  CHECK(b2f_reducer_create(gap, 1, 4, nullptr) == nullptr);
+}
+
 static void test_mailbox() {
   const std::string name = "/b2f_selftest_" + std::to_string((long)getpid());
   void* rx = b2f_chan_create(name.c_str(), 1 << 16);
@@ -145,6 +181,7 @@ static void test_mailbox() {
 int main() {
   test_indices();
   test_buckets();
+  test_reducer();
   test_mailbox();
   if (failures) {
     std::fprintf(stderr, "host_selftest: %d failure(s)\n", failures);
