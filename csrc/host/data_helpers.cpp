@@ -1,7 +1,7 @@
 // b200flow — dataset index builders for the mmap'd GPT dataset (host C++).
 //
 // Equivalent in purpose to Megatron's pybind11 `helpers.cpp`
-// (build_sample_idx / build_blending_indices; SURVEY.md §2E, §2H C31 — compiled at
+// (build_sample_idx / build_blending_indices / build_mapping; SURVEY.md §2E, §2H C31 — compiled at
 // run time by `_compile_dependencies` in the reference's Megatron-DeepSpeed pin,
 // containers/megatron-deepspeed/Dockerfile:13).  Written against a plain C ABI so
 // it is callable through ctypes with numpy buffers.
@@ -86,6 +86,68 @@ void b2f_build_doc_idx(int32_t* out, const int32_t* documents, long long num_doc
       std::swap(dst[i], dst[j]);
     }
   }
+}
+
+// Sentence-pair sample map for BERT-style pre-training over a corpus whose items are sentences
+// (Megatron `build_mapping`).  A document d owns the sentences [docs[d], docs[d + 1]).  Each epoch
+// walks the documents, packing consecutive sentences into one sample until the sample's target
+// length is reached — the target is max_seq_length, or with probability short_seq_prob a uniform
+// length in [2, max_seq_length] — while at least two sentences remain for the next sample; the
+// sentences left at the end of a document close its last sample.  Documents with fewer than
+// min_num_sent sentences, or with a sentence longer than `long_sentence_len` tokens, are skipped.
+// Rows are {first sentence, last sentence + 1, target length}; they are shuffled at the end.
+// Pass maps == NULL to count: the return value is the number of rows (at most max_num_samples),
+// and a second call with a buffer of that many rows fills them identically.
+long long b2f_build_bert_mapping(const int64_t* docs, long long num_docs, const int32_t* sizes,
+                                 int32_t num_epochs, long long max_num_samples, int32_t max_seq_length,
+                                 double short_seq_prob, uint64_t seed, int32_t min_num_sent,
+                                 int32_t long_sentence_len, int64_t* maps) {
+  const int32_t short_every = short_seq_prob > 0.0 ? static_cast<int32_t>(1.0 / short_seq_prob + 0.5) : 0;
+  std::mt19937 rng(static_cast<uint32_t>(seed));
+  auto next_target = [&]() -> int32_t {
+    const uint32_t r = rng();
+    if (short_every > 0 && r % static_cast<uint32_t>(short_every) == 0)
+      return 2 + static_cast<int32_t>(rng() % static_cast<uint32_t>(max_seq_length - 1));
+    return max_seq_length;
+  };
+  long long rows = 0;
+  for (int32_t epoch = 0; epoch < num_epochs && rows < max_num_samples; ++epoch) {
+    for (long long d = 0; d < num_docs && rows < max_num_samples; ++d) {
+      const int64_t first = docs[d], last = docs[d + 1];
+      if (last - first < min_num_sent) continue;
+      bool too_long = false;
+      for (int64_t s = first; s < last; ++s)
+        if (sizes[s] > long_sentence_len) { too_long = true; break; }
+      if (too_long) continue;
+      int64_t start = first;
+      int32_t tokens = 0, nsent = 0, target = next_target();
+      for (int64_t s = first; s < last && rows < max_num_samples; ++s) {
+        tokens += sizes[s];
+        ++nsent;
+        const int64_t remaining = last - s - 1;
+        if ((tokens >= target && remaining > 1 && nsent >= min_num_sent) || remaining == 0) {
+          if (maps) {
+            maps[3 * rows + 0] = start;
+            maps[3 * rows + 1] = s + 1;
+            maps[3 * rows + 2] = target;
+          }
+          ++rows;
+          start = s + 1;
+          tokens = 0;
+          nsent = 0;
+          target = next_target();
+        }
+      }
+    }
+  }
+  if (maps) {
+    std::mt19937_64 shuf(seed + 1);
+    for (long long i = rows - 1; i > 0; --i) {
+      const uint64_t j = shuf() % static_cast<uint64_t>(i + 1);
+      for (int c = 0; c < 3; ++c) std::swap(maps[3 * i + c], maps[3 * j + c]);
+    }
+  }
+  return rows;
 }
 
 }  // extern "C"

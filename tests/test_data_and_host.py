@@ -176,3 +176,148 @@ def test_polygon_rasteriser_oracle_and_rle_round_trip():
     assert full["counts"] == [0, 20]
     assert rle_iou(rle_encode(m[0]), rle_encode(m[0])) == 1.0
     assert 0.0 < rle_iou(rle_encode(m[0]), rle_encode(m[2])) < 1.0
+
+
+def _sentence_corpus(tmp_path, rng):
+    from b200flow.data.indexed_dataset import MMapIndexedDatasetBuilder
+
+    prefix = str(tmp_path / "bert_sentences")
+    b = MMapIndexedDatasetBuilder(prefix, dtype=np.int32)
+    doc_sents = []
+    for d in range(60):
+        nsent = int(rng.randint(1, 12))               # some single-sentence documents: skipped (min_num_sent = 2)
+        lens = rng.randint(3, 40, size=nsent)
+        if d == 7:
+            lens[0] = 600                             # a sentence beyond the long-sentence limit: document skipped
+        for n in lens:
+            b.add_item(rng.randint(5, 1000, size=int(n)))
+        b.end_document()
+        doc_sents.append(lens.tolist())
+    b.finalize()
+    return prefix, doc_sents
+
+
+def _python_bert_mapping(docs, sizes, num_epochs, max_num_samples, max_len, short_prob, seed, min_sent=2, long_len=512):
+    """The same walk in Python, drawing from the same Mersenne-Twister stream."""
+    rs = np.random.RandomState(seed)
+    draw = lambda: int(rs.randint(0, 2 ** 32, dtype=np.uint64))     # noqa: E731
+    every = int(1.0 / short_prob + 0.5) if short_prob > 0 else 0
+
+    def target():
+        r = draw()
+        if every > 0 and r % every == 0:
+            return 2 + draw() % (max_len - 1)
+        return max_len
+
+    rows = []
+    for _ in range(num_epochs):
+        for d in range(len(docs) - 1):
+            first, last = int(docs[d]), int(docs[d + 1])
+            if last - first < min_sent or any(sizes[s] > long_len for s in range(first, last)):
+                continue
+            start, tok, ns, tgt = first, 0, 0, target()
+            for s in range(first, last):
+                if len(rows) >= max_num_samples:
+                    break
+                tok += int(sizes[s])
+                ns += 1
+                rem = last - s - 1
+                if (tok >= tgt and rem > 1 and ns >= min_sent) or rem == 0:
+                    rows.append((start, s + 1, tgt))
+                    start, tok, ns, tgt = s + 1, 0, 0, target()
+    return rows[:max_num_samples]
+
+
+def test_bert_sentence_mapping_cpp_matches_python_walk(tmp_path):
+    from b200flow.data.bert_dataset import build_bert_mapping
+    from b200flow.data.indexed_dataset import MMapIndexedDataset
+
+    prefix, doc_sents = _sentence_corpus(tmp_path, np.random.RandomState(3))
+    ds = MMapIndexedDataset(prefix)
+    docs, sizes = np.asarray(ds.doc_idx), np.asarray(ds.sizes)
+    assert len(docs) == 61 and len(sizes) == sum(len(x) for x in doc_sents)
+    for epochs, cap, prob in ((1, 10 ** 9, 0.0), (3, 10 ** 9, 0.1), (5, 40, 0.25)):
+        got = build_bert_mapping(docs, sizes, num_epochs=epochs, max_num_samples=cap, max_seq_length=61,
+                                 short_seq_prob=prob, seed=99)
+        want = _python_bert_mapping(docs, sizes, epochs, cap, 61, prob, 99)
+        assert len(got) == len(want) and len(got) > 0
+        assert sorted(map(tuple, got.tolist())) == sorted(want)            # same rows, shuffled order
+        assert got.tolist() != sorted(got.tolist())
+        again = build_bert_mapping(docs, sizes, num_epochs=epochs, max_num_samples=cap, max_seq_length=61,
+                                   short_seq_prob=prob, seed=99)
+        assert np.array_equal(got, again)                                   # deterministic
+    # every row stays inside one document and skips document 7 (over-long sentence) and 1-sentence documents
+    bounds = docs.tolist()
+    for first, last, tgt in got.tolist():
+        d = max(i for i in range(60) if bounds[i] <= first)
+        assert last <= bounds[d + 1] and d != 7 and len(doc_sents[d]) >= 2 and 2 <= tgt <= 61
+
+
+def test_bert_pretraining_samples(tmp_path):
+    from b200flow.data.bert_dataset import BertPretrainingDataset
+
+    prefix, _ = _sentence_corpus(tmp_path, np.random.RandomState(4))
+    ds = BertPretrainingDataset(prefix, vocab_size=1000, cls_id=1, sep_id=2, mask_id=3, pad_id=0, max_seq_length=64,
+                                num_epochs=2, seed=7)
+    assert len(ds) > 50
+    nsp = []
+    for i in range(0, len(ds), 3):
+        s = ds[i]
+        ids, tt, am, lab = s["input_ids"], s["token_type_ids"], s["attention_mask"], s["labels"]
+        n = int(am.sum())
+        assert ids.shape == (64,) and n <= 64 and ids[0] == 1 and ids[n - 1] == 2 and (ids[n:] == 0).all()
+        seps = (ids[:n] == 2).nonzero().flatten()
+        assert len(seps) == 2 and (tt[:seps[0] + 1] == 0).all() and (tt[seps[0] + 1:n] == 1).all()
+        pred = (lab != -100).nonzero().flatten()
+        assert 1 <= len(pred) <= max(1, round(n * 0.15)) and (pred < n).all()
+        assert not any(int(ids[p]) in (1, 2) and int(lab[p]) in (1, 2) for p in pred)   # specials are never predicted
+        unchanged = (lab == -100)[:n]
+        assert ((ids[:n] != 3) | ~unchanged).all()                                      # [MASK] only at predicted positions
+        nsp.append(int(s["next_sentence_label"]))
+        assert torch.equal(ds[i]["input_ids"], ids)                                     # a sample is a pure function of its index
+    assert 0 < sum(nsp) < len(nsp)
+
+
+def test_wordpiece_tokenizer_and_sentence_level_preprocessing(tmp_path):
+    import json
+    import subprocess
+    import sys
+    from pathlib import Path
+
+    from b200flow.data.bert_dataset import BertPretrainingDataset
+    from b200flow.data.tokenizer import BertWordPieceTokenizer, split_sentences, write_wordpiece_vocab
+
+    vocab = tmp_path / "vocab.txt"
+    vocab.write_text("\n".join(["[PAD]", "[UNK]", "[CLS]", "[SEP]", "[MASK]", "the", "un", "##aff", "##able", "runn",
+                                "##ing", ",", ".", "he", "is", "cafe", "!"]) + "\n")
+    tok = BertWordPieceTokenizer(vocab, lower_case=True)
+    ids = tok.tokenize("He is UNAFFABLE, running. Café!  xyzzy")
+    toks = [tok.inv[i] for i in ids]
+    assert toks == ["he", "is", "un", "##aff", "##able", ",", "runn", "##ing", ".", "cafe", "!", "[UNK]"]
+    assert tok.detokenize(ids[:5]) == "he is unaffable"
+    pair, types = tok.encode_pair("he is", "the cafe", max_length=6)
+    assert [tok.inv[i] for i in pair] == ["[CLS]", "he", "[SEP]", "the", "cafe", "[SEP]"] or len(pair) == 6
+    assert len(pair) == len(types) == 6 and types[0] == 0 and types[-1] == 1
+    assert BertWordPieceTokenizer(vocab, lower_case=False).tokenize("He") == [tok.unk]     # cased: "He" not in vocab
+    assert split_sentences('It rained. "Why?" he asked (twice)! No answer came.\nNew line') == [
+        "It rained.", '"Why?" he asked (twice)!', "No answer came.", "New line"]
+
+    # synthetic vocabulary + sentence-level corpus through the Megatron preprocess tool, then BERT samples from it
+    docs = [" ".join(f"Sentence number {i} of document {d} talks about topic {(i * d) % 7}." for i in range(2 + d % 5))
+            for d in range(30)]
+    big = tmp_path / "bert-vocab.txt"
+    write_wordpiece_vocab(big, docs, size=400)
+    src = tmp_path / "train.json"
+    src.write_text("\n".join(json.dumps({"text": t}) for t in docs) + "\n")
+    tool = Path(__file__).resolve().parent.parent / "b200flow/workloads/trees/megatron_deepspeed/tools/preprocess_data.py"
+    res = subprocess.run([sys.executable, str(tool), "--input", str(src), "--output-prefix", str(tmp_path / "bert"),
+                          "--vocab-file", str(big), "--tokenizer-type", "BertWordPieceLowerCase", "--split-sentences",
+                          "--workers", "2"], capture_output=True, text=True, timeout=300,
+                         env=dict(__import__("os").environ, PYTHONPATH=str(tool.parents[5])))
+    assert res.returncode == 0, res.stdout + res.stderr
+    t2 = BertWordPieceTokenizer(big)
+    ds = BertPretrainingDataset(str(tmp_path / "bert_text_sentence"), vocab_size=t2.vocab_size, cls_id=t2.cls,
+                                sep_id=t2.sep, mask_id=t2.mask, pad_id=t2.pad, max_seq_length=48, num_epochs=1)
+    assert len(ds.ds.doc_idx) == 31 and len(ds.ds) == sum(2 + d % 5 for d in range(30)) and len(ds) >= 30
+    s = ds[0]
+    assert s["input_ids"][0] == t2.cls and t2.unk not in s["input_ids"].tolist()   # character fallback: nothing is unknown
