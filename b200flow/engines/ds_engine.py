@@ -37,7 +37,7 @@ from ..utils.flat import FlatParams
 _KNOWN = {"train_micro_batch_size_per_gpu", "gradient_accumulation_steps", "zero_optimization",
           "bf16", "fp16", "gradient_clipping", "optimizer", "wall_clock_breakdown",
           "train_batch_size", "steps_per_print", "scheduler", "fused_collectives",
-          "activation_checkpointing", "sequence_parallel", "expert_parallel_size"}
+          "activation_checkpointing", "sequence_parallel", "expert_parallel_size", "flops_profiler"}
 
 
 def split_layers(num_layers: int, stages: int) -> list[tuple[int, int]]:
@@ -163,6 +163,15 @@ class TrainEngine:
         self.loss_scaler = make_loss_scaler(config.get("fp16"))
         self.skipped_steps = 0
         self._overflow = torch.zeros(1, dtype=torch.int32, device=self.device)
+        # DeepSpeed's `wall_clock_breakdown` / `flops_profiler`: off unless the config asks
+        self.timers = None
+        if config.get("wall_clock_breakdown"):
+            from ..obs.tracking import Timers
+
+            self.timers = Timers(use_cuda=self.device.type == "cuda")
+        self.steps_per_print = int(config.get("steps_per_print", 10))
+        fp = config.get("flops_profiler") or {}
+        self._flops_profile_step = int(fp.get("profile_step", 1)) if fp.get("enabled") else -1
         self.global_steps = 0
         self._micro_steps, self._stepped_at = 0, -1
         self.p2p = None
@@ -201,17 +210,38 @@ class TrainEngine:
         if self.expert_optimizer is not None:
             self.expert_optimizer.zero_grad()
         batches = [next(data_iter) for _ in range(self.gas)]
+        tm = self.timers
+        if tm is not None or self._flops_profile_step == self.global_steps + 1:
+            import time
+
+            self._sync()
+            t_step = time.perf_counter()
         if self.pp_world == 1:
             losses = []
             for mb in batches:
+                tm and tm.start("fwd")
                 loss = self._forward_micro(mb, None)
+                tm and (tm.stop("fwd"), tm.start("bwd"))
                 loss.backward()
+                tm and tm.stop("bwd")
                 losses.append(loss.detach())
         else:
             seq = batches[0][0].shape[1]
+            tm and tm.start("pipeline_fwd_bwd")
             losses = PP.run_1f1b(self.stage, self.pp_world, self.gas,
                                  lambda i, act: self._forward_micro(batches[i], act), self._p2p(seq))
+            tm and tm.stop("pipeline_fwd_bwd")
+        tm and tm.start("step")
         scale = self._optimizer_step()
+        tm and tm.stop("step")
+        if tm is not None and self.global_steps % self.steps_per_print == 0:
+            ms = tm.summary(reset=True)                     # max over ranks
+            if not dist.is_initialized() or dist.get_rank() == 0:
+                print("time (ms) | " + " | ".join(f"{k}: {v / self.steps_per_print:.2f}" for k, v in sorted(ms.items())),
+                      flush=True)
+        if self._flops_profile_step == self.global_steps:
+            self._sync()
+            self._print_flops_profile(batches, time.perf_counter() - t_step)
         loss = torch.stack(losses).mean() if losses else torch.zeros((), device=self.device)
         if scale != 1.0:
             loss = loss / scale
@@ -219,6 +249,25 @@ class TrainEngine:
             dist.broadcast(loss, src=self.ps.pp_ranks[-1], group=self.ps.pp_group)
         self.last_loss = loss
         return loss
+
+    def _sync(self):
+        if self.device.type == "cuda":
+            torch.cuda.synchronize()
+
+    def _print_flops_profile(self, batches, seconds: float) -> None:
+        """DeepSpeed flops-profiler summary of one step: parameters, model FLOPs, achieved rate."""
+        b, s = batches[0][0].shape
+        tokens = b * s * self.gas * self.dp_world
+        flops = self.cfg.flops_per_token(s) * tokens
+        world = dist.get_world_size() if dist.is_initialized() else 1
+        self.flops_profile = {"step": self.global_steps, "params": self.cfg.param_count(), "tokens_per_step": tokens,
+                              "flops_per_step": flops, "seconds": seconds,
+                              "tflops_per_gpu": flops / seconds / world / 1e12}
+        if not dist.is_initialized() or dist.get_rank() == 0:
+            p = self.flops_profile
+            print(f"flops profiler | step {p['step']} | params {p['params'] / 1e6:.1f} M | fwd+bwd flops per step "
+                  f"{p['flops_per_step'] / 1e12:.3f} T | step latency {seconds * 1e3:.1f} ms | "
+                  f"{p['tflops_per_gpu']:.2f} TFLOPS per GPU", flush=True)
 
     def _optimizer_step(self) -> float:
         """Everything after the last backward of a step: gradient collection, TP / tied-weight reductions,

@@ -170,3 +170,18 @@ def test_forward_backward_step_triple_equals_train_batch():
     for x, y in zip(la, lb):
         assert abs(x - y) < 1e-5, (la, lb)
     assert torch.allclose(a.flat.params, b.flat.params, atol=1e-6)
+
+
+def test_wall_clock_breakdown_and_flops_profiler_print(capsys):
+    cfg, eng = _engine({"wall_clock_breakdown": True, "steps_per_print": 2,
+                        "flops_profiler": {"enabled": True, "profile_step": 2}})
+    it = itertools.cycle(_batches(cfg))
+    for _ in range(4):
+        eng.train_batch(it)
+    out = capsys.readouterr().out
+    lines = [l for l in out.splitlines() if l.startswith("time (ms) |")]
+    assert len(lines) == 2 and all(k in lines[0] for k in ("fwd:", "bwd:", "step:"))
+    assert out.count("flops profiler | step 2 |") == 1
+    p = eng.flops_profile
+    assert p["tokens_per_step"] == 2 * 32 * 2 and p["flops_per_step"] == cfg.flops_per_token(32) * p["tokens_per_step"]
+    assert p["tflops_per_gpu"] > 0
