@@ -12,7 +12,6 @@ Ray's and Lightning's APIs are provided by `b200flow.engines.ray_train_api` /
 Size knobs: B2F_MODEL, B2F_EPOCHS, B2F_TRAIN_SAMPLES, B2F_EVAL_SAMPLES.
 """
 import os
-import tempfile
 
 import torch
 

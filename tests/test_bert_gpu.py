@@ -1,6 +1,5 @@
 """GPU: BERT on the native kernels (fused FFN, key-length attention, group LayerNorm) against the
 fp32 CPU oracle, and the masked-position MLM head against the all-positions head."""
-import copy
 
 import pytest
 import torch

@@ -7,7 +7,6 @@
 * GPT-2 byte-level BPE on a locally written vocab / merges pair.
 * Bucket planner (torch DDP Reducer bucket assignment) and the shared-memory mailbox.
 """
-import ctypes
 import multiprocessing as mp
 
 import numpy as np

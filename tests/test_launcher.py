@@ -4,7 +4,6 @@ import os
 import sys
 from pathlib import Path
 
-import pytest
 
 from b200flow.jobspec.render import render_job
 from b200flow.launcher import runner as R

@@ -3,7 +3,6 @@ import os
 import sys
 from pathlib import Path
 
-import pytest
 import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
