@@ -331,6 +331,56 @@ class MaskRCNN(nn.Module):
         return results
 
 
+def tensorpack_to_torchvision_names(blocks=(3, 4, 6, 3)) -> dict[str, tuple[str, str]]:
+    """tensorpack ResNet variable name -> (torchvision parameter / buffer name, kind) for the body of a
+    bottleneck ResNet.  Kinds: "conv" (HWIO -> OIHW), "vec".  The reference starts Mask R-CNN from
+    `BACKBONE.WEIGHTS=.../ImageNet-R50-AlignPadding.npz` (examples/maskrcnn/train-maskrcnn-tensorpack.yaml:32,
+    fetched by charts/machine-learning/data-prep/coco-data/templates/coco-data.yaml:31-35)."""
+    bn = {"gamma": "weight", "beta": "bias", "mean/EMA": "running_mean", "variance/EMA": "running_var"}
+    out = {"conv0/W": ("conv1.weight", "conv")}
+    for k, v in bn.items():
+        out[f"conv0/bn/{k}"] = (f"bn1.{v}", "vec")
+    for g, nb in enumerate(blocks):
+        for b in range(nb):
+            tp, tv = f"group{g}/block{b}", f"layer{g + 1}.{b}"
+            for i in (1, 2, 3):
+                out[f"{tp}/conv{i}/W"] = (f"{tv}.conv{i}.weight", "conv")
+                for k, v in bn.items():
+                    out[f"{tp}/conv{i}/bn/{k}"] = (f"{tv}.bn{i}.{v}", "vec")
+            if b == 0:
+                out[f"{tp}/convshortcut/W"] = (f"{tv}.downsample.0.weight", "conv")
+                for k, v in bn.items():
+                    out[f"{tp}/convshortcut/bn/{k}"] = (f"{tv}.downsample.1.{v}", "vec")
+    return out
+
+
+def load_tensorpack_backbone(body: nn.Module, npz_path) -> dict:
+    """Copy a tensorpack ResNet `.npz` into a torchvision-style body.  Returns a report
+    {"loaded": n, "missing": [...], "unused": [...], "placeholder": bool}; the offline stand-in written by
+    the coco-data chart (`synthetic` key only) is reported as a placeholder and leaves the body as it is."""
+    import numpy as np
+
+    with np.load(str(npz_path)) as z:
+        keys = set(z.files)
+        if keys <= {"synthetic"}:
+            return {"loaded": 0, "missing": [], "unused": [], "placeholder": True}
+        table = tensorpack_to_torchvision_names()
+        sd = body.state_dict()
+        loaded, missing = 0, []
+        for tp_name, (tv_name, kind) in table.items():
+            if tp_name not in keys or tv_name not in sd:
+                missing.append(tp_name)
+                continue
+            w = torch.from_numpy(np.asarray(z[tp_name]))
+            if kind == "conv":
+                w = w.permute(3, 2, 0, 1)          # [kh, kw, in, out] -> [out, in, kh, kw]
+            assert tuple(w.shape) == tuple(sd[tv_name].shape), (tp_name, tuple(w.shape), tuple(sd[tv_name].shape))
+            sd[tv_name].copy_(w.to(sd[tv_name].dtype))
+            loaded += 1
+        unused = sorted(k for k in keys if k not in table)
+    return {"loaded": loaded, "missing": missing, "unused": unused, "placeholder": False}
+
+
 def paste_masks(det: dict, H: int, W: int) -> torch.Tensor:
     """28x28 probabilities -> full-image binary masks (the notebook's `get_mask` step)."""
     if "masks" not in det or det["masks"].numel() == 0:

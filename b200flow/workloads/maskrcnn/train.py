@@ -13,7 +13,7 @@ and ignored).  Ranks come from the launcher's mpirun mode (OMPI_COMM_WORLD_* / R
 
 Callbacks mirror tensorpack's: periodic model saver (`model-<step>.pt` + `model-<step>.index`
 marker + `checkpoint` file under `<logdir>`, auto-resume from the newest), LR schedule with
-linear warm-up, throughput tracker, evaluation every EVAL_PERIOD epochs (COCO bbox / segm mAP on the
+linear warm-up, throughput / memory / time-left trackers, evaluation every EVAL_PERIOD epochs (COCO bbox / segm mAP on the
 synthetic validation split, coco_eval.py), TensorBoard scalars.  COCO-shaped synthetic images.
 
 Test-size knobs: B2F_MRCNN_WIDTH, B2F_MRCNN_IMAGE (HxW), B2F_MRCNN_EPOCHS, B2F_MRCNN_STEPS.
@@ -122,6 +122,15 @@ def main():
         mcfg.roi_batch = 128
     torch.manual_seed(1234)
     model = MaskRCNN(mcfg).to(dev)
+    wpath = str(cfgd.get("BACKBONE.WEIGHTS", "") or "")
+    if wpath and os.path.exists(wpath) and width >= 1.0:       # ImageNet ResNet-50 in tensorpack's npz naming
+        from b200flow.models.maskrcnn import load_tensorpack_backbone
+
+        rep = load_tensorpack_backbone(model.backbone.body, wpath)
+        if rank == 0:
+            what = "offline placeholder, backbone stays randomly initialised" if rep["placeholder"] else \
+                f"{rep['loaded']} tensors loaded, {len(rep['missing'])} missing, {len(rep['unused'])} unused"
+            print(f"[b200flow] BACKBONE.WEIGHTS={wpath}: {what}", flush=True)
     if use_cuda:
         model = model.to(torch.bfloat16).to(memory_format=torch.channels_last)
     ddp, tuner = None, None
@@ -191,8 +200,17 @@ def main():
             msg = {k: v / steps_per_epoch for k, v in agg.items()}
             print(f"[epoch {epoch}] step {step} | " + " ".join(f"{k}={v:.4f}" for k, v in msg.items()) +
                   f" | lr={opt.param_groups[0]['lr']:.5f} | throughput={seen / dt:.2f} images/s", flush=True)
+            # tensorpack's GPUMemoryTracker / HostMemoryTracker / EstimatedTimeLeft callbacks
+            import psutil
+
+            gpu_gb = torch.cuda.max_memory_allocated() / 2 ** 30 if use_cuda else 0.0
+            host_gb = psutil.Process().memory_info().rss / 2 ** 30
+            eta_min = (total_epochs - epoch) * dt / 60.0
+            print(f"[epoch {epoch}] PeakMemory(GPU) {gpu_gb:.2f} GiB | HostMemory {host_gb:.2f} GiB | "
+                  f"estimated time left {eta_min:.1f} min", flush=True)
             tracker.log({**{f"loss/{k}": v for k, v in msg.items()}, "learning_rate": opt.param_groups[0]["lr"],
-                         "throughput/images_per_sec": seen / dt}, step)
+                         "throughput/images_per_sec": seen / dt, "memory/gpu_peak_gib": gpu_gb,
+                         "memory/host_rss_gib": host_gb}, step)
         if epoch % eval_period == 0:
             model.eval()
             val = list(coco_like(4, H, W, seed=77 + rank, device="cpu"))

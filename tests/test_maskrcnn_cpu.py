@@ -48,3 +48,34 @@ def test_maskrcnn_chart_then_jupyter_chart(tmp_root):
     assert pngs and pngs[0].read_bytes()[:8] == b"\x89PNG\r\n\x1a\n"
     dets = json.loads((viz / "detections.json").read_text())
     assert isinstance(dets, (list, dict)) and len(dets) > 0
+
+
+def test_tensorpack_npz_backbone_loads_into_resnet50(tmp_path):
+    """BACKBONE.WEIGHTS: a tensorpack-named ResNet-50 npz (HWIO convolutions, bn gamma/beta/EMA statistics)
+    fills every convolution and norm tensor of the body; the offline placeholder is recognised."""
+    import numpy as np
+    import torch
+    import torchvision
+    from torchvision.ops import FrozenBatchNorm2d
+
+    from b200flow.models.maskrcnn import load_tensorpack_backbone, tensorpack_to_torchvision_names
+
+    torch.manual_seed(0)
+    src = torchvision.models.resnet50(weights=None, norm_layer=FrozenBatchNorm2d)
+    for k, v in src.state_dict().items():
+        if "bn" in k or "downsample.1" in k:
+            v.copy_(torch.rand_like(v) + 0.5)
+    table = tensorpack_to_torchvision_names()
+    sd = src.state_dict()
+    body_keys = {k for k in sd if not k.startswith("fc.")}
+    assert {tv for tv, _ in table.values()} == body_keys           # the table covers the whole body, nothing else
+    arrays = {tp: (sd[tv].permute(2, 3, 1, 0) if kind == "conv" else sd[tv]).numpy() for tp, (tv, kind) in table.items()}
+    arrays["linear/W"] = np.zeros((2048, 1000), dtype=np.float32)   # classifier head: present upstream, unused here
+    np.savez(tmp_path / "ImageNet-R50-AlignPadding.npz", **arrays)
+    dst = torchvision.models.resnet50(weights=None, norm_layer=FrozenBatchNorm2d)
+    rep = load_tensorpack_backbone(dst, tmp_path / "ImageNet-R50-AlignPadding.npz")
+    assert rep == {"loaded": len(table), "missing": [], "unused": ["linear/W"], "placeholder": False}
+    for k in body_keys:
+        assert torch.equal(dst.state_dict()[k], sd[k]), k
+    np.savez(tmp_path / "placeholder.npz", synthetic=np.zeros(1))
+    assert load_tensorpack_backbone(dst, tmp_path / "placeholder.npz")["placeholder"] is True
