@@ -14,6 +14,7 @@ from __future__ import annotations
 
 import argparse
 import json
+import math
 from pathlib import Path
 
 import numpy as np
@@ -130,8 +131,12 @@ def write_coco_tree(out: Path, num_train: int = 16, num_val: int = 4) -> None:
             torch.save(s["image"].half(), out / split / f"{i:012d}.pt")
             images.append({"id": i, "file_name": f"{i:012d}.pt", "height": 128, "width": 160})
             for b, l in zip(s["boxes"].tolist(), s["labels"].tolist()):
+                cx, cy, rx, ry = (b[0] + b[2]) / 2, (b[1] + b[3]) / 2, (b[2] - b[0]) / 2, (b[3] - b[1]) / 2
+                poly = [v for k in range(16) for v in (cx + rx * math.cos(2 * math.pi * k / 16),
+                                                       cy + ry * math.sin(2 * math.pi * k / 16))]
                 anns.append({"image_id": i, "bbox": [b[0], b[1], b[2] - b[0], b[3] - b[1]],
-                             "category_id": l, "iscrowd": 0, "id": len(anns)})
+                             "category_id": l, "iscrowd": 0, "id": len(anns), "segmentation": [poly],
+                             "area": math.pi * rx * ry})
         (out / "annotations").mkdir(exist_ok=True)
         (out / "annotations" / f"instances_{split}.json").write_text(json.dumps(
             {"images": images, "annotations": anns,

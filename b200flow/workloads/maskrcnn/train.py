@@ -77,11 +77,13 @@ def evaluate_coco(model, val, dev, use_cuda, mode_mask):
     for d, g in zip(dets, val):
         d = {k: v for k, v in d.items() if k != "fastrcnn_all_scores"}
         evs["bbox"].add({"boxes": d["boxes"].float().cpu(), "labels": d["labels"].cpu(), "scores": d["scores"].float().cpu()},
-                        {"boxes": g["boxes"].float().cpu(), "labels": g["labels"].cpu()})
+                        {"boxes": g["boxes"].float().cpu(), "labels": g["labels"].cpu(),
+                         **({"iscrowd": g["iscrowd"].cpu()} if "iscrowd" in g else {})})
         if mode_mask:
             pm = paste_masks(d, H, W).cpu() if d["labels"].numel() else torch.zeros(0, H, W, dtype=torch.uint8)
             evs["segm"].add({"masks": pm, "labels": d["labels"].cpu(), "scores": d["scores"].float().cpu()},
-                            {"masks": g["masks"].cpu(), "labels": g["labels"].cpu()})
+                            {"masks": g["masks"].cpu(), "labels": g["labels"].cpu(),
+                             **({"iscrowd": g["iscrowd"].cpu()} if "iscrowd" in g else {})})
     out = {}
     for ev in evs.values():
         out.update(ev.gather().tensorpack_names())
@@ -166,14 +168,39 @@ def main():
     ckpt_period = int(cfgd.get("TRAIN.CHECKPOINT_PERIOD", 1))
     eval_period = int(cfgd.get("TRAIN.EVAL_PERIOD", 1))
     data = coco_like(10 ** 9, H, W, seed=1000 + rank, device="cpu")
+    # DATA.BASEDIR with COCO annotations (the coco-data chart's output): train on it, evaluate on DATA.VAL
+    train_set = val_set = None
+    basedir = str(cfgd.get("DATA.BASEDIR", "") or "")
+    def split_name(v, default):        # tensorpack registers COCO splits as "coco_train2017": ["coco_train2017"] / ("coco_val2017")
+        v = str(v if v else default).strip("[]()'\", ")
+        return v[len("coco_"):] if v.startswith("coco_") else v
+
+    split_t, split_v = split_name(cfgd.get("DATA.TRAIN"), "train2017"), split_name(cfgd.get("DATA.VAL"), "val2017")
+    if basedir and os.path.exists(os.path.join(basedir, "annotations", f"instances_{split_t}.json")):
+        from b200flow.data.coco import COCODetection
+
+        kw = dict(short_side=min(H, W), max_side=max(H, W), with_masks=mcfg.mode_mask)
+        train_set = COCODetection(basedir, split_t, train=True, seed=1000, **kw)
+        if os.path.exists(os.path.join(basedir, "annotations", f"instances_{split_v}.json")):
+            val_set = COCODetection(basedir, split_v, train=False, **kw)
+        if rank == 0:
+            print(f"[b200flow] DATA.BASEDIR={basedir}: {len(train_set)} training images"
+                  + (f", {len(val_set)} validation images" if val_set is not None else ""), flush=True)
     start_epoch = step // max(1, steps_per_epoch)
     for epoch in range(start_epoch + 1, total_epochs + 1):
         model.train()
         t0, seen, agg = time.time(), 0, {}
         for _ in range(steps_per_epoch):
             maybe_inject_fault(step)
-            samples = [next(data) for _ in range(batch)]
-            imgs = torch.stack([s["image"] for s in samples]).to(dev)
+            if train_set is not None:
+                from b200flow.data.coco import collate_padded
+
+                first = (step * world + rank) * batch
+                imgs, samples = collate_padded([train_set[(first + j) % len(train_set)] for j in range(batch)])
+                imgs = imgs.to(dev)
+            else:
+                samples = [next(data) for _ in range(batch)]
+                imgs = torch.stack([s["image"] for s in samples]).to(dev)
             if use_cuda:
                 imgs = imgs.to(torch.bfloat16)
             tg = [{k: s[k].to(dev) for k in ("boxes", "labels", "masks")} for s in samples]
@@ -213,7 +240,14 @@ def main():
                          "memory/host_rss_gib": host_gb}, step)
         if epoch % eval_period == 0:
             model.eval()
-            val = list(coco_like(4, H, W, seed=77 + rank, device="cpu"))
+            if val_set is not None:      # each rank predicts its shard of the validation split
+                from b200flow.data.coco import collate_padded
+
+                mine = list(range(rank, min(len(val_set), 8 * world), world)) or [0]
+                vimgs, vt = collate_padded([val_set[j] for j in mine])
+                val = [{"image": vimgs[j], **vt[j]} for j in range(len(mine))]
+            else:
+                val = list(coco_like(4, H, W, seed=77 + rank, device="cpu"))
             scores = evaluate_coco(model, val, dev, use_cuda, mcfg.mode_mask)
             if rank == 0:
                 print(f"[epoch {epoch}] " + " | ".join(f"{k}: {v:.4f}" for k, v in scores.items()), flush=True)

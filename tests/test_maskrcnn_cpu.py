@@ -79,3 +79,42 @@ def test_tensorpack_npz_backbone_loads_into_resnet50(tmp_path):
         assert torch.equal(dst.state_dict()[k], sd[k]), k
     np.savez(tmp_path / "placeholder.npz", synthetic=np.zeros(1))
     assert load_tensorpack_backbone(dst, tmp_path / "placeholder.npz")["placeholder"] is True
+
+
+def test_training_reads_the_coco_tree_written_by_the_coco_data_chart(tmp_root):
+    """coco-data chart (offline: synthetic COCO-format tree with polygon segmentations) -> maskrcnn chart with
+    its default DATA.BASEDIR: annotations are parsed, polygons rasterised, images resized / flipped / padded,
+    and the validation split is scored with the COCO protocol."""
+    import torch
+
+    from b200flow.data.coco import COCODetection, collate_padded
+
+    v = tmp_root / "data.yaml"
+    v.write_text("{}\n")
+    rc, st, out = _install("d-coco", "coco-data", v, tmp_root, TINY)
+    assert rc == 0, out
+    base = tmp_root / "fsx/data/coco2017"
+    ds = COCODetection(base, "train2017", train=True, short_side=96, max_side=128, seed=3)
+    assert len(ds) == 16
+    s = ds[0]
+    h, w = s["image"].shape[-2:]
+    assert min(h, w) <= 96 and max(h, w) <= 128 and s["masks"].shape == (len(s["labels"]), h, w)
+    for b, m in zip(s["boxes"], s["masks"]):                      # a rasterised ellipse fills ~pi/4 of its box
+        x0, y0, x1, y1 = b.tolist()
+        frac = float(m.sum()) / max(1.0, (x1 - x0) * (y1 - y0))
+        assert 0.55 < frac < 1.0 and float(m[:, : max(0, int(x0) - 1)].sum()) == 0
+    flipped = [i for i in range(len(ds)) if not torch.equal(ds[i]["boxes"], COCODetection(
+        base, "train2017", train=False, short_side=96, max_side=128)[i]["boxes"])]
+    assert 0 < len(flipped) < len(ds)                              # the training view flips about half the images
+    imgs, tg = collate_padded([ds[0], ds[1]])
+    assert imgs.shape[-1] % 32 == 0 and imgs.shape[-2] % 32 == 0 and tg[0]["masks"].shape[-2:] == imgs.shape[-2:]
+
+    t = tmp_root / "train.yaml"
+    t.write_text("maskrcnn:\n  gpus: 2\n  gpu_nodes: 1\n  gpus_per_node: 2\n  steps_per_epoch: 2\n"
+                 "  lr_schedule: \"[4,6,8]\"\n")
+    rc, st, out = _install("mrcnn-coco", "maskrcnn", t, tmp_root, dict(TINY, B2F_MRCNN_EPOCHS="1"))
+    logs = "\n".join(p.read_text(errors="replace") for p in
+                     (tmp_root / ".b200flow/releases/mrcnn-coco/pods").glob("*/stdout.log"))
+    assert rc == 0 and st["phase"] == "Succeeded", logs[-3000:]
+    assert "16 training images, 4 validation images" in logs and "mAP(segm)/IoU=0.5:0.95" in logs
+    assert "BACKBONE.WEIGHTS" not in logs or "placeholder" in logs
