@@ -190,13 +190,18 @@ def main():
     for epoch in range(start_epoch + 1, total_epochs + 1):
         model.train()
         t0, seen, agg = time.time(), 0, {}
+        if train_set is not None:      # this rank's images of the epoch, produced ahead by worker processes
+            from b200flow.data.prefetch import PrefetchLoader
+
+            order = [((step + k) * world + rank) * batch + j for k in range(steps_per_epoch) for j in range(batch)]
+            feed = iter(PrefetchLoader(train_set, [i % len(train_set) for i in order],
+                                       workers=int(os.environ.get("B2F_DATA_WORKERS", 4 if use_cuda else 0))))
         for _ in range(steps_per_epoch):
             maybe_inject_fault(step)
             if train_set is not None:
                 from b200flow.data.coco import collate_padded
 
-                first = (step * world + rank) * batch
-                imgs, samples = collate_padded([train_set[(first + j) % len(train_set)] for j in range(batch)])
+                imgs, samples = collate_padded([next(feed) for _ in range(batch)])
                 imgs = imgs.to(dev)
             else:
                 samples = [next(data) for _ in range(batch)]

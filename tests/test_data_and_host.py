@@ -320,3 +320,30 @@ def test_wordpiece_tokenizer_and_sentence_level_preprocessing(tmp_path):
     assert len(ds.ds.doc_idx) == 31 and len(ds.ds) == sum(2 + d % 5 for d in range(30)) and len(ds) >= 30
     s = ds[0]
     assert s["input_ids"][0] == t2.cls and t2.unk not in s["input_ids"].tolist()   # character fallback: nothing is unknown
+
+
+class _SlowSquares:
+    """Picklable toy dataset: worker 0's items are slow, so ordering cannot come from timing."""
+
+    def __len__(self):
+        return 64
+
+    def __getitem__(self, i):
+        import time
+
+        if i == 13:
+            raise ValueError("bad sample 13")
+        if i % 2 == 0:
+            time.sleep(0.01)
+        return {"i": i, "x": torch.full((1000,), float(i * i))}
+
+
+def test_prefetch_loader_keeps_order_and_reports_worker_errors():
+    from b200flow.data.prefetch import PrefetchLoader
+
+    order = [5, 2, 8, 1, 40, 41, 42, 3, 0, 63, 62, 7]
+    got = list(PrefetchLoader(_SlowSquares(), order, workers=3, capacity=1 << 20))
+    assert [g["i"] for g in got] == order and all(float(g["x"][0]) == g["i"] ** 2 for g in got)
+    assert [g["i"] for g in PrefetchLoader(_SlowSquares(), order, workers=0)] == order
+    with pytest.raises(RuntimeError, match="bad sample 13"):
+        list(PrefetchLoader(_SlowSquares(), [1, 2, 13, 4], workers=2, capacity=1 << 20))
