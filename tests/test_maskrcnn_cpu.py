@@ -112,7 +112,7 @@ def test_training_reads_the_coco_tree_written_by_the_coco_data_chart(tmp_root):
     t = tmp_root / "train.yaml"
     t.write_text("maskrcnn:\n  gpus: 2\n  gpu_nodes: 1\n  gpus_per_node: 2\n  steps_per_epoch: 2\n"
                  "  lr_schedule: \"[4,6,8]\"\n")
-    rc, st, out = _install("mrcnn-coco", "maskrcnn", t, tmp_root, dict(TINY, B2F_MRCNN_EPOCHS="1"))
+    rc, st, out = _install("mrcnn-coco", "maskrcnn", t, tmp_root, dict(TINY, B2F_MRCNN_EPOCHS="1", B2F_DATA_WORKERS="2"))
     logs = "\n".join(p.read_text(errors="replace") for p in
                      (tmp_root / ".b200flow/releases/mrcnn-coco/pods").glob("*/stdout.log"))
     assert rc == 0 and st["phase"] == "Succeeded", logs[-3000:]
