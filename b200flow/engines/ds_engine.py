@@ -37,7 +37,8 @@ from ..utils.flat import FlatParams
 _KNOWN = {"train_micro_batch_size_per_gpu", "gradient_accumulation_steps", "zero_optimization",
           "bf16", "fp16", "gradient_clipping", "optimizer", "wall_clock_breakdown",
           "train_batch_size", "steps_per_print", "scheduler", "fused_collectives",
-          "activation_checkpointing", "sequence_parallel", "expert_parallel_size", "flops_profiler"}
+          "activation_checkpointing", "sequence_parallel", "expert_parallel_size", "flops_profiler",
+          "comms_logger"}
 
 
 def split_layers(num_layers: int, stages: int) -> list[tuple[int, int]]:
@@ -169,6 +170,12 @@ class TrainEngine:
             from ..obs.tracking import Timers
 
             self.timers = Timers(use_cuda=self.device.type == "cuda")
+        self.comms_logger = None
+        cl = config.get("comms_logger") or {}
+        if cl.get("enabled"):       # DeepSpeed's comms_logger: library collectives and fused comm kernels per step
+            from ..obs.comms import CommsLogger
+
+            self.comms_logger = CommsLogger(sync=bool(cl.get("prof_all", False)), verbose=bool(cl.get("verbose", False))).enable()
         self.steps_per_print = int(config.get("steps_per_print", 10))
         fp = config.get("flops_profiler") or {}
         self._flops_profile_step = int(fp.get("profile_step", 1)) if fp.get("enabled") else -1
@@ -239,6 +246,10 @@ class TrainEngine:
             if not dist.is_initialized() or dist.get_rank() == 0:
                 print("time (ms) | " + " | ".join(f"{k}: {v / self.steps_per_print:.2f}" for k, v in sorted(ms.items())),
                       flush=True)
+        if self.comms_logger is not None and self.global_steps % self.steps_per_print == 0:
+            if not dist.is_initialized() or dist.get_rank() == 0:
+                self.comms_logger.log_summary()
+            self.comms_logger.reset()
         if self._flops_profile_step == self.global_steps:
             self._sync()
             self._print_flops_profile(batches, time.perf_counter() - t_step)

@@ -55,6 +55,7 @@ def loaded_libraries() -> list[str]:
 
 
 _launches = 0
+call_hook = None      # optional callable(fn_name): observers of native entry points (obs/comms.py)
 # kernels launched per entry point (default 1)
 _NVTX = os.environ.get("B2F_NVTX", "0") == "1"
 _KERNELS_PER_CALL = {"b2f_norm_bwd": 2, "b2f_norm_bwd_noalloc": 2, "b2f_sumsq": 2, "b2f_attn_bwd": 3,
@@ -102,6 +103,8 @@ def call(fn_name: str, *args) -> None:
     else:
         rc = fn(*args)
     _launches += _KERNELS_PER_CALL.get(fn_name, 1)
+    if call_hook is not None:
+        call_hook(fn_name)
     if rc != 0:
         msg = lib.b2f_last_error()
         raise NativeError(f"{fn_name} failed (rc={rc}): {msg.decode() if msg else '?'}")

@@ -185,3 +185,39 @@ def test_wall_clock_breakdown_and_flops_profiler_print(capsys):
     p = eng.flops_profile
     assert p["tokens_per_step"] == 2 * 32 * 2 and p["flops_per_step"] == cfg.flops_per_token(32) * p["tokens_per_step"]
     assert p["tflops_per_gpu"] > 0
+
+
+def _comms_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.set_num_threads(1)
+    import contextlib
+    import io
+
+    from b200flow.parallel.groups import ParallelState
+
+    ps = ParallelState.initialize(tp=2, pp=1)
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        cfg, eng = _engine({"comms_logger": {"enabled": True}, "steps_per_print": 2}, ps)
+        it = itertools.cycle(_batches(cfg))
+        for _ in range(2):
+            eng.train_batch(it)
+        eng.comms_logger.disable()
+    q.put((rank, buf.getvalue()))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_comms_logger_in_the_engine_reports_tensor_parallel_collectives():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_comms_worker, args=(r, 2, 29642, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=300) for _ in range(2))
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert "comm op" in got[0] and "all_reduce" in got[0] and "all_gather" in got[0]   # SP all-gathers, norm all-reduce
+    assert got[1].count("comm op") == 0                                                    # rank 0 prints
