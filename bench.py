@@ -7,7 +7,8 @@ sub-topology (tp1 -> tp2 -> tp2.pp2), as BASELINE.md §3 specifies.  Synthetic t
 streams, random-init weights (no network here).  `--workload bert-large` measures
 BASELINE.json config 2 (BERT-large pre-training samples/s, DDP), `--workload maskrcnn` config 3
 (Mask R-CNN R50-FPN images/s, DDP), `--workload gpt-moe-1.3b` config 5 (fp8 experts, EP = #GPUs);
-`--impl twin` runs the stock-library arm (torch nn + cuBLAS + SDPA + torch DDP).
+`--impl twin` runs the stock-library arm of the same workload (torch nn + cuBLAS + SDPA + torch DDP;
+HF BERT; torchvision Mask R-CNN; all_to_all_single MoE).
 
 Contract (see the task statement): W untimed warm-up steps, then exactly K steps
 timed on the device with CUDA events between barrier+synchronize pairs, max over

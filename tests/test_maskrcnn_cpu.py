@@ -118,3 +118,20 @@ def test_training_reads_the_coco_tree_written_by_the_coco_data_chart(tmp_root):
     assert rc == 0 and st["phase"] == "Succeeded", logs[-3000:]
     assert "16 training images, 4 validation images" in logs and "mAP(segm)/IoU=0.5:0.95" in logs
     assert "BACKBONE.WEIGHTS" not in logs or "placeholder" in logs
+
+
+def test_stock_library_twin_of_maskrcnn_builds_and_steps_on_cpu():
+    """`bench.py --impl twin --workload maskrcnn`: torchvision's Mask R-CNN on the same synthetic stream.  The
+    model / batch / loss pieces are checked here at a small image size (the timing harness needs a GPU)."""
+    import torch
+
+    from b200flow.workloads.twin import maskrcnn_twin
+
+    torch.manual_seed(0)
+    model, make, loss_fn = maskrcnn_twin(torch.device("cpu"), torch.float32, batch=2, H=128, W=160, seed=5)
+    b = make()
+    assert b["images"].shape == (2, 3, 128, 160) and b["masks0"].shape[1:] == (128, 160)
+    model.train()
+    loss = loss_fn(model, b)
+    loss.backward()
+    assert torch.isfinite(loss) and any(p.grad is not None and p.grad.abs().sum() > 0 for p in model.parameters())

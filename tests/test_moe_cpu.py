@@ -158,3 +158,29 @@ def test_top2_layer_matches_dense_oracle_and_trains():
     assert torch.allclose(y, ref, atol=1e-5)
     (y.square().sum() + layer.last_aux).backward()
     assert x.grad is not None and layer.wg.grad.abs().sum() > 0 and layer.w2.grad.abs().sum() > 0
+
+
+def test_stock_library_twin_of_gpt_moe_trains_on_cpu():
+    """`bench.py --impl twin --workload gpt-moe-1.3b` at toy size: the stock-ops MoE GPT runs forward / backward
+    and its routing follows the same top-1 + capacity rule as the native router."""
+    from b200flow.workloads.twin import TwinGPTMoE, _TwinMoE
+
+    torch.manual_seed(0)
+    m = TwinGPTMoE(256, 64, 4, 4, 128, 32, experts=4, moe_every=2, world=1, group=None, dtype=torch.float32,
+                   device=torch.device("cpu"))
+    t = torch.randint(0, 256, (2, 33))
+    opt = torch.optim.AdamW(m.parameters(), lr=3e-3)
+    losses = []
+    for _ in range(8):
+        loss = m(t[:, :-1], t[:, 1:])
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+        losses.append(float(loss))
+    assert losses[-1] < losses[0] and len(m.expert_parameters()) == 2 * 4
+    moe = _TwinMoE(32, 64, 4, 1, None, torch.float32, torch.device("cpu"))
+    x = torch.randn(40, 32)
+    y = moe(x)
+    r = route_top1(moe.gate(x).float(), (max(4, 10) + 7) // 8 * 8)
+    dropped = r["expert"] < 0
+    assert torch.equal(y[dropped], torch.zeros_like(y[dropped])) and (y[~dropped].abs().sum(1) > 0).all()
