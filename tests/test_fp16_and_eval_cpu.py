@@ -221,3 +221,15 @@ def test_comms_logger_in_the_engine_reports_tensor_parallel_collectives():
         assert p.exitcode == 0
     assert "comm op" in got[0] and "all_reduce" in got[0] and "all_gather" in got[0]   # SP all-gathers, norm all-reduce
     assert got[1].count("comm op") == 0                                                    # rank 0 prints
+
+
+def test_activation_recompute_changes_memory_not_math():
+    """`--checkpoint-activations` / `"activation_checkpointing": {"enabled": true}`: identical updates."""
+    cfg, plain = _engine({})
+    _, ckpt = _engine({"activation_checkpointing": {"enabled": True}})
+    assert ckpt.model.recompute and not plain.model.recompute
+    ia, ib = itertools.cycle(_batches(cfg)), itertools.cycle(_batches(cfg))
+    for _ in range(3):
+        la, lb = float(plain.train_batch(ia)), float(ckpt.train_batch(ib))
+        assert abs(la - lb) < 1e-5, (la, lb)
+    assert torch.allclose(plain.flat.params, ckpt.flat.params, atol=1e-6)
