@@ -9,7 +9,10 @@ underneath: the model is flattened and wrapped in the bucketed K1 DDP, bf16 para
 fp32 master weights in the fused AdamW, checkpoints in Accelerate's directory layout.
 
 `mixed_precision="fp16"` (what the reference passes) is honoured as reduced-precision
-compute; on B200 that is bf16 (no loss scaling needed), on CPU it is fp32.
+compute — bf16 storage on B200, fp32 on CPU — with Accelerate's fp16 behaviour around it: a
+`torch.amp.GradScaler`-style dynamic loss scale (65536, x2 after 2000 clean steps, x0.5 on overflow),
+optimizer and scheduler steps skipped on overflow (`optimizer_step_was_skipped`), `scaler.pt` in
+`save_state`.
 """
 from __future__ import annotations
 
@@ -74,20 +77,87 @@ class _ShardedLoader:
         self.skip = 0
 
 
+class GradScaler:
+    """Dynamic loss scale with `torch.amp.GradScaler`'s constants and state-dict keys."""
+
+    def __init__(self, init_scale: float = 65536.0, growth_factor: float = 2.0, backoff_factor: float = 0.5,
+                 growth_interval: int = 2000):
+        self.scale = float(init_scale)
+        self.growth_factor, self.backoff_factor, self.growth_interval = growth_factor, backoff_factor, growth_interval
+        self._growth_tracker = 0
+
+    def update(self, found_inf: bool) -> None:
+        if found_inf:
+            self.scale *= self.backoff_factor
+            self._growth_tracker = 0
+            return
+        self._growth_tracker += 1
+        if self._growth_tracker == self.growth_interval:
+            self.scale *= self.growth_factor
+            self._growth_tracker = 0
+
+    def state_dict(self) -> dict:
+        return {"scale": self.scale, "growth_factor": self.growth_factor, "backoff_factor": self.backoff_factor,
+                "growth_interval": self.growth_interval, "_growth_tracker": self._growth_tracker}
+
+    def load_state_dict(self, sd: dict) -> None:
+        self.scale = float(sd["scale"])
+        self.growth_factor, self.backoff_factor = float(sd["growth_factor"]), float(sd["backoff_factor"])
+        self.growth_interval, self._growth_tracker = int(sd["growth_interval"]), int(sd["_growth_tracker"])
+
+
 class _Optimizer:
     """AcceleratedOptimizer: defers to the wrapped optimizer, finishing the DDP reduction first
-    and honouring gradient accumulation."""
+    and honouring gradient accumulation; under fp16 it unscales, checks for inf / nan and skips."""
 
     def __init__(self, opt, acc):
         self.optimizer, self.acc = opt, acc
+        self.step_was_skipped = False
 
     @property
     def param_groups(self):
         return self.optimizer.param_groups
 
+    def _grads(self):
+        seen, out = set(), []
+        for g in self.optimizer.param_groups:
+            for p in g["params"]:
+                owner = getattr(p, "_flat_owner", None)
+                if owner is not None:
+                    if id(owner) not in seen:
+                        seen.add(id(owner))
+                        out.append(owner.grads)
+                    continue
+                t = getattr(p, "main_grad", None)
+                t = t if t is not None else p.grad
+                if t is not None:
+                    out.append(t)
+        return out
+
     def step(self):
-        if self.acc.sync_gradients:
+        if not self.acc.sync_gradients:
+            return
+        scaler = self.acc.scaler
+        if scaler is None:
             self.optimizer.step()
+            return
+        grads = self._grads()
+        found_inf = not all(bool(torch.isfinite(g).all()) for g in grads)    # reduced gradients: same on every rank
+        self.step_was_skipped = found_inf
+        if not found_inf:
+            inv = 1.0 if self.acc._unscaled else 1.0 / scaler.scale
+            if hasattr(self.optimizer, "grad_scale"):      # fused AdamW: the unscale rides on its gradient scale
+                prev = self.optimizer.grad_scale
+                self.optimizer.grad_scale = torch.full((1,), inv, dtype=torch.float32, device=grads[0].device) \
+                    if prev is None else prev * inv
+                self.optimizer.step()
+                self.optimizer.grad_scale = prev
+            else:
+                for g in grads:
+                    g.mul_(inv)
+                self.optimizer.step()
+        self.acc._unscaled = False
+        scaler.update(found_inf)
 
     def zero_grad(self, set_to_none=True):
         if self.acc.sync_gradients:
@@ -105,7 +175,7 @@ class _Scheduler:
         self.scheduler, self.acc = sch, acc
 
     def step(self):
-        if self.acc.sync_gradients:
+        if self.acc.sync_gradients and not self.acc.optimizer_step_was_skipped:
             self.scheduler.step()
 
     def get_last_lr(self):
@@ -137,6 +207,8 @@ class Accelerator:
         self.local_process_index = int(os.environ.get("LOCAL_RANK", 0))
         self.device = torch.device("cuda", torch.cuda.current_device()) if use_cuda else torch.device("cpu")
         self.param_dtype = torch.bfloat16 if use_cuda else torch.float32
+        self.scaler = GradScaler() if self.mixed_precision == "fp16" else None
+        self._unscaled = False
         self.trackers: list[Tracker] = []
         self._models, self._optimizers, self._schedulers, self._loaders = [], [], [], []
         self._custom = []
@@ -220,16 +292,32 @@ class Accelerator:
                 st.enter_context(c)
             yield
 
+    @property
+    def optimizer_step_was_skipped(self) -> bool:
+        return any(o.step_was_skipped for o in self._optimizers)
+
     def backward(self, loss, **kw):
         if self.gradient_accumulation_steps > 1:
             loss = loss / self.gradient_accumulation_steps
+        if self.scaler is not None:
+            loss = loss * self.scaler.scale
         loss.backward(**kw)
         if self.sync_gradients:
             for m in self._models:
                 m.finish_reduction()
             self.step += 1
 
+    def unscale_gradients(self) -> None:
+        """Divide the (reduced) gradients by the loss scale once per step (fp16 only)."""
+        if self.scaler is None or self._unscaled:
+            return
+        for o in self._optimizers:
+            for g in o._grads():
+                g.mul_(1.0 / self.scaler.scale)
+        self._unscaled = True
+
     def clip_grad_norm_(self, parameters, max_norm: float, norm_type: float = 2.0):
+        self.unscale_gradients()
         grads = [getattr(p, "main_grad", None) if getattr(p, "main_grad", None) is not None else p.grad
                  for p in parameters]
         grads = [g for g in grads if g is not None]
@@ -286,7 +374,7 @@ class Accelerator:
         self.wait_for_everyone()
         models = [self.unwrap_model(m) for m in self._models]
         L.save_state(output_dir, models, [o.optimizer for o in self._optimizers],
-                     [s.scheduler for s in self._schedulers], [], None, self.process_index,
+                     [s.scheduler for s in self._schedulers], [], self.scaler, self.process_index,
                      self.is_main_process, self._custom, safe_serialization)
         self.wait_for_everyone()
         return output_dir
@@ -294,7 +382,7 @@ class Accelerator:
     def load_state(self, input_dir: str) -> None:
         models = [self.unwrap_model(m) for m in self._models]
         L.load_state(input_dir, models, [o.optimizer for o in self._optimizers],
-                     [s.scheduler for s in self._schedulers], None, self.process_index, self._custom)
+                     [s.scheduler for s in self._schedulers], self.scaler, self.process_index, self._custom)
 
     def skip_first_batches(self, dataloader, num_batches: int):
         dataloader.skip = num_batches

@@ -233,3 +233,49 @@ def test_activation_recompute_changes_memory_not_math():
         la, lb = float(plain.train_batch(ia)), float(ckpt.train_batch(ib))
         assert abs(la - lb) < 1e-5, (la, lb)
     assert torch.allclose(plain.flat.params, ckpt.flat.params, atol=1e-6)
+
+
+def test_accelerator_fp16_grad_scaler_skips_and_checkpoints(tmp_path):
+    """Accelerate under `--mixed_precision fp16` (what the reference's BERT example passes): dynamic loss scale,
+    inf / nan gradients skip optimizer and scheduler, `scaler.pt` is part of `save_state`."""
+    from b200flow.engines.accelerate_api import Accelerator
+    from b200flow.optim import AdamW, get_linear_schedule_with_warmup
+
+    def build(mp_mode):
+        torch.manual_seed(0)
+        acc = Accelerator(cpu=True, mixed_precision=mp_mode)
+        model = torch.nn.Sequential(torch.nn.Linear(8, 16), torch.nn.Tanh(), torch.nn.Linear(16, 1))
+        opt = AdamW(model.parameters(), lr=1e-2, weight_decay=0.0)
+        sch = get_linear_schedule_with_warmup(opt, 2, 20)
+        model, opt, sch = acc.prepare(model, opt, sch)
+        return acc, model, opt, sch
+
+    (a, ma, oa, sa), (b, mb, ob, sb) = build("no"), build("fp16")
+    assert a.scaler is None and b.scaler.scale == 65536.0
+    x, y = torch.randn(32, 8), torch.randn(32, 1)
+    for _ in range(3):
+        for acc, m, o, s in ((a, ma, oa, sa), (b, mb, ob, sb)):
+            loss = torch.nn.functional.mse_loss(m(x), y)
+            acc.backward(loss)
+            acc.clip_grad_norm_(m.parameters(), 1.0)           # unscales first under fp16
+            o.step()
+            s.step()
+            o.zero_grad()
+    wa = torch.cat([p.detach().reshape(-1) for p in ma.parameters()])
+    wb = torch.cat([p.detach().reshape(-1) for p in mb.parameters()])
+    assert torch.allclose(wa, wb, atol=1e-5) and sa.get_last_lr() == sb.get_last_lr()
+    # an overflowing step: parameters, Adam step count and the schedule stay put, the scale halves
+    before, lr = wb.clone(), sb.get_last_lr()
+    loss = torch.nn.functional.mse_loss(mb(x), y) * float("inf")
+    b.backward(loss)
+    ob.step()
+    sb.step()
+    ob.zero_grad()
+    wb2 = torch.cat([p.detach().reshape(-1) for p in mb.parameters()])
+    assert b.optimizer_step_was_skipped and torch.equal(before, wb2) and sb.get_last_lr() == lr
+    assert b.scaler.scale == 32768.0
+    out = b.save_state(str(tmp_path / "step_4"))
+    assert (tmp_path / "step_4" / "scaler.pt").exists()
+    c, mc, oc, sc = build("fp16")
+    c.load_state(out)
+    assert c.scaler.scale == 32768.0 and c.scaler.state_dict() == b.scaler.state_dict()
