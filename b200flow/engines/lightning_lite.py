@@ -87,3 +87,35 @@ class Trainer:
                     model.on_validation_epoch_end()
             for cb in self.callbacks:
                 cb.on_train_epoch_end(self, model)
+
+
+class RayDDPStrategy:
+    """`ray.train.lightning.RayDDPStrategy`: in the reference's script it tells Lightning to use the process
+    group Ray Train already created.  Here `Trainer.fit` always wraps the module in b200flow's DDP on the
+    existing process group, so the object only carries its options (`find_unused_parameters` is not needed:
+    the reducer sweeps buckets whose parameters received no gradient)."""
+
+    def __init__(self, find_unused_parameters: bool = False, **kw):
+        self.find_unused_parameters, self.options = find_unused_parameters, kw
+
+
+class RayLightningEnvironment:
+    """`ray.train.lightning.RayLightningEnvironment`: rank / world size as the worker group set them."""
+
+    def world_size(self) -> int:
+        return dist.get_world_size() if dist.is_initialized() else 1
+
+    def global_rank(self) -> int:
+        return dist.get_rank() if dist.is_initialized() else 0
+
+    def local_rank(self) -> int:
+        return int(os.environ.get("LOCAL_RANK", 0))
+
+    def node_rank(self) -> int:
+        return 0
+
+
+def prepare_trainer(trainer: Trainer) -> Trainer:
+    """`ray.train.lightning.prepare_trainer`: validates that the trainer is set up for the worker group; the
+    local trainer has nothing to patch, so it is returned as it is."""
+    return trainer

@@ -17,7 +17,8 @@ import torch
 
 from b200flow.data.synthetic import cola_like, collate_pad
 from b200flow.engines import ray_train_api as train
-from b200flow.engines.lightning_lite import LightningModule, RayTrainReportCallback, Trainer
+from b200flow.engines.lightning_lite import (LightningModule, RayDDPStrategy, RayLightningEnvironment,
+                                             RayTrainReportCallback, Trainer, prepare_trainer)
 from b200flow.engines.ray_train_api import (CheckpointConfig, ListDataset, RunConfig, ScalingConfig,
                                             TorchTrainer)
 from b200flow.models.bert import BertForSequenceClassification, bert_config
@@ -71,8 +72,10 @@ def train_func(config):
     train_dl = lambda: train_ds.iter_torch_batches(batch_size=batch_size, collate_fn=collate_pad)  # noqa: E731
     val_dl = lambda: val_ds.iter_torch_batches(batch_size=batch_size, collate_fn=collate_pad)      # noqa: E731
     model = SentimentModel(lr=lr, eps=eps)
-    trainer = Trainer(max_epochs=max_epochs, accelerator="auto", callbacks=[RayTrainReportCallback()],
+    trainer = Trainer(max_epochs=max_epochs, accelerator="auto", devices="auto", strategy=RayDDPStrategy(),
+                      plugins=[RayLightningEnvironment()], callbacks=[RayTrainReportCallback()],
                       enable_progress_bar=False)
+    trainer = prepare_trainer(trainer)
     trainer.fit(model, train_dataloaders=train_dl, val_dataloaders=val_dl)
 
 
