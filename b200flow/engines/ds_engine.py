@@ -31,7 +31,7 @@ from ..parallel import pipeline as PP
 from ..parallel.groups import ParallelState
 from ..parallel.loss_scaler import make_loss_scaler
 from ..parallel.tensor_parallel import SINGLE, TPContext, allreduce_replicated_grads
-from ..parallel.zero1 import AdamConfig, Zero1Optimizer, cosine_lr
+from ..parallel.zero1 import AdamConfig, Zero1Optimizer, megatron_lr
 from ..utils.flat import FlatParams
 
 _KNOWN = {"train_micro_batch_size_per_gpu", "gradient_accumulation_steps", "zero_optimization",
@@ -414,11 +414,12 @@ class TrainEngine:
     def _apply_lr(self):
         if self.sched:
             p = self.sched
-            self.optimizer.lr = cosine_lr(self.global_steps - self.skipped_steps + 1,
-                                          base_lr=float(p["max_lr"]),
-                                          min_lr=float(p.get("min_lr", 0.0)),
-                                          warmup_steps=int(p.get("warmup_steps", 0)),
-                                          decay_steps=int(p.get("decay_steps", 1)))
+            self.optimizer.lr = megatron_lr(self.global_steps - self.skipped_steps + 1,
+                                            style=str(p.get("decay_style", "cosine")),
+                                            base_lr=float(p["max_lr"]),
+                                            min_lr=float(p.get("min_lr", 0.0)),
+                                            warmup_steps=int(p.get("warmup_steps", 0)),
+                                            decay_steps=int(p.get("decay_steps", 1)))
 
     # ----------------------------------------------------------- checkpoints
     def save_checkpoint(self, save_dir: str, tag: str | None = None, client_state: dict | None = None):

@@ -138,3 +138,26 @@ def cosine_lr(step: int, *, base_lr: float, min_lr: float, warmup_steps: int, de
         return min_lr
     frac = (step - warmup_steps) / max(1, decay_steps - warmup_steps)
     return min_lr + 0.5 * (base_lr - min_lr) * (1.0 + math.cos(math.pi * frac))
+
+
+def megatron_lr(step: int, *, style: str = "cosine", base_lr: float, min_lr: float, warmup_steps: int,
+                decay_steps: int) -> float:
+    """Megatron's `OptimizerParamScheduler.get_lr` for `--lr-decay-style` constant / linear / cosine /
+    inverse-square-root: linear warm-up to `base_lr`, then the decay between `base_lr` and `min_lr` over
+    `decay_steps`, `min_lr` afterwards."""
+    if warmup_steps > 0 and step <= warmup_steps:
+        return base_lr * step / warmup_steps
+    if style == "constant":
+        return base_lr
+    if style == "inverse-square-root":
+        return max(min_lr, base_lr * math.sqrt(max(warmup_steps, 1)) / math.sqrt(max(step, 1)))
+    if step >= decay_steps:
+        return min_lr
+    frac = (step - warmup_steps) / max(1, decay_steps - warmup_steps)
+    if style == "linear":
+        coeff = 1.0 - frac
+    elif style == "cosine":
+        coeff = 0.5 * (1.0 + math.cos(math.pi * frac))
+    else:
+        raise ValueError(f"unknown --lr-decay-style {style!r}")
+    return min_lr + coeff * (base_lr - min_lr)

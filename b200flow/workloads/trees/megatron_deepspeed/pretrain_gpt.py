@@ -135,7 +135,7 @@ def main():
         "optimizer": {"params": {"lr": args.lr, "betas": (args.adam_beta1, args.adam_beta2),
                                  "eps": args.adam_eps, "weight_decay": args.weight_decay}},
         "scheduler": {"params": {"max_lr": args.lr, "min_lr": args.min_lr, "warmup_steps": warm,
-                                 "decay_steps": decay_iters}},
+                                 "decay_steps": decay_iters, "decay_style": args.lr_decay_style}},
         # Megatron's --sequence-parallel only changes where activations live between the TP linears; the
         # numerics are the same.  The engine therefore shards the sequence whenever TP > 1 (that is the form
         # the fused all-gather->GEMM / GEMM->reduce-scatter kernels implement) unless B2F_AUTO_SP=0 asks for

@@ -279,3 +279,17 @@ def test_accelerator_fp16_grad_scaler_skips_and_checkpoints(tmp_path):
     c, mc, oc, sc = build("fp16")
     c.load_state(out)
     assert c.scaler.scale == 32768.0 and c.scaler.state_dict() == b.scaler.state_dict()
+
+
+def test_megatron_lr_decay_styles():
+    from b200flow.parallel.zero1 import cosine_lr, megatron_lr
+
+    kw = dict(base_lr=1e-3, min_lr=1e-5, warmup_steps=10, decay_steps=110)
+    for step in (1, 5, 10, 11, 60, 109, 110, 500):
+        assert abs(megatron_lr(step, style="cosine", **kw) - cosine_lr(step, **kw)) < 1e-15
+    assert megatron_lr(5, style="linear", **kw) == 5e-4                       # warm-up is shared
+    assert abs(megatron_lr(60, style="linear", **kw) - (1e-5 + 0.5 * (1e-3 - 1e-5))) < 1e-12
+    assert megatron_lr(60, style="constant", **kw) == 1e-3 and megatron_lr(10 ** 6, style="constant", **kw) == 1e-3
+    assert abs(megatron_lr(40, style="inverse-square-root", **kw) - 1e-3 * (10 / 40) ** 0.5) < 1e-12
+    assert megatron_lr(10 ** 9, style="inverse-square-root", **kw) == 1e-5
+    assert megatron_lr(200, style="linear", **kw) == 1e-5
