@@ -130,3 +130,56 @@ def synthetic_corpus(prefix: str | Path, vocab_size: int, num_docs: int = 2000, 
         b.end_document()
     b.finalize()
     return str(prefix)
+
+
+class BlendableDataset(torch.utils.data.Dataset):
+    """Megatron's `BlendableDataset`: samples drawn from several datasets in proportion to their weights
+    (`--data-path 0.3 corpusA 0.7 corpusB`).  The assignment of every global sample to (dataset, sample within
+    it) is built once by `b2f_build_blending_indices` (csrc/host/data_helpers.cpp): always the dataset whose
+    realised share lags its target share the most, so any prefix of the stream is mixed in proportion."""
+
+    def __init__(self, datasets: list, weights: list[float], size: int):
+        assert len(datasets) == len(weights) and 0 < len(datasets) < 255
+        w = np.asarray(weights, dtype=np.float64)
+        assert (w > 0).all(), "blend weights must be positive"
+        self.datasets, self.weights, self.size = datasets, w / w.sum(), int(size)
+        self.dataset_index = np.zeros(self.size, dtype=np.uint8)
+        self.dataset_sample_index = np.zeros(self.size, dtype=np.int64)
+        _host().b2f_build_blending_indices(
+            self.dataset_index.ctypes.data_as(ctypes.c_void_p), self.dataset_sample_index.ctypes.data_as(ctypes.c_void_p),
+            self.weights.ctypes.data_as(ctypes.c_void_p), ctypes.c_int(len(datasets)), ctypes.c_longlong(self.size))
+
+    def __len__(self) -> int:
+        return self.size
+
+    def __getitem__(self, i: int) -> dict:
+        d = int(self.dataset_index[i % self.size])
+        return self.datasets[d][int(self.dataset_sample_index[i % self.size])]
+
+
+def parse_data_path(data_path: list[str]) -> tuple[list[float], list[str]]:
+    """`--data-path` is either one prefix or `weight prefix weight prefix ...`."""
+    if len(data_path) == 1:
+        return [1.0], [data_path[0]]
+    assert len(data_path) % 2 == 0, "--data-path takes one prefix or weight / prefix pairs"
+    return [float(x) for x in data_path[0::2]], list(data_path[1::2])
+
+
+def build_train_valid_test_blended(data_path: list[str], split: str, seq_length: int, samples: tuple[int, int, int],
+                                   seed: int, cache_dir=None):
+    """Train / valid / test datasets over one corpus or a weighted blend of corpora (Megatron
+    `build_train_valid_test_datasets`): every corpus is split by `--split` on its own and contributes
+    ceil(weight x samples x 1.005) samples to each blend, like upstream's safety margin."""
+    weights, prefixes = parse_data_path(data_path)
+    if len(prefixes) == 1:
+        return build_train_valid_test(prefixes[0], split, seq_length, samples, seed, cache_dir)
+    w = np.asarray(weights, dtype=np.float64)
+    w = w / w.sum()
+    per = [build_train_valid_test(p, split, seq_length,
+                                  tuple(int(np.ceil(n * wi * 1.005)) for n in samples), seed, cache_dir)
+           for p, wi in zip(prefixes, w)]
+    out = []
+    for k, n in enumerate(samples):
+        parts = [(ds[k], wi) for ds, wi in zip(per, w) if ds[k] is not None]
+        out.append(BlendableDataset([p for p, _ in parts], [wi for _, wi in parts], n) if parts and n > 0 else None)
+    return out

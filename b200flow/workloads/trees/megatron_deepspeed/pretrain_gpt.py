@@ -28,7 +28,7 @@ import time
 import torch
 import torch.distributed as dist
 
-from b200flow.data.gpt_dataset import build_train_valid_test, synthetic_corpus
+from b200flow.data.gpt_dataset import build_train_valid_test_blended, synthetic_corpus
 from b200flow.data.indexed_dataset import MMapIndexedDataset
 from b200flow.engines.ds_engine import initialize
 from b200flow.models.gpt import GPTConfig
@@ -162,9 +162,15 @@ def main():
             dist.barrier()
     gbs = micro * gas * dp
     n_eval = (train_iters // max(1, args.eval_interval) + 1) * args.eval_iters * gbs
-    train_ds, valid_ds, _ = build_train_valid_test(prefix, args.split, args.seq_length,
-                                                   (train_iters * gbs, max(n_eval, gbs), 0), args.seed,
-                                                   args.data_cache_path)
+    data_path = [prefix]
+    if args.data_path and len(args.data_path) > 1:      # weight / prefix pairs: a blend of corpora
+        from b200flow.data.gpt_dataset import parse_data_path
+
+        if all(MMapIndexedDataset.exists(pfx) for pfx in parse_data_path(args.data_path)[1]):
+            data_path = list(args.data_path)
+    train_ds, valid_ds, _ = build_train_valid_test_blended(data_path, args.split, args.seq_length,
+                                                           (train_iters * gbs, max(n_eval, gbs), 0), args.seed,
+                                                           args.data_cache_path)
     dp_rank = ps.dp_rank if ps else 0
 
     def batches(dataset, start_step):

@@ -347,3 +347,28 @@ def test_prefetch_loader_keeps_order_and_reports_worker_errors():
     assert [g["i"] for g in PrefetchLoader(_SlowSquares(), order, workers=0)] == order
     with pytest.raises(RuntimeError, match="bad sample 13"):
         list(PrefetchLoader(_SlowSquares(), [1, 2, 13, 4], workers=2, capacity=1 << 20))
+
+
+def test_blended_corpora_follow_their_weights(tmp_path):
+    """`--data-path 0.25 A 0.75 B`: every prefix of the sample stream is mixed in proportion, each sample comes
+    from the corpus the index names (corpus A only holds token 7, corpus B only token 9)."""
+    from b200flow.data.gpt_dataset import BlendableDataset, build_train_valid_test_blended, parse_data_path
+
+    for name, tok in (("a", 7), ("b", 9)):
+        b = MMapIndexedDatasetBuilder(str(tmp_path / name), dtype=np.int32)
+        for d in range(40):
+            b.add_item(np.full(50 + d, tok, dtype=np.int32))
+            b.end_document()
+        b.finalize()
+    assert parse_data_path(["0.25", "x", "0.75", "y"]) == ([0.25, 0.75], ["x", "y"])
+    args = ["0.25", str(tmp_path / "a"), "0.75", str(tmp_path / "b")]
+    train, valid, test = build_train_valid_test_blended(args, "90,10,0", 16, (200, 20, 0), seed=3,
+                                                        cache_dir=tmp_path / "cache")
+    assert isinstance(train, BlendableDataset) and len(train) == 200 and len(valid) == 20 and test is None
+    toks = [int(train[i]["text"][0]) for i in range(200)]
+    assert all((train[i]["text"] == toks[i]).all() and train[i]["text"].numel() == 17 for i in range(0, 200, 7))
+    for n in (20, 80, 200):                          # proportion holds on every prefix, not only at the end
+        share_a = sum(t == 7 for t in toks[:n]) / n
+        assert abs(share_a - 0.25) <= 1.0 / n + 1e-9, (n, share_a)
+    single = build_train_valid_test_blended([str(tmp_path / "a")], "90,10,0", 16, (50, 5, 0), seed=3)
+    assert not isinstance(single[0], BlendableDataset) and len(single[0]) >= 50
