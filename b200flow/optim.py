@@ -71,6 +71,17 @@ class AdamW(torch.optim.Optimizer):
                                    weight_decay=group["weight_decay"], step=self._step)
                     p.data.copy_(st["master"].to(p.dtype))
 
+    def state_dict(self):
+        sd = super().state_dict()
+        sd["b2f_step"] = self._step            # bias correction continues where it stopped
+        return sd
+
+    def load_state_dict(self, sd):
+        sd = dict(sd)
+        self._step = int(sd.pop("b2f_step", self._step))
+        super().load_state_dict(sd)
+        self._tables = {}                      # the device tables point at the tensors just replaced
+
     def zero_grad(self, set_to_none: bool = True):
         owners = {}
         for group in self.param_groups:

@@ -293,3 +293,34 @@ def test_megatron_lr_decay_styles():
     assert abs(megatron_lr(40, style="inverse-square-root", **kw) - 1e-3 * (10 / 40) ** 0.5) < 1e-12
     assert megatron_lr(10 ** 9, style="inverse-square-root", **kw) == 1e-5
     assert megatron_lr(200, style="linear", **kw) == 1e-5
+
+
+def test_fused_adamw_front_end_resumes_with_its_step_count():
+    """`optimizer.bin` of an Accelerate checkpoint: the bias-correction step travels with the state, so a
+    reloaded optimizer continues exactly (and its cached device tables are dropped)."""
+    from b200flow.optim import AdamW
+
+    def make():
+        torch.manual_seed(0)
+        w = torch.nn.Parameter(torch.randn(7, 5))
+        return w, AdamW([w], lr=1e-2, weight_decay=0.01)
+
+    def step(w, opt, k):
+        w.grad = torch.full_like(w, 0.1 * (k + 1)) * w.detach().sign()
+        opt.step()
+
+    wa, oa = make()
+    for k in range(3):
+        step(wa, oa, k)
+    import copy
+
+    sd = copy.deepcopy(oa.state_dict())     # as if read back from optimizer.bin (state tensors are shared otherwise)
+    assert sd["b2f_step"] == 3
+    wb, ob = make()
+    wb.data.copy_(wa.data)
+    ob.load_state_dict(sd)
+    assert ob._step == 3 and ob._tables == {}
+    for k in range(3, 6):
+        step(wa, oa, k)
+        step(wb, ob, k)
+    assert torch.allclose(wa, wb, atol=1e-7)
