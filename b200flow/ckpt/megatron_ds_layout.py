@@ -156,6 +156,51 @@ def save_checkpoint(engine, save_dir: str, tag: str | None = None, client_state:
     return str(d)
 
 
+def _optim_name(engine, dp: int, dp_world: int, tp: int, bf16: bool) -> str:
+    if engine.pp_world > 1:
+        return ("bf16_" if bf16 else "") + f"zero_pp_rank_{dp + dp_world * engine.stage}_mp_rank_{tp:02d}_optim_states.pt"
+    return optim_file(dp, tp, bf16)
+
+
+def _load_optimizer_state(d: Path, name: str, engine, tp: int, bf16: bool) -> dict:
+    """This rank's ZeRO-1 optimizer state.  When the checkpoint was written by a different data-parallel size
+    (a job restarted on fewer or more GPUs — DeepSpeed's elastic checkpoint for ZeRO-1), the saved partitions of
+    this (stage, TP rank) are joined into the full flat state and cut again for the current layout; only the
+    zero padding at the end of the flat buffer can differ in length."""
+    opt = engine.optimizer
+    own = d / name
+    if own.exists():
+        osd = torch.load(own, map_location="cpu", weights_only=False)["optimizer_state_dict"]
+        if int(osd.get("dp_world", engine.dp_world)) == engine.dp_world and tuple(osd["partition"]) == (opt.lo, opt.hi):
+            return osd
+    first = d / _optim_name(engine, 0, 1, tp, bf16)      # dp index 0 has the same name for every saved dp size
+    if engine.pp_world > 1:
+        # under PP the file index mixes stage and dp: find the saved dp size from any file of this stage
+        first = None
+        for cand in range(1, 65):
+            f = d / _optim_name(engine, 0, cand, tp, bf16)
+            if f.exists():
+                o = torch.load(f, map_location="cpu", weights_only=False)["optimizer_state_dict"]
+                if int(o.get("stage", engine.stage)) == engine.stage and int(o.get("dp_world", cand)) == cand:
+                    first = f
+                    break
+        assert first is not None, f"no optimizer state for stage {engine.stage}, TP rank {tp} in {d}"
+    head = torch.load(first, map_location="cpu", weights_only=False)["optimizer_state_dict"]
+    saved_dp = int(head["dp_world"])
+    parts = [head] + [torch.load(d / _optim_name(engine, i, saved_dp, tp, bf16), map_location="cpu",
+                                 weights_only=False)["optimizer_state_dict"] for i in range(1, saved_dp)]
+    parts.sort(key=lambda o: o["partition"][0])
+    out = dict(head)
+    for key in ("fp32_flat", "exp_avg", "exp_avg_sq"):
+        full = torch.cat([o[key].reshape(-1) for o in parts])
+        now = torch.zeros(engine.flat.numel, dtype=full.dtype)
+        n = min(full.numel(), now.numel())
+        now[:n] = full[:n]
+        out[key] = now[opt.lo:opt.hi].clone()
+    out["partition"], out["dp_world"], out["dp_rank"] = (opt.lo, opt.hi), engine.dp_world, opt.dp_rank
+    return out
+
+
 def load_checkpoint(engine, load_dir: str, tag: str | None = None):
     wait_for_pending_saves()
     root = Path(load_dir)
@@ -198,7 +243,7 @@ def load_checkpoint(engine, load_dir: str, tag: str | None = None):
                 sd[k] = torch.stack(rows)
         model.load_state_dict(sd, strict=False)
         name = optim_file(dp, tp, bf16)
-    osd = torch.load(d / name, map_location="cpu", weights_only=False)["optimizer_state_dict"]
+    osd = _load_optimizer_state(d, name, engine, tp, bf16)
     dev = engine.flat.params.device
     osd = {k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in osd.items()}
     engine.optimizer.load_state_dict(osd)

@@ -44,3 +44,89 @@ def test_save_load_continues_identically(tmp_path, preset, expert_files):
         next(it2)                                    # the data position is the caller's business
     resumed = [float(fresh.train_batch(it2)) for _ in range(2)]
     assert resumed == pytest.approx(after_save, rel=1e-5, abs=1e-6)
+
+
+def _dp2_worker(rank, port, save_dir, mode, q, world=2, pp=1):
+    import os
+
+    import torch.distributed as dist
+
+    from b200flow.parallel.groups import ParallelState
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.set_num_threads(1)
+    ps = ParallelState.initialize(tp=1, pp=pp)
+    cfg = config_from_preset("gpt2-tiny")
+    eng = initialize(cfg, {"train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": 1,
+                           "optimizer": {"params": {"lr": 1e-3}}}, ps, device=torch.device("cpu"), seed=11)
+    if mode == "save":
+        g = torch.Generator().manual_seed(5 + ps.dp_rank)
+        toks = [torch.randint(0, cfg.vocab_size, (2, 33), generator=g) for _ in range(3)]
+        it = itertools.cycle([(t[:, :-1].contiguous(), t[:, 1:].contiguous()) for t in toks])
+        for _ in range(3):
+            eng.train_batch(it)
+        eng.save_checkpoint(save_dir)
+        o = eng.optimizer
+        q.put((rank, o.lo, o.hi, eng.flat.params.clone(), o.exp_avg.clone(), o.exp_avg_sq.clone(), o.step_count,
+               eng.stage, ps.dp_rank))
+    else:
+        eng.load_checkpoint(save_dir)
+        o = eng.optimizer
+        q.put((rank, o.lo, o.hi, eng.flat.params.clone(), o.master.clone(), o.exp_avg.clone(), o.step_count,
+               eng.stage, ps.dp_rank))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def _spawn(mode, save_dir, port, world=2, pp=1):
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_dp2_worker, args=(r, port, save_dir, mode, q, world, pp)) for r in range(world)]
+    for p in procs:
+        p.start()
+    out = sorted((q.get(timeout=300) for _ in procs), key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    return out
+
+
+def test_zero1_state_is_resharded_when_the_data_parallel_size_changes(tmp_path):
+    """A job saved on 2 data-parallel ranks resumes on 1, and the other way round (elastic restart on a
+    different number of GPUs): the partitions are joined and cut again."""
+    two = _spawn("save", str(tmp_path / "dp2"), 29681)
+    names = {p.name for p in (tmp_path / "dp2" / "global_step3").iterdir()}
+    assert {n for n in names if "optim_states" in n} == {"zero_pp_rank_0_mp_rank_00_optim_states.pt",
+                                                         "zero_pp_rank_1_mp_rank_00_optim_states.pt"}
+    _, one, _ = _engine("gpt2-tiny", seed=99)
+    one.load_checkpoint(str(tmp_path / "dp2"))
+    o = one.optimizer
+    n = min(one.flat.numel, two[0][3].numel())
+    assert torch.equal(one.flat.params[:n], two[0][3][:n]) and torch.equal(o.master[:n], two[0][3][:n].float())
+    joined = torch.cat([two[0][4], two[1][4]])
+    assert torch.equal(o.exp_avg[:n], joined[:n]) and o.exp_avg.abs().sum() > 0 and o.step_count == 3
+    assert one.global_steps == 3
+    # 1 -> 2: save from the single-process engine, load on two ranks
+    one.save_checkpoint(str(tmp_path / "dp1"))
+    back = _spawn("load", str(tmp_path / "dp1"), 29682)
+    for rank, lo, hi, params, master, exp_avg, steps, _stage, _dp in back:
+        m = min(n, hi)
+        assert torch.equal(master[: m - lo], one.flat.params[lo:m].float())
+        assert torch.equal(exp_avg[: m - lo], o.exp_avg[lo:m]) and steps == 3
+        assert torch.equal(params[:n], one.flat.params[:n])
+
+
+def test_zero1_resharding_under_pipeline_parallelism(tmp_path):
+    """PP2 x DP2 (4 ranks) -> PP2 x DP1 (2 ranks): each stage joins the two partitions of its own layers."""
+    saved = _spawn("save", str(tmp_path / "pp2dp2"), 29683, world=4, pp=2)
+    loaded = _spawn("load", str(tmp_path / "pp2dp2"), 29684, world=2, pp=2)
+    for rank, lo, hi, params, master, exp_avg, steps, stage, _dp in loaded:
+        mine = sorted((t for t in saved if t[7] == stage), key=lambda t: t[1])        # the stage's two partitions
+        assert len(mine) == 2 and steps == 3
+        joined = torch.cat([mine[0][4], mine[1][4]])
+        n = min(joined.numel(), exp_avg.numel())
+        assert torch.equal(exp_avg[:n], joined[:n]) and exp_avg.abs().sum() > 0
+        assert torch.equal(params[:n], mine[0][3][:n]) and torch.equal(master[:n], params[:n].float())
