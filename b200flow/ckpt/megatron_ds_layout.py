@@ -201,7 +201,10 @@ def _load_optimizer_state(d: Path, name: str, engine, tp: int, bf16: bool) -> di
     return out
 
 
-def load_checkpoint(engine, load_dir: str, tag: str | None = None):
+def load_checkpoint(engine, load_dir: str, tag: str | None = None, load_optimizer: bool = True,
+                    load_rng: bool = True, finetune: bool = False):
+    """`load_optimizer=False` / `load_rng=False` / `finetune=True` are Megatron's `--no-load-optim`,
+    `--no-load-rng` and `--finetune` (weights only, iteration back to 0)."""
     wait_for_pending_saves()
     root = Path(load_dir)
     if tag is None:
@@ -243,6 +246,14 @@ def load_checkpoint(engine, load_dir: str, tag: str | None = None):
                 sd[k] = torch.stack(rows)
         model.load_state_dict(sd, strict=False)
         name = optim_file(dp, tp, bf16)
+    if not load_optimizer or finetune:      # weights only: master copies follow the loaded weights, moments stay zero
+        for o in (engine.optimizer, getattr(engine, "expert_optimizer", None)):
+            if o is not None:
+                o.master.copy_(o.flat.params[o.lo:o.hi].float())
+        engine.global_steps = 0 if finetune else int(client.get("global_steps", 0))
+        if load_rng and not finetune and "rng_state" in client:
+            torch.set_rng_state(client["rng_state"])
+        return str(d), client
     osd = _load_optimizer_state(d, name, engine, tp, bf16)
     dev = engine.flat.params.device
     osd = {k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in osd.items()}
@@ -256,6 +267,6 @@ def load_checkpoint(engine, load_dir: str, tag: str | None = None):
         esd = torch.load(ef, map_location="cpu", weights_only=False)["optimizer_state_dict"]
         eopt.load_state_dict({k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in esd.items()})
     engine.global_steps = int(client.get("global_steps", osd.get("step", 0)))
-    if "rng_state" in client:
+    if load_rng and "rng_state" in client:
         torch.set_rng_state(client["rng_state"])
     return str(d), client

@@ -427,10 +427,11 @@ class TrainEngine:
 
         return save_checkpoint(self, save_dir, tag, client_state or {})
 
-    def load_checkpoint(self, load_dir: str, tag: str | None = None):
+    def load_checkpoint(self, load_dir: str, tag: str | None = None, load_optimizer_states: bool = True,
+                        load_rng: bool = True, finetune: bool = False):
         from ..ckpt.megatron_ds_layout import load_checkpoint
 
-        return load_checkpoint(self, load_dir, tag)
+        return load_checkpoint(self, load_dir, tag, load_optimizer_states, load_rng, finetune)
 
     def grad_norm(self) -> float:
         g = self.optimizer.last_grad_norm

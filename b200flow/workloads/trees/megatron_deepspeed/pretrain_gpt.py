@@ -69,6 +69,7 @@ def parse_args():
     a("--eval-interval", type=int, default=1000); a("--eval-iters", type=int, default=10)
     a("--distributed-backend", default="nccl"); a("--save", default=None); a("--load", default=None)
     a("--tensorboard-dir", default=None); a("--seed", type=int, default=1234)
+    a("--no-load-optim", action="store_true"); a("--no-load-rng", action="store_true"); a("--finetune", action="store_true")
     a("--deepspeed", action="store_true"); a("--deepspeed_config", default=None)
     a("--zero-stage", type=int, default=None); a("--no-pipeline-parallel", action="store_true")
     a("--local_rank", "--local-rank", type=int, default=None)
@@ -187,7 +188,8 @@ def main():
     if not args.load and args.save and os.environ.get("B2F_AUTO_RESUME") == "1":
         args.load = args.save          # launcher --auto-resume: continue from what this job saved before
     if args.load and os.path.exists(os.path.join(args.load, "latest")):
-        path, client = engine.load_checkpoint(args.load)
+        path, client = engine.load_checkpoint(args.load, load_optimizer_states=not args.no_load_optim,
+                                              load_rng=not args.no_load_rng, finetune=args.finetune)
         start = engine.global_steps
         if rank == 0:
             print(f" successfully loaded checkpoint from {path} at iteration {start}", flush=True)

@@ -130,3 +130,20 @@ def test_zero1_resharding_under_pipeline_parallelism(tmp_path):
         n = min(joined.numel(), exp_avg.numel())
         assert torch.equal(exp_avg[:n], joined[:n]) and exp_avg.abs().sum() > 0
         assert torch.equal(params[:n], mine[0][3][:n]) and torch.equal(master[:n], params[:n].float())
+
+
+def test_finetune_and_no_load_optim_take_weights_only(tmp_path):
+    cfg, eng, batches = _engine("gpt2-tiny")
+    it = itertools.cycle(batches)
+    for _ in range(2):
+        eng.train_batch(it)
+    eng.save_checkpoint(str(tmp_path))
+    _, a, _ = _engine("gpt2-tiny", seed=99)
+    a.load_checkpoint(str(tmp_path), load_optimizer_states=False)
+    assert torch.equal(a.flat.params, eng.flat.params) and a.global_steps == 2
+    assert float(a.optimizer.exp_avg.abs().sum()) == 0.0 and a.optimizer.step_count == 0
+    assert torch.equal(a.optimizer.master, a.flat.params[a.optimizer.lo:a.optimizer.hi].float())
+    _, b, _ = _engine("gpt2-tiny", seed=98)
+    b.load_checkpoint(str(tmp_path), finetune=True)
+    assert torch.equal(b.flat.params, eng.flat.params) and b.global_steps == 0
+    assert float(b.train_batch(itertools.cycle(batches))) > 0
