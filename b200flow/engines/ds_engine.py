@@ -115,6 +115,12 @@ class TrainEngine:
             for n, p in self.model.named_parameters():
                 if getattr(p, "is_expert", False) and p.dim() > 2:
                     p.data.normal_(0, model_config.init_std, generator=g)
+        if tp_world > 1:
+            # tensors every TP rank holds whole (embedding tables, norms, row-parallel biases) must start equal:
+            # the per-rank seed above only suits the sharded weights
+            for n, p in self.model.named_parameters():
+                if n.startswith("embed.") or getattr(p, "tp_replicated", False):
+                    dist.broadcast(p.data, src=ps.tp_ranks[0], group=ps.tp_group)
         self.model.recompute = bool(config.get("activation_checkpointing", {}).get("enabled", False))
         self.dp_comm = None
         allocator = None
