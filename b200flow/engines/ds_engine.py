@@ -293,6 +293,10 @@ class TrainEngine:
         if self.flat_expert is not None:
             self.flat_expert.collect_autograd_grads()
         allreduce_replicated_grads(self.flat, self.tp)
+        if self.tp_world > 1:
+            for _, p in self.flat.named_parameters():
+                if getattr(p, "tp_sum_grad", False):
+                    dist.all_reduce(p.main_grad, group=self.ps.tp_group)
         self._reduce_tied_grads()
         div, scale = float(self.gas * self.dp_world), 1.0
         overflow = False

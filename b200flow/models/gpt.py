@@ -244,10 +244,24 @@ class TransformerLayer(nn.Module):
         return h
 
 
+class _ScaleGrad(torch.autograd.Function):
+    """Identity forward; the gradient is multiplied by a constant."""
+
+    @staticmethod
+    def forward(ctx, x, scale):
+        ctx.scale = scale
+        return x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, dy):
+        return dy * ctx.scale, None
+
+
 class Embedding(nn.Module):
     def __init__(self, cfg: GPTConfig, tp, dtype=torch.bfloat16, device=None):
         super().__init__()
         self.cfg, self.tp = cfg, tp
+        self.grad_scale = 1.0      # see GPTModel: tied table under tensor parallelism
         kw = dict(dtype=dtype, device=device)
         self.wte = nn.Parameter(torch.empty(cfg.vocab_size, cfg.hidden, **kw).normal_(0, cfg.init_std))
         if cfg.learned_pos:
@@ -259,6 +273,8 @@ class Embedding(nn.Module):
         """tokens: [b, s] int64 -> [s*b, hidden] (sequence-major; SP shard taken by tp.scatter)."""
         b, s = tokens.shape
         x = torch.nn.functional.embedding(tokens.t().contiguous(), self.wte)  # [s, b, h]
+        if self.grad_scale != 1.0:
+            x = _ScaleGrad.apply(x, self.grad_scale)
         if self.wpe is not None:
             x = x + self.wpe[:s].unsqueeze(1)
         return self.tp.scatter_sequence(x.view(s * b, self.cfg.hidden))
@@ -276,8 +292,13 @@ class LMHead(nn.Module):
             self.lnf_b.tp_replicated = True
         else:
             self.lnf_b = None
+        self.tied_slice = None       # (lo, hi): this TP rank's vocabulary rows of a tied, replicated table
         if tied_weight is not None:
             self.weight = tied_weight
+            if tp.world > 1:
+                assert cfg.vocab_size % tp.world == 0
+                n = cfg.vocab_size // tp.world
+                self.tied_slice = (tp.rank * n, (tp.rank + 1) * n)
         else:
             assert cfg.vocab_size % tp.world == 0
             self.weight = nn.Parameter(
@@ -288,7 +309,14 @@ class LMHead(nn.Module):
         cfg = self.cfg
         y = N.norm(h, self.lnf_w, self.lnf_b, eps=cfg.eps, rms=cfg.norm == "rms")
         tgt = labels.t().contiguous().view(-1)  # sequence-major, matches the activations
-        return self.tp.lm_head_loss(y, self.weight, tgt)
+        w = self.weight
+        if self.tied_slice is not None:      # vocab-parallel head over this rank's rows of the shared table
+            lo, hi = self.tied_slice
+            w = self.weight[lo:hi]
+            mg = getattr(self.weight, "main_grad", None)
+            if mg is not None:
+                w.main_grad = mg[lo:hi]      # the wgrad GEMM accumulates straight into those rows
+        return self.tp.lm_head_loss(y, w, tgt)
 
 
 class GPTModel(nn.Module):
@@ -310,6 +338,12 @@ class GPTModel(nn.Module):
         if post:
             tied = self.embed.wte if (cfg.tie_embeddings and pre) else None
             self.head = LMHead(cfg, self.tp, tied, dtype, device)
+            if tied is not None and self.tp.world > 1:
+                # One table, two uses, TP ranks: the lookup's gradient is complete (and equal) on every rank, the
+                # head's only covers the rank's own vocabulary rows.  Scaling the lookup's gradient by 1/TP makes
+                # the plain sum over the TP group (engine: `tp_sum_grad`) equal lookup + head gradient.
+                self.embed.grad_scale = 1.0 / self.tp.world
+                self.embed.wte.tp_sum_grad = True
         else:
             self.head = None
         self.recompute = False

@@ -100,3 +100,62 @@ def test_resharding_the_per_layer_files_of_a_pipeline_checkpoint(tmp_path):
     names = {p.name for p in (Path(b) / "global_step2").iterdir()}
     assert "layer_01-model_00-model_states.pt" in names and not any("model_01" in n for n in names)
     assert abs(_run(2, 1, 2, 29695, "load", b) - want) < 2e-4
+
+
+def _tied_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    ps = None
+    if world > 1:
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        from b200flow.parallel.groups import ParallelState
+
+        ps = ParallelState.initialize(tp=world, pp=1)
+    torch.set_num_threads(1)
+    from b200flow.engines.ds_engine import initialize
+    from b200flow.models.gpt import GPTModel, config_from_preset
+
+    cfg = config_from_preset("gpt2-tiny", hidden=64, heads=4, ffn=128, vocab_size=128, max_seq=32)   # tied, biases, GELU
+    eng = initialize(cfg, {"train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": 2,
+                           "optimizer": {"params": {"lr": 2e-3, "weight_decay": 0.0}}}, ps, device=torch.device("cpu"), seed=4)
+    torch.manual_seed(77)
+    full = GPTModel(cfg, dtype=torch.float32, device=torch.device("cpu")).state_dict()
+    geo = Geometry(heads=4, kv_heads=4, swiglu=False)
+    with torch.no_grad():
+        for name, p in eng.model.named_parameters():
+            p.copy_(split(name, full[name], world, geo, head_replicated=True)[rank if world > 1 else 0])
+    o = eng.optimizer
+    o.master.copy_(eng.flat.params[o.lo:o.hi].float())
+    it = itertools.cycle(_batches(cfg))
+    losses = [float(eng.train_batch(it)) for _ in range(4)]
+    wte = eng.model.embed.wte.detach().clone()
+    if world > 1:
+        other = [torch.empty_like(wte) for _ in range(world)]
+        dist.all_gather(other, wte)
+        same = all(torch.allclose(other[0], t, atol=1e-6) for t in other)
+    else:
+        same = True
+    if rank == 0:
+        q.put((losses, same))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def test_tied_embeddings_under_tensor_parallelism_without_pipeline_stages():
+    """GPT-2 (tied input / output embeddings) at TP 2, PP 1: the head works on each rank's vocabulary rows of the
+    shared table, the table stays identical on both ranks, and the loss curve is the single-process one."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    _tied_worker(0, 1, 29696, q)
+    want, _ = q.get()
+    procs = [ctx.Process(target=_tied_worker, args=(r, 2, 29697, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got, same = q.get(timeout=300)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert same, "the replicated embedding table diverged between TP ranks"
+    assert got[-1] < got[0]
+    for a, b in zip(got, want):
+        assert abs(a - b) < 2e-3, (got, want)
