@@ -102,17 +102,19 @@ def test_resharding_the_per_layer_files_of_a_pipeline_checkpoint(tmp_path):
     assert abs(_run(2, 1, 2, 29695, "load", b) - want) < 2e-4
 
 
-def _tied_worker(rank, world, port, q):
+def _tied_worker(rank, world, port, q, pp=1):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     ps = None
     if world > 1:
         dist.init_process_group("gloo", rank=rank, world_size=world)
         from b200flow.parallel.groups import ParallelState
 
-        ps = ParallelState.initialize(tp=world, pp=1)
+        ps = ParallelState.initialize(tp=world // pp, pp=pp)
     torch.set_num_threads(1)
     from b200flow.engines.ds_engine import initialize
     from b200flow.models.gpt import GPTModel, config_from_preset
+
+    tp_w, tp_r = (ps.topo.tp, ps.tp_rank) if ps else (1, 0)
 
     cfg = config_from_preset("gpt2-tiny", hidden=64, heads=4, ffn=128, vocab_size=128, max_seq=32)   # tied, biases, GELU
     eng = initialize(cfg, {"train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": 2,
@@ -120,20 +122,35 @@ def _tied_worker(rank, world, port, q):
     torch.manual_seed(77)
     full = GPTModel(cfg, dtype=torch.float32, device=torch.device("cpu")).state_dict()
     geo = Geometry(heads=4, kv_heads=4, swiglu=False)
+    lo = eng.model.layer_range[0]
     with torch.no_grad():
         for name, p in eng.model.named_parameters():
-            p.copy_(split(name, full[name], world, geo, head_replicated=True)[rank if world > 1 else 0])
+            src = name
+            if name.startswith("layers."):
+                parts = name.split(".")
+                src = ".".join(["layers", str(int(parts[1]) + lo)] + parts[2:])
+            if name == "head.weight" and pp > 1:      # last stage: its own vocab-parallel copy of the tied table
+                p.copy_(full["embed.wte"].chunk(tp_w)[tp_r])
+                continue
+            p.copy_(split(src, full[src], tp_w, geo, head_replicated=True)[tp_r])
     o = eng.optimizer
     o.master.copy_(eng.flat.params[o.lo:o.hi].float())
     it = itertools.cycle(_batches(cfg))
     losses = [float(eng.train_batch(it)) for _ in range(4)]
-    wte = eng.model.embed.wte.detach().clone()
-    if world > 1:
+    same = True
+    if world > 1 and pp == 1:
+        wte = eng.model.embed.wte.detach().clone()
         other = [torch.empty_like(wte) for _ in range(world)]
         dist.all_gather(other, wte)
         same = all(torch.allclose(other[0], t, atol=1e-6) for t in other)
-    else:
-        same = True
+    if pp > 1:            # the last stage's head rows must still equal the first stage's table rows
+        mine = eng.model.embed.wte.detach()[tp_r * (cfg.vocab_size // tp_w):(tp_r + 1) * (cfg.vocab_size // tp_w)] \
+            if eng.stage == 0 else eng.model.head.weight.detach()
+        pair = [torch.empty_like(mine) for _ in range(2)]
+        dist.all_gather(pair, mine.contiguous(), group=ps.embedding_group)
+        ok = torch.tensor([float(torch.allclose(pair[0], pair[1], atol=1e-6))])
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        same = bool(ok.item())
     if rank == 0:
         q.put((losses, same))
     if world > 1:
@@ -157,5 +174,25 @@ def test_tied_embeddings_under_tensor_parallelism_without_pipeline_stages():
         assert p.exitcode == 0
     assert same, "the replicated embedding table diverged between TP ranks"
     assert got[-1] < got[0]
+    for a, b in zip(got, want):
+        assert abs(a - b) < 2e-3, (got, want)
+
+
+def test_tied_embeddings_under_tp2_pp2_follow_the_single_process_curve():
+    """The reference's GPT-2 345M TP2 x PP2 example ties the output layer to the input embedding across the first
+    and the last pipeline stage: same loss curve as one process, head rows stay equal to the
+    table rows."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    _tied_worker(0, 1, 29698, q)
+    want, _ = q.get()
+    procs = [ctx.Process(target=_tied_worker, args=(r, 4, 29699, q, 2)) for r in range(4)]
+    for p in procs:
+        p.start()
+    got, same = q.get(timeout=300)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert same, "tied head rows and embedding rows diverged"
     for a, b in zip(got, want):
         assert abs(a - b) < 2e-3, (got, want)
