@@ -184,3 +184,69 @@ def test_stock_library_twin_of_gpt_moe_trains_on_cpu():
     r = route_top1(moe.gate(x).float(), (max(4, 10) + 7) // 8 * 8)
     dropped = r["expert"] < 0
     assert torch.equal(y[dropped], torch.zeros_like(y[dropped])) and (y[~dropped].abs().sum(1) > 0).all()
+
+
+def _ep_engine_worker(rank, world, port, q):
+    import itertools
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    ps = None
+    if world > 1:
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        from b200flow.parallel.groups import ParallelState
+
+        ps = ParallelState.initialize(tp=1, pp=1, ep=world)
+    torch.set_num_threads(1)
+    from b200flow.engines.ds_engine import initialize
+    from b200flow.models.gpt import GPTModel, config_from_preset
+
+    cfg = config_from_preset("gpt-moe-tiny")
+    gas = 4 // world
+    eng = initialize(cfg, {"train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": gas,
+                           "optimizer": {"params": {"lr": 2e-3, "weight_decay": 0.0}}}, ps, device=torch.device("cpu"), seed=4)
+    torch.manual_seed(123)
+    full = GPTModel(cfg, dtype=torch.float32, device=torch.device("cpu")).state_dict()
+    with torch.no_grad():
+        for name, p in eng.model.named_parameters():
+            src = full[name]
+            if getattr(p, "is_expert", False) and world > 1:
+                el = p.shape[0]
+                src = src[rank * el:(rank + 1) * el]
+            p.copy_(src)
+    for o in (eng.optimizer, eng.expert_optimizer):
+        o.master.copy_(o.flat.params[o.lo:o.hi].float())
+    g = torch.Generator().manual_seed(9)
+    toks = [torch.randint(0, cfg.vocab_size, (2, 33), generator=g) for _ in range(4)]
+    mine = toks[rank::world] if world > 1 else toks
+    it = itertools.cycle([(t[:, :-1].contiguous(), t[:, 1:].contiguous()) for t in mine])
+    losses = []
+    for _ in range(3):
+        loss = eng.train_batch(it).clone()
+        if world > 1:
+            dist.all_reduce(loss)
+            loss /= world
+        losses.append(float(loss))
+    if rank == 0:
+        q.put(losses)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def test_engine_with_expert_parallelism_follows_the_single_process_curve():
+    """GPT-MoE through the engine at EP = DP = 2 (experts split over the ranks, dense parameters under ZeRO-1 over
+    both, expert parameters in their own group) against one process holding all experts on the same global batch."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    _ep_engine_worker(0, 1, 29661, q)
+    want = q.get()
+    procs = [ctx.Process(target=_ep_engine_worker, args=(r, 2, 29662, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = q.get(timeout=300)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert got[-1] < got[0]
+    for a, b in zip(got, want):
+        assert abs(a - b) < 2e-3, (got, want)
