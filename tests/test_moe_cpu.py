@@ -3,6 +3,7 @@ import os
 import sys
 from pathlib import Path
 
+import pytest
 import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
@@ -55,13 +56,13 @@ def test_single_process_layer_matches_dense_oracle():
     assert x.grad is not None and layer.wg.grad is not None and layer.w1.grad.abs().sum() > 0
 
 
-def _ep_worker(rank, world, port, q):
+def _ep_worker(rank, world, port, q, top_k=1):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     torch.manual_seed(5)
-    full = MoELayer(32, 64, 4, dtype=torch.float32)                     # all 4 experts, identical on both ranks
+    full = MoELayer(32, 64, 4, dtype=torch.float32, top_k=top_k)        # all 4 experts, identical on both ranks
     ep = EPContext(dist.group.WORLD, world, rank)
-    part = MoELayer(32, 64, 4, ep=ep, dtype=torch.float32, fused=False)
+    part = MoELayer(32, 64, 4, ep=ep, dtype=torch.float32, fused=False, top_k=top_k)
     with torch.no_grad():
         part.wg.copy_(full.wg)
         lo = rank * part.El
@@ -84,10 +85,11 @@ def _ep_worker(rank, world, port, q):
     dist.destroy_process_group()
 
 
-def test_expert_parallel_all_to_all_matches_local():
+@pytest.mark.parametrize("top_k", [1, 2])
+def test_expert_parallel_all_to_all_matches_local(top_k):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_ep_worker, args=(r, 2, 29641, q)) for r in range(2)]
+    procs = [ctx.Process(target=_ep_worker, args=(r, 2, 29643 + top_k, q, top_k)) for r in range(2)]
     for p in procs:
         p.start()
     res = [q.get(timeout=120) for _ in range(2)]
