@@ -68,13 +68,13 @@ def _dp2_worker(rank, port, save_dir, mode, q, world=2, pp=1):
             eng.train_batch(it)
         eng.save_checkpoint(save_dir)
         o = eng.optimizer
-        q.put((rank, o.lo, o.hi, eng.flat.params.clone(), o.exp_avg.clone(), o.exp_avg_sq.clone(), o.step_count,
-               eng.stage, ps.dp_rank))
+        q.put((rank, o.lo, o.hi, eng.flat.params.numpy().copy(), o.exp_avg.numpy().copy(), o.exp_avg_sq.numpy().copy(),
+               o.step_count, eng.stage, ps.dp_rank))       # numpy: pickled by value, safe after this process exits
     else:
         eng.load_checkpoint(save_dir)
         o = eng.optimizer
-        q.put((rank, o.lo, o.hi, eng.flat.params.clone(), o.master.clone(), o.exp_avg.clone(), o.step_count,
-               eng.stage, ps.dp_rank))
+        q.put((rank, o.lo, o.hi, eng.flat.params.numpy().copy(), o.master.numpy().copy(), o.exp_avg.numpy().copy(),
+               o.step_count, eng.stage, ps.dp_rank))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -87,7 +87,10 @@ def _spawn(mode, save_dir, port, world=2, pp=1):
     procs = [ctx.Process(target=_dp2_worker, args=(r, port, save_dir, mode, q, world, pp)) for r in range(world)]
     for p in procs:
         p.start()
-    out = sorted((q.get(timeout=300) for _ in procs), key=lambda t: t[0])
+    import numpy as np
+
+    out = sorted((tuple(torch.from_numpy(v) if isinstance(v, np.ndarray) else v for v in q.get(timeout=300))
+                  for _ in procs), key=lambda t: t[0])
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0

@@ -324,3 +324,57 @@ def test_fused_adamw_front_end_resumes_with_its_step_count():
         step(wa, oa, k)
         step(wb, ob, k)
     assert torch.allclose(wa, wb, atol=1e-7)
+
+
+def _accum_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    from b200flow.engines.accelerate_api import Accelerator
+    from b200flow.optim import AdamW
+
+    acc = Accelerator(cpu=True, gradient_accumulation_steps=2)
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(8, 16), torch.nn.Tanh(), torch.nn.Linear(16, 1))
+    opt = AdamW(model.parameters(), lr=1e-2, weight_decay=0.0)
+    model, opt = acc.prepare(model, opt)
+    g = torch.Generator().manual_seed(1)
+    x, y = torch.randn(2, 16, 8, generator=g), torch.randn(2, 16, 1, generator=g)       # 2 optimizer steps x 16 samples
+    for step in range(2):
+        for micro in range(2):                                                        # this rank's 2 micro-batches of 4
+            lo = (rank * 2 + micro) * 4
+            with acc.accumulate(model):
+                loss = torch.nn.functional.mse_loss(model(x[step, lo:lo + 4]), y[step, lo:lo + 4])
+                acc.backward(loss)
+                opt.step()
+                opt.zero_grad()
+    if rank == 0:
+        q.put(torch.cat([p.detach().reshape(-1) for p in model.parameters()]).tolist())
+    acc.wait_for_everyone()
+    dist.destroy_process_group()
+
+
+def test_accumulation_over_ddp_equals_one_large_batch():
+    """Accelerate's `accumulate` on two ranks (2 micro-batches each, reduction only on the last one) makes the
+    update a single process makes on the 16-sample batch."""
+    from b200flow.optim import AdamW
+
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(8, 16), torch.nn.Tanh(), torch.nn.Linear(16, 1))
+    opt = AdamW(model.parameters(), lr=1e-2, weight_decay=0.0)
+    g = torch.Generator().manual_seed(1)
+    x, y = torch.randn(2, 16, 8, generator=g), torch.randn(2, 16, 1, generator=g)
+    for step in range(2):
+        torch.nn.functional.mse_loss(model(x[step]), y[step]).backward()
+        opt.step()
+        opt.zero_grad()
+    want = torch.cat([p.detach().reshape(-1) for p in model.parameters()])
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_accum_worker, args=(r, 2, 29644, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = torch.tensor(q.get(timeout=300))
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert torch.allclose(got, want, atol=1e-6), float((got - want).abs().max())
