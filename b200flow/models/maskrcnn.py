@@ -149,6 +149,9 @@ class MaskRCNN(nn.Module):
         from torchvision.ops import FrozenBatchNorm2d
 
         self.cfg = cfg = cfg or MaskRCNNConfig()
+        if not cfg.mode_fpn:
+            raise NotImplementedError("MODE_FPN=False (tensorpack's ResNet-C4 variant) is not built; every Mask R-CNN "
+                                      "configuration of the reference sets MODE_FPN=True")
         c = max(16, int(256 * cfg.width) // 8 * 8)
         if cfg.width >= 1.0:
             body = torchvision.models.resnet50(weights=None, norm_layer=FrozenBatchNorm2d)   # BACKBONE.NORM=FreezeBN
