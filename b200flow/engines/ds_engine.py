@@ -187,6 +187,7 @@ class TrainEngine:
         self._flops_profile_step = int(fp.get("profile_step", 1)) if fp.get("enabled") else -1
         self.global_steps = 0
         self._micro_steps, self._stepped_at = 0, -1
+        self._drop_calls, self._seed = 0, int(seed)
         self.p2p = None
         self.last_loss = None
 
@@ -202,10 +203,19 @@ class TrainEngine:
                               (tokens, self.cfg.hidden), self.dtype, self.device)
         return self.p2p
 
+    def _set_drop_seed(self):
+        """One dropout seed per micro-batch: equal on the TP / PP ranks of a replica, different between replicas;
+        a recomputed forward (activation checkpointing) reads the same value again."""
+        if self.cfg.dropout > 0 and self.model.training:
+            self._drop_calls += 1
+            self.model.drop_seed = (self._seed * 1000003 + self._drop_calls * 4099
+                                    + (self.ps.dp_rank if self.ps else 0) * 15485863) & 0x3FFFFFFF
+
     def _forward_micro(self, batch, act):
         tokens, labels = batch
         b, s = tokens.shape
         last = self.stage == self.pp_world - 1
+        self._set_drop_seed()
         if self.stage == 0:
             out = self.model(tokens=tokens, labels=labels if self.pp_world == 1 else None)
         else:
@@ -329,6 +339,7 @@ class TrainEngine:
             self.optimizer.zero_grad()
             if self.expert_optimizer is not None:
                 self.expert_optimizer.zero_grad()
+        self._set_drop_seed()
         return self.model(tokens=tokens, labels=labels)
 
     def backward(self, loss: torch.Tensor) -> torch.Tensor:
@@ -351,6 +362,14 @@ class TrainEngine:
         this; examples/megatron-deepspeed/gpt2_345m/pretrain-ddp-tp-pp-zero1.yaml:57).  Under pipeline
         parallelism the micro-batches stream through the stages and every stage returns the loss."""
         batches = [next(data_iter) for _ in range(num_micro_batches)]
+        was_training = self.model.training
+        self.model.eval()                  # no dropout while evaluating
+        try:
+            return self._eval_micro_batches(batches, num_micro_batches)
+        finally:
+            self.model.train(was_training)
+
+    def _eval_micro_batches(self, batches, num_micro_batches):
         with torch.no_grad():
             if self.pp_world == 1:
                 losses = [self.model(tokens=t, labels=l) for t, l in batches]

@@ -42,7 +42,7 @@ class GPTConfig:
     tie_embeddings: bool = False
     eps: float = 1e-5
     init_std: float = 0.02
-    dropout: float = 0.0
+    dropout: float = 0.0          # --hidden-dropout (embeddings, attention output, MLP output)
     name: str = "llama"
     num_experts: int = 0          # > 0: MoE FFN every `moe_every`-th layer (DeepSpeed --num-experts)
     moe_every: int = 2            # --expert-interval
@@ -224,15 +224,27 @@ class TransformerLayer(nn.Module):
             if p is not None:
                 p.tp_replicated = True
 
-    def forward(self, h, seq: int, batch: int, rope_tables=None, kv_lens=None):
+    def _dropout_add(self, x, residual, p, seed):
+        """residual + dropout(x).  Sequence-parallel activations are different rows on every TP rank and take a
+        per-rank mask; replicated activations must get the same mask everywhere (Megatron's two RNG streams)."""
+        if self.tp.world > 1 and self.tp.sequence_parallel:
+            seed = seed + 7919 * (self.tp.rank + 1)
+        return E.bias_dropout_add(x, None, residual, p, seed)
+
+    def forward(self, h, seq: int, batch: int, rope_tables=None, kv_lens=None, drop_seed: int = 0):
         cfg, tp = self.cfg, self.tp
         rms = cfg.norm == "rms"
         d = cfg.head_dim
+        p = cfg.dropout if self.training else 0.0
+        seed = drop_seed + 2 * self.layer_idx
         y = N.norm(h, self.ln1_w, self.ln1_b, eps=cfg.eps, rms=rms)
         qkv = tp.column_linear(y, self.wqkv, self.bqkv)              # [s*b, (h+2kv)*d] full sequence
         o = qkv_attention(qkv.view(seq, batch, self.h_local + 2 * self.kv_local, d), self.h_local,
                           self.kv_local, True, 1.0 / math.sqrt(d), rope_tables, kv_lens)
-        h = tp.row_linear(o, self.wo, self.bo, residual=h)           # residual fused in the epilogue
+        if p > 0:      # --hidden-dropout: the residual add moves out of the GEMM epilogue, behind the mask
+            h = self._dropout_add(tp.row_linear(o, self.wo, self.bo), h, p, seed)
+        else:
+            h = tp.row_linear(o, self.wo, self.bo, residual=h)       # residual fused in the epilogue
         y = N.norm(h, self.ln2_w, self.ln2_b, eps=cfg.eps, rms=rms)
         if self.moe is not None:
             return h + self.moe(y)
@@ -240,6 +252,8 @@ class TransformerLayer(nn.Module):
             a = E.swiglu(tp.column_linear(y, self.w1, self.b1))
         else:
             a = tp.column_linear_gelu(y, self.w1, self.b1)
+        if p > 0:
+            return self._dropout_add(tp.row_linear(a, self.w2, self.b2), h, p, seed + 1)
         h = tp.row_linear(a, self.w2, self.b2, residual=h)
         return h
 
@@ -347,6 +361,7 @@ class GPTModel(nn.Module):
         else:
             self.head = None
         self.recompute = False
+        self.drop_seed = 0       # set per micro-batch by the engine, so a recomputed forward draws the same masks
 
     def _rope(self, seq, device):
         if not self.cfg.rope:
@@ -362,12 +377,17 @@ class GPTModel(nn.Module):
         else:
             h = hidden
         rope = self._rope(seq, h.device)
+        drop = self.cfg.dropout if self.training else 0.0
+        seed = int(self.drop_seed)
+        if drop > 0 and self.embed is not None:      # Megatron applies the hidden dropout to the embeddings too
+            es = seed - 1 + (7919 * (self.tp.rank + 1) if self.tp.world > 1 and self.tp.sequence_parallel else 0)
+            h = E.bias_dropout_add(h, None, None, drop, es)
         for layer in self.layers:
             if self.recompute and torch.is_grad_enabled():
-                h = torch.utils.checkpoint.checkpoint(layer, h, seq, batch, rope, kv_lens,
+                h = torch.utils.checkpoint.checkpoint(layer, h, seq, batch, rope, kv_lens, seed,
                                                       use_reentrant=False)
             else:
-                h = layer(h, seq, batch, rope, kv_lens)
+                h = layer(h, seq, batch, rope, kv_lens, seed)
         if self.head is not None and labels is not None:
             loss = self.head(h, labels)
             if self.cfg.num_experts:

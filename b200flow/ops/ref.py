@@ -44,8 +44,10 @@ def bias_gelu(x, bias=None):
 
 def bias_dropout_add(x, bias, residual, p=0.0, seed=0, training=True):
     y = x + bias if bias is not None else x
-    if p > 0 and training:
-        y = F.dropout(y, p, True)
+    if p > 0 and training:      # the mask is a function of the seed alone, like the kernel's counter-based one
+        g = torch.Generator().manual_seed(int(seed) & 0x7FFFFFFFFFFFFFFF)
+        keep = (torch.rand(y.shape, generator=g) >= p).to(y.dtype)
+        y = y * keep / (1.0 - p)
     return y + residual if residual is not None else y
 
 

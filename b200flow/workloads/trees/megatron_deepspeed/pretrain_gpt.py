@@ -52,6 +52,9 @@ def parse_args():
     a("--adam-beta1", type=float, default=0.9); a("--adam-beta2", type=float, default=0.999)
     a("--adam-eps", type=float, default=1e-8)
     a("--fp16", action="store_true"); a("--bf16", action="store_true")
+    a("--hidden-dropout", type=float, default=0.1); a("--attention-dropout", type=float, default=0.1)
+    a("--init-method-std", type=float, default=0.02); a("--layernorm-epsilon", type=float, default=1e-5)
+    a("--exit-interval", type=int, default=None)
     a("--tensor-model-parallel-size", type=int, default=1)
     a("--pipeline-model-parallel-size", type=int, default=1)
     a("--sequence-parallel", action="store_true")
@@ -120,7 +123,9 @@ def main():
         max_seq=args.max_position_embeddings, norm="rms" if args.normalization.lower() == "rmsnorm" else "ln",
         act="swiglu" if args.swiglu else "gelu", rope=args.use_rotary_position_embeddings,
         learned_pos=not args.use_rotary_position_embeddings, bias=not args.disable_bias_linear,
-        tie_embeddings=not args.untie_embeddings_and_output_weights, name="llama" if llama else "gpt2")
+        tie_embeddings=not args.untie_embeddings_and_output_weights, name="llama" if llama else "gpt2",
+        dropout=args.hidden_dropout, init_std=args.init_method_std, eps=args.layernorm_epsilon)
+    # --attention-dropout has no counterpart: the attention kernel keeps no probability matrix to drop from
     if n_experts > 1:
         cfg.num_experts, cfg.moe_every, cfg.moe_top_k = n_experts, args.expert_interval, args.topk
         cfg.aux_loss_coeff, cfg.moe_min_capacity = args.moe_loss_coeff, args.moe_min_capacity
@@ -232,6 +237,11 @@ def main():
             engine.save_checkpoint(args.save)
             if rank == 0:
                 print(f"  successfully saved checkpoint at iteration {iteration:7d} to {args.save}", flush=True)
+        if args.exit_interval and iteration % args.exit_interval == 0:
+            if rank == 0:
+                print(f" exiting program at iteration {iteration}", flush=True)
+            train_iters = iteration
+            break
     if args.save and (not args.save_interval or train_iters % args.save_interval != 0):
         engine.save_checkpoint(args.save)
     if tracker:

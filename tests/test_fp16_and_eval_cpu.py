@@ -378,3 +378,73 @@ def test_accumulation_over_ddp_equals_one_large_batch():
         p.join(timeout=120)
         assert p.exitcode == 0
     assert torch.allclose(got, want, atol=1e-6), float((got - want).abs().max())
+
+
+def test_hidden_dropout_masks_are_seeded_and_survive_recompute():
+    """--hidden-dropout: training differs from the dropout-free run, evaluation does not; the masks are a function
+    of the per-micro-batch seed, so activation recomputation reproduces them exactly."""
+    from b200flow.engines.ds_engine import initialize
+    from b200flow.models.gpt import config_from_preset
+
+    def engine(dropout, recompute=False):
+        cfg = config_from_preset("llama-tiny", hidden=64, heads=4, ffn=128, layers=4, vocab_size=128, max_seq=32,
+                                 dropout=dropout)
+        return cfg, initialize(cfg, {"train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": 2,
+                                     "optimizer": {"params": {"lr": 2e-3}},
+                                     "activation_checkpointing": {"enabled": recompute}},
+                               device=torch.device("cpu"), seed=5)
+
+    cfg, plain = engine(0.0)
+    _, drop = engine(0.2)
+    _, drop_ckpt = engine(0.2, recompute=True)
+    data = _batches(cfg)
+    e0 = float(plain.eval_batch(itertools.cycle(data)))
+    assert abs(float(drop.eval_batch(itertools.cycle(data))) - e0) < 1e-6 and drop.model.training
+    ia, ib, ic = (itertools.cycle(data) for _ in range(3))
+    for step in range(3):
+        la, lb, lc = float(plain.train_batch(ia)), float(drop.train_batch(ib)), float(drop_ckpt.train_batch(ic))
+        assert abs(lb - lc) < 1e-6, (step, lb, lc)            # recompute draws the same masks
+        assert abs(la - lb) > 1e-4                            # and dropout is really applied
+    assert torch.allclose(drop.flat.params, drop_ckpt.flat.params, atol=1e-6)
+
+
+def _dropout_tp_worker(rank, world, port, sp, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.set_num_threads(1)
+    from b200flow.engines.ds_engine import initialize
+    from b200flow.models.gpt import config_from_preset
+    from b200flow.parallel.groups import ParallelState
+
+    ps = ParallelState.initialize(tp=2, pp=1)
+    cfg = config_from_preset("llama-tiny", hidden=64, heads=4, ffn=128, layers=2, vocab_size=128, max_seq=32, dropout=0.3)
+    eng = initialize(cfg, {"train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": 2, "sequence_parallel": sp,
+                           "optimizer": {"params": {"lr": 5e-3}}}, ps, device=torch.device("cpu"), seed=5)
+    it = itertools.cycle(_batches(cfg))
+    losses = [float(eng.train_batch(it)) for _ in range(3)]
+    rep = torch.cat([p.detach().reshape(-1) for n, p in eng.model.named_parameters()
+                     if n.startswith("embed.") or getattr(p, "tp_replicated", False)])
+    both = [torch.empty_like(rep) for _ in range(2)]
+    dist.all_gather(both, rep)
+    q.put((rank, losses, bool(torch.equal(both[0], both[1])), float((rep - 1).abs().max())))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_dropout_under_tensor_parallelism_keeps_replicated_state_identical():
+    """Replicated activations (no sequence parallelism) need the same mask on every TP rank, sequence shards a
+    different one per rank; either way the tensors every TP rank holds whole stay bit-identical while they train."""
+    for sp, port in ((False, 29645), (True, 29646)):
+        ctx = mp.get_context("spawn")
+        q = ctx.Queue()
+        procs = [ctx.Process(target=_dropout_tp_worker, args=(r, 2, port, sp, q)) for r in range(2)]
+        for p in procs:
+            p.start()
+        res = [q.get(timeout=300) for _ in procs]
+        for p in procs:
+            p.join(timeout=120)
+            assert p.exitcode == 0
+        for rank, losses, same, moved in res:
+            assert same, f"replicated tensors diverged between TP ranks (sequence_parallel={sp})"
+            assert moved > 0 and all(v == v for v in losses)
+        assert res[0][1] == res[1][1]                          # both ranks report the same loss
