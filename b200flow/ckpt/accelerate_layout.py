@@ -29,27 +29,36 @@ def _name(base: str, i: int) -> str:
     return f"{stem}{_suffix(i)}{dot}{ext}"
 
 
+def save_model_weights(model, out_dir, safe_serialization: bool = True, index: int = 0) -> Path:
+    """One model's weights as `model[_i].safetensors` (or `pytorch_model[_i].bin`)."""
+    out = Path(out_dir)
+    sd = {k: v.detach().cpu().contiguous() for k, v in model.state_dict().items()}
+    if safe_serialization:
+        from safetensors.torch import save_file
+
+        # tied tensors share storage; safetensors wants each saved once
+        seen, uniq = {}, {}
+        for k, v in sd.items():
+            key = (v.data_ptr(), tuple(v.shape))
+            if key in seen:
+                continue
+            seen[key] = k
+            uniq[k] = v
+        path = out / _name(MODEL_NAME, index)
+        save_file(uniq, str(path), metadata={"format": "pt"})
+    else:
+        path = out / _name(MODEL_BIN, index)
+        torch.save(sd, path)
+    return path
+
+
 def save_state(out_dir, models, optimizers, schedulers, samplers, scaler, rank: int, is_main: bool,
                custom_objects=(), safe_serialization: bool = True) -> Path:
     out = Path(out_dir)
     out.mkdir(parents=True, exist_ok=True)
     if is_main:
         for i, m in enumerate(models):
-            sd = {k: v.detach().cpu().contiguous() for k, v in m.state_dict().items()}
-            if safe_serialization:
-                from safetensors.torch import save_file
-
-                # tied tensors share storage; safetensors wants each saved once
-                seen, uniq = {}, {}
-                for k, v in sd.items():
-                    key = (v.data_ptr(), tuple(v.shape))
-                    if key in seen:
-                        continue
-                    seen[key] = k
-                    uniq[k] = v
-                save_file(uniq, str(out / _name(MODEL_NAME, i)), metadata={"format": "pt"})
-            else:
-                torch.save(sd, out / _name(MODEL_BIN, i))
+            save_model_weights(m, out, safe_serialization, i)
         for i, o in enumerate(optimizers):
             torch.save(o.state_dict(), out / _name(OPTIMIZER_NAME, i))
         for i, s in enumerate(schedulers):

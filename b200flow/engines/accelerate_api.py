@@ -355,6 +355,61 @@ class Accelerator:
             out = [o[:ld.remainder] if o.shape[0] > ld.remainder else o for o in out]
         return out[0] if single else tuple(out)
 
+    def reduce(self, t: torch.Tensor, reduction: str = "sum", scale: float = 1.0) -> torch.Tensor:
+        """`accelerator.reduce`: all-reduce a tensor over the processes ("sum" or "mean"), times `scale`."""
+        out = t.clone()
+        if self.use_distributed:
+            dist.all_reduce(out)
+            if reduction == "mean":
+                out = out / self.num_processes
+        return out * scale if scale != 1.0 else out
+
+    def pad_across_processes(self, t: torch.Tensor, dim: int = 0, pad_index: int = 0, pad_first: bool = False):
+        """Pad `t` along `dim` to the largest size any process holds, so that it can be gathered."""
+        if not self.use_distributed:
+            return t
+        n = torch.tensor([t.shape[dim]], device=t.device)
+        sizes = [torch.zeros_like(n) for _ in range(self.num_processes)]
+        dist.all_gather(sizes, n)
+        m = int(max(s.item() for s in sizes))
+        if m == t.shape[dim]:
+            return t
+        shape = list(t.shape)
+        shape[dim] = m - t.shape[dim]
+        pad = t.new_full(shape, pad_index)
+        return torch.cat([pad, t] if pad_first else [t, pad], dim)
+
+    @contextlib.contextmanager
+    def autocast(self):
+        """Mixed-precision region.  Parameters already live in the compute dtype (bf16 on B200), so this only
+        wraps CPU-side or stray fp32 modules in torch's autocast."""
+        if self.device.type == "cuda" and self.mixed_precision in ("fp16", "bf16"):
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                yield
+        else:
+            yield
+
+    def on_main_process(self, fn):
+        """Decorator: run `fn` on the main process only."""
+        def wrapped(*a, **kw):
+            return fn(*a, **kw) if self.is_main_process else None
+        return wrapped
+
+    @property
+    def is_last_process(self) -> bool:
+        return self.process_index == self.num_processes - 1
+
+    def save_model(self, model, save_directory: str, safe_serialization: bool = True) -> None:
+        """Weights of one model in Accelerate's file naming (`model.safetensors` / `pytorch_model.bin`)."""
+        self.wait_for_everyone()
+        if self.is_main_process:
+            os.makedirs(save_directory, exist_ok=True)
+            L.save_model_weights(self.unwrap_model(model), save_directory, safe_serialization)
+        self.wait_for_everyone()
+
+    def get_tracker(self, name: str = "all"):
+        return self.trackers[0] if self.trackers else None
+
     # -------------------------------------------------------------- tracking
     def init_trackers(self, project_name: str, config: dict | None = None):
         if self.is_main_process and self.log_with is not None:

@@ -448,3 +448,38 @@ def test_dropout_under_tensor_parallelism_keeps_replicated_state_identical():
             assert same, f"replicated tensors diverged between TP ranks (sequence_parallel={sp})"
             assert moved > 0 and all(v == v for v in losses)
         assert res[0][1] == res[1][1]                          # both ranks report the same loss
+
+
+def _acc_api_worker(rank, world, port, tmp, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    from b200flow.engines.accelerate_api import Accelerator
+
+    acc = Accelerator(cpu=True)
+    t = torch.arange(3 + rank, dtype=torch.float32)
+    padded = acc.pad_across_processes(t, pad_index=-1)
+    red = acc.reduce(torch.tensor([float(rank + 1)]), "mean")
+    model = acc.prepare(torch.nn.Linear(4, 2))
+    acc.save_model(model, tmp)
+    ran = acc.on_main_process(lambda: "ran")()
+    with acc.autocast():
+        y = model(torch.ones(1, 4))
+    q.put((rank, padded.tolist(), float(red), ran, acc.is_last_process, list(y.shape)))
+    acc.wait_for_everyone()
+    dist.destroy_process_group()
+
+
+def test_accelerator_utility_calls(tmp_path):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_acc_api_worker, args=(r, 2, 29647, str(tmp_path), q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=300) for _ in procs)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert res[0][1] == [0.0, 1.0, 2.0, -1.0] and res[1][1] == [0.0, 1.0, 2.0, 3.0]
+    assert res[0][2] == res[1][2] == 1.5
+    assert res[0][3] == "ran" and res[1][3] is None and res[1][4] and not res[0][4]
+    assert (tmp_path / "model.safetensors").exists()

@@ -57,7 +57,7 @@ def test_megatron_tp2_pp2_zero1_and_resume(tmp_root):
     sets = ["resources.nnodes=1", "resources.nproc_per_node=4"]
     rc, st, logs = _install("mds", "pytorchjob-distributed", values, tmp_root, sets, env)
     assert rc == 0 and st["phase"] == "Succeeded", logs[-3000:]
-    assert "iteration        4/       4" in logs and "lm loss" in logs
+    assert "iteration        4/       4" in logs and "lm loss" in logs, logs[-4000:]
     # the values file trains in fp16: DeepSpeed's loss-scale state and skipped-step count are logged
     assert "loss scale: 65536.0" in logs and "number of skipped iterations:   0" in logs
     # --eval-interval under PP=2: forward-only pipeline schedule
