@@ -77,9 +77,16 @@ class GPTDataset(torch.utils.data.Dataset):
             self.doc_idx, self.sample_idx, self.shuffle_idx = build_indices(
                 np.asarray(indexed.sizes), documents, seq_length, num_samples, seed)
             try:
+                # Several ranks may build the same arrays at once, and others memory-map the files as soon as all
+                # three exist: write under a private name and rename, so a file that exists is complete (a
+                # half-written one under a reader's mmap is a bus error).
+                import os
+
                 cache.mkdir(parents=True, exist_ok=True)
                 for f, a in zip(files, (self.doc_idx, self.sample_idx, self.shuffle_idx)):
-                    np.save(f, a)
+                    tmp = f.with_name(f"{f.stem}.{os.getpid()}.tmp.npy")
+                    np.save(tmp, a)
+                    os.replace(tmp, f)
             except OSError:
                 pass
 

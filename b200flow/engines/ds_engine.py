@@ -31,7 +31,7 @@ from ..parallel import pipeline as PP
 from ..parallel.groups import ParallelState
 from ..parallel.loss_scaler import make_loss_scaler
 from ..parallel.tensor_parallel import SINGLE, TPContext, allreduce_replicated_grads
-from ..parallel.zero1 import AdamConfig, Zero1Optimizer, megatron_lr
+from ..parallel.zero1 import AdamConfig, Zero1Optimizer
 from ..utils.flat import FlatParams
 
 _KNOWN = {"train_micro_batch_size_per_gpu", "gradient_accumulation_steps", "zero_optimization",
@@ -166,6 +166,9 @@ class TrainEngine:
             o = self.optimizer      # master copy of the re-tied head rows
             o.master.copy_(self.flat.params[o.lo:o.hi].float())
         self.sched = config.get("scheduler", {}).get("params", None)
+        from ..parallel.lr_schedules import make_schedule
+
+        self._lr_fn = make_schedule(config.get("scheduler"), acfg.lr)     # Megatron's block or a DeepSpeed type
         # "fp16": {"enabled": true} keeps DeepSpeed's loss-scale state machine (parallel/loss_scaler.py)
         self.loss_scaler = make_loss_scaler(config.get("fp16"))
         self.skipped_steps = 0
@@ -441,14 +444,8 @@ class TrainEngine:
         return self.loss_scaler.scale if self.loss_scaler is not None else 1.0
 
     def _apply_lr(self):
-        if self.sched:
-            p = self.sched
-            self.optimizer.lr = megatron_lr(self.global_steps - self.skipped_steps + 1,
-                                            style=str(p.get("decay_style", "cosine")),
-                                            base_lr=float(p["max_lr"]),
-                                            min_lr=float(p.get("min_lr", 0.0)),
-                                            warmup_steps=int(p.get("warmup_steps", 0)),
-                                            decay_steps=int(p.get("decay_steps", 1)))
+        if self._lr_fn is not None:
+            self.optimizer.lr = self._lr_fn(self.global_steps - self.skipped_steps + 1)
 
     # ----------------------------------------------------------- checkpoints
     def save_checkpoint(self, save_dir: str, tag: str | None = None, client_state: dict | None = None):

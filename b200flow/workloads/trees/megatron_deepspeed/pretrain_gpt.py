@@ -158,12 +158,20 @@ def main():
 
     # ---- data: TP rank 0 semantics collapse to "every rank of a DP replica reads the same sample"
     prefix = args.data_path[-1] if args.data_path else None
-    if not prefix or not MMapIndexedDataset.exists(prefix):
+    # rank 0 decides whether a corpus has to be generated and everyone follows its decision: ranks looking at the
+    # directory on their own could see rank 0's half-written files, take them for a corpus and skip the barrier
+    need = [bool(not prefix or not MMapIndexedDataset.exists(prefix))]
+    if world > 1:
+        dist.broadcast_object_list(need, src=0)
+    if need[0]:
         home = os.environ.get("HOME", "/tmp")
         prefix = os.path.join(home, "synthetic-corpus", "gpt2_text_document")
         if rank == 0 and not MMapIndexedDataset.exists(prefix):
             print(f"[b200flow] no corpus at --data-path; generating a synthetic one at {prefix}", flush=True)
-            synthetic_corpus(prefix, min(vocab, 50257), num_docs=1500, mean_len=max(256, args.seq_length // 2))
+            tmp = prefix + f".tmp{os.getpid()}"
+            synthetic_corpus(tmp, min(vocab, 50257), num_docs=1500, mean_len=max(256, args.seq_length // 2))
+            os.replace(tmp + ".bin", prefix + ".bin")      # complete files appear under the final names
+            os.replace(tmp + ".idx", prefix + ".idx")
         if world > 1:
             dist.barrier()
     gbs = micro * gas * dp
