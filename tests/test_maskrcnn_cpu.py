@@ -135,3 +135,22 @@ def test_stock_library_twin_of_maskrcnn_builds_and_steps_on_cpu():
     loss = loss_fn(model, b)
     loss.backward()
     assert torch.isfinite(loss) and any(p.grad is not None and p.grad.abs().sum() > 0 for p in model.parameters())
+
+
+def test_faster_rcnn_mode_without_mask_head(tmp_path):
+    """`MODE_MASK=False` (tensorpack's Faster R-CNN configuration of the same script): no mask head, no mask loss,
+    bbox metrics only."""
+    import subprocess
+
+    env = dict(os.environ, **TINY, B2F_MRCNN_EPOCHS="1", B2F_MRCNN_STEPS="2", PYTHONPATH=str(REPO))
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        env.pop(k, None)
+    res = subprocess.run([sys.executable, "-m", "b200flow.workloads.maskrcnn.train", "--logdir", str(tmp_path / "log"),
+                          "--config", "MODE_MASK=False", "MODE_FPN=True", "TRAIN.EVAL_PERIOD=1"],
+                         cwd=REPO, env=env, capture_output=True, text=True, timeout=600)
+    out = res.stdout + res.stderr
+    assert res.returncode == 0, out[-2000:]
+    assert "mAP(bbox)/IoU=0.5:0.95" in out and "mAP(segm)" not in out and "mask" not in out.split("[epoch 1]")[1].split("|")[1]
+    refused = subprocess.run([sys.executable, "-m", "b200flow.workloads.maskrcnn.train", "--logdir", str(tmp_path / "c4"),
+                              "--config", "MODE_FPN=False"], cwd=REPO, env=env, capture_output=True, text=True, timeout=600)
+    assert refused.returncode != 0 and "MODE_FPN=False" in refused.stderr
