@@ -67,6 +67,7 @@ class TrainEngine:
         self.micro_batch = int(config.get("train_micro_batch_size_per_gpu", 1))
         self.gas = int(config.get("gradient_accumulation_steps", 1))
         zero_stage = int(config.get("zero_optimization", {}).get("stage", 1))
+        self._train_batch_size = config.get("train_batch_size")      # checked against micro x accumulation x DP below
         assert zero_stage in (0, 1), "b200flow implements ZeRO stage 0/1 (what the reference uses)"
         dtype = torch.bfloat16 if self.device.type == "cuda" else torch.float32
         if config.get("bf16", {}).get("enabled") and self.device.type == "cpu":
@@ -79,6 +80,17 @@ class TrainEngine:
         pp_world = ps.topo.pp if ps else 1
         dp_world = ps.topo.dp if ps else 1
         self.tp_world, self.pp_world, self.dp_world = tp_world, pp_world, dp_world
+        if self._train_batch_size is not None:
+            # DeepSpeed's rule: train_batch_size = micro batch x accumulation steps x data-parallel size; any one of
+            # the three may be left out of the config and is derived from the other two
+            tbs = int(self._train_batch_size)
+            if "gradient_accumulation_steps" not in config and "train_micro_batch_size_per_gpu" in config:
+                self.gas = max(1, tbs // (self.micro_batch * dp_world))
+            elif "train_micro_batch_size_per_gpu" not in config:
+                self.micro_batch = max(1, tbs // (self.gas * dp_world))
+            if self.micro_batch * self.gas * dp_world != tbs:
+                raise ValueError(f"ds_config: train_batch_size {tbs} != micro batch {self.micro_batch} x accumulation "
+                                 f"steps {self.gas} x data-parallel size {dp_world}")
         self.stage = ps.pp_rank if ps else 0
 
         fused_tp = None

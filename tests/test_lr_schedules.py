@@ -54,3 +54,19 @@ def test_engine_follows_a_deepspeed_scheduler_block():
         eng.train_batch(it)
         seen.append(eng.optimizer.lr)
     assert seen == pytest.approx([5e-4, 1e-3, 7.5e-4, 5e-4, 2.5e-4])
+
+
+def test_train_batch_size_rule_of_the_ds_config():
+    import torch
+
+    from b200flow.engines.ds_engine import initialize
+    from b200flow.models.gpt import config_from_preset
+
+    cfg = config_from_preset("llama-tiny", hidden=64, heads=4, ffn=128, layers=2, vocab_size=128, max_seq=32)
+    mk = lambda ds: initialize(cfg, ds, device=torch.device("cpu"))  # noqa: E731
+    assert mk({"train_batch_size": 8, "train_micro_batch_size_per_gpu": 2}).gas == 4           # accumulation derived
+    assert mk({"train_batch_size": 6, "gradient_accumulation_steps": 3}).micro_batch == 2      # micro batch derived
+    e = mk({"train_batch_size": 8, "train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": 4})
+    assert (e.micro_batch, e.gas) == (2, 4)
+    with pytest.raises(ValueError, match="train_batch_size"):
+        mk({"train_batch_size": 10, "train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": 4})
