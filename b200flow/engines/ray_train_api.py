@@ -97,10 +97,18 @@ class CheckpointConfig:
 
 
 @dataclass
+class FailureConfig:
+    """`max_failures`: how often a failed worker group is started again (from the newest reported checkpoint,
+    which the training function picks up with `get_checkpoint()`); -1 = without limit."""
+    max_failures: int = 0
+
+
+@dataclass
 class RunConfig:
     name: str | None = None
     storage_path: str | None = None
     checkpoint_config: CheckpointConfig = field(default_factory=CheckpointConfig)
+    failure_config: FailureConfig = field(default_factory=FailureConfig)
 
 
 class Checkpoint:
@@ -132,6 +140,12 @@ class Result:
     error: str | None = None
     best_checkpoints: list = field(default_factory=list)
     metrics_history: list = field(default_factory=list)
+
+    @property
+    def metrics_dataframe(self):
+        import pandas as pd
+
+        return pd.DataFrame(self.metrics_history)
 
 
 class ListDataset:
@@ -175,10 +189,11 @@ class ListDataset:
 
 # ---------------------------------------------------------- worker context
 class _Context:
-    def __init__(self, rank, world, local_rank, shards, report_chan, run_dir):
+    def __init__(self, rank, world, local_rank, shards, report_chan, run_dir, checkpoint=None):
         self.rank, self.world, self.local_rank = rank, world, local_rank
         self.shards, self.report_chan, self.run_dir = shards, report_chan, run_dir
         self.iteration = 0
+        self.checkpoint = checkpoint
 
     def get_world_rank(self):
         return self.rank
@@ -199,6 +214,12 @@ _ctx: _Context | None = None
 def get_context() -> _Context:
     assert _ctx is not None, "not inside a TorchTrainer worker"
     return _ctx
+
+
+def get_checkpoint() -> Checkpoint | None:
+    """The checkpoint to continue from: `TorchTrainer(resume_from_checkpoint=...)`, or the newest one reported
+    before a worker failure when the run was restarted under `FailureConfig`."""
+    return get_context().checkpoint
 
 
 def get_dataset_shard(name: str) -> ListDataset:
@@ -245,7 +266,8 @@ def _worker_main(rank, world, use_gpu, port, train_fn, config, run_id, run_dir):
         while shards is None:
             shards = data_chan.recv(1000)
         chan = Channel(f"/b2f_{run_id}_report_{rank}", create=False)
-        _ctx = _Context(rank, world, rank, shards, chan, run_dir)
+        start = shards.pop("__checkpoint__", None)
+        _ctx = _Context(rank, world, rank, shards, chan, run_dir, Checkpoint(start) if start else None)
         train_fn(config) if config is not None else train_fn()
         chan.send({"rank": rank, "done": True})
         dist.barrier()
@@ -264,13 +286,34 @@ def _worker_main(rank, world, use_gpu, port, train_fn, config, run_id, run_dir):
 class TorchTrainer:
     def __init__(self, train_loop_per_worker, *, train_loop_config: dict | None = None,
                  scaling_config: ScalingConfig | None = None, run_config: RunConfig | None = None,
-                 datasets: dict | None = None):
+                 datasets: dict | None = None, resume_from_checkpoint: Checkpoint | None = None):
+        self.resume = resume_from_checkpoint
         self.fn, self.config = train_loop_per_worker, train_loop_config
         self.scaling = scaling_config or ScalingConfig()
         self.run = run_config or RunConfig()
         self.datasets = datasets or {}
 
     def fit(self) -> Result:
+        """Run the worker group; on a worker failure start it again (at most `failure_config.max_failures` times)
+        from the newest checkpoint reported so far."""
+        budget = self.run.failure_config.max_failures
+        start = self.resume.path if self.resume is not None else None
+        history: list = []
+        attempt = 0
+        while True:
+            try:
+                res = self._fit_once(start, attempt)
+                res.metrics_history = history + res.metrics_history
+                return res
+            except _GroupFailed as e:
+                history += e.history
+                if budget >= 0 and attempt >= budget:
+                    raise RuntimeError(f"TorchTrainer worker failed:\n{e.error}") from None
+                attempt += 1
+                start = e.last_checkpoint or start
+                print(f"[b200flow] worker group failed; restart {attempt} from {start or 'scratch'}", flush=True)
+
+    def _fit_once(self, start_checkpoint: str | None, attempt: int) -> Result:
         n = int(os.environ.get("B2F_RAY_WORKERS_OVERRIDE", self.scaling.num_workers))
         name = self.run.name or f"TorchTrainer_{time.strftime('%Y-%m-%d_%H-%M-%S')}"
         root = Path(self.run.storage_path or os.path.expanduser("~/ray_results")) / name
@@ -288,12 +331,12 @@ class TorchTrainer:
         # hand every worker its shard of every dataset ("train" is split, the rest replicated-split too)
         split = {k: (d.split(n) if hasattr(d, "split") else [d] * n) for k, d in self.datasets.items()}
         for r in range(n):
-            data_ch[r].send({k: split[k][r] for k in split})
+            data_ch[r].send({**{k: split[k][r] for k in split}, "__checkpoint__": start_checkpoint})
         cc = self.run.checkpoint_config
         kept: list[tuple[float, str, dict]] = []
         history, last_metrics, last_ckpt, error = [], None, None, None
         done = set()
-        idx = 0
+        idx = len(list(root.glob("checkpoint_*")))       # a restarted group keeps numbering where the last one stopped
         while len(done) < n and error is None:
             progressed = False
             for r in range(n):
@@ -339,11 +382,18 @@ class TorchTrainer:
                 p.terminate()
         for c in data_ch + rep_ch:
             c.free()
-        (root / "result.json").write_text("\n".join(__import__("json").dumps(m) for m in history))
+        with open(root / "result.json", "a" if attempt else "w") as f:
+            f.write("".join(__import__("json").dumps(m) + "\n" for m in history))
         if last_ckpt is not None and not os.path.exists(last_ckpt.path) and kept:
             last_ckpt = Checkpoint(kept[0][1])
         res = Result(last_metrics, last_ckpt, str(root), error,
                      [(Checkpoint(p), m) for _, p, m in kept], history)
         if error:
-            raise RuntimeError(f"TorchTrainer worker failed:\n{error}")
+            raise _GroupFailed(error, last_ckpt.path if last_ckpt is not None else None, history)
         return res
+
+
+class _GroupFailed(Exception):
+    def __init__(self, error, last_checkpoint, history):
+        super().__init__(error)
+        self.error, self.last_checkpoint, self.history = error, last_checkpoint, history
