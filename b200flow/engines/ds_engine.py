@@ -102,6 +102,10 @@ class TrainEngine:
                             sequence_parallel=bool(config.get("sequence_parallel", True)),
                             fused=fused_tp) if tp_world > 1 else SINGLE
 
+        if model_config.num_experts and pp_world > 1:
+            # like the pinned Megatron-DeepSpeed: the load-balancing losses of earlier stages would be lost
+            raise ValueError("MoE layers and pipeline parallelism cannot be combined (--num-experts needs "
+                             "--pipeline-model-parallel-size 1)")
         # expert parallelism: EP groups are carved out of the DP dimension
         self.ep_world = ps.topo.ep if ps else 1
         self.ep_ctx = None

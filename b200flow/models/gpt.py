@@ -50,6 +50,7 @@ class GPTConfig:
     aux_loss_coeff: float = 0.01
     moe_top_k: int = 1            # --topk (DeepSpeed TopKGate: 1 or 2)
     moe_min_capacity: int = 4     # --moe-min-capacity
+    moe_eval_capacity_factor: float | None = None   # --moe-eval-capacity-factor (None: same as training)
     moe_fp8: bool = False         # expert GEMMs (forward + dgrad) in e4m3
 
     def __post_init__(self):
@@ -207,7 +208,7 @@ class TransformerLayer(nn.Module):
             self.moe = MoELayer(H, cfg.ffn, cfg.num_experts, ep, cfg.capacity_factor, act="gelu",
                                 aux_loss_coeff=cfg.aux_loss_coeff, init_std=std, dtype=dtype, device=device,
                                 fused=fused_moe, fp8=cfg.moe_fp8, top_k=cfg.moe_top_k,
-                                min_capacity=cfg.moe_min_capacity)
+                                min_capacity=cfg.moe_min_capacity, eval_capacity_factor=cfg.moe_eval_capacity_factor)
             self.w1 = self.w2 = None
         else:
             self.w1 = nn.Parameter(torch.empty(n_up, H, **kw).normal_(0, std))       # gate|up or fc1

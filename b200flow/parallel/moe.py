@@ -295,7 +295,7 @@ class MoELayer(nn.Module):
     def __init__(self, hidden: int, ffn: int, num_experts: int, ep: EPContext | None = None,
                  capacity_factor: float = 1.0, min_capacity: int = 4, act: str = "gelu",
                  aux_loss_coeff: float = 0.01, init_std: float = 0.02, dtype=torch.bfloat16, device=None,
-                 fused: bool = True, fp8: bool = False, top_k: int = 1):
+                 fused: bool = True, fp8: bool = False, top_k: int = 1, eval_capacity_factor: float | None = None):
         super().__init__()
         assert top_k in (1, 2), "DeepSpeed's TopKGate supports k = 1 or 2"
         self.fp8, self.top_k = fp8, top_k
@@ -303,6 +303,7 @@ class MoELayer(nn.Module):
         assert num_experts % self.ep.world == 0
         self.E, self.El = num_experts, num_experts // self.ep.world
         self.hidden, self.ffn, self.cf, self.min_cap = hidden, ffn, capacity_factor, min_capacity
+        self.eval_cf = capacity_factor if eval_capacity_factor is None else eval_capacity_factor   # --moe-eval-capacity-factor
         self.aux_coeff, self.fused = aux_loss_coeff, fused
         kw = dict(dtype=dtype, device=device)
         e_pad = (num_experts + 7) // 8 * 8
@@ -317,7 +318,8 @@ class MoELayer(nn.Module):
         self.last_counts = None
 
     def capacity(self, tokens: int) -> int:
-        c = max(self.min_cap, math.ceil(tokens / self.E * self.cf * self.top_k))
+        cf = self.cf if self.training else self.eval_cf
+        c = max(self.min_cap, math.ceil(tokens / self.E * cf * self.top_k))
         return (c + 7) // 8 * 8
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:

@@ -131,6 +131,7 @@ def main():
         cfg.aux_loss_coeff, cfg.moe_min_capacity = args.moe_loss_coeff, args.moe_min_capacity
         # without token dropping every token must fit even if all of them pick one expert
         cfg.capacity_factor = float(n_experts) if args.disable_moe_token_dropping else args.moe_train_capacity_factor
+        cfg.moe_eval_capacity_factor = args.moe_eval_capacity_factor
         cfg.name = "gpt-moe"
     decay_iters = args.lr_decay_iters or args.train_iters
     warm = args.lr_warmup_iters if args.lr_warmup_iters is not None else int(args.lr_warmup_fraction * decay_iters)

@@ -252,3 +252,30 @@ def test_engine_with_expert_parallelism_follows_the_single_process_curve():
     assert got[-1] < got[0]
     for a, b in zip(got, want):
         assert abs(a - b) < 2e-3, (got, want)
+
+
+def test_eval_capacity_factor_applies_in_eval_mode_only():
+    layer = MoELayer(32, 64, 4, dtype=torch.float32, capacity_factor=1.0, eval_capacity_factor=2.0)
+    assert layer.capacity(64) == 16
+    layer.eval()
+    assert layer.capacity(64) == 32
+    layer.train()
+    assert layer.capacity(64) == 16
+    x = torch.randn(64, 32)
+    layer.eval()
+    y = layer(x)
+    assert torch.isfinite(y).all()
+
+
+def test_moe_with_pipeline_stages_is_refused():
+    from b200flow.engines.ds_engine import TrainEngine
+    from b200flow.models.gpt import config_from_preset
+
+    class _Topo:
+        tp, pp, dp, ep = 1, 2, 1, 1
+
+    class _PS:
+        topo, pp_rank, tp_rank, dp_rank = _Topo(), 0, 0, 0
+
+    with pytest.raises(ValueError, match="pipeline"):
+        TrainEngine(config_from_preset("gpt-moe-tiny"), {}, _PS(), device=torch.device("cpu"))
