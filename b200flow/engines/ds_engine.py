@@ -38,7 +38,7 @@ _KNOWN = {"train_micro_batch_size_per_gpu", "gradient_accumulation_steps", "zero
           "bf16", "fp16", "gradient_clipping", "optimizer", "wall_clock_breakdown",
           "train_batch_size", "steps_per_print", "scheduler", "fused_collectives",
           "activation_checkpointing", "sequence_parallel", "expert_parallel_size", "flops_profiler",
-          "comms_logger"}
+          "comms_logger", "sequence_parallel_size"}
 
 
 def split_layers(num_layers: int, stages: int) -> list[tuple[int, int]]:
@@ -137,6 +137,15 @@ class TrainEngine:
             for n, p in self.model.named_parameters():
                 if n.startswith("embed.") or getattr(p, "tp_replicated", False):
                     dist.broadcast(p.data, src=ps.tp_ranks[0], group=ps.tp_group)
+        # DeepSpeed-Ulysses (`--ds-sequence-parallel-size`): ranks of a group share each micro-batch and split its
+        # sequence; outside attention everything is local, for gradients they are ordinary data-parallel ranks
+        self.sp_world = ps.topo.sp if ps else 1
+        if self.sp_world > 1:
+            if tp_world > 1 or pp_world > 1 or model_config.num_experts:
+                raise ValueError("sequence_parallel_size > 1 (Ulysses) is built for TP = PP = 1 dense models")
+            for layer in self.model.layers:
+                layer.ulysses_group = ps.sp_group
+            self.model.seq_mult = self.sp_world
         self.model.recompute = bool(config.get("activation_checkpointing", {}).get("enabled", False))
         self.dp_comm = None
         allocator = None
@@ -230,8 +239,25 @@ class TrainEngine:
             self.model.drop_seed = (self._seed * 1000003 + self._drop_calls * 4099
                                     + (self.ps.dp_rank if self.ps else 0) * 15485863) & 0x3FFFFFFF
 
+    def _sp_slice(self, tokens, labels):
+        """This rank's slice of the sequence under Ulysses sequence parallelism (identity otherwise)."""
+        if self.sp_world == 1:
+            return tokens, labels
+        assert tokens.shape[1] % self.sp_world == 0, "sequence length must divide by the sequence-parallel size"
+        sl = tokens.shape[1] // self.sp_world
+        lo = self.ps.sp_rank * sl
+        self.model.embed.pos_offset = lo
+        return tokens[:, lo:lo + sl].contiguous(), labels[:, lo:lo + sl].contiguous()
+
+    def _sp_mean(self, loss):
+        if self.sp_world > 1:  # mean over the whole sequence = mean of the slices' means
+            loss = loss.clone()
+            dist.all_reduce(loss, group=self.ps.sp_group)
+            loss /= self.sp_world
+        return loss
+
     def _forward_micro(self, batch, act):
-        tokens, labels = batch
+        tokens, labels = self._sp_slice(*batch)
         b, s = tokens.shape
         last = self.stage == self.pp_world - 1
         self._set_drop_seed()
@@ -293,6 +319,7 @@ class TrainEngine:
             loss = loss / scale
         if self.pp_world > 1:  # make the loss visible on every stage (for logging)
             dist.broadcast(loss, src=self.ps.pp_ranks[-1], group=self.ps.pp_group)
+        loss = self._sp_mean(loss)
         self.last_loss = loss
         return loss
 
@@ -359,6 +386,7 @@ class TrainEngine:
             if self.expert_optimizer is not None:
                 self.expert_optimizer.zero_grad()
         self._set_drop_seed()
+        tokens, labels = self._sp_slice(tokens, labels)
         return self.model(tokens=tokens, labels=labels)
 
     def backward(self, loss: torch.Tensor) -> torch.Tensor:
@@ -391,7 +419,7 @@ class TrainEngine:
     def _eval_micro_batches(self, batches, num_micro_batches):
         with torch.no_grad():
             if self.pp_world == 1:
-                losses = [self.model(tokens=t, labels=l) for t, l in batches]
+                losses = [self.model(tokens=t, labels=l) for t, l in (self._sp_slice(*b) for b in batches)]
             else:
                 seq = batches[0][0].shape[1]
                 losses = PP.run_forward_only(self.stage, self.pp_world, num_micro_batches,
@@ -399,7 +427,7 @@ class TrainEngine:
             loss = torch.stack(losses).mean() if losses else torch.zeros((), device=self.device)
             if self.pp_world > 1:
                 dist.broadcast(loss, src=self.ps.pp_ranks[-1], group=self.ps.pp_group)
-        return loss
+        return self._sp_mean(loss)
 
     def _tied_slice(self, t):
         """Stage 0 keeps the whole (replicated) embedding table, the last stage a vocab-parallel

@@ -180,6 +180,7 @@ class TransformerLayer(nn.Module):
                  fused_moe: bool = True):
         super().__init__()
         self.cfg, self.tp, self.layer_idx = cfg, tp, layer_idx
+        self.ulysses_group = None      # set by the engine (`sequence_parallel_size` > 1)
         self.is_moe = cfg.num_experts > 0 and (layer_idx + 1) % cfg.moe_every == 0
         d = cfg.head_dim
         assert cfg.heads % tp.world == 0 and cfg.kv_heads % tp.world == 0 and cfg.ffn % tp.world == 0
@@ -240,8 +241,15 @@ class TransformerLayer(nn.Module):
         seed = drop_seed + 2 * self.layer_idx
         y = N.norm(h, self.ln1_w, self.ln1_b, eps=cfg.eps, rms=rms)
         qkv = tp.column_linear(y, self.wqkv, self.bqkv)              # [s*b, (h+2kv)*d] full sequence
-        o = qkv_attention(qkv.view(seq, batch, self.h_local + 2 * self.kv_local, d), self.h_local,
-                          self.kv_local, True, 1.0 / math.sqrt(d), rope_tables, kv_lens)
+        if self.ulysses_group is not None:     # this rank holds a sequence slice: regroup to whole sequences of fewer heads
+            from ..parallel.ulysses import ulysses_qkv_attention
+
+            o = ulysses_qkv_attention(qkv.view(seq, batch, self.h_local + 2 * self.kv_local, d), self.h_local,
+                                      self.kv_local, True, 1.0 / math.sqrt(d), self.ulysses_group, qkv_attention,
+                                      rope_tables, kv_lens)
+        else:
+            o = qkv_attention(qkv.view(seq, batch, self.h_local + 2 * self.kv_local, d), self.h_local,
+                              self.kv_local, True, 1.0 / math.sqrt(d), rope_tables, kv_lens)
         if p > 0:      # --hidden-dropout: the residual add moves out of the GEMM epilogue, behind the mask
             h = self._dropout_add(tp.row_linear(o, self.wo, self.bo), h, p, seed)
         else:
@@ -277,6 +285,7 @@ class Embedding(nn.Module):
         super().__init__()
         self.cfg, self.tp = cfg, tp
         self.grad_scale = 1.0      # see GPTModel: tied table under tensor parallelism
+        self.pos_offset = 0        # first position of this rank's sequence slice (Ulysses)
         kw = dict(dtype=dtype, device=device)
         self.wte = nn.Parameter(torch.empty(cfg.vocab_size, cfg.hidden, **kw).normal_(0, cfg.init_std))
         if cfg.learned_pos:
@@ -291,7 +300,7 @@ class Embedding(nn.Module):
         if self.grad_scale != 1.0:
             x = _ScaleGrad.apply(x, self.grad_scale)
         if self.wpe is not None:
-            x = x + self.wpe[:s].unsqueeze(1)
+            x = x + self.wpe[self.pos_offset:self.pos_offset + s].unsqueeze(1)
         return self.tp.scatter_sequence(x.view(s * b, self.cfg.hidden))
 
 
@@ -362,6 +371,7 @@ class GPTModel(nn.Module):
         else:
             self.head = None
         self.recompute = False
+        self.seq_mult = 1        # Ulysses: rotary tables cover the whole sequence, `seq` is this rank's slice
         self.drop_seed = 0       # set per micro-batch by the engine, so a recomputed forward draws the same masks
 
     def _rope(self, seq, device):
@@ -377,7 +387,7 @@ class GPTModel(nn.Module):
             h = self.embed(tokens)
         else:
             h = hidden
-        rope = self._rope(seq, h.device)
+        rope = self._rope(seq * self.seq_mult, h.device)
         drop = self.cfg.dropout if self.training else 0.0
         seed = int(self.drop_seed)
         if drop > 0 and self.embed is not None:      # Megatron applies the hidden dropout to the embeddings too

@@ -24,10 +24,12 @@ class Topology:
     tp: int = 1
     pp: int = 1
     ep: int = 1
+    sp: int = 1      # DeepSpeed-Ulysses sequence-parallel size, carved out of the data-parallel dimension
 
     def __post_init__(self):
         assert self.world % (self.tp * self.pp) == 0, "world must be divisible by tp*pp"
         assert self.dp % self.ep == 0, "expert parallel size must divide the data-parallel size"
+        assert self.dp % self.sp == 0, "sequence parallel size must divide the data-parallel size"
 
     @property
     def dp(self) -> int:
@@ -65,6 +67,15 @@ class Topology:
                 out.append(g[i:i + self.ep])
         return out
 
+    def sp_groups(self) -> list[list[int]]:
+        """Ulysses groups: consecutive blocks of `sp` data-parallel ranks; they share every micro-batch and split
+        its sequence.  For gradient reduction they stay ordinary data-parallel ranks."""
+        out = []
+        for g in self.dp_groups():
+            for i in range(0, len(g), self.sp):
+                out.append(g[i:i + self.sp])
+        return out
+
     def expert_dp_groups(self) -> list[list[int]]:
         """Ranks holding the same expert shard: stride `ep` through each DP group."""
         out = []
@@ -86,7 +97,8 @@ class Topology:
         raise ValueError(f"rank {rank} is in no group")
 
     def describe(self) -> str:
-        return f"tp{self.tp}pp{self.pp}dp{self.dp}" + (f"ep{self.ep}" if self.ep > 1 else "")
+        return f"tp{self.tp}pp{self.pp}dp{self.dp}" + (f"ep{self.ep}" if self.ep > 1 else "") + (
+            f"sp{self.sp}" if self.sp > 1 else "")
 
 
 class ParallelState:
@@ -96,17 +108,19 @@ class ParallelState:
         self.topo, self.rank = topo, rank
         self.tp_rank, self.dp_rank, self.pp_rank = topo.coords(rank)
         self.tp_group = self.dp_group = self.pp_group = self.ep_group = None
-        self.expert_dp_group = self.embedding_group = None
+        self.expert_dp_group = self.embedding_group = self.sp_group = None
+        self.sp_ranks = topo.group_containing(topo.sp_groups(), rank)
+        self.sp_rank = self.sp_ranks.index(rank)
         self.tp_ranks = topo.group_containing(topo.tp_groups(), rank)
         self.dp_ranks = topo.group_containing(topo.dp_groups(), rank)
         self.pp_ranks = topo.group_containing(topo.pp_groups(), rank)
         self.ep_ranks = topo.group_containing(topo.ep_groups(), rank)
 
     @classmethod
-    def initialize(cls, tp: int = 1, pp: int = 1, ep: int = 1) -> "ParallelState":
+    def initialize(cls, tp: int = 1, pp: int = 1, ep: int = 1, sp: int = 1) -> "ParallelState":
         """Create every group (all ranks must call; new_group is collective)."""
         assert dist.is_initialized()
-        topo = Topology(dist.get_world_size(), tp, pp, ep)
+        topo = Topology(dist.get_world_size(), tp, pp, ep, sp)
         st = cls(topo, dist.get_rank())
 
         def make(groups, mine_attr):
@@ -121,6 +135,8 @@ class ParallelState:
         if ep > 1:
             make(topo.ep_groups(), "ep_group")
             make(topo.expert_dp_groups(), "expert_dp_group")
+        if sp > 1:
+            make(topo.sp_groups(), "sp_group")
         make(topo.embedding_groups(), "embedding_group")
         return st
 

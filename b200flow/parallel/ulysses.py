@@ -94,3 +94,38 @@ def ulysses_attention(q, k, v, group=None, causal: bool = True, scale: float | N
     vh = _SeqToHeads.apply(v, group)
     oh = A.flash_attention(qh, kh, vh, causal=causal, scale=scale)
     return _HeadsToSeq.apply(oh.contiguous(), group)
+
+
+class _AllToAll(torch.autograd.Function):
+    """Chunk r of the leading dimension goes to rank r; the gradient takes the same route back."""
+
+    @staticmethod
+    def forward(ctx, x, group):
+        ctx.group = group
+        return _all_to_all(x.contiguous(), group)
+
+    @staticmethod
+    def backward(ctx, g):
+        return _all_to_all(g.contiguous(), ctx.group), None
+
+
+def ulysses_qkv_attention(qkv, heads: int, kv_heads: int, causal: bool, scale: float, group, attention_fn,
+                          rope_tables=None, kv_lens=None):
+    """The engine's form of DeepSpeed-Ulysses (`--ds-sequence-parallel-size`).
+
+    qkv: this rank's sequence slice of the fused projection, `[s/P, b, heads + 2 kv_heads, d]` (sequence-major,
+    slice r = positions r s/P ...).  One all-to-all regroups it to the whole sequence of `heads/P + 2 kv_heads/P`
+    heads — still the packed layout, so the ordinary fused RoPE + flash-attention node (`attention_fn`) runs on it
+    unchanged, with positions counted over the full sequence — and a second one brings the output back to
+    `[s/P * b, heads * d]`."""
+    P = dist.get_world_size(group)
+    sl, b, _, d = qkv.shape
+    assert heads % P == 0 and kv_heads % P == 0, "query and key/value heads must divide by the sequence-parallel size"
+    hl, kl = heads // P, kv_heads // P
+    q, k, v = qkv[:, :, :heads], qkv[:, :, heads:heads + kv_heads], qkv[:, :, heads + kv_heads:]
+    send = torch.cat([q.reshape(sl, b, P, hl, d), k.reshape(sl, b, P, kl, d), v.reshape(sl, b, P, kl, d)], dim=3)
+    recv = _AllToAll.apply(send.permute(2, 0, 1, 3, 4), group)                 # [P (sequence slice), s/P, b, nh/P, d]
+    full = recv.reshape(P * sl, b, hl + 2 * kl, d)
+    o = attention_fn(full, hl, kl, causal, scale, rope_tables, kv_lens)          # [s * b, hl * d]
+    back = _AllToAll.apply(o.reshape(P, sl, b, hl, d), group)                    # [P (head group), s/P, b, hl, d]
+    return back.permute(1, 2, 0, 3, 4).reshape(sl * b, heads * d)

@@ -57,7 +57,7 @@ def parse_args():
     a("--exit-interval", type=int, default=None)
     a("--tensor-model-parallel-size", type=int, default=1)
     a("--pipeline-model-parallel-size", type=int, default=1)
-    a("--sequence-parallel", action="store_true")
+    a("--sequence-parallel", action="store_true"); a("--ds-sequence-parallel-size", type=int, default=1)
     a("--swiglu", action="store_true"); a("--normalization", default="layernorm")
     a("--use-rotary-position-embeddings", action="store_true")
     a("--untie-embeddings-and-output-weights", action="store_true")
@@ -103,8 +103,9 @@ def main():
     tp, pp = args.tensor_model_parallel_size, args.pipeline_model_parallel_size
     n_experts = max(args.num_experts)
     ep = min(args.moe_expert_parallel_size, world // (tp * pp)) if n_experts > 1 else 1
-    ps = ParallelState.initialize(tp=tp, pp=pp, ep=ep) if world > 1 else None
-    dp = world // (tp * pp)
+    usp = args.ds_sequence_parallel_size        # DeepSpeed-Ulysses: ranks of a group share the micro-batches
+    ps = ParallelState.initialize(tp=tp, pp=pp, ep=ep, sp=usp) if world > 1 else None
+    dp = world // (tp * pp * usp)                # replicas that read different samples
     ds = json.load(open(args.deepspeed_config)) if args.deepspeed_config else {}
     micro = int(ds.get("train_micro_batch_size_per_gpu", args.micro_batch_size))
     gas = int(ds.get("gradient_accumulation_steps", 1))
@@ -186,7 +187,7 @@ def main():
     train_ds, valid_ds, _ = build_train_valid_test_blended(data_path, args.split, args.seq_length,
                                                            (train_iters * gbs, max(n_eval, gbs), 0), args.seed,
                                                            args.data_cache_path)
-    dp_rank = ps.dp_rank if ps else 0
+    dp_rank = (ps.dp_rank // usp) if ps else 0
 
     def batches(dataset, start_step):
         step = start_step

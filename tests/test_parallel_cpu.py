@@ -337,3 +337,71 @@ def test_horovod_autotune_replans_buckets_and_keeps_gradients_right(tmp_path):
     assert sum(int(r.split(",")[2]) for r in rows[1:]) == 1
     ev = json.loads((tmp_path / "timeline.json").read_text())["traceEvents"]
     assert ev and all(e["name"] == "allreduce" and e["args"]["bytes"] > 0 for e in ev)
+
+
+def _ulysses_engine_worker(rank, world, sp, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    ps = None
+    if world > 1:
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        from b200flow.parallel.groups import ParallelState
+
+        ps = ParallelState.initialize(tp=1, pp=1, sp=sp)
+    torch.set_num_threads(1)
+    from b200flow.engines.ds_engine import initialize
+    from b200flow.models.gpt import GPTModel, config_from_preset
+
+    results = {}
+    for preset, kw in (("llama-tiny", dict(kv_heads=2)), ("gpt2-tiny", {})):     # RoPE + GQA; learned positions + biases
+        cfg = config_from_preset(preset, hidden=64, heads=4, ffn=128, layers=2, vocab_size=128, max_seq=32, **kw)
+        dp_data = world // sp                                                     # replicas that see different data
+        eng = initialize(cfg, {"train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": 4 // dp_data,
+                               "optimizer": {"params": {"lr": 2e-3, "weight_decay": 0.0}}}, ps,
+                         device=torch.device("cpu"), seed=3)
+        torch.manual_seed(55)
+        full = GPTModel(cfg, dtype=torch.float32, device=torch.device("cpu")).state_dict()
+        with torch.no_grad():
+            for name, p in eng.model.named_parameters():
+                p.copy_(full[name])
+        o = eng.optimizer
+        o.master.copy_(eng.flat.params[o.lo:o.hi].float())
+        g = torch.Generator().manual_seed(0)
+        mbs = [torch.randint(0, cfg.vocab_size, (2, 33), generator=g) for _ in range(4)]
+        data_rank = (ps.dp_rank // sp) if ps else 0
+        mine = mbs[data_rank::dp_data]
+        it = itertools.cycle([(t[:, :-1].contiguous(), t[:, 1:].contiguous()) for t in mine])
+        losses = []
+        for _ in range(3):
+            loss = eng.train_batch(it).clone()
+            if ps is not None and dp_data > 1:
+                dist.all_reduce(loss, group=ps.dp_group)
+                loss /= world
+            losses.append(float(loss))
+        ev = float(eng.eval_batch(itertools.cycle([(mbs[0][:, :-1].contiguous(), mbs[0][:, 1:].contiguous())])))
+        results[preset] = (losses, ev)
+    if rank == 0:
+        q.put(results)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def test_ulysses_sequence_parallel_engine_matches_single_process():
+    """`sequence_parallel_size` (DeepSpeed-Ulysses) through the engine: SP 2 alone and SP 2 x DP 2 reproduce the
+    single-process loss curve and evaluation loss, for a RoPE / GQA model and for one with learned positions."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    _ulysses_engine_worker(0, 1, 1, 29621, q)
+    want = q.get()
+    for world, sp, port in ((2, 2, 29622), (4, 2, 29623)):
+        procs = [ctx.Process(target=_ulysses_engine_worker, args=(r, world, sp, port, q)) for r in range(world)]
+        for p in procs:
+            p.start()
+        got = q.get(timeout=300)
+        for p in procs:
+            p.join(timeout=120)
+            assert p.exitcode == 0
+        for preset in want:
+            for a, b in zip(got[preset][0], want[preset][0]):
+                assert abs(a - b) < 2e-3, (world, sp, preset, got[preset], want[preset])
+            assert abs(got[preset][1] - want[preset][1]) < 2e-3

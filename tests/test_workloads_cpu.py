@@ -95,6 +95,18 @@ def test_megatron_moe_flags_top2_expert_parallel(tmp_root):
     assert "expp_rank_0_mp_rank_00_optim_states.pt" in names and "expp_rank_1_mp_rank_00_optim_states.pt" in names
 
 
+def test_megatron_ulysses_sequence_parallel_flag(tmp_root):
+    """`--ds-sequence-parallel-size 2` (DeepSpeed-Ulysses of the pinned Megatron-DeepSpeed) on the DP + ZeRO-1 values
+    file: 4 ranks = 2 replicas x 2 sequence slices; the global batch counts replicas, not ranks."""
+    values = EX / "megatron-deepspeed/gpt2_345m/pretrain-ddp-zero1.yaml"
+    env = {"B2F_TRAIN_ITERS": "4", "B2F_OVERRIDE_ARGS": TINY_GPT + " --ds-sequence-parallel-size 2"}
+    rc, st, logs = _install("mds-sp", "pytorchjob-distributed", values, tmp_root,
+                            ["resources.nnodes=1", "resources.nproc_per_node=4"], env)
+    assert rc == 0 and st["phase"] == "Succeeded", logs[-3000:]
+    assert "iteration        4/       4" in logs and "unknown arguments" not in logs, logs[-3000:]
+    assert "global batch size:     8" in logs          # ds_config micro batch 4 x 2 replicas (4 ranks / SP 2)
+
+
 def test_wikicorpus_preprocess_then_ddp_zero1_pipeline(tmp_root):
     """KFP-style pipeline: data-process(wikicorpus) then pytorchjob-distributed (W4 -> W2)."""
     from b200flow.jobspec.values import load_yaml
