@@ -33,8 +33,8 @@ def _build(tp, pp, world, rank):
     from b200flow.models.gpt import config_from_preset
     from b200flow.parallel.groups import ParallelState
 
-    cfg = config_from_preset("llama-tiny", hidden=64, heads=4, ffn=128, layers=4, vocab_size=128,
-                             max_seq=32)
+    cfg = config_from_preset("llama-tiny", hidden=64, heads=4, ffn=128,
+                             layers=int(os.environ.get("B2F_TEST_LAYERS", 4)), vocab_size=128, max_seq=32)
     ps = ParallelState.initialize(tp=tp, pp=pp) if world > 1 else None
     dp = world // (tp * pp)
     eng = initialize(cfg, {"train_micro_batch_size_per_gpu": 2,
@@ -157,6 +157,16 @@ def test_tp_without_sequence_parallel_matches_single_process(single, monkeypatch
         got = _run(world, tp, pp, port)
         for a, b in zip(got, single):
             assert abs(a - b) < 2e-3, (world, got, single)
+
+
+def test_uneven_pipeline_split_matches_single_process(monkeypatch):
+    """3 layers over 2 stages (2 + 1, DeepSpeed's uniform partition with a remainder) and 5 layers over TP2 x PP2."""
+    for layers, world, tp, pp, port in ((3, 2, 1, 2, 29624), (5, 4, 2, 2, 29626)):
+        monkeypatch.setenv("B2F_TEST_LAYERS", str(layers))
+        want = _run(1, 1, 1, port)
+        got = _run(world, tp, pp, port + 1)
+        for a, b in zip(got, want):
+            assert abs(a - b) < 2e-3, (layers, got, want)
 
 
 def test_topology_rank_order_tp_fastest():
