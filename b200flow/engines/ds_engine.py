@@ -503,6 +503,33 @@ class TrainEngine:
 
         return load_checkpoint(self, load_dir, tag, load_optimizer_states, load_rng, finetune)
 
+    # ----------------------------------------------------- DeepSpeed accessors
+    @property
+    def module(self):
+        return self.model
+
+    def get_lr(self) -> list[float]:
+        return [self.optimizer.lr]
+
+    def get_global_grad_norm(self) -> float:
+        return self.grad_norm()
+
+    def train_micro_batch_size_per_gpu(self) -> int:
+        return self.micro_batch
+
+    def gradient_accumulation_steps(self) -> int:
+        return self.gas
+
+    def train_batch_size(self) -> int:
+        return self.micro_batch * self.gas * (self.dp_world // self.sp_world)
+
+    def train(self, mode: bool = True):
+        self.model.train(mode)
+        return self
+
+    def eval(self):
+        return self.train(False)
+
     def grad_norm(self) -> float:
         g = self.optimizer.last_grad_norm
         return float(g.item()) if g is not None else float("nan")
@@ -512,3 +539,11 @@ def initialize(model_config: GPTConfig | None = None, config: dict | None = None
                parallel: ParallelState | None = None, **kw) -> TrainEngine:
     """DeepSpeed-style entry point (`deepspeed.initialize`)."""
     return TrainEngine(model_config, config or {}, parallel, **kw)
+
+
+def initialize_tuple(model_config: GPTConfig | None = None, config: dict | None = None,
+                     parallel: ParallelState | None = None, **kw):
+    """`engine, optimizer, dataloader, lr_scheduler = deepspeed.initialize(...)`: the four-tuple form scripts
+    unpack (the data loader is the caller's; the schedule lives in the engine)."""
+    eng = initialize(model_config, config, parallel, **kw)
+    return eng, eng.optimizer, None, eng

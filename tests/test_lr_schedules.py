@@ -70,3 +70,17 @@ def test_train_batch_size_rule_of_the_ds_config():
     assert (e.micro_batch, e.gas) == (2, 4)
     with pytest.raises(ValueError, match="train_batch_size"):
         mk({"train_batch_size": 10, "train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": 4})
+
+
+def test_deepspeed_accessors_and_tuple_form():
+    import torch
+
+    from b200flow.engines.ds_engine import initialize_tuple
+    from b200flow.models.gpt import config_from_preset
+
+    cfg = config_from_preset("llama-tiny", hidden=64, heads=4, ffn=128, layers=2, vocab_size=128, max_seq=32)
+    eng, opt, loader, sched = initialize_tuple(cfg, {"train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": 3,
+                                                      "optimizer": {"params": {"lr": 1e-3}}}, device=torch.device("cpu"))
+    assert opt is eng.optimizer and loader is None and sched.get_lr() == [1e-3]
+    assert (eng.train_micro_batch_size_per_gpu(), eng.gradient_accumulation_steps(), eng.train_batch_size()) == (2, 3, 6)
+    assert eng.module is eng.model and eng.eval().model.training is False and eng.train().model.training is True
