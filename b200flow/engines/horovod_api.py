@@ -90,6 +90,97 @@ def broadcast(tensor: torch.Tensor, root_rank: int = 0, name: str | None = None)
     return out
 
 
+def allreduce_(tensor: torch.Tensor, op: str = Average, name: str | None = None) -> torch.Tensor:
+    """In-place form of `allreduce`."""
+    tensor.copy_(allreduce(tensor, op))
+    return tensor
+
+
+def alltoall(tensor: torch.Tensor, splits=None, name: str | None = None) -> torch.Tensor:
+    """Equal splits along dim 0: chunk r goes to rank r (gloo: through an all-gather)."""
+    n = size()
+    if n == 1:
+        return tensor.clone()
+    assert splits is None and tensor.shape[0] % n == 0, "alltoall: equal splits along dim 0"
+    if tensor.is_cuda:
+        out = torch.empty_like(tensor)
+        dist.all_to_all_single(out, tensor.contiguous())
+        return out
+    everyone = [torch.empty_like(tensor) for _ in range(n)]
+    dist.all_gather(everyone, tensor.contiguous())
+    k = tensor.shape[0] // n
+    return torch.cat([everyone[r][rank() * k:(rank() + 1) * k] for r in range(n)], 0)
+
+
+def reducescatter(tensor: torch.Tensor, op: str = Average, name: str | None = None) -> torch.Tensor:
+    """Rank r keeps rows r of the reduced tensor (dim 0 split evenly)."""
+    n = size()
+    if n == 1:
+        return tensor.clone()
+    full = allreduce(tensor, op)
+    k = tensor.shape[0] // n
+    return full[rank() * k:(rank() + 1) * k].clone()
+
+
+def barrier() -> None:
+    if size() > 1:
+        dist.barrier()
+
+
+def join() -> int:
+    """Ranks that ran out of data wait here for the others; returns the last rank to join (here: the last rank)."""
+    barrier()
+    return size() - 1
+
+
+def broadcast_object(obj, root_rank: int = 0, name: str | None = None):
+    if size() == 1:
+        return obj
+    box = [obj]
+    dist.broadcast_object_list(box, src=root_rank)
+    return box[0]
+
+
+def allgather_object(obj, name: str | None = None) -> list:
+    if size() == 1:
+        return [obj]
+    out = [None] * size()
+    dist.all_gather_object(out, obj)
+    return out
+
+
+def cross_rank() -> int:
+    """Node index (one box: always 0) and number of nodes, as Horovod reports them."""
+    return 0
+
+
+def cross_size() -> int:
+    return 1
+
+
+def nccl_built() -> bool:
+    return torch.cuda.is_available()
+
+
+def mpi_built() -> bool:
+    return False            # ranks come from the launcher's mpirun mode, there is no MPI control plane
+
+
+def gloo_built() -> bool:
+    return True
+
+
+def is_homogeneous() -> bool:
+    return True
+
+
+class Compression:
+    """`hvd.Compression.none / fp16`: gradient compression for the all-reduce.  The flat fp32 gradient buffer is
+    reduced in place by K1, so `fp16` is accepted and means the same as `none`."""
+    none = "none"
+    fp16 = "fp16"
+
+
 def broadcast_parameters(params, root_rank: int = 0) -> None:
     """`hvd.broadcast_parameters(model.state_dict(), root_rank=0)` — start every rank from rank 0's weights."""
     if size() == 1:
@@ -115,8 +206,10 @@ class _DistributedOptimizer:
     backward (pass `ddp=`); otherwise every gradient is all-reduced here (one flat collective per dtype:
     the fusion buffer)."""
 
-    def __init__(self, optimizer, named_parameters=None, ddp=None, op: str = Average):
+    def __init__(self, optimizer, named_parameters=None, ddp=None, op: str = Average,
+                 backward_passes_per_step: int = 1):
         self.optimizer, self.ddp, self.op = optimizer, ddp, op
+        self.passes, self._seen = max(1, int(backward_passes_per_step)), 0
         self.params = [p for _, p in named_parameters] if named_parameters is not None else [
             p for g in optimizer.param_groups for p in g["params"]]
 
@@ -145,10 +238,17 @@ class _DistributedOptimizer:
                 off += g.numel()
 
     def step(self, closure=None):
+        """With `backward_passes_per_step` = k the gradients of k backward passes are accumulated locally and
+        reduced once: only every k-th call reduces and updates."""
+        self._seen += 1
+        if self._seen % self.passes:
+            return None
         self.synchronize()
         return self.optimizer.step(closure) if closure is not None else self.optimizer.step()
 
     def zero_grad(self, *a, **kw):
+        if self._seen % self.passes:
+            return None            # inside an accumulation window the gradients are kept
         return self.optimizer.zero_grad(*a, **kw)
 
     def state_dict(self):
@@ -196,5 +296,6 @@ def make_ddp(module, env=None, **kw):
     return ddp, tuner
 
 
-def DistributedOptimizer(optimizer, named_parameters=None, ddp=None, op: str = Average, **_ignored):
-    return _DistributedOptimizer(optimizer, named_parameters, ddp, op)
+def DistributedOptimizer(optimizer, named_parameters=None, ddp=None, op: str = Average,
+                         backward_passes_per_step: int = 1, compression=Compression.none, **_ignored):
+    return _DistributedOptimizer(optimizer, named_parameters, ddp, op, backward_passes_per_step)

@@ -266,7 +266,27 @@ def _hvd_worker(rank, world, port, q_out):
     opt.step()
     avg = hvd.allreduce(g_local)                     # what every rank should have applied
     ok = torch.allclose(model.weight.detach(), w0 - 0.1 * avg, atol=1e-6)
-    q_out.put((rank, hvd.size(), bool(ok), float(hvd.allreduce(torch.tensor([float(rank)]), op=hvd.Sum))))
+    # the smaller calls of the API
+    a2a = hvd.alltoall(torch.arange(4.0) + 10 * rank)                      # rank r receives chunk r of everyone
+    rs = hvd.reducescatter(torch.arange(4.0) * (rank + 1), op=hvd.Sum)
+    objs = hvd.allgather_object({"rank": rank})
+    extras = (a2a.tolist() == [2.0 * rank, 2.0 * rank + 1, 10 + 2.0 * rank, 11 + 2.0 * rank]
+              and rs.tolist() == [(2 * rank) * 3.0, (2 * rank + 1) * 3.0]
+              and [o["rank"] for o in objs] == [0, 1] and hvd.broadcast_object("x" * (rank + 1), 1) == "xx"
+              and hvd.cross_size() == 1 and hvd.join() == 1 and hvd.is_homogeneous())
+    # backward_passes_per_step = 2: two local backward passes, one reduction + update
+    m2 = torch.nn.Linear(2, 1, bias=False)
+    with torch.no_grad():
+        m2.weight.fill_(1.0)
+    o2 = hvd.DistributedOptimizer(torch.optim.SGD(m2.parameters(), lr=1.0), named_parameters=m2.named_parameters(),
+                                  backward_passes_per_step=2, compression=hvd.Compression.fp16)
+    for k in range(2):
+        m2(torch.full((1, 2), float(rank + 1))).sum().backward()
+        o2.step()
+        o2.zero_grad()
+    # each rank accumulated 2 x (rank + 1); the average over ranks is 3 -> weight 1 - 3
+    extras = extras and torch.allclose(m2.weight.detach(), torch.full((1, 2), -2.0))
+    q_out.put((rank, hvd.size(), bool(ok and extras), float(hvd.allreduce(torch.tensor([float(rank)]), op=hvd.Sum))))
     hvd.shutdown()
 
 
