@@ -110,7 +110,11 @@ def main():
         total_epochs = sched[-1][0]
         boundaries = [e * 120000 // 8 for e, _ in sched[:-1]]
     else:
-        boundaries = list(cfgd.get("TRAIN.LR_SCHEDULE", [240000, 320000, 360000]))
+        sched = cfgd.get("TRAIN.LR_SCHEDULE", [240000, 320000, 360000])
+        if isinstance(sched, str) and sched.endswith("x"):      # tensorpack's "1x" / "2x" ... = multiples of 90k steps
+            mult = float(sched[:-1])
+            sched = [int(120000 * mult), int(160000 * mult), int(180000 * mult)]
+        boundaries = list(sched)
         total_epochs = max(1, int(boundaries[-1] * 8 / (world * batch)) // max(1, steps_per_epoch))
         boundaries = boundaries[:-1]
     total_epochs = int(os.environ.get("B2F_MRCNN_EPOCHS", total_epochs))
@@ -164,6 +168,15 @@ def main():
         step = sd["global_step"]
         if rank == 0:
             print(f"[b200flow] resumed from {name} (step {step})", flush=True)
+    elif args.load:          # --load <model-N.pt | logdir>: initial weights only (tensorpack's `--load`), step stays 0
+        src = Path(args.load)
+        if src.is_dir():
+            src = src / (json.loads((src / "checkpoint").read_text())["model_checkpoint_path"] + ".pt")
+        sd = torch.load(src, map_location="cpu", weights_only=False)
+        model.load_state_dict(sd["model"] if "model" in sd else sd)
+        opt.master.copy_(flat.params.float())          # the fp32 master copy follows the loaded weights
+        if rank == 0:
+            print(f"[b200flow] initial weights from {src}", flush=True)
     warmup = int(cfgd.get("TRAIN.WARMUP", min(1000, steps_per_epoch)))
     ckpt_period = int(cfgd.get("TRAIN.CHECKPOINT_PERIOD", 1))
     eval_period = int(cfgd.get("TRAIN.EVAL_PERIOD", 1))

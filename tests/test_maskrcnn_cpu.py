@@ -151,6 +151,11 @@ def test_faster_rcnn_mode_without_mask_head(tmp_path):
     out = res.stdout + res.stderr
     assert res.returncode == 0, out[-2000:]
     assert "mAP(bbox)/IoU=0.5:0.95" in out and "mAP(segm)" not in out and "mask" not in out.split("[epoch 1]")[1].split("|")[1]
+    again = subprocess.run([sys.executable, "-m", "b200flow.workloads.maskrcnn.train", "--logdir", str(tmp_path / "log2"),
+                            "--load", str(tmp_path / "log"), "--config", "MODE_MASK=False", "TRAIN.LR_SCHEDULE=1x"],
+                           cwd=REPO, env=env, capture_output=True, text=True, timeout=600)
+    assert again.returncode == 0 and "initial weights from" in again.stdout and "resumed from" not in again.stdout, \
+        (again.stdout + again.stderr)[-2000:]
     refused = subprocess.run([sys.executable, "-m", "b200flow.workloads.maskrcnn.train", "--logdir", str(tmp_path / "c4"),
                               "--config", "MODE_FPN=False"], cwd=REPO, env=env, capture_output=True, text=True, timeout=600)
     assert refused.returncode != 0 and "MODE_FPN=False" in refused.stderr
