@@ -112,12 +112,32 @@ def test_training_reads_the_coco_tree_written_by_the_coco_data_chart(tmp_root):
     t = tmp_root / "train.yaml"
     t.write_text("maskrcnn:\n  gpus: 2\n  gpu_nodes: 1\n  gpus_per_node: 2\n  steps_per_epoch: 2\n"
                  "  lr_schedule: \"[4,6,8]\"\n")
-    rc, st, out = _install("mrcnn-coco", "maskrcnn", t, tmp_root, dict(TINY, B2F_MRCNN_EPOCHS="1", B2F_DATA_WORKERS="2"))
+    rc, st, out = _install("mrcnn-coco", "maskrcnn", t, tmp_root, dict(TINY, B2F_MRCNN_EPOCHS="2", B2F_DATA_WORKERS="2"))
     logs = "\n".join(p.read_text(errors="replace") for p in
                      (tmp_root / ".b200flow/releases/mrcnn-coco/pods").glob("*/stdout.log"))
     assert rc == 0 and st["phase"] == "Succeeded", logs[-3000:]
     assert "16 training images, 4 validation images" in logs and "mAP(segm)/IoU=0.5:0.95" in logs
     assert "BACKBONE.WEIGHTS" not in logs or "placeholder" in logs
+    # tensorpack's predict.py modes on the checkpoint just written: COCO results file + metrics, and a rendered image
+    import subprocess
+
+    logdir = next((tmp_root / "fsx/logs").iterdir())
+    env = dict(os.environ, **TINY, PYTHONPATH=str(REPO))
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        env.pop(k, None)
+    res = subprocess.run([sys.executable, "-m", "b200flow.workloads.maskrcnn.predict", "--load", str(logdir),
+                          "--evaluate", str(tmp_root / "out" / "results.json"), "--image-size", "96x128",
+                          "--score-thresh", "0.0", "--config", f"DATA.BASEDIR={base}", 'DATA.VAL=("coco_val2017")',
+                          "--predict", str(base / "val2017" / "000000000000.pt"), "--out", str(tmp_root / "out")],
+                         cwd=REPO, env=env, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, (res.stdout + res.stderr)[-3000:]
+    assert "mAP(bbox)/IoU=0.5:0.95" in res.stdout and "mAP(segm)/IoU=0.5" in res.stdout
+    results = json.loads((tmp_root / "out" / "results.json").read_text())
+    assert results and {"image_id", "category_id", "bbox", "score", "segmentation"} <= set(results[0])
+    r0 = results[0]
+    assert r0["segmentation"]["size"] == [128, 160] and sum(r0["segmentation"]["counts"]) == 128 * 160
+    assert 1 <= r0["category_id"] <= 80 and len(r0["bbox"]) == 4 and r0["bbox"][2] > 0
+    assert (tmp_root / "out" / "000000000000.png").read_bytes()[:8] == b"\x89PNG\r\n\x1a\n"
 
 
 def test_stock_library_twin_of_maskrcnn_builds_and_steps_on_cpu():
