@@ -149,10 +149,16 @@ def save_checkpoint(engine, save_dir: str, tag: str | None = None, client_state:
                async_save)
     if dist.is_initialized():
         dist.barrier()
-    if (not dist.is_initialized()) or dist.get_rank() == 0:
-        wait_for_pending_saves() if not async_save else None
-        (Path(save_dir) / "latest").write_text(tag)
-        (Path(save_dir) / "latest_checkpointed_iteration.txt").write_text(str(step))
+    # Every rank names the checkpoint in ITS save directory: the reference's examples save to
+    # `$CKPT_ROOT/$PET_NODE_RANK`, one directory per node, and a node without `latest` could not resume.
+    # Same content from every writer, put in place by a rename.
+    import os
+
+    wait_for_pending_saves() if not async_save else None
+    for name, text in (("latest", tag), ("latest_checkpointed_iteration.txt", str(step))):
+        tmp = Path(save_dir) / f".{name}.{os.getpid()}.tmp"
+        tmp.write_text(text)
+        os.replace(tmp, Path(save_dir) / name)
     return str(d)
 
 

@@ -95,6 +95,35 @@ def test_megatron_moe_flags_top2_expert_parallel(tmp_root):
     assert "expp_rank_0_mp_rank_00_optim_states.pt" in names and "expp_rank_1_mp_rank_00_optim_states.pt" in names
 
 
+def test_llama_flags_on_the_tp2_pp2_dp2_topology(tmp_root):
+    """BASELINE.json config 4 at test size: Llama architecture flags of the pinned Megatron-DeepSpeed (SwiGLU, RMSNorm,
+    rotary positions, untied output layer, no biases, grouped-query attention) with TP2 x PP2 x DP2, ZeRO-1, sequence
+    parallelism and bf16, through the unchanged TP / PP values file on 8 ranks."""
+    values = EX / "megatron-deepspeed/gpt2_345m/pretrain-ddp-tp-pp-zero1.yaml"
+    llama = (" --swiglu --normalization rmsnorm --use-rotary-position-embeddings --untie-embeddings-and-output-weights"
+             " --disable-bias-linear --num-key-value-heads 2 --ffn-hidden-size 128 --sequence-parallel --bf16"
+             " --hidden-dropout 0 --attention-dropout 0 --global-batch-size 16")
+    env = {"B2F_TRAIN_ITERS": "4", "B2F_OVERRIDE_ARGS": TINY_GPT + llama}
+    rc, st, logs = _install("llama", "pytorchjob-distributed", values, tmp_root,
+                            ["resources.nnodes=2", "resources.nproc_per_node=4"], env)
+    assert rc == 0 and st["phase"] == "Succeeded" and len(st["pods"]) == 2, logs[-3000:]
+    assert "iteration        4/       4" in logs and "unknown arguments" not in logs, logs[-3000:]
+    assert "global batch size:    16" in logs
+    # the values file saves to $CKPT_ROOT/$PET_NODE_RANK: node 0 holds the first pipeline stage, node 1 the second,
+    # and both directories name their newest checkpoint
+    ck = tmp_root / "fsx/home/llama/checkpoints"
+    n0 = {p.name for p in (ck / "0/global_step4").iterdir()}
+    n1 = {p.name for p in (ck / "1/global_step4").iterdir()}
+    assert "layer_00-model_00-model_states.pt" in n0 and "layer_03-model_01-model_states.pt" in n1
+    assert any("zero_pp_rank_3_mp_rank_01" in n for n in n1), n1
+    assert (ck / "0/latest").read_text() == (ck / "1/latest").read_text() == "global_step4"
+    # resume on both nodes
+    env2 = {"B2F_TRAIN_ITERS": "6", "B2F_OVERRIDE_ARGS": TINY_GPT + llama + " --save-interval 100"}
+    rc, st, logs = _install("llama", "pytorchjob-distributed", values, tmp_root,
+                            ["resources.nnodes=2", "resources.nproc_per_node=4"], dict(env2), extra=["--auto-resume"])
+    assert rc == 0 and "at iteration 4" in logs and "iteration        6/       6" in logs, logs[-3000:]
+
+
 def test_megatron_ulysses_sequence_parallel_flag(tmp_root):
     """`--ds-sequence-parallel-size 2` (DeepSpeed-Ulysses of the pinned Megatron-DeepSpeed) on the DP + ZeRO-1 values
     file: 4 ranks = 2 replicas x 2 sequence slices; the global batch counts replicas, not ranks."""
