@@ -49,6 +49,19 @@ def test_accelerate_bert_mrpc_gloo_ws2(tmp_root):
     assert "git clone https://github.com/huggingface/accelerate.git -> local tree" in logs
 
 
+def test_accelerate_elastic_chart_on_two_nodes_rendezvous(tmp_root):
+    """`pytorchjob-elastic` with two worker pods: both run `torchrun --rdzv_backend c10d` against the shared
+    `PET_RDZV_ENDPOINT` and form one job (charts/machine-learning/training/pytorchjob-elastic/templates/train.yaml:58-71)."""
+    rc, st, logs = _install("accel2", "pytorchjob-elastic", EX / "accelerate/bert-glue-mrpc/pretrain.yaml", tmp_root,
+                            sets=["resources.nnodes=2", "resources.nproc_per_node=1", "elastic_policy.min_replicas=2",
+                                  "elastic_policy.max_replicas=2"],
+                            env={"B2F_MODEL": "bert-tiny", "B2F_EPOCHS": "1", "B2F_TRAIN_SAMPLES": "64",
+                                 "B2F_EVAL_SAMPLES": "32"})
+    assert rc == 0 and st["phase"] == "Succeeded" and sorted(st["pods"]) == ["accel2-worker-0", "accel2-worker-1"], logs[-2000:]
+    assert logs.count("--nnodes 2 --nproc_per_node 1 --rdzv_id accel2 --rdzv_backend c10d") == 2
+    assert logs.count("epoch 0: {'accuracy'") == 1          # one job: the main process alone prints the metrics
+
+
 def test_megatron_tp2_pp2_zero1_and_resume(tmp_root):
     """W3: the TP=2 x PP=2 values file (test-size model), Megatron-DS checkpoint layout, resume."""
     values = EX / "megatron-deepspeed/gpt2_345m/pretrain-ddp-tp-pp-zero1.yaml"
