@@ -8,6 +8,8 @@ import subprocess
 import sys
 from pathlib import Path
 
+import pytest
+
 REPO = Path(__file__).resolve().parent.parent
 TINY = {"B2F_MRCNN_WIDTH": "0.125", "B2F_MRCNN_IMAGE": "128x128", "CUDA_VISIBLE_DEVICES": ""}
 
@@ -179,3 +181,31 @@ def test_faster_rcnn_mode_without_mask_head(tmp_path):
     refused = subprocess.run([sys.executable, "-m", "b200flow.workloads.maskrcnn.train", "--logdir", str(tmp_path / "c4"),
                               "--config", "MODE_FPN=False"], cwd=REPO, env=env, capture_output=True, text=True, timeout=600)
     assert refused.returncode != 0 and "MODE_FPN=False" in refused.stderr
+
+
+@pytest.mark.parametrize("values,expect", [
+    ("maskrcnn/train-maskrcnn-tensorpack.yaml", {"batch": 1}),       # W6: tensorpack, 1 image per GPU
+    ("maskrcnn/train-maskrcnn-aws.yaml", {"batch": 4}),              # W7: aws-samples fork, TRAIN.BATCH_SIZE_PER_GPU=4
+])
+def test_reference_mpijob_values_files_run_unchanged(tmp_root, values, expect):
+    """The two Mask R-CNN example values files through the `mpijob-horovod-tensorflow-gpu` chart in the launcher's
+    mpirun mode (2 ranks), including their `cd /mask-rcnn-tensorflow` line that fails harmlessly as it does upstream."""
+    ex = Path("/root/reference/examples")
+    if not ex.exists():
+        pytest.skip("reference tree not mounted")
+    cmd = [sys.executable, "-m", "b200flow.launcher", "install", "w", "mpijob-horovod-tensorflow-gpu", "-f", str(ex / values),
+           "--root", str(tmp_root), "--max-restarts", "0", "--set", "resources.gpu_nodes=1", "--set", "resources.gpus_per_node=2"]
+    env = dict(os.environ, **TINY, B2F_MRCNN_EPOCHS="1", B2F_MRCNN_STEPS="2")
+    res = subprocess.run(cmd, cwd=REPO, env=env, capture_output=True, text=True, timeout=900)
+    st = json.loads(res.stdout.strip().splitlines()[-1])
+    logs = "\n".join(p.read_text(errors="replace") for p in (tmp_root / ".b200flow/releases/w/pods").glob("*/stdout.log"))
+    assert res.returncode == 0 and st["phase"] == "Succeeded" and len(st["pods"]) == 2, logs[-3000:]
+    assert "[epoch 1] step 2" in logs and "mAP(bbox)/IoU=0.5:0.95" in logs, logs[-3000:]
+    import re
+
+    thr = float(re.search(r"throughput=([0-9.]+) images/s", logs).group(1))
+    assert thr > 0
+    cfg = json.loads(next((tmp_root / "efs/home/w/logs").rglob("config.json")).read_text()) if list(
+        (tmp_root / "efs/home/w/logs").rglob("config.json")) else None
+    if cfg is not None:
+        assert int(cfg["config"].get("TRAIN.BATCH_SIZE_PER_GPU", 1)) == expect["batch"] and cfg["world"] == 2
