@@ -168,6 +168,39 @@ def group_tp_replicated():
         TPM._FUSED_AR = False
 
 
+def group_ulysses():
+    """DeepSpeed-Ulysses through the engine on GPUs: SP = world against the same model on one GPU (weights copied
+    from a seed-fixed reference, so the curves must agree to bf16 tolerance)."""
+    from b200flow.engines.ds_engine import initialize
+    from b200flow.models.gpt import GPTModel, config_from_preset
+
+    world = dist.get_world_size()
+    cfg = config_from_preset("llama-tiny", hidden=512, heads=8, kv_heads=4, ffn=1024, layers=2, vocab_size=2048, max_seq=512)
+    torch.manual_seed(55)
+    full = GPTModel(cfg, dtype=torch.bfloat16, device=torch.device("cuda")).state_dict()
+    g = torch.Generator().manual_seed(0)
+    data = [torch.randint(0, cfg.vocab_size, (2, 513), generator=g) for _ in range(2)]
+    batches = [(t[:, :-1].contiguous().cuda(), t[:, 1:].contiguous().cuda()) for t in data]
+    curves = {}
+    for name, ps in (("sp", ParallelState.initialize(tp=1, pp=1, sp=world)), ("single", None)):
+        if name == "single" and dist.get_rank() != 0:
+            continue
+        eng = initialize(cfg, {"train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": 2,
+                               "optimizer": {"params": {"lr": 1e-3, "weight_decay": 0.0}},
+                               "fused_collectives": name == "sp"}, ps, seed=3)
+        with torch.no_grad():
+            for n, p in eng.model.named_parameters():
+                p.copy_(full[n])
+        o = eng.optimizer
+        o.master.copy_(eng.flat.params[o.lo:o.hi].float())
+        it = itertools.cycle(batches)
+        curves[name] = [float(eng.train_batch(it)) for _ in range(4)]
+    if dist.get_rank() == 0:
+        ok = all(abs(a - b) < 3e-2 for a, b in zip(curves["sp"], curves["single"]))
+        report("ulysses_engine_vs_single_gpu", ok, sp=curves["sp"], single=curves["single"])
+    dist.barrier()
+
+
 def group_pp():
     base, _ = _engine_curve(1, dist.get_world_size(), False)
     report("pp_nccl_runs", base[-1] < base[0], losses=base)
@@ -284,7 +317,8 @@ def group_moe_ep():
 
 
 GROUPS = {"moe_ep": group_moe_ep, "fused_gemm": group_fused_gemm, "arena": group_arena, "allreduce": group_allreduce, "zero1": group_zero1, "tp": group_tp,
-          "pp": group_pp, "tp_replicated": group_tp_replicated}
+          "pp": group_pp, "tp_replicated": group_tp_replicated,
+          "ulysses": group_ulysses}
 
 if __name__ == "__main__":
     init_distributed("nccl")
