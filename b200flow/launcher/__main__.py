@@ -28,6 +28,27 @@ def _common(p):
     p.add_argument("--root", default=os.environ.get("B2F_ROOT", "/tmp/b200flow"))
 
 
+def _install_detached(a, plan, argv) -> int:
+    """`--no-wait`: a supervisor process of its own runs the release; this call returns once the pods are up."""
+    import subprocess
+    import time
+    from pathlib import Path
+
+    state = R.ReleaseState(Path(a.root), a.release)
+    state.dir.mkdir(parents=True, exist_ok=True)
+    (state.dir / "status.json").unlink(missing_ok=True)
+    cmd = [sys.executable, "-m", "b200flow.launcher"] + [x for x in argv if x != "--no-wait"]
+    log = open(state.dir / "supervisor.log", "ab")
+    sup = subprocess.Popen(cmd, stdout=log, stderr=subprocess.STDOUT, start_new_session=True)
+    deadline = time.time() + 30
+    while time.time() < deadline and sup.poll() is None and state.read_status().get("phase") is None:
+        time.sleep(0.1)
+    if state.exists():
+        state.write_status(supervisor_pid=sup.pid)
+    print(json.dumps(R.status(a.root, a.release)))
+    return 0 if sup.poll() in (None, 0) else int(sup.returncode)
+
+
 def main(argv=None) -> int:
     ap = argparse.ArgumentParser(prog="b200flow")
     sub = ap.add_subparsers(dest="cmd", required=True)
@@ -42,6 +63,9 @@ def main(argv=None) -> int:
                        help="propagate the training command's exit status (reference masks it with | tee)")
         p.add_argument("--online", action="store_true", help="do not install the offline git/pip shims")
         p.add_argument("--timeout", type=float, default=None)
+        p.add_argument("--no-wait", action="store_true",
+                       help="return as soon as the pods run, like `helm install` without --wait; follow with status / logs")
+        p.add_argument("--wait", action="store_true", help="wait for the job to finish (the default)")
         p.add_argument("--inject-fault", default=None, help="rank=R,step=S,kind={exit,hang,sigkill}")
         p.add_argument("--max-restarts", type=int, default=None)
         p.add_argument("--hang-timeout", type=float, default=None,
@@ -86,6 +110,8 @@ def main(argv=None) -> int:
             print("---")
             print(script)
             return 0
+        if a.no_wait:
+            return _install_detached(a, plan, argv if argv is not None else sys.argv[1:])
         run = R.Runner(plan, a.root, offline=not a.online, fault=a.inject_fault,
                        max_restarts=a.max_restarts,
                        extra_env={"B2F_AUTO_RESUME": "1"} if a.auto_resume else None)

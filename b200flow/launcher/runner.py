@@ -328,12 +328,22 @@ def uninstall(root: str | Path, release: str) -> bool:
     st = ReleaseState(Path(root), release)
     if not st.exists():
         return False
+    cur = st.read_status()
+    sup = cur.get("supervisor_pid")
+    if sup:        # a release installed with --no-wait: its supervisor takes the pods down when it is told to stop
+        try:
+            os.kill(int(sup), signal.SIGTERM)
+            for _ in range(100):
+                os.kill(int(sup), 0)
+                time.sleep(0.1)
+        except (ProcessLookupError, PermissionError):
+            pass
     for name, pid in (st.read_status().get("pods") or {}).items():
         try:
             os.killpg(int(pid), signal.SIGTERM)
         except (ProcessLookupError, PermissionError):
             pass
-    st.write_status(phase="Uninstalled")
+    st.write_status(phase="Uninstalled", supervisor_pid=None)
     return True
 
 

@@ -157,3 +157,33 @@ def test_smoke_stage_data_attach_commands(tmp_path):
     r = run("attach")
     listing = json.loads(r.stdout)
     assert "/efs/data/coco2017/a.txt" in listing["/efs"]["entries"]
+
+
+def test_install_no_wait_then_status_logs_uninstall(tmp_path):
+    """`helm install` without --wait returns at once; the job is followed with status / logs and stopped by uninstall."""
+    import json
+    import subprocess
+    import sys
+    import time
+    from pathlib import Path
+
+    repo = Path(__file__).resolve().parent.parent
+    v = tmp_path / "v.yaml"
+    v.write_text("process:\n  command: [bash, -c]\n  args:\n    - \"'for i in $(seq 1 600); do echo tick $i; sleep 0.2; done'\"\n")
+    run = lambda *a: subprocess.run([sys.executable, "-m", "b200flow.launcher", *a, "--root", str(tmp_path)], cwd=repo,  # noqa: E731
+                                    capture_output=True, text=True, timeout=120)
+    t0 = time.time()
+    r = run("install", "bg", "data-process", "-f", str(v), "--no-wait")
+    assert r.returncode == 0 and time.time() - t0 < 60, r.stdout + r.stderr
+    st = json.loads(r.stdout.strip().splitlines()[-1])
+    assert st["phase"] == "Running" and st["pods"] and st.get("supervisor_pid")
+    time.sleep(1.5)
+    assert "tick" in run("logs", "bg", "--tail", "3").stdout
+    assert json.loads(run("status", "bg").stdout)["phase"] == "Running"
+    assert run("uninstall", "bg").returncode == 0
+    time.sleep(0.5)
+    st2 = json.loads(run("status", "bg").stdout)
+    assert st2["phase"] == "Uninstalled"
+    n1 = run("logs", "bg").stdout.count("tick")
+    time.sleep(1.0)
+    assert run("logs", "bg").stdout.count("tick") == n1          # nothing is running any more
