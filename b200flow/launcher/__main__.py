@@ -4,7 +4,7 @@
     template  <release> <chart> [-f ...] [--set ...]        (print the rendered script + plan)
     uninstall <release> [--root DIR]
     status    <release> [--root DIR]
-    logs      <release> [--root DIR] [--tail N]
+    logs      <release> [--root DIR] [--tail N] [-f]
     smoke     [--gpus N] [--root DIR]            (GPU / mounts / native libraries / collective check)
     stage-data <src> <dst under /efs or /fsx> [--root DIR]
     attach    [release] [--root DIR]             (where /efs and /fsx live locally and what is in them)
@@ -78,6 +78,7 @@ def main(argv=None) -> int:
         p = sub.add_parser(name)
         p.add_argument("release")
         p.add_argument("--tail", type=int, default=None)
+        p.add_argument("-f", "--follow", action="store_true", help="logs: keep printing until the release stops running")
         _common(p)
     p = sub.add_parser("smoke")
     p.add_argument("--gpus", type=int, default=0)
@@ -129,6 +130,20 @@ def main(argv=None) -> int:
         for pod, txt in R.logs(a.root, a.release, a.tail).items():
             print(f"==> {pod} <==")
             print(txt)
+        if a.follow:          # `kubectl logs -f`: new lines of every pod until the release is no longer running
+            import time
+
+            seen = {pod: len(txt) for pod, txt in R.logs(a.root, a.release).items()}
+            while True:
+                running = R.status(a.root, a.release).get("phase") in ("Running", "Restarting")
+                for pod, txt in R.logs(a.root, a.release).items():
+                    if len(txt) > seen.get(pod, 0):
+                        for line in txt[seen.get(pod, 0):].splitlines():
+                            print(f"[{pod}] {line}", flush=True)
+                        seen[pod] = len(txt)
+                if not running:
+                    break
+                time.sleep(0.5)
         return 0
     return 2
 

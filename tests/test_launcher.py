@@ -180,7 +180,12 @@ def test_install_no_wait_then_status_logs_uninstall(tmp_path):
     time.sleep(1.5)
     assert "tick" in run("logs", "bg", "--tail", "3").stdout
     assert json.loads(run("status", "bg").stdout)["phase"] == "Running"
+    follower = subprocess.Popen([sys.executable, "-m", "b200flow.launcher", "logs", "bg", "-f", "--tail", "1", "--root", str(tmp_path)],
+                                cwd=repo, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    time.sleep(2.0)
     assert run("uninstall", "bg").returncode == 0
+    out, _ = follower.communicate(timeout=30)                     # the follower ends when the release stops
+    assert follower.returncode == 0 and out.count("[bg-pod] tick") >= 3, out[-500:]
     time.sleep(0.5)
     st2 = json.loads(run("status", "bg").stdout)
     assert st2["phase"] == "Uninstalled"
