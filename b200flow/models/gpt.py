@@ -21,6 +21,7 @@ from torch import nn
 
 from ..ops import attention as A
 from ..ops import elementwise as E
+from ..ops import gemm as G
 from ..ops import norm as N
 
 
@@ -373,6 +374,51 @@ class GPTModel(nn.Module):
         self.recompute = False
         self.seq_mult = 1        # Ulysses: rotary tables cover the whole sequence, `seq` is this rank's slice
         self.drop_seed = 0       # set per micro-batch by the engine, so a recomputed forward draws the same masks
+
+    @torch.no_grad()
+    def logits(self, tokens: torch.Tensor) -> torch.Tensor:
+        """tokens [b, s] -> next-token logits [b, s, vocab] (single process, no pipeline stages): the forward pass
+        without the loss, for evaluation by hand and for `generate`."""
+        assert self.embed is not None and self.head is not None and self.tp.world == 1
+        was = self.training
+        self.eval()
+        try:
+            b, s = tokens.shape
+            h = self.forward(tokens=tokens)                                   # [s*b, hidden], sequence-major
+            y = N.norm(h, self.head.lnf_w, self.head.lnf_b, eps=self.cfg.eps, rms=self.cfg.norm == "rms")
+            w = self.head.weight
+            out = G.linear(y, w) if y.is_cuda else torch.nn.functional.linear(y, w)
+            return out.view(s, b, -1).transpose(0, 1)
+        finally:
+            self.train(was)
+
+    @torch.no_grad()
+    def generate(self, tokens: torch.Tensor, max_new_tokens: int, temperature: float = 0.0, top_k: int = 0,
+                 eos_id: int | None = None, generator: torch.Generator | None = None) -> torch.Tensor:
+        """Autoregressive sampling (Megatron's text-generation utilities: greedy when temperature is 0, otherwise
+        temperature / top-k sampling).  The whole prefix is re-encoded for every new token — no key/value cache —
+        which is fine for checking a trained model, not for serving."""
+        out = tokens
+        for _ in range(max_new_tokens):
+            ctx = out[:, -self.cfg.max_seq:]
+            pad = (-ctx.shape[1]) % 8 if ctx.is_cuda else 0                 # the attention kernel wants multiples of 8
+            if pad and ctx.shape[1] + pad <= self.cfg.max_seq:
+                ctx = torch.nn.functional.pad(ctx, (0, pad))
+            else:
+                pad = 0
+            last = self.logits(ctx)[:, ctx.shape[1] - 1 - pad].float()        # causal: padding behind it is not seen
+            if temperature <= 0:
+                nxt = last.argmax(-1, keepdim=True)
+            else:
+                last = last / temperature
+                if top_k > 0:
+                    kth = last.topk(min(top_k, last.shape[-1]), dim=-1).values[:, -1:]
+                    last = last.masked_fill(last < kth, float("-inf"))
+                nxt = torch.multinomial(last.softmax(-1), 1, generator=generator)
+            out = torch.cat([out, nxt], 1)
+            if eos_id is not None and bool((nxt == eos_id).all()):
+                break
+        return out
 
     def _rope(self, seq, device):
         if not self.cfg.rope:

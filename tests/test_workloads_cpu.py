@@ -173,6 +173,14 @@ def test_wikicorpus_preprocess_then_ddp_zero1_pipeline(tmp_root):
     assert (data / "gpt2_text_document.bin").stat().st_size > 0 and (data / "gpt2_text_document.idx").exists()
     log = next((tmp_root / "efs/home/mds-gpt2-345m/logs").rglob("*.log")).read_text()
     assert "iteration        3/       3" in log and "synthetic" not in log   # trained on the preprocessed corpus
+    # text generation from the checkpoint that run saved (model geometry from the stored arguments)
+    ck = tmp_root / "fsx/home/mds-gpt2-345m/checkpoints/0"
+    res = subprocess.run([sys.executable, "-m", "b200flow.workloads.generate_gpt", "--load", str(ck), "--prompt-ids", "5", "6", "7",
+                          "--max-new-tokens", "5"], cwd=REPO, env=dict(os.environ, CUDA_VISIBLE_DEVICES="", PYTHONPATH=str(REPO)),
+                         capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, (res.stdout + res.stderr)[-2000:]
+    ids = json.loads(res.stdout.split("token ids:")[1].strip().splitlines()[0])
+    assert ids[:3] == [5, 6, 7] and len(ids) == 8
 
 
 def test_ray_lightning_bert(tmp_root):
