@@ -5,6 +5,7 @@
     uninstall <release> [--root DIR]
     status    <release> [--root DIR]
     logs      <release> [--root DIR] [--tail N] [-f]
+    list      [--root DIR]                       (releases with chart, phase, restarts)
     smoke     [--gpus N] [--root DIR]            (GPU / mounts / native libraries / collective check)
     stage-data <src> <dst under /efs or /fsx> [--root DIR]
     attach    [release] [--root DIR]             (where /efs and /fsx live locally and what is in them)
@@ -80,6 +81,8 @@ def main(argv=None) -> int:
         p.add_argument("--tail", type=int, default=None)
         p.add_argument("-f", "--follow", action="store_true", help="logs: keep printing until the release stops running")
         _common(p)
+    p = sub.add_parser("list")
+    _common(p)
     p = sub.add_parser("smoke")
     p.add_argument("--gpus", type=int, default=0)
     _common(p)
@@ -91,6 +94,17 @@ def main(argv=None) -> int:
     p.add_argument("release", nargs="?", default=None)
     _common(p)
     a = ap.parse_args(argv)
+    if a.cmd == "list":        # `helm list`: every release under the root with its chart, phase and restart count
+        from pathlib import Path
+
+        rows = []
+        for d in sorted((Path(a.root) / ".b200flow" / "releases").glob("*")):
+            st = R.status(a.root, d.name)
+            plan = json.loads((d / "plan.json").read_text()) if (d / "plan.json").exists() else {}
+            rows.append({"name": d.name, "chart": plan.get("chart"), "kind": plan.get("kind"), "phase": st.get("phase"),
+                         "restarts": st.get("restarts", 0), "pods": len(st.get("pods") or {})})
+        print(json.dumps(rows, indent=1))
+        return 0
     if a.cmd in ("smoke", "stage-data", "attach"):
         from . import tools as T
 

@@ -189,6 +189,8 @@ def test_install_no_wait_then_status_logs_uninstall(tmp_path):
     time.sleep(0.5)
     st2 = json.loads(run("status", "bg").stdout)
     assert st2["phase"] == "Uninstalled"
+    listed = json.loads(run("list").stdout)
+    assert [(r["name"], r["chart"], r["phase"]) for r in listed] == [("bg", "data-process", "Uninstalled")]
     n1 = run("logs", "bg").stdout.count("tick")
     time.sleep(1.0)
     assert run("logs", "bg").stdout.count("tick") == n1          # nothing is running any more
