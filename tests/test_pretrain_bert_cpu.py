@@ -70,3 +70,30 @@ def test_pretrain_bert_two_ranks_synthetic(tmp_path):
                 "--log-interval", "2", "--cpu", "--mixed_precision", "fp16", "--gradient_accumulation_steps", "2"],
                nproc=2)
     assert len(_losses(out)) == 2 and "step       4/4" in out
+
+
+def test_text_to_wordpiece_corpus_to_pretraining(tmp_path):
+    """The whole BERT data path on text: WordPiece vocabulary -> sentence-level preprocessing with the Megatron tool ->
+    pre-training that takes its special tokens and vocabulary size from the same vocab.txt."""
+    import json
+
+    from b200flow.data.tokenizer import BertWordPieceTokenizer, write_wordpiece_vocab
+
+    docs = [" ".join(f"Sentence {i} of document {d} mentions topic {(i * d) % 5} again." for i in range(3 + d % 4))
+            for d in range(40)]
+    vocab = tmp_path / "vocab.txt"
+    write_wordpiece_vocab(vocab, docs, size=300)
+    (tmp_path / "train.json").write_text("\n".join(json.dumps({"text": t}) for t in docs) + "\n")
+    tool = ROOT / "b200flow/workloads/trees/megatron_deepspeed/tools/preprocess_data.py"
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="", PYTHONPATH=str(ROOT))
+    res = subprocess.run([sys.executable, str(tool), "--input", str(tmp_path / "train.json"), "--output-prefix",
+                          str(tmp_path / "wiki"), "--vocab-file", str(vocab), "--tokenizer-type", "BertWordPieceLowerCase",
+                          "--split-sentences"], env=env, capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout + res.stderr
+    out = _run(["--model", "bert-tiny", "--data-prefix", str(tmp_path / "wiki_text_sentence"), "--vocab-file", str(vocab),
+                "--max-seq-length", "48", "--per-device-batch", "8", "--max-steps", "30", "--lr", "3e-3", "--warmup-steps", "3",
+                "--dropout", "0", "--log-interval", "10", "--cpu", "--mixed_precision", "no"])
+    ls = _losses(out)
+    tok = BertWordPieceTokenizer(vocab)
+    assert len(ls) == 3 and ls[-1] < ls[0] - 0.5, out[-1500:]          # real text has structure: the loss falls
+    assert ls[0] < 1.3 * (__import__("math").log((tok.vocab_size + 127) // 128 * 128) + 0.7)
