@@ -95,7 +95,7 @@ def _ep_rank(engine) -> int:
 
 
 def save_checkpoint(engine, save_dir: str, tag: str | None = None, client_state: dict | None = None,
-                    async_save: bool = False) -> str:
+                    async_save: bool = False, save_optimizer: bool = True, save_rng: bool = True) -> str:
     ps = engine.ps
     tp = ps.tp_rank if ps else 0
     dp = ps.dp_rank if ps else 0
@@ -107,7 +107,7 @@ def save_checkpoint(engine, save_dir: str, tag: str | None = None, client_state:
     bf16 = engine.dtype == torch.bfloat16
     model = engine.model
     client = {"iteration": step, "global_steps": step, "args": getattr(engine, "args", None),
-              "rng_state": torch.get_rng_state(), "lr": engine.optimizer.lr,
+              **({"rng_state": torch.get_rng_state()} if save_rng else {}), "lr": engine.optimizer.lr,
               "parallel": {"tp": engine.tp_world, "pp": pp_world, "dp": engine.dp_world},
               **(client_state or {})}
     if dp == 0:      # one DP replica writes the module
@@ -131,22 +131,23 @@ def save_checkpoint(engine, save_dir: str, tag: str | None = None, client_state:
         _, experts = _split_expert_state(_cpu(model.state_dict()), _ep_rank(engine))
         for (L, E), sd in experts.items():
             _write(sd, d / expert_file(L, E, tp), async_save)
-    osd = engine.optimizer.state_dict()
-    osd = {k: (v.detach().cpu() if isinstance(v, torch.Tensor) else v) for k, v in osd.items()}
-    osd["stage"] = engine.stage
-    scaler = getattr(engine, "loss_scaler", None)
-    if scaler is not None:     # DeepSpeed keeps the fp16 loss-scale state with the optimizer state
-        osd["loss_scaler"] = scaler.state_dict()
-        osd["skipped_steps"] = engine.skipped_steps
-    name = optim_file(dp, tp, bf16)
-    if pp_world > 1:   # one file per (stage, dp, tp): stage goes into the DeepSpeed "pp_rank" slot
-        name = ("bf16_" if bf16 else "") + f"zero_pp_rank_{dp + engine.dp_world * engine.stage}_mp_rank_{tp:02d}_optim_states.pt"
-    _write({"optimizer_state_dict": osd, "ds_version": "b200flow"}, d / name, async_save)
-    eopt = getattr(engine, "expert_optimizer", None)
-    if eopt is not None:        # expert parameters have their own (expert-data-parallel) optimizer shard
-        esd = {k: (v.detach().cpu() if isinstance(v, torch.Tensor) else v) for k, v in eopt.state_dict().items()}
-        _write({"optimizer_state_dict": esd, "ds_version": "b200flow"}, d / expert_optim_file(_ep_rank(engine), tp),
-               async_save)
+    if save_optimizer:        # Megatron's --no-save-optim leaves the ZeRO partitions out (load with --no-load-optim)
+        osd = engine.optimizer.state_dict()
+        osd = {k: (v.detach().cpu() if isinstance(v, torch.Tensor) else v) for k, v in osd.items()}
+        osd["stage"] = engine.stage
+        scaler = getattr(engine, "loss_scaler", None)
+        if scaler is not None:     # DeepSpeed keeps the fp16 loss-scale state with the optimizer state
+            osd["loss_scaler"] = scaler.state_dict()
+            osd["skipped_steps"] = engine.skipped_steps
+        name = optim_file(dp, tp, bf16)
+        if pp_world > 1:   # one file per (stage, dp, tp): stage goes into the DeepSpeed "pp_rank" slot
+            name = ("bf16_" if bf16 else "") + f"zero_pp_rank_{dp + engine.dp_world * engine.stage}_mp_rank_{tp:02d}_optim_states.pt"
+        _write({"optimizer_state_dict": osd, "ds_version": "b200flow"}, d / name, async_save)
+        eopt = getattr(engine, "expert_optimizer", None)
+        if eopt is not None:        # expert parameters have their own (expert-data-parallel) optimizer shard
+            esd = {k: (v.detach().cpu() if isinstance(v, torch.Tensor) else v) for k, v in eopt.state_dict().items()}
+            _write({"optimizer_state_dict": esd, "ds_version": "b200flow"}, d / expert_optim_file(_ep_rank(engine), tp),
+                   async_save)
     if dist.is_initialized():
         dist.barrier()
     # Every rank names the checkpoint in ITS save directory: the reference's examples save to

@@ -492,10 +492,11 @@ class TrainEngine:
             self.optimizer.lr = self._lr_fn(self.global_steps - self.skipped_steps + 1)
 
     # ----------------------------------------------------------- checkpoints
-    def save_checkpoint(self, save_dir: str, tag: str | None = None, client_state: dict | None = None):
+    def save_checkpoint(self, save_dir: str, tag: str | None = None, client_state: dict | None = None,
+                        save_optimizer: bool = True, save_rng: bool = True):
         from ..ckpt.megatron_ds_layout import save_checkpoint
 
-        return save_checkpoint(self, save_dir, tag, client_state or {})
+        return save_checkpoint(self, save_dir, tag, client_state or {}, save_optimizer=save_optimizer, save_rng=save_rng)
 
     def load_checkpoint(self, load_dir: str, tag: str | None = None, load_optimizer_states: bool = True,
                         load_rng: bool = True, finetune: bool = False):

@@ -72,6 +72,7 @@ def parse_args():
     a("--eval-interval", type=int, default=1000); a("--eval-iters", type=int, default=10)
     a("--distributed-backend", default="nccl"); a("--save", default=None); a("--load", default=None)
     a("--tensorboard-dir", default=None); a("--seed", type=int, default=1234)
+    a("--no-save-optim", action="store_true"); a("--no-save-rng", action="store_true")
     a("--no-load-optim", action="store_true"); a("--no-load-rng", action="store_true"); a("--finetune", action="store_true")
     a("--deepspeed", action="store_true"); a("--deepspeed_config", default=None)
     a("--zero-stage", type=int, default=None); a("--no-pipeline-parallel", action="store_true")
@@ -244,7 +245,7 @@ def main():
                 print(f" validation loss at iteration {iteration} | lm loss value: {vl:.6E} | "
                       f"lm loss PPL: {math.exp(min(20, vl)):.6E} |", flush=True)
         if args.save and args.save_interval and iteration % args.save_interval == 0:
-            engine.save_checkpoint(args.save)
+            engine.save_checkpoint(args.save, save_optimizer=not args.no_save_optim, save_rng=not args.no_save_rng)
             if rank == 0:
                 print(f"  successfully saved checkpoint at iteration {iteration:7d} to {args.save}", flush=True)
         if args.exit_interval and iteration % args.exit_interval == 0:
@@ -253,7 +254,7 @@ def main():
             train_iters = iteration
             break
     if args.save and (not args.save_interval or train_iters % args.save_interval != 0):
-        engine.save_checkpoint(args.save)
+        engine.save_checkpoint(args.save, save_optimizer=not args.no_save_optim, save_rng=not args.no_save_rng)
     if tracker:
         tracker.finish()
     if world > 1:

@@ -150,3 +150,16 @@ def test_finetune_and_no_load_optim_take_weights_only(tmp_path):
     b.load_checkpoint(str(tmp_path), finetune=True)
     assert torch.equal(b.flat.params, eng.flat.params) and b.global_steps == 0
     assert float(b.train_batch(itertools.cycle(batches))) > 0
+
+
+def test_no_save_optim_writes_weights_only(tmp_path):
+    cfg, eng, batches = _engine("gpt2-tiny")
+    eng.train_batch(itertools.cycle(batches))
+    eng.save_checkpoint(str(tmp_path), save_optimizer=False, save_rng=False)
+    names = {p.name for p in (tmp_path / "global_step1").iterdir()}
+    assert "mp_rank_00_model_states.pt" in names and not any("optim_states" in n for n in names)
+    client = torch.load(tmp_path / "global_step1" / "mp_rank_00_model_states.pt", weights_only=False)
+    assert "rng_state" not in client
+    _, fresh, _ = _engine("gpt2-tiny", seed=99)
+    fresh.load_checkpoint(str(tmp_path), load_optimizer_states=False)
+    assert torch.equal(fresh.flat.params, eng.flat.params)
