@@ -12,7 +12,8 @@ The reference saves with `--save $CKPT_ROOT/$PET_NODE_RANK --save-interval 10000
         zero_pp_rank_<DP>_mp_rank_<TP:02d>_optim_states.pt     ZeRO-1 shard (fp16)
         bf16_zero_pp_rank_<DP>_mp_rank_<TP:02d>_optim_states.pt   … under bf16
         layer_<L>_expert_<E>_mp_rank_<TP:02d>_model_states.pt  MoE expert weights
-        expp_rank_<EP>_mp_rank_<TP:02d>_optim_states.pt        MoE expert optimizer shard
+        expp_rank_<EP>_mp_rank_<TP:02d>_optim_states.pt        MoE expert optimizer shard (expert-DP rank 0)
+        expp_rank_<EP>_edp_<R>_mp_rank_<TP:02d>_optim_states.pt   … of expert-data-parallel rank R > 0
 
 Pipeline layer indices follow the PipelineModule convention: embedding = 00, transformer
 layer i = i + 1, final norm + head = layers + 1.  Saves run on a background thread
@@ -68,8 +69,17 @@ def expert_file(layer: int, expert: int, tp: int) -> str:
     return f"layer_{layer}_expert_{expert}_mp_rank_{tp:02d}_model_states.pt"
 
 
-def expert_optim_file(ep: int, tp: int) -> str:
-    return f"expp_rank_{ep}_mp_rank_{tp:02d}_optim_states.pt"
+def expert_optim_file(ep: int, tp: int, edp: int = 0) -> str:
+    """The expert optimizer is ZeRO-partitioned over the expert-data-parallel group (dp / ep ranks that hold the
+    same experts), so every (EP rank, expert-DP rank) pair owns a distinct shard and needs its own file;
+    expert-DP rank 0 keeps DeepSpeed's name."""
+    mid = f"_edp_{edp}" if edp else ""
+    return f"expp_rank_{ep}{mid}_mp_rank_{tp:02d}_optim_states.pt"
+
+
+def _edp_rank(engine) -> int:
+    eo = getattr(engine, "expert_optimizer", None)
+    return int(getattr(eo, "dp_rank", 0)) if eo is not None else 0
 
 
 _EXPERT_TENSORS = ("w1", "b1", "w2", "b2")     # MoELayer keeps its local experts batched: [E_local, ...]
@@ -106,8 +116,13 @@ def save_checkpoint(engine, save_dir: str, tag: str | None = None, client_state:
     d.mkdir(parents=True, exist_ok=True)
     bf16 = engine.dtype == torch.bfloat16
     model = engine.model
+    rng = {}
+    if save_rng:     # CPU + CUDA generators and the engine's dropout-call counter: masks continue, not restart
+        rng = {"rng_state": torch.get_rng_state(), "drop_calls": int(getattr(engine, "_drop_calls", 0))}
+        if torch.cuda.is_available() and engine.device.type == "cuda":
+            rng["cuda_rng_state"] = torch.cuda.get_rng_state(engine.device)
     client = {"iteration": step, "global_steps": step, "args": getattr(engine, "args", None),
-              **({"rng_state": torch.get_rng_state()} if save_rng else {}), "lr": engine.optimizer.lr,
+              **rng, "lr": engine.optimizer.lr,
               "parallel": {"tp": engine.tp_world, "pp": pp_world, "dp": engine.dp_world},
               **(client_state or {})}
     if dp == 0:      # one DP replica writes the module
@@ -146,20 +161,52 @@ def save_checkpoint(engine, save_dir: str, tag: str | None = None, client_state:
         eopt = getattr(engine, "expert_optimizer", None)
         if eopt is not None:        # expert parameters have their own (expert-data-parallel) optimizer shard
             esd = {k: (v.detach().cpu() if isinstance(v, torch.Tensor) else v) for k, v in eopt.state_dict().items()}
-            _write({"optimizer_state_dict": esd, "ds_version": "b200flow"}, d / expert_optim_file(_ep_rank(engine), tp),
-                   async_save)
-    if dist.is_initialized():
-        dist.barrier()
-    # Every rank names the checkpoint in ITS save directory: the reference's examples save to
-    # `$CKPT_ROOT/$PET_NODE_RANK`, one directory per node, and a node without `latest` could not resume.
-    # Same content from every writer, put in place by a rename.
+            _write({"optimizer_state_dict": esd, "ds_version": "b200flow"},
+                   d / expert_optim_file(_ep_rank(engine), tp, _edp_rank(engine)), async_save)
+    # `latest` may only name a complete checkpoint.  Every rank names the checkpoint in ITS save directory: the
+    # reference's examples save to `$CKPT_ROOT/$PET_NODE_RANK`, one directory per node, and a node without
+    # `latest` could not resume.  Same content from every writer, put in place by a rename.
     import os
 
-    wait_for_pending_saves() if not async_save else None
-    for name, text in (("latest", tag), ("latest_checkpointed_iteration.txt", str(step))):
-        tmp = Path(save_dir) / f".{name}.{os.getpid()}.tmp"
-        tmp.write_text(text)
-        os.replace(tmp, Path(save_dir) / name)
+    def publish():
+        for name, text in (("latest", tag), ("latest_checkpointed_iteration.txt", str(step))):
+            tmp = Path(save_dir) / f".{name}.{os.getpid()}.tmp"
+            tmp.write_text(text)
+            os.replace(tmp, Path(save_dir) / name)
+
+    if not async_save:
+        wait_for_pending_saves()             # earlier asynchronous saves, if any
+        if dist.is_initialized():
+            dist.barrier()                   # every rank's files are on disk
+        publish()
+        return str(d)
+    # asynchronous: training continues now; a publisher thread joins this rank's writers, drops a marker into the
+    # checkpoint directory and renames `latest` into place once the markers of every rank that writes into this
+    # directory are there - a crash before that leaves `latest` on the previous, complete checkpoint
+    rank = dist.get_rank() if dist.is_initialized() else 0
+    peers = 1
+    if dist.is_initialized():
+        dirs = [None] * dist.get_world_size()
+        dist.all_gather_object(dirs, str(Path(save_dir).resolve()))
+        peers = sum(1 for x in dirs if x == str(Path(save_dir).resolve()))
+    writers = list(_pending)
+    del _pending[:]
+
+    def finish():
+        import time
+
+        for t in writers:
+            t.join()
+        (d / f".complete_rank_{rank}").write_text(tag)
+        deadline = time.monotonic() + 3600
+        while len(list(d.glob(".complete_rank_*"))) < peers and time.monotonic() < deadline:
+            time.sleep(0.05)
+        if len(list(d.glob(".complete_rank_*"))) >= peers:
+            publish()
+
+    t = threading.Thread(target=finish, daemon=False)
+    t.start()
+    _pending.append(t)
     return str(d)
 
 
@@ -206,6 +253,15 @@ def _load_optimizer_state(d: Path, name: str, engine, tp: int, bf16: bool) -> di
         out[key] = now[opt.lo:opt.hi].clone()
     out["partition"], out["dp_world"], out["dp_rank"] = (opt.lo, opt.hi), engine.dp_world, opt.dp_rank
     return out
+
+
+def _restore_rng(engine, client: dict) -> None:
+    if "rng_state" in client:
+        torch.set_rng_state(client["rng_state"])
+    if "cuda_rng_state" in client and engine.device.type == "cuda":
+        torch.cuda.set_rng_state(client["cuda_rng_state"], engine.device)
+    if "drop_calls" in client and hasattr(engine, "_drop_calls"):
+        engine._drop_calls = int(client["drop_calls"])
 
 
 def load_checkpoint(engine, load_dir: str, tag: str | None = None, load_optimizer: bool = True,
@@ -258,8 +314,8 @@ def load_checkpoint(engine, load_dir: str, tag: str | None = None, load_optimize
             if o is not None:
                 o.master.copy_(o.flat.params[o.lo:o.hi].float())
         engine.global_steps = 0 if finetune else int(client.get("global_steps", 0))
-        if load_rng and not finetune and "rng_state" in client:
-            torch.set_rng_state(client["rng_state"])
+        if load_rng and not finetune:
+            _restore_rng(engine, client)
         return str(d), client
     osd = _load_optimizer_state(d, name, engine, tp, bf16)
     dev = engine.flat.params.device
@@ -269,11 +325,11 @@ def load_checkpoint(engine, load_dir: str, tag: str | None = None, load_optimize
         engine.loss_scaler.load_state_dict(osd["loss_scaler"])
         engine.skipped_steps = int(osd.get("skipped_steps", 0))
     eopt = getattr(engine, "expert_optimizer", None)
-    ef = d / expert_optim_file(_ep_rank(engine), tp)
+    ef = d / expert_optim_file(_ep_rank(engine), tp, _edp_rank(engine))
     if eopt is not None and ef.exists():
         esd = torch.load(ef, map_location="cpu", weights_only=False)["optimizer_state_dict"]
         eopt.load_state_dict({k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in esd.items()})
     engine.global_steps = int(client.get("global_steps", osd.get("step", 0)))
-    if load_rng and "rng_state" in client:
-        torch.set_rng_state(client["rng_state"])
+    if load_rng:
+        _restore_rng(engine, client)
     return str(d), client

@@ -113,6 +113,28 @@ class _Optimizer:
     def __init__(self, opt, acc):
         self.optimizer, self.acc = opt, acc
         self.step_was_skipped = False
+        # the DDP hooks move every gradient into `p.main_grad` (fp32, flat) and clear `p.grad`; b200flow's own
+        # optimizers read `main_grad`, a stock torch.optim optimizer (what the Accelerate example constructs:
+        # AdamW) reads `p.grad` and would silently step on nothing
+        self._reads_main_grad = hasattr(opt, "_grad") or hasattr(opt, "flat")
+
+    def _expose_grads(self):
+        """Hand the reduced `main_grad` to an optimizer that only knows `p.grad`."""
+        for g in self.optimizer.param_groups:
+            for p in g["params"]:
+                mg = getattr(p, "main_grad", None)
+                if mg is not None and p.requires_grad:
+                    p.grad = mg.to(p.dtype) if mg.dtype != p.dtype else mg
+
+    def _step_inner(self):
+        if not self._reads_main_grad:
+            self._expose_grads()
+        self.optimizer.step()
+        if not self._reads_main_grad:
+            for g in self.optimizer.param_groups:
+                for p in g["params"]:
+                    if getattr(p, "main_grad", None) is not None:
+                        p.grad = None
 
     @property
     def param_groups(self):
@@ -139,7 +161,7 @@ class _Optimizer:
             return
         scaler = self.acc.scaler
         if scaler is None:
-            self.optimizer.step()
+            self._step_inner()
             return
         grads = self._grads()
         found_inf = not all(bool(torch.isfinite(g).all()) for g in grads)    # reduced gradients: same on every rank
@@ -155,13 +177,16 @@ class _Optimizer:
             else:
                 for g in grads:
                     g.mul_(inv)
-                self.optimizer.step()
+                self._step_inner()
         self.acc._unscaled = False
         scaler.update(found_inf)
 
     def zero_grad(self, set_to_none=True):
         if self.acc.sync_gradients:
             self.optimizer.zero_grad()
+            if not self._reads_main_grad:      # a stock optimizer clears p.grad only; the flat buffer is ours
+                for m in self.acc._models:
+                    m.zero_grad()
 
     def state_dict(self):
         return self.optimizer.state_dict()

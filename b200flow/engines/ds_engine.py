@@ -38,7 +38,7 @@ _KNOWN = {"train_micro_batch_size_per_gpu", "gradient_accumulation_steps", "zero
           "bf16", "fp16", "gradient_clipping", "optimizer", "wall_clock_breakdown",
           "train_batch_size", "steps_per_print", "scheduler", "fused_collectives",
           "activation_checkpointing", "sequence_parallel", "expert_parallel_size", "flops_profiler",
-          "comms_logger", "sequence_parallel_size"}
+          "comms_logger", "sequence_parallel_size", "checkpoint"}
 
 
 def split_layers(num_layers: int, stages: int) -> list[tuple[int, int]]:
@@ -493,10 +493,14 @@ class TrainEngine:
 
     # ----------------------------------------------------------- checkpoints
     def save_checkpoint(self, save_dir: str, tag: str | None = None, client_state: dict | None = None,
-                        save_optimizer: bool = True, save_rng: bool = True):
+                        save_optimizer: bool = True, save_rng: bool = True, async_save: bool = False):
+        """`async_save=True` (or `"checkpoint": {"async_save": true}` in the config) returns once tensors are staged on the
+        host; files and `latest` follow on background threads (`ckpt.megatron_ds_layout.wait_for_pending_saves`)."""
         from ..ckpt.megatron_ds_layout import save_checkpoint
 
-        return save_checkpoint(self, save_dir, tag, client_state or {}, save_optimizer=save_optimizer, save_rng=save_rng)
+        async_save = async_save or bool((self.ds.get("checkpoint") or {}).get("async_save", False))
+        return save_checkpoint(self, save_dir, tag, client_state or {}, async_save=async_save,
+                               save_optimizer=save_optimizer, save_rng=save_rng)
 
     def load_checkpoint(self, load_dir: str, tag: str | None = None, load_optimizer_states: bool = True,
                         load_rng: bool = True, finetune: bool = False):

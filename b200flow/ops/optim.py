@@ -32,6 +32,11 @@ class MultiTensorTable:
         rows, first = [], 0
         for i, mst in enumerate(masters):
             n = mst.numel()
+            # the kernel reads raw pointers as fp32 master / moments of n elements each
+            for t in (mst, ms[i], vs[i]):
+                assert t.dtype == torch.float32 and t.numel() == n and t.is_contiguous(), \
+                    f"AdamW state must be contiguous float32 (got {t.dtype}, {t.numel()} vs {n})"
+            assert grads[i].dtype == grads[0].dtype and grads[i].numel() == n
             po = params_out[i].data_ptr() if params_out is not None and params_out[i] is not None else 0
             rows.append([mst.data_ptr(), ms[i].data_ptr(), vs[i].data_ptr(), grads[i].data_ptr(),
                          po, n, first])

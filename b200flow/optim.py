@@ -80,6 +80,20 @@ class AdamW(torch.optim.Optimizer):
         sd = dict(sd)
         self._step = int(sd.pop("b2f_step", self._step))
         super().load_state_dict(sd)
+        # torch's loader casts floating-point state to the parameter's dtype; with bf16 parameters that
+        # would turn the fp32 master / moments into bf16 while the kernel reads them as fp32.  Restore
+        # them from the checkpoint's own tensors, as float32 on the parameter's device.
+        saved = sd.get("state", {})
+        ids = [i for g in sd.get("param_groups", []) for i in g["params"]]
+        params = [p for g in self.param_groups for p in g["params"]]
+        for i, p in zip(ids, params):
+            src = saved.get(i)
+            if src is None:
+                continue
+            st = self.state[p]
+            for k in ("master", "exp_avg", "exp_avg_sq"):
+                if k in src:
+                    st[k] = src[k].detach().to(device=p.device, dtype=torch.float32).clone()
         self._tables = {}                      # the device tables point at the tensors just replaced
 
     def zero_grad(self, set_to_none: bool = True):

@@ -7,6 +7,8 @@ re-designed around flat storage:
 
 * gradients live in ONE flat fp32 buffer (symmetric peer memory on GPUs), so a bucket is a
   slice and needs no copy-in / copy-out;
+* buckets are launched strictly in index order (a complete bucket waits behind an incomplete earlier one), so
+  every rank issues the same sequence of reductions whatever order its autograd hooks fire in;
 * the bucket plan comes from the host C++ planner (`csrc/host/bucket_plan.cpp`) and the per-event
   readiness bookkeeping runs in the host C++ reducer (`csrc/host/reducer.cpp`): a gradient-ready event is
   one call that answers "which bucket, if any, is now complete";
@@ -101,8 +103,10 @@ class DistributedDataParallel(nn.Module):
         lib = host_lib()
         lib.b2f_reducer_create.restype = ctypes.c_void_p
         lib.b2f_reducer_mark.restype = lib.b2f_reducer_next_unlaunched.restype = ctypes.c_int
+        lib.b2f_reducer_next_ready.restype = ctypes.c_int
         lib.b2f_reducer_mark.argtypes = [ctypes.c_void_p, ctypes.c_int]
         lib.b2f_reducer_next_unlaunched.argtypes = lib.b2f_reducer_reset.argtypes = [ctypes.c_void_p]
+        lib.b2f_reducer_next_ready.argtypes = [ctypes.c_void_p]
         lib.b2f_reducer_destroy.argtypes = [ctypes.c_void_p]
         self._free_reducer()
         plan = np.array(self.buckets, dtype=np.int64).reshape(-1)
@@ -146,8 +150,9 @@ class DistributedDataParallel(nn.Module):
         if not self.require_sync:
             return
         bi = self._lib.b2f_reducer_mark(self._state, si)
-        if bi >= 0:
+        while bi >= 0:          # buckets leave in index order; one event can release several in a row
             self._launch(bi)
+            bi = self._lib.b2f_reducer_next_ready(self._state)
 
     def _launch(self, bi):
         if self.world == 1:

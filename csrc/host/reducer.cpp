@@ -10,6 +10,12 @@
 // after its last use.  A bucket is handed out exactly once per step, either by the mark that
 // completes it or by the sweep at the end of backward that collects buckets some of whose
 // parameters received no gradient.
+//
+// Buckets are handed out strictly in bucket-index order: bucket b only after buckets 0..b-1.  The
+// cross-rank matching of the reductions (epoch-keyed flags of K1, NCCL call order) depends on every
+// rank launching the same sequence, and the order in which autograd hooks fire may differ between
+// ranks (data-dependent branches, unused heads).  A complete bucket therefore waits behind an
+// incomplete earlier one, exactly as in torch's Reducer.
 #include <cstdint>
 #include <new>
 #include <vector>
@@ -23,7 +29,7 @@ struct Reducer {
   std::vector<int32_t> uses;          // ... still outstanding
   std::vector<int32_t> pending;       // per bucket: slots not yet ready
   std::vector<uint8_t> launched;      // per bucket: already handed out this step
-  int sweep = 0;
+  int next = 0;                       // first bucket not handed out yet (in-order cursor)
 };
 
 }  // namespace
@@ -66,33 +72,40 @@ void b2f_reducer_reset(void* h) {
   r->uses = r->uses_init;
   r->pending = r->bucket_slots;
   r->launched.assign(r->launched.size(), 0);
-  r->sweep = 0;
+  r->next = 0;
 }
 
-// One gradient-ready event of `slot`.  Returns the bucket that just became complete (now marked as
-// handed out), or -1.  Events beyond the expected count are ignored.
+// The next bucket in index order if it is complete (now marked as handed out), or -1.  Call until -1
+// after every mark that returned a bucket: one event can release a run of consecutive buckets.
+int b2f_reducer_next_ready(void* h) {
+  Reducer* r = static_cast<Reducer*>(h);
+  const int nb = static_cast<int>(r->launched.size());
+  if (r->next >= nb || r->pending[r->next] != 0) return -1;
+  const int b = r->next++;
+  r->launched[b] = 1;
+  return b;
+}
+
+// One gradient-ready event of `slot`.  Returns the next bucket to launch (in index order, now marked
+// as handed out) if this event made one available, or -1.  Events beyond the expected count are ignored.
 int b2f_reducer_mark(void* h, int slot) {
   Reducer* r = static_cast<Reducer*>(h);
   if (slot < 0 || slot >= static_cast<int>(r->uses.size()) || r->uses[slot] <= 0) return -1;
   if (--r->uses[slot] > 0) return -1;
   const int b = r->slot_bucket[slot];
-  if (--r->pending[b] != 0 || r->launched[b]) return -1;
-  r->launched[b] = 1;
-  return b;
+  if (--r->pending[b] != 0 || b != r->next) return -1;
+  return b2f_reducer_next_ready(h);
 }
 
-// End-of-backward sweep: the next bucket that has not been handed out yet (now marked), or -1.
+// End-of-backward sweep: the next bucket that has not been handed out yet (now marked), complete or
+// not, in index order; -1 when all are out.
 int b2f_reducer_next_unlaunched(void* h) {
   Reducer* r = static_cast<Reducer*>(h);
   const int nb = static_cast<int>(r->launched.size());
-  while (r->sweep < nb) {
-    const int b = r->sweep++;
-    if (!r->launched[b]) {
-      r->launched[b] = 1;
-      return b;
-    }
-  }
-  return -1;
+  if (r->next >= nb) return -1;
+  const int b = r->next++;
+  r->launched[b] = 1;
+  return b;
 }
 
 int b2f_reducer_num_buckets(void* h) { return static_cast<int>(static_cast<Reducer*>(h)->launched.size()); }

@@ -31,6 +31,7 @@ void b2f_reducer_destroy(void* h);
 void b2f_reducer_reset(void* h);
 int b2f_reducer_mark(void* h, int slot);
 int b2f_reducer_next_unlaunched(void* h);
+int b2f_reducer_next_ready(void* h);
 int b2f_reducer_num_buckets(void* h);
 void* b2f_chan_create(const char* name, uint64_t capacity);
 void* b2f_chan_open(const char* name);
@@ -133,6 +134,21 @@ static void test_reducer() {
     CHECK(b2f_reducer_mark(r, 0) == -1);         // a late event cannot hand bucket 2 out again
     b2f_reducer_reset(r);
   }
+  // hooks firing out of bucket order (a rank whose head ran late): bucket 1 completes first but is only
+  // handed out behind bucket 0, so the launch sequence is 0, 1, 2 on every rank
+  CHECK(b2f_reducer_mark(r, 4) == -1);
+  CHECK(b2f_reducer_mark(r, 3) == -1);
+  CHECK(b2f_reducer_mark(r, 3) == -1);
+  CHECK(b2f_reducer_mark(r, 2) == -1);           // bucket 1 complete, bucket 0 not: nothing leaves
+  CHECK(b2f_reducer_next_ready(r) == -1);
+  CHECK(b2f_reducer_mark(r, 6) == -1);
+  CHECK(b2f_reducer_mark(r, 5) == 0);            // bucket 0 leaves ...
+  CHECK(b2f_reducer_next_ready(r) == 1);         // ... and releases bucket 1 behind it
+  CHECK(b2f_reducer_next_ready(r) == -1);
+  CHECK(b2f_reducer_mark(r, 1) == -1);
+  CHECK(b2f_reducer_mark(r, 0) == 2);
+  CHECK(b2f_reducer_next_unlaunched(r) == -1);
+  b2f_reducer_reset(r);
   CHECK(b2f_reducer_mark(r, 99) == -1 && b2f_reducer_mark(r, -1) == -1);
   b2f_reducer_destroy(r);
   const int64_t overlap[8] = {0, 3, 0, 30, 2, 4, 20, 40};   // slot 2 in two buckets

@@ -163,3 +163,114 @@ def test_no_save_optim_writes_weights_only(tmp_path):
     _, fresh, _ = _engine("gpt2-tiny", seed=99)
     fresh.load_checkpoint(str(tmp_path), load_optimizer_states=False)
     assert torch.equal(fresh.flat.params, eng.flat.params)
+
+
+def _moe_ckpt_worker(rank, world, ep, port, save_dir, q):
+    """GPT-MoE engine at data-parallel size `world`, expert-parallel size `ep`: save, keep training, then a fresh
+    engine loads and must continue identically (every (EP rank, expert-DP rank) shard in its own file)."""
+    import os
+
+    import torch.distributed as dist
+
+    from b200flow.parallel.groups import ParallelState
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.set_num_threads(1)
+    ps = ParallelState.initialize(tp=1, pp=1, ep=ep)
+    cfg = config_from_preset("gpt-moe-tiny")
+    dsc = {"train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": 1, "optimizer": {"params": {"lr": 1e-3}}}
+    g = torch.Generator().manual_seed(5 + rank)
+    toks = [torch.randint(0, cfg.vocab_size, (2, 33), generator=g) for _ in range(4)]
+    batches = [(t[:, :-1].contiguous(), t[:, 1:].contiguous()) for t in toks]
+    eng = initialize(cfg, dsc, ps, device=torch.device("cpu"), seed=11)
+    it = itertools.cycle(batches)
+    for _ in range(2):
+        eng.train_batch(it)
+    eng.save_checkpoint(save_dir)
+    after = [float(eng.train_batch(it)) for _ in range(2)]
+    fresh = initialize(cfg, dsc, ps, device=torch.device("cpu"), seed=99)
+    fresh.load_checkpoint(save_dir)
+    it2 = itertools.cycle(batches)
+    next(it2), next(it2)
+    resumed = [float(fresh.train_batch(it2)) for _ in range(2)]
+    eo = eng.expert_optimizer
+    q.put((rank, after, resumed, (eo.lo, eo.hi), eo.dp_rank))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,ep,port", [(4, 2, 29687), (2, 1, 29688)])
+def test_expert_optimizer_shards_do_not_collide_when_dp_exceeds_ep(tmp_path, world, ep, port):
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_moe_ckpt_worker, args=(r, world, ep, port, str(tmp_path), q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    out = sorted(q.get(timeout=600) for _ in procs)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    names = {p.name for p in (tmp_path / "global_step2").iterdir() if p.name.startswith("expp_rank_")}
+    assert len(names) == world, names            # one expert optimizer shard per rank: (ep ranks) x (expert-dp ranks)
+    assert "expp_rank_0_mp_rank_00_optim_states.pt" in names
+    for rank, after, resumed, _part, _edp in out:
+        assert resumed == pytest.approx(after, rel=1e-5, abs=1e-6), (rank, after, resumed)
+
+
+def test_async_save_publishes_latest_only_when_the_files_are_complete(tmp_path, monkeypatch):
+    from b200flow.ckpt import megatron_ds_layout as L
+
+    cfg, eng, batches = _engine("gpt2-tiny")
+    it = itertools.cycle(batches)
+    eng.train_batch(it)
+    eng.save_checkpoint(str(tmp_path))                           # step 1, synchronous
+    eng.train_batch(it)
+    import threading
+
+    gate = threading.Event()
+    real_save = torch.save
+
+    def slow_save(obj, path, *a, **kw):
+        gate.wait(timeout=60)
+        return real_save(obj, path, *a, **kw)
+
+    monkeypatch.setattr(torch, "save", slow_save)
+    eng.save_checkpoint(str(tmp_path), async_save=True)         # returns while the writers are still blocked
+    assert (tmp_path / "latest").read_text() == "global_step1"   # a crash here resumes from the complete checkpoint
+    gate.set()
+    L.wait_for_pending_saves()
+    monkeypatch.setattr(torch, "save", real_save)
+    assert (tmp_path / "latest").read_text() == "global_step2"
+    _, fresh, _ = _engine("gpt2-tiny", seed=99)
+    fresh.load_checkpoint(str(tmp_path))
+    assert fresh.global_steps == 2 and torch.equal(fresh.flat.params, eng.flat.params)
+
+
+def test_resume_with_dropout_reproduces_the_masks(tmp_path):
+    """The dropout-call counter travels with the checkpoint, so the resumed run draws the masks the
+    uninterrupted run draws (not the ones from step 0 again)."""
+    def make(seed):
+        cfg = config_from_preset("gpt2-tiny")
+        cfg.dropout = 0.1
+        return cfg, initialize(cfg, {"train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": 1,
+                                     "optimizer": {"params": {"lr": 1e-3}}}, device=torch.device("cpu"), seed=seed)
+
+    cfg, eng = make(11)
+    g = torch.Generator().manual_seed(5)
+    toks = [torch.randint(0, cfg.vocab_size, (2, 33), generator=g) for _ in range(3)]
+    batches = [(t[:, :-1].contiguous(), t[:, 1:].contiguous()) for t in toks]
+    it = itertools.cycle(batches)
+    for _ in range(2):
+        eng.train_batch(it)
+    eng.save_checkpoint(str(tmp_path))
+    after = [float(eng.train_batch(it)) for _ in range(2)]
+    _, fresh = make(11)
+    fresh.load_checkpoint(str(tmp_path))
+    assert fresh._drop_calls == 2
+    it2 = itertools.cycle(batches)
+    next(it2), next(it2)
+    resumed = [float(fresh.train_batch(it2)) for _ in range(2)]
+    assert resumed == pytest.approx(after, rel=1e-5, abs=1e-6)
