@@ -6,6 +6,7 @@
     status    <release> [--root DIR]
     logs      <release> [--root DIR] [--tail N] [-f]
     list      [--root DIR]                       (releases with chart, phase, restarts)
+    scale     <release> <replicas> [--root DIR]  (elastic releases: worker pods within min_replicas..max_replicas)
     smoke     [--gpus N] [--root DIR]            (GPU / mounts / native libraries / collective check)
     stage-data <src> <dst under /efs or /fsx> [--root DIR]
     attach    [release] [--root DIR]             (where /efs and /fsx live locally and what is in them)
@@ -83,6 +84,10 @@ def main(argv=None) -> int:
         _common(p)
     p = sub.add_parser("list")
     _common(p)
+    p = sub.add_parser("scale")
+    p.add_argument("release")
+    p.add_argument("replicas", type=int)
+    _common(p)
     p = sub.add_parser("smoke")
     p.add_argument("--gpus", type=int, default=0)
     _common(p)
@@ -105,6 +110,10 @@ def main(argv=None) -> int:
                          "restarts": st.get("restarts", 0), "pods": len(st.get("pods") or {})})
         print(json.dumps(rows, indent=1))
         return 0
+    if a.cmd == "scale":
+        ok = R.scale(a.root, a.release, a.replicas)
+        print(f'release "{a.release}" ' + (f"scaling to {a.replicas}" if ok else "not found"))
+        return 0 if ok else 1
     if a.cmd in ("smoke", "stage-data", "attach"):
         from . import tools as T
 

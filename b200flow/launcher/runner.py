@@ -15,6 +15,13 @@ environment contract the user scripts rely on:
   local "cluster address"; `engines/ray_train_api.py` spawns the workers;
 * Pod / Deployment  : one process.
 
+Elastic jobs whose `elastic_policy` gives `min_replicas < max_replicas` keep the chart's per-pod
+`restartPolicy: OnFailure` instead: a failed worker pod is restarted alone while the survivors
+re-rendezvous among themselves (torchrun's c10d rendezvous admits between min and max nodes), the
+launcher hosts the rendezvous store so that no pod's death takes it down, and `scale` changes the
+number of worker pods inside `[min_replicas, max_replicas]` while the job runs
+(charts/machine-learning/training/pytorchjob-elastic/templates/train.yaml:58-71).
+
 GPUs are sliced per pod through `CUDA_VISIBLE_DEVICES`; `/efs`- and `/fsx`-style mount paths
 are remapped under `--root`; a failed pod kills the group and the group restarts up to
 `backoff_limit` times (`restartPolicy: OnFailure`); SIGINT/SIGTERM tear everything down.
@@ -171,18 +178,8 @@ class Runner:
                 specs.append(PodSpec(name, sh, env, slices[r]))
         elif p.kind == "elastic":
             port = free_port()
-            el = p.elastic or {}
-            slices = self._gpu_slices(p.nnodes)
-            lo, hi = el.get("min_replicas", 1), el.get("max_replicas", 1)
             for r in range(p.nnodes):
-                name = f"{rel}-worker-{r}"
-                env = self._base_env(name)
-                env.update(PET_NNODES=f"{lo}:{hi}" if lo != hi else str(p.nnodes),
-                           PET_RDZV_ID=rel, PET_RDZV_BACKEND=str(el.get("rdzv_backend", "c10d")),
-                           PET_RDZV_ENDPOINT=f"127.0.0.1:{port}")
-                if p.nproc_per_node:
-                    env["PET_NPROC_PER_NODE"] = str(p.nproc_per_node)
-                specs.append(PodSpec(name, sh, env, slices[r]))
+                specs.append(self._elastic_pod(r, port, max(p.nnodes, 1)))
         elif p.kind in ("mpijob", "maskrcnn"):
             np_ = p.mpirun_np or 1
             total = visible_gpu_count()
@@ -212,6 +209,30 @@ class Runner:
             name = f"{rel}-pod"
             specs.append(PodSpec(name, sh, self._base_env(name), self._gpu_slices(1)[0]))
         return specs
+
+    def _elastic_bounds(self) -> tuple[int, int]:
+        el = self.plan.elastic or {}
+        lo, hi = int(el.get("min_replicas", 1)), int(el.get("max_replicas", 1))
+        return lo, max(lo, hi)
+
+    def _elastic_pod(self, r: int, port: int, npods: int) -> PodSpec:
+        p = self.plan
+        el = p.elastic or {}
+        lo, hi = self._elastic_bounds()
+        name = f"{p.release}-worker-{r}"
+        env = self._base_env(name)
+        env.update(PET_NNODES=f"{lo}:{hi}" if lo != hi else str(p.nnodes),
+                   PET_RDZV_ID=p.release, PET_RDZV_BACKEND=str(el.get("rdzv_backend", "c10d")),
+                   PET_RDZV_ENDPOINT=f"127.0.0.1:{port}")
+        if p.nproc_per_node:
+            env["PET_NPROC_PER_NODE"] = str(p.nproc_per_node)
+        if lo != hi:
+            # torch's dynamic rendezvous caches the trainers' bootstrap store of the FIRST round it joined; a node
+            # that joins a later round would wait forever for an address nobody publishes again.  Without the
+            # shared store every round publishes its own (rank 0 sets, the others get).
+            env.setdefault("TORCH_DISABLE_SHARE_RDZV_TCP_STORE", "1")
+        slices = self._gpu_slices(max(npods, r + 1))
+        return PodSpec(name, ["bash", str(self.state.dir / p.script_name)], env, slices[r])
 
     # ------------------------------------------------------------- execution
     def _spawn(self, spec: PodSpec) -> subprocess.Popen:
@@ -244,9 +265,13 @@ class Runner:
                 except ProcessLookupError:
                     pass
 
-    def _on_signal(self, signum, frame):
+    def stop(self) -> None:
+        """Take the release's pods down and make `run` return (what `helm uninstall` does to a running job)."""
         self._stop = True
         self._kill_all()
+
+    def _on_signal(self, signum, frame):
+        self.stop()
 
     def _log_progress(self) -> int:
         """Total bytes the pods have logged so far: the job's heartbeat."""
@@ -258,8 +283,53 @@ class Runner:
                 pass
         return total
 
-    def run(self, timeout: float | None = None, poll: float = 0.2, hang_timeout: float | None = None) -> int:
+    # ------------------------------------------------------------- admission
+    def gpus_needed(self) -> int:
+        p = self.plan
+        per = int(p.gpus_per_node or 0)
+        if p.kind in ("mpijob", "maskrcnn"):
+            return min(int(p.mpirun_np or 1), visible_gpu_count()) if per else 0
+        if p.kind == "elastic":
+            return per * min(self._elastic_bounds()[1], max(self._elastic_bounds()[0], int(p.nnodes or 1)))
+        if p.kind == "rayjob":
+            return per * int((p.ray or {}).get("workers", 1))
+        return per * int(p.nnodes or 1) if p.kind == "static" else per
+
+    def _gpus_claimed_by_others(self) -> int:
+        total = 0
+        for f in (self.root / ".b200flow" / "releases").glob("*/status.json"):
+            if f.parent.name == self.plan.release:
+                continue
+            try:
+                st = json.loads(f.read_text())
+                if st.get("phase") in ("Running", "Restarting") and st.get("runner_pid"):
+                    os.kill(int(st["runner_pid"]), 0)          # a dead runner holds nothing
+                    total += int(st.get("gpus_claimed", 0))
+            except (OSError, ValueError, ProcessLookupError, PermissionError):
+                continue
+        return total
+
+    def _admit(self, pending_timeout: float | None, poll: float) -> bool:
+        """A release stays Pending while the GPUs its pods request are held by other running releases under the
+        same root (the scheduler's side of a pod's `Pending` phase); over-subscribed requests on a box with fewer
+        GPUs than asked are admitted when nothing else runs, as before."""
+        need, have = self.gpus_needed(), visible_gpu_count()
+        t0 = time.time()
+        while need and have and not self._stop:
+            used = self._gpus_claimed_by_others()
+            if used == 0 or used + need <= have:
+                break
+            if pending_timeout is not None and time.time() - t0 > pending_timeout:
+                return False
+            time.sleep(poll)
+        self.state.write_status(gpus_claimed=need if have else 0, runner_pid=os.getpid())
+        return not self._stop
+
+    def run(self, timeout: float | None = None, poll: float = 0.2, hang_timeout: float | None = None,
+            pending_timeout: float | None = None) -> int:
         """Run to completion. Returns 0 on success, the failing exit code otherwise.
+
+        `pending_timeout`: seconds the release may wait for GPUs held by other releases before it fails (exit 126).
 
         `hang_timeout`: seconds without a single new log byte from any pod after which the group is declared
         hung (exit code 125), killed and restarted like any other failure — the local stand-in for the NCCL
@@ -271,8 +341,21 @@ class Runner:
                 old[s] = signal.signal(s, self._on_signal)
             except ValueError:      # not the main thread
                 pass
+        if not self._admit(pending_timeout, max(poll, 0.2)):
+            self.state.write_status(phase="Failed", exit_code=126, reason="Pending: GPUs not available in time")
+            for s, h in old.items():
+                signal.signal(s, h)
+            return 126
         t0 = time.time()
         rc = 1
+        lo, hi = self._elastic_bounds()
+        if self.plan.kind == "elastic" and lo < hi:
+            try:
+                return self._run_elastic(lo, hi, timeout, poll, t0)
+            finally:
+                self._kill_all()
+                for s, h in old.items():
+                    signal.signal(s, h)
         try:
             while not self._stop:
                 specs = self.pods()
@@ -321,6 +404,138 @@ class Runner:
             for s, h in old.items():
                 signal.signal(s, h)
         return rc
+
+
+    # ----------------------------------------- elastic jobs with membership change (min_replicas < max_replicas)
+    def _start_rdzv_store(self, port: int):
+        """The c10d rendezvous store lives with the launcher (the operator's side), not inside a worker pod, so any
+        pod may die.  torchrun's c10d backend falls back to a client connection when the port is already served."""
+        code = ("import sys, time\nfrom datetime import timedelta\nfrom torch.distributed import TCPStore\n"
+                f"s = TCPStore('127.0.0.1', {port}, None, True, timedelta(seconds=30), wait_for_workers=False)\n"
+                "print('rdzv store up', flush=True)\n"
+                "while True:\n    time.sleep(3600)\n")
+        log = open(self.state.dir / "rdzv_store.log", "ab")
+        pr = subprocess.Popen([os.environ.get("B2F_PYTHON", "python"), "-c", code], stdout=log,
+                              stderr=subprocess.STDOUT, start_new_session=True)
+        deadline = time.time() + 120
+        while time.time() < deadline and pr.poll() is None:
+            try:
+                with socket.create_connection(("127.0.0.1", port), timeout=0.5):
+                    return pr
+            except OSError:
+                time.sleep(0.1)
+        return pr
+
+    def scale_request(self) -> int | None:
+        f = self.state.dir / "scale"
+        try:
+            return int(f.read_text().strip())
+        except (OSError, ValueError):
+            return None
+
+    def _run_elastic(self, lo: int, hi: int, timeout, poll, t0) -> int:
+        p = self.plan
+        port = free_port()
+        backend = str((p.elastic or {}).get("rdzv_backend", "c10d"))
+        store = self._start_rdzv_store(port) if backend == "c10d" else None
+        desired = min(hi, max(lo, p.nnodes))
+        pods: dict[int, subprocess.Popen] = {}        # worker index -> running process
+        respawn_at: dict[int, float] = {}             # failed workers waiting out their back-off
+        done: set[int] = set()                        # exited 0
+        removed: set[int] = set()                     # scaled away on request
+        pod_restarts: dict[int, int] = {}
+        changes = 0
+        (self.state.dir / "scale").unlink(missing_ok=True)
+
+        def spawn(r: int):
+            spec = self._elastic_pod(r, port, hi)
+            spec.env["B2F_RESTART_COUNT"] = str(pod_restarts.get(r, 0))
+            pods[r] = self._spawn(spec)
+            self.procs = list(pods.values()) + ([store] if store is not None else [])
+
+        def publish(phase="Running"):
+            self.state.write_status(phase=phase, restarts=self.restarts, replicas=len(pods) + len(respawn_at),
+                                    desired_replicas=desired, min_replicas=lo, max_replicas=hi,
+                                    membership_changes=changes,
+                                    pods={f"{p.release}-worker-{r}": pr.pid for r, pr in pods.items()})
+
+        for r in range(desired):
+            spawn(r)
+        publish()
+        rc = 1
+        try:
+            while True:
+                if self._stop:
+                    rc = 130
+                    break
+                if timeout is not None and time.time() - t0 > timeout:
+                    rc, self._stop = 124, True
+                    break
+                want = self.scale_request()
+                if want is not None and min(hi, max(lo, want)) != desired:
+                    desired = min(hi, max(lo, want))
+                live = sorted(set(pods) | set(respawn_at))
+                if len(live) + len(done) > desired and live and not done:        # scale in: highest indices leave
+                    r = live[-1]
+                    removed.add(r)
+                    respawn_at.pop(r, None)
+                    pr = pods.pop(r, None)
+                    if pr is not None and pr.poll() is None:
+                        try:
+                            os.killpg(pr.pid, signal.SIGTERM)
+                        except ProcessLookupError:
+                            pass
+                    changes += 1
+                    publish()
+                elif len(live) < desired and not done:                            # scale out: lowest free index joins
+                    r = next(i for i in range(hi + 1) if i not in pods and i not in respawn_at)
+                    removed.discard(r)
+                    spawn(r)
+                    changes += 1
+                    publish()
+                for r, pr in list(pods.items()):
+                    code = pr.poll()
+                    if code is None:
+                        continue
+                    del pods[r]
+                    if code == 0:
+                        done.add(r)
+                        continue
+                    self.restarts += 1
+                    pod_restarts[r] = pod_restarts.get(r, 0) + 1
+                    changes += 1
+                    if self.restarts > self.max_restarts:
+                        rc = code
+                        self.state.write_status(phase="Failed", exit_code=code, restarts=self.restarts)
+                        return rc
+                    # restartPolicy OnFailure: this pod alone comes back; the others re-rendezvous meanwhile
+                    respawn_at[r] = time.time() + min(10.0, 0.5 * (2 ** min(pod_restarts[r], 4)))
+                    publish()
+                for r, at in list(respawn_at.items()):
+                    if time.time() >= at:
+                        del respawn_at[r]
+                        spawn(r)
+                        publish()
+                if not pods and not respawn_at:
+                    rc = 0 if done else 1
+                    break
+                time.sleep(poll)
+            self.state.write_status(phase="Succeeded" if rc == 0 else "Failed", exit_code=rc, restarts=self.restarts,
+                                    membership_changes=changes)
+            return rc
+        finally:
+            self.procs = list(pods.values()) + ([store] if store is not None else [])
+
+
+def scale(root: str | Path, release: str, replicas: int) -> bool:
+    """Ask a running elastic release for `replicas` worker pods (clamped to its min..max by the runner)."""
+    st = ReleaseState(Path(root), release)
+    if not st.exists():
+        return False
+    tmp = st.dir / ".scale.tmp"
+    tmp.write_text(str(int(replicas)))
+    os.replace(tmp, st.dir / "scale")
+    return True
 
 
 def uninstall(root: str | Path, release: str) -> bool:

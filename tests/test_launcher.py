@@ -194,3 +194,97 @@ def test_install_no_wait_then_status_logs_uninstall(tmp_path):
     n1 = run("logs", "bg").stdout.count("tick")
     time.sleep(1.0)
     assert run("logs", "bg").stdout.count("tick") == n1          # nothing is running any more
+
+
+def test_elastic_membership_changes_between_min_and_max_replicas(tmp_root):
+    """`elastic_policy.min_replicas < max_replicas`: the job starts on one worker pod, is scaled out to two while it
+    runs (the pods re-rendezvous through torchrun's c10d backend and the world doubles), then scaled back in; the
+    training continues across every change of membership and the release succeeds
+    (charts/machine-learning/training/pytorchjob-elastic/templates/train.yaml:58-71)."""
+    import re
+    import threading
+    import time
+
+    stub = Path(__file__).resolve().parent / "elastic_train_stub.py"
+    prog = tmp_root / "progress.txt"
+    cmd = (f"torchrun --nnodes $PET_NNODES --nproc_per_node 1 --rdzv_id $PET_RDZV_ID --rdzv_backend $PET_RDZV_BACKEND "
+           f"--rdzv_endpoint $PET_RDZV_ENDPOINT --rdzv_conf last_call_timeout=2,join_timeout=120 --max_restarts 10 "
+           f"--monitor_interval 0.5 {stub} {prog} 10000")
+    vals = _vals(cmd, resources={"nnodes": 1, "nproc_per_node": 1})
+    vals["elastic_policy"] = {"rdzv_backend": "c10d", "rdzv_port": 44000, "min_replicas": 1, "max_replicas": 2}
+    plan = render_job("pytorchjob-elastic", "el", [vals], root=tmp_root, strict_exit=True)
+    assert plan.env is not None
+    run = R.Runner(plan, tmp_root, max_restarts=5)
+    out = {}
+    th = threading.Thread(target=lambda: out.setdefault("rc", run.run(timeout=400)))
+    th.start()
+
+    def worlds():
+        txt = "".join(R.logs(tmp_root, "el").values())
+        return [int(m) for m in re.findall(r"step \d+ world (\d+)", txt)]
+
+    def wait_for(pred, secs):
+        end = time.time() + secs
+        while time.time() < end and not pred():
+            time.sleep(0.5)
+        return pred()
+
+    try:
+        assert wait_for(lambda: len(worlds()) >= 3, 120), R.logs(tmp_root, "el")
+        assert set(worlds()) == {1}
+        assert "PET_NNODES" not in "".join(R.logs(tmp_root, "el").values())
+        assert R.scale(tmp_root, "el", 5)                                   # clamped to max_replicas = 2
+        assert wait_for(lambda: 2 in worlds(), 180), R.logs(tmp_root, "el")
+        st = R.status(tmp_root, "el")
+        assert st["desired_replicas"] == 2 and st["replicas"] == 2 and st["membership_changes"] >= 1
+        n2 = len(worlds())
+        assert R.scale(tmp_root, "el", 1)
+        assert wait_for(lambda: 1 in worlds()[n2:], 180), R.logs(tmp_root, "el")
+        steps = [int(m) for m in re.findall(r"step (\d+) world", R.logs(tmp_root, "el")["el-worker-0"])]
+        assert steps == sorted(steps) and len(set(steps)) >= len(steps) - 4     # progress carried across worlds
+        Path(str(prog) + ".stop").write_text("1")                           # let it finish
+    finally:
+        if not wait_for(lambda: not th.is_alive(), 120):
+            run.stop()
+        th.join(timeout=60)
+    assert out.get("rc") == 0, (out, R.logs(tmp_root, "el"))
+    assert R.status(tmp_root, "el")["phase"] == "Succeeded"
+
+
+def test_pipeline_pending_bound_and_phase_polling(tmp_root, monkeypatch):
+    """KFP `wait_for_pods` (kfp/components/src/helm-charts-component/helm_charts_component.py:135-197): a release
+    whose GPUs are held by another running release stays Pending for at most `pod_error_timeout`; a running one is
+    polled every `pod_check_secs`; `pod_complete_timeout` bounds the run."""
+    import threading
+    import time
+
+    monkeypatch.setenv("CUDA_VISIBLE_DEVICES", "0,1")            # a two-GPU box as far as the scheduler is concerned
+    hold = render_job("pytorchjob-distributed", "holder",
+                      [_vals("sleep 30", resources={"nnodes": 1, "limits": {"nvidia.com/gpu": 2}})], root=tmp_root)
+    holder = R.Runner(hold, tmp_root)
+    th = threading.Thread(target=lambda: holder.run(timeout=60))
+    th.start()
+    try:
+        end = time.time() + 30
+        while time.time() < end and R.status(tmp_root, "holder").get("phase") != "Running":
+            time.sleep(0.1)
+        assert R.status(tmp_root, "holder")["gpus_claimed"] == 2
+        msgs = []
+        want_gpu = {"release_name": "p-pend", "chart": "pytorchjob-distributed", "pod_error_timeout": 2, "pod_check_secs": 1,
+                    "values": _vals("echo ran", resources={"nnodes": 1, "limits": {"nvidia.com/gpu": 1}})}
+        t0 = time.time()
+        assert run_pipeline([want_gpu], root=str(tmp_root), log=msgs.append) == "Failure"
+        assert 2 <= time.time() - t0 < 20
+        assert any("phase: Pending" in m for m in msgs) and "ran" not in "".join(R.logs(tmp_root, "p-pend").values())
+        cpu_only = {"release_name": "p-cpu", "chart": "data-process", "pod_check_secs": 0.2,
+                    "values": {"process": {"command": ["bash -c"], "args": ["'sleep 1; echo fine'"]}}}
+        msgs.clear()
+        assert run_pipeline([cpu_only], root=str(tmp_root), log=msgs.append) == "Success"     # needs no GPU: admitted at once
+        assert sum("phase: Running" in m for m in msgs) >= 2                                   # polled while running
+    finally:
+        holder.stop()
+        th.join(timeout=30)
+    slow = {"release_name": "p-slow", "chart": "data-process", "pod_complete_timeout": 1, "max_restarts": 0,
+            "values": {"process": {"command": ["sleep"], "args": ["30"]}}}
+    t0 = time.time()
+    assert run_pipeline([slow], root=str(tmp_root), log=lambda m: None) == "Failure" and time.time() - t0 < 25

@@ -65,7 +65,7 @@ def main(out_md: Path, out_listing: Path) -> None:
             if m:
                 flush()
                 cur, lines = m.group(1), []
-            elif cur and re.search(r"/\*[0-9a-f]{4}\*/", ln):
+            elif cur and re.search(r"/\*[0-9a-f]{4,}\*/", ln):      # addresses grow past 4 hex digits after 64 KB of code
                 lines.append(ln)
         flush()
     with out_md.open("w") as f:
@@ -76,6 +76,35 @@ def main(out_md: Path, out_listing: Path) -> None:
     out_listing.write_text("# SASS excerpts around the first tensor-core / multimem instruction\n\n" + "\n".join(listing))
 
 
+FULL = {   # complete listings committed for the kernels the fused paths rest on (K0, K3/K4, K5, K7)
+    "kernels_gemm2": "k0_gemm2", "comm_fused_gemm": "k3_k4_fused_gemm", "kernels_attention": "k7_attention",
+    "kernels_gemm_mx": "k0_gemm_mxfp8", "comm_fused_moe": "k5_fused_moe", "comm_collectives": "k1_k2_collectives",
+}
+
+
+def full_listings(out_dir: Path) -> list[str]:
+    """`cuobjdump -sass` of whole objects, instruction text only (encodings stripped to keep the files readable)."""
+    out_dir.mkdir(parents=True, exist_ok=True)
+    done = []
+    for stem, name in FULL.items():
+        obj = OBJ / f"{stem}.o"
+        if not obj.exists():
+            continue
+        sass = subprocess.run(["cuobjdump", "-sass", str(obj)], capture_output=True, text=True).stdout
+        keep = []
+        for ln in sass.splitlines():
+            if "Function :" in ln:
+                keep.append("\n" + ln.strip())
+            else:
+                m = re.search(r"/\*([0-9a-f]{4,})\*/\s+(.*?)\s*/\* 0x", ln)
+                if m:
+                    keep.append(f"/*{m.group(1)}*/ {m.group(2)}")
+        (out_dir / f"{name}.sass").write_text("\n".join(keep) + "\n")
+        done.append(name)
+    return done
+
+
 if __name__ == "__main__":
     main(ROOT / "profiles" / "sass_summary.md", ROOT / "profiles" / "sass_excerpts.md")
     print("wrote profiles/sass_summary.md, profiles/sass_excerpts.md")
+    print("full listings:", full_listings(ROOT / "profiles" / "sass"))
