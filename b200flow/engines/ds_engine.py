@@ -38,7 +38,7 @@ _KNOWN = {"train_micro_batch_size_per_gpu", "gradient_accumulation_steps", "zero
           "bf16", "fp16", "gradient_clipping", "optimizer", "wall_clock_breakdown",
           "train_batch_size", "steps_per_print", "scheduler", "fused_collectives",
           "activation_checkpointing", "sequence_parallel", "expert_parallel_size", "flops_profiler",
-          "comms_logger", "sequence_parallel_size", "checkpoint"}
+          "comms_logger", "sequence_parallel_size", "checkpoint", "pipeline"}
 
 
 def split_layers(num_layers: int, stages: int) -> list[tuple[int, int]]:
@@ -92,6 +92,13 @@ class TrainEngine:
                 raise ValueError(f"ds_config: train_batch_size {tbs} != micro batch {self.micro_batch} x accumulation "
                                  f"steps {self.gas} x data-parallel size {dp_world}")
         self.stage = ps.pp_rank if ps else 0
+        # pipeline bubble filling: split backward into dgrad and deferred wgrad (parallel/pipeline.py `schedule_zb`);
+        # "pipeline": {"zero_bubble": false} restores plain 1F1B
+        self.zero_bubble = pp_world > 1 and bool((config.get("pipeline") or {}).get("zero_bubble", True))
+        if self.zero_bubble:
+            from ..ops import gemm as _G
+
+            _G.DEFER_CAPABLE = True
 
         fused_tp = None
         if tp_world > 1 and use_fused:
@@ -297,7 +304,8 @@ class TrainEngine:
             seq = batches[0][0].shape[1]
             tm and tm.start("pipeline_fwd_bwd")
             losses = PP.run_1f1b(self.stage, self.pp_world, self.gas,
-                                 lambda i, act: self._forward_micro(batches[i], act), self._p2p(seq))
+                                 lambda i, act: self._forward_micro(batches[i], act), self._p2p(seq),
+                                 zero_bubble=self.zero_bubble)
             tm and tm.stop("pipeline_fwd_bwd")
         tm and tm.start("step")
         scale = self._optimizer_step()

@@ -88,16 +88,82 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_maj
     return out
 
 
+# ---- deferred weight gradients (pipeline bubble filling) --------------------------------------------------------
+# A backward pass is two independent halves per linear: dgrad (needed by the previous layer / pipeline stage right
+# away) and wgrad (needed only by the optimizer).  Inside `defer_wgrad(queue)` every wgrad GEMM whose target is a
+# `main_grad` buffer is queued instead of launched; `run_deferred(queue)` launches them later - the pipeline schedule
+# runs them where a stage would otherwise idle (parallel/pipeline.py, "W" instructions).
+DEFER_CAPABLE = False            # engines that split backward set this, so CPU linears take the same autograd node
+_DEFERRED: list | None = None
+
+
+class defer_wgrad:
+    def __init__(self, queue: list):
+        self.queue = queue
+
+    def __enter__(self):
+        global _DEFERRED
+        self._prev, _DEFERRED = _DEFERRED, self.queue
+        return self.queue
+
+    def __exit__(self, *exc):
+        global _DEFERRED
+        _DEFERRED = self._prev
+
+
+def run_deferred(queue: list) -> None:
+    global _DEFERRED
+    prev, _DEFERRED = _DEFERRED, None
+    try:
+        with torch.no_grad():
+            for x2, dy2, weight in queue:
+                _wgrad(x2, dy2, weight)
+    finally:
+        _DEFERRED = prev
+        queue.clear()
+
+
 def _wgrad(x2: torch.Tensor, dy2: torch.Tensor, weight: torch.Tensor):
     """dW[N, K] = dyᵀ x, accumulated into weight.main_grad when present."""
     main_grad = getattr(weight, "main_grad", None)
     if main_grad is not None:
-        gemm(dy2, x2, a_mn_major=True, b_mn_major=True, out=main_grad, accumulate=True)
+        if _DEFERRED is not None:
+            _DEFERRED.append((x2, dy2, weight))
+            return None
+        if dy2.is_cuda:
+            gemm(dy2, x2, a_mn_major=True, b_mn_major=True, out=main_grad, accumulate=True)
+        else:
+            main_grad.add_((dy2.t().to(main_grad.dtype) @ x2.to(main_grad.dtype)))
         cb = getattr(weight, "grad_ready", None)   # DDP bucket bookkeeping
         if cb is not None:
             cb()
         return None
+    if not dy2.is_cuda:
+        return dy2.t() @ x2
     return gemm(dy2, x2, a_mn_major=True, b_mn_major=True)
+
+
+class _LinearCPU(torch.autograd.Function):
+    """The CPU (oracle) linear as ONE node with the same dgrad / wgrad split as the GPU node, so that schedules which
+    defer weight gradients are testable over gloo."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, residual):
+        x2 = x.reshape(-1, x.shape[-1])
+        y = torch.nn.functional.linear(x2, weight, bias)
+        if residual is not None:
+            y = y + residual.reshape(-1, weight.shape[0])
+        ctx.save_for_backward(x2, weight)
+        ctx.has_bias, ctx.has_res, ctx.x_shape = bias is not None, residual is not None, x.shape
+        return y.reshape(*x.shape[:-1], weight.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, weight = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1])
+        dx = (dy2 @ weight).reshape(ctx.x_shape) if ctx.needs_input_grad[0] else None
+        dw = _wgrad(x2, dy2, weight)
+        return dx, dw, (dy2.sum(0) if ctx.has_bias else None), (dy if ctx.has_res else None)
 
 
 class _Linear(torch.autograd.Function):
@@ -128,6 +194,8 @@ def linear(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor | None = No
            residual: torch.Tensor | None = None) -> torch.Tensor:
     """y = x @ weightᵀ (+ bias) (+ residual) on the tcgen05 GEMM."""
     if not x.is_cuda:
+        if DEFER_CAPABLE and getattr(weight, "main_grad", None) is not None:
+            return _LinearCPU.apply(x, weight, bias, residual)
         from . import ref
         return ref.linear(x, weight, bias, residual)
     return _Linear.apply(x, weight, bias, residual)

@@ -10,6 +10,26 @@ steady-state send with the receive that the peer is blocked on).
 
 `schedule_1f1b` is a pure function returning the instruction list of one stage, so
 the schedule itself is unit-tested without any process group.
+
+Bubble filling (`schedule_zb`).  A backward pass is two halves per linear: dgrad, which the
+previous stage is waiting for, and wgrad, which only the optimizer needs.  With the halves split
+("B" = dgrad only, "W" = the queued wgrad GEMMs of one micro-batch, `ops.gemm.defer_wgrad`) the
+1F1B order is kept, stage s runs W_j right after B_{j+s}, and whatever is left runs at the end.
+The last stage then hands the final gradients upstream before doing its last weight gradients,
+and earlier stages fill their wait for the next gradient with weight gradients: the idle time per
+stage falls from (p-1)(f + b) to (p-1)(f + dgrad - wgrad), i.e. to about a third for
+f = dgrad = wgrad (the "ZB-H1" schedule of the zero-bubble pipeline papers); `simulate` is the
+event model the unit tests hold both schedules against.
+
+Why the exchanges stay rendezvous-at-need on the compute stream.  NCCL send / recv are kernels
+that occupy SMs until the peer shows up.  The GEMMs here are persistent kernels with one CTA (pair)
+per SM and a static tile loop, so a receive posted far ahead of its data, or a send posted far ahead
+of its receive, parks a communication kernel on an SM for tens of milliseconds and every GEMM in that
+window loses the SM to a straggler CTA.  Posting each send together with the receive the stage needs
+next keeps those kernels short-lived (both sides arrive within microseconds of each other), and the
+time a stage spends inside them is time it had to wait for its peer's result anyway: per micro-batch
+the exposed cost is one 16 MiB NVLink transfer (tens of microseconds) against ~100 ms of compute.
+What the schedule can win is the bubble, hence `schedule_zb`.
 """
 from __future__ import annotations
 
@@ -36,8 +56,56 @@ def schedule_1f1b(stage: int, stages: int, micro_batches: int) -> list[Instr]:
     return out
 
 
+def schedule_zb(stage: int, stages: int, micro_batches: int) -> list[Instr]:
+    """1F1B order with split backward: "B" is dgrad only, "W" the deferred weight gradients of a micro-batch;
+    stage s runs W_j right after B_{j+s} and the remainder at the end."""
+    out, nb, nw = [], 0, 0
+    for ins in schedule_1f1b(stage, stages, micro_batches):
+        out.append(ins)
+        if ins.op == "B":
+            nb += 1
+            if nb - nw > stage:
+                out.append(Instr("W", nw))
+                nw += 1
+    out += [Instr("W", j) for j in range(nw, micro_batches)]
+    return out
+
+
 def bubble_fraction(stages: int, micro_batches: int) -> float:
     return (stages - 1) / (micro_batches + stages - 1)
+
+
+def simulate(stages: int, micro_batches: int, schedule, f: float = 1.0, dgrad: float = 1.0, wgrad: float = 1.0) -> float:
+    """Makespan of one batch under the dependency model: F_i on stage s after F_i on s-1; B_i on s after F_i on s and
+    B_i on s+1; W_i after B_i.  A schedule without "W" instructions pays dgrad + wgrad inside "B"."""
+    lists = [schedule(s, stages, micro_batches) for s in range(stages)]
+    split = any(i.op == "W" for l in lists for i in l)
+    done: dict[tuple, float] = {}
+    t, idx = [0.0] * stages, [0] * stages
+    moved = True
+    while moved:
+        moved = False
+        for s in range(stages):
+            while idx[s] < len(lists[s]):
+                ins = lists[s][idx[s]]
+                deps = []
+                if ins.op == "F" and s > 0:
+                    deps.append(("F", s - 1, ins.mb))
+                if ins.op == "B":
+                    deps.append(("F", s, ins.mb))
+                    if s < stages - 1:
+                        deps.append(("B", s + 1, ins.mb))
+                if ins.op == "W":
+                    deps.append(("B", s, ins.mb))
+                if any(d not in done for d in deps):
+                    break
+                start = max([t[s]] + [done[d] for d in deps])
+                dur = {"F": f, "B": dgrad + (0.0 if split else wgrad), "W": wgrad}[ins.op]
+                t[s] = done[(ins.op, s, ins.mb)] = start + dur
+                idx[s] += 1
+                moved = True
+    assert all(idx[s] == len(lists[s]) for s in range(stages)), "schedule deadlocks"
+    return max(t)
 
 
 class P2P:
@@ -73,22 +141,31 @@ class P2P:
         return act_in, grad_in
 
 
-def run_1f1b(stage: int, stages: int, micro_batches: int, forward_fn, p2p: P2P):
+def run_1f1b(stage: int, stages: int, micro_batches: int, forward_fn, p2p: P2P, zero_bubble: bool = False):
     """Execute one training batch on this stage.
 
     forward_fn(mb_index, activation_in_or_None) -> output tensor (activation for the next
     stage, or the scalar loss on the last stage).  Returns the list of last-stage losses
     (empty on other stages).  Gradients accumulate into the parameters' main_grad.
+    `zero_bubble`: run `schedule_zb` - backward passes queue their weight-gradient GEMMs and the
+    "W" instructions launch them later.
     """
+    from ..ops import gemm as G
+
     first, last = stage == 0, stage == stages - 1
-    instrs = schedule_1f1b(stage, stages, micro_batches)
+    instrs = (schedule_zb if zero_bubble else schedule_1f1b)(stage, stages, micro_batches)
     inputs: dict[int, torch.Tensor] = {}
     outputs: dict[int, torch.Tensor] = {}
+    wqueues: dict[int, list] = {}
     losses = []
     pending_act = None      # activation received ahead of its forward
     pending_grad = None     # gradient received ahead of its backward
     for k, ins in enumerate(instrs):
-        nxt = instrs[k + 1] if k + 1 < len(instrs) else None
+        # the exchange after this instruction is paired with what the next F / B needs ("W" has no traffic)
+        nxt = next((i for i in instrs[k + 1:] if i.op != "W"), None)
+        if ins.op == "W":
+            G.run_deferred(wqueues.pop(ins.mb))
+            continue
         if ins.op == "F":
             if not first:
                 act = pending_act
@@ -114,13 +191,18 @@ def run_1f1b(stage: int, stages: int, micro_batches: int, forward_fn, p2p: P2P):
         else:
             out = outputs.pop(ins.mb)
             act = inputs.pop(ins.mb)
-            if last:
-                out.backward()
-            else:
+            grad = None
+            if not last:
                 grad = pending_grad
                 pending_grad = None
                 if grad is None:
                     _, grad = p2p.exchange(recv_bwd=True)
+            if zero_bubble:
+                with G.defer_wgrad(wqueues.setdefault(ins.mb, [])):
+                    out.backward() if last else torch.autograd.backward(out, grad)
+            elif last:
+                out.backward()
+            else:
                 torch.autograd.backward(out, grad)
             dact = act.grad if act is not None else None
             want_act = (not first) and nxt is not None and nxt.op == "F"
@@ -130,6 +212,7 @@ def run_1f1b(stage: int, stages: int, micro_batches: int, forward_fn, p2p: P2P):
                 pending_act = a
             if g is not None:
                 pending_grad = g
+    assert not wqueues, "weight gradients left in the queue"
     return losses
 
 

@@ -51,7 +51,7 @@ def _mm_dgrad(dy, w):
 
 def _mm_wgrad(x, dy, w):
     """Returns dW, or None when accumulated into w.main_grad by the GEMM epilogue."""
-    if dy.is_cuda:
+    if dy.is_cuda or (G._DEFERRED is not None and getattr(w, "main_grad", None) is not None):
         return G._wgrad(x, dy, w)
     return dy.t() @ x
 

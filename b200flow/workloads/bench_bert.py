@@ -28,7 +28,7 @@ def _batches(cfg, n, batch, seq, gen):
     return out
 
 
-def run_bert_bench(args, rank, world, dev, ClockSampler):
+def run_bert_bench(args, rank, world, dev, ClockSampler, emit=None):
     from b200flow.engines.accelerate_api import Accelerator
     from b200flow.models.bert import BertForPreTraining, bert_config
     from b200flow.ops import _lib
@@ -90,7 +90,7 @@ def run_bert_bench(args, rank, world, dev, ClockSampler):
     ms_e2e = timed(lambda: step(host, True), args.steps)
     if rank == 0:
         gb = batch * world
-        print(json.dumps({
+        (emit or (lambda o: print(json.dumps(o))))({
             "metric": "BERT-large pretraining samples/s", "value": gb * args.steps / (ms / 1e3),
             "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -103,7 +103,7 @@ def run_bert_bench(args, rank, world, dev, ClockSampler):
                     "h2d_bytes_per_step": sum(v.numel() * v.element_size() for v in host[0].values()),
                     "d2h_bytes_per_step": 4},
             "gpu_launches": launches, "loss_first_last": [first, last],
-            "native_libs": _lib.loaded_libraries()}))
+            "native_libs": _lib.loaded_libraries()})
     if world > 1:
         dist.destroy_process_group()
     return 0

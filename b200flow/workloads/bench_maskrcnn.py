@@ -13,7 +13,7 @@ import torch
 import torch.distributed as dist
 
 
-def run_maskrcnn_bench(args, rank, world, dev, ClockSampler):
+def run_maskrcnn_bench(args, rank, world, dev, ClockSampler, emit=None):
     from b200flow.data.synthetic import coco_like
     from b200flow.models.maskrcnn import MaskRCNN, MaskRCNNConfig
     from b200flow.ops import _lib
@@ -86,7 +86,7 @@ def run_maskrcnn_bench(args, rank, world, dev, ClockSampler):
     if rank == 0:
         gb = batch * world
         h2d = host[0][0].numel() * 2 + sum(v.numel() * v.element_size() for t in host[0][1] for v in t.values())
-        print(json.dumps({
+        (emit or (lambda o: print(json.dumps(o))))({
             "metric": "Mask R-CNN R50-FPN training images/s", "value": gb * args.steps / (ms / 1e3),
             "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -98,7 +98,7 @@ def run_maskrcnn_bench(args, rank, world, dev, ClockSampler):
             "e2e": {"value": gb * args.steps / (ms_e2e / 1e3), "unit": "images/s",
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
             "gpu_launches": launches, "loss_first_last": [first, last],
-            "native_libs": _lib.loaded_libraries()}))
+            "native_libs": _lib.loaded_libraries()})
     if world > 1:
         dist.destroy_process_group()
     return 0

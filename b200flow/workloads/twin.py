@@ -255,7 +255,27 @@ def run_twin(args, rank, world, dev, ClockSampler):
         batch = args.micro_batch if args.micro_batch > 1 else 64
         cfg = BertConfig(vocab_size=30592, hidden_size=1024, num_hidden_layers=24, num_attention_heads=16,
                          intermediate_size=4096, max_position_embeddings=512, attn_implementation="sdpa")
-        model = BertForPreTraining(cfg).to(dev, torch.bfloat16)
+        hf = BertForPreTraining(cfg).to(dev, torch.bfloat16)
+
+        class _GatheredHeads(nn.Module):
+            """HF encoder + heads with the MLM decoder applied to the masked positions only - the same work the
+            b200flow model does (NVIDIA-style `masked_lm_positions`), so the two arms are like for like."""
+
+            def __init__(self, m):
+                super().__init__()
+                self.m = m
+
+            def forward(self, input_ids, token_type_ids, attention_mask, labels, next_sentence_label):
+                o = self.m.bert(input_ids=input_ids, token_type_ids=token_type_ids, attention_mask=attention_mask)
+                seq_out, pooled = o[0], o[1]
+                flat = labels.reshape(-1)
+                pos = (flat != -100).nonzero().squeeze(-1)
+                logits = self.m.cls.predictions(seq_out.reshape(-1, seq_out.shape[-1])[pos])
+                mlm = F.cross_entropy(logits.float(), flat[pos])
+                nsp = F.cross_entropy(self.m.cls.seq_relationship(pooled).float(), next_sentence_label)
+                return mlm + nsp
+
+        model = _GatheredHeads(hf)
         gas = 1
         gen = torch.Generator().manual_seed(77 + rank)
 
@@ -270,10 +290,10 @@ def run_twin(args, rank, world, dev, ClockSampler):
                     "labels": labels, "next_sentence_label": torch.randint(0, 2, (batch,), generator=gen)}
 
         def loss_fn(mod, b):
-            return mod(**b).loss
+            return mod(**b)
         metric, unit, per_step = "BERT-large pretraining samples/s", "samples/s", batch
         name = "bert-large"
-        notes.append("HF BertForPreTraining(sdpa): decoder over all positions (HF has no masked-position gather)")
+        notes.append("HF BertForPreTraining(sdpa) encoder and heads; MLM decoder on the masked positions only, as in the b200flow arm")
     else:
         seq, batch, gas = args.seq, args.micro_batch, args.gas
         model = TwinLlama(32000, 4096, 32, 32, 11008, seq, torch.bfloat16, dev)
@@ -322,8 +342,9 @@ def run_twin(args, rank, world, dev, ClockSampler):
         opt.zero_grad(set_to_none=True)
         return float(loss) if read_loss else loss
 
+    warm_loss = None
     for _ in range(args.warmup):
-        step(devb, True)
+        warm_loss = step(devb, True)
     with ClockSampler(torch.cuda.current_device()) as clocks:
         ms = _timed(lambda: step(devb, False), args.steps, world, dev)
     ms_e2e = _timed(lambda: step(host, True), args.steps, world, dev)
@@ -341,7 +362,7 @@ def run_twin(args, rank, world, dev, ClockSampler):
             "e2e": {"value": total * args.steps / (ms_e2e / 1e3), "unit": unit,
                     "h2d_bytes_per_step": sum(v.numel() * v.element_size() for mb in host[0] for v in mb.values()),
                     "d2h_bytes_per_step": 4},
-            "gpu_launches": 0}))
+            "gpu_launches": 0, "loss_after_warmup": warm_loss}))
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -46,7 +46,44 @@ def parse_args():
     ap.add_argument("--tp", type=int, default=0, help="override the tensor-parallel size")
     ap.add_argument("--pp", type=int, default=0, help="override the pipeline-parallel size")
     ap.add_argument("--profile", default="", help="write a torch.profiler kernel table of one extra step to this file")
+    ap.add_argument("--baseline", default="auto", choices=["auto", "none"],
+                    help="auto: first time the stock arm of the same workload in a subprocess (N=1: --impl twin, torch nn + "
+                         "cuBLAS + SDPA + fused AdamW; N>1: this engine with NCCL collectives around the GEMMs, --no-fused) "
+                         "and report vs_baseline = value / that")
+    ap.add_argument("--baseline-steps", type=int, default=10)
     return ap.parse_args()
+
+
+def stock_arm(args, world: int) -> dict | None:
+    """Runs the comparison arm BEFORE this process touches the GPU, one subprocess per rank (they form their own
+    process group on another port), so its memory is gone when the measured arm starts.  Returns rank 0's JSON line
+    (other ranks: None).  The reference itself has nothing installable (see `reference_arm`); this is what its user
+    would get from the stock libraries on this box."""
+    if args.baseline == "none" or args.impl != "b200flow" or args.no_fused:
+        return None
+    cmd = [sys.executable, str(Path(__file__).resolve()), "--gpus", str(world), "--steps",
+           str(min(args.steps, args.baseline_steps) if args.steps >= 10 else args.steps), "--warmup", str(args.warmup),
+           "--workload", args.workload, "--seq", str(args.seq), "--micro-batch", str(args.micro_batch),
+           "--gas", str(args.gas), "--baseline", "none"]
+    if args.tp or args.pp:
+        cmd += ["--tp", str(args.tp), "--pp", str(args.pp)]
+    # Llama at N > 1: torch has no TP/PP engine to call, so the stock arm is this engine with NCCL collectives around
+    # the same GEMMs; the DP-only workloads (BERT, Mask R-CNN, MoE) have a stock twin at every N
+    cmd += ["--no-fused"] if (world > 1 and args.workload.startswith("llama")) else ["--impl", "twin"]
+    env = dict(os.environ)
+    if world > 1:
+        env["MASTER_PORT"] = str(int(env.get("MASTER_PORT", "29500")) + 17)
+    try:
+        res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=1500)
+        for line in reversed(res.stdout.strip().splitlines()):
+            if line.startswith("{"):
+                return json.loads(line)
+        if int(os.environ.get("RANK", "0")) == 0:
+            return {"error": f"stock arm exit {res.returncode}: {res.stderr.strip()[-300:]}"}
+    except Exception as e:  # noqa: BLE001 - the measured arm must still run
+        if int(os.environ.get("RANK", "0")) == 0:
+            return {"error": repr(e)[:300]}
+    return None
 
 
 class ClockSampler:
@@ -106,24 +143,53 @@ def reference_arm(args):
     return 0
 
 
+def attach_baseline(out: dict, base: dict | None, world: int) -> None:
+    """vs_baseline = value / the stock arm's value measured just before on the same GPUs; both numbers, the stock
+    arm's clocks and (same engine, same seed and data: N > 1) the agreement of the two loss curves after warm-up."""
+    if not base:
+        return
+    if "value" not in base:
+        out["baseline"] = base
+        return
+    out["baseline"] = {"impl": base.get("impl"), "value": base["value"], "unit": base.get("unit"),
+                       "steps": base.get("steps"), "ms_per_step": base.get("ms_per_step"),
+                       "clocks": base.get("clocks"), "e2e_value": (base.get("e2e") or {}).get("value"),
+                       "what": ("stock twin: torch nn / HF / torchvision modules, cuBLAS + cuDNN, fused AdamW, torch DDP over NCCL"
+                                if base.get("impl") == "twin" else
+                                "same engine and GEMM kernels, NCCL collectives instead of the fused peer-memory kernels")}
+    out["vs_baseline"] = out["value"] / base["value"] if base["value"] else None
+    a, b = out.get("loss_after_warmup"), base.get("loss_after_warmup")
+    if world > 1 and a is not None and b is not None and base.get("impl") != "twin":
+        rel = abs(a - b) / max(abs(b), 1e-6)
+        out["loss_parity"] = {"fused": a, "nccl": b, "rel_diff": rel, "ok": rel <= 1e-2}
+        if rel > 1e-2:
+            print(f"WARNING: fused and NCCL loss after warm-up differ by {rel:.3e} (> 1e-2)", file=sys.stderr)
+
+
 def main():
     args = parse_args()
     if args.impl == "reference":
         return reference_arm(args)
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world} (launch with torchrun)"
+    base = stock_arm(args, world)
 
     import torch
     import torch.distributed as dist
 
     from b200flow.parallel.groups import ParallelState, init_distributed
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world} (launch with torchrun)"
     rank, local_rank = 0, 0
     if world > 1:
         rank, local_rank, world = init_distributed("nccl")
     else:
         torch.cuda.set_device(0)
     dev = torch.device("cuda", torch.cuda.current_device())
+
+    def emit(out: dict) -> None:
+        attach_baseline(out, base, world)
+        print(json.dumps(out))
 
     if args.impl == "twin":
         from b200flow.workloads.twin import run_twin
@@ -133,12 +199,12 @@ def main():
     if args.workload.startswith("maskrcnn"):
         from b200flow.workloads.bench_maskrcnn import run_maskrcnn_bench
 
-        return run_maskrcnn_bench(args, rank, world, dev, ClockSampler)
+        return run_maskrcnn_bench(args, rank, world, dev, ClockSampler, emit)
 
     if args.workload.startswith("bert"):
         from b200flow.workloads.bench_bert import run_bert_bench
 
-        return run_bert_bench(args, rank, world, dev, ClockSampler)
+        return run_bert_bench(args, rank, world, dev, ClockSampler, emit)
 
     from b200flow.engines.ds_engine import initialize
     from b200flow.models.gpt import config_from_preset
@@ -215,6 +281,7 @@ def main():
     losses = []
     for _ in range(args.warmup):
         losses.append(float(engine.train_batch(it_dev)))
+    loss_warm = losses[-1] if losses else None
     _lib.reset_launch_count()
     with ClockSampler(torch.cuda.current_device()) as clocks:
         ms = timed(lambda: engine.train_batch(it_dev), args.steps)
@@ -249,8 +316,12 @@ def main():
                   else f"{args.workload} tokens/s"),
             "value": val, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "impl": "b200flow",
+            # N = 1, 2, 4 split one global batch of 16 sequences over more GPUs (strong); N = 8 adds the DP = 2 replica
+            # on top of the N = 4 topology with its own 16 sequences (weak from 4 to 8)
+            "scaling": "strong" if world <= 4 and not is_moe else "weak",
+            "vs_baseline": None,
+            "dtype": "fp8(e4m3 expert GEMMs)+bf16" if is_moe else "bf16", "data": "synthetic",
+            "impl": "b200flow" if not args.no_fused else "b200flow-nccl-collectives",
             "config": {"model": args.workload, "global_batch": B * args.gas * dp, "seq_len": S,
                        "micro_batch": B, "grad_accum": args.gas,
                        "parallelism": (ps.topo.describe() if ps else "tp1pp1dp1") + "+zero1+sp",
@@ -263,9 +334,10 @@ def main():
             "gpu_launches": launches,
             "model_tflops_per_gpu": model_tflops / world,
             "loss_first_last": [losses[0] if losses else None, e2e_loss[-1] if e2e_loss else None],
+            "loss_after_warmup": loss_warm,
             "native_libs": _lib.loaded_libraries(),
         }
-        print(json.dumps(out))
+        emit(out)
     if world > 1:
         dist.destroy_process_group()
     return 0

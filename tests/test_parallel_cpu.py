@@ -202,6 +202,33 @@ def test_1f1b_schedule_shape():
     assert abs(bubble_fraction(2, 8) - 1 / 9) < 1e-9
 
 
+def test_zero_bubble_schedule_fills_the_pipeline_bubble():
+    """`schedule_zb`: same F / B order as 1F1B, one W per micro-batch after its B, W_j at most `stage` backward passes
+    late; in the event model the idle time falls from (p-1)(f+b) to (p-1)(f + dgrad - wgrad)."""
+    from b200flow.parallel.pipeline import schedule_zb, simulate
+
+    for stages in (2, 4, 8):
+        for m in (1, 4, 16):
+            for s in range(stages):
+                zb = schedule_zb(s, stages, m)
+                assert [i for i in zb if i.op != "W"] == schedule_1f1b(s, stages, m)
+                assert sorted(i.mb for i in zb if i.op == "W") == list(range(m))
+                pos = {(i.op, i.mb): k for k, i in enumerate(zb)}
+                assert all(pos[("B", j)] < pos[("W", j)] for j in range(m))
+                done_b = 0
+                for i in zb:           # never more than stage + 1 micro-batches of queued weight gradients
+                    done_b += i.op == "B"
+                    if i.op == "W":
+                        assert done_b - i.mb <= s + 1
+            if m >= stages:
+                base, zbt = simulate(stages, m, schedule_1f1b), simulate(stages, m, schedule_zb)
+                assert base == pytest.approx(3 * m + 3 * (stages - 1))
+                assert zbt == pytest.approx(3 * m + (stages - 1))
+    # the bench topology: 2 stages x 16 micro-batches, 5.9 % bubble -> 2.0 %
+    assert simulate(2, 16, schedule_1f1b) / 48 - 1 == pytest.approx(3 / 48)
+    assert simulate(2, 16, schedule_zb) / 48 - 1 == pytest.approx(1 / 48)
+
+
 def _ulysses_worker(rank, world, port, q_out):
     import torch.distributed as dist
     from b200flow.ops import ref
