@@ -322,6 +322,17 @@ class MoELayer(nn.Module):
         c = max(self.min_cap, math.ceil(tokens / self.E * cf * self.top_k))
         return (c + 7) // 8 * 8
 
+    def _use_k5(self, x, C) -> bool:
+        import os
+
+        from . import fused_moe as FM
+
+        if not (self.fp8 and x.is_cuda and self.fused and os.environ.get("B2F_FUSED_MOE", "1") == "1"):
+            return False
+        if self.ep.world > 1 and self.ep.comm is None:
+            return False
+        return FM.supported(self.hidden, self.ffn, C, x.shape[0])
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         T, H = x.shape
         C = self.capacity(T)
@@ -339,6 +350,15 @@ class MoELayer(nn.Module):
         else:
             gate, aux, expert, slot, counts = _Gate.apply(logits.float(), C)
         self.last_aux, self.last_counts = aux, counts
+        if self._use_k5(x, C):
+            # K5: dispatch + expert GEMM 1 and expert GEMM 2 + combine as two fused block-scaled-fp8 kernels
+            from . import fused_moe as FM
+
+            if getattr(self.ep, "fused_moe", None) is None:
+                self.ep.fused_moe = FM.FusedMoE(self.ep)
+            y = FM.fused_experts(x, gate, self.w1, self.b1, self.w2, self.b2, expert, slot, counts, self.E, C,
+                                 self.ep.fused_moe)
+            return y[:T] + y[T:] if self.top_k == 2 else y
         xin = _Dispatch.apply(x, expert, slot, self.E, C, self.ep, self.fused)       # [El, ep*C, H]
         outs = []
         if self.fp8 and x.is_cuda:

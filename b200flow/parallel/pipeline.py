@@ -141,6 +141,30 @@ class P2P:
         return act_in, grad_in
 
 
+class _Trace:
+    """B2F_PP_TRACE=<prefix>: device timestamps of every schedule instruction ("x" = the exchange that follows an
+    F / B), one JSON line per batch and stage in <prefix>.stage<k>.jsonl - the 2-GPU timeline evidence."""
+
+    def __init__(self, stage):
+        self.stage, self.ev = stage, []
+        self.mark("start", -1)
+
+    def mark(self, op, mb):
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        self.ev.append((op, mb, e))
+
+    def dump(self, prefix):
+        import json
+
+        self.mark("end", -1)
+        torch.cuda.synchronize()
+        t0 = self.ev[0][2]
+        rows = [(op, mb, round(t0.elapsed_time(e), 3)) for op, mb, e in self.ev]
+        with open(f"{prefix}.stage{self.stage}.jsonl", "a") as f:
+            f.write(json.dumps(rows) + "\n")
+
+
 def run_1f1b(stage: int, stages: int, micro_batches: int, forward_fn, p2p: P2P, zero_bubble: bool = False):
     """Execute one training batch on this stage.
 
@@ -150,10 +174,13 @@ def run_1f1b(stage: int, stages: int, micro_batches: int, forward_fn, p2p: P2P, 
     `zero_bubble`: run `schedule_zb` - backward passes queue their weight-gradient GEMMs and the
     "W" instructions launch them later.
     """
+    import os
+
     from ..ops import gemm as G
 
     first, last = stage == 0, stage == stages - 1
     instrs = (schedule_zb if zero_bubble else schedule_1f1b)(stage, stages, micro_batches)
+    trace = _Trace(stage) if (os.environ.get("B2F_PP_TRACE") and p2p.device.type == "cuda") else None
     inputs: dict[int, torch.Tensor] = {}
     outputs: dict[int, torch.Tensor] = {}
     wqueues: dict[int, list] = {}
@@ -163,6 +190,7 @@ def run_1f1b(stage: int, stages: int, micro_batches: int, forward_fn, p2p: P2P, 
     for k, ins in enumerate(instrs):
         # the exchange after this instruction is paired with what the next F / B needs ("W" has no traffic)
         nxt = next((i for i in instrs[k + 1:] if i.op != "W"), None)
+        trace and trace.mark(ins.op, ins.mb)
         if ins.op == "W":
             G.run_deferred(wqueues.pop(ins.mb))
             continue
@@ -179,6 +207,7 @@ def run_1f1b(stage: int, stages: int, micro_batches: int, forward_fn, p2p: P2P, 
             inputs[ins.mb], outputs[ins.mb] = act, out
             if last:
                 losses.append(out.detach())
+            trace and trace.mark("x", ins.mb)
             # send the activation on; pair it with the receive the next instruction needs
             want_grad = (not last) and nxt is not None and nxt.op == "B"
             want_act = (not first) and nxt is not None and nxt.op == "F"
@@ -205,6 +234,7 @@ def run_1f1b(stage: int, stages: int, micro_batches: int, forward_fn, p2p: P2P, 
             else:
                 torch.autograd.backward(out, grad)
             dact = act.grad if act is not None else None
+            trace and trace.mark("x", ins.mb)
             want_act = (not first) and nxt is not None and nxt.op == "F"
             want_grad = (not last) and nxt is not None and nxt.op == "B"
             a, g = p2p.exchange(send_bwd=dact, recv_fwd=want_act, recv_bwd=want_grad)
@@ -213,6 +243,7 @@ def run_1f1b(stage: int, stages: int, micro_batches: int, forward_fn, p2p: P2P, 
             if g is not None:
                 pending_grad = g
     assert not wqueues, "weight gradients left in the queue"
+    trace and trace.dump(os.environ["B2F_PP_TRACE"])
     return losses
 
 

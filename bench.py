@@ -46,6 +46,7 @@ def parse_args():
     ap.add_argument("--tp", type=int, default=0, help="override the tensor-parallel size")
     ap.add_argument("--pp", type=int, default=0, help="override the pipeline-parallel size")
     ap.add_argument("--profile", default="", help="write a torch.profiler kernel table of one extra step to this file")
+    ap.add_argument("--no-zero-bubble", action="store_true", help="plain 1F1B instead of the split-backward schedule")
     ap.add_argument("--baseline", default="auto", choices=["auto", "none"],
                     help="auto: first time the stock arm of the same workload in a subprocess (N=1: --impl twin, torch nn + "
                          "cuBLAS + SDPA + fused AdamW; N>1: this engine with NCCL collectives around the GEMMs, --no-fused) "
@@ -67,12 +68,17 @@ def stock_arm(args, world: int) -> dict | None:
            "--gas", str(args.gas), "--baseline", "none"]
     if args.tp or args.pp:
         cmd += ["--tp", str(args.tp), "--pp", str(args.pp)]
+    if args.no_zero_bubble:
+        cmd += ["--no-zero-bubble"]
     # Llama at N > 1: torch has no TP/PP engine to call, so the stock arm is this engine with NCCL collectives around
     # the same GEMMs; the DP-only workloads (BERT, Mask R-CNN, MoE) have a stock twin at every N
     cmd += ["--no-fused"] if (world > 1 and args.workload.startswith("llama")) else ["--impl", "twin"]
     env = dict(os.environ)
     if world > 1:
         env["MASTER_PORT"] = str(int(env.get("MASTER_PORT", "29500")) + 17)
+        # torchrun's agent serves the rendezvous store of ITS port; on the new port rank 0 of the stock arm hosts one
+        for k in [k for k in env if k.startswith("TORCHELASTIC_")]:
+            env.pop(k)
     try:
         res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=1500)
         for line in reversed(res.stdout.strip().splitlines()):
@@ -234,6 +240,7 @@ def main():
         "gradient_clipping": 1.0,
         "optimizer": {"params": {"lr": 1.5e-4, "betas": (0.9, 0.95), "eps": 1e-8, "weight_decay": 0.1}},
         "fused_collectives": not args.no_fused,
+        "pipeline": {"zero_bubble": not args.no_zero_bubble},
     }
     engine = initialize(cfg, ds_config, ps, device=dev)
     B, S = args.micro_batch, args.seq

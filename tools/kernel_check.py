@@ -8,6 +8,7 @@ kernel blind.   usage: python tools/kernel_check.py <group> [...]
 from __future__ import annotations
 
 import json
+import os
 import sys
 import time
 from pathlib import Path
@@ -25,17 +26,40 @@ DEV = "cuda"
 RESULTS = []
 
 
-def report(name, got, ref, tol):
+def report_rms(name, got, ref, tol):
+    """Quantisation-noise comparisons (fp8 result against the unquantised product): the error of one element is a sum
+    of many independent rounding errors, so single elements legitimately stray several sigma; what the format
+    promises is the noise level.  Checks ||got - ref|| / ||ref|| per row (last dimension) against `tol`, and that no
+    element is further off than 8 x tol x the row's rms (a systematic error - wrong scale, dropped block - is far
+    beyond either)."""
+    got = got.float()
+    ref = ref.float().to(got.device)
+    err = got - ref
+    rms_ref = ref.pow(2).mean(-1, keepdim=True).sqrt().clamp_min(ref.pow(2).mean().sqrt() * 1e-3 + 1e-12)
+    row_noise = (err.pow(2).mean(-1, keepdim=True).sqrt() / rms_ref).max().item()
+    worst_elem = (err.abs() / rms_ref).max().item()
+    ok = bool(row_noise <= tol) and bool(worst_elem <= 8 * tol) and bool(torch.isfinite(got).all())
+    rec = {"name": name, "ok": ok, "row_noise": row_noise, "worst_elem": worst_elem, "tol": tol}
+    RESULTS.append(rec)
+    print(json.dumps(rec), flush=True)
+    return ok
+
+
+def report(name, got, ref, tol, floor=1e-3):
     """Per-element check  |got - ref| <= tol * (rms_row(ref) + |ref|):  the relative part bounds the rounding of the
     bf16 / fp32 result itself (1 bf16 ulp = 0.4 %), the absolute part is scaled by the rms of the element's own row
     (last dimension), not by the tensor's global maximum, so a wrong low-magnitude row or a dropped K tail cannot
-    hide behind large values elsewhere.  `worst` is the largest ratio error / bound over all elements."""
+    hide behind large values elsewhere.  `worst` is the largest ratio error / bound over all elements.
+    `floor`: rows are held to at least this fraction of the tensor's overall rms.  Kernels whose result is a difference
+    of rounded intermediates (attention backward: dS = P (dP - rowsum(O dO)) with O and P in bf16) have an error that
+    scales with the tensor, not with the row - rows that attend to one or two keys have an exactly-zero gradient -
+    and pass a floor of order 1."""
     got = got.float()
     ref = ref.float().to(got.device)
     err = (got - ref).abs()
     rows = ref.reshape(-1, ref.shape[-1]) if ref.dim() >= 1 and ref.numel() else ref.reshape(1, -1)
     rms = rows.pow(2).mean(-1, keepdim=True).sqrt().reshape(*ref.shape[:-1], 1) if ref.dim() >= 1 else ref.abs()
-    floor = ref.pow(2).mean().sqrt() * 1e-3 + 1e-12        # an all-zero row is held to the tensor's scale
+    floor = ref.pow(2).mean().sqrt() * floor + 1e-12       # an all-zero row is held to the tensor's scale
     bound = tol * (torch.maximum(rms, floor) + ref.abs())
     ratio = err / bound
     worst = ratio.max().item() if ratio.numel() else 0.0
@@ -84,6 +108,12 @@ def group_gemm(mode):
               # odd shapes and K tails: K not a multiple of the 64-element k-block, M / N off the tile grid
               (130, 264, 72), (257, 520, 200), (129, 8, 24), (513, 1032, 328), (64, 136, 8)]
     for (M, Nn, K) in shapes:
+        # an MN-major operand is a [K, MN] matrix read through TMA: its row pitch (MN elements) must be a multiple
+        # of 16 bytes, so the transposed layouts take MN in multiples of 8
+        if mode in ("tn", "tt"):
+            M = (M + 7) // 8 * 8
+        if mode in ("nn", "tn"):
+            Nn = (Nn + 7) // 8 * 8
         a = torch.randn(M, K, device=DEV, dtype=torch.bfloat16)
         b = torch.randn(Nn, K, device=DEV, dtype=torch.bfloat16)
         ref = a.float() @ b.float().t()
@@ -96,7 +126,7 @@ def group_gemm(mode):
         elif mode == "tt":
             got = G.gemm(a.t().contiguous(), b, a_mn_major=True)
         torch.cuda.synchronize()
-        report(f"gemm_{mode}_{M}x{Nn}x{K}", got, ref, 2e-2)
+        report(f"gemm_{mode}_{M}x{Nn}x{K}", got, ref, 5e-3)      # fp32 accumulation, one bf16 rounding (0.4 %) at the end
 
 
 def group_gemm_epi():
@@ -416,9 +446,9 @@ def group_attn(which):
             ref.backward(do.float())
             torch.cuda.synchronize()
             report(f"attn_fwd_{tag}", o.reshape(B * S, -1), ref.reshape(B * S, -1), 2e-2)
-            report(f"attn_dq_{tag}", q.grad.reshape(B * S, -1), qf.grad.reshape(B * S, -1), 3e-2)
-            report(f"attn_dk_{tag}", k.grad.reshape(B * S, -1), kf.grad.reshape(B * S, -1), 3e-2)
-            report(f"attn_dv_{tag}", v.grad.reshape(B * S, -1), vf.grad.reshape(B * S, -1), 3e-2)
+            report(f"attn_dq_{tag}", q.grad.reshape(B * S, -1), qf.grad.reshape(B * S, -1), 3e-2, floor=2.0)
+            report(f"attn_dk_{tag}", k.grad.reshape(B * S, -1), kf.grad.reshape(B * S, -1), 3e-2, floor=2.0)
+            report(f"attn_dv_{tag}", v.grad.reshape(B * S, -1), vf.grad.reshape(B * S, -1), 3e-2, floor=1.0)
     if which == "bwd":
         # key-padding lengths + packed qkv path
         B, S, H, D = 2, 256, 2, 128
@@ -431,7 +461,7 @@ def group_attn(which):
         ref = _attn_ref(qf[:, :, 0], qf[:, :, 1], qf[:, :, 2], False, D ** -0.5, lens)
         ref.backward(do.float())
         report("attn_packed_fwd", o.reshape(B * S, -1), ref.reshape(B * S, -1), 2e-2)
-        report("attn_packed_dqkv", qkv.grad.reshape(B * S, -1), qf.grad.reshape(B * S, -1), 3e-2)
+        report("attn_packed_dqkv", qkv.grad.reshape(B * S, -1), qf.grad.reshape(B * S, -1), 3e-2, floor=2.0)
 
 
 def group_attn_perf():
@@ -622,6 +652,57 @@ def group_moe():
     report("moe_dwg", layer.wg.grad[:8], ref_layer.wg.grad[:8], 8e-2)
 
 
+def group_k5():
+    """K5 on one GPU (all experts local): the fused dispatch + block-scaled GEMM / GEMM + combine kernels against the fp32
+    layer, forward and backward, with an uneven routing (some experts overflow, one nearly empty) and twice in a row
+    (buffer parity, counters)."""
+    from b200flow.parallel.moe import MoELayer
+    torch.manual_seed(8)
+    H, F, E, T = 512, 1024, 8, 4096
+    layer = MoELayer(H, F, E, dtype=torch.bfloat16, device=DEV, fp8=True, capacity_factor=1.0)
+    with torch.no_grad():
+        layer.b1.normal_(0, 0.05)
+        layer.b2.normal_(0, 0.05)
+        layer.wg[1] *= 3.0          # expert 1 attracts more tokens than its capacity, others run short
+    assert layer._use_k5(torch.empty(T, H, device=DEV), layer.capacity(T)), "K5 path not taken"
+    ref_layer = MoELayer(H, F, E, dtype=torch.float32, capacity_factor=1.0)
+    ref_layer.load_state_dict({k: v.float().cpu() for k, v in layer.state_dict().items()})
+    for rep in range(2):
+        x = (torch.randn(T, H, device=DEV) * 0.5).to(torch.bfloat16).requires_grad_()
+        y = layer(x)
+        (y.float().square().sum() + layer.last_aux).backward()
+        torch.cuda.synchronize()
+        xr = x.detach().float().cpu().requires_grad_()
+        yr = ref_layer(xr)
+        (yr.square().sum() + ref_layer.last_aux).backward()
+        agree = float((layer.last_counts.cpu() == ref_layer.last_counts).float().mean())
+        RESULTS.append({"name": f"k5_route_agree_r{rep}", "ok": agree > 0.99, "agree": agree,
+                        "counts": layer.last_counts.tolist()})
+        print(json.dumps(RESULTS[-1]), flush=True)
+        report_rms(f"k5_fwd_r{rep}", y, yr, 6e-2)
+        report_rms(f"k5_dx_r{rep}", x.grad, xr.grad, 8e-2)
+        report_rms(f"k5_dw1_r{rep}", layer.w1.grad.reshape(E, -1), ref_layer.w1.grad.reshape(E, -1), 8e-2)
+        report_rms(f"k5_dw2_r{rep}", layer.w2.grad.reshape(E, -1), ref_layer.w2.grad.reshape(E, -1), 8e-2)
+        report_rms(f"k5_db1_r{rep}", layer.b1.grad.reshape(1, -1), ref_layer.b1.grad.reshape(1, -1), 8e-2)
+        report_rms(f"k5_db2_r{rep}", layer.b2.grad.reshape(1, -1), ref_layer.b2.grad.reshape(1, -1), 8e-2)
+        report_rms(f"k5_dwg_r{rep}", layer.wg.grad[:E], ref_layer.wg.grad[:E], 1e-1)
+        layer.zero_grad(); ref_layer.zero_grad()
+    # the size of BASELINE config 5 on one GPU: 8 experts x 2048 tokens each
+    big = MoELayer(2048, 8192, 8, dtype=torch.bfloat16, device=DEV, fp8=True)
+    xb = (torch.randn(16384, 2048, device=DEV) * 0.5).to(torch.bfloat16).requires_grad_()
+    def step():
+        big(xb).float().sum().backward()
+    ms = timeit(step, iters=5, warmup=2)
+    flops = 3 * 2 * 2 * 16384 * 2048 * 8192
+    print(json.dumps({"name": "k5_layer_fwd_bwd_16384x2048x8192", "ms": ms, "model_tflops": flops / ms / 1e9}), flush=True)
+    os.environ["B2F_FUSED_MOE"] = "0"
+    try:
+        ms0 = timeit(step, iters=5, warmup=2)
+    finally:
+        os.environ["B2F_FUSED_MOE"] = "1"
+    print(json.dumps({"name": "unfused_rowscaled_layer_fwd_bwd_16384x2048x8192", "ms": ms0}), flush=True)
+
+
 def group_fp8():
     from b200flow.ops import gemm_fp8 as F8
     torch.manual_seed(9)
@@ -635,7 +716,7 @@ def group_fp8():
         exact = (aq.view(torch.float8_e4m3fn).float() @ bq.view(torch.float8_e4m3fn).float().t()) * sa[:, None] * sb[None, :]
         got = F8.gemm_fp8(aq, sa, bq, sb)
         report(f"fp8_gemm_exact_{M}x{Nn}x{K}", got, exact, 1e-2)       # vs the same quantised operands
-        report(f"fp8_gemm_vs_bf16_{M}x{Nn}x{K}", got, a.float() @ b.float().t(), 6e-2)
+        report_rms(f"fp8_gemm_vs_bf16_{M}x{Nn}x{K}", got, a.float() @ b.float().t(), 6e-2)
     x = (torch.randn(2048, 2048, device=DEV)).to(torch.bfloat16).requires_grad_()
     w = (torch.randn(8192, 2048, device=DEV) * 0.02).to(torch.bfloat16).requires_grad_()
     bias = torch.zeros(8192, device=DEV, dtype=torch.bfloat16, requires_grad=True)
@@ -645,9 +726,9 @@ def group_fp8():
     xf, wf = x.detach().float().requires_grad_(), w.detach().float().requires_grad_()
     yf = torch.nn.functional.gelu(xf @ wf.t(), approximate="tanh")
     yf.backward(dy.float())
-    report("fp8_linear_gelu_fwd", y, yf, 6e-2)
-    report("fp8_linear_gelu_dx", x.grad, xf.grad, 8e-2)
-    report("fp8_linear_gelu_dw", w.grad, wf.grad, 4e-2)
+    report_rms("fp8_linear_gelu_fwd", y, yf, 6e-2)
+    report_rms("fp8_linear_gelu_dx", x.grad, xf.grad, 8e-2)
+    report_rms("fp8_linear_gelu_dw", w.grad, wf.grad, 6e-2)
     a = torch.randn(4096, 4096, device=DEV, dtype=torch.bfloat16)
     b = torch.randn(8192, 4096, device=DEV, dtype=torch.bfloat16)
     aq, sa = F8.quantize_rows(a); bq, sb = F8.quantize_rows(b)
@@ -686,7 +767,75 @@ def group_gemm2():
     RESULTS.append({"name": "gemm2_perf", "ok": True})
 
 
+def group_mx():
+    """Block-scaled fp8 GEMM (kind::mxf8f6f4, scale factors in TMEM) against fp32 products of the dequantised operands.
+    The structured cases separate the parts of the scale-factor layout: uniform magnitudes need no layout at all,
+    then only A rows, only B rows (output columns), only K groups vary."""
+    from b200flow.ops import gemm_mx as MX
+
+    torch.manual_seed(3)
+
+    def case(name, a, b, tol=5e-3, **kw):
+        ta, tb = MX.quantize_mx(a), MX.quantize_mx(b)
+        da, db = MX.dequantize_mx(ta).float(), MX.dequantize_mx(tb).float()
+        ra, _ = MX.quantize_mx_reference(a)
+        report(f"mx_quant_{name}", da, ra, 1e-3)                     # kernel quantiser == restated quantiser
+        got = MX.gemm_mx(ta, tb, **kw)
+        torch.cuda.synchronize()
+        ref = da @ db.transpose(-1, -2)
+        return got, ref
+
+    M, Nn, K = 256, 384, 256
+    a = torch.randn(M, K, device=DEV, dtype=torch.bfloat16)
+    b = torch.randn(Nn, K, device=DEV, dtype=torch.bfloat16)
+    ones_a, ones_b = torch.ones_like(a), torch.ones_like(b)
+    got, ref = case("uniform", ones_a, ones_b)
+    report("mx_gemm_uniform", got, ref, 5e-3)
+    rows = torch.pow(2.0, (torch.arange(M, device=DEV) % 11).float())[:, None]
+    got, ref = case("a_rows", (ones_a.float() * rows).to(torch.bfloat16), ones_b)
+    report("mx_gemm_a_rows", got, ref, 5e-3)
+    cols = torch.pow(2.0, (torch.arange(Nn, device=DEV) % 13).float())[:, None]
+    got, ref = case("b_rows", ones_a, (ones_b.float() * cols).to(torch.bfloat16))
+    report("mx_gemm_b_rows", got, ref, 5e-3)
+    kg = torch.pow(2.0, ((torch.arange(K, device=DEV) // 32) % 5).float())[None, :]
+    got, ref = case("k_groups", (ones_a.float() * kg).to(torch.bfloat16), (ones_b.float() / kg).to(torch.bfloat16))
+    report("mx_gemm_k_groups", got, ref, 5e-3)
+    for (M, Nn, K) in [(128, 192, 128), (256, 384, 256), (384, 8192, 2048), (200, 328, 384), (4096, 2048, 8192)]:
+        a = torch.randn(M, K, device=DEV, dtype=torch.bfloat16) * torch.pow(
+            2.0, torch.randint(-6, 6, (M, 1), device=DEV).float()).to(torch.bfloat16)
+        b = (torch.randn(Nn, K, device=DEV) * 0.05).to(torch.bfloat16)
+        got, ref = case(f"{M}x{Nn}x{K}", a, b)
+        report(f"mx_gemm_{M}x{Nn}x{K}", got, ref, 5e-3)
+        report_rms(f"mx_gemm_vs_bf16_{M}x{Nn}x{K}", got, a.float() @ b.float().t(), 6e-2)
+    # epilogue: bias + gelu with the pre-activation copy, batched operands
+    E_, M, Nn, K = 2, 256, 320, 256
+    a = torch.randn(E_, M, K, device=DEV, dtype=torch.bfloat16)
+    b = (torch.randn(E_, Nn, K, device=DEV) * 0.05).to(torch.bfloat16)
+    got, ref = case("batched", a, b)
+    report("mx_gemm_batched", got.reshape(E_ * M, Nn), ref.reshape(E_ * M, Nn), 5e-3)
+    bias = torch.randn(Nn, device=DEV, dtype=torch.bfloat16)
+    aux = torch.empty(M, Nn, device=DEV, dtype=torch.bfloat16)
+    got, ref = case("gelu", a[0], b[0], bias=bias, gelu=True, aux=aux)
+    report("mx_gemm_gelu_aux", aux, ref + bias.float(), 5e-3)
+    report("mx_gemm_gelu", got, torch.nn.functional.gelu(ref + bias.float(), approximate="tanh"), 1e-2)
+    a = torch.randn(4096, 2048, device=DEV, dtype=torch.bfloat16)
+    b = torch.randn(8192, 2048, device=DEV, dtype=torch.bfloat16)
+    ta, tb = MX.quantize_mx(a), MX.quantize_mx(b)
+    ms = timeit(lambda: MX.gemm_mx(ta, tb))
+    print(json.dumps({"name": "mx_gemm_perf_4096x8192x2048", "ms": ms,
+                      "tflops": 2 * 4096 * 8192 * 2048 / ms / 1e9}), flush=True)
+    ta2, tb2 = MX.quantize_mx(torch.randn(4096, 8192, device=DEV, dtype=torch.bfloat16)), MX.quantize_mx(
+        torch.randn(2048, 8192, device=DEV, dtype=torch.bfloat16))
+    ms = timeit(lambda: MX.gemm_mx(ta2, tb2))
+    print(json.dumps({"name": "mx_gemm_perf_4096x2048x8192", "ms": ms,
+                      "tflops": 2 * 4096 * 8192 * 2048 / ms / 1e9}), flush=True)
+    ms = timeit(lambda: MX.quantize_mx(a))
+    print(json.dumps({"name": "mx_quantize_4096x2048", "ms": ms, "gbs": 4096 * 2048 * 3 / ms / 1e6}), flush=True)
+
+
 GROUPS = {
+    "mx": group_mx,
+    "k5": group_k5,
     "gemm2": group_gemm2,
     "fp8": group_fp8,
     "moe": group_moe,

@@ -34,6 +34,11 @@ def rel(a, b):
     return ((a.float() - b.float()).abs().max() / (b.float().abs().max() + 1e-6)).item()
 
 
+def relrms(a, b):
+    """||a - b|| / ||b||: the noise level of a quantised result against the unquantised one."""
+    return ((a.float() - b.float()).norm() / (b.float().norm() + 1e-12)).item()
+
+
 def timeit(fn, iters=10, warmup=3):
     for _ in range(warmup):
         fn()
@@ -316,7 +321,60 @@ def group_moe_ep():
     report("moe_ep_perf", True, baseline_a2a_ms=tb, fused_peer_ms=tf)
 
 
-GROUPS = {"moe_ep": group_moe_ep, "fused_gemm": group_fused_gemm, "arena": group_arena, "allreduce": group_allreduce, "zero1": group_zero1, "tp": group_tp,
+def group_moe_k5():
+    """K5 across GPUs: fused dispatch + block-scaled fp8 GEMMs + combine against the bf16 all_to_all_single layer
+    (fp8 quantisation noise apart), uneven routing, three calls in a row (buffer parity, epoch-tagged flags)."""
+    from b200flow.comm.arena import PeerComm
+    from b200flow.parallel.moe import EPContext, MoELayer
+
+    rank, world = dist.get_rank(), dist.get_world_size()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    comm = PeerComm(dist.group.WORLD, rank, world, dev)
+    ep = EPContext(dist.group.WORLD, world, rank, comm)
+    E = int(os.environ.get("B2F_CHECK_EXPERTS_PER_RANK", 2)) * world
+    H, F, T = 512, 1024, 2048 * max(1, E // 4)
+    torch.manual_seed(31)
+    base = MoELayer(H, F, E, ep=ep, dtype=torch.bfloat16, device=dev, fused=False)
+    k5 = MoELayer(H, F, E, ep=ep, dtype=torch.bfloat16, device=dev, fused=True, fp8=True)
+    with torch.no_grad():
+        base.wg[1] *= 3.0
+        base.b1.normal_(0, 0.05)
+        base.b2.normal_(0, 0.05)
+    k5.load_state_dict(base.state_dict())
+    assert k5._use_k5(torch.empty(T, H, device=dev), k5.capacity(T)), "K5 path not taken"
+    for rep in range(3):
+        torch.manual_seed(50 + rank + 7 * rep)
+        x = (torch.randn(T, H, device=dev) * 0.5).to(torch.bfloat16)
+        xa, xb = x.clone().requires_grad_(), x.clone().requires_grad_()
+        ya, yb = base(xa), k5(xb)
+        ya.float().square().sum().backward()
+        yb.float().square().sum().backward()
+        torch.cuda.synchronize()
+        report(f"moe_k5_fwd_r{rep}", relrms(yb, ya) < 6e-2, err=relrms(yb, ya), counts=k5.last_counts.tolist())
+        report(f"moe_k5_dx_r{rep}", relrms(xb.grad, xa.grad) < 8e-2, err=relrms(xb.grad, xa.grad))
+        report(f"moe_k5_dw1_r{rep}", relrms(k5.w1.grad, base.w1.grad) < 8e-2, err=relrms(k5.w1.grad, base.w1.grad))
+        report(f"moe_k5_dw2_r{rep}", relrms(k5.w2.grad, base.w2.grad) < 8e-2, err=relrms(k5.w2.grad, base.w2.grad))
+        report(f"moe_k5_db1_r{rep}", relrms(k5.b1.grad, base.b1.grad) < 8e-2, err=relrms(k5.b1.grad, base.b1.grad))
+        report(f"moe_k5_dwg_r{rep}", relrms(k5.wg.grad, base.wg.grad) < 1e-1, err=relrms(k5.wg.grad, base.wg.grad))
+        base.zero_grad(); k5.zero_grad()
+    # BASELINE config 5 shapes: hidden 2048, ffn 8192, 8 x 2048 tokens per rank
+    Eb = max(world, 8) if 8 % world == 0 else world
+    big_base = MoELayer(2048, 8192, Eb, ep=ep, dtype=torch.bfloat16, device=dev, fused=True, fp8=True)
+    xx = (torch.randn(16384, 2048, device=dev) * 0.5).to(torch.bfloat16)
+    def run(layer):
+        xg = xx.clone().requires_grad_()
+        layer(xg).float().sum().backward()
+    t_k5 = timeit(lambda: run(big_base))
+    os.environ["B2F_FUSED_MOE"] = "0"
+    try:
+        t_old = timeit(lambda: run(big_base))
+    finally:
+        os.environ["B2F_FUSED_MOE"] = "1"
+    report("moe_k5_perf", True, k5_ms=t_k5, unfused_rowscaled_fp8_ms=t_old, experts=Eb,
+           wire_bytes_per_a2a_mb=16384 * 2048 * (1 + 1 / 32) * (world - 1) / world / 2 ** 20)
+
+
+GROUPS = {"moe_k5": group_moe_k5, "moe_ep": group_moe_ep, "fused_gemm": group_fused_gemm, "arena": group_arena, "allreduce": group_allreduce, "zero1": group_zero1, "tp": group_tp,
           "pp": group_pp, "tp_replicated": group_tp_replicated,
           "ulysses": group_ulysses}
 
