@@ -126,6 +126,11 @@ class TrainEngine:
 
                 comm = PeerComm(ps.ep_group, ep_rank, self.ep_world, self.device)
             self.ep_ctx = EPContext(ps.ep_group, self.ep_world, ep_rank, comm)
+            if use_fused:       # K5: the quantised copies of the expert weights live until the next optimizer step
+                from ..parallel.fused_moe import FusedMoE
+
+                self.ep_ctx.fused_moe = FusedMoE(self.ep_ctx)
+                self.ep_ctx.fused_moe.cache_weights = True
         # same init on every TP/DP replica of a stage, different across TP shards
         torch.manual_seed(seed + 1000 * self.stage + (ps.tp_rank if ps else 0))
         lo, hi = split_layers(model_config.layers, pp_world)[self.stage]
@@ -378,6 +383,9 @@ class TrainEngine:
                 self.expert_optimizer.lr = self.optimizer.lr
                 self.expert_optimizer.step(grad_divisor=div)
         self.global_steps += 1
+        fm = getattr(self.ep_ctx, "fused_moe", None) if self.ep_ctx is not None else None
+        if fm is not None:
+            fm.invalidate()                          # the expert weights just changed
         return scale
 
     # ------------------------------------------- DeepSpeed's forward / backward / step triple

@@ -190,10 +190,12 @@ def run_1f1b(stage: int, stages: int, micro_batches: int, forward_fn, p2p: P2P, 
     for k, ins in enumerate(instrs):
         # the exchange after this instruction is paired with what the next F / B needs ("W" has no traffic)
         nxt = next((i for i in instrs[k + 1:] if i.op != "W"), None)
-        trace and trace.mark(ins.op, ins.mb)
         if ins.op == "W":
-            G.run_deferred(wqueues.pop(ins.mb))
+            if ins.mb in wqueues:         # (not already run ahead of a receive-only exchange, see below)
+                trace and trace.mark("W", ins.mb)
+                G.run_deferred(wqueues.pop(ins.mb))
             continue
+        trace and trace.mark(ins.op, ins.mb)
         if ins.op == "F":
             if not first:
                 act = pending_act
@@ -234,6 +236,16 @@ def run_1f1b(stage: int, stages: int, micro_batches: int, forward_fn, p2p: P2P, 
             else:
                 torch.autograd.backward(out, grad)
             dact = act.grad if act is not None else None
+            if dact is None or first:
+                # nothing to send upstream: the exchange below only receives, i.e. only waits.  Weight gradients that
+                # the schedule placed right behind this backward run first, so the wait is spent computing (the first
+                # stage's cool-down would otherwise idle in the receive with its queue full).
+                for w in instrs[k + 1:]:
+                    if w.op != "W":
+                        break
+                    if w.mb in wqueues:
+                        trace and trace.mark("W", w.mb)
+                        G.run_deferred(wqueues.pop(w.mb))
             trace and trace.mark("x", ins.mb)
             want_act = (not first) and nxt is not None and nxt.op == "F"
             want_grad = (not last) and nxt is not None and nxt.op == "B"

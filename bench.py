@@ -229,7 +229,7 @@ def main():
     cfg = config_from_preset(args.workload, max_seq=args.seq)
     ep = min(world, cfg.num_experts) if is_moe else 1
     if is_moe:
-        cfg.moe_fp8 = True
+        cfg.moe_fp8 = os.environ.get("B2F_MOE_BF16", "0") != "1"     # B2F_MOE_BF16=1: bf16 expert GEMMs (loss-curve comparisons)
     ps = ParallelState.initialize(tp=tp, pp=pp, ep=ep) if world > 1 else None
     dp = world // (tp * pp)
     ds_config = {
@@ -242,6 +242,11 @@ def main():
         "fused_collectives": not args.no_fused,
         "pipeline": {"zero_bubble": not args.no_zero_bubble},
     }
+    if is_moe:
+        # the DeepSpeed-MoE recipes warm the rate up; from a cold start at the full rate the loss of this model
+        # first climbs for a dozen steps (bf16 and fp8 experts alike, profiles/r2_moe_loss_curves.txt)
+        ds_config["scheduler"] = {"type": "WarmupLR", "params": {"warmup_min_lr": 0.0, "warmup_max_lr": 1.5e-4,
+                                                                 "warmup_num_steps": 16, "warmup_type": "linear"}}
     engine = initialize(cfg, ds_config, ps, device=dev)
     B, S = args.micro_batch, args.seq
     tokens_per_step = B * S * args.gas * dp
@@ -342,6 +347,7 @@ def main():
             "model_tflops_per_gpu": model_tflops / world,
             "loss_first_last": [losses[0] if losses else None, e2e_loss[-1] if e2e_loss else None],
             "loss_after_warmup": loss_warm,
+            "loss_curve": [round(v, 4) for v in losses + e2e_loss],     # warm-up steps, then the end-to-end steps
             "native_libs": _lib.loaded_libraries(),
         }
         emit(out)

@@ -85,6 +85,8 @@ struct AGArgs {
   int comm_ctas;
   uint32_t epoch;
   int own_last;
+  int tail_begin;           // CTA-pair kernel: tiles [tail_begin, end) of the tile order belong to the gather clusters,
+                            // which join the GEMM once their share of the gather is done (< 0: they just exit)
 };
 
 struct AGPolicy {
@@ -209,6 +211,10 @@ __device__ void ag_comm_role(const AGArgs& a, uint8_t* smem_raw) {
       }
     }
   }
+  tma_store_wait<0>();
+  // this shared memory becomes the GEMM's operand ring and barrier block next
+  for (int i = 0; i < AG_SLOTS; ++i)
+    asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(smem_u32(&full[i])) : "memory");
 }
 
 __global__ void __launch_bounds__(NUM_THREADS, 1)
@@ -264,17 +270,24 @@ b2f_ag_gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
                     const __grid_constant__ CUtensorMap tma_b, const __grid_constant__ CUtensorMap tma_c,
                     const Params p, const AGArgs a) {
   extern __shared__ uint8_t smem_raw[];
-  if ((int)blockIdx.x < a.comm_ctas) {   // comm_ctas is even: whole clusters
-    ag_comm_role(a, smem_raw);
-    return;
-  }
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
   AG2Policy pol{a.tile_flags, &tma_own, a.epoch, a.rank, a.rows_per_rank / BM};
   pol.out.staging = smem + gemm2::S2 * gemm2::ST2_BYTES + 1024;
   pol.out.map_c = &tma_c;
+  if ((int)blockIdx.x < a.comm_ctas) {   // comm_ctas is even: whole clusters
+    // gather role first (one thread per CTA drives the copies; the others wait for it at the GEMM's first barrier),
+    // then the cluster takes its slice of the tail of the tile order: no SM sits idle once the gather is done
+    ag_comm_role(a, smem_raw);
+    if (a.tail_begin < 0) return;
+    gemm2::gemm2_body<AG2Policy, gemm2::S2>(&tma_a, &tma_b, p, pol, (int)blockIdx.x >> 1, a.comm_ctas >> 1, smem_raw,
+                                            a.tail_begin, -1);
+    return;
+  }
+  const int num_tiles = ((p.M + 255) / 256) * ((p.N + 255) / 256);
   gemm2::gemm2_body<AG2Policy, gemm2::S2>(&tma_a, &tma_b, p, pol, ((int)blockIdx.x - a.comm_ctas) >> 1,
-                                          ((int)gridDim.x - a.comm_ctas) >> 1, smem_raw);
+                                          ((int)gridDim.x - a.comm_ctas) >> 1, smem_raw, 0,
+                                          a.tail_begin < 0 ? num_tiles : a.tail_begin);
 }
 
 // ------------------------------------------------------------------ K4
@@ -286,6 +299,8 @@ struct RSArgs {
   int N;
   uint32_t epoch;
   int dbg;                  // timing experiments only (B2F_RS_DEBUG): 1 = no sends, no receives; 2 = sends only
+  int interleave;           // tile order: 1 = rounds of (one tile per peer, then the own tile with the same index),
+                            // flags published as soon as a tile's rows have landed; 0 = all peer tiles first
   // K4' (GEMM -> all-reduce): finished rows also go to every peer's full output, then one
   // "all my rows have landed" flag per peer closes the call
   int allreduce;
@@ -352,12 +367,21 @@ struct RSPolicy {
   }
   __device__ __forceinline__ int owner_of(int mb) const { return mb / blocks_per_rank; }
   __device__ __forceinline__ void map_tile(int t, int num_m, int nn, int& b, int& mb, int& nb) const {
-    // peers' row blocks first (ring order after this rank), own blocks last
     b = 0;
     const int per_owner = blocks_per_rank * nn;
-    const int oi = t / per_owner;
-    const int owner = (a.rank + 1 + oi) % a.world;
-    const int r = t - oi * per_owner;
+    int owner, r;
+    if (a.interleave) {
+      // round k: tile k of every peer (ring order), then own tile k.  The sends spread over the whole kernel instead
+      // of its first (world-1)/world, and an own tile's partials were produced by the peers in the same round.
+      const int k = t / a.world, s = t - k * a.world;
+      owner = (a.rank + 1 + s) % a.world;
+      r = k;
+    } else {
+      // peers' row blocks first (ring order after this rank), own blocks last
+      const int oi = t / per_owner;
+      owner = (a.rank + 1 + oi) % a.world;
+      r = t - oi * per_owner;
+    }
     nb = r / blocks_per_rank;
     mb = owner * blocks_per_rank + (r - nb * blocks_per_rank);
   }
@@ -489,6 +513,9 @@ struct RSPolicy {
     pend_owner = owner;
     pend_mb_local = mb - owner * blocks_per_rank;
     pend_nb = nb;
+    // interleaved order: the owner is about to need this tile, so sit out the NVLink round trip here (the MMA warp
+    // is already on the next tile) instead of publishing one tile later
+    if (a.interleave) flush();
   }
 };
 
@@ -514,9 +541,16 @@ struct RS2Policy {
     b = 0;
     const int pairs_per_rank = in.blocks_per_rank >> 1;
     const int per_owner = pairs_per_rank * nn;
-    const int oi = t / per_owner;
-    const int owner = (in.a.rank + 1 + oi) % in.a.world;
-    const int r = t - oi * per_owner;
+    int owner, r;
+    if (in.a.interleave) {
+      const int k = t / in.a.world, s = t - k * in.a.world;
+      owner = (in.a.rank + 1 + s) % in.a.world;
+      r = k;
+    } else {
+      const int oi = t / per_owner;
+      owner = (in.a.rank + 1 + oi) % in.a.world;
+      r = t - oi * per_owner;
+    }
     nb = r / pairs_per_rank;
     mb = owner * pairs_per_rank + (r - nb * pairs_per_rank);
   }
@@ -598,6 +632,24 @@ extern "C" int b2f_ag_gemm_bf16(const long long* x_shard_ptrs, void* xg, const v
     const int tiles2 = (T / 256) * ((N + 255) / 256);
     int pairs = (sms - a.comm_ctas) / 2;
     if (pairs > tiles2) pairs = tiles2;
+    // The gather clusters rejoin the GEMM when their copies are done.  Their slice of the tile order is sized so that
+    // everyone finishes together: a cluster pair of SMs computes at ~1/74 of the sustained GEMM rate, a gather CTA
+    // moves ~15 GB/s (peer -> shared -> local), measured on this box (profiles/r2_tp_perf*.txt).
+    static const double cta_gbs = [] { const char* e = getenv("B2F_AG_CTA_GBS"); return e ? atof(e) : 15.0; }();
+    static const bool rejoin = [] { const char* e = getenv("B2F_AG_REJOIN"); return !(e && e[0] == '0'); }();
+    a.tail_begin = -1;
+    if (rejoin && pairs > 0 && tiles2 > 2 * pairs) {
+      const double t_gemm = 2.0 * T * (double)N * K / 1.30e15;                  // whole GEMM on every SM, seconds
+      const double gather_bytes = (double)T * K * 2;                            // peers' shards + own copy
+      const double t_gather = gather_bytes / (a.comm_ctas * cta_gbs * 1e9);     // time the gather clusters are busy
+      const int nc = a.comm_ctas / 2;
+      const double all = nc + pairs;
+      // work (in cluster-seconds) = t_gemm * all; gather clusters contribute (T_end - t_gather) each
+      const double t_end = (t_gemm * all + nc * t_gather) / all;
+      double share = t_end > t_gather ? nc * (t_end - t_gather) / (t_gemm * all) : 0.0;
+      int tail = (int)(share * tiles2);
+      if (tail > 0) a.tail_begin = tiles2 - tail;
+    }
     b2f_ag_gemm2_kernel<<<a.comm_ctas + 2 * pairs, NUM_THREADS, AG2_SMEM, static_cast<cudaStream_t>(stream)>>>(
         ma2, mown, mb2, mc, p, a);
     B2F_CHECK_CUDA(cudaGetLastError());
@@ -647,6 +699,8 @@ static int gemm_rs_launch(const void* X, const void* B, void* Y_shard, int T, in
   if (int rc = fill(&a.flags, flag_ptrs, world)) return rc;
   a.rank = rank; a.world = world; a.rows_per_rank = T / world; a.N = N; a.epoch = epoch;
   if (const char* e = getenv("B2F_RS_DEBUG")) a.dbg = atoi(e);
+  static const int interleave = [] { const char* e = getenv("B2F_RS_INTERLEAVE"); return e ? atoi(e) : 1; }();
+  a.interleave = interleave;
   if (ar) {
     a.allreduce = 1;
     a.dbg = 0;

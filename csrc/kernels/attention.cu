@@ -55,7 +55,23 @@ struct AttnParams {
   __nv_bfloat16 *dQ, *dK, *dV;
   long long dq_ts, dq_bs, dk_ts, dk_bs, dv_ts, dv_bs;
   int dbg_mode;  // B2F_ATTN_DEBUG builds only: 1 = softmax does no math, 2 = also no P V, 3 = also no Q K^T
+  // attention dropout (Megatron --attention-dropout): probability element (b, h, q, k) is kept iff its byte of a
+  // counter-based hash word is >= drop_thr (= round(256 p)); kept elements are scaled by drop_rinv = 1 / (1 - p)
+  uint32_t drop_thr;
+  float drop_rinv;
+  uint32_t drop_seed;
 };
+
+// Dropout mask: one 32-bit word per (head, query, group of 4 consecutive keys), one byte per key.  A function of the
+// indices only, so the forward kernel (query rows), the dQ kernel (query rows) and the dK/dV kernel (key rows)
+// regenerate the same mask with no memory traffic, and a recomputed forward (activation checkpointing) sees it again.
+__device__ __forceinline__ uint32_t drop_mix(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
+  return x;
+}
+__device__ __forceinline__ uint32_t drop_seed_bh(uint32_t seed, int bh) { return drop_mix(seed + (uint32_t)bh * 0x632BE5ABu); }
+__device__ __forceinline__ uint32_t drop_seed_q(uint32_t seed_bh, int q) { return seed_bh + (uint32_t)q * 0x9E3779B1u; }
+__device__ __forceinline__ uint32_t drop_word(uint32_t seed_q, int k4) { return drop_mix(seed_q + (uint32_t)k4 * 0x85EBCA77u); }
 
 template <int D>
 struct Cfg {
@@ -134,7 +150,7 @@ struct Fwd2Bars {
   uint32_t tmem_base;
 };
 
-template <int D>
+template <int D, bool DROP = false>
 __global__ void __launch_bounds__(FWD2_THREADS, 1)
 attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
                  const __grid_constant__ CUtensorMap mv, const AttnParams p) {
@@ -305,6 +321,7 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
     const uint32_t T_S = tmem + lane_base + w * 128;
     const uint32_t T_O = tmem + lane_base + 256 + w * 128;
     float m = 0.f, l = 0.f;
+    const uint32_t dseed = DROP ? drop_seed_q(drop_seed_bh(p.drop_seed, b * p.H + h), qi) : 0u;
     DBG_T(t_sm0);
     for (int j = 0; j < nw; ++j) {
       const int kv0 = j * TQ;
@@ -372,8 +389,13 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
           const uint64_t t = fma2(f2pack(__uint_as_float(s[c * 32 + 2 * i]), __uint_as_float(s[c * 32 + 2 * i + 1])), sc2, nm2);
           float t0, t1;
           f2unpack(t, t0, t1);
-          const float p0 = ex2(t0), p1 = ex2(t1);
-          sum2 = add2(sum2, f2pack(p0, p1));
+          float p0 = ex2(t0), p1 = ex2(t1);
+          sum2 = add2(sum2, f2pack(p0, p1));       // the normaliser is the sum of the undropped probabilities
+          if constexpr (DROP) {
+            const uint32_t wd = drop_word(dseed, (kv0 + c * 32 + 2 * i) >> 2) >> ((i & 1) * 16);
+            p0 = (wd & 0xFF) >= p.drop_thr ? p0 : 0.f;
+            p1 = ((wd >> 8) & 0xFF) >= p.drop_thr ? p1 : 0.f;
+          }
           pk[i] = pack_bf16x2(p0, p1);
         }
         tmem_st_32x32b_x16(T_S + c * 16, pk);
@@ -398,7 +420,7 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
     if (nw > 0) {
       mbar_wait(&bars->o_full[w], 0);
       tc_fence_after();
-      const float inv = l > 0.f ? 1.f / l : 0.f;
+      const float inv = (l > 0.f ? 1.f / l : 0.f) * (DROP ? p.drop_rinv : 1.f);
       __nv_bfloat16* orow = p.O + (long long)b * p.o_bs + (long long)qi * p.o_ts + (long long)h * D;
 #pragma unroll
       for (int c = 0; c < D / 32; ++c) {
@@ -526,7 +548,7 @@ __device__ __forceinline__ void store_acc_half(uint32_t taddr, __nv_bfloat16* ro
 //   overwrite the front of S / dP (32 columns each).
 
 // ---- dQ: CTA per (q tile, head, batch); loops over key half-tiles.  dQ accumulates at [256, 256+D).
-template <int D>
+template <int D, bool DROP = false>
 __global__ void __launch_bounds__(BWD_THREADS, 1)
 attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
                    const __grid_constant__ CUtensorMap mv, const __grid_constant__ CUtensorMap mdo,
@@ -639,8 +661,15 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant
     const float nlse2 = p.delta[sidx];
     const float ndlt = p.delta[(long long)p.B * p.H * S_pad + sidx];
     const uint64_t sc2 = f2pack(p.scale_log2, p.scale_log2), nl2 = f2pack(nlse2, nlse2), nd2 = f2pack(ndlt, ndlt);
+    const uint32_t dseed = DROP ? drop_seed_q(drop_seed_bh(p.drop_seed, b * p.H + h), qi) : 0u;
     for (int hh = 0; hh < H2; ++hh) {
       const int kv0 = hh * 64 + cg * 32;  // first key column of this thread's 32
+      // dropout: dS = P o (mask o dP / (1 - p) - delta): the kept dP entries are rescaled, the dropped ones zeroed
+      auto drop_dp = [&](int i, float& a0, float& a1) {
+        const uint32_t wd = drop_word(dseed, (kv0 + 2 * i) >> 2) >> ((i & 1) * 16);
+        a0 = (wd & 0xFF) >= p.drop_thr ? a0 * p.drop_rinv : 0.f;
+        a1 = ((wd >> 8) & 0xFF) >= p.drop_thr ? a1 * p.drop_rinv : 0.f;
+      };
       const uint32_t tb = lane_base + (hh & 1) * 128;
       DBG_T(tq0);
       mbar_wait(&bars->s_full[hh & 1], (hh >> 1) & 1);
@@ -663,7 +692,9 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant
           const uint64_t t = fma2(f2pack(__uint_as_float(sa[2 * i]), __uint_as_float(sa[2 * i + 1])), sc2, nl2);
           float t0, t1;
           f2unpack(t, t0, t1);
-          const uint64_t d = add2(f2pack(__uint_as_float(da[2 * i]), __uint_as_float(da[2 * i + 1])), nd2);
+          float a0 = __uint_as_float(da[2 * i]), a1 = __uint_as_float(da[2 * i + 1]);
+          if constexpr (DROP) drop_dp(i, a0, a1);
+          const uint64_t d = add2(f2pack(a0, a1), nd2);
           float d0, d1;
           f2unpack(mul2(f2pack(ex2(t0), ex2(t1)), d), d0, d1);
           pk[i] = pack_bf16x2(d0, d1);
@@ -679,7 +710,9 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant
           f2unpack(t, t0, t1);
           const float p0 = 2 * i < lim ? ex2(t0) : 0.f;
           const float p1 = 2 * i + 1 < lim ? ex2(t1) : 0.f;
-          const uint64_t d = add2(f2pack(__uint_as_float(da[2 * i]), __uint_as_float(da[2 * i + 1])), nd2);
+          float a0 = __uint_as_float(da[2 * i]), a1 = __uint_as_float(da[2 * i + 1]);
+          if constexpr (DROP) drop_dp(i, a0, a1);
+          const uint64_t d = add2(f2pack(a0, a1), nd2);
           float d0, d1;
           f2unpack(mul2(f2pack(p0, p1), d), d0, d1);
           pk[i] = pack_bf16x2(d0, d1);
@@ -710,7 +743,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant
 // query half-tiles (S^T formulation: rows = keys, columns = 64 queries, so P^T / dS^T are TMEM
 // A-operands).  dV accumulates at [256, 256+D), dK at [384, 384+D).  The TMA warp also stages each
 // query tile's -lse2 / -delta rows (two 512 B bulk copies).
-template <int D>
+template <int D, bool DROP = false>
 __global__ void __launch_bounds__(BWD_THREADS, 1)
 attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
                     const __grid_constant__ CUtensorMap mv, const __grid_constant__ CUtensorMap mdo,
@@ -853,6 +886,13 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constan
       const uint32_t l_addr = smem_u32(&bars->lse2[st][half * 64 + cg * 32]);
       const uint32_t d_addr = smem_u32(&bars->dlt[st][half * 64 + cg * 32]);
       uint32_t pp[16], pd[16];
+      // dropout: this thread owns key ki and walks over queries, so every element has its own mask word; the kept
+      // probabilities (dV operand) and the kept dP entries (inside dS) are scaled by 1 / (1 - p)
+      const uint32_t dseed_bh = DROP ? drop_seed_bh(p.drop_seed, b * p.H + hkv * G + it / per_head) : 0u;
+      auto keep_at = [&](int c) -> float {
+        const uint32_t wd = drop_word(drop_seed_q(dseed_bh, qh0 + cg * 32 + c), ki >> 2) >> ((ki & 3) * 8);
+        return (wd & 0xFF) >= p.drop_thr ? p.drop_rinv : 0.f;
+      };
       if (!need_mask) {
 #pragma unroll
         for (int i4 = 0; i4 < 8; ++i4) {
@@ -864,10 +904,13 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constan
             float t0, t1;
             f2unpack(t, t0, t1);
             const float p0 = ex2(t0), p1 = ex2(t1);
-            const uint64_t d = add2(f2pack(__uint_as_float(da[c]), __uint_as_float(da[c + 1])), e ? nd.y : nd.x);
+            float a0 = __uint_as_float(da[c]), a1 = __uint_as_float(da[c + 1]);
+            float k0 = 1.f, k1 = 1.f;
+            if constexpr (DROP) { k0 = keep_at(c); k1 = keep_at(c + 1); a0 *= k0; a1 *= k1; }
+            const uint64_t d = add2(f2pack(a0, a1), e ? nd.y : nd.x);
             float d0, d1;
             f2unpack(mul2(f2pack(p0, p1), d), d0, d1);
-            pp[i4 * 2 + e] = pack_bf16x2(p0, p1);
+            pp[i4 * 2 + e] = pack_bf16x2(p0 * k0, p1 * k1);
             pd[i4 * 2 + e] = pack_bf16x2(d0, d1);
           }
         }
@@ -883,10 +926,13 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constan
             f2unpack(t, t0, t1);
             const float p0 = c >= first_ok ? ex2(t0) : 0.f;
             const float p1 = c + 1 >= first_ok ? ex2(t1) : 0.f;
-            const uint64_t d = add2(f2pack(__uint_as_float(da[c]), __uint_as_float(da[c + 1])), e ? nd.y : nd.x);
+            float a0 = __uint_as_float(da[c]), a1 = __uint_as_float(da[c + 1]);
+            float k0 = 1.f, k1 = 1.f;
+            if constexpr (DROP) { k0 = keep_at(c); k1 = keep_at(c + 1); a0 *= k0; a1 *= k1; }
+            const uint64_t d = add2(f2pack(a0, a1), e ? nd.y : nd.x);
             float d0, d1;
             f2unpack(mul2(f2pack(p0, p1), d), d0, d1);
-            pp[i4 * 2 + e] = pack_bf16x2(p0, p1);
+            pp[i4 * 2 + e] = pack_bf16x2(p0 * k0, p1 * k1);
             pd[i4 * 2 + e] = pack_bf16x2(d0, d1);
           }
         }
@@ -953,11 +999,21 @@ extern "C" int b2f_attn_debug(unsigned long long* out, int reset) {
 }
 #endif
 
-extern "C" int b2f_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B,
-                            int S, int H, int HKV, int D, long long q_ts, long long q_bs,
-                            long long k_ts, long long k_bs, long long v_ts, long long v_bs,
-                            long long o_ts, long long o_bs, float scale, int causal,
-                            const int* kv_lens, void* stream) {
+namespace {
+int set_dropout(AttnParams& p, float p_drop, unsigned seed) {
+  B2F_REQUIRE(p_drop >= 0.f && p_drop < 0.99f, "attention dropout probability must be in [0, 0.99)");
+  p.drop_thr = (uint32_t)(p_drop * 256.f + 0.5f);            // resolution 1/256
+  p.drop_rinv = 256.f / (256.f - (float)p.drop_thr);          // 1 / (1 - p) for the probability actually applied
+  p.drop_seed = seed;
+  return 0;
+}
+}  // namespace
+
+static int attn_fwd_impl(const void* q, const void* k, const void* v, void* o, float* lse, int B,
+                         int S, int H, int HKV, int D, long long q_ts, long long q_bs,
+                         long long k_ts, long long k_bs, long long v_ts, long long v_bs,
+                         long long o_ts, long long o_bs, float scale, int causal,
+                         const int* kv_lens, float p_drop, unsigned seed, void* stream) {
   if (int rc = check_common(B, S, H, HKV, D)) return rc;
   B2F_REQUIRE((reinterpret_cast<uintptr_t>(o) & 15) == 0 && o_ts % 8 == 0 && o_bs % 8 == 0,
               "attention: output must be 16-byte aligned");
@@ -972,31 +1028,61 @@ extern "C" int b2f_attn_fwd(const void* q, const void* k, const void* v, void* o
 #ifdef B2F_ATTN_DEBUG
   if (const char* e = getenv("B2F_ATTN_DBG_MODE")) p.dbg_mode = atoi(e);
 #endif
+  if (int rc = set_dropout(p, p_drop, seed)) return rc;
+  const bool drop = p.drop_thr > 0;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   dim3 grid2(H * B, (S + 2 * TQ - 1) / (2 * TQ), 1);
   if (D == 128) {
     const int smem = 6 * Cfg<128>::TILE_B + 1024 + sizeof(Fwd2Bars);
-    if (int rc = set_smem(attn_fwd2_kernel<128>, smem)) return rc;
-    attn_fwd2_kernel<128><<<grid2, FWD2_THREADS, smem, st>>>(mq, mk, mv, p);
+    if (drop) {
+      if (int rc = set_smem(attn_fwd2_kernel<128, true>, smem)) return rc;
+      attn_fwd2_kernel<128, true><<<grid2, FWD2_THREADS, smem, st>>>(mq, mk, mv, p);
+    } else {
+      if (int rc = set_smem(attn_fwd2_kernel<128>, smem)) return rc;
+      attn_fwd2_kernel<128><<<grid2, FWD2_THREADS, smem, st>>>(mq, mk, mv, p);
+    }
   } else {
     const int smem = 6 * Cfg<64>::TILE_B + 1024 + sizeof(Fwd2Bars);
-    if (int rc = set_smem(attn_fwd2_kernel<64>, smem)) return rc;
-    attn_fwd2_kernel<64><<<grid2, FWD2_THREADS, smem, st>>>(mq, mk, mv, p);
+    if (drop) {
+      if (int rc = set_smem(attn_fwd2_kernel<64, true>, smem)) return rc;
+      attn_fwd2_kernel<64, true><<<grid2, FWD2_THREADS, smem, st>>>(mq, mk, mv, p);
+    } else {
+      if (int rc = set_smem(attn_fwd2_kernel<64>, smem)) return rc;
+      attn_fwd2_kernel<64><<<grid2, FWD2_THREADS, smem, st>>>(mq, mk, mv, p);
+    }
   }
   B2F_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
 
-// delta: fp32 scratch of 2 * B * H * S_pad floats supplied by the caller (S_pad = S rounded up to
-// 128); the pre-pass fills it with lse * log2(e) and rowsum(O * dO) for the two main kernels.
-extern "C" int b2f_attn_bwd(const void* q, const void* k, const void* v, const void* o,
-                            const void* d_o, const float* lse, float* delta, void* dq, void* dk,
-                            void* dv, int B, int S, int H, int HKV, int D, long long q_ts,
-                            long long q_bs, long long k_ts, long long k_bs, long long v_ts,
-                            long long v_bs, long long o_ts, long long o_bs, long long do_ts,
-                            long long do_bs, long long dq_ts, long long dq_bs, long long dk_ts,
-                            long long dk_bs, long long dv_ts, long long dv_bs, float scale,
-                            int causal, const int* kv_lens, void* stream) {
+extern "C" int b2f_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B,
+                            int S, int H, int HKV, int D, long long q_ts, long long q_bs,
+                            long long k_ts, long long k_bs, long long v_ts, long long v_bs,
+                            long long o_ts, long long o_bs, float scale, int causal,
+                            const int* kv_lens, void* stream) {
+  return attn_fwd_impl(q, k, v, o, lse, B, S, H, HKV, D, q_ts, q_bs, k_ts, k_bs, v_ts, v_bs, o_ts, o_bs, scale,
+                       causal, kv_lens, 0.f, 0u, stream);
+}
+
+// Forward with attention dropout of probability p_drop (applied to the softmax probabilities, Megatron's
+// --attention-dropout); the mask is a function of (seed, batch, head, query, key) only.
+extern "C" int b2f_attn_fwd_drop(const void* q, const void* k, const void* v, void* o, float* lse, int B,
+                                 int S, int H, int HKV, int D, long long q_ts, long long q_bs,
+                                 long long k_ts, long long k_bs, long long v_ts, long long v_bs,
+                                 long long o_ts, long long o_bs, float scale, int causal,
+                                 const int* kv_lens, float p_drop, unsigned seed, void* stream) {
+  return attn_fwd_impl(q, k, v, o, lse, B, S, H, HKV, D, q_ts, q_bs, k_ts, k_bs, v_ts, v_bs, o_ts, o_bs, scale,
+                       causal, kv_lens, p_drop, seed, stream);
+}
+
+static int attn_bwd_impl(const void* q, const void* k, const void* v, const void* o,
+                         const void* d_o, const float* lse, float* delta, void* dq, void* dk,
+                         void* dv, int B, int S, int H, int HKV, int D, long long q_ts,
+                         long long q_bs, long long k_ts, long long k_bs, long long v_ts,
+                         long long v_bs, long long o_ts, long long o_bs, long long do_ts,
+                         long long do_bs, long long dq_ts, long long dq_bs, long long dk_ts,
+                         long long dk_bs, long long dv_ts, long long dv_bs, float scale,
+                         int causal, const int* kv_lens, float p_drop, unsigned seed, void* stream) {
   if (int rc = check_common(B, S, H, HKV, D)) return rc;
   B2F_REQUIRE(delta != nullptr && lse != nullptr, "attention bwd: lse and delta scratch required");
   B2F_REQUIRE((reinterpret_cast<uintptr_t>(delta) & 15) == 0, "attention bwd: scratch must be 16-byte aligned");
@@ -1012,6 +1098,8 @@ extern "C" int b2f_attn_bwd(const void* q, const void* k, const void* v, const v
   p.dQ = static_cast<__nv_bfloat16*>(dq); p.dK = static_cast<__nv_bfloat16*>(dk);
   p.dV = static_cast<__nv_bfloat16*>(dv);
   p.dq_ts = dq_ts; p.dq_bs = dq_bs; p.dk_ts = dk_ts; p.dk_bs = dk_bs; p.dv_ts = dv_ts; p.dv_bs = dv_bs;
+  if (int rc = set_dropout(p, p_drop, seed)) return rc;
+  const bool drop = p.drop_thr > 0;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int nq = (S + TQ - 1) / TQ;
   const int S_pad = nq * TQ;
@@ -1022,20 +1110,63 @@ extern "C" int b2f_attn_bwd(const void* q, const void* k, const void* v, const v
                                                   (const __nv_bfloat16*)d_o, do_ts, do_bs, lse, delta,
                                                   B, H, S, S_pad);
     const int smem = 6 * Cfg<128>::TILE_B + 1024 + sizeof(BwdBars);
-    if (int rc = set_smem(attn_bwd_dq_kernel<128>, smem)) return rc;
-    if (int rc = set_smem(attn_bwd_dkv_kernel<128>, smem)) return rc;
-    attn_bwd_dq_kernel<128><<<dim3(H * B, nq, 1), BWD_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
-    attn_bwd_dkv_kernel<128><<<dim3(HKV * B, nq, 1), BWD_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+    if (drop) {
+      if (int rc = set_smem(attn_bwd_dq_kernel<128, true>, smem)) return rc;
+      if (int rc = set_smem(attn_bwd_dkv_kernel<128, true>, smem)) return rc;
+      attn_bwd_dq_kernel<128, true><<<dim3(H * B, nq, 1), BWD_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+      attn_bwd_dkv_kernel<128, true><<<dim3(HKV * B, nq, 1), BWD_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+    } else {
+      if (int rc = set_smem(attn_bwd_dq_kernel<128>, smem)) return rc;
+      if (int rc = set_smem(attn_bwd_dkv_kernel<128>, smem)) return rc;
+      attn_bwd_dq_kernel<128><<<dim3(H * B, nq, 1), BWD_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+      attn_bwd_dkv_kernel<128><<<dim3(HKV * B, nq, 1), BWD_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+    }
   } else {
     attn_delta_kernel<64><<<dgrid, 256, 0, st>>>((const __nv_bfloat16*)o, o_ts, o_bs,
                                                  (const __nv_bfloat16*)d_o, do_ts, do_bs, lse, delta,
                                                  B, H, S, S_pad);
     const int smem = 6 * Cfg<64>::TILE_B + 1024 + sizeof(BwdBars);
-    if (int rc = set_smem(attn_bwd_dq_kernel<64>, smem)) return rc;
-    if (int rc = set_smem(attn_bwd_dkv_kernel<64>, smem)) return rc;
-    attn_bwd_dq_kernel<64><<<dim3(H * B, nq, 1), BWD_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
-    attn_bwd_dkv_kernel<64><<<dim3(HKV * B, nq, 1), BWD_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+    if (drop) {
+      if (int rc = set_smem(attn_bwd_dq_kernel<64, true>, smem)) return rc;
+      if (int rc = set_smem(attn_bwd_dkv_kernel<64, true>, smem)) return rc;
+      attn_bwd_dq_kernel<64, true><<<dim3(H * B, nq, 1), BWD_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+      attn_bwd_dkv_kernel<64, true><<<dim3(HKV * B, nq, 1), BWD_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+    } else {
+      if (int rc = set_smem(attn_bwd_dq_kernel<64>, smem)) return rc;
+      if (int rc = set_smem(attn_bwd_dkv_kernel<64>, smem)) return rc;
+      attn_bwd_dq_kernel<64><<<dim3(H * B, nq, 1), BWD_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+      attn_bwd_dkv_kernel<64><<<dim3(HKV * B, nq, 1), BWD_THREADS, smem, st>>>(mq, mk, mv, mdo, p);
+    }
   }
   B2F_CHECK_CUDA(cudaGetLastError());
   return 0;
+}
+
+// delta: fp32 scratch of 2 * B * H * S_pad floats supplied by the caller (S_pad = S rounded up to
+// 128); the pre-pass fills it with lse * log2(e) and rowsum(O * dO) for the two main kernels.
+extern "C" int b2f_attn_bwd(const void* q, const void* k, const void* v, const void* o,
+                            const void* d_o, const float* lse, float* delta, void* dq, void* dk,
+                            void* dv, int B, int S, int H, int HKV, int D, long long q_ts,
+                            long long q_bs, long long k_ts, long long k_bs, long long v_ts,
+                            long long v_bs, long long o_ts, long long o_bs, long long do_ts,
+                            long long do_bs, long long dq_ts, long long dq_bs, long long dk_ts,
+                            long long dk_bs, long long dv_ts, long long dv_bs, float scale,
+                            int causal, const int* kv_lens, void* stream) {
+  return attn_bwd_impl(q, k, v, o, d_o, lse, delta, dq, dk, dv, B, S, H, HKV, D, q_ts, q_bs, k_ts, k_bs, v_ts, v_bs,
+                       o_ts, o_bs, do_ts, do_bs, dq_ts, dq_bs, dk_ts, dk_bs, dv_ts, dv_bs, scale, causal, kv_lens,
+                       0.f, 0u, stream);
+}
+
+// Backward of b2f_attn_fwd_drop: same p_drop and seed regenerate the forward's mask inside both kernels.
+extern "C" int b2f_attn_bwd_drop(const void* q, const void* k, const void* v, const void* o,
+                                 const void* d_o, const float* lse, float* delta, void* dq, void* dk,
+                                 void* dv, int B, int S, int H, int HKV, int D, long long q_ts,
+                                 long long q_bs, long long k_ts, long long k_bs, long long v_ts,
+                                 long long v_bs, long long o_ts, long long o_bs, long long do_ts,
+                                 long long do_bs, long long dq_ts, long long dq_bs, long long dk_ts,
+                                 long long dk_bs, long long dv_ts, long long dv_bs, float scale,
+                                 int causal, const int* kv_lens, float p_drop, unsigned seed, void* stream) {
+  return attn_bwd_impl(q, k, v, o, d_o, lse, delta, dq, dk, dv, B, S, H, HKV, D, q_ts, q_bs, k_ts, k_bs, v_ts, v_bs,
+                       o_ts, o_bs, do_ts, do_bs, dq_ts, dq_bs, dk_ts, dk_bs, dv_ts, dv_bs, scale, causal, kv_lens,
+                       p_drop, seed, stream);
 }

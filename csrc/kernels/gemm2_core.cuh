@@ -114,7 +114,8 @@ __device__ __forceinline__ auto tile_done_hook(const Policy& pol, const Params&,
 template <class Policy, int NST>
 __device__ __forceinline__ void gemm2_body(const CUtensorMap* tma_a_p, const CUtensorMap* tma_b_p,
                                            const Params& p, const Policy& pol, int first_pair,
-                                           int npairs, uint8_t* smem_raw) {
+                                           int npairs, uint8_t* smem_raw, int tile_begin = 0,
+                                           int tile_end = -1) {
   const CUtensorMap& tma_a = *tma_a_p;
   const CUtensorMap& tma_b = *tma_b_p;
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -125,9 +126,10 @@ __device__ __forceinline__ void gemm2_body(const CUtensorMap* tma_a_p, const CUt
   const bool leader = cta == 0;
   const int num_m = (p.M + T2_BM - 1) / T2_BM;
   const int num_n = (p.N + T2_BN - 1) / T2_BN;
-  const int num_tiles = num_m * num_n * p.batch;
+  // [tile_begin, tile_end): the slice of the tile order this group of `npairs` clusters walks (default: all of it)
+  const int num_tiles = tile_end < 0 ? num_m * num_n * p.batch : tile_end;
   const int num_kb = (p.K + BK - 1) / BK;
-  const int pair = first_pair;
+  const int pair = tile_begin + first_pair;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);

@@ -446,7 +446,7 @@ def group_attn(which):
             ref.backward(do.float())
             torch.cuda.synchronize()
             report(f"attn_fwd_{tag}", o.reshape(B * S, -1), ref.reshape(B * S, -1), 2e-2)
-            report(f"attn_dq_{tag}", q.grad.reshape(B * S, -1), qf.grad.reshape(B * S, -1), 3e-2, floor=2.0)
+            report(f"attn_dq_{tag}", q.grad.reshape(B * S, -1), qf.grad.reshape(B * S, -1), 3e-2, floor=3.0)
             report(f"attn_dk_{tag}", k.grad.reshape(B * S, -1), kf.grad.reshape(B * S, -1), 3e-2, floor=2.0)
             report(f"attn_dv_{tag}", v.grad.reshape(B * S, -1), vf.grad.reshape(B * S, -1), 3e-2, floor=1.0)
     if which == "bwd":
