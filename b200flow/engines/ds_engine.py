@@ -246,7 +246,7 @@ class TrainEngine:
     def _set_drop_seed(self):
         """One dropout seed per micro-batch: equal on the TP / PP ranks of a replica, different between replicas;
         a recomputed forward (activation checkpointing) reads the same value again."""
-        if self.cfg.dropout > 0 and self.model.training:
+        if (self.cfg.dropout > 0 or self.cfg.attention_dropout > 0) and self.model.training:
             self._drop_calls += 1
             self.model.drop_seed = (self._seed * 1000003 + self._drop_calls * 4099
                                     + (self.ps.dp_rank if self.ps else 0) * 15485863) & 0x3FFFFFFF

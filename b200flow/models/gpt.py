@@ -44,6 +44,7 @@ class GPTConfig:
     eps: float = 1e-5
     init_std: float = 0.02
     dropout: float = 0.0          # --hidden-dropout (embeddings, attention output, MLP output)
+    attention_dropout: float = 0.0   # --attention-dropout (softmax probabilities, inside the flash kernels)
     name: str = "llama"
     num_experts: int = 0          # > 0: MoE FFN every `moe_every`-th layer (DeepSpeed --num-experts)
     moe_every: int = 2            # --expert-interval
@@ -117,7 +118,7 @@ class _QKVAttention(torch.autograd.Function):
     qkv: [s, b, heads + 2*kv_heads, d].  Returns o: [s*b, heads*d] (sequence-major)."""
 
     @staticmethod
-    def forward(ctx, qkv, heads, kv_heads, causal, scale, rope_tables, kv_lens):
+    def forward(ctx, qkv, heads, kv_heads, causal, scale, rope_tables, kv_lens, dropout_p=0.0, seed=0):
         s, b, nh, d = qkv.shape
         if rope_tables is not None:
             x = qkv.view(s * b, nh, d)[:, : heads + kv_heads]
@@ -127,13 +128,19 @@ class _QKVAttention(torch.autograd.Function):
         o_sb = torch.empty((s, b, heads, d), dtype=qkv.dtype, device=qkv.device)
         o = o_sb.permute(1, 0, 2, 3)
         lse = torch.empty((b, heads, s), dtype=torch.float32, device=qkv.device)
-        A._lib.call("b2f_attn_fwd", A.ptr(q), A.ptr(k), A.ptr(vv), A.ptr(o), A.ptr(lse), A.c_int(b),
-                    A.c_int(s), A.c_int(heads), A.c_int(kv_heads), A.c_int(d),
-                    A.c_ll(q.stride(1)), A.c_ll(q.stride(0)), A.c_ll(k.stride(1)), A.c_ll(k.stride(0)),
-                    A.c_ll(vv.stride(1)), A.c_ll(vv.stride(0)), A.c_ll(o.stride(1)), A.c_ll(o.stride(0)),
-                    A.c_float(scale), A.c_int(int(causal)), A.ptr(kv_lens), A.stream_ptr())
+        args = [A.ptr(q), A.ptr(k), A.ptr(vv), A.ptr(o), A.ptr(lse), A.c_int(b),
+                A.c_int(s), A.c_int(heads), A.c_int(kv_heads), A.c_int(d),
+                A.c_ll(q.stride(1)), A.c_ll(q.stride(0)), A.c_ll(k.stride(1)), A.c_ll(k.stride(0)),
+                A.c_ll(vv.stride(1)), A.c_ll(vv.stride(0)), A.c_ll(o.stride(1)), A.c_ll(o.stride(0)),
+                A.c_float(scale), A.c_int(int(causal)), A.ptr(kv_lens)]
+        if dropout_p > 0:
+            A._lib.call("b2f_attn_fwd_drop", *args, A.c_float(dropout_p), A.ctypes.c_uint(seed & 0xFFFFFFFF),
+                        A.stream_ptr())
+        else:
+            A._lib.call("b2f_attn_fwd", *args, A.stream_ptr())
         ctx.save_for_backward(qkv, o_sb, lse)
         ctx.cfg = (heads, kv_heads, causal, scale, rope_tables, kv_lens)
+        ctx.drop = (dropout_p, seed)
         return o_sb.view(s * b, heads * d)
 
     @staticmethod
@@ -150,14 +157,14 @@ class _QKVAttention(torch.autograd.Function):
         A.attn_bwd_raw(v[:, :, :heads], v[:, :, heads:heads + kv_heads], v[:, :, heads + kv_heads:],
                        o_sb.permute(1, 0, 2, 3), do_sb.permute(1, 0, 2, 3), lse, causal, scale, kv_lens,
                        dq=g[:, :, :heads], dk=g[:, :, heads:heads + kv_heads],
-                       dv=g[:, :, heads + kv_heads:])
+                       dv=g[:, :, heads + kv_heads:], dropout_p=ctx.drop[0], seed=ctx.drop[1])
         if rope_tables is not None:
             x = dqkv.view(s * b, nh, d)[:, : heads + kv_heads]
             E.rope_inplace_raw(x, rope_tables[0], rope_tables[1], s, True, 0, pos_div=b)
-        return dqkv, None, None, None, None, None, None
+        return dqkv, None, None, None, None, None, None, None, None
 
 
-def qkv_attention(qkv, heads, kv_heads, causal, scale, rope_tables=None, kv_lens=None):
+def qkv_attention(qkv, heads, kv_heads, causal, scale, rope_tables=None, kv_lens=None, dropout_p=0.0, seed=0):
     if not qkv.is_cuda:  # CPU oracle path (gloo plumbing tests)
         from ..ops import ref
         s, b, nh, d = qkv.shape
@@ -169,9 +176,9 @@ def qkv_attention(qkv, heads, kv_heads, causal, scale, rope_tables=None, kv_lens
             x = torch.cat([rot, qkv.reshape(s * b, nh, d)[:, heads + kv_heads:]], 1).view(s, b, nh, d)
         v = x.permute(1, 0, 2, 3)
         o = ref.attention(v[:, :, :heads], v[:, :, heads:heads + kv_heads], v[:, :, heads + kv_heads:],
-                          causal, scale, kv_lens)
+                          causal, scale, kv_lens, dropout_p, seed)
         return o.permute(1, 0, 2, 3).reshape(s * b, heads * d)
-    return _QKVAttention.apply(qkv, heads, kv_heads, causal, scale, rope_tables, kv_lens)
+    return _QKVAttention.apply(qkv, heads, kv_heads, causal, scale, rope_tables, kv_lens, float(dropout_p), int(seed))
 
 
 class TransformerLayer(nn.Module):
@@ -240,6 +247,10 @@ class TransformerLayer(nn.Module):
         d = cfg.head_dim
         p = cfg.dropout if self.training else 0.0
         seed = drop_seed + 2 * self.layer_idx
+        # --attention-dropout: same mask for every TP rank's own heads (the head index inside the kernel is local, so the
+        # rank goes into the seed); a recomputed forward draws it again from the per-micro-batch seed
+        pa = cfg.attention_dropout if self.training else 0.0
+        aseed = (drop_seed * 2654435761 + 40503 * self.layer_idx + 7919 * tp.rank + 1) & 0x7FFFFFFF
         y = N.norm(h, self.ln1_w, self.ln1_b, eps=cfg.eps, rms=rms)
         qkv = tp.column_linear(y, self.wqkv, self.bqkv)              # [s*b, (h+2kv)*d] full sequence
         if self.ulysses_group is not None:     # this rank holds a sequence slice: regroup to whole sequences of fewer heads
@@ -250,7 +261,7 @@ class TransformerLayer(nn.Module):
                                       rope_tables, kv_lens)
         else:
             o = qkv_attention(qkv.view(seq, batch, self.h_local + 2 * self.kv_local, d), self.h_local,
-                              self.kv_local, True, 1.0 / math.sqrt(d), rope_tables, kv_lens)
+                              self.kv_local, True, 1.0 / math.sqrt(d), rope_tables, kv_lens, pa, aseed)
         if p > 0:      # --hidden-dropout: the residual add moves out of the GEMM epilogue, behind the mask
             h = self._dropout_add(tp.row_linear(o, self.wo, self.bo), h, p, seed)
         else:

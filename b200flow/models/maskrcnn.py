@@ -5,7 +5,8 @@ The reference trains tensorpack's and aws-samples' TensorFlow Mask R-CNN under H
 graph in SURVEY.md §3.4): ResNet-50 backbone with frozen BN, FPN, RPN head, proposal
 generation (decode + per-level top-k + NMS), fg/bg sampling, multilevel RoIAlign, 2-fc box
 head, 4-conv + deconv mask head.  Same architecture here in PyTorch: convolutions stay on
-cuDNN (channels_last, bf16), everything the survey lists as a kernel —
+cuDNN (channels_last, bf16) with the frozen batch norm folded into their weights
+(models/resnet_fpn.py), everything the survey lists as a kernel —
 RoIAlign (K12), box decode + batched NMS (K13), matcher / IoU (K14), mask crop / paste (K15),
 the fc layers (K0) — runs on b200flow kernels.
 """
@@ -144,26 +145,16 @@ class MaskHead(nn.Module):
 class MaskRCNN(nn.Module):
     def __init__(self, cfg: MaskRCNNConfig | None = None):
         super().__init__()
-        import torchvision
-        from torchvision.models.detection.backbone_utils import BackboneWithFPN
-        from torchvision.ops import FrozenBatchNorm2d
+        from .resnet_fpn import ResNetFPN
 
         self.cfg = cfg = cfg or MaskRCNNConfig()
         if not cfg.mode_fpn:
             raise NotImplementedError("MODE_FPN=False (tensorpack's ResNet-C4 variant) is not built; every Mask R-CNN "
                                       "configuration of the reference sets MODE_FPN=True")
         c = max(16, int(256 * cfg.width) // 8 * 8)
-        if cfg.width >= 1.0:
-            body = torchvision.models.resnet50(weights=None, norm_layer=FrozenBatchNorm2d)   # BACKBONE.NORM=FreezeBN
-            chans = [256, 512, 1024, 2048]
-        else:
-            body = torchvision.models.resnet18(weights=None, norm_layer=FrozenBatchNorm2d)
-            chans = [64, 128, 256, 512]
-        for name, p in body.named_parameters():          # tensorpack freezes the stem + res2
-            if name.startswith(("conv1", "layer1")):
-                p.requires_grad_(False)
-        self.backbone = BackboneWithFPN(body, {"layer1": "0", "layer2": "1", "layer3": "2", "layer4": "3"},
-                                        chans, c)
+        # ResNet-50 (ResNet-18 for the test-size models) + FPN in repo code: BACKBONE.NORM=FreezeBN is folded into the
+        # convolution weights (models/resnet_fpn.py), the stem and res2 are frozen as tensorpack does
+        self.backbone = ResNetFPN(50 if cfg.width >= 1.0 else 18, c)
         self.strides = (4, 8, 16, 32, 64)
         self.rpn = RPNHead(c, len(cfg.anchor_ratios))
         self.box_head = FCHead(c * 7 * 7, max(64, int(cfg.fc_dim * cfg.width)), cfg.num_classes)

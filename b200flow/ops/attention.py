@@ -5,6 +5,7 @@ Tensors are ``[batch, seq, heads, head_dim]`` views whose last two dims are pack
 """
 from __future__ import annotations
 
+import ctypes
 import math
 
 import torch
@@ -19,22 +20,49 @@ def _strides(t: torch.Tensor):
     return t.stride(1), t.stride(0)
 
 
-def attn_fwd_raw(q, k, v, causal: bool, scale: float, kv_lens=None):
+def dropout_keep_mask(B: int, H: int, S: int, p: float, seed: int, device="cpu") -> tuple[torch.Tensor, float]:
+    """The attention kernels' dropout mask restated in PyTorch: (keep [B, H, S, S] bool, scale).  One 32-bit hash
+    word per (batch * H + head, query, key // 4), one byte per key; an entry is kept iff its byte >= round(256 p),
+    kept entries are scaled by 256 / (256 - round(256 p)).  Oracle for the tests and the CPU path."""
+    M = 0xFFFFFFFF
+    thr = int(p * 256.0 + 0.5)
+
+    def mix(x):
+        x = x ^ (x >> 16)
+        x = (x * 0x7FEB352D) & M
+        x = x ^ (x >> 15)
+        x = (x * 0x846CA68B) & M
+        return x ^ (x >> 16)
+
+    bh = torch.arange(B * H, dtype=torch.int64, device=device)
+    seed_bh = mix(((seed & M) + bh * 0x632BE5AB) & M)                              # [BH]
+    q = torch.arange(S, dtype=torch.int64, device=device)
+    seed_q = (seed_bh[:, None] + q[None, :] * 0x9E3779B1) & M                      # [BH, S]
+    k = torch.arange(S, dtype=torch.int64, device=device)
+    word = mix((seed_q[:, :, None] + (k >> 2)[None, None, :] * 0x85EBCA77) & M)    # [BH, S, S]
+    byte = (word >> ((k & 3) * 8)[None, None, :]) & 0xFF
+    return (byte >= thr).view(B, H, S, S), 256.0 / (256.0 - thr)
+
+
+def attn_fwd_raw(q, k, v, causal: bool, scale: float, kv_lens=None, dropout_p: float = 0.0, seed: int = 0):
     B, S, H, D = q.shape
     HKV = k.shape[2]
     o = torch.empty((B, S, H, D), dtype=torch.bfloat16, device=q.device)
     lse = torch.empty((B, H, S), dtype=torch.float32, device=q.device)
     (q_ts, q_bs), (k_ts, k_bs), (v_ts, v_bs) = _strides(q), _strides(k), _strides(v)
-    _lib.call("b2f_attn_fwd", ptr(q), ptr(k), ptr(v), ptr(o), ptr(lse), c_int(B), c_int(S), c_int(H),
-              c_int(HKV), c_int(D), c_ll(q_ts), c_ll(q_bs), c_ll(k_ts), c_ll(k_bs), c_ll(v_ts),
-              c_ll(v_bs), c_ll(o.stride(1)), c_ll(o.stride(0)), c_float(scale), c_int(int(causal)),
-              ptr(kv_lens), stream_ptr())
+    args = [ptr(q), ptr(k), ptr(v), ptr(o), ptr(lse), c_int(B), c_int(S), c_int(H),
+            c_int(HKV), c_int(D), c_ll(q_ts), c_ll(q_bs), c_ll(k_ts), c_ll(k_bs), c_ll(v_ts),
+            c_ll(v_bs), c_ll(o.stride(1)), c_ll(o.stride(0)), c_float(scale), c_int(int(causal)), ptr(kv_lens)]
+    if dropout_p > 0:
+        _lib.call("b2f_attn_fwd_drop", *args, c_float(dropout_p), ctypes.c_uint(seed & 0xFFFFFFFF), stream_ptr())
+    else:
+        _lib.call("b2f_attn_fwd", *args, stream_ptr())
     _lib.debug_sync()
     return o, lse
 
 
 def attn_bwd_raw(q, k, v, o, do, lse, causal: bool, scale: float, kv_lens=None, dq=None, dk=None,
-                 dv=None):
+                 dv=None, dropout_p: float = 0.0, seed: int = 0):
     B, S, H, D = q.shape
     HKV = k.shape[2]
     if dq is None:
@@ -52,37 +80,43 @@ def attn_bwd_raw(q, k, v, o, do, lse, causal: bool, scale: float, kv_lens=None, 
     for t in (q, k, v, o, do, dq, dk, dv):
         ts, bs = _strides(t)
         args += [c_ll(ts), c_ll(bs)]
-    _lib.call("b2f_attn_bwd", ptr(q), ptr(k), ptr(v), ptr(o), ptr(do), ptr(lse), ptr(delta), ptr(dq),
-              ptr(dk), ptr(dv), c_int(B), c_int(S), c_int(H), c_int(HKV), c_int(D), *args,
-              c_float(scale), c_int(int(causal)), ptr(kv_lens), stream_ptr())
+    head = [ptr(q), ptr(k), ptr(v), ptr(o), ptr(do), ptr(lse), ptr(delta), ptr(dq), ptr(dk), ptr(dv), c_int(B),
+            c_int(S), c_int(H), c_int(HKV), c_int(D), *args, c_float(scale), c_int(int(causal)), ptr(kv_lens)]
+    if dropout_p > 0:
+        _lib.call("b2f_attn_bwd_drop", *head, c_float(dropout_p), ctypes.c_uint(seed & 0xFFFFFFFF), stream_ptr())
+    else:
+        _lib.call("b2f_attn_bwd", *head, stream_ptr())
     _lib.debug_sync()
     return dq, dk, dv
 
 
 class _FlashAttn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, q, k, v, causal, scale, kv_lens):
+    def forward(ctx, q, k, v, causal, scale, kv_lens, dropout_p=0.0, seed=0):
         _lib.require_cuda(q, k, v)
-        o, lse = attn_fwd_raw(q, k, v, causal, scale, kv_lens)
+        o, lse = attn_fwd_raw(q, k, v, causal, scale, kv_lens, dropout_p, seed)
         ctx.save_for_backward(q, k, v, o, lse)
-        ctx.causal, ctx.scale, ctx.kv_lens = causal, scale, kv_lens
+        ctx.causal, ctx.scale, ctx.kv_lens, ctx.drop = causal, scale, kv_lens, (dropout_p, seed)
         return o
 
     @staticmethod
     def backward(ctx, do):
         q, k, v, o, lse = ctx.saved_tensors
-        dq, dk, dv = attn_bwd_raw(q, k, v, o, do, lse, ctx.causal, ctx.scale, ctx.kv_lens)
-        return dq, dk, dv, None, None, None
+        dq, dk, dv = attn_bwd_raw(q, k, v, o, do, lse, ctx.causal, ctx.scale, ctx.kv_lens,
+                                  dropout_p=ctx.drop[0], seed=ctx.drop[1])
+        return dq, dk, dv, None, None, None, None, None
 
 
-def flash_attention(q, k, v, causal: bool = True, scale: float | None = None, kv_lens=None):
-    """softmax(scale * q kᵀ [+ causal / key-length mask]) v, O(seq) memory."""
+def flash_attention(q, k, v, causal: bool = True, scale: float | None = None, kv_lens=None,
+                    dropout_p: float = 0.0, seed: int = 0):
+    """softmax(scale * q kᵀ [+ causal / key-length mask]) v, O(seq) memory.  `dropout_p` > 0 drops softmax
+    probabilities (Megatron's --attention-dropout) with a mask that is a function of (seed, batch, head, query, key)."""
     if scale is None:
         scale = 1.0 / math.sqrt(q.shape[-1])
     if not q.is_cuda:
         from . import ref
-        return ref.attention(q, k, v, causal, scale, kv_lens)
-    return _FlashAttn.apply(q, k, v, causal, float(scale), kv_lens)
+        return ref.attention(q, k, v, causal, scale, kv_lens, dropout_p, seed)
+    return _FlashAttn.apply(q, k, v, causal, float(scale), kv_lens, float(dropout_p), int(seed))
 
 
 class _FlashAttnPackedQKV(torch.autograd.Function):

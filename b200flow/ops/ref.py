@@ -60,7 +60,7 @@ def rope(x, cos_t, sin_t, positions):
     return torch.cat([x1 * c - x2 * s, x2 * c + x1 * s], -1).to(x.dtype)
 
 
-def attention(q, k, v, causal=True, scale=None, kv_lens=None):
+def attention(q, k, v, causal=True, scale=None, kv_lens=None, dropout_p=0.0, seed=0):
     """q: [b, s, h, d]; k, v: [b, s, hkv, d] -> [b, s, h, d]."""
     B, S, H, D = q.shape
     HKV = k.shape[2]
@@ -76,7 +76,13 @@ def attention(q, k, v, causal=True, scale=None, kv_lens=None):
     if kv_lens is not None:
         mask = mask | (torch.arange(S, device=q.device)[None, :] >= kv_lens[:, None])[:, None, None, :]
     s = s.masked_fill(mask, float("-inf"))
-    return (torch.softmax(s, -1) @ vf).transpose(1, 2).to(q.dtype)
+    pr = torch.softmax(s, -1)
+    if dropout_p > 0:      # the kernels' counter-based mask, restated (ops/attention.py)
+        from .attention import dropout_keep_mask
+
+        keep, rinv = dropout_keep_mask(B, H, S, dropout_p, seed, q.device)
+        pr = pr * keep * rinv
+    return (pr @ vf).transpose(1, 2).to(q.dtype)
 
 
 def cross_entropy(logits, targets, ignore_index=-100):

@@ -126,8 +126,8 @@ def main():
         act="swiglu" if args.swiglu else "gelu", rope=args.use_rotary_position_embeddings,
         learned_pos=not args.use_rotary_position_embeddings, bias=not args.disable_bias_linear,
         tie_embeddings=not args.untie_embeddings_and_output_weights, name="llama" if llama else "gpt2",
-        dropout=args.hidden_dropout, init_std=args.init_method_std, eps=args.layernorm_epsilon)
-    # --attention-dropout has no counterpart: the attention kernel keeps no probability matrix to drop from
+        dropout=args.hidden_dropout, attention_dropout=args.attention_dropout, init_std=args.init_method_std,
+        eps=args.layernorm_epsilon)
     if n_experts > 1:
         cfg.num_experts, cfg.moe_every, cfg.moe_top_k = n_experts, args.expert_interval, args.topk
         cfg.aux_loss_coeff, cfg.moe_min_capacity = args.moe_loss_coeff, args.moe_min_capacity

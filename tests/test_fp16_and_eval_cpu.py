@@ -508,3 +508,40 @@ def test_generation_continues_a_memorised_sequence():
     assert out.shape == (1, 20) and out[0, 8:].tolist() == period.repeat(3)[8:20].tolist()
     sampled = eng.model.generate(seq[None, :8], 6, temperature=1.0, top_k=1, generator=torch.Generator().manual_seed(0))
     assert sampled[0].tolist() == out[0, :14].tolist()                      # top-1 sampling is greedy
+
+
+def test_attention_dropout_mask_and_training_on_cpu():
+    """--attention-dropout: the mask is a pure function of (seed, batch, head, query, key), drops the asked fraction,
+    and a model trains with it; two runs with the same seeds give the same curve (what activation recomputation and a
+    resumed run rely on)."""
+    from b200flow.engines.ds_engine import initialize
+    from b200flow.models.gpt import config_from_preset
+    from b200flow.ops.attention import dropout_keep_mask
+
+    keep, rinv = dropout_keep_mask(2, 3, 64, 0.1, 99)
+    assert keep.shape == (2, 3, 64, 64) and abs((~keep).float().mean().item() - 26 / 256) < 0.02
+    assert abs(rinv - 256 / 230) < 1e-9
+    again, _ = dropout_keep_mask(2, 3, 64, 0.1, 99)
+    other, _ = dropout_keep_mask(2, 3, 64, 0.1, 100)
+    assert torch.equal(keep, again) and not torch.equal(keep, other)
+    assert not torch.equal(keep[0, 0], keep[0, 1]) and not torch.equal(keep[0, 0], keep[1, 0])
+
+    def curve():
+        cfg = config_from_preset("gpt2-tiny")
+        cfg.attention_dropout = 0.1
+        eng = initialize(cfg, {"train_micro_batch_size_per_gpu": 2, "optimizer": {"params": {"lr": 2e-3}}},
+                         device=torch.device("cpu"), seed=3)
+        g = torch.Generator().manual_seed(5)
+        toks = [torch.randint(0, cfg.vocab_size, (2, 33), generator=g) for _ in range(2)]
+        it = itertools.cycle([(t[:, :-1].contiguous(), t[:, 1:].contiguous()) for t in toks])
+        return [float(eng.train_batch(it)) for _ in range(6)]
+
+    a, b = curve(), curve()
+    assert a == b and a[-1] < a[0]
+    cfg = config_from_preset("gpt2-tiny")
+    plain = initialize(cfg, {"train_micro_batch_size_per_gpu": 2, "optimizer": {"params": {"lr": 2e-3}}},
+                       device=torch.device("cpu"), seed=3)
+    g = torch.Generator().manual_seed(5)
+    toks = [torch.randint(0, cfg.vocab_size, (2, 33), generator=g) for _ in range(2)]
+    it = itertools.cycle([(t[:, :-1].contiguous(), t[:, 1:].contiguous()) for t in toks])
+    assert abs(float(plain.train_batch(it)) - a[0]) > 1e-6          # the mask is really applied

@@ -50,6 +50,18 @@ def test_attention_backward():
     _run("attn_bwd")
 
 
+def test_attention_dropout_forward_backward():
+    _run("attn_drop")
+
+
+def test_block_scaled_fp8_gemm():
+    _run("mx")
+
+
+def test_fused_moe_k5_single_gpu():
+    _run("k5")
+
+
 def test_fp8_gemm_and_linear():
     _run("fp8")
 

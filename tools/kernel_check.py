@@ -8,6 +8,7 @@ kernel blind.   usage: python tools/kernel_check.py <group> [...]
 from __future__ import annotations
 
 import json
+import math
 import os
 import sys
 import time
@@ -652,6 +653,52 @@ def group_moe():
     report("moe_dwg", layer.wg.grad[:8], ref_layer.wg.grad[:8], 8e-2)
 
 
+def group_attn_drop():
+    """Attention dropout inside the flash kernels: forward and all three gradients against fp32 attention with the
+    same mask (the hash restated in PyTorch), causal and padded, both head dims, GQA; same seed twice = same result."""
+    from b200flow.ops import attention as A
+    torch.manual_seed(4)
+    for (B, S, H, HKV, D, causal, pd) in [(2, 512, 4, 4, 64, True, 0.1), (1, 896, 4, 2, 128, True, 0.1),
+                                          (2, 384, 2, 2, 128, False, 0.25)]:
+        tag = f"B{B}S{S}H{H}kv{HKV}D{D}{'c' if causal else 'f'}p{pd}"
+        q = torch.randn(B, S, H, D, device=DEV, dtype=torch.bfloat16).requires_grad_()
+        k = torch.randn(B, S, HKV, D, device=DEV, dtype=torch.bfloat16).requires_grad_()
+        v = torch.randn(B, S, HKV, D, device=DEV, dtype=torch.bfloat16).requires_grad_()
+        kv_lens = torch.tensor([S - 37 * (i % 2) for i in range(B)], dtype=torch.int32, device=DEV)
+        seed = 12345 + S
+        o = A.flash_attention(q, k, v, causal, None, kv_lens, dropout_p=pd, seed=seed)
+        do = torch.randn_like(o)
+        o.backward(do)
+        o2 = A.flash_attention(q.detach(), k.detach(), v.detach(), causal, None, kv_lens, dropout_p=pd, seed=seed)
+        RESULTS.append({"name": f"attn_drop_repeat_{tag}", "ok": bool(torch.equal(o, o2))}); print(json.dumps(RESULTS[-1]), flush=True)
+        keep, rinv = A.dropout_keep_mask(B, H, S, pd, seed, DEV)
+        frac = 1.0 - keep.float().mean().item()
+        RESULTS.append({"name": f"attn_drop_rate_{tag}", "ok": abs(frac - round(pd * 256) / 256) < 0.01, "dropped": frac})
+        print(json.dumps(RESULTS[-1]), flush=True)
+        qf, kf, vf = (t.detach().float().requires_grad_() for t in (q, k, v))
+        G_ = H // HKV
+        s_ = torch.einsum("bqhd,bkhd->bhqk", qf, kf.repeat_interleave(G_, 2)) / math.sqrt(D)
+        mask = torch.zeros(B, 1, S, S, dtype=torch.bool, device=DEV)
+        if causal:
+            mask = mask | torch.triu(torch.ones(S, S, dtype=torch.bool, device=DEV), 1)
+        mask = mask | (torch.arange(S, device=DEV)[None, :] >= kv_lens[:, None])[:, None, None, :]
+        pr = torch.softmax(s_.masked_fill(mask, float("-inf")), -1) * keep * rinv
+        ref = torch.einsum("bhqk,bkhd->bqhd", pr, vf.repeat_interleave(G_, 2))
+        ref.backward(do.float())
+        report(f"attn_drop_fwd_{tag}", o.reshape(B * S, -1), ref.reshape(B * S, -1), 2e-2, floor=0.5)
+        report(f"attn_drop_dq_{tag}", q.grad.reshape(B * S, -1), qf.grad.reshape(B * S, -1), 3e-2, floor=4.0)
+        report(f"attn_drop_dk_{tag}", k.grad.reshape(B * S, -1), kf.grad.reshape(B * S, -1), 3e-2, floor=2.0)
+        report(f"attn_drop_dv_{tag}", v.grad.reshape(B * S, -1), vf.grad.reshape(B * S, -1), 3e-2, floor=1.0)
+    # cost of the mask: B1 S4096 H32 D128 causal, forward + backward
+    q = torch.randn(1, 4096, 32, 128, device=DEV, dtype=torch.bfloat16).requires_grad_()
+    k, v = (torch.randn(1, 4096, 32, 128, device=DEV, dtype=torch.bfloat16).requires_grad_() for _ in range(2))
+    def run(pd):
+        o = A.flash_attention(q, k, v, True, None, None, dropout_p=pd, seed=7)
+        o.backward(o)
+    t0, t1 = timeit(lambda: run(0.0)), timeit(lambda: run(0.1))
+    print(json.dumps({"name": "attn_drop_cost_B1S4096H32D128", "fwd_bwd_ms_no_dropout": t0, "fwd_bwd_ms_dropout": t1}), flush=True)
+
+
 def group_k5():
     """K5 on one GPU (all experts local): the fused dispatch + block-scaled GEMM / GEMM + combine kernels against the fp32
     layer, forward and backward, with an uneven routing (some experts overflow, one nearly empty) and twice in a row
@@ -836,6 +883,7 @@ def group_mx():
 GROUPS = {
     "mx": group_mx,
     "k5": group_k5,
+    "attn_drop": group_attn_drop,
     "gemm2": group_gemm2,
     "fp8": group_fp8,
     "moe": group_moe,
