@@ -4,6 +4,8 @@ Two shared objects are produced under ``b200flow/lib/``:
 
 * ``libb200flow_cuda.so`` — every sm_100a kernel under ``csrc/kernels`` and
   ``csrc/comm`` (nvcc, ``-gencode arch=compute_100a,code=sm_100a -lineinfo``).
+* ``libb200flow_cuda_fp16.so`` — the same sources with ``-DB2F_HALF_FP16``: IEEE fp16 as the 16-bit storage /
+  tensor-core operand type instead of bf16 (``B2F_HALF=fp16``; the reference's GPT-2 examples train with ``--fp16``).
 * ``libb200flow_host.so`` — pure C++ runtime pieces under ``csrc/host`` (dataset
   index builders, shared-memory mailbox, bucket planner); loads without a GPU.
 
@@ -61,26 +63,28 @@ def _compile(cmd: list[str], log: Path) -> None:
         raise RuntimeError(f"compile failed: {' '.join(cmd)}\n{res.stdout}\n{res.stderr}")
 
 
-def build_cuda(verbose: bool = False) -> Path:
+def build_cuda(verbose: bool = False, half: str = "bf16") -> Path:
     nvcc = _nvcc()
     LIB_DIR.mkdir(parents=True, exist_ok=True)
-    OBJ_DIR.mkdir(parents=True, exist_ok=True)
+    obj_dir = OBJ_DIR if half == "bf16" else OBJ_DIR.parent / "obj_fp16"
+    obj_dir.mkdir(parents=True, exist_ok=True)
+    extra = [] if half == "bf16" else ["-DB2F_HALF_FP16"]
     hdrs = _headers()
     srcs = sorted([*CSRC.glob("kernels/*.cu"), *CSRC.glob("comm/*.cu"), *CSRC.glob("common/*.cpp")])
     jobs, objs = [], []
     for s in srcs:
-        o = OBJ_DIR / (s.parent.name + "_" + s.stem + ".o")
+        o = obj_dir / (s.parent.name + "_" + s.stem + ".o")
         objs.append(o)
         if _newer(s, o, hdrs):
-            cmd = [nvcc, *NVCC_FLAGS, "-x", "cu", "-c", str(s), "-o", str(o)]
+            cmd = [nvcc, *NVCC_FLAGS, *extra, "-x", "cu", "-c", str(s), "-o", str(o)]
             jobs.append((cmd, o.with_suffix(".log")))
     if jobs:
         with cf.ThreadPoolExecutor(max_workers=min(8, len(jobs))) as ex:
             list(ex.map(lambda j: _compile(*j), jobs))
-    out = LIB_DIR / "libb200flow_cuda.so"
+    out = LIB_DIR / ("libb200flow_cuda.so" if half == "bf16" else "libb200flow_cuda_fp16.so")
     if jobs or not out.exists():
         _compile([nvcc, "-shared", "-o", str(out), *map(str, objs), "-lcudart"],
-                 OBJ_DIR / "link_cuda.log")
+                 obj_dir / "link_cuda.log")
     if verbose:
         print(f"built {out} ({len(jobs)} recompiled / {len(srcs)} sources)")
     return out
@@ -104,6 +108,7 @@ def build_host(verbose: bool = False) -> Path:
 def build_all(verbose: bool = False) -> None:
     build_host(verbose)
     build_cuda(verbose)
+    build_cuda(verbose, half="fp16")
 
 
 if __name__ == "__main__":

@@ -232,6 +232,11 @@ class Accelerator:
         self.local_process_index = int(os.environ.get("LOCAL_RANK", 0))
         self.device = torch.device("cuda", torch.cuda.current_device()) if use_cuda else torch.device("cpu")
         self.param_dtype = torch.bfloat16 if use_cuda else torch.float32
+        if use_cuda:       # mixed_precision="fp16" (the reference's --mixed_precision fp16): the fp16 build of the kernels
+            from ..ops import _lib
+
+            _lib.set_half("fp16" if self.mixed_precision == "fp16" else "bf16")
+            self.param_dtype = _lib.HALF
         self.scaler = GradScaler() if self.mixed_precision == "fp16" else None
         self._unscaled = False
         self.trackers: list[Tracker] = []
@@ -409,7 +414,7 @@ class Accelerator:
         """Mixed-precision region.  Parameters already live in the compute dtype (bf16 on B200), so this only
         wraps CPU-side or stray fp32 modules in torch's autocast."""
         if self.device.type == "cuda" and self.mixed_precision in ("fp16", "bf16"):
-            with torch.autocast("cuda", dtype=torch.bfloat16):
+            with torch.autocast("cuda", dtype=self.param_dtype):
                 yield
         else:
             yield

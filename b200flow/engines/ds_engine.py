@@ -20,6 +20,7 @@ ZeRO-1 over the DP group, TP+SP through TPContext, 1F1B over NCCL p2p.
 """
 from __future__ import annotations
 
+import os
 import warnings
 from typing import Iterator
 
@@ -72,6 +73,17 @@ class TrainEngine:
         dtype = torch.bfloat16 if self.device.type == "cuda" else torch.float32
         if config.get("bf16", {}).get("enabled") and self.device.type == "cpu":
             dtype = torch.bfloat16
+        if self.device.type == "cuda":
+            # "fp16": {"enabled": true} (both GPT-2 values files of the reference, with --fp16): IEEE fp16 storage and
+            # tensor-core operands, loss scaling below; anything else: bf16.  The choice is process-wide (ops/_lib.py).
+            from ..ops import _lib
+
+            want = "fp16" if (config.get("fp16") or {}).get("enabled") and not (config.get("bf16") or {}).get("enabled") \
+                else "bf16"
+            if os.environ.get("B2F_FP16_AS_BF16", "0") == "1":      # round-1 behaviour: keep the loss scaler, compute in bf16
+                want = "bf16"
+            _lib.set_half(want)
+            dtype = _lib.HALF
         self.dtype = dtype
         use_fused = bool(config.get("fused_collectives", True)) and self.device.type == "cuda"
 

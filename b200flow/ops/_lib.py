@@ -15,6 +15,38 @@ _LIB_DIR = Path(__file__).resolve().parent.parent / "lib"
 _cuda = None
 _host = None
 
+# The 16-bit type of activations / weights on the GPU, process-wide: bf16 (default) or IEEE fp16 (`B2F_HALF=fp16`, set by
+# the front ends when a job asks for fp16: `"fp16": {"enabled": true}`, --fp16, mixed_precision="fp16").  The two are
+# separate builds of the same kernels (b200flow/build.py), chosen when the library is first loaded.
+HALF_NAME = os.environ.get("B2F_HALF", "bf16").lower()
+assert HALF_NAME in ("bf16", "fp16"), f"B2F_HALF must be bf16 or fp16, not {HALF_NAME!r}"
+HALF = torch.float16 if HALF_NAME == "fp16" else torch.bfloat16
+_CUDA_LIB_NAME = "libb200flow_cuda_fp16.so" if HALF_NAME == "fp16" else "libb200flow_cuda.so"
+
+
+def set_half(name: str) -> bool:
+    """Select the 16-bit type before the first kernel call.  Returns False (and changes nothing) when the other build
+    is already loaded in this process - the choice is per process; callers then keep computing in the loaded type."""
+    global HALF_NAME, HALF, _CUDA_LIB_NAME
+    name = name.lower()
+    if name == HALF_NAME:
+        return True
+    if _cuda is not None:
+        import warnings
+
+        warnings.warn(f"b200flow: {name} kernels were asked for but the {HALF_NAME} build is already loaded in this "
+                      f"process; continuing in {HALF_NAME} (start the job with B2F_HALF={name})")
+        return False
+    assert name in ("bf16", "fp16")
+    HALF_NAME, HALF = name, (torch.float16 if name == "fp16" else torch.bfloat16)
+    _CUDA_LIB_NAME = "libb200flow_cuda_fp16.so" if name == "fp16" else "libb200flow_cuda.so"
+    os.environ["B2F_HALF"] = name
+    return True
+
+
+def half_dtype() -> torch.dtype:
+    return HALF
+
 
 class NativeError(RuntimeError):
     pass
@@ -27,7 +59,7 @@ def _load(name: str) -> ctypes.CDLL:
         from .. import build as _build
 
         if "cuda" in name:
-            _build.build_cuda()
+            _build.build_cuda(half="fp16" if "fp16" in name else "bf16")
         else:
             _build.build_host()
     if not path.exists():
@@ -38,7 +70,7 @@ def _load(name: str) -> ctypes.CDLL:
 def cuda_lib() -> ctypes.CDLL:
     global _cuda
     if _cuda is None:
-        _cuda = _load("libb200flow_cuda.so")
+        _cuda = _load(_CUDA_LIB_NAME)
         _cuda.b2f_last_error.restype = ctypes.c_char_p
     return _cuda
 
@@ -51,7 +83,7 @@ def host_lib() -> ctypes.CDLL:
 
 
 def loaded_libraries() -> list[str]:
-    return [str(_LIB_DIR / n) for n, l in (("libb200flow_cuda.so", _cuda), ("libb200flow_host.so", _host)) if l]
+    return [str(_LIB_DIR / n) for n, l in ((_CUDA_LIB_NAME, _cuda), ("libb200flow_host.so", _host)) if l]
 
 
 _launches = 0

@@ -47,7 +47,7 @@ def dropout_keep_mask(B: int, H: int, S: int, p: float, seed: int, device="cpu")
 def attn_fwd_raw(q, k, v, causal: bool, scale: float, kv_lens=None, dropout_p: float = 0.0, seed: int = 0):
     B, S, H, D = q.shape
     HKV = k.shape[2]
-    o = torch.empty((B, S, H, D), dtype=torch.bfloat16, device=q.device)
+    o = torch.empty((B, S, H, D), dtype=_lib.HALF, device=q.device)
     lse = torch.empty((B, H, S), dtype=torch.float32, device=q.device)
     (q_ts, q_bs), (k_ts, k_bs), (v_ts, v_bs) = _strides(q), _strides(k), _strides(v)
     args = [ptr(q), ptr(k), ptr(v), ptr(o), ptr(lse), c_int(B), c_int(S), c_int(H),
@@ -66,11 +66,11 @@ def attn_bwd_raw(q, k, v, o, do, lse, causal: bool, scale: float, kv_lens=None, 
     B, S, H, D = q.shape
     HKV = k.shape[2]
     if dq is None:
-        dq = torch.empty((B, S, H, D), dtype=torch.bfloat16, device=q.device)
+        dq = torch.empty((B, S, H, D), dtype=_lib.HALF, device=q.device)
     if dk is None:
-        dk = torch.empty((B, S, HKV, D), dtype=torch.bfloat16, device=q.device)
+        dk = torch.empty((B, S, HKV, D), dtype=_lib.HALF, device=q.device)
     if dv is None:
-        dv = torch.empty((B, S, HKV, D), dtype=torch.bfloat16, device=q.device)
+        dv = torch.empty((B, S, HKV, D), dtype=_lib.HALF, device=q.device)
     s_pad = (S + 127) // 128 * 128
     # scratch for the pre-pass: [lse * log2e | rowsum(o * do)], query rows padded to whole tiles
     delta = torch.empty((2, B, H, s_pad), dtype=torch.float32, device=q.device)

@@ -34,7 +34,7 @@ class _RoIAlign(torch.autograd.Function):
     @staticmethod
     def forward(ctx, rois, P, sampling, aligned, scales, *feats):
         R, C = rois.shape[0], feats[0].shape[-1]
-        out = torch.empty((R, P, P, C), dtype=torch.bfloat16, device=rois.device)
+        out = torch.empty((R, P, P, C), dtype=_lib.HALF, device=rois.device)
         H = [f.shape[1] for f in feats]
         W = [f.shape[2] for f in feats]
         feats = [f.contiguous() for f in feats]
@@ -54,7 +54,7 @@ class _RoIAlign(torch.autograd.Function):
         _lib.call("b2f_roi_align_bwd", _ptr_array(feats), _ptr_array(grads), _int_array(H), _int_array(W),
                   _float_array(scales), c_int(len(feats)), c_int(feats[0].shape[-1]), ptr(rois),
                   c_int(rois.shape[0]), c_int(P), c_int(sampling), c_int(int(aligned)), ptr(dout), stream_ptr())
-        return (None, None, None, None, None, *[g.to(torch.bfloat16) for g in grads])
+        return (None, None, None, None, None, *[g.to(_lib.HALF) for g in grads])
 
 
 def roi_align(feats_nhwc: list[torch.Tensor], scales: list[float], rois: torch.Tensor, P: int,

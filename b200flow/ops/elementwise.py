@@ -213,6 +213,6 @@ def scaled_masked_softmax(x, mask=None, scale: float = 1.0, causal: bool = False
 
 def cast_f32_bf16(x: torch.Tensor, out: torch.Tensor | None = None, scale: float = 1.0):
     if out is None:
-        out = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
+        out = torch.empty(x.shape, dtype=_lib.HALF, device=x.device)
     _lib.call("b2f_cast_f32_bf16", ptr(x), ptr(out), c_ll(x.numel()), c_float(scale), stream_ptr())
     return out

@@ -33,7 +33,7 @@ def _ld(t: torch.Tensor) -> int:
 
 
 def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_major: bool = False,
-         out: torch.Tensor | None = None, out_dtype: torch.dtype = torch.bfloat16,
+         out: torch.Tensor | None = None, out_dtype: torch.dtype | None = None,
          bias: torch.Tensor | None = None, residual: torch.Tensor | None = None,
          aux: torch.Tensor | None = None, gelu: bool = False, relu: bool = False,
          accumulate: bool = False, alpha: float = 1.0, dgelu: bool = False) -> torch.Tensor:
@@ -42,7 +42,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_maj
     a: [.., M, K] (or [.., K, M] if a_mn_major);  b: [.., N, K] (or [.., K, N] if b_mn_major).
     """
     _lib.require_cuda(a, b)
-    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    assert a.dtype == _lib.HALF and b.dtype == _lib.HALF
     assert a.dim() == b.dim() and a.dim() in (2, 3)
     batch = a.shape[0] if a.dim() == 3 else 1
     if a_mn_major:
@@ -54,6 +54,8 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_maj
     else:
         N, Kb = b.shape[-2], b.shape[-1]
     assert K == Kb, f"contraction mismatch {K} vs {Kb}"
+    if out_dtype is None:
+        out_dtype = _lib.HALF
     if out is None:
         shape = (batch, M, N) if a.dim() == 3 else (M, N)
         out = torch.empty(shape, dtype=out_dtype, device=a.device)
@@ -62,7 +64,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_maj
     if out.dtype == torch.float32:
         flags |= EPI_OUT_F32
     else:
-        assert out.dtype == torch.bfloat16
+        assert out.dtype == _lib.HALF
     if accumulate:
         flags |= EPI_ACCUM
     if gelu:
@@ -207,7 +209,7 @@ class _LinearGelu(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias):
         x2 = x.reshape(-1, x.shape[-1])
-        pre = torch.empty((x2.shape[0], weight.shape[0]), dtype=torch.bfloat16, device=x.device)
+        pre = torch.empty((x2.shape[0], weight.shape[0]), dtype=_lib.HALF, device=x.device)
         y = gemm(x2, weight, bias=bias, aux=pre, gelu=True)
         ctx.save_for_backward(x2, weight, pre)
         ctx.x_shape = x.shape
@@ -232,7 +234,7 @@ class _MlpGelu(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w1, b1, w2, b2):
         x2 = x.reshape(-1, x.shape[-1])
-        pre = torch.empty((x2.shape[0], w1.shape[0]), dtype=torch.bfloat16, device=x.device)
+        pre = torch.empty((x2.shape[0], w1.shape[0]), dtype=_lib.HALF, device=x.device)
         h = gemm(x2, w1, bias=b1, aux=pre, gelu=True)
         y = gemm(h, w2, bias=b2)
         ctx.save_for_backward(x2, w1, w2, pre, h)

@@ -20,7 +20,7 @@ from ._lib import c_int, c_ll, ptr, stream_ptr
 
 def quantize_rows(x: torch.Tensor):
     """x bf16 [R, K] -> (q uint8 [R, K] holding e4m3 bits, scale fp32 [R])."""
-    assert x.dim() == 2 and x.dtype == torch.bfloat16 and x.stride(1) == 1
+    assert x.dim() == 2 and x.dtype == _lib.HALF and x.stride(1) == 1
     R, K = x.shape
     q = torch.empty((R, K), dtype=torch.uint8, device=x.device)
     s = torch.empty(R, dtype=torch.float32, device=x.device)
@@ -30,10 +30,11 @@ def quantize_rows(x: torch.Tensor):
 
 
 def gemm_fp8(aq, a_scale, bq, b_scale, bias=None, residual=None, aux=None, gelu=False,
-             out_dtype=torch.bfloat16):
+             out_dtype=None):
     """(aq [M,K] x bq [N,K]^T) * a_scale[m] * b_scale[n] (+bias) (gelu) (+residual)."""
     M, K = aq.shape
     N = bq.shape[0]
+    out_dtype = out_dtype or _lib.HALF
     out = torch.empty((M, N), dtype=out_dtype, device=aq.device)
     flags = (G.EPI_GELU if gelu else 0) | (G.EPI_OUT_F32 if out_dtype == torch.float32 else 0)
     _lib.call("b2f_gemm_fp8", ptr(aq), ptr(bq), ptr(out), c_int(M), c_int(N), c_int(K), c_ll(aq.stride(0)),
@@ -51,7 +52,7 @@ class _LinearFP8(torch.autograd.Function):
             x2 = x2.contiguous()
         xq, sx = quantize_rows(x2)
         wq, sw = quantize_rows(weight)
-        pre = torch.empty((x2.shape[0], weight.shape[0]), dtype=torch.bfloat16, device=x.device) if gelu else None
+        pre = torch.empty((x2.shape[0], weight.shape[0]), dtype=_lib.HALF, device=x.device) if gelu else None
         y = gemm_fp8(xq, sx, wq, sw, bias=bias, aux=pre, gelu=gelu)
         ctx.save_for_backward(x2, weight, pre if gelu else x2.new_empty(0))
         ctx.gelu, ctx.has_bias, ctx.shape = gelu, bias is not None, x.shape

@@ -46,7 +46,7 @@ class MxTensor:
 def quantize_mx(x: torch.Tensor) -> MxTensor:
     """bf16 [R, K] or [B, R, K] (K a multiple of 128, rows contiguous) -> MxTensor."""
     _lib.require_cuda(x)
-    assert x.dtype == torch.bfloat16 and x.dim() in (2, 3) and x.stride(-1) == 1
+    assert x.dtype == _lib.HALF and x.dim() in (2, 3) and x.stride(-1) == 1
     batch = x.shape[0] if x.dim() == 3 else 1
     R, K = x.shape[-2], x.shape[-1]
     assert K % 128 == 0, "MX quantisation needs K % 128 == 0"
@@ -59,7 +59,7 @@ def quantize_mx(x: torch.Tensor) -> MxTensor:
 
 
 def dequantize_mx(t: MxTensor) -> torch.Tensor:
-    y = torch.empty(t.q.shape, dtype=torch.bfloat16, device=t.q.device)
+    y = torch.empty(t.q.shape, dtype=_lib.HALF, device=t.q.device)
     R, K = t.rows, t.k
     _lib.call("b2f_dequantize_mx", ptr(t.q), ptr(t.sf), ptr(y), c_int(R), c_int(K), c_ll(K), c_int(t.batch),
               c_ll(R * K), stream_ptr())
@@ -67,11 +67,12 @@ def dequantize_mx(t: MxTensor) -> torch.Tensor:
 
 
 def gemm_mx(a: MxTensor, b: MxTensor, bias=None, residual=None, aux=None, gelu: bool = False,
-            out_dtype=torch.bfloat16) -> torch.Tensor:
+            out_dtype=None) -> torch.Tensor:
     """C = dequant(a) @ dequant(b)^T (+bias) (gelu; `aux` receives the pre-activation) (+residual)."""
     assert a.k == b.k and a.batch == b.batch
     M, N, K, batch = a.rows, b.rows, a.k, a.batch
     shape = (batch, M, N) if a.q.dim() == 3 else (M, N)
+    out_dtype = out_dtype or _lib.HALF
     out = torch.empty(shape, dtype=out_dtype, device=a.q.device)
     flags = (G.EPI_GELU if gelu else 0) | (G.EPI_OUT_F32 if out_dtype == torch.float32 else 0)
     _lib.call("b2f_gemm_mx", ptr(a.q), ptr(a.sf), ptr(b.q), ptr(b.sf), ptr(out), c_int(M), c_int(N), c_int(K),

@@ -14,12 +14,12 @@ def adamw_flat_(master: torch.Tensor, m: torch.Tensor, v: torch.Tensor, grad: to
     """One AdamW step over a flat fp32 master buffer; writes the bf16 working copy too."""
     _lib.require_cuda(master, grad)
     assert master.dtype == torch.float32 and m.dtype == torch.float32 and v.dtype == torch.float32
-    assert grad.dtype in (torch.bfloat16, torch.float32) and grad.numel() == master.numel()
+    assert grad.dtype in (_lib.HALF, torch.float32) and grad.numel() == master.numel()
     assert master.is_contiguous() and grad.is_contiguous()
     if param_out is not None:
-        assert param_out.dtype == torch.bfloat16 and param_out.numel() == master.numel()
+        assert param_out.dtype == _lib.HALF and param_out.numel() == master.numel()
     _lib.call("b2f_adamw_flat", ptr(master), ptr(m), ptr(v), ptr(grad),
-              c_int(int(grad.dtype == torch.bfloat16)), ptr(param_out), c_ll(master.numel()),
+              c_int(int(grad.dtype == _lib.HALF)), ptr(param_out), c_ll(master.numel()),
               c_float(lr), c_float(beta1), c_float(beta2), c_float(eps), c_float(weight_decay),
               c_int(step), ptr(grad_scale), ptr(skip), stream_ptr())
 
@@ -43,7 +43,7 @@ class MultiTensorTable:
             first += (n + chunk - 1) // chunk
         self.total_chunks = first
         self.nsegs = len(rows)
-        self.grad_bf16 = grads[0].dtype == torch.bfloat16
+        self.grad_bf16 = grads[0].dtype == _lib.HALF
         self.table = torch.tensor(rows, dtype=torch.int64, device=masters[0].device)
         self._keep = (masters, ms, vs, grads, params_out)
 
@@ -59,7 +59,7 @@ def sumsq(x: torch.Tensor, out: torch.Tensor | None = None, overflow: torch.Tens
           accumulate: bool = False, scratch: torch.Tensor | None = None) -> torch.Tensor:
     """out[0] (+)= sum(x^2) in fp32 (deterministic two-stage reduction)."""
     _lib.require_cuda(x)
-    assert x.is_contiguous() and x.dtype in (torch.bfloat16, torch.float32)
+    assert x.is_contiguous() and x.dtype in (_lib.HALF, torch.float32)
     n = x.numel()
     nparts = _lib.call_int("b2f_sumsq_num_partials", c_ll(n))
     if scratch is None:
@@ -82,6 +82,6 @@ def clip_coef(sumsq_t: torch.Tensor, max_norm: float, extra_scale: float = 1.0):
 
 
 def scale_(x: torch.Tensor, scale: float = 1.0, scale_ptr: torch.Tensor | None = None) -> None:
-    assert x.is_contiguous() and x.dtype in (torch.bfloat16, torch.float32)
+    assert x.is_contiguous() and x.dtype in (_lib.HALF, torch.float32)
     _lib.call("b2f_scale", ptr(x), c_ll(x.numel()), c_int(int(x.dtype == torch.float32)),
               ptr(scale_ptr), c_float(scale), stream_ptr())

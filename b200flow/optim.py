@@ -12,6 +12,7 @@ import math
 
 import torch
 
+from .ops import _lib
 from .ops import optim as O
 from .ops import ref
 
@@ -49,7 +50,7 @@ class AdamW(torch.optim.Optimizer):
                 tab = self._tables.get(key)
                 if tab is None:
                     sts = [self._init_state(p) for p in ps]
-                    outs = [p.data if p.dtype == torch.bfloat16 else None for p in ps]
+                    outs = [p.data if p.dtype == _lib.HALF else None for p in ps]
                     tab = O.MultiTensorTable([s["master"] for s in sts], [s["exp_avg"] for s in sts],
                                              [s["exp_avg_sq"] for s in sts],
                                              [self._grad(p).contiguous() for p in ps], outs)
@@ -58,7 +59,7 @@ class AdamW(torch.optim.Optimizer):
                                weight_decay=group["weight_decay"], step=self._step,
                                grad_scale=self.grad_scale, skip=self.skip)
                 for p in ps:
-                    if p.dtype != torch.bfloat16:   # fp32 params: master is the truth
+                    if p.dtype != _lib.HALF:   # fp32 params: master is the truth
                         p.data.copy_(self.state[p]["master"])
             else:
                 for p in ps:
@@ -149,9 +150,9 @@ class FlatMomentumSGD:
         lr = self.param_groups[0]["lr"]
         f = self.flat
         if f.params.is_cuda:
-            out = f.params if f.params.dtype == torch.bfloat16 else None
+            out = f.params if f.params.dtype == _lib.HALF else None
             _lib.call("b2f_sgd_momentum_flat", ptr(self.master), ptr(self.buf), ptr(f.grads),
-                      c_int(int(f.grads.dtype == torch.bfloat16)), ptr(out), c_ll(f.numel), c_float(lr),
+                      c_int(int(f.grads.dtype == _lib.HALF)), ptr(out), c_ll(f.numel), c_float(lr),
                       c_float(self.momentum), c_float(self.weight_decay), ptr(self.grad_scale), stream_ptr())
             if out is None:
                 f.params.copy_(self.master)

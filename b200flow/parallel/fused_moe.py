@@ -106,7 +106,7 @@ class FusedMoE:
         rows = self._alloc("rows", E * C * Hout * 2, dev)[par]
         done = self._alloc("done", 256, dev)
         done[1 - par].view(torch.int32, 1).zero_()        # next call's counter; see the module docstring
-        keep = torch.empty((El, R, F), dtype=torch.bfloat16, device=dev)
+        keep = torch.empty((El, R, F), dtype=_lib.HALF, device=dev)
         hq = torch.empty((El, R, F), dtype=torch.uint8, device=dev)
         hsf = torch.empty(El * MX.sf_bytes(R, F), dtype=torch.uint8, device=dev)
         _lib.call("b2f_moe_up", ptr(x), ptr(token_of), ptr(counts), c_int(T), c_int(H), c_int(E), c_int(C),
@@ -123,7 +123,7 @@ class FusedMoE:
         for buf, n in ((xhat, H), (keep, F)):
             _lib.call("b2f_moe_zero_inactive", ptr(buf), ptr(my_cnt), c_int(El), c_int(W), c_int(C), c_int(n), stream_ptr())
         _lib.call("b2f_moe_wait_rows", ptr(done[par].view(torch.int32, 1)), ptr(counts), c_int(E), c_int(Hout), stream_ptr())
-        return rows.view(torch.bfloat16, E * C * Hout).view(E * C, Hout), keep, xhat
+        return rows.view(_lib.HALF, E * C * Hout).view(E * C, Hout), keep, xhat
 
 
 def token_map(expert, slot, E, C):

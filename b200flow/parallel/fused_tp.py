@@ -57,9 +57,9 @@ class FusedTP:
         n = w.shape[1] if b_mn_major else w.shape[0]
         self.ag_calls += 1
         slot = self._slots(self._x_slots, ts * k * 2)[self.ag_calls & 1]
-        slot.view(torch.bfloat16, ts * k).copy_(x_shard.reshape(-1))
-        xg = torch.empty((t, k), dtype=torch.bfloat16, device=x_shard.device)
-        y = torch.empty((t, n), dtype=torch.bfloat16, device=x_shard.device)
+        slot.view(_lib.HALF, ts * k).copy_(x_shard.reshape(-1))
+        xg = torch.empty((t, k), dtype=_lib.HALF, device=x_shard.device)
+        y = torch.empty((t, n), dtype=_lib.HALF, device=x_shard.device)
         assert t // 128 <= self.tile_flags.numel()
         _lib.call("b2f_ag_gemm_bf16", slot.ptr_array, ptr(xg), ptr(w), ptr(y), c_int(t), c_int(n),
                   c_int(k), c_ll(w.stride(0)), c_ll(y.stride(0)), c_int(int(b_mn_major)), ptr(bias),
@@ -79,7 +79,7 @@ class FusedTP:
         recv = self._slots(self._recv_slots, comm.world * ts * n * 2)[par]
         flags = self.rs_flags[par]
         assert comm.world * (ts // 128) * ((n + 255) // 256) <= self.FLAG_WORDS
-        y = torch.empty((ts, n), dtype=torch.bfloat16, device=x.device)
+        y = torch.empty((ts, n), dtype=_lib.HALF, device=x.device)
         _lib.call("b2f_gemm_rs_bf16", ptr(x), ptr(w), ptr(y), c_int(t), c_int(n), c_int(k),
                   c_ll(x.stride(0)), c_ll(w.stride(0)), c_ll(y.stride(0)), c_int(int(b_mn_major)),
                   ptr(bias), ptr(residual), c_ll(residual.stride(0) if residual is not None else 0),
@@ -113,7 +113,7 @@ class FusedTP:
                   ptr(bias), ptr(res), c_ll(res.stride(0) if res is not None else 0),
                   recv.ptr_array, flags.ptr_array, self.ar_done.ptr_array, ptr(self.ar_counter),
                   c_int(comm.rank), c_int(comm.world), ctypes.c_uint(self.rs_calls), stream_ptr())
-        return out.view(torch.bfloat16, t * n).view(t, n).clone()
+        return out.view(_lib.HALF, t * n).view(t, n).clone()
 
     def vocab_ce_exchange(self, logits: torch.Tensor, targets: torch.Tensor, lo: int) -> torch.Tensor:
         """K9 statistics pass with the exchange done by the kernel's stores: every rank writes its

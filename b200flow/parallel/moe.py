@@ -242,7 +242,7 @@ def _dispatch_fwd(x, expert, slot, E, capacity, ep: EPContext, fused):
     if fused and x.is_cuda:
         ep.calls += 1
         recv = ep.symmetric("in", ep.world * El * capacity * H * 2)[ep.calls & 1]
-        view = recv.view(torch.bfloat16, ep.world * El * capacity * H)
+        view = recv.view(_lib.HALF, ep.world * El * capacity * H)
         view.zero_()
         ep.barrier()                      # everyone's buffer is cleared before anyone stores into it
         _lib.call("b2f_moe_dispatch", ptr(x), ptr(expert), ptr(slot), c_int(T), c_int(H), c_int(capacity),
@@ -267,7 +267,7 @@ def _combine_fwd(out, expert, slot, gate, E, capacity, ep: EPContext, fused, ret
     if fused and out.is_cuda:
         ep.calls += 1
         sym = ep.symmetric("out", back.numel() * 2)[ep.calls & 1]
-        sym.view(torch.bfloat16, back.numel()).copy_(back.reshape(-1))
+        sym.view(_lib.HALF, back.numel()).copy_(back.reshape(-1))
         ep.barrier()                      # all owners published their expert outputs
         y = torch.empty((T, H), dtype=out.dtype, device=out.device)
         _lib.call("b2f_moe_combine", ptr(None), sym.ptr_array, c_int(ep.world), c_int(El), c_int(ep.rank),
@@ -387,8 +387,8 @@ class _GateLogits(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dl):
         x, wg = ctx.saved_tensors
-        d = torch.zeros((x.shape[0], wg.shape[0]), dtype=torch.bfloat16, device=x.device)
-        d[:, :ctx.E] = dl.to(torch.bfloat16)
+        d = torch.zeros((x.shape[0], wg.shape[0]), dtype=_lib.HALF, device=x.device)
+        d[:, :ctx.E] = dl.to(_lib.HALF)
         dx = G.gemm(d, wg, b_mn_major=True)
         dw = G._wgrad(x, d, wg)
         return dx, dw, None

@@ -28,6 +28,7 @@ import torch.distributed as dist
 import torch.nn.functional as F
 
 from ..ops import elementwise as E
+from ..ops import _lib
 from ..ops import gemm as G
 
 
@@ -165,7 +166,7 @@ class _VocabParallelCE(torch.autograd.Function):
     def forward(ctx, logits, targets, tp, ignore_index):
         T, Vl = logits.shape
         lo = tp.rank * Vl
-        if logits.is_cuda and logits.dtype == torch.bfloat16 and Vl % 8 == 0 and logits.stride(1) == 1 \
+        if logits.is_cuda and logits.dtype == _lib.HALF and Vl % 8 == 0 and logits.stride(1) == 1 \
                 and logits.stride(0) % 8 == 0:
             return _VocabParallelCE._forward_native(ctx, logits, targets.reshape(-1).to(torch.int64).contiguous(),
                                                     tp, ignore_index, lo)

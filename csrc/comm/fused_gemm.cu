@@ -323,12 +323,13 @@ struct RSPolicy {
   uint8_t* staging;
   __nv_bfloat16* out;   // local output shard [Ts, N] and its row pitch (elements)
   long long ldo;
+  int pitch;            // bytes between staged rows (the CTA-pair kernel trades the bank-spreading pad for a ring stage)
   // the flag of a shipped tile is published one tile later (its bulk copies have long landed by
   // then), so the epilogue never sits out an NVLink round trip
   mutable int pend_owner = -1, pend_mb_local = 0, pend_nb = 0;
   mutable uint32_t rx_phase = 0;
   __device__ __forceinline__ uint64_t* rx_bar() const {
-    return reinterpret_cast<uint64_t*>(staging + BM * RS_PITCH);
+    return reinterpret_cast<uint64_t*>(staging + BM * pitch);
   }
   // kernel prologue (one thread, before the CTA-wide sync): barrier for the partial-row prefetch
   __device__ __forceinline__ void init_smem() const { mbar_init(rx_bar(), 128); fence_mbar_init(); }
@@ -413,7 +414,7 @@ struct RSPolicy {
                                  ((size_t)(a.rank ^ 1) * a.rows_per_rank + (size_t)mb_local * BM + row_in_tile) * a.N + n0;
       asm volatile("fence.proxy.async;" ::: "memory");
       mbar_arrive_expect_tx(rx_bar(), (uint32_t)cols * 2);
-      bulk_load_1d(staging + (size_t)row_in_tile * RS_PITCH, src, (uint32_t)cols * 2, rx_bar());
+      bulk_load_1d(staging + (size_t)row_in_tile * pitch, src, (uint32_t)cols * 2, rx_bar());
       mbar_wait(rx_bar(), rx_phase);
       rx_phase ^= 1;
     }
@@ -425,7 +426,7 @@ struct RSPolicy {
     if (m >= p.M || n0 >= p.N) return;
     if (owner != a.rank) {
       // partial tile -> bf16 row in the staging buffer; tile_done ships the rows
-      uint8_t* dst = staging + (size_t)(m - mb * BM) * RS_PITCH + (size_t)(n0 - nb * BN) * 2;
+      uint8_t* dst = staging + (size_t)(m - mb * BM) * pitch + (size_t)(n0 - nb * BN) * 2;
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         uint4 u;
@@ -445,7 +446,7 @@ struct RSPolicy {
       if (s == a.rank || a.dbg) continue;
       const __nv_bfloat16* src = static_cast<const __nv_bfloat16*>(a.recv.ptr[a.rank]) +
                                  ((size_t)s * a.rows_per_rank + row_local) * a.N + n0;
-      const uint8_t* staged = staging + (size_t)(m - mb * BM) * RS_PITCH + (size_t)(n0 - nb * BN) * 2;
+      const uint8_t* staged = staging + (size_t)(m - mb * BM) * pitch + (size_t)(n0 - nb * BN) * 2;
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         const uint4 u = a.world == 2 ? *reinterpret_cast<const uint4*>(staged + q * 16) : ld_cv_v4(src + q * 8);
@@ -468,7 +469,7 @@ struct RSPolicy {
     q.M = a.rows_per_rank;
     float v[32];
     epilogue_values(q, b, row_local, n0, sum, v);
-    uint8_t* dst = staging + (size_t)(m - mb * BM) * RS_PITCH + (size_t)(n0 - nb * BN) * 2;
+    uint8_t* dst = staging + (size_t)(m - mb * BM) * pitch + (size_t)(n0 - nb * BN) * 2;
 #pragma unroll
     for (int qq = 0; qq < 4; ++qq) {
       uint4 u;
@@ -486,13 +487,13 @@ struct RSPolicy {
       const int n0 = nb * BN;
       const int cols = a.N - n0 < BN ? a.N - n0 : BN;
       asm volatile("fence.proxy.async;" ::: "memory");
-      bulk_store_1d(out + (size_t)row_local * ldo + n0, staging + (size_t)row_in_tile * RS_PITCH, (uint32_t)cols * 2);
+      bulk_store_1d(out + (size_t)row_local * ldo + n0, staging + (size_t)row_in_tile * pitch, (uint32_t)cols * 2);
       if (a.allreduce) {   // K4': the same finished row into every peer's full output
         const size_t row_global = (size_t)mb * BM + row_in_tile;
         for (int s = 0; s < a.world; ++s)
           if (s != a.rank)
             bulk_store_1d(static_cast<__nv_bfloat16*>(a.bcast.ptr[s]) + row_global * a.ld_bcast + n0,
-                          staging + (size_t)row_in_tile * RS_PITCH, (uint32_t)cols * 2);
+                          staging + (size_t)row_in_tile * pitch, (uint32_t)cols * 2);
       }
       tma_store_commit();
       return;
@@ -508,7 +509,7 @@ struct RSPolicy {
     flush();
     if (a.dbg == 1) return;
     asm volatile("fence.proxy.async;" ::: "memory");  // generic-proxy staging writes -> bulk copy reads
-    bulk_store_1d(dst, staging + (size_t)row_in_tile * RS_PITCH, (uint32_t)cols * 2);
+    bulk_store_1d(dst, staging + (size_t)row_in_tile * pitch, (uint32_t)cols * 2);
     tma_store_commit();
     pend_owner = owner;
     pend_mb_local = mb - owner * blocks_per_rank;
@@ -526,14 +527,20 @@ b2f_gemm_rs_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_const
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
   RSPolicy pol{a, a.rows_per_rank / BM, (p.N + BN - 1) / BN, smem + RS_STAGES * STAGE_BYTES + 1024,
-               reinterpret_cast<__nv_bfloat16*>(p.C), p.ldc};
+               reinterpret_cast<__nv_bfloat16*>(p.C), p.ldc, RS_PITCH};
   if (threadIdx.x == 0) pol.init_smem();
   gemm_body<RSPolicy, 0, RS_STAGES>(&tma_a, &tma_b, p, pol, blockIdx.x, gridDim.x, smem_raw);
 }
 
 // ---- K4 on the CTA-pair core: same protocol, each CTA of a pair handles its own 128-row block.
-constexpr int RS2_STAGES = 4;
-constexpr int RS2_SMEM_BYTES = gemm2::smem2_bytes(RS2_STAGES, BM * RS_PITCH + 16);
+// Five ring stages (the plain kernel has six; with four the main loop ran ~10 % slower in single-GPU loopback,
+// profiles/r2_call6_k3_k4_loopback.txt) fit next to the 128-row staging block once its rows are packed at 512 B: the
+// one-row-per-thread 16 B staging writes then collide on the banks, ~2 us per tile inside an epilogue that overlaps a
+// 15+ us main loop.
+constexpr int RS2_STAGES = 5;
+constexpr int RS2_PITCH = BN * 2;
+constexpr int RS2_SMEM_BYTES = gemm2::smem2_bytes(RS2_STAGES, BM * RS2_PITCH + 16);
+static_assert(RS2_SMEM_BYTES <= 227 * 1024, "K4 CTA-pair kernel: shared memory budget");
 
 struct RS2Policy {
   RSPolicy in;   // 128-row-block logic is identical; only the tile order differs
@@ -572,7 +579,8 @@ b2f_gemm_rs2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
   RS2Policy pol{RSPolicy{a, a.rows_per_rank / BM, (p.N + BN - 1) / BN,
-                         smem + RS2_STAGES * gemm2::ST2_BYTES + 1024, reinterpret_cast<__nv_bfloat16*>(p.C), p.ldc}};
+                         smem + RS2_STAGES * gemm2::ST2_BYTES + 1024, reinterpret_cast<__nv_bfloat16*>(p.C), p.ldc,
+                         RS2_PITCH}};
   if (threadIdx.x == 0) pol.in.init_smem();
   gemm2::gemm2_body<RS2Policy, RS2_STAGES>(&tma_a, &tma_b, p, pol, blockIdx.x >> 1, gridDim.x >> 1, smem_raw);
 }
@@ -699,7 +707,9 @@ static int gemm_rs_launch(const void* X, const void* B, void* Y_shard, int T, in
   if (int rc = fill(&a.flags, flag_ptrs, world)) return rc;
   a.rank = rank; a.world = world; a.rows_per_rank = T / world; a.N = N; a.epoch = epoch;
   if (const char* e = getenv("B2F_RS_DEBUG")) a.dbg = atoi(e);
-  static const int interleave = [] { const char* e = getenv("B2F_RS_INTERLEAVE"); return e ? atoi(e) : 1; }();
+  // measured at the Llama TP2 shapes (profiles/r2_call7_*): the interleaved order is 0-7 % slower than "peers first",
+  // so it stays an experiment switch
+  static const int interleave = [] { const char* e = getenv("B2F_RS_INTERLEAVE"); return e ? atoi(e) : 0; }();
   a.interleave = interleave;
   if (ar) {
     a.allreduce = 1;

@@ -6,6 +6,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -412,6 +413,31 @@ __device__ __forceinline__ void st_v4(void* p, const uint4& v) {
                : "memory");
 }
 
+// ---- the 16-bit storage type of activations / weights -----------------------------------------------------------
+// The library is built twice from these sources: as is (bf16) and with -DB2F_HALF_FP16 (IEEE fp16, what
+// `"fp16": {"enabled": true}` / --fp16 of the reference's GPT-2 examples ask for: tcgen05 kind::f16 takes either).
+// Every conversion goes through the four helpers below and every kind::f16 instruction descriptor takes its operand
+// format from B2F_MMA_FMT, so the kernels are otherwise identical; pointer types keep their bf16 names (16-bit
+// storage either way).
+#ifdef B2F_HALF_FP16
+#define B2F_MMA_FMT 0u             // kind::f16 operand format: f16
+#define B2F_HALF_PTX "f16x2"
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __half2 v = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ float2 unpack_bf16x2(uint32_t u) {
+  __half2 v = *reinterpret_cast<__half2*>(&u);
+  return __half22float2(v);
+}
+__device__ __forceinline__ float h2f(__nv_bfloat16 v) { return __half2float(*reinterpret_cast<const __half*>(&v)); }
+__device__ __forceinline__ __nv_bfloat16 f2h(float f) {
+  __half h = __float2half_rn(f);
+  return *reinterpret_cast<__nv_bfloat16*>(&h);
+}
+#else
+#define B2F_MMA_FMT 1u             // kind::f16 operand format: bf16
+#define B2F_HALF_PTX "bf16x2"
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
@@ -420,5 +446,8 @@ __device__ __forceinline__ float2 unpack_bf16x2(uint32_t u) {
   __nv_bfloat162 v = *reinterpret_cast<__nv_bfloat162*>(&u);
   return __bfloat1622float2(v);
 }
+__device__ __forceinline__ float h2f(__nv_bfloat16 v) { return __bfloat162float(v); }
+__device__ __forceinline__ __nv_bfloat16 f2h(float f) { return __float2bfloat16(f); }
+#endif
 
 }  // namespace b2f

@@ -239,8 +239,8 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
     } else if (warp == 1) {
       // all 32 lanes walk the loop (uniform control flow keeps the issue sequence in uniform
       // registers); one elected lane issues the MMAs and commits
-      const uint32_t idesc_s = make_idesc(1, 1, 128, 128, 0, 0);
-      const uint32_t idesc_pv = make_idesc(1, 1, 128, D, 0, 1);
+      const uint32_t idesc_s = make_idesc(B2F_MMA_FMT, B2F_MMA_FMT, 128, 128, 0, 0);
+      const uint32_t idesc_pv = make_idesc(B2F_MMA_FMT, B2F_MMA_FMT, 128, D, 0, 1);
       // S_w(j) = Q_w K_j^T ; the last reader of K_j releases its stage.
       auto issue_s = [&](int w, int j) {
         const int st = j & 1;
@@ -608,8 +608,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant
         load_tile<D>(sV + st * TILE_B, &mv, &bars->st_full[st], j * TQ, hkv, b);
       }
     } else if (warp == 1) {
-      const uint32_t idesc_s = make_idesc(1, 1, 128, 64, 0, 0);
-      const uint32_t idesc_dq = make_idesc(1, 1, 128, D, 0, 1);
+      const uint32_t idesc_s = make_idesc(B2F_MMA_FMT, B2F_MMA_FMT, 128, 64, 0, 0);
+      const uint32_t idesc_dq = make_idesc(B2F_MMA_FMT, B2F_MMA_FMT, 128, D, 0, 1);
       const uint32_t aQ = lo_k(smem_u32(sQ)), adO = lo_k(smem_u32(sdO));
       // S_h = Q K_h^T and dP_h = dO V_h^T for key half hh (64 keys = rows [64 half, +64) of the stage)
       auto issue_sdp = [&](int hh) {
@@ -809,8 +809,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constan
         bulk_load_1d(bars->dlt[st], stats + (long long)p.B * p.H * S_pad, TQ * 4, &bars->st_full[st]);
       }
     } else if (warp == 1) {
-      const uint32_t idesc_s = make_idesc(1, 1, 128, 64, 0, 0);
-      const uint32_t idesc_acc = make_idesc(1, 1, 128, D, 0, 1);
+      const uint32_t idesc_s = make_idesc(B2F_MMA_FMT, B2F_MMA_FMT, 128, 64, 0, 0);
+      const uint32_t idesc_acc = make_idesc(B2F_MMA_FMT, B2F_MMA_FMT, 128, D, 0, 1);
       const uint32_t aK = lo_k(smem_u32(sK)), aV = lo_k(smem_u32(sV));
       // S^T_h = K Q_h^T and dP^T_h = V dO_h^T for query half hh (rows [64 half, +64) of the stage)
       auto issue_sdp = [&](int hh) {

@@ -251,7 +251,7 @@ cross_entropy_kernel(const __nv_bfloat16* __restrict__ logits, const long long* 
     mx = nm;
   }
   for (int c = (vv << 3) + threadIdx.x; c < V; c += blockDim.x) {  // tail when V % 8 != 0
-    const float f = __bfloat162float(lr[c]);
+    const float f = h2f(lr[c]);
     const float nm = fmaxf(mx, f);
     sm = sm * __expf(mx - nm) + __expf(f - nm);
     mx = nm;
@@ -277,7 +277,7 @@ cross_entropy_kernel(const __nv_bfloat16* __restrict__ logits, const long long* 
   const bool ignored = (tgt == ignore_index) || tgt < 0 || tgt >= V;
   const float lse = gm + __logf(gs);
   if (threadIdx.x == 0)
-    loss[row] = ignored ? 0.f : lse - __bfloat162float(lr[tgt]);
+    loss[row] = ignored ? 0.f : lse - h2f(lr[tgt]);
   if (!dlogits) return;
   __nv_bfloat16* dr = dlogits + row * ld;
   const float inv = 1.f / gs;
@@ -294,9 +294,9 @@ cross_entropy_kernel(const __nv_bfloat16* __restrict__ logits, const long long* 
     reinterpret_cast<uint4*>(dr)[c] = pack8(f);
   }
   for (int c = (vv << 3) + threadIdx.x; c < V; c += blockDim.x) {
-    float pj = __expf(__bfloat162float(lr[c]) - gm) * inv;
+    float pj = __expf(h2f(lr[c]) - gm) * inv;
     if ((long long)c == tgt) pj -= 1.f;
-    dr[c] = __float2bfloat16(pj * scale);
+    dr[c] = f2h(pj * scale);
   }
 }
 
@@ -352,7 +352,7 @@ vocab_ce_stats_kernel(const __nv_bfloat16* __restrict__ logits, const long long*
       gm = nm;
     }
     const long long tgt = targets[row] - lo;
-    const float tl = (tgt >= 0 && tgt < Vl) ? __bfloat162float(lr[tgt]) : 0.f;
+    const float tl = (tgt >= 0 && tgt < Vl) ? h2f(lr[tgt]) : 0.f;
     for (int r = 0; r < world; ++r) {
       if (!out.ptr[r]) continue;
       float* dst = out.ptr[r] + ((long long)rank * T + row) * 3;
@@ -414,7 +414,7 @@ scaled_masked_softmax_kernel(const __nv_bfloat16* __restrict__ x, const uint8_t*
   float mx = -INFINITY;
   for (int c = threadIdx.x; c < sk; c += blockDim.x) {
     const bool dead = c >= limit || (mr && mr[c]);
-    if (!dead) mx = fmaxf(mx, __bfloat162float(xr[c]) * scale);
+    if (!dead) mx = fmaxf(mx, h2f(xr[c]) * scale);
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
@@ -426,7 +426,7 @@ scaled_masked_softmax_kernel(const __nv_bfloat16* __restrict__ x, const uint8_t*
   float sm = 0.f;
   for (int c = threadIdx.x; c < sk; c += blockDim.x) {
     const bool dead = c >= limit || (mr && mr[c]);
-    if (!dead) sm += __expf(__bfloat162float(xr[c]) * scale - mx);
+    if (!dead) sm += __expf(h2f(xr[c]) * scale - mx);
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) sm += __shfl_xor_sync(0xffffffffu, sm, o);
@@ -438,7 +438,7 @@ scaled_masked_softmax_kernel(const __nv_bfloat16* __restrict__ x, const uint8_t*
   for (int c = threadIdx.x; c < sk; c += blockDim.x) {
     const bool dead = c >= limit || (mr && mr[c]);
     y[row * sk + c] =
-        __float2bfloat16(dead ? 0.f : __expf(__bfloat162float(xr[c]) * scale - mx) * inv);
+        f2h(dead ? 0.f : __expf(h2f(xr[c]) * scale - mx) * inv);
   }
 }
 
@@ -455,7 +455,7 @@ cast_f32_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y,
     reinterpret_cast<uint4*>(y)[i] = pack8(f);
   }
   const long long t = (nv << 3) + (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t < n) y[t] = __float2bfloat16(x[t] * scale);
+  if (t < n) y[t] = f2h(x[t] * scale);
 }
 
 }  // namespace

@@ -195,7 +195,7 @@ __device__ __forceinline__ void gemm2_body(const CUtensorMap* tma_a_p, const CUt
       // ------------------------------------------- MMA issuer (leader CTA only).  The whole warp
       // walks the loop (uniform control flow, operands stay in uniform registers) and one elected
       // lane issues; descriptors are a precomputed low word plus a constant per K step.
-      const uint32_t idesc = make_idesc(1, 1, T2_BM, T2_BN, p.a_mn_major, p.b_mn_major);
+      const uint32_t idesc = make_idesc(B2F_MMA_FMT, B2F_MMA_FMT, T2_BM, T2_BN, p.a_mn_major, p.b_mn_major);
       const uint32_t a_kstep = p.a_mn_major ? 2048u : 32u;
       const uint32_t b_kstep = p.b_mn_major ? 2048u : 32u;
       const uint32_t a_lbo = p.a_mn_major ? (uint32_t)CHUNK_BYTES : 16u;

@@ -134,7 +134,7 @@ __device__ __forceinline__ void epilogue_values(const Params& p, int b, int m, i
   }
   if (p.bias) {
     if (flags & EPI_BIAS_ROW) {
-      float bv = __bfloat162float(p.bias[m]);
+      float bv = h2f(p.bias[m]);
 #pragma unroll
       for (int i = 0; i < 32; ++i) v[i] += bv;
     } else if (full) {
@@ -149,7 +149,7 @@ __device__ __forceinline__ void epilogue_values(const Params& p, int b, int m, i
       }
     } else {
       for (int i = 0; i < 32; ++i)
-        if (n0 + i < p.N) v[i] += __bfloat162float(p.bias[n0 + i]);
+        if (n0 + i < p.N) v[i] += h2f(p.bias[n0 + i]);
     }
   }
   if (p.aux) {
@@ -164,7 +164,7 @@ __device__ __forceinline__ void epilogue_values(const Params& p, int b, int m, i
       }
     } else {
       for (int i = 0; i < 32; ++i)
-        if (n0 + i < p.N) ap[i] = __float2bfloat16(v[i]);
+        if (n0 + i < p.N) ap[i] = f2h(v[i]);
     }
   }
   if (flags & EPI_GELU) {
@@ -189,7 +189,7 @@ __device__ __forceinline__ void epilogue_values(const Params& p, int b, int m, i
         r[q * 8 + 4] = f2.x; r[q * 8 + 5] = f2.y; r[q * 8 + 6] = f3.x; r[q * 8 + 7] = f3.y;
       }
     } else {
-      for (int i = 0; i < 32; ++i) r[i] = (n0 + i < p.N) ? __bfloat162float(rp[i]) : 0.f;
+      for (int i = 0; i < 32; ++i) r[i] = (n0 + i < p.N) ? h2f(rp[i]) : 0.f;
     }
     if (flags & EPI_DGELU) {
 #pragma unroll
@@ -234,7 +234,7 @@ __device__ __forceinline__ void epilogue_store(const Params& p, int b, int m, in
       }
     } else {
       for (int i = 0; i < 32; ++i)
-        if (n0 + i < p.N) cp[i] = __float2bfloat16(v[i]);
+        if (n0 + i < p.N) cp[i] = f2h(v[i]);
     }
   }
 }
@@ -337,7 +337,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap* tma_a, const CUtens
       // ------------------------------------------------------------ MMA issuer: the whole warp
       // walks the loop, one elected lane issues (keeps descriptors in uniform registers)
       const uint32_t idesc = KIND == 1 ? make_idesc(0, 0, BM, BN, 0, 0)
-                                       : make_idesc(1, 1, BM, BN, p.a_mn_major, p.b_mn_major);
+                                       : make_idesc(B2F_MMA_FMT, B2F_MMA_FMT, BM, BN, p.a_mn_major, p.b_mn_major);
       // K-major: +32 B per UMMA_K inside the swizzle atom; MN-major: +16 rows * 128 B.
       const uint32_t a_kstep = p.a_mn_major ? 2048u : 32u;
       const uint32_t b_kstep = p.b_mn_major ? 2048u : 32u;

@@ -74,12 +74,12 @@ adamw_flat_kernel(float* __restrict__ master, float* __restrict__ m, float* __re
   const long long base = nv << 2;
   const long long t = base + (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (t < n) {
-    float g = GRAD_BF16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(grad)[t])
+    float g = GRAD_BF16 ? h2f(reinterpret_cast<const __nv_bfloat16*>(grad)[t])
                         : reinterpret_cast<const float*>(grad)[t];
     float p = master[t], mm = m[t], vv = v[t];
     adam_update(p, mm, vv, g * gs, h);
     master[t] = p; m[t] = mm; v[t] = vv;
-    if (param_out) param_out[t] = __float2bfloat16(p);
+    if (param_out) param_out[t] = f2h(p);
   }
 }
 
@@ -115,12 +115,12 @@ adamw_multi_kernel(const Segment* __restrict__ segs, int nsegs, AdamHyper h,
   float* v = static_cast<float*>(s.v);
   __nv_bfloat16* po = static_cast<__nv_bfloat16*>(s.param_out);
   for (long long i = start + threadIdx.x; i < end; i += blockDim.x) {
-    float g = GRAD_BF16 ? __bfloat162float(static_cast<const __nv_bfloat16*>(s.grad)[i])
+    float g = GRAD_BF16 ? h2f(static_cast<const __nv_bfloat16*>(s.grad)[i])
                         : static_cast<const float*>(s.grad)[i];
     float p = master[i], mm = m[i], vv = v[i];
     adam_update(p, mm, vv, g * gs, h);
     master[i] = p; m[i] = mm; v[i] = vv;
-    if (po) po[i] = __float2bfloat16(p);
+    if (po) po[i] = f2h(p);
   }
 }
 
@@ -141,7 +141,7 @@ sumsq_partial_kernel(const void* __restrict__ x, long long n, float* __restrict_
     }
     const long long t = (nv << 3) + (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t < n) {
-      float f = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(x)[t]);
+      float f = h2f(reinterpret_cast<const __nv_bfloat16*>(x)[t]);
       acc += f * f;
     }
   } else {
@@ -206,7 +206,7 @@ scale_kernel(void* __restrict__ x, long long n, const float* __restrict__ scale_
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     if (DT == 0) {
       __nv_bfloat16* p = static_cast<__nv_bfloat16*>(x);
-      p[i] = __float2bfloat16(__bfloat162float(p[i]) * s);
+      p[i] = f2h(h2f(p[i]) * s);
     } else {
       float* p = static_cast<float*>(x);
       p[i] *= s;
@@ -225,14 +225,14 @@ sgd_momentum_flat_kernel(float* __restrict__ master, float* __restrict__ buf,
   const float gs = grad_scale ? *grad_scale : 1.f;
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const float g = (GRAD_BF16 ? __bfloat162float(static_cast<const __nv_bfloat16*>(grad)[i])
+    const float g = (GRAD_BF16 ? h2f(static_cast<const __nv_bfloat16*>(grad)[i])
                                : static_cast<const float*>(grad)[i]) * gs;
     float p = master[i];
     const float b = mu * buf[i] + g + wd * p;
     p -= lr * b;
     buf[i] = b;
     master[i] = p;
-    if (param_out) param_out[i] = __float2bfloat16(p);
+    if (param_out) param_out[i] = f2h(p);
   }
 }
 

@@ -148,3 +148,21 @@ def test_kernels_are_deterministic():
     logits = torch.randn(5000, 8, device=dev)
     r1, r2 = route_top1(logits, 700), route_top1(logits, 700)
     assert all(torch.equal(r1[k], r2[k]) for k in ("expert", "slot", "gate", "counts", "me", "ce"))
+
+
+def test_fp16_build_of_the_kernels():
+    """The -DB2F_HALF_FP16 build (IEEE fp16 storage and tensor-core operands, what `--fp16` selects) in a process of
+    its own: GEMM layouts and epilogues, norms, elementwise family, optimizer, attention forward / backward."""
+    import os
+    import subprocess
+    import sys
+    from pathlib import Path
+
+    root = Path(__file__).resolve().parent.parent
+    env = dict(os.environ, B2F_HALF="fp16")
+    res = subprocess.run([sys.executable, str(root / "tools" / "kernel_check.py"), "gemm_nt", "gemm_tn", "gemm_epi", "norm",
+                          "elementwise", "optim", "attn_fwd", "attn_bwd"], env=env, capture_output=True, text=True,
+                         timeout=600, cwd=root)
+    tail = "\n".join((res.stdout + res.stderr).splitlines()[-12:])
+    assert "libb200flow_cuda_fp16" in res.stdout or res.returncode == 0, tail
+    assert res.returncode == 0 and '"failed": 0' in res.stdout, tail

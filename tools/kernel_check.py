@@ -23,7 +23,10 @@ from b200flow.ops import gemm as G  # noqa: E402
 from b200flow.ops import norm as N  # noqa: E402
 from b200flow.ops import optim as O  # noqa: E402
 
+from b200flow.ops import _lib as _b2f_lib  # noqa: E402
+
 DEV = "cuda"
+HALF = _b2f_lib.HALF          # bf16, or fp16 when the process runs the fp16 build (B2F_HALF=fp16)
 RESULTS = []
 
 
@@ -115,8 +118,8 @@ def group_gemm(mode):
             M = (M + 7) // 8 * 8
         if mode in ("nn", "tn"):
             Nn = (Nn + 7) // 8 * 8
-        a = torch.randn(M, K, device=DEV, dtype=torch.bfloat16)
-        b = torch.randn(Nn, K, device=DEV, dtype=torch.bfloat16)
+        a = torch.randn(M, K, device=DEV, dtype=HALF)
+        b = torch.randn(Nn, K, device=DEV, dtype=HALF)
         ref = a.float() @ b.float().t()
         if mode == "nt":
             got = G.gemm(a, b)
@@ -133,14 +136,14 @@ def group_gemm(mode):
 def group_gemm_epi():
     torch.manual_seed(1)
     M, Nn, K = 512, 768, 256
-    a = torch.randn(M, K, device=DEV, dtype=torch.bfloat16)
-    b = torch.randn(Nn, K, device=DEV, dtype=torch.bfloat16) * 0.05
-    bias = torch.randn(Nn, device=DEV, dtype=torch.bfloat16)
-    res = torch.randn(M, Nn, device=DEV, dtype=torch.bfloat16)
+    a = torch.randn(M, K, device=DEV, dtype=HALF)
+    b = torch.randn(Nn, K, device=DEV, dtype=HALF) * 0.05
+    bias = torch.randn(Nn, device=DEV, dtype=HALF)
+    res = torch.randn(M, Nn, device=DEV, dtype=HALF)
     ref = a.float() @ b.float().t()
     report("epi_bias", G.gemm(a, b, bias=bias), ref + bias.float(), 2e-2)
     report("epi_res", G.gemm(a, b, residual=res), ref + res.float(), 2e-2)
-    aux = torch.empty(M, Nn, device=DEV, dtype=torch.bfloat16)
+    aux = torch.empty(M, Nn, device=DEV, dtype=HALF)
     got = G.gemm(a, b, bias=bias, gelu=True, aux=aux)
     pre = ref + bias.float()
     report("epi_gelu", got, torch.nn.functional.gelu(pre, approximate="tanh"), 2e-2)
@@ -152,17 +155,17 @@ def group_gemm_epi():
     G.gemm(a, b, out=c32b, alpha=0.5)
     report("epi_f32_alpha", c32b, 0.5 * ref, 2e-2)
     # dgelu epilogue: C = (A B^T) * gelu'(z), z passed through the residual pointer
-    z = torch.randn(M, Nn, device=DEV, dtype=torch.bfloat16)
+    z = torch.randn(M, Nn, device=DEV, dtype=HALF)
     zf = z.float().requires_grad_()
     torch.nn.functional.gelu(zf, approximate="tanh").sum().backward()
     report("epi_dgelu", G.gemm(a, b, residual=z, dgelu=True), ref * zf.grad, 2e-2)
     # fused FFN (two GEMMs forward, four backward) against fp32 autograd
     H_, F_ = 256, 1024
-    x = torch.randn(384, H_, device=DEV, dtype=torch.bfloat16, requires_grad=True)
-    w1 = (torch.randn(F_, H_, device=DEV) * 0.05).to(torch.bfloat16).requires_grad_()
-    b1 = (torch.randn(F_, device=DEV) * 0.1).to(torch.bfloat16).requires_grad_()
-    w2 = (torch.randn(H_, F_, device=DEV) * 0.05).to(torch.bfloat16).requires_grad_()
-    b2 = (torch.randn(H_, device=DEV) * 0.1).to(torch.bfloat16).requires_grad_()
+    x = torch.randn(384, H_, device=DEV, dtype=HALF, requires_grad=True)
+    w1 = (torch.randn(F_, H_, device=DEV) * 0.05).to(HALF).requires_grad_()
+    b1 = (torch.randn(F_, device=DEV) * 0.1).to(HALF).requires_grad_()
+    w2 = (torch.randn(H_, F_, device=DEV) * 0.05).to(HALF).requires_grad_()
+    b2 = (torch.randn(H_, device=DEV) * 0.1).to(HALF).requires_grad_()
     y = G.mlp_gelu(x, w1, b1, w2, b2)
     dy = torch.randn_like(y)
     y.backward(dy)
@@ -174,8 +177,8 @@ def group_gemm_epi():
                           ("dw2", w2.grad, fw2.grad), ("db2", b2.grad, fb2.grad)):
         report(f"mlp_{nm}", got.reshape(-1, got.shape[-1]), want.reshape(-1, want.shape[-1]), 3e-2)
     # batched
-    ab = torch.randn(3, 256, 128, device=DEV, dtype=torch.bfloat16)
-    bb = torch.randn(3, 512, 128, device=DEV, dtype=torch.bfloat16)
+    ab = torch.randn(3, 256, 128, device=DEV, dtype=HALF)
+    bb = torch.randn(3, 512, 128, device=DEV, dtype=HALF)
     report("gemm_batched", G.gemm(ab, bb).reshape(-1, 512),
            torch.bmm(ab.float(), bb.float().transpose(1, 2)).reshape(-1, 512), 2e-2)
 
@@ -184,9 +187,9 @@ def group_gemm_perf():
     out = {}
     for (M, Nn, K) in [(4096, 4096, 4096), (8192, 8192, 8192), (4096, 22016, 4096), (4096, 4096, 11008),
                        (4096, 12288, 4096), (4096, 32000, 4096)]:
-        a = torch.randn(M, K, device=DEV, dtype=torch.bfloat16)
-        b = torch.randn(Nn, K, device=DEV, dtype=torch.bfloat16)
-        c = torch.empty(M, Nn, device=DEV, dtype=torch.bfloat16)
+        a = torch.randn(M, K, device=DEV, dtype=HALF)
+        b = torch.randn(Nn, K, device=DEV, dtype=HALF)
+        c = torch.empty(M, Nn, device=DEV, dtype=HALF)
         t_ours = timeit(lambda: G.gemm(a, b, out=c))
         t_cublas = timeit(lambda: torch.matmul(a, b.t(), out=c))
         fl = 2.0 * M * Nn * K
@@ -208,10 +211,10 @@ def group_norm():
     torch.manual_seed(2)
     for rms in (True, False):
         for (rows, H) in [(64, 1024), (300, 4096), (4096, 4096), (17, 768), (33, 2048), (9, 8192), (70, 5120), (5, 16384)]:
-            x = torch.randn(rows, H, device=DEV, dtype=torch.bfloat16, requires_grad=True)
-            r = torch.randn(rows, H, device=DEV, dtype=torch.bfloat16, requires_grad=True)
-            g = (1 + 0.1 * torch.randn(H, device=DEV)).to(torch.bfloat16).requires_grad_()
-            bta = None if rms else (0.1 * torch.randn(H, device=DEV)).to(torch.bfloat16).requires_grad_()
+            x = torch.randn(rows, H, device=DEV, dtype=HALF, requires_grad=True)
+            r = torch.randn(rows, H, device=DEV, dtype=HALF, requires_grad=True)
+            g = (1 + 0.1 * torch.randn(H, device=DEV)).to(HALF).requires_grad_()
+            bta = None if rms else (0.1 * torch.randn(H, device=DEV)).to(HALF).requires_grad_()
             y, h = N.norm(x, g, bta, residual=r, rms=rms, eps=1e-5)
             dy = torch.randn_like(y)
             dh = torch.randn_like(h)
@@ -221,7 +224,7 @@ def group_norm():
             rf = r.detach().float().requires_grad_()
             gf = g.detach().float().requires_grad_()
             bf = bta.detach().float().requires_grad_() if bta is not None else None
-            hf = (xf + rf).to(torch.bfloat16).float() + 0 * (xf + rf)
+            hf = (xf + rf).to(HALF).float() + 0 * (xf + rf)
             hf = xf + rf
             if rms:
                 yf = hf * torch.rsqrt(hf.pow(2).mean(-1, keepdim=True) + 1e-5) * gf
@@ -240,10 +243,10 @@ def group_norm():
 def group_norm_perf():
     """Bandwidth of the norm kernels (bytes = algorithmic minimum) against the measured HBM peak."""
     for (rows, H, rms) in [(32768, 1024, False), (4096, 4096, True), (16384, 4096, True), (8192, 8192, True)]:
-        x = torch.randn(rows, H, device=DEV, dtype=torch.bfloat16, requires_grad=True)
-        r = torch.randn(rows, H, device=DEV, dtype=torch.bfloat16)
-        g = torch.ones(H, device=DEV, dtype=torch.bfloat16, requires_grad=True)
-        b = None if rms else torch.zeros(H, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+        x = torch.randn(rows, H, device=DEV, dtype=HALF, requires_grad=True)
+        r = torch.randn(rows, H, device=DEV, dtype=HALF)
+        g = torch.ones(H, device=DEV, dtype=HALF, requires_grad=True)
+        b = None if rms else torch.zeros(H, device=DEV, dtype=HALF, requires_grad=True)
         y, h = N.norm(x, g, b, residual=r, rms=rms, eps=1e-5)
         dy = torch.randn_like(y)
         t_f = timeit(lambda: N.norm(x.detach(), g.detach(), None if b is None else b.detach(), residual=r, rms=rms, eps=1e-5))
@@ -263,7 +266,7 @@ def group_vocab_ce():
     torch.manual_seed(11)
     T, V, world = 300, 2048, 2
     Vl = V // world
-    logits = (torch.randn(T, V, device=DEV) * 3).to(torch.bfloat16)
+    logits = (torch.randn(T, V, device=DEV) * 3).to(HALF)
     targets = torch.randint(0, V, (T,), device=DEV)
     targets[::7] = -100
     lf = logits.float().requires_grad_()
@@ -293,7 +296,7 @@ def group_optim():
         p = torch.randn(n, device=DEV)
         m = torch.zeros(n, device=DEV)
         v = torch.zeros(n, device=DEV)
-        pb = torch.empty(n, device=DEV, dtype=torch.bfloat16)
+        pb = torch.empty(n, device=DEV, dtype=HALF)
         ref_p = torch.nn.Parameter(p.clone())
         opt = torch.optim.AdamW([ref_p], lr=1e-2, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
         for step in range(1, 4):
@@ -306,7 +309,7 @@ def group_optim():
         report(f"adamw_flat_bf16out_{n}", pb, ref_p.detach(), 1e-2)
     x = torch.randn(3000001, device=DEV)
     report("sumsq_f32", O.sumsq(x), (x.double() ** 2).sum().float().reshape(1), 1e-4)
-    xb = x.to(torch.bfloat16)
+    xb = x.to(HALF)
     report("sumsq_bf16", O.sumsq(xb), (xb.double() ** 2).sum().float().reshape(1), 1e-4)
     coef, nrm = O.clip_coef(O.sumsq(x), 1.0)
     report("clip_norm", nrm, x.norm().reshape(1), 1e-4)
@@ -319,8 +322,8 @@ def group_optim():
     ps = [torch.randn(s, device=DEV) for s in sizes]
     ms = [torch.zeros_like(t) for t in ps]
     vs = [torch.zeros_like(t) for t in ps]
-    gs = [torch.randn(s, device=DEV).to(torch.bfloat16) for s in sizes]
-    pbs = [torch.empty(s, device=DEV, dtype=torch.bfloat16) for s in sizes]
+    gs = [torch.randn(s, device=DEV).to(HALF) for s in sizes]
+    pbs = [torch.empty(s, device=DEV, dtype=HALF) for s in sizes]
     refs = [torch.nn.Parameter(t.clone()) for t in ps]
     opt = torch.optim.AdamW(refs, lr=1e-2, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.01)
     for r_, g_ in zip(refs, gs):
@@ -334,7 +337,7 @@ def group_optim():
 def group_elementwise():
     torch.manual_seed(4)
     rows, F = 300, 1024
-    gu = torch.randn(rows, 2 * F, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    gu = torch.randn(rows, 2 * F, device=DEV, dtype=HALF, requires_grad=True)
     out = ew.swiglu(gu)
     d = torch.randn_like(out)
     out.backward(d)
@@ -343,8 +346,8 @@ def group_elementwise():
     of.backward(d.float())
     report("swiglu_fwd", out, of, 2e-2)
     report("swiglu_bwd", gu.grad, gf.grad, 2e-2)
-    x = torch.randn(rows, F, device=DEV, dtype=torch.bfloat16, requires_grad=True)
-    b = torch.randn(F, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    x = torch.randn(rows, F, device=DEV, dtype=HALF, requires_grad=True)
+    b = torch.randn(F, device=DEV, dtype=HALF, requires_grad=True)
     y = ew.bias_gelu(x, b)
     y.backward(d)
     xf, bf = x.detach().float().requires_grad_(), b.detach().float().requires_grad_()
@@ -353,10 +356,10 @@ def group_elementwise():
     report("gelu_fwd", y, yf, 2e-2)
     report("gelu_bwd", x.grad, xf.grad, 2e-2)
     report("gelu_dbias", b.grad, bf.grad, 3e-2)
-    r = torch.randn(rows, F, device=DEV, dtype=torch.bfloat16)
+    r = torch.randn(rows, F, device=DEV, dtype=HALF)
     o0 = ew.bias_dropout_add(x.detach(), b.detach(), r, 0.0)
     report("bda_p0", o0, x.detach().float() + b.detach().float() + r.float(), 2e-2)
-    xx = torch.ones(4096, 1024, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    xx = torch.ones(4096, 1024, device=DEV, dtype=HALF, requires_grad=True)
     o1 = ew.bias_dropout_add(xx, None, None, 0.25, seed=123)
     keep = (o1 != 0).float().mean().item()
     RESULTS.append({"name": "bda_keep_frac", "ok": abs(keep - 0.75) < 0.01, "keep": keep})
@@ -365,7 +368,7 @@ def group_elementwise():
     report("bda_bwd_mask", xx.grad, o1.detach(), 1e-3)
     # rope
     tokens, nh, dh, seq = 256, 4, 128, 128
-    q = torch.randn(tokens, nh, dh, device=DEV, dtype=torch.bfloat16)
+    q = torch.randn(tokens, nh, dh, device=DEV, dtype=HALF)
     cos_t, sin_t = ew.rope_tables(seq, dh, 10000.0, DEV)
     q2 = q.clone()
     ew.rope_inplace_raw(q2, cos_t, sin_t, seq, False)
@@ -379,7 +382,7 @@ def group_elementwise():
     report("rope_roundtrip", q2.reshape(tokens, -1), qf.reshape(tokens, -1), 3e-2)
     # cross entropy
     T, V = 512, 32000
-    logits = (torch.randn(T, V, device=DEV) * 2).to(torch.bfloat16).requires_grad_()
+    logits = (torch.randn(T, V, device=DEV) * 2).to(HALF).requires_grad_()
     tg = torch.randint(0, V, (T,), device=DEV)
     tg[:7] = -100
     lf = logits.detach().float().requires_grad_()
@@ -391,7 +394,7 @@ def group_elementwise():
     report("ce_loss", loss.reshape(1), ref_loss.reshape(1), 1e-3)
     report("ce_grad", lc.grad, lf.grad, 2e-2)
     # softmax
-    xs = torch.randn(2, 3, 64, 64, device=DEV, dtype=torch.bfloat16)
+    xs = torch.randn(2, 3, 64, 64, device=DEV, dtype=HALF)
     ys = ew.scaled_masked_softmax(xs, None, 0.125, causal=True)
     mask = torch.triu(torch.ones(64, 64, device=DEV, dtype=torch.bool), 1)
     refs = torch.softmax((xs.float() * 0.125).masked_fill(mask, float("-inf")), -1)
@@ -428,7 +431,7 @@ def group_attn(which):
         (B, S, H, HKV, D, causal), amp = cfg[:6], (cfg[6] if len(cfg) > 6 else 1.0)
         qkv_shape = (B, S, H + 2 * HKV, D)
         # amp > 1 makes the row max jump between key tiles (exercises the lazy O rescale)
-        buf = (torch.randn(qkv_shape, device=DEV) * amp).to(torch.bfloat16)
+        buf = (torch.randn(qkv_shape, device=DEV) * amp).to(HALF)
         q = buf[:, :, :H].detach().requires_grad_()
         k = buf[:, :, H:H + HKV].detach().requires_grad_()
         v = buf[:, :, H + HKV:].detach().requires_grad_()
@@ -453,7 +456,7 @@ def group_attn(which):
     if which == "bwd":
         # key-padding lengths + packed qkv path
         B, S, H, D = 2, 256, 2, 128
-        qkv = torch.randn(B, S, 3, H, D, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+        qkv = torch.randn(B, S, 3, H, D, device=DEV, dtype=HALF, requires_grad=True)
         lens = torch.tensor([256, 130], device=DEV, dtype=torch.int32)
         o = A.flash_attention_qkvpacked(qkv, False, D ** -0.5, lens)
         do = torch.randn_like(o)
@@ -468,7 +471,7 @@ def group_attn(which):
 def group_attn_perf():
     from b200flow.ops import attention as A
     for (B, S, H, D, causal) in [(1, 4096, 32, 128, True), (8, 512, 16, 64, False)]:
-        qkv = torch.randn(B, S, 3, H, D, device=DEV, dtype=torch.bfloat16)
+        qkv = torch.randn(B, S, 3, H, D, device=DEV, dtype=HALF)
         q, k, v = qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2]
         scale = D ** -0.5
         o, lse = A.attn_fwd_raw(q, k, v, causal, scale)
@@ -497,7 +500,7 @@ def group_detection():
     C = 64
     shapes = [(2, 200, 336), (2, 100, 168), (2, 50, 84), (2, 25, 42)]
     scales = [0.25, 0.125, 0.0625, 0.03125]
-    feats = [torch.randn(n, h, w, C, device=DEV).to(torch.bfloat16).requires_grad_() for n, h, w in shapes]
+    feats = [torch.randn(n, h, w, C, device=DEV).to(HALF).requires_grad_() for n, h, w in shapes]
     R = 300
     xy = torch.rand(R, 2, device=DEV) * torch.tensor([1000.0, 600.0], device=DEV)
     wh = torch.rand(R, 2, device=DEV) * 500 + 8
@@ -595,11 +598,11 @@ def group_maskrcnn_step():
     from b200flow.optim import FlatMomentumSGD
     from b200flow.utils.flat import FlatParams
     torch.manual_seed(0)
-    model = MaskRCNN(MaskRCNNConfig()).to(DEV).to(torch.bfloat16).to(memory_format=torch.channels_last)
+    model = MaskRCNN(MaskRCNNConfig()).to(DEV).to(HALF).to(memory_format=torch.channels_last)
     flat = FlatParams(model)
     opt = FlatMomentumSGD(flat, lr=0.005)
     data = list(coco_like(2, 800, 1344, seed=3))
-    imgs = torch.stack([s["image"] for s in data]).to(DEV).to(torch.bfloat16)
+    imgs = torch.stack([s["image"] for s in data]).to(DEV).to(HALF)
     tg = [{k: s[k].to(DEV) for k in ("boxes", "labels", "masks")} for s in data]
     model.train()
     ls = []
@@ -636,8 +639,8 @@ def group_moe():
     report("router_gate", r["gate"].reshape(1, -1), rc["gate"].reshape(1, -1), 1e-5)
     report("router_me", r["me"].reshape(1, -1), rc["me"].reshape(1, -1), 1e-4)
     report("router_ce", r["ce"].reshape(1, -1), rc["ce"].reshape(1, -1), 1e-6)
-    layer = MoELayer(256, 512, 8, dtype=torch.bfloat16, device=DEV)
-    x = (torch.randn(1024, 256, device=DEV) * 0.5).to(torch.bfloat16).requires_grad_()
+    layer = MoELayer(256, 512, 8, dtype=HALF, device=DEV)
+    x = (torch.randn(1024, 256, device=DEV) * 0.5).to(HALF).requires_grad_()
     y = layer(x)
     (y.float().square().sum() + layer.last_aux).backward()
     ref_layer = MoELayer(256, 512, 8, dtype=torch.float32)
@@ -661,9 +664,9 @@ def group_attn_drop():
     for (B, S, H, HKV, D, causal, pd) in [(2, 512, 4, 4, 64, True, 0.1), (1, 896, 4, 2, 128, True, 0.1),
                                           (2, 384, 2, 2, 128, False, 0.25)]:
         tag = f"B{B}S{S}H{H}kv{HKV}D{D}{'c' if causal else 'f'}p{pd}"
-        q = torch.randn(B, S, H, D, device=DEV, dtype=torch.bfloat16).requires_grad_()
-        k = torch.randn(B, S, HKV, D, device=DEV, dtype=torch.bfloat16).requires_grad_()
-        v = torch.randn(B, S, HKV, D, device=DEV, dtype=torch.bfloat16).requires_grad_()
+        q = torch.randn(B, S, H, D, device=DEV, dtype=HALF).requires_grad_()
+        k = torch.randn(B, S, HKV, D, device=DEV, dtype=HALF).requires_grad_()
+        v = torch.randn(B, S, HKV, D, device=DEV, dtype=HALF).requires_grad_()
         kv_lens = torch.tensor([S - 37 * (i % 2) for i in range(B)], dtype=torch.int32, device=DEV)
         seed = 12345 + S
         o = A.flash_attention(q, k, v, causal, None, kv_lens, dropout_p=pd, seed=seed)
@@ -690,8 +693,8 @@ def group_attn_drop():
         report(f"attn_drop_dk_{tag}", k.grad.reshape(B * S, -1), kf.grad.reshape(B * S, -1), 3e-2, floor=2.0)
         report(f"attn_drop_dv_{tag}", v.grad.reshape(B * S, -1), vf.grad.reshape(B * S, -1), 3e-2, floor=1.0)
     # cost of the mask: B1 S4096 H32 D128 causal, forward + backward
-    q = torch.randn(1, 4096, 32, 128, device=DEV, dtype=torch.bfloat16).requires_grad_()
-    k, v = (torch.randn(1, 4096, 32, 128, device=DEV, dtype=torch.bfloat16).requires_grad_() for _ in range(2))
+    q = torch.randn(1, 4096, 32, 128, device=DEV, dtype=HALF).requires_grad_()
+    k, v = (torch.randn(1, 4096, 32, 128, device=DEV, dtype=HALF).requires_grad_() for _ in range(2))
     def run(pd):
         o = A.flash_attention(q, k, v, True, None, None, dropout_p=pd, seed=7)
         o.backward(o)
@@ -706,7 +709,7 @@ def group_k5():
     from b200flow.parallel.moe import MoELayer
     torch.manual_seed(8)
     H, F, E, T = 512, 1024, 8, 4096
-    layer = MoELayer(H, F, E, dtype=torch.bfloat16, device=DEV, fp8=True, capacity_factor=1.0)
+    layer = MoELayer(H, F, E, dtype=HALF, device=DEV, fp8=True, capacity_factor=1.0)
     with torch.no_grad():
         layer.b1.normal_(0, 0.05)
         layer.b2.normal_(0, 0.05)
@@ -715,7 +718,7 @@ def group_k5():
     ref_layer = MoELayer(H, F, E, dtype=torch.float32, capacity_factor=1.0)
     ref_layer.load_state_dict({k: v.float().cpu() for k, v in layer.state_dict().items()})
     for rep in range(2):
-        x = (torch.randn(T, H, device=DEV) * 0.5).to(torch.bfloat16).requires_grad_()
+        x = (torch.randn(T, H, device=DEV) * 0.5).to(HALF).requires_grad_()
         y = layer(x)
         (y.float().square().sum() + layer.last_aux).backward()
         torch.cuda.synchronize()
@@ -735,8 +738,8 @@ def group_k5():
         report_rms(f"k5_dwg_r{rep}", layer.wg.grad[:E], ref_layer.wg.grad[:E], 1e-1)
         layer.zero_grad(); ref_layer.zero_grad()
     # the size of BASELINE config 5 on one GPU: 8 experts x 2048 tokens each
-    big = MoELayer(2048, 8192, 8, dtype=torch.bfloat16, device=DEV, fp8=True)
-    xb = (torch.randn(16384, 2048, device=DEV) * 0.5).to(torch.bfloat16).requires_grad_()
+    big = MoELayer(2048, 8192, 8, dtype=HALF, device=DEV, fp8=True)
+    xb = (torch.randn(16384, 2048, device=DEV) * 0.5).to(HALF).requires_grad_()
     def step():
         big(xb).float().sum().backward()
     ms = timeit(step, iters=5, warmup=2)
@@ -754,8 +757,8 @@ def group_fp8():
     from b200flow.ops import gemm_fp8 as F8
     torch.manual_seed(9)
     for (M, Nn, K) in [(256, 512, 256), (1000, 2048, 1024), (4096, 8192, 2048)]:
-        a = (torch.randn(M, K, device=DEV) * torch.rand(M, 1, device=DEV) * 3).to(torch.bfloat16)
-        b = (torch.randn(Nn, K, device=DEV) * 0.05).to(torch.bfloat16)
+        a = (torch.randn(M, K, device=DEV) * torch.rand(M, 1, device=DEV) * 3).to(HALF)
+        b = (torch.randn(Nn, K, device=DEV) * 0.05).to(HALF)
         aq, sa = F8.quantize_rows(a)
         bq, sb = F8.quantize_rows(b)
         deq = aq.view(torch.float8_e4m3fn).float() * sa[:, None]
@@ -764,9 +767,9 @@ def group_fp8():
         got = F8.gemm_fp8(aq, sa, bq, sb)
         report(f"fp8_gemm_exact_{M}x{Nn}x{K}", got, exact, 1e-2)       # vs the same quantised operands
         report_rms(f"fp8_gemm_vs_bf16_{M}x{Nn}x{K}", got, a.float() @ b.float().t(), 6e-2)
-    x = (torch.randn(2048, 2048, device=DEV)).to(torch.bfloat16).requires_grad_()
-    w = (torch.randn(8192, 2048, device=DEV) * 0.02).to(torch.bfloat16).requires_grad_()
-    bias = torch.zeros(8192, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    x = (torch.randn(2048, 2048, device=DEV)).to(HALF).requires_grad_()
+    w = (torch.randn(8192, 2048, device=DEV) * 0.02).to(HALF).requires_grad_()
+    bias = torch.zeros(8192, device=DEV, dtype=HALF, requires_grad=True)
     y = F8.linear_gelu_fp8(x, w, bias)
     dy = torch.randn_like(y)
     y.backward(dy)
@@ -776,8 +779,8 @@ def group_fp8():
     report_rms("fp8_linear_gelu_fwd", y, yf, 6e-2)
     report_rms("fp8_linear_gelu_dx", x.grad, xf.grad, 8e-2)
     report_rms("fp8_linear_gelu_dw", w.grad, wf.grad, 6e-2)
-    a = torch.randn(4096, 4096, device=DEV, dtype=torch.bfloat16)
-    b = torch.randn(8192, 4096, device=DEV, dtype=torch.bfloat16)
+    a = torch.randn(4096, 4096, device=DEV, dtype=HALF)
+    b = torch.randn(8192, 4096, device=DEV, dtype=HALF)
     aq, sa = F8.quantize_rows(a); bq, sb = F8.quantize_rows(b)
     t8 = timeit(lambda: F8.gemm_fp8(aq, sa, bq, sb))
     t16 = timeit(lambda: G.gemm(a, b))
@@ -795,9 +798,9 @@ def group_gemm2():
     out = {}
     for (M, Nn, K) in [(4096, 4096, 4096), (8192, 8192, 8192), (4096, 22016, 4096), (4096, 4096, 11008),
                        (4096, 12288, 4096), (4096, 32000, 4096)]:
-        a = torch.randn(M, K, device=DEV, dtype=torch.bfloat16)
-        b = torch.randn(Nn, K, device=DEV, dtype=torch.bfloat16)
-        c = torch.empty(M, Nn, device=DEV, dtype=torch.bfloat16)
+        a = torch.randn(M, K, device=DEV, dtype=HALF)
+        b = torch.randn(Nn, K, device=DEV, dtype=HALF)
+        c = torch.empty(M, Nn, device=DEV, dtype=HALF)
         fl = 2.0 * M * Nn * K
         G.GEMM_IMPL = "2cta"
         t2 = timeit(lambda: G.gemm(a, b, out=c))
@@ -833,46 +836,46 @@ def group_mx():
         return got, ref
 
     M, Nn, K = 256, 384, 256
-    a = torch.randn(M, K, device=DEV, dtype=torch.bfloat16)
-    b = torch.randn(Nn, K, device=DEV, dtype=torch.bfloat16)
+    a = torch.randn(M, K, device=DEV, dtype=HALF)
+    b = torch.randn(Nn, K, device=DEV, dtype=HALF)
     ones_a, ones_b = torch.ones_like(a), torch.ones_like(b)
     got, ref = case("uniform", ones_a, ones_b)
     report("mx_gemm_uniform", got, ref, 5e-3)
     rows = torch.pow(2.0, (torch.arange(M, device=DEV) % 11).float())[:, None]
-    got, ref = case("a_rows", (ones_a.float() * rows).to(torch.bfloat16), ones_b)
+    got, ref = case("a_rows", (ones_a.float() * rows).to(HALF), ones_b)
     report("mx_gemm_a_rows", got, ref, 5e-3)
     cols = torch.pow(2.0, (torch.arange(Nn, device=DEV) % 13).float())[:, None]
-    got, ref = case("b_rows", ones_a, (ones_b.float() * cols).to(torch.bfloat16))
+    got, ref = case("b_rows", ones_a, (ones_b.float() * cols).to(HALF))
     report("mx_gemm_b_rows", got, ref, 5e-3)
     kg = torch.pow(2.0, ((torch.arange(K, device=DEV) // 32) % 5).float())[None, :]
-    got, ref = case("k_groups", (ones_a.float() * kg).to(torch.bfloat16), (ones_b.float() / kg).to(torch.bfloat16))
+    got, ref = case("k_groups", (ones_a.float() * kg).to(HALF), (ones_b.float() / kg).to(HALF))
     report("mx_gemm_k_groups", got, ref, 5e-3)
     for (M, Nn, K) in [(128, 192, 128), (256, 384, 256), (384, 8192, 2048), (200, 328, 384), (4096, 2048, 8192)]:
-        a = torch.randn(M, K, device=DEV, dtype=torch.bfloat16) * torch.pow(
-            2.0, torch.randint(-6, 6, (M, 1), device=DEV).float()).to(torch.bfloat16)
-        b = (torch.randn(Nn, K, device=DEV) * 0.05).to(torch.bfloat16)
+        a = torch.randn(M, K, device=DEV, dtype=HALF) * torch.pow(
+            2.0, torch.randint(-6, 6, (M, 1), device=DEV).float()).to(HALF)
+        b = (torch.randn(Nn, K, device=DEV) * 0.05).to(HALF)
         got, ref = case(f"{M}x{Nn}x{K}", a, b)
         report(f"mx_gemm_{M}x{Nn}x{K}", got, ref, 5e-3)
         report_rms(f"mx_gemm_vs_bf16_{M}x{Nn}x{K}", got, a.float() @ b.float().t(), 6e-2)
     # epilogue: bias + gelu with the pre-activation copy, batched operands
     E_, M, Nn, K = 2, 256, 320, 256
-    a = torch.randn(E_, M, K, device=DEV, dtype=torch.bfloat16)
-    b = (torch.randn(E_, Nn, K, device=DEV) * 0.05).to(torch.bfloat16)
+    a = torch.randn(E_, M, K, device=DEV, dtype=HALF)
+    b = (torch.randn(E_, Nn, K, device=DEV) * 0.05).to(HALF)
     got, ref = case("batched", a, b)
     report("mx_gemm_batched", got.reshape(E_ * M, Nn), ref.reshape(E_ * M, Nn), 5e-3)
-    bias = torch.randn(Nn, device=DEV, dtype=torch.bfloat16)
-    aux = torch.empty(M, Nn, device=DEV, dtype=torch.bfloat16)
+    bias = torch.randn(Nn, device=DEV, dtype=HALF)
+    aux = torch.empty(M, Nn, device=DEV, dtype=HALF)
     got, ref = case("gelu", a[0], b[0], bias=bias, gelu=True, aux=aux)
     report("mx_gemm_gelu_aux", aux, ref + bias.float(), 5e-3)
     report("mx_gemm_gelu", got, torch.nn.functional.gelu(ref + bias.float(), approximate="tanh"), 1e-2)
-    a = torch.randn(4096, 2048, device=DEV, dtype=torch.bfloat16)
-    b = torch.randn(8192, 2048, device=DEV, dtype=torch.bfloat16)
+    a = torch.randn(4096, 2048, device=DEV, dtype=HALF)
+    b = torch.randn(8192, 2048, device=DEV, dtype=HALF)
     ta, tb = MX.quantize_mx(a), MX.quantize_mx(b)
     ms = timeit(lambda: MX.gemm_mx(ta, tb))
     print(json.dumps({"name": "mx_gemm_perf_4096x8192x2048", "ms": ms,
                       "tflops": 2 * 4096 * 8192 * 2048 / ms / 1e9}), flush=True)
-    ta2, tb2 = MX.quantize_mx(torch.randn(4096, 8192, device=DEV, dtype=torch.bfloat16)), MX.quantize_mx(
-        torch.randn(2048, 8192, device=DEV, dtype=torch.bfloat16))
+    ta2, tb2 = MX.quantize_mx(torch.randn(4096, 8192, device=DEV, dtype=HALF)), MX.quantize_mx(
+        torch.randn(2048, 8192, device=DEV, dtype=HALF))
     ms = timeit(lambda: MX.gemm_mx(ta2, tb2))
     print(json.dumps({"name": "mx_gemm_perf_4096x2048x8192", "ms": ms,
                       "tflops": 2 * 4096 * 8192 * 2048 / ms / 1e9}), flush=True)

@@ -77,42 +77,108 @@ def group_arena():
 
 
 def group_allreduce():
+    """K1 in its four forms (fp32 or bf16 on the wire x peer loads / stores or NVLS multimem) against NCCL: numerics
+    on a whole buffer and on a slice, then bus bandwidth at a DDP bucket (25 MB) and at 1 GB of fp32 gradients."""
     from b200flow.comm.arena import PeerComm
     from b200flow.parallel.fused_dp import FusedAllReduce
 
     rank, world = dist.get_rank(), dist.get_world_size()
     dev = torch.device("cuda", torch.cuda.current_device())
     comm = PeerComm(dist.group.WORLD, rank, world, dev)
-    n = 64 << 20
+    n = 256 << 20                                       # 1 GiB of fp32
     buf = comm.alloc(n * 4)
     g = buf.view(torch.float32, n)
-    for use_mc in ([False, True] if buf.multicast_ptr else [False]):
-        ar = FusedAllReduce(comm, buf, blocks=32, use_multicast=use_mc)
-        torch.manual_seed(rank)
-        src = torch.randn(n, device=dev)
-        g.copy_(src)
-        ref = src.clone()
-        dist.all_reduce(ref)
-        ref /= world
-        bf = torch.empty(n, device=dev, dtype=torch.bfloat16)
-        torch.cuda.synchronize(); dist.barrier()
-        ar(0, n, 1.0 / world, bf)
-        torch.cuda.synchronize()
-        tag = "nvls" if use_mc else "p2p"
-        report(f"allreduce_{tag}", rel(g, ref) < 1e-5, err=rel(g, ref))
-        report(f"allreduce_{tag}_bf16", rel(bf, ref) < 1e-2)
-        # slice of the buffer
-        g.copy_(src)
-        torch.cuda.synchronize(); dist.barrier()
-        ar(1024, 4096, 1.0 / world)
-        torch.cuda.synchronize()
-        report(f"allreduce_{tag}_slice", rel(g[1024:5120], ref[1024:5120]) < 1e-5 and
-               torch.equal(g[:1024], src[:1024]))
-        t = timeit(lambda: ar(0, n, 1.0 / world))
-        tn = timeit(lambda: dist.all_reduce(ref))
-        bus = 2 * (world - 1) / world * n * 4 / 1e9
-        report(f"allreduce_{tag}_perf", True, ms=t, nccl_ms=tn, busbw_gbs=bus / (t / 1e3),
-               nccl_busbw_gbs=bus / (tn / 1e3))
+    torch.manual_seed(rank)
+    src = torch.randn(n, device=dev)
+    ref = src.clone()
+    dist.all_reduce(ref)
+    ref /= world
+    for wire in (False, True):
+        for use_mc in ([False, True] if buf.multicast_ptr else [False]):
+            ar = FusedAllReduce(comm, buf, blocks=32, use_multicast=use_mc, wire_bf16=wire)
+            tol = 1e-2 if wire else 1e-5
+            tag = ("bf16wire_" if wire else "fp32_") + ("nvls" if use_mc else "p2p")
+            g.copy_(src)
+            torch.cuda.synchronize(); dist.barrier()
+            ar(0, n, 1.0 / world)
+            torch.cuda.synchronize()
+            report(f"allreduce_{tag}", rel(g, ref) < tol, err=rel(g, ref))
+            if not wire:
+                g.copy_(src)
+                bf = torch.empty(n, device=dev, dtype=torch.bfloat16)
+                torch.cuda.synchronize(); dist.barrier()
+                ar(0, n, 1.0 / world, bf)
+                torch.cuda.synchronize()
+                report(f"allreduce_{tag}_bf16_out", rel(bf, ref) < 1e-2)
+                del bf
+            g.copy_(src)
+            torch.cuda.synchronize(); dist.barrier()
+            ar(1024, 4096, 1.0 / world)
+            torch.cuda.synchronize()
+            report(f"allreduce_{tag}_slice", rel(g[1024:5120], ref[1024:5120]) < tol and
+                   torch.equal(g[:1024], src[:1024]) and torch.equal(g[5120:8192], src[5120:8192]))
+            for blocks in (32, 128):      # 32: the overlapped DDP setting (few SMs); 128: the kernel on its own
+                arp = FusedAllReduce(comm, buf, blocks=blocks, use_multicast=use_mc, wire_bf16=wire)
+                for label, m in (("25MB", 25 * (1 << 20) // 4 // 8 * 8), ("1GiB", n)):
+                    t = timeit(lambda: arp(0, m, 1.0 / world))
+                    bus = 2 * (world - 1) / world * m * 4 / 1e9           # fp32-equivalent bus bandwidth
+                    report(f"allreduce_{tag}_perf_{label}_blocks{blocks}", True, ms=t, busbw_gbs=bus / (t / 1e3), world=world)
+    scratch = torch.randn(n, device=dev)
+    for label, m in (("25MB", 25 * (1 << 20) // 4 // 8 * 8), ("1GiB", n)):
+        tn = timeit(lambda: dist.all_reduce(scratch[:m]))
+        bus = 2 * (world - 1) / world * m * 4 / 1e9
+        report(f"nccl_fp32_allreduce_perf_{label}", True, ms=tn, busbw_gbs=bus / (tn / 1e3), world=world)
+    del scratch
+    rb = ref[:25 * (1 << 20) // 4].to(torch.bfloat16)
+    tb = timeit(lambda: dist.all_reduce(rb))
+    report("nccl_bf16_allreduce_25MB_elements", True, ms=tb, world=world)
+
+
+def group_zero1_perf():
+    """K2 in isolation at the shard size of BASELINE config 4 (0.84 B elements owned per rank at DP 2): the two fused
+    kernels against NCCL reduce-scatter + fused AdamW (the same K11 kernel) + NCCL all-gather."""
+    from b200flow.comm.arena import PeerComm
+    from b200flow.ops import optim as O
+    from b200flow.parallel.fused_dp import FusedZero1
+    from b200flow.parallel.zero1 import AdamConfig
+
+    rank, world = dist.get_rank(), dist.get_world_size()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    comm = PeerComm(dist.group.WORLD, rank, world, dev)
+    per = int(os.environ.get("B2F_ZERO1_PERF_ELEMS", 840 * (1 << 20))) // 1024 * 1024
+    n = per * world
+    gbuf, pbuf = comm.alloc(n * 4), comm.alloc(n * 2)
+    grads, params = gbuf.view(torch.float32, n), pbuf.view(torch.bfloat16, n)
+    grads.normal_(0, 1e-3)
+
+    class Opt:   # what FusedZero1.step reads of a Zero1Optimizer
+        pass
+    opt = Opt()
+    opt.flat, opt.cfg = None, AdamConfig(lr=1e-4, beta1=0.9, beta2=0.95, eps=1e-8, weight_decay=0.1, clip_grad=1.0)
+    opt.lo, opt.hi = rank * per, (rank + 1) * per
+    opt.master = torch.randn(per, device=dev) * 0.02
+    opt.exp_avg, opt.exp_avg_sq = torch.zeros(per, device=dev), torch.zeros(per, device=dev)
+    opt.lr, opt.step_count, opt.dp_group, opt.norm_groups = 1e-4, 1, dist.group.WORLD, []
+    for mm in (True, False):
+        os.environ["B2F_ZERO1_MULTIMEM"] = "1" if mm else "0"
+        fz = FusedZero1(comm, gbuf, pbuf)
+        t = timeit(lambda: fz.step(opt, 1.0), iters=5, warmup=2)
+        report(f"zero1_fused_{'multimem' if mm else 'p2p'}_perf", True, ms=t, elems_per_rank=per, world=world,
+               multicast=bool(gbuf.multicast_ptr))
+    shard = torch.empty(per, device=dev)
+    pshard = torch.empty(per, device=dev, dtype=torch.bfloat16)
+    sq = torch.zeros(1, device=dev)
+
+    def nccl_path():
+        dist.reduce_scatter_tensor(shard, grads)
+        O.sumsq(shard, sq)
+        dist.all_reduce(sq)
+        coef, _ = O.clip_coef(sq, 1.0)
+        O.adamw_flat_(opt.master, opt.exp_avg, opt.exp_avg_sq, shard, pshard, lr=1e-4, beta1=0.9, beta2=0.95, eps=1e-8,
+                      weight_decay=0.1, step=1, grad_scale=coef)
+        dist.all_gather_into_tensor(params, pshard)
+    tn = timeit(nccl_path, iters=5, warmup=2)
+    report("zero1_nccl_rs_adam_ag_perf", True, ms=tn, elems_per_rank=per, world=world)
 
 
 def _engine_curve(tp, pp, fused, steps=4, preset_kw=None, ds_extra=None):
@@ -374,7 +440,7 @@ def group_moe_k5():
            wire_bytes_per_a2a_mb=16384 * 2048 * (1 + 1 / 32) * (world - 1) / world / 2 ** 20)
 
 
-GROUPS = {"moe_k5": group_moe_k5, "moe_ep": group_moe_ep, "fused_gemm": group_fused_gemm, "arena": group_arena, "allreduce": group_allreduce, "zero1": group_zero1, "tp": group_tp,
+GROUPS = {"zero1_perf": group_zero1_perf, "moe_k5": group_moe_k5, "moe_ep": group_moe_ep, "fused_gemm": group_fused_gemm, "arena": group_arena, "allreduce": group_allreduce, "zero1": group_zero1, "tp": group_tp,
           "pp": group_pp, "tp_replicated": group_tp_replicated,
           "ulysses": group_ulysses}
 
