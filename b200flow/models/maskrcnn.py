@@ -85,6 +85,22 @@ def _sample(pos_mask, neg_mask, batch, pos_frac):
     return pos, neg
 
 
+def _sample_static(pos_mask, neg_mask, batch: int, pos_frac: float):
+    """Fixed-shape version of the fg / bg sampler: no `nonzero`, no data-dependent sizes, so the step never waits for
+    the GPU.  Returns (pos_idx [P], pos_ok [P], neg_idx [Q], neg_ok [Q]) with P = batch * pos_frac, Q = batch: random
+    members of each set (top-k of uniform noise restricted to the set), `*_ok` marking the entries that are real and
+    inside the quota - negatives fill whatever the positives leave of `batch`, as in tensorpack's sampler."""
+    P = int(batch * pos_frac)
+    n = pos_mask.numel()
+    noise = torch.rand(2, n, device=pos_mask.device)
+    ps, pos_idx = torch.where(pos_mask, noise[0], noise.new_full((), -1.0)).topk(min(P, n))
+    pos_ok = ps >= 0
+    quota = batch - pos_ok.sum()                                   # a device scalar: never read on the host
+    ns, neg_idx = torch.where(neg_mask, noise[1], noise.new_full((), -1.0)).topk(min(batch, n))
+    neg_ok = (ns >= 0) & (torch.arange(neg_idx.numel(), device=ns.device) < quota)
+    return pos_idx, pos_ok, neg_idx, neg_ok
+
+
 class RPNHead(nn.Module):
     def __init__(self, c, a):
         super().__init__()
@@ -156,12 +172,17 @@ class MaskRCNN(nn.Module):
         # convolution weights (models/resnet_fpn.py), the stem and res2 are frozen as tensorpack does
         self.backbone = ResNetFPN(50 if cfg.width >= 1.0 else 18, c)
         self.strides = (4, 8, 16, 32, 64)
+        # fixed-shape training path (no host synchronisation inside the step); B2F_MASKRCNN_STATIC=0 restores the
+        # variable-length formulation, which is also what the CPU oracle tests compare against
+        import os
+
+        self.static_shapes = os.environ.get("B2F_MASKRCNN_STATIC", "1") == "1"
         self.rpn = RPNHead(c, len(cfg.anchor_ratios))
         self.box_head = FCHead(c * 7 * 7, max(64, int(cfg.fc_dim * cfg.width)), cfg.num_classes)
         self.mask_head = MaskHead(c, cfg.num_classes, c) if cfg.mode_mask else None
 
     # ------------------------------------------------------------------ RPN
-    def _proposals(self, logits, deltas, anchors, img_hw, training):
+    def _proposals(self, logits, deltas, anchors, img_hw, training, static=False):
         cfg = self.cfg
         n = logits[0].shape[0]
         pre = cfg.rpn_pre_nms_train if training else cfg.rpn_pre_nms_test
@@ -185,14 +206,12 @@ class MaskRCNN(nn.Module):
         wh_ok = ((boxes[:, 2] - boxes[:, 0]) > 1e-3) & ((boxes[:, 3] - boxes[:, 1]) > 1e-3)
         scores = torch.where(keep & wh_ok, scores, scores.new_full((), -1e9))
         per_img = sum(seg_sizes)
-        out = []
-        for i in range(n):
-            s = scores[i * per_img:(i + 1) * per_img]
-            k = min(post, s.numel())
-            top, idx = s.topk(k)
-            sel = idx[top > -1e8]
-            out.append(boxes[i * per_img:(i + 1) * per_img][sel])
-        return out
+        k = min(post, per_img)
+        top, idx = scores.view(n, per_img).topk(k, dim=1)
+        picked = torch.gather(boxes.view(n, per_img, 4), 1, idx[..., None].expand(-1, -1, 4))
+        if static:      # fixed [n, k, 4] + validity mask: nothing on the host depends on how many survived NMS
+            return picked, top > -1e8
+        return [picked[i][top[i] > -1e8] for i in range(n)]
 
     def _rpn_loss(self, logits, deltas, anchors, targets):
         cfg = self.cfg
@@ -222,6 +241,103 @@ class MaskRCNN(nn.Module):
         n = max(1, len(targets))
         return cls_loss / n, box_loss / n
 
+    def _rpn_loss_static(self, logits, deltas, anchors, targets):
+        """`_rpn_loss` with fixed shapes (see `_sample_static`): the same labels and the same losses in expectation,
+        no host synchronisation."""
+        cfg = self.cfg
+        lg = torch.cat(logits, 1).float()
+        dl = torch.cat(deltas, 1).float()
+        an = torch.cat(anchors, 0)
+        cls_loss, box_loss = lg.new_zeros(()), lg.new_zeros(())
+        for i, t in enumerate(targets):
+            gt = t["boxes"].float()
+            if gt.shape[0] == 0:                       # a host-side shape, not a device value
+                pos_m = torch.zeros(an.shape[0], dtype=torch.bool, device=an.device)
+                neg_m = ~pos_m
+                arg = torch.zeros(an.shape[0], dtype=torch.long, device=an.device)
+                gt = an.new_zeros(1, 4)
+            else:
+                iou = D.pairwise_iou(an, gt)
+                best, arg = iou.max(1)
+                labels = torch.full_like(best, -1)
+                labels[best < cfg.rpn_bg_iou] = 0
+                labels[best >= cfg.rpn_fg_iou] = 1
+                labels[iou.argmax(0)] = 1
+                pos_m, neg_m = labels == 1, labels == 0
+            pi, pok, ni, nok = _sample_static(pos_m, neg_m, cfg.rpn_batch, 0.5)
+            tgt = encode_boxes(gt[arg[pi]], an[pi], (1.0, 1.0, 1.0, 1.0))
+            bl = F.smooth_l1_loss(dl[i, pi], tgt, beta=1.0 / 9, reduction="none").sum(1)
+            box_loss = box_loss + (bl * pok).sum() / cfg.rpn_batch
+            sel = torch.cat([pi, ni])
+            y = torch.cat([torch.ones_like(pi, dtype=torch.float32), torch.zeros_like(ni, dtype=torch.float32)])
+            w = torch.cat([pok, nok]).float()
+            ce = F.binary_cross_entropy_with_logits(lg[i, sel], y, reduction="none")
+            cls_loss = cls_loss + (ce * w).sum() / cfg.rpn_batch
+        n = max(1, len(targets))
+        return cls_loss / n, box_loss / n
+
+    def _train_static(self, feats_nhwc, dt, logits, deltas, anchors, targets, props, pvalid, images):
+        """The training half of `forward` with fixed shapes: per image `roi_batch` sampled RoIs (a quarter of them
+        foreground slots, unused slots masked out of the losses) and `roi_batch * roi_fg_fraction` mask RoIs."""
+        cfg = self.cfg
+        dev = images.device
+        rpn_cls, rpn_box = self._rpn_loss_static(logits, deltas, anchors, targets)
+        gt_all = torch.cat([t["boxes"].float() for t in targets], 0)
+        counts = [t["boxes"].shape[0] for t in targets]
+        offs = [0]
+        for c in counts:
+            offs.append(offs[-1] + c)
+        gt_off = torch.tensor(offs, device=dev, dtype=torch.int32)
+        all_labels = torch.cat([tt["labels"] for tt in targets]) if offs[-1] else torch.zeros(0, dtype=torch.long, device=dev)
+        rois, labels, weights, reg_t, fgw, m_rois, m_tgt, m_lbl, m_w = [], [], [], [], [], [], [], [], []
+        for i, t in enumerate(targets):
+            p = torch.cat([props[i], t["boxes"].float()], 0)                      # gt boxes join the proposals
+            valid = torch.cat([pvalid[i], torch.ones(counts[i], dtype=torch.bool, device=dev)])
+            pb = torch.full((p.shape[0],), i, device=dev, dtype=torch.int32)
+            if counts[i]:
+                iou, idx = D.match_proposals(p, pb, gt_all, gt_off)
+            else:
+                iou, idx = p.new_zeros(p.shape[0]), torch.zeros(p.shape[0], dtype=torch.int32, device=dev)
+            fi, fok, bi, bok = _sample_static(valid & (iou >= cfg.roi_fg_iou), valid & (iou < cfg.roi_fg_iou),
+                                              cfg.roi_batch, cfg.roi_fg_fraction)
+            sel = torch.cat([fi, bi])
+            ok = torch.cat([fok, bok])
+            gidx = idx[fi].long().clamp(min=0)
+            lab = torch.zeros(sel.numel(), dtype=torch.long, device=dev)
+            if offs[-1]:
+                lab[:fi.numel()] = torch.where(fok, all_labels[gidx.clamp(max=offs[-1] - 1)], torch.zeros_like(gidx))
+            rois.append(torch.cat([pb[sel].float()[:, None], p[sel]], 1))
+            labels.append(lab)
+            weights.append(ok.float())
+            reg = torch.zeros(sel.numel(), 4, device=dev)
+            if offs[-1]:
+                reg[:fi.numel()] = encode_boxes(gt_all[gidx.clamp(max=offs[-1] - 1)], p[fi], cfg.box_weights)
+            reg_t.append(reg)
+            fgw.append(torch.cat([fok.float(), torch.zeros(bi.numel(), device=dev)]))
+            if cfg.mode_mask and counts[i]:
+                m_rois.append(torch.cat([pb[fi].float()[:, None], p[fi]], 1))
+                local = (gidx - offs[i]).clamp(0, counts[i] - 1)
+                m_tgt.append(D.mask_crop(t["masks"], p[fi], local.int(), cfg.mask_res))
+                m_lbl.append(all_labels[gidx.clamp(max=offs[-1] - 1)])
+                m_w.append(fok.float())
+        rois, labels, weights, reg_t, fgw = (torch.cat(v) for v in (rois, labels, weights, reg_t, fgw))
+        box_feat = self._roi_feats(feats_nhwc, rois, 7).permute(0, 3, 1, 2).flatten(1).to(dt)
+        cls_logits, box_reg = self.box_head(box_feat)
+        denom = weights.sum().clamp(min=1.0)
+        loss_cls = (F.cross_entropy(cls_logits, labels, reduction="none") * weights).sum() / denom
+        br = box_reg.view(-1, cfg.num_classes, 4)[torch.arange(labels.numel(), device=dev), labels]
+        loss_box = (F.smooth_l1_loss(br, reg_t, beta=1.0, reduction="none").sum(1) * fgw).sum() / denom
+        losses = {"rpn_cls": rpn_cls, "rpn_box": rpn_box, "frcnn_cls": loss_cls, "frcnn_box": loss_box}
+        if cfg.mode_mask and m_rois:
+            mr, ml, mw = torch.cat(m_rois), torch.cat(m_lbl), torch.cat(m_w)
+            mfeat = self._roi_feats(feats_nhwc, mr, 14).permute(0, 3, 1, 2).to(dt)
+            mlogits = self.mask_head(mfeat.contiguous(memory_format=torch.channels_last)).float()
+            sel_logits = mlogits[torch.arange(ml.numel(), device=dev), ml]
+            per_roi = F.binary_cross_entropy_with_logits(sel_logits, torch.cat(m_tgt), reduction="none").mean((1, 2))
+            losses["mrcnn"] = (per_roi * mw).sum() / mw.sum().clamp(min=1.0)
+        losses["total"] = sum(losses.values())
+        return losses
+
     # ------------------------------------------------------------- ROI heads
     def _roi_feats(self, feats_nhwc, rois, P):
         scales = [1.0 / s for s in self.strides[:4]]
@@ -239,11 +355,14 @@ class MaskRCNN(nn.Module):
         anchors = make_anchors([f.shape[-2:] for f in feats], self.strides, cfg.anchor_sizes,
                                cfg.anchor_ratios, images.device)
         logits, deltas = self.rpn(feats)
-        proposals = self._proposals(logits, deltas, anchors, img_hw, training)
+        static = training and self.static_shapes
+        proposals = self._proposals(logits, deltas, anchors, img_hw, training, static=static)
         feats_nhwc = [f.permute(0, 2, 3, 1).contiguous() if not f.permute(0, 2, 3, 1).is_contiguous()
                       else f.permute(0, 2, 3, 1) for f in feats]
         feats_nhwc = [f.to(torch.bfloat16) if f.is_cuda else f for f in feats_nhwc]
         dt = feats[0].dtype
+        if static:
+            return self._train_static(feats_nhwc, dt, logits, deltas, anchors, targets, proposals[0], proposals[1], images)
         if training:
             rpn_cls, rpn_box = self._rpn_loss(logits, deltas, anchors, targets)
             rois, labels, reg_t, mask_rois, mask_gt, mask_lbl = [], [], [], [], [], []

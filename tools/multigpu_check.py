@@ -21,6 +21,7 @@ from b200flow.ops import _lib  # noqa: E402
 from b200flow.ops._lib import c_float, c_int, c_ll, ptr, stream_ptr  # noqa: E402
 from b200flow.parallel.groups import ParallelState, init_distributed  # noqa: E402
 
+HALF = _lib.HALF          # bf16, or fp16 when the process runs the fp16 build (B2F_HALF=fp16)
 RESULTS = []
 
 
@@ -105,7 +106,7 @@ def group_allreduce():
             report(f"allreduce_{tag}", rel(g, ref) < tol, err=rel(g, ref))
             if not wire:
                 g.copy_(src)
-                bf = torch.empty(n, device=dev, dtype=torch.bfloat16)
+                bf = torch.empty(n, device=dev, dtype=HALF)
                 torch.cuda.synchronize(); dist.barrier()
                 ar(0, n, 1.0 / world, bf)
                 torch.cuda.synchronize()
@@ -129,7 +130,7 @@ def group_allreduce():
         bus = 2 * (world - 1) / world * m * 4 / 1e9
         report(f"nccl_fp32_allreduce_perf_{label}", True, ms=tn, busbw_gbs=bus / (tn / 1e3), world=world)
     del scratch
-    rb = ref[:25 * (1 << 20) // 4].to(torch.bfloat16)
+    rb = ref[:25 * (1 << 20) // 4].to(HALF)
     tb = timeit(lambda: dist.all_reduce(rb))
     report("nccl_bf16_allreduce_25MB_elements", True, ms=tb, world=world)
 
@@ -148,7 +149,7 @@ def group_zero1_perf():
     per = int(os.environ.get("B2F_ZERO1_PERF_ELEMS", 840 * (1 << 20))) // 1024 * 1024
     n = per * world
     gbuf, pbuf = comm.alloc(n * 4), comm.alloc(n * 2)
-    grads, params = gbuf.view(torch.float32, n), pbuf.view(torch.bfloat16, n)
+    grads, params = gbuf.view(torch.float32, n), pbuf.view(HALF, n)
     grads.normal_(0, 1e-3)
 
     class Opt:   # what FusedZero1.step reads of a Zero1Optimizer
@@ -166,7 +167,7 @@ def group_zero1_perf():
         report(f"zero1_fused_{'multimem' if mm else 'p2p'}_perf", True, ms=t, elems_per_rank=per, world=world,
                multicast=bool(gbuf.multicast_ptr))
     shard = torch.empty(per, device=dev)
-    pshard = torch.empty(per, device=dev, dtype=torch.bfloat16)
+    pshard = torch.empty(per, device=dev, dtype=HALF)
     sq = torch.zeros(1, device=dev)
 
     def nccl_path():
@@ -248,7 +249,7 @@ def group_ulysses():
     world = dist.get_world_size()
     cfg = config_from_preset("llama-tiny", hidden=512, heads=8, kv_heads=4, ffn=1024, layers=2, vocab_size=2048, max_seq=512)
     torch.manual_seed(55)
-    full = GPTModel(cfg, dtype=torch.bfloat16, device=torch.device("cuda")).state_dict()
+    full = GPTModel(cfg, dtype=HALF, device=torch.device("cuda")).state_dict()
     g = torch.Generator().manual_seed(0)
     data = [torch.randint(0, cfg.vocab_size, (2, 513), generator=g) for _ in range(2)]
     batches = [(t[:, :-1].contiguous().cuda(), t[:, 1:].contiguous().cuda()) for t in data]
@@ -286,10 +287,10 @@ def group_fused_gemm():
     for (T, N, K) in [(256 * world, 512, 256), (1024 * world, 768, 1024), (4096, 6144, 4096)]:
         ts = T // world
         torch.manual_seed(7)
-        x_full = torch.randn(T, K, device=dev, dtype=torch.bfloat16)
+        x_full = torch.randn(T, K, device=dev, dtype=HALF)
         torch.manual_seed(100 + rank)
-        w = torch.randn(N, K, device=dev, dtype=torch.bfloat16) * 0.05
-        bias = torch.randn(N, device=dev, dtype=torch.bfloat16)
+        w = torch.randn(N, K, device=dev, dtype=HALF) * 0.05
+        bias = torch.randn(N, device=dev, dtype=HALF)
         for rep in range(3):   # repeated calls exercise slot reuse / epochs
             y, xg = ftp.ag_gemm(x_full[rank * ts:(rank + 1) * ts].contiguous(), w, bias)
             torch.cuda.synchronize()
@@ -302,9 +303,9 @@ def group_fused_gemm():
         report(f"ag_gemm_mn_{T}x{N}x{K}", rel(y, x_full.float() @ w.float().t()) < 2e-2)
         # GEMM -> RS: every rank multiplies its own K-shard; sum over ranks, scatter rows
         torch.manual_seed(200 + rank)
-        xr = torch.randn(T, K, device=dev, dtype=torch.bfloat16)
-        wr = torch.randn(N, K, device=dev, dtype=torch.bfloat16) * 0.05
-        res = torch.randn(ts, N, device=dev, dtype=torch.bfloat16)
+        xr = torch.randn(T, K, device=dev, dtype=HALF)
+        wr = torch.randn(N, K, device=dev, dtype=HALF) * 0.05
+        res = torch.randn(ts, N, device=dev, dtype=HALF)
         part = (xr.float() @ wr.float().t()).contiguous()
         full = part.clone()
         dist.all_reduce(full)
@@ -314,7 +315,7 @@ def group_fused_gemm():
             torch.cuda.synchronize()
             report(f"gemm_rs_{T}x{N}x{K}_r{rep}", rel(ys, ref) < 2e-2, err=rel(ys, ref))
         # K4': GEMM -> all-reduce, the complete matrix on every rank (bias once, residual on top)
-        res_full = torch.randn(T, N, device=dev, dtype=torch.bfloat16)
+        res_full = torch.randn(T, N, device=dev, dtype=HALF)
         dist.broadcast(res_full, src=0)
         bias_rep = bias.clone()                      # a row-parallel bias is the same on every rank
         dist.broadcast(bias_rep, src=0)
@@ -328,11 +329,11 @@ def group_fused_gemm():
         report(f"gemm_ar_mn_{T}x{N}x{K}", rel(ya, full) < 2e-2, err=rel(ya, full))
     T, N, K = 4096, 4096, 4096 // world * 2
     ts = T // world
-    x = torch.randn(T, K, device=dev, dtype=torch.bfloat16)
-    w = torch.randn(N, K, device=dev, dtype=torch.bfloat16)
+    x = torch.randn(T, K, device=dev, dtype=HALF)
+    w = torch.randn(N, K, device=dev, dtype=HALF)
     xs = x[:ts].contiguous()
-    out = torch.empty(ts, N, device=dev, dtype=torch.bfloat16)
-    xgb = torch.empty(T, K, device=dev, dtype=torch.bfloat16)
+    out = torch.empty(ts, N, device=dev, dtype=HALF)
+    xgb = torch.empty(T, K, device=dev, dtype=HALF)
     t_ag = timeit(lambda: ftp.ag_gemm(xs, w))
     def nccl_ag():
         dist.all_gather_into_tensor(xgb, xs)
@@ -365,11 +366,11 @@ def group_moe_ep():
     ep = EPContext(dist.group.WORLD, world, rank, comm)
     E = int(os.environ.get("B2F_CHECK_EXPERTS_PER_RANK", 2)) * world
     torch.manual_seed(31)
-    base = MoELayer(512, 1024, E, ep=ep, dtype=torch.bfloat16, device=dev, fused=False)
-    fused = MoELayer(512, 1024, E, ep=ep, dtype=torch.bfloat16, device=dev, fused=True)
+    base = MoELayer(512, 1024, E, ep=ep, dtype=HALF, device=dev, fused=False)
+    fused = MoELayer(512, 1024, E, ep=ep, dtype=HALF, device=dev, fused=True)
     fused.load_state_dict(base.state_dict())
     torch.manual_seed(50 + rank)
-    x = (torch.randn(2048, 512, device=dev) * 0.5).to(torch.bfloat16)
+    x = (torch.randn(2048, 512, device=dev) * 0.5).to(HALF)
     for rep in range(2):
         xa, xb = x.clone().requires_grad_(), x.clone().requires_grad_()
         ya, yb = base(xa), fused(xb)
@@ -400,8 +401,8 @@ def group_moe_k5():
     E = int(os.environ.get("B2F_CHECK_EXPERTS_PER_RANK", 2)) * world
     H, F, T = 512, 1024, 2048 * max(1, E // 4)
     torch.manual_seed(31)
-    base = MoELayer(H, F, E, ep=ep, dtype=torch.bfloat16, device=dev, fused=False)
-    k5 = MoELayer(H, F, E, ep=ep, dtype=torch.bfloat16, device=dev, fused=True, fp8=True)
+    base = MoELayer(H, F, E, ep=ep, dtype=HALF, device=dev, fused=False)
+    k5 = MoELayer(H, F, E, ep=ep, dtype=HALF, device=dev, fused=True, fp8=True)
     with torch.no_grad():
         base.wg[1] *= 3.0
         base.b1.normal_(0, 0.05)
@@ -410,7 +411,7 @@ def group_moe_k5():
     assert k5._use_k5(torch.empty(T, H, device=dev), k5.capacity(T)), "K5 path not taken"
     for rep in range(3):
         torch.manual_seed(50 + rank + 7 * rep)
-        x = (torch.randn(T, H, device=dev) * 0.5).to(torch.bfloat16)
+        x = (torch.randn(T, H, device=dev) * 0.5).to(HALF)
         xa, xb = x.clone().requires_grad_(), x.clone().requires_grad_()
         ya, yb = base(xa), k5(xb)
         ya.float().square().sum().backward()
@@ -425,8 +426,8 @@ def group_moe_k5():
         base.zero_grad(); k5.zero_grad()
     # BASELINE config 5 shapes: hidden 2048, ffn 8192, 8 x 2048 tokens per rank
     Eb = max(world, 8) if 8 % world == 0 else world
-    big_base = MoELayer(2048, 8192, Eb, ep=ep, dtype=torch.bfloat16, device=dev, fused=True, fp8=True)
-    xx = (torch.randn(16384, 2048, device=dev) * 0.5).to(torch.bfloat16)
+    big_base = MoELayer(2048, 8192, Eb, ep=ep, dtype=HALF, device=dev, fused=True, fp8=True)
+    xx = (torch.randn(16384, 2048, device=dev) * 0.5).to(HALF)
     def run(layer):
         xg = xx.clone().requires_grad_()
         layer(xg).float().sum().backward()

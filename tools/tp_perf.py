@@ -10,6 +10,7 @@ sys.path.insert(0, "/root/repo")
 from tools.multigpu_check import init_distributed, timeit  # noqa: E402
 
 init_distributed("nccl")
+from b200flow.ops import _lib  # noqa: E402
 from b200flow.ops import gemm as G  # noqa: E402
 from b200flow.parallel.fused_tp import FusedTP  # noqa: E402
 
@@ -37,27 +38,27 @@ for c in ctas:
     ftp = FusedTP.create(dist.group.WORLD, rank, world, dev)
     ftp.comm_ctas = c
     for name, kind, N, K, mn in shapes:
-        w = (torch.randn(K, N, device=dev) if mn else torch.randn(N, K, device=dev)).to(torch.bfloat16)
+        w = (torch.randn(K, N, device=dev) if mn else torch.randn(N, K, device=dev)).to(_lib.HALF)
         if kind == "ag":
-            xs = torch.randn(T // world, K, device=dev, dtype=torch.bfloat16)
-            xf = torch.randn(T, K, device=dev, dtype=torch.bfloat16)
+            xs = torch.randn(T // world, K, device=dev, dtype=_lib.HALF)
+            xf = torch.randn(T, K, device=dev, dtype=_lib.HALF)
             t_f = t_of(lambda: ftp.ag_gemm(xs, w, b_mn_major=mn))
             t_g = t_of(lambda: G.gemm(xf, w, b_mn_major=mn))
 
             def nccl():
-                out = torch.empty(T, K, device=dev, dtype=torch.bfloat16)
+                out = torch.empty(T, K, device=dev, dtype=_lib.HALF)
                 dist.all_gather_into_tensor(out, xs)
                 G.gemm(out, w, b_mn_major=mn)
             t_n = t_of(nccl)
             wire = T // world * K * 2 * (world - 1)
         else:
-            x = torch.randn(T, K, device=dev, dtype=torch.bfloat16)
+            x = torch.randn(T, K, device=dev, dtype=_lib.HALF)
             t_f = t_of(lambda: ftp.gemm_rs(x, w, b_mn_major=mn))
             t_g = t_of(lambda: G.gemm(x, w, b_mn_major=mn))
 
             def nccl():
                 y = G.gemm(x, w, b_mn_major=mn)
-                out = torch.empty(T // world, N, device=dev, dtype=torch.bfloat16)
+                out = torch.empty(T // world, N, device=dev, dtype=_lib.HALF)
                 dist.reduce_scatter_tensor(out, y)
             t_n = t_of(nccl)
             wire = T // world * N * 2 * (world - 1)
