@@ -101,6 +101,12 @@ def _sample_static(pos_mask, neg_mask, batch: int, pos_frac: float):
     return pos_idx, pos_ok, neg_idx, neg_ok
 
 
+def _masked(v, ok):
+    """v where `ok` (per row), exact zeros elsewhere - also when v is inf or nan there."""
+    ok = ok.view(-1, *([1] * (v.dim() - 1)))
+    return torch.where(ok, v, torch.zeros_like(v))
+
+
 class RPNHead(nn.Module):
     def __init__(self, c, a):
         super().__init__()
@@ -265,14 +271,15 @@ class MaskRCNN(nn.Module):
                 labels[iou.argmax(0)] = 1
                 pos_m, neg_m = labels == 1, labels == 0
             pi, pok, ni, nok = _sample_static(pos_m, neg_m, cfg.rpn_batch, 0.5)
-            tgt = encode_boxes(gt[arg[pi]], an[pi], (1.0, 1.0, 1.0, 1.0))
+            # unused slots are selected away, not multiplied away: 0 * inf would poison the sum
+            tgt = _masked(encode_boxes(gt[arg[pi]], an[pi], (1.0, 1.0, 1.0, 1.0)), pok)
             bl = F.smooth_l1_loss(dl[i, pi], tgt, beta=1.0 / 9, reduction="none").sum(1)
-            box_loss = box_loss + (bl * pok).sum() / cfg.rpn_batch
+            box_loss = box_loss + _masked(bl, pok).sum() / cfg.rpn_batch
             sel = torch.cat([pi, ni])
             y = torch.cat([torch.ones_like(pi, dtype=torch.float32), torch.zeros_like(ni, dtype=torch.float32)])
             w = torch.cat([pok, nok]).float()
             ce = F.binary_cross_entropy_with_logits(lg[i, sel], y, reduction="none")
-            cls_loss = cls_loss + (ce * w).sum() / cfg.rpn_batch
+            cls_loss = cls_loss + _masked(ce, w > 0).sum() / cfg.rpn_batch
         n = max(1, len(targets))
         return cls_loss / n, box_loss / n
 
@@ -311,7 +318,7 @@ class MaskRCNN(nn.Module):
             weights.append(ok.float())
             reg = torch.zeros(sel.numel(), 4, device=dev)
             if offs[-1]:
-                reg[:fi.numel()] = encode_boxes(gt_all[gidx.clamp(max=offs[-1] - 1)], p[fi], cfg.box_weights)
+                reg[:fi.numel()] = _masked(encode_boxes(gt_all[gidx.clamp(max=offs[-1] - 1)], p[fi], cfg.box_weights), fok)
             reg_t.append(reg)
             fgw.append(torch.cat([fok.float(), torch.zeros(bi.numel(), device=dev)]))
             if cfg.mode_mask and counts[i]:
@@ -324,9 +331,9 @@ class MaskRCNN(nn.Module):
         box_feat = self._roi_feats(feats_nhwc, rois, 7).permute(0, 3, 1, 2).flatten(1).to(dt)
         cls_logits, box_reg = self.box_head(box_feat)
         denom = weights.sum().clamp(min=1.0)
-        loss_cls = (F.cross_entropy(cls_logits, labels, reduction="none") * weights).sum() / denom
+        loss_cls = _masked(F.cross_entropy(cls_logits, labels, reduction="none"), weights > 0).sum() / denom
         br = box_reg.view(-1, cfg.num_classes, 4)[torch.arange(labels.numel(), device=dev), labels]
-        loss_box = (F.smooth_l1_loss(br, reg_t, beta=1.0, reduction="none").sum(1) * fgw).sum() / denom
+        loss_box = _masked(F.smooth_l1_loss(br, reg_t, beta=1.0, reduction="none").sum(1), fgw > 0).sum() / denom
         losses = {"rpn_cls": rpn_cls, "rpn_box": rpn_box, "frcnn_cls": loss_cls, "frcnn_box": loss_box}
         if cfg.mode_mask and m_rois:
             mr, ml, mw = torch.cat(m_rois), torch.cat(m_lbl), torch.cat(m_w)
@@ -334,7 +341,7 @@ class MaskRCNN(nn.Module):
             mlogits = self.mask_head(mfeat.contiguous(memory_format=torch.channels_last)).float()
             sel_logits = mlogits[torch.arange(ml.numel(), device=dev), ml]
             per_roi = F.binary_cross_entropy_with_logits(sel_logits, torch.cat(m_tgt), reduction="none").mean((1, 2))
-            losses["mrcnn"] = (per_roi * mw).sum() / mw.sum().clamp(min=1.0)
+            losses["mrcnn"] = _masked(per_roi, mw > 0).sum() / mw.sum().clamp(min=1.0)
         losses["total"] = sum(losses.values())
         return losses
 

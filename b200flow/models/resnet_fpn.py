@@ -18,13 +18,19 @@ import torch.nn.functional as F
 from torch import nn
 
 
+# Random initialisation only (a backbone checkpoint overwrites every buffer): with the statistics frozen at identity
+# nothing re-normalises the residual stream, so the last scale of every block starts small and the activation variance
+# grows by (1 + RESIDUAL_GAIN^2) per block instead of doubling.
+RESIDUAL_GAIN = 0.25
+
+
 class ConvW(nn.Module):
     """A convolution's weight plus its geometry (the normalisation that follows it owns the bias)."""
 
     def __init__(self, cin, cout, k, stride=1, padding=0):
         super().__init__()
         self.weight = nn.Parameter(torch.empty(cout, cin, k, k))
-        nn.init.kaiming_normal_(self.weight, mode="fan_out", nonlinearity="relu")
+        nn.init.kaiming_normal_(self.weight, mode="fan_in", nonlinearity="relu")   # variance-preserving under ReLU
         self.stride, self.padding = stride, padding
 
 
@@ -76,6 +82,7 @@ class Bottleneck(nn.Module):
         self.conv1, self.bn1 = ConvW(cin, planes, 1), FrozenBN(planes)
         self.conv2, self.bn2 = ConvW(planes, planes, 3, stride, 1), FrozenBN(planes)       # stride on the 3x3 (v1.5)
         self.conv3, self.bn3 = ConvW(planes, planes * 4, 1), FrozenBN(planes * 4)
+        self.bn3.weight.fill_(RESIDUAL_GAIN)
         self.downsample = None
         if downsample:
             self.downsample = nn.Sequential(ConvW(cin, planes * 4, 1, stride), FrozenBN(planes * 4))
@@ -95,6 +102,7 @@ class BasicBlock(nn.Module):
         super().__init__()
         self.conv1, self.bn1 = ConvW(cin, planes, 3, stride, 1), FrozenBN(planes)
         self.conv2, self.bn2 = ConvW(planes, planes, 3, 1, 1), FrozenBN(planes)
+        self.bn2.weight.fill_(RESIDUAL_GAIN)
         self.downsample = None
         if downsample:
             self.downsample = nn.Sequential(ConvW(cin, planes, 1, stride), FrozenBN(planes))

@@ -53,7 +53,7 @@ def run_maskrcnn_bench(args, rank, world, dev, ClockSampler, emit=None):
         if ddp is not None:
             ddp.finish_reduction()
         opt.step()
-        return float(losses["total"]) if read_loss else losses["total"]
+        return float(losses["total"].detach()) if read_loss else losses["total"]
 
     def barrier():
         if world > 1:
@@ -73,10 +73,10 @@ def run_maskrcnn_bench(args, rank, world, dev, ClockSampler, emit=None):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t)
 
-    first = None
+    first = after_warmup = None
     for _ in range(args.warmup):
-        l = step(devb, True)
-        first = first if first is not None else l
+        after_warmup = step(devb, True)
+        first = first if first is not None else after_warmup
     _lib.reset_launch_count()
     with ClockSampler(torch.cuda.current_device()) as clocks:
         ms = timed(lambda: step(devb, False), args.steps)
@@ -97,7 +97,8 @@ def run_maskrcnn_bench(args, rank, world, dev, ClockSampler, emit=None):
             "clocks": clocks.summary(),
             "e2e": {"value": gb * args.steps / (ms_e2e / 1e3), "unit": "images/s",
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
-            "gpu_launches": launches, "loss_first_last": [first, last],
+            "gpu_launches": launches, "loss_first_last": [first, last], "loss_after_warmup": after_warmup,
+            **({} if (last == last and abs(last) < 1e4) else {"invalid": "training diverged: the loss is not finite"}),
             "native_libs": _lib.loaded_libraries()})
     if world > 1:
         dist.destroy_process_group()

@@ -209,3 +209,41 @@ def test_reference_mpijob_values_files_run_unchanged(tmp_root, values, expect):
         (tmp_root / "efs/home/w/logs").rglob("config.json")) else None
     if cfg is not None:
         assert int(cfg["config"].get("TRAIN.BATCH_SIZE_PER_GPU", 1)) == expect["batch"] and cfg["world"] == 2
+
+
+def test_fixed_shape_losses_stay_finite_with_unused_slots():
+    """Unused sampler slots may hold degenerate boxes (zero width -> inf / nan box targets); they must be selected out
+    of the losses, not multiplied by zero, and a randomly initialised backbone must start near the chance losses."""
+    import torch
+
+    from b200flow.data.synthetic import coco_like
+    from b200flow.models import maskrcnn as M
+    from b200flow.optim import FlatMomentumSGD
+    from b200flow.utils.flat import FlatParams
+
+    assert float(M._masked(torch.tensor([float("nan"), float("inf"), 2.0]), torch.tensor([False, False, True])).sum()) == 2.0
+    a = torch.tensor([[5.0, 5.0, 5.0, 5.0]])                       # a zero-size proposal
+    bad = M.encode_boxes(torch.tensor([[0.0, 0.0, 4.0, 4.0]]), a, (1.0, 1.0, 1.0, 1.0))
+    assert not torch.isfinite(bad).all()
+    assert torch.equal(M._masked(bad, torch.tensor([False])), torch.zeros(1, 4))
+
+    torch.manual_seed(0)
+    model = M.MaskRCNN(M.MaskRCNNConfig(width=0.25))
+    model.static_shapes = True
+    flat = FlatParams(model)
+    opt = FlatMomentumSGD(flat, lr=0.005, momentum=0.9, weight_decay=1e-4)
+    model.train()
+    data = coco_like(10 ** 9, 128, 160, seed=3, device="cpu")
+    totals = []
+    for _ in range(4):
+        s = [next(data) for _ in range(2)]
+        im = torch.stack([x["image"] for x in s])
+        tg = [{k: x[k] for k in ("boxes", "labels", "masks")} for x in s]
+        opt.zero_grad()
+        losses = model(im, tg)
+        losses["total"].backward()
+        flat.collect_autograd_grads()
+        opt.step()
+        assert all(torch.isfinite(v) for v in losses.values()), losses
+        totals.append(float(losses["total"].detach()))
+    assert totals[0] < 12.0, totals          # ln(81) + ln 2 + ln 2 + box terms; the old initialisation started at 20-40
