@@ -58,6 +58,22 @@ def quantize_mx(x: torch.Tensor) -> MxTensor:
     return MxTensor(q, sf)
 
 
+def quantize_mx_t(x: torch.Tensor) -> MxTensor:
+    """MX copy of x^T in one pass: x [N, K] or [B, N, K] -> MxTensor with rows K, contracting over N
+    (N a multiple of 128).  Same bits as `quantize_mx(x.transpose(-1, -2).contiguous())` without the copy."""
+    _lib.require_cuda(x)
+    assert x.dtype == _lib.HALF and x.dim() in (2, 3) and x.stride(-1) == 1
+    batch = x.shape[0] if x.dim() == 3 else 1
+    N, K = x.shape[-2], x.shape[-1]
+    assert N % 128 == 0 and K % 8 == 0, "transposed MX quantisation needs N % 128 == 0 and K % 8 == 0"
+    lead = (batch,) if x.dim() == 3 else ()
+    q = torch.empty(lead + (K, N), dtype=torch.uint8, device=x.device)
+    sf = torch.zeros(lead + (N // 128, sf_atoms(K), 512), dtype=torch.uint8, device=x.device)
+    _lib.call("b2f_quantize_mx_t", ptr(x), ptr(q), ptr(sf), c_int(N), c_int(K), c_ll(x.stride(-2)), c_int(batch),
+              c_ll(x.stride(0) if x.dim() == 3 else 0), stream_ptr())
+    return MxTensor(q, sf)
+
+
 def dequantize_mx(t: MxTensor) -> torch.Tensor:
     y = torch.empty(t.q.shape, dtype=_lib.HALF, device=t.q.device)
     R, K = t.rows, t.k

@@ -81,8 +81,7 @@ class FusedMoE:
         key = (id(w), transpose)
         hit = self._wq.get(key) if self.cache_weights else None
         if hit is None:
-            src = w.detach().transpose(1, 2).contiguous() if transpose else w.detach()
-            hit = MX.quantize_mx(src)
+            hit = MX.quantize_mx_t(w.detach()) if transpose else MX.quantize_mx(w.detach())
             if self.cache_weights:
                 self._wq[key] = hit
         return hit

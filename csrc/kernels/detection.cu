@@ -60,6 +60,15 @@ __device__ __forceinline__ Taps bilinear_taps(float y, float x, int H, int W) {
   return t;
 }
 
+// p[0..8) += g[0..8) * w as two 16-byte reductions (REDG.ADD.F32x4): a quarter of the atomic operations of the
+// scalar form; p is 32-byte aligned (8-channel groups of an NHWC fp32 buffer).
+__device__ __forceinline__ void red_add8(float* p, const float (&g)[8], float w) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(g[0] * w), "f"(g[1] * w),
+               "f"(g[2] * w), "f"(g[3] * w) : "memory");
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p + 4), "f"(g[4] * w), "f"(g[5] * w),
+               "f"(g[6] * w), "f"(g[7] * w) : "memory");
+}
+
 // rois: [R, 5] = (batch, x1, y1, x2, y2) in image coordinates. out: [R, P, P, C] bf16 (NHWC).
 // One thread = one (roi, ph, pw, 8-channel group).  `aligned`: half-pixel shift.
 template <bool BWD>
@@ -114,13 +123,10 @@ roi_align_kernel(Pyramid pyr, const float* __restrict__ rois, int R, int P, int 
             acc[j] += tp.w00 * v00[j] + tp.w01 * v01[j] + tp.w10 * v10[j] + tp.w11 * v11[j];
         } else {
           float* gb = pyr.grad[lv] + (long long)b * H * W * C + c8 * 8;
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            atomicAdd(gb + ((long long)tp.y0 * W + tp.x0) * C + j, g[j] * tp.w00);
-            atomicAdd(gb + ((long long)tp.y0 * W + tp.x1) * C + j, g[j] * tp.w01);
-            atomicAdd(gb + ((long long)tp.y1 * W + tp.x0) * C + j, g[j] * tp.w10);
-            atomicAdd(gb + ((long long)tp.y1 * W + tp.x1) * C + j, g[j] * tp.w11);
-          }
+          red_add8(gb + ((long long)tp.y0 * W + tp.x0) * C, g, tp.w00);
+          red_add8(gb + ((long long)tp.y0 * W + tp.x1) * C, g, tp.w01);
+          red_add8(gb + ((long long)tp.y1 * W + tp.x0) * C, g, tp.w10);
+          red_add8(gb + ((long long)tp.y1 * W + tp.x1) * C, g, tp.w11);
         }
       }
     }

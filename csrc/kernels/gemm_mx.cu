@@ -59,6 +59,53 @@ quantize_mx_kernel(const __nv_bfloat16* __restrict__ x, uint8_t* __restrict__ q,
   }
 }
 
+// MX copy of the TRANSPOSE of x: x is [batch][N, K] (K contiguous), the output has rows k and contracts over n -
+// q [batch][K, N] bytes, scales for (K rows, N deep).  The backward GEMMs of the expert FFNs multiply by W^T; this
+// replaces a strided transpose copy followed by the row quantiser.  One CTA owns a 128 (n) x 128 (k) tile: it goes
+// through shared memory once, every thread then owns output row k = tid % 128 and two of the four 32-wide n groups.
+constexpr int QT_TILE = 128;
+constexpr int QT_PITCH = QT_TILE + 8;      // bf16 elements; 272 B rows keep the 16-byte stores aligned
+__global__ void __launch_bounds__(256)
+quantize_mx_t_kernel(const __nv_bfloat16* __restrict__ x, uint8_t* __restrict__ q, uint8_t* __restrict__ sf,
+                     int N, int K, long long ldx, int atoms, long long x_batch, long long q_batch,
+                     long long sf_batch) {
+  __shared__ __align__(16) __nv_bfloat16 tile[QT_TILE * QT_PITCH];
+  const int k0 = blockIdx.x * QT_TILE, n0 = blockIdx.y * QT_TILE, b = blockIdx.z;
+  const __nv_bfloat16* xb = x + b * x_batch;
+  const int c8 = (threadIdx.x & 15) * 8;                      // 8 consecutive k per 16-byte load
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int n = (threadIdx.x >> 4) + 16 * i;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (k0 + c8 < K) v = ld_nc_v4(reinterpret_cast<const uint4*>(xb + (long long)(n0 + n) * ldx + k0 + c8));
+    *reinterpret_cast<uint4*>(&tile[n * QT_PITCH + c8]) = v;
+  }
+  __syncthreads();
+  const int r = threadIdx.x & 127;
+  if (k0 + r >= K) return;
+#pragma unroll
+  for (int gg = 0; gg < 2; ++gg) {
+    const int g = (threadIdx.x >> 7) * 2 + gg;
+    float v[32];
+    float amax = 0.f;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      v[j] = __bfloat162float(tile[(g * 32 + j) * QT_PITCH + r]);
+      amax = fmaxf(amax, fabsf(v[j]));
+    }
+    float inv;
+    const uint32_t e = ue8m0_scale(amax, inv);
+    uint32_t o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      o[j] = cvt_e4m3x2(v[j * 4] * inv, v[j * 4 + 1] * inv) | (cvt_e4m3x2(v[j * 4 + 2] * inv, v[j * 4 + 3] * inv) << 16);
+    uint4* dst = reinterpret_cast<uint4*>(q + b * q_batch + (long long)(k0 + r) * N + n0 + g * 32);
+    dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+    dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+    sf[b * sf_batch + sf_offset(k0 + r, n0 >> 7, g, atoms)] = (uint8_t)e;
+  }
+}
+
 // e4m3 bytes + atom-layout scales -> bf16 (the bf16 wgrad GEMMs and the tests read quantised operands back).
 __global__ void __launch_bounds__(256)
 dequantize_mx_kernel(const uint8_t* __restrict__ q, const uint8_t* __restrict__ sf, __nv_bfloat16* __restrict__ y,
@@ -120,6 +167,20 @@ extern "C" int b2f_quantize_mx(const void* x, void* q, void* sf, int rows, int K
   quantize_mx_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(x), static_cast<uint8_t*>(q), static_cast<uint8_t*>(sf), rows, K, ldx,
       atoms, batch, x_batch, (long long)rows * K, b2f_mx_sf_bytes(rows, K));
+  B2F_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// x [batch][N, K] -> MX of x^T: q [batch][K, N], scales of (K rows, N deep).  N % 128 == 0, K % 8 == 0.
+extern "C" int b2f_quantize_mx_t(const void* x, void* q, void* sf, int N, int K, long long ldx, int batch,
+                                 long long x_batch, void* stream) {
+  B2F_REQUIRE(N > 0 && K > 0 && N % 128 == 0 && K % 8 == 0 && ldx % 8 == 0 && batch > 0 && batch < 65536,
+              "quantize_mx_t: N must be a multiple of 128, K and the row pitch of 8");
+  const int atoms = b2f_mx_sf_atoms(K);
+  dim3 grid((K + QT_TILE - 1) / QT_TILE, N / QT_TILE, batch);
+  quantize_mx_t_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<uint8_t*>(q), static_cast<uint8_t*>(sf), N, K, ldx, atoms,
+      x_batch, (long long)N * K, b2f_mx_sf_bytes(K, N));
   B2F_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

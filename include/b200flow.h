@@ -139,6 +139,23 @@ int b2f_attn_bwd(const void* q, const void* k, const void* v, const void* o, con
                  long long dv_ts, long long dv_bs, float scale, int causal, const int* kv_lens,
                  void* stream);
 
+/* The same kernels with attention dropout (Megatron `--attention-dropout`, GPT-2 345M values files:
+ * examples/megatron-deepspeed/gpt2_345m/pretrain-ddp-zero1.yaml).  The keep mask is a counter-based hash of
+ * (seed, batch*head, query, key): no mask tensor is stored, forward and both backward kernels regenerate the same
+ * bits; kept probabilities are scaled by 1 / (1 - p_drop). */
+int b2f_attn_fwd_drop(const void* q, const void* k, const void* v, void* o, float* lse, int B, int S,
+                      int H, int HKV, int D, long long q_ts, long long q_bs, long long k_ts,
+                      long long k_bs, long long v_ts, long long v_bs, long long o_ts, long long o_bs,
+                      float scale, int causal, const int* kv_lens, float p_drop, unsigned seed,
+                      void* stream);
+int b2f_attn_bwd_drop(const void* q, const void* k, const void* v, const void* o, const void* d_o,
+                      const float* lse, float* delta, void* dq, void* dk, void* dv, int B, int S,
+                      int H, int HKV, int D, long long q_ts, long long q_bs, long long k_ts,
+                      long long k_bs, long long v_ts, long long v_bs, long long o_ts, long long o_bs,
+                      long long do_ts, long long do_bs, long long dq_ts, long long dq_bs,
+                      long long dk_ts, long long dk_bs, long long dv_ts, long long dv_bs, float scale,
+                      int causal, const int* kv_lens, float p_drop, unsigned seed, void* stream);
+
 /* ---- K1 / K2: gradient collectives over NVLink peer memory, fused with scale / Adam
  * (torch DDP Reducer + NCCL, Horovod fusion buffer, DeepSpeed ZeRO-1 phases).
  * *_ptrs: host arrays of `world` device addresses of the same symmetric buffer on every
@@ -155,6 +172,24 @@ int b2f_zero1_adam_gather(const float* reduced, float* master, float* m, float* 
                           int world, long long lo, long long n, float lr, float beta1, float beta2,
                           float eps, float weight_decay, int step, const float* grad_scale,
                           const int* skip, int blocks, unsigned epoch, void* stream);
+/* K1 with half-precision on the wire: the fp32 bucket is cast into a symmetric staging buffer, reduced there
+ * (multimem.ld_reduce when stage_multicast_ptr != 0, peer loads otherwise) and written back as fp32 * scale
+ * (torch DDP `bf16_compress_hook`; NCCL moves half the bytes). */
+int b2f_allreduce_bf16wire(void* grads, const long long* stage_ptrs, long long stage_multicast_ptr,
+                           const long long* flags_ptrs, int rank, int world, long long off, long long n,
+                           float scale, int blocks, unsigned epoch, void* stream);
+/* K2 through the switch: *_multicast_ptr != 0 reduces with multimem.ld_reduce and publishes the updated
+ * half-precision shard with multimem.st; 0 falls back to the peer-pointer loops of the entry points above. */
+int b2f_zero1_reduce_mc(const long long* grads_ptrs, long long grads_multicast_ptr,
+                        const long long* flags_ptrs, int rank, int world, long long lo, long long n,
+                        float* reduced, float* partial, float* sumsq_out, int blocks, unsigned epoch,
+                        void* stream);
+int b2f_zero1_adam_gather_mc(const float* reduced, float* master, float* m, float* v,
+                             const long long* params_ptrs, long long params_multicast_ptr,
+                             const long long* flags_ptrs, int rank, int world, long long lo, long long n,
+                             float lr, float beta1, float beta2, float eps, float weight_decay, int step,
+                             const float* grad_scale, const int* skip, int blocks, unsigned epoch,
+                             void* stream);
 int b2f_peer_barrier(const long long* flags_ptrs, int rank, int world, unsigned epoch, void* stream);
 int b2f_peer_sum_test(const long long* buf_ptrs, const long long* flags_ptrs, int rank, int world,
                       long long n, float* out, int blocks, unsigned epoch, void* stream);
@@ -221,6 +256,94 @@ int b2f_moe_combine(const void* src_local, const long long* peer_ptrs, int world
                     const float* gate, int T, int H, int capacity, void* y, void* stream);
 int b2f_moe_gate_grad(const void* rows, const int* expert, const int* slot, const void* dy, int T,
                       int H, int capacity, float* dgate, void* stream);
+
+/* ---- Block-scaled fp8 (MXFP8): e4m3 values with one UE8M0 scale per 32 elements along K, multiplied by
+ * tcgen05.mma kind::mxf8f6f4.block_scale with the scale factors in TMEM (Transformer Engine MXFP8 recipe;
+ * DeepSpeed-MoE expert GEMMs of examples/megatron-deepspeed/gpt2_moe/).
+ * Scale-factor layout ("atoms"): sf[k/128][row/128][512 B], byte (row%32)*16 + ((row%128)/32)*4 + (k%128)/32;
+ * rows are padded to 128 and K to 128 (b2f_mx_sf_bytes). */
+int b2f_mx_sf_atoms(int rows);
+long long b2f_mx_sf_bytes(int rows, int K);
+int b2f_quantize_mx(const void* x, void* q, void* sf, int rows, int K, long long ldx, int batch,
+                    long long x_batch, void* stream);
+/* x [N, K] -> MX copy of x^T (rows K, contracting over N; N % 128 == 0) without materialising the transpose. */
+int b2f_quantize_mx_t(const void* x, void* q, void* sf, int N, int K, long long ldx, int batch,
+                      long long x_batch, void* stream);
+int b2f_dequantize_mx(const void* q, const void* sf, void* y, int rows, int K, long long ldy, int batch,
+                      long long y_batch, void* stream);
+/* C[b] = epilogue(A[b] B[b]^T): A [M, K], B [N, K] quantised as above; flags as b2f_gemm_bf16. */
+int b2f_gemm_mx(const void* Aq, const void* sfa, const void* Bq, const void* sfb, void* C, int M, int N,
+                int K, int batch, long long ldc, long long strideC, const void* bias, long long bias_batch,
+                const void* residual, long long ldr, long long strideR, void* aux, long long ldaux,
+                long long strideAux, int flags, void* stream);
+
+/* ---- K5: the expert FFN of an expert-parallel MoE layer as two fused kernels per direction
+ * (DeepSpeed MOELayer: all_to_all -> experts -> all_to_all, three NCCL / cuBLAS phases upstream).
+ *   up:   tokens leave as e4m3 + scales into the owners' symmetric buffers (bulk stores over NVLink) and the owner's
+ *         GEMM 1 starts on a 128-row unit as soon as its flag shows the epoch; epilogue + bias, keep, GELU
+ *         (backward: x gelu'(pre)), requantise for GEMM 2.
+ *   down: GEMM 2, epilogue + bias, rows stored straight into the source rank's home buffer; a release counter per
+ *         source tells it when all of its rows have landed (b2f_moe_wait_rows).
+ * C % 128 == 0, H % 512 == 0.  *_ptrs: `world` addresses of the same symmetric buffer on every rank. */
+int b2f_moe_token_of(const int* expert, const int* slot, int T, int C, int* token_of, void* stream);
+int b2f_moe_up(const void* x, const int* token_of, const int* counts, int T, int H, int E, int C,
+               const long long* xq_ptrs, const long long* xsf_ptrs, const long long* flag_ptrs,
+               const long long* cnt_ptrs, const void* Wq, const void* wsf, int N, const void* bias,
+               void* keep, const void* pre, void* hq, void* hsf, int backward, int rank, int world,
+               unsigned epoch, void* stream);
+int b2f_moe_down(const void* hq, const void* hsf, const void* Wq, const void* wsf, int K, int N,
+                 const void* bias, const long long* rows_ptrs, const long long* done_ptrs,
+                 const void* my_cnt, int E, int C, int rank, int world, unsigned epoch, void* stream);
+int b2f_moe_wait_rows(const void* done, const int* counts, int E, int N, void* stream);
+int b2f_moe_zero_inactive(void* buf, const void* my_cnt, int El, int world, int C, int N, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+
+/* ======================= host runtime: libb200flow_host.so ========================================
+ * C++ (no CUDA) pieces of the runtime, loaded by b200flow/ops/_lib.py the same way. */
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Gradient bucket planning and the ready-order bookkeeping of DDP (torch Reducer, Horovod fusion buffer).
+ * plan rows: {first_slot, last_slot, elem_lo, elem_hi}.  `mark` returns the next bucket that may launch
+ * (buckets launch strictly in index order on every rank) or -1; `next_ready` continues after a launch. */
+int b2f_plan_buckets(const int64_t* offsets, const int64_t* numels, int nslots, int64_t total_elems,
+                     int64_t elem_bytes, int64_t cap_bytes, int64_t first_cap_bytes, int64_t* out,
+                     int max_buckets);
+void* b2f_reducer_create(const int64_t* plan, int nb, int nslots, const int32_t* uses);
+void b2f_reducer_destroy(void* h);
+void b2f_reducer_reset(void* h);
+int b2f_reducer_num_buckets(void* h);
+int b2f_reducer_mark(void* h, int slot);
+int b2f_reducer_next_ready(void* h);
+int b2f_reducer_next_unlaunched(void* h);
+
+/* Megatron dataset index builders (megatron/data/helpers.cpp, compiled by `make` in the reference image:
+ * containers/megatron-deepspeed/Dockerfile). */
+void b2f_build_doc_idx(int32_t* out, const int32_t* documents, long long num_docs, int32_t num_epochs,
+                       uint64_t seed);
+long long b2f_build_sample_idx(const int32_t* sizes, const int32_t* doc_idx, long long doc_idx_len,
+                               int32_t seq_length, long long num_samples, int64_t* sample_idx);
+void b2f_build_shuffle_idx(int64_t* out, long long n, uint64_t seed);
+void b2f_build_blending_indices(uint8_t* dataset_index, int64_t* dataset_sample_index,
+                                const double* weights, int32_t num_datasets, long long size);
+long long b2f_build_bert_mapping(const int64_t* docs, long long num_docs, const int32_t* sizes,
+                                 int32_t num_epochs, long long max_num_samples, int32_t max_seq_length,
+                                 double short_seq_prob, uint64_t seed, int32_t min_num_sent,
+                                 int32_t long_sentence_len, int64_t* maps);
+
+/* Shared-memory message channel between data-loader workers and the trainer (torch DataLoader's
+ * shared-memory queues / tensorpack's ZMQ pipes). */
+void* b2f_chan_create(const char* name, uint64_t capacity);
+void* b2f_chan_open(const char* name);
+int b2f_chan_send(void* ch, const void* buf, uint32_t len, long timeout_ms);
+long long b2f_chan_recv(void* ch, void* buf, uint32_t buf_len, long timeout_ms, uint32_t* need_out);
+void b2f_chan_close(void* ch);
+void b2f_chan_free(void* ch);
 
 #ifdef __cplusplus
 }

@@ -881,6 +881,21 @@ def group_mx():
                       "tflops": 2 * 4096 * 8192 * 2048 / ms / 1e9}), flush=True)
     ms = timeit(lambda: MX.quantize_mx(a))
     print(json.dumps({"name": "mx_quantize_4096x2048", "ms": ms, "gbs": 4096 * 2048 * 3 / ms / 1e6}), flush=True)
+    # transposed quantiser: the same bytes and scales as transpose-copy + row quantiser, without the copy
+    for shape in [(256, 384), (3, 384, 200), (8, 2048, 8192)]:
+        w = (torch.randn(*shape, device=DEV) * 0.05).to(HALF)
+        t1 = MX.quantize_mx_t(w)
+        t0 = MX.quantize_mx(w.transpose(-1, -2).contiguous())
+        same = bool(torch.equal(t1.q, t0.q)) and bool(torch.equal(t1.sf, t0.sf))
+        rec = {"name": f"mx_quantize_t_{'x'.join(map(str, shape))}", "ok": same,
+               "q_mismatch": int((t1.q != t0.q).sum()), "sf_mismatch": int((t1.sf != t0.sf).sum())}
+        RESULTS.append(rec)
+        print(json.dumps(rec), flush=True)
+    w = (torch.randn(8, 2048, 8192, device=DEV) * 0.05).to(HALF)
+    ms_t = timeit(lambda: MX.quantize_mx_t(w))
+    ms_c = timeit(lambda: MX.quantize_mx(w.transpose(1, 2).contiguous()))
+    print(json.dumps({"name": "mx_quantize_t_perf_8x2048x8192", "ms": ms_t, "ms_transpose_copy_then_quantize": ms_c,
+                      "gbs": w.numel() * 3 / ms_t / 1e6}), flush=True)
 
 
 GROUPS = {
