@@ -301,6 +301,26 @@ __device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
   asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
   return d;
 }
+// 2^x for two values on the FMA pipe instead of the special-function unit (16 ex2 per clock per SM is the scarce
+// resource of a softmax over 128-wide tiles): x = n + f with n = round(x) taken from the mantissa of x + 1.5 * 2^23,
+// 2^f on [-0.5, 0.5] by a cubic (relative error 7.5e-5, far below the bf16 rounding of the probabilities), and n added
+// into the exponent field.  x is clamped at -125, where the result (2^-125) stands in for zero.
+__device__ __forceinline__ void ex2_poly2(uint64_t t, float& p0, float& p1) {
+  float x0, x1;
+  f2unpack(t, x0, x1);
+  const uint64_t x = f2pack(fmaxf(x0, -125.f), fmaxf(x1, -125.f));
+  const uint64_t tt = add2(x, f2pack(12582912.f, 12582912.f));
+  const uint64_t r = add2(tt, f2pack(-12582912.f, -12582912.f));
+  const uint64_t f = fma2(r, f2pack(-1.f, -1.f), x);
+  uint64_t q = fma2(f, f2pack(0.05517164617776871f, 0.05517164617776871f), f2pack(0.2426111251115799f, 0.2426111251115799f));
+  q = fma2(q, f, f2pack(0.6932609677314758f, 0.6932609677314758f));
+  q = fma2(q, f, f2pack(0.9999280571937561f, 0.9999280571937561f));
+  float q0, q1, n0, n1;
+  f2unpack(q, q0, q1);
+  f2unpack(tt, n0, n1);
+  p0 = __int_as_float(__float_as_int(q0) + (__float_as_int(n0) << 23));
+  p1 = __int_as_float(__float_as_int(q1) + (__float_as_int(n1) << 23));
+}
 __device__ __forceinline__ ulonglong2 lds_v2_u64(uint32_t saddr) {
   ulonglong2 v;
   asm volatile("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "r"(saddr));

@@ -28,6 +28,8 @@
 // attention core.
 #include <stdlib.h>
 
+#include <type_traits>
+
 #include "../common/ptx.cuh"
 #include "../common/host.h"
 #include "../../include/b200flow.h"
@@ -144,13 +146,17 @@ __device__ unsigned long long g_attn_dbg[16];
 #endif
 constexpr int FWD2_THREADS = 384;  // warpgroup 0: TMA + MMA (+2 idle warps); 1, 2: softmax A, B
 constexpr float RESCALE_THRESHOLD = 8.f;
+constexpr int ATTN_POLY_DEFAULT = 0;   // pairs of four whose exp2 runs on the FMA pipe (B2F_ATTN_POLY overrides)
 
 struct Fwd2Bars {
   uint64_t q_full[2], k_full[2], v_full[2], k_empty[2], v_empty[2], s_full[2], p_full[2], o_full[2];
   uint32_t tmem_base;
 };
 
-template <int D, bool DROP = false>
+// POLY: of every four pairs of probabilities of an unmasked tile, this many take their exp2 on the FMA pipe
+// (ex2_poly2) and the rest on the special-function unit; masked tiles (diagonal, sequence end) use the unit only,
+// so that masked elements stay exact zeros.
+template <int D, bool DROP = false, int POLY = 0>
 __global__ void __launch_bounds__(FWD2_THREADS, 1)
 attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
                  const __grid_constant__ CUtensorMap mv, const AttnParams p) {
@@ -381,25 +387,36 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
       DBG_T(ts2);
       const uint64_t sc2 = f2pack(p.scale_log2, p.scale_log2), nm2 = f2pack(-m, -m);
       uint64_t sum2 = f2pack(0.f, 0.f);
+      auto probabilities = [&](auto mix_tag) {
+        constexpr bool MIX = decltype(mix_tag)::value;
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        uint32_t pk[16];
+        for (int c = 0; c < 4; ++c) {
+          uint32_t pk[16];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          const uint64_t t = fma2(f2pack(__uint_as_float(s[c * 32 + 2 * i]), __uint_as_float(s[c * 32 + 2 * i + 1])), sc2, nm2);
-          float t0, t1;
-          f2unpack(t, t0, t1);
-          float p0 = ex2(t0), p1 = ex2(t1);
-          sum2 = add2(sum2, f2pack(p0, p1));       // the normaliser is the sum of the undropped probabilities
-          if constexpr (DROP) {
-            const uint32_t wd = drop_word(dseed, (kv0 + c * 32 + 2 * i) >> 2) >> ((i & 1) * 16);
-            p0 = (wd & 0xFF) >= p.drop_thr ? p0 : 0.f;
-            p1 = ((wd >> 8) & 0xFF) >= p.drop_thr ? p1 : 0.f;
+          for (int i = 0; i < 16; ++i) {
+            const uint64_t t = fma2(f2pack(__uint_as_float(s[c * 32 + 2 * i]), __uint_as_float(s[c * 32 + 2 * i + 1])), sc2, nm2);
+            float p0, p1;
+            if (MIX && (i & 3) < POLY) {
+              ex2_poly2(t, p0, p1);
+            } else {
+              float t0, t1;
+              f2unpack(t, t0, t1);
+              p0 = ex2(t0);
+              p1 = ex2(t1);
+            }
+            sum2 = add2(sum2, f2pack(p0, p1));       // the normaliser is the sum of the undropped probabilities
+            if constexpr (DROP) {
+              const uint32_t wd = drop_word(dseed, (kv0 + c * 32 + 2 * i) >> 2) >> ((i & 1) * 16);
+              p0 = (wd & 0xFF) >= p.drop_thr ? p0 : 0.f;
+              p1 = ((wd >> 8) & 0xFF) >= p.drop_thr ? p1 : 0.f;
+            }
+            pk[i] = pack_bf16x2(p0, p1);
           }
-          pk[i] = pack_bf16x2(p0, p1);
+          tmem_st_32x32b_x16(T_S + c * 16, pk);
         }
-        tmem_st_32x32b_x16(T_S + c * 16, pk);
-      }
+      };
+      if (POLY > 0 && !need_mask) probabilities(std::true_type{});
+      else probabilities(std::false_type{});
       float sum0, sum1;
       f2unpack(sum2, sum0, sum1);
       l += sum0 + sum1;
@@ -1032,23 +1049,36 @@ static int attn_fwd_impl(const void* q, const void* k, const void* v, void* o, f
   const bool drop = p.drop_thr > 0;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   dim3 grid2(H * B, (S + 2 * TQ - 1) / (2 * TQ), 1);
+  static const int poly = [] { const char* e = getenv("B2F_ATTN_POLY"); return e ? atoi(e) : ATTN_POLY_DEFAULT; }();
   if (D == 128) {
     const int smem = 6 * Cfg<128>::TILE_B + 1024 + sizeof(Fwd2Bars);
     if (drop) {
       if (int rc = set_smem(attn_fwd2_kernel<128, true>, smem)) return rc;
       attn_fwd2_kernel<128, true><<<grid2, FWD2_THREADS, smem, st>>>(mq, mk, mv, p);
-    } else {
+    } else if (poly == 0) {
       if (int rc = set_smem(attn_fwd2_kernel<128>, smem)) return rc;
       attn_fwd2_kernel<128><<<grid2, FWD2_THREADS, smem, st>>>(mq, mk, mv, p);
+    } else if (poly == 1) {
+      if (int rc = set_smem(attn_fwd2_kernel<128, false, 1>, smem)) return rc;
+      attn_fwd2_kernel<128, false, 1><<<grid2, FWD2_THREADS, smem, st>>>(mq, mk, mv, p);
+    } else {
+      if (int rc = set_smem(attn_fwd2_kernel<128, false, 2>, smem)) return rc;
+      attn_fwd2_kernel<128, false, 2><<<grid2, FWD2_THREADS, smem, st>>>(mq, mk, mv, p);
     }
   } else {
     const int smem = 6 * Cfg<64>::TILE_B + 1024 + sizeof(Fwd2Bars);
     if (drop) {
       if (int rc = set_smem(attn_fwd2_kernel<64, true>, smem)) return rc;
       attn_fwd2_kernel<64, true><<<grid2, FWD2_THREADS, smem, st>>>(mq, mk, mv, p);
-    } else {
+    } else if (poly == 0) {
       if (int rc = set_smem(attn_fwd2_kernel<64>, smem)) return rc;
       attn_fwd2_kernel<64><<<grid2, FWD2_THREADS, smem, st>>>(mq, mk, mv, p);
+    } else if (poly == 1) {
+      if (int rc = set_smem(attn_fwd2_kernel<64, false, 1>, smem)) return rc;
+      attn_fwd2_kernel<64, false, 1><<<grid2, FWD2_THREADS, smem, st>>>(mq, mk, mv, p);
+    } else {
+      if (int rc = set_smem(attn_fwd2_kernel<64, false, 2>, smem)) return rc;
+      attn_fwd2_kernel<64, false, 2><<<grid2, FWD2_THREADS, smem, st>>>(mq, mk, mv, p);
     }
   }
   B2F_CHECK_CUDA(cudaGetLastError());
