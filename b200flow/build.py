@@ -63,12 +63,16 @@ def _compile(cmd: list[str], log: Path) -> None:
         raise RuntimeError(f"compile failed: {' '.join(cmd)}\n{res.stdout}\n{res.stderr}")
 
 
-def build_cuda(verbose: bool = False, half: str = "bf16") -> Path:
+def build_cuda(verbose: bool = False, half: str = "bf16", variant: str = "", variant_flags=()) -> Path:
+    """`variant`: an instrumented copy next to the product libraries (e.g. "attndbg" with -DB2F_ATTN_DEBUG for the
+    cycle counters); a process picks it with B2F_CUDA_LIB=libb200flow_cuda_<variant>.so."""
     nvcc = _nvcc()
     LIB_DIR.mkdir(parents=True, exist_ok=True)
     obj_dir = OBJ_DIR if half == "bf16" else OBJ_DIR.parent / "obj_fp16"
+    if variant:
+        obj_dir = OBJ_DIR.parent / f"obj_{variant}"
     obj_dir.mkdir(parents=True, exist_ok=True)
-    extra = [] if half == "bf16" else ["-DB2F_HALF_FP16"]
+    extra = ([] if half == "bf16" else ["-DB2F_HALF_FP16"]) + list(variant_flags)
     hdrs = _headers()
     srcs = sorted([*CSRC.glob("kernels/*.cu"), *CSRC.glob("comm/*.cu"), *CSRC.glob("common/*.cpp")])
     jobs, objs = [], []
@@ -82,6 +86,8 @@ def build_cuda(verbose: bool = False, half: str = "bf16") -> Path:
         with cf.ThreadPoolExecutor(max_workers=min(8, len(jobs))) as ex:
             list(ex.map(lambda j: _compile(*j), jobs))
     out = LIB_DIR / ("libb200flow_cuda.so" if half == "bf16" else "libb200flow_cuda_fp16.so")
+    if variant:
+        out = LIB_DIR / f"libb200flow_cuda_{variant}.so"
     if jobs or not out.exists():
         _compile([nvcc, "-shared", "-o", str(out), *map(str, objs), "-lcudart"],
                  obj_dir / "link_cuda.log")

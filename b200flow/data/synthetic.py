@@ -81,6 +81,26 @@ def token_stream(num_docs: int, vocab: int = 50257, mean_len: int = 400, seed: i
         yield rng.integers(0, vocab, n, dtype=np.int64)
 
 
+_ZIPF_CDF: dict = {}
+
+
+def zipf_tokens(vocab: int, shape, generator=None, exponent: float = 1.1, offset: float = 2.7):
+    """Token ids with a natural-language-like (Zipf-Mandelbrot) unigram distribution, p(r) ~ 1 / (r + offset)^exponent
+    over a fixed pseudo-random assignment of ranks to ids.  The benches train on these instead of uniform noise so
+    that a loss curve means something: a language model first learns the unigram distribution, and the loss falls from
+    ~ln(vocab) + initial logit noise towards the entropy of the distribution (about 7 nats at vocab 50k) - or it does
+    not, which is what a broken fp8 path or optimizer would show."""
+    key = (vocab, exponent, offset)
+    if key not in _ZIPF_CDF:
+        r = torch.arange(vocab, dtype=torch.float64)
+        w = (r + offset).pow(-exponent)
+        perm = torch.randperm(vocab, generator=torch.Generator().manual_seed(97))
+        _ZIPF_CDF[key] = ((w / w.sum()).cumsum(0), perm)
+    cdf, perm = _ZIPF_CDF[key]
+    u = torch.rand(shape, generator=generator, dtype=torch.float64)
+    return perm[torch.searchsorted(cdf, u).clamp_(max=vocab - 1)]
+
+
 def text_documents(num_docs: int, seed: int = 0):
     """Plain-text pseudo documents (json lines with a "text" field, as wikicorpus -> train.json)."""
     rng = np.random.default_rng(seed)

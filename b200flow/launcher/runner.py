@@ -33,6 +33,7 @@ import json
 import os
 import re
 import signal
+import sys
 import socket
 import subprocess
 import time
@@ -159,6 +160,18 @@ class Runner:
             sl = ids[(i * per) % total:(i * per) % total + per]
             out.append(sl if len(sl) == per else ids[:min(per, total)])
         return out
+
+    def spec_error(self) -> str | None:
+        """A job spec this box can never run, found before anything is spawned."""
+        p = self.plan
+        if p.kind in ("static", "elastic") and p.gpus_per_node and p.nproc_per_node and visible_gpu_count() \
+                and int(p.nproc_per_node) > int(p.gpus_per_node):
+            # a pod sees only the GPUs of its `nvidia.com/gpu` limit: more ranks than that would share devices and
+            # die inside NCCL ("Duplicate GPU detected") after the whole pre-script has run
+            return (f"resources.nproc_per_node={p.nproc_per_node} exceeds the pod's GPU limit "
+                    f"(resources.limits.\"nvidia.com/gpu\"={p.gpus_per_node}); raise the limit, e.g. "
+                    f"--set 'resources.limits.nvidia\\.com/gpu={p.nproc_per_node}'")
+        return None
 
     def pods(self) -> list[PodSpec]:
         p, script = self.plan, str(self.state.dir / self.plan.script_name)
@@ -335,6 +348,11 @@ class Runner:
         hung (exit code 125), killed and restarted like any other failure — the local stand-in for the NCCL
         watchdog / lost-heartbeat detection a cluster would provide."""
         self.prepare()
+        err = self.spec_error()
+        if err:
+            print(f"[b200flow] {self.plan.release}: {err}", file=sys.stderr, flush=True)
+            self.state.write_status(phase="Failed", exit_code=2, message=err)
+            return 2
         old = {}
         for s in (signal.SIGINT, signal.SIGTERM):
             try:

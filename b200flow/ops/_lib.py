@@ -21,7 +21,8 @@ _host = None
 HALF_NAME = os.environ.get("B2F_HALF", "bf16").lower()
 assert HALF_NAME in ("bf16", "fp16"), f"B2F_HALF must be bf16 or fp16, not {HALF_NAME!r}"
 HALF = torch.float16 if HALF_NAME == "fp16" else torch.bfloat16
-_CUDA_LIB_NAME = "libb200flow_cuda_fp16.so" if HALF_NAME == "fp16" else "libb200flow_cuda.so"
+_CUDA_LIB_NAME = os.environ.get("B2F_CUDA_LIB") or (
+    "libb200flow_cuda_fp16.so" if HALF_NAME == "fp16" else "libb200flow_cuda.so")   # B2F_CUDA_LIB: an instrumented variant
 
 
 def set_half(name: str) -> bool:

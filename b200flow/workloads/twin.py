@@ -18,6 +18,8 @@ from __future__ import annotations
 import json
 
 import torch
+
+from ..data.synthetic import zipf_tokens
 import torch.distributed as dist
 import torch.nn.functional as F
 from torch import nn
@@ -240,7 +242,7 @@ def run_twin(args, rank, world, dev, ClockSampler):
         gen = torch.Generator().manual_seed(77 + rank)
 
         def make():
-            t = torch.randint(0, 50304, (batch, seq + 1), generator=gen)
+            t = zipf_tokens(50304, (batch, seq + 1), generator=gen)
             return {"tokens": t[:, :-1].contiguous(), "labels": t[:, 1:].contiguous()}
 
         def loss_fn(mod, b):
@@ -300,7 +302,7 @@ def run_twin(args, rank, world, dev, ClockSampler):
         gen = torch.Generator().manual_seed(77 + rank)
 
         def make():
-            t = torch.randint(0, 32000, (batch, seq + 1), generator=gen)
+            t = zipf_tokens(32000, (batch, seq + 1), generator=gen)
             return {"tokens": t[:, :-1].contiguous(), "labels": t[:, 1:].contiguous()}
 
         def loss_fn(mod, b):

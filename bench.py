@@ -251,10 +251,12 @@ def main():
     B, S = args.micro_batch, args.seq
     tokens_per_step = B * S * args.gas * dp
 
-    # ---- synthetic data: same stream on every rank of a DP replica
+    # ---- synthetic data (Zipf unigram tokens): same stream on every rank of a DP replica
+    from b200flow.data.synthetic import zipf_tokens
+
     g = torch.Generator().manual_seed(1234 + (ps.dp_rank if ps else 0))
     n_host = args.gas * 2
-    host = [torch.randint(0, cfg.vocab_size, (B, S + 1), generator=g).pin_memory() for _ in range(n_host)]
+    host = [zipf_tokens(cfg.vocab_size, (B, S + 1), generator=g).pin_memory() for _ in range(n_host)]
     dev_batches = [(h[:, :-1].to(dev), h[:, 1:].to(dev)) for h in host]
 
     def device_iter():

@@ -149,7 +149,8 @@ constexpr float RESCALE_THRESHOLD = 8.f;
 constexpr int ATTN_POLY_DEFAULT = 0;   // pairs of four whose exp2 runs on the FMA pipe (B2F_ATTN_POLY overrides)
 
 struct Fwd2Bars {
-  uint64_t q_full[2], k_full[2], v_full[2], k_empty[2], v_empty[2], s_full[2], p_full[2], o_full[2];
+  uint64_t q_full[2], k_full[2], v_full[2], k_empty[2], v_empty[2], s_full[2], o_full[2];
+  uint64_t p_full[2][4];   // per query tile, per 32-key quarter of P: the P V product starts on the first quarter
   uint32_t tmem_base;
 };
 
@@ -205,7 +206,7 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
       mbar_init(&bars->k_empty[i], 1);
       mbar_init(&bars->v_empty[i], 1);
       mbar_init(&bars->s_full[i], 1);
-      mbar_init(&bars->p_full[i], 128);
+      for (int c = 0; c < 4; ++c) mbar_init(&bars->p_full[i][c], 128);
       mbar_init(&bars->o_full[i], 1);
     }
     fence_mbar_init();
@@ -264,7 +265,8 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
         }
         __syncwarp();
       };
-      auto issue_pv = [&](int w, int j) {
+      // O_w += P_w(j) V_j, one quarter of P (32 keys, two K=16 MMAs) at a time as the softmax warps publish it
+      auto issue_pv = [&](int w, int j, int c) {
         const int st = j & 1;
         const uint32_t aV = lo_mn(smem_u32(sV + st * TILE_B));
         const bool last_reader = (w == 1) || j >= nB;
@@ -273,11 +275,13 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
           if (p.dbg_mode != 2)
 #endif
 #pragma unroll
-          for (int k = 0; k < TQ / 16; ++k)
+          for (int k = 2 * c; k < 2 * c + 2; ++k)
             umma_f16_ts(tmem + 256 + w * 128, tmem + w * 128 + k * 8, desc_mn(aV, k), idesc_pv,
                         (j | k) != 0);
-          if (last_reader) umma_commit(&bars->v_empty[st]);
-          if (j + 1 == n_w[w]) umma_commit(&bars->o_full[w]);
+          if (c == 3) {
+            if (last_reader) umma_commit(&bars->v_empty[st]);
+            if (j + 1 == n_w[w]) umma_commit(&bars->o_full[w]);
+          }
         }
         __syncwarp();
       };
@@ -293,12 +297,18 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
         for (int w = 0; w < 2; ++w) {
           if (j >= n_w[w]) continue;
           DBG_T(t0);
-          mbar_wait(&bars->p_full[w], j & 1);
+          mbar_wait(&bars->p_full[w][0], j & 1);
           DBG_T(t1);
           mbar_wait(&bars->v_full[st], ph);
           tc_fence_after();
           DBG_T(t2);
-          issue_pv(w, j);
+          issue_pv(w, j, 0);
+#pragma unroll
+          for (int c = 1; c < 4; ++c) {
+            mbar_wait(&bars->p_full[w][c], j & 1);
+            tc_fence_after();
+            issue_pv(w, j, c);
+          }
           DBG_T(t3);
           if (j + 1 < n_w[w]) {
             mbar_wait(&bars->k_full[st ^ 1], ((j + 1) >> 1) & 1);
@@ -338,7 +348,7 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
 #ifdef B2F_ATTN_DEBUG
       if (p.dbg_mode >= 1) {
         tc_fence_before();
-        mbar_arrive(&bars->p_full[w]);
+        for (int c = 0; c < 4; ++c) mbar_arrive(&bars->p_full[w][c]);
         continue;
       }
 #endif
@@ -358,11 +368,11 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
       }
       float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
-      for (int i = 0; i < 128; i += 4) {
-        mx0 = fmaxf(mx0, __uint_as_float(s[i]));
-        mx1 = fmaxf(mx1, __uint_as_float(s[i + 1]));
-        mx2 = fmaxf(mx2, __uint_as_float(s[i + 2]));
-        mx3 = fmaxf(mx3, __uint_as_float(s[i + 3]));
+      for (int i = 0; i < 128; i += 8) {      // FMNMX3: two new values per instruction
+        mx0 = max3(mx0, __uint_as_float(s[i]), __uint_as_float(s[i + 4]));
+        mx1 = max3(mx1, __uint_as_float(s[i + 1]), __uint_as_float(s[i + 5]));
+        mx2 = max3(mx2, __uint_as_float(s[i + 2]), __uint_as_float(s[i + 6]));
+        mx3 = max3(mx3, __uint_as_float(s[i + 3]), __uint_as_float(s[i + 7]));
       }
       const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * p.scale_log2;
       if (j == 0) {
@@ -413,6 +423,9 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
             pk[i] = pack_bf16x2(p0, p1);
           }
           tmem_st_32x32b_x16(T_S + c * 16, pk);
+          tmem_st_wait();
+          tc_fence_before();
+          mbar_arrive(&bars->p_full[w][c]);
         }
       };
       if (POLY > 0 && !need_mask) probabilities(std::true_type{});
@@ -420,9 +433,6 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__
       float sum0, sum1;
       f2unpack(sum2, sum0, sum1);
       l += sum0 + sum1;
-      tmem_st_wait();
-      tc_fence_before();
-      mbar_arrive(&bars->p_full[w]);
 #ifdef B2F_ATTN_DEBUG
       if (threadIdx.x == 128) {
         DBG_T(ts3);

@@ -288,3 +288,16 @@ def test_pipeline_pending_bound_and_phase_polling(tmp_root, monkeypatch):
             "values": {"process": {"command": ["sleep"], "args": ["30"]}}}
     t0 = time.time()
     assert run_pipeline([slow], root=str(tmp_root), log=lambda m: None) == "Failure" and time.time() - t0 < 25
+
+
+def test_more_ranks_than_the_pods_gpu_limit_fails_before_spawning(tmp_root, monkeypatch):
+    """A pod only sees the GPUs of its `nvidia.com/gpu` limit; nproc_per_node above it is refused with the --set
+    that fixes it, instead of dying in NCCL after the pre-script (what the reference's 4-GPU values files did when
+    only nproc_per_node was raised to 8)."""
+    monkeypatch.setattr(R, "visible_gpu_count", lambda: 8)
+    vals = _vals("echo should-not-run", resources={"nnodes": 1, "nproc_per_node": 8, "limits": {"nvidia.com/gpu": 4}})
+    rc, logs, st = _run("pytorchjob-distributed", "lim", vals, tmp_root)
+    assert rc == 2 and st["phase"] == "Failed" and "nvidia\\.com/gpu=8" in st["message"]
+    assert not any("should-not-run" in v for v in logs.values())
+    rc, logs, st = _run("pytorchjob-distributed", "lim2", vals, tmp_root, sets=[r"resources.limits.nvidia\.com/gpu=8"])
+    assert st.get("message") is None and "should-not-run" in "".join(logs.values())
