@@ -187,6 +187,43 @@ class MaskRCNN(nn.Module):
         self.box_head = FCHead(c * 7 * 7, max(64, int(cfg.fc_dim * cfg.width)), cfg.num_classes)
         self.mask_head = MaskHead(c, cfg.num_classes, c) if cfg.mode_mask else None
 
+    # ------------------------------------------------------------------ trunk: backbone + FPN + RPN head
+    def _run_trunk(self, x, training):
+        g = self.__dict__.get("_trunk_graph")
+        if g is not None and training and tuple(x.shape) == g[1] and x.dtype == g[2]:
+            out = g[0](x)
+            return list(out[:5]), list(out[5:10]), list(out[10:15])
+        fmap = self.backbone(x)
+        feats = [fmap[k] for k in ("0", "1", "2", "3", "pool")]
+        logits, deltas = self.rpn(feats)
+        return feats, logits, deltas
+
+    def enable_trunk_graph(self, example_images: torch.Tensor):
+        """Capture backbone + FPN + RPN head (forward and backward) as CUDA graphs for this image shape: the part of
+        the training step whose shapes never depend on the data, and more than half of its kernel launches.  Frozen-BN
+        folds of the frozen layers are baked in, so call this after the backbone weights are loaded; other shapes,
+        eval mode and CPU keep the eager path."""
+        if not example_images.is_cuda:
+            return False
+
+        class Trunk(nn.Module):
+            def __init__(self, backbone, rpn):
+                super().__init__()
+                self.backbone, self.rpn = backbone, rpn
+
+            def forward(self, x):
+                fmap = self.backbone(x)
+                feats = [fmap[k] for k in ("0", "1", "2", "3", "pool")]
+                logits, deltas = self.rpn(feats)
+                return (*feats, *logits, *deltas)
+
+        trunk = Trunk(self.backbone, self.rpn)
+        trunk.train(self.training)
+        x = example_images.detach().contiguous(memory_format=torch.channels_last).clone()
+        graphed = torch.cuda.make_graphed_callables(trunk, (x,))
+        self.__dict__["_trunk_graph"] = (graphed, tuple(x.shape), x.dtype)     # not a registered submodule
+        return True
+
     # ------------------------------------------------------------------ RPN
     def _proposals(self, logits, deltas, anchors, img_hw, training, static=False):
         cfg = self.cfg
@@ -356,12 +393,10 @@ class MaskRCNN(nn.Module):
         cfg = self.cfg
         training = self.training and targets is not None
         x = images.contiguous(memory_format=torch.channels_last)
-        fmap = self.backbone(x)
-        feats = [fmap[k] for k in ("0", "1", "2", "3", "pool")]
+        feats, logits, deltas = self._run_trunk(x, training)
         img_hw = images.shape[-2:]
         anchors = make_anchors([f.shape[-2:] for f in feats], self.strides, cfg.anchor_sizes,
                                cfg.anchor_ratios, images.device)
-        logits, deltas = self.rpn(feats)
         static = training and self.static_shapes
         proposals = self._proposals(logits, deltas, anchors, img_hw, training, static=static)
         feats_nhwc = [f.permute(0, 2, 3, 1).contiguous() if not f.permute(0, 2, 3, 1).is_contiguous()

@@ -37,6 +37,11 @@ def run_maskrcnn_bench(args, rank, world, dev, ClockSampler, emit=None):
                 [{k: s[k].pin_memory() for k in ("boxes", "labels", "masks")} for s in samples])
 
     host = [make() for _ in range(3)]
+    import os
+
+    graphed = False
+    if model.static_shapes and os.environ.get("B2F_MASKRCNN_GRAPH", "1") == "1":
+        graphed = model.enable_trunk_graph(host[0][0].to(dev))
     devb = [(im.to(dev), [{k: v.to(dev) for k, v in t.items()} for t in tg]) for im, tg in host]
     state = {"i": 0}
 
@@ -93,7 +98,7 @@ def run_maskrcnn_bench(args, rank, world, dev, ClockSampler, emit=None):
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "b200flow",
             "config": {"model": "maskrcnn-r50-fpn", "global_batch": gb, "image": [H, W],
                        "parallelism": f"dp{world}", "l2_policy": "activations per step >> 126 MB L2",
-                       "fused_collectives": not args.no_fused},
+                       "fused_collectives": not args.no_fused, "trunk_cuda_graph": graphed},
             "clocks": clocks.summary(),
             "e2e": {"value": gb * args.steps / (ms_e2e / 1e3), "unit": "images/s",
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},

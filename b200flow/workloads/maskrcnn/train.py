@@ -200,6 +200,7 @@ def main():
             print(f"[b200flow] DATA.BASEDIR={basedir}: {len(train_set)} training images"
                   + (f", {len(val_set)} validation images" if val_set is not None else ""), flush=True)
     start_epoch = step // max(1, steps_per_epoch)
+    graph_tried = False
     for epoch in range(start_epoch + 1, total_epochs + 1):
         model.train()
         t0, seen, agg = time.time(), 0, {}
@@ -224,6 +225,11 @@ def main():
             tg = [{k: s[k].to(dev) for k in ("boxes", "labels", "masks")} for s in samples]
             opt.param_groups[0]["lr"] = lr_at(step, float(cfgd.get("TRAIN.BASE_LR", 0.01)), world, batch,
                                               warmup, boundaries)
+            if use_cuda and not graph_tried:
+                # backbone + FPN + RPN head as CUDA graphs once the weights are final and the image shape is known
+                graph_tried = True
+                if model.static_shapes and os.environ.get("B2F_MASKRCNN_GRAPH", "1") == "1":
+                    model.enable_trunk_graph(imgs)
             opt.zero_grad()
             losses = model(imgs, tg)
             losses["total"].backward()

@@ -242,11 +242,12 @@ def main():
         "fused_collectives": not args.no_fused,
         "pipeline": {"zero_bubble": not args.no_zero_bubble},
     }
-    if is_moe:
-        # the DeepSpeed-MoE recipes warm the rate up; from a cold start at the full rate the loss of this model
-        # first climbs for a dozen steps (bf16 and fp8 experts alike, profiles/r2_moe_loss_curves.txt)
-        ds_config["scheduler"] = {"type": "WarmupLR", "params": {"warmup_min_lr": 0.0, "warmup_max_lr": 1.5e-4,
-                                                                 "warmup_num_steps": 16, "warmup_type": "linear"}}
+    # Linear warm-up of the rate, as the Megatron / DeepSpeed recipes of both models do (--lr-warmup-*): from a cold
+    # start at the full rate the loss first climbs for several steps (fused and NCCL arms, bf16 and fp8 experts alike:
+    # profiles/r2_call4_*, r2_call15_*), which says nothing about the kernels and makes the curves hard to read.
+    ds_config["scheduler"] = {"type": "WarmupLR", "params": {"warmup_min_lr": 0.0, "warmup_max_lr": 1.5e-4,
+                                                             "warmup_num_steps": 16 if is_moe else 8,
+                                                             "warmup_type": "linear"}}
     engine = initialize(cfg, ds_config, ps, device=dev)
     B, S = args.micro_batch, args.seq
     tokens_per_step = B * S * args.gas * dp
