@@ -87,18 +87,36 @@ def _sample(pos_mask, neg_mask, batch, pos_frac):
 
 def _sample_static(pos_mask, neg_mask, batch: int, pos_frac: float):
     """Fixed-shape version of the fg / bg sampler: no `nonzero`, no data-dependent sizes, so the step never waits for
-    the GPU.  Returns (pos_idx [P], pos_ok [P], neg_idx [Q], neg_ok [Q]) with P = batch * pos_frac, Q = batch: random
-    members of each set (top-k of uniform noise restricted to the set), `*_ok` marking the entries that are real and
-    inside the quota - negatives fill whatever the positives leave of `batch`, as in tensorpack's sampler."""
+    the GPU.  Masks are [n] or [N, n] (one row per image, sampled independently).  Returns (pos_idx [.., P],
+    pos_ok [.., P], neg_idx [.., Q], neg_ok [.., Q]) with P = batch * pos_frac, Q = batch: random members of each set
+    (top-k of uniform noise restricted to the set), `*_ok` marking the entries that are real and inside the quota -
+    negatives fill whatever the positives leave of `batch`, as in tensorpack's sampler."""
     P = int(batch * pos_frac)
-    n = pos_mask.numel()
-    noise = torch.rand(2, n, device=pos_mask.device)
-    ps, pos_idx = torch.where(pos_mask, noise[0], noise.new_full((), -1.0)).topk(min(P, n))
+    n = pos_mask.shape[-1]
+    noise = torch.rand((2, *pos_mask.shape), device=pos_mask.device)
+    ps, pos_idx = torch.where(pos_mask, noise[0], noise.new_full((), -1.0)).topk(min(P, n), dim=-1)
     pos_ok = ps >= 0
-    quota = batch - pos_ok.sum()                                   # a device scalar: never read on the host
-    ns, neg_idx = torch.where(neg_mask, noise[1], noise.new_full((), -1.0)).topk(min(batch, n))
-    neg_ok = (ns >= 0) & (torch.arange(neg_idx.numel(), device=ns.device) < quota)
+    quota = batch - pos_ok.sum(-1, keepdim=True)                   # device values: never read on the host
+    ns, neg_idx = torch.where(neg_mask, noise[1], noise.new_full((), -1.0)).topk(min(batch, n), dim=-1)
+    neg_ok = (ns >= 0) & (torch.arange(neg_idx.shape[-1], device=ns.device) < quota)
     return pos_idx, pos_ok, neg_idx, neg_ok
+
+
+def pad_targets(targets):
+    """Per-image target lists -> ([N, G, 4] boxes, [N, G] labels, [N, G] valid) with G = the largest count of the
+    batch (at least 1); padding boxes are zeros, which have IoU 0 with everything.  Shapes come from the host-side
+    sizes of the lists, values never leave the device."""
+    from torch.nn.utils.rnn import pad_sequence
+
+    dev = targets[0]["boxes"].device
+    boxes = pad_sequence([t["boxes"].float().reshape(-1, 4) for t in targets], batch_first=True)
+    labels = pad_sequence([t["labels"].long().reshape(-1) for t in targets], batch_first=True)
+    valid = pad_sequence([torch.ones(t["boxes"].shape[0], dtype=torch.bool, device=dev) for t in targets], batch_first=True)
+    if boxes.shape[1] == 0:
+        n = len(targets)
+        boxes, labels = boxes.new_zeros(n, 1, 4), labels.new_zeros(n, 1)
+        valid = torch.zeros(n, 1, dtype=torch.bool, device=dev)
+    return boxes, labels, valid
 
 
 def _masked(v, ok):
@@ -120,7 +138,7 @@ class RPNHead(nn.Module):
     def forward(self, feats):
         logits, deltas = [], []
         for f in feats:
-            t = F.relu(self.conv(f))
+            t = D.conv_bias_act(f, self.conv, relu=True)
             logits.append(self.cls(t).permute(0, 2, 3, 1).flatten(1))               # [N, H*W*A]
             n, _, h, w = f.shape
             deltas.append(self.box(t).view(n, -1, 4, h, w).permute(0, 3, 4, 1, 2).reshape(n, -1, 4))
@@ -160,7 +178,7 @@ class MaskHead(nn.Module):
 
     def forward(self, x):
         for c in self.convs:
-            x = F.relu(c(x))
+            x = D.conv_bias_act(x, c, relu=True)
         return self.pred(F.relu(self.deconv(x)))
 
 
@@ -284,101 +302,97 @@ class MaskRCNN(nn.Module):
         n = max(1, len(targets))
         return cls_loss / n, box_loss / n
 
-    def _rpn_loss_static(self, logits, deltas, anchors, targets):
-        """`_rpn_loss` with fixed shapes (see `_sample_static`): the same labels and the same losses in expectation,
-        no host synchronisation."""
+    def _rpn_loss_static(self, logits, deltas, anchors, gt_boxes, gt_valid):
+        """`_rpn_loss` with fixed shapes and all images at once (see `_sample_static`, `pad_targets`): the same labels
+        and the same losses in expectation, one pass of launches for the whole batch, no host synchronisation."""
         cfg = self.cfg
-        lg = torch.cat(logits, 1).float()
-        dl = torch.cat(deltas, 1).float()
-        an = torch.cat(anchors, 0)
-        cls_loss, box_loss = lg.new_zeros(()), lg.new_zeros(())
-        for i, t in enumerate(targets):
-            gt = t["boxes"].float()
-            if gt.shape[0] == 0:                       # a host-side shape, not a device value
-                pos_m = torch.zeros(an.shape[0], dtype=torch.bool, device=an.device)
-                neg_m = ~pos_m
-                arg = torch.zeros(an.shape[0], dtype=torch.long, device=an.device)
-                gt = an.new_zeros(1, 4)
-            else:
-                iou = D.pairwise_iou(an, gt)
-                best, arg = iou.max(1)
-                labels = torch.full_like(best, -1)
-                labels[best < cfg.rpn_bg_iou] = 0
-                labels[best >= cfg.rpn_fg_iou] = 1
-                labels[iou.argmax(0)] = 1
-                pos_m, neg_m = labels == 1, labels == 0
-            pi, pok, ni, nok = _sample_static(pos_m, neg_m, cfg.rpn_batch, 0.5)
-            # unused slots are selected away, not multiplied away: 0 * inf would poison the sum
-            tgt = _masked(encode_boxes(gt[arg[pi]], an[pi], (1.0, 1.0, 1.0, 1.0)), pok)
-            bl = F.smooth_l1_loss(dl[i, pi], tgt, beta=1.0 / 9, reduction="none").sum(1)
-            box_loss = box_loss + _masked(bl, pok).sum() / cfg.rpn_batch
-            sel = torch.cat([pi, ni])
-            y = torch.cat([torch.ones_like(pi, dtype=torch.float32), torch.zeros_like(ni, dtype=torch.float32)])
-            w = torch.cat([pok, nok]).float()
-            ce = F.binary_cross_entropy_with_logits(lg[i, sel], y, reduction="none")
-            cls_loss = cls_loss + _masked(ce, w > 0).sum() / cfg.rpn_batch
-        n = max(1, len(targets))
-        return cls_loss / n, box_loss / n
+        lg = torch.cat(logits, 1).float()                               # [N, A]
+        dl = torch.cat(deltas, 1).float()                               # [N, A, 4]
+        an = torch.cat(anchors, 0)                                      # [A, 4]
+        N, G = gt_valid.shape
+        A = an.shape[0]
+        iou = D.pairwise_iou(an, gt_boxes.reshape(N * G, 4)).view(A, N, G).permute(1, 0, 2)     # [N, A, G]
+        iou = torch.where(gt_valid[:, None, :], iou, iou.new_full((), -1.0))
+        best, arg = iou.max(2)                                          # [N, A]
+        labels = torch.full_like(best, -1)
+        labels = torch.where(best < cfg.rpn_bg_iou, torch.zeros_like(labels), labels)
+        labels = torch.where(best >= cfg.rpn_fg_iou, torch.ones_like(labels), labels)
+        top_anchor = iou.argmax(1)                                      # [N, G]: every valid gt gets an anchor
+        labels.scatter_(1, top_anchor, torch.where(gt_valid, torch.ones_like(best[:, :G]),
+                                                    torch.gather(labels, 1, top_anchor)))
+        pi, pok, ni, nok = _sample_static(labels == 1, labels == 0, cfg.rpn_batch, 0.5)        # [N, P], [N, Q]
+        gsel = torch.gather(arg, 1, pi)                                 # [N, P] gt of each sampled positive
+        gtb = torch.gather(gt_boxes, 1, gsel[..., None].expand(-1, -1, 4))
+        # unused slots are selected away, not multiplied away: 0 * inf would poison the sum
+        tgt = _masked(encode_boxes(gtb.reshape(-1, 4), an[pi.reshape(-1)], (1.0, 1.0, 1.0, 1.0)), pok.reshape(-1))
+        pred = torch.gather(dl, 1, pi[..., None].expand(-1, -1, 4)).reshape(-1, 4)
+        bl = F.smooth_l1_loss(pred, tgt, beta=1.0 / 9, reduction="none").sum(1)
+        box_loss = _masked(bl, pok.reshape(-1)).sum() / cfg.rpn_batch
+        sel = torch.cat([pi, ni], 1)
+        y = torch.cat([torch.ones_like(pi, dtype=torch.float32), torch.zeros_like(ni, dtype=torch.float32)], 1)
+        ce = F.binary_cross_entropy_with_logits(torch.gather(lg, 1, sel), y, reduction="none")
+        cls_loss = _masked(ce.reshape(-1), torch.cat([pok, nok], 1).reshape(-1)).sum() / cfg.rpn_batch
+        return cls_loss / max(1, N), box_loss / max(1, N)
 
     def _train_static(self, feats_nhwc, dt, logits, deltas, anchors, targets, props, pvalid, images):
-        """The training half of `forward` with fixed shapes: per image `roi_batch` sampled RoIs (a quarter of them
-        foreground slots, unused slots masked out of the losses) and `roi_batch * roi_fg_fraction` mask RoIs."""
+        """The training half of `forward` with fixed shapes, all images at once: per image `roi_batch` sampled RoIs (a
+        quarter of them foreground slots, unused slots masked out of the losses) and `roi_batch * roi_fg_fraction`
+        mask RoIs."""
         cfg = self.cfg
         dev = images.device
-        rpn_cls, rpn_box = self._rpn_loss_static(logits, deltas, anchors, targets)
-        gt_all = torch.cat([t["boxes"].float() for t in targets], 0)
-        counts = [t["boxes"].shape[0] for t in targets]
-        offs = [0]
-        for c in counts:
-            offs.append(offs[-1] + c)
-        gt_off = torch.tensor(offs, device=dev, dtype=torch.int32)
-        all_labels = torch.cat([tt["labels"] for tt in targets]) if offs[-1] else torch.zeros(0, dtype=torch.long, device=dev)
-        rois, labels, weights, reg_t, fgw, m_rois, m_tgt, m_lbl, m_w = [], [], [], [], [], [], [], [], []
-        for i, t in enumerate(targets):
-            p = torch.cat([props[i], t["boxes"].float()], 0)                      # gt boxes join the proposals
-            valid = torch.cat([pvalid[i], torch.ones(counts[i], dtype=torch.bool, device=dev)])
-            pb = torch.full((p.shape[0],), i, device=dev, dtype=torch.int32)
-            if counts[i]:
-                iou, idx = D.match_proposals(p, pb, gt_all, gt_off)
-            else:
-                iou, idx = p.new_zeros(p.shape[0]), torch.zeros(p.shape[0], dtype=torch.int32, device=dev)
-            fi, fok, bi, bok = _sample_static(valid & (iou >= cfg.roi_fg_iou), valid & (iou < cfg.roi_fg_iou),
-                                              cfg.roi_batch, cfg.roi_fg_fraction)
-            sel = torch.cat([fi, bi])
-            ok = torch.cat([fok, bok])
-            gidx = idx[fi].long().clamp(min=0)
-            lab = torch.zeros(sel.numel(), dtype=torch.long, device=dev)
-            if offs[-1]:
-                lab[:fi.numel()] = torch.where(fok, all_labels[gidx.clamp(max=offs[-1] - 1)], torch.zeros_like(gidx))
-            rois.append(torch.cat([pb[sel].float()[:, None], p[sel]], 1))
-            labels.append(lab)
-            weights.append(ok.float())
-            reg = torch.zeros(sel.numel(), 4, device=dev)
-            if offs[-1]:
-                reg[:fi.numel()] = _masked(encode_boxes(gt_all[gidx.clamp(max=offs[-1] - 1)], p[fi], cfg.box_weights), fok)
-            reg_t.append(reg)
-            fgw.append(torch.cat([fok.float(), torch.zeros(bi.numel(), device=dev)]))
-            if cfg.mode_mask and counts[i]:
-                m_rois.append(torch.cat([pb[fi].float()[:, None], p[fi]], 1))
-                local = (gidx - offs[i]).clamp(0, counts[i] - 1)
-                m_tgt.append(D.mask_crop(t["masks"], p[fi], local.int(), cfg.mask_res))
-                m_lbl.append(all_labels[gidx.clamp(max=offs[-1] - 1)])
-                m_w.append(fok.float())
-        rois, labels, weights, reg_t, fgw = (torch.cat(v) for v in (rois, labels, weights, reg_t, fgw))
+        gt_boxes, gt_labels, gt_valid = pad_targets(targets)
+        N, G = gt_valid.shape
+        rpn_cls, rpn_box = self._rpn_loss_static(logits, deltas, anchors, gt_boxes, gt_valid)
+        p = torch.cat([props, gt_boxes], 1)                                       # gt boxes join the proposals
+        valid = torch.cat([pvalid, gt_valid], 1)                                  # [N, K]
+        K = p.shape[1]
+        pb = torch.arange(N, device=dev, dtype=torch.int32)[:, None].expand(N, K)
+        gt_off = torch.arange(N + 1, device=dev, dtype=torch.int32) * G
+        # padding boxes have zero area: IoU 0 with every proposal, so they are never anybody's foreground match
+        iou, idx = D.match_proposals(p.reshape(-1, 4), pb.reshape(-1), gt_boxes.reshape(-1, 4), gt_off)
+        iou, idx = iou.view(N, K), idx.view(N, K)
+        fi, fok, bi, bok = _sample_static(valid & (iou >= cfg.roi_fg_iou), valid & (iou < cfg.roi_fg_iou),
+                                          cfg.roi_batch, cfg.roi_fg_fraction)     # [N, Fg], [N, Bg]
+        Fg = fi.shape[1]
+        sel = torch.cat([fi, bi], 1)
+        ok = torch.cat([fok, bok], 1).reshape(-1)
+        gidx = torch.gather(idx, 1, fi).long().clamp(0, N * G - 1)                # [N, Fg] global gt index
+        fg_labels = torch.where(fok, gt_labels.reshape(-1)[gidx], torch.zeros_like(gidx))
+        labels = torch.cat([fg_labels, torch.zeros_like(bi)], 1).reshape(-1)
+        boxes_sel = torch.gather(p, 1, sel[..., None].expand(-1, -1, 4))          # [N, Fg + Bg, 4]
+        bcol = torch.arange(N, device=dev, dtype=torch.float32)[:, None, None].expand(N, sel.shape[1], 1)
+        rois = torch.cat([bcol, boxes_sel], 2).reshape(-1, 5)
+        fg_boxes = boxes_sel[:, :Fg]
+        reg_fg = _masked(encode_boxes(gt_boxes.reshape(-1, 4)[gidx.reshape(-1)], fg_boxes.reshape(-1, 4),
+                                      cfg.box_weights), fok.reshape(-1)).view(N, Fg, 4)
+        reg_t = torch.cat([reg_fg, reg_fg.new_zeros(N, bi.shape[1], 4)], 1).reshape(-1, 4)
+        fgw = torch.cat([fok, torch.zeros_like(bok)], 1).reshape(-1)
         box_feat = self._roi_feats(feats_nhwc, rois, 7).permute(0, 3, 1, 2).flatten(1).to(dt)
         cls_logits, box_reg = self.box_head(box_feat)
-        denom = weights.sum().clamp(min=1.0)
-        loss_cls = _masked(F.cross_entropy(cls_logits, labels, reduction="none"), weights > 0).sum() / denom
+        denom = ok.sum().clamp(min=1).float()
+        loss_cls = _masked(F.cross_entropy(cls_logits, labels, reduction="none"), ok).sum() / denom
         br = box_reg.view(-1, cfg.num_classes, 4)[torch.arange(labels.numel(), device=dev), labels]
-        loss_box = _masked(F.smooth_l1_loss(br, reg_t, beta=1.0, reduction="none").sum(1), fgw > 0).sum() / denom
+        loss_box = _masked(F.smooth_l1_loss(br, reg_t, beta=1.0, reduction="none").sum(1), fgw).sum() / denom
         losses = {"rpn_cls": rpn_cls, "rpn_box": rpn_box, "frcnn_cls": loss_cls, "frcnn_box": loss_box}
-        if cfg.mode_mask and m_rois:
-            mr, ml, mw = torch.cat(m_rois), torch.cat(m_lbl), torch.cat(m_w)
-            mfeat = self._roi_feats(feats_nhwc, mr, 14).permute(0, 3, 1, 2).to(dt)
+        counts = [t["boxes"].shape[0] for t in targets]                            # host-side sizes
+        if cfg.mode_mask and sum(counts):
+            # masks stay unpadded: [sum of counts, H, W]; the padded gt index (image * G + local) becomes an index
+            # into that stack through the per-image offsets
+            offs = [0]
+            for c in counts:
+                offs.append(offs[-1] + c)
+            offs_dev = torch.tensor(offs[:-1], device=dev)
+            midx = (offs_dev[gidx // G] + gidx % G).clamp(max=offs[-1] - 1)
+            all_masks = torch.cat([t["masks"] for t in targets if t["masks"].shape[0]], 0)
+            m_rois = torch.cat([bcol[:, :Fg], fg_boxes], 2).reshape(-1, 5)
+            m_tgt = D.mask_crop(all_masks, fg_boxes.reshape(-1, 4), midx.reshape(-1).int(), cfg.mask_res)
+            mfeat = self._roi_feats(feats_nhwc, m_rois, 14).permute(0, 3, 1, 2).to(dt)
             mlogits = self.mask_head(mfeat.contiguous(memory_format=torch.channels_last)).float()
+            ml = fg_labels.reshape(-1)
             sel_logits = mlogits[torch.arange(ml.numel(), device=dev), ml]
-            per_roi = F.binary_cross_entropy_with_logits(sel_logits, torch.cat(m_tgt), reduction="none").mean((1, 2))
-            losses["mrcnn"] = _masked(per_roi, mw > 0).sum() / mw.sum().clamp(min=1.0)
+            per_roi = F.binary_cross_entropy_with_logits(sel_logits, m_tgt, reduction="none").mean((1, 2))
+            mw = fok.reshape(-1)
+            losses["mrcnn"] = _masked(per_roi, mw).sum() / mw.sum().clamp(min=1).float()
         losses["total"] = sum(losses.values())
         return losses
 

@@ -17,6 +17,8 @@ import torch
 import torch.nn.functional as F
 from torch import nn
 
+from ..ops.detection import bias_act_, conv_bias_act
+
 
 # Random initialisation only (a backbone checkpoint overwrites every buffer): with the statistics frozen at identity
 # nothing re-normalises the residual stream, so the last scale of every block starts small and the activation variance
@@ -57,8 +59,10 @@ class FrozenBN(nn.Module):
         return self._cache[1], self._cache[2]
 
 
-def conv_bn(x, conv: ConvW, bn: FrozenBN, relu: bool, cache: dict | None = None):
-    """relu?(bn(conv(x))) as one cuDNN convolution with a scaled weight and a bias."""
+def conv_bn(x, conv: ConvW, bn: FrozenBN, relu: bool, cache: dict | None = None, residual=None):
+    """relu?(bn(conv(x)) (+ residual)) as one cuDNN convolution with a scaled weight, followed by ONE in-place pass
+    over the output for shift, residual and ReLU (`ops.detection.bias_act_`; cuDNN would add the bias with a separate
+    broadcast kernel and leave the other two to two more passes)."""
     s, t = bn.scale_shift(x.dtype)
     w = conv.weight
     if not w.requires_grad and cache is not None:          # frozen layers: fold once per weight version
@@ -70,8 +74,8 @@ def conv_bn(x, conv: ConvW, bn: FrozenBN, relu: bool, cache: dict | None = None)
         wf = hit[1]
     else:
         wf = w.to(x.dtype) * s
-    y = F.conv2d(x, wf, t, conv.stride, conv.padding)
-    return F.relu_(y) if relu else y
+    y = F.conv2d(x, wf, None, conv.stride, conv.padding)
+    return bias_act_(y, t, residual, relu)
 
 
 class Bottleneck(nn.Module):
@@ -91,8 +95,7 @@ class Bottleneck(nn.Module):
         idt = x if self.downsample is None else conv_bn(x, self.downsample[0], self.downsample[1], False, cache)
         y = conv_bn(x, self.conv1, self.bn1, True, cache)
         y = conv_bn(y, self.conv2, self.bn2, True, cache)
-        y = conv_bn(y, self.conv3, self.bn3, False, cache)
-        return F.relu_(y.add_(idt))
+        return conv_bn(y, self.conv3, self.bn3, True, cache, residual=idt)
 
 
 class BasicBlock(nn.Module):
@@ -110,8 +113,7 @@ class BasicBlock(nn.Module):
     def forward(self, x, cache):
         idt = x if self.downsample is None else conv_bn(x, self.downsample[0], self.downsample[1], False, cache)
         y = conv_bn(x, self.conv1, self.bn1, True, cache)
-        y = conv_bn(y, self.conv2, self.bn2, False, cache)
-        return F.relu_(y.add_(idt))
+        return conv_bn(y, self.conv2, self.bn2, True, cache, residual=idt)
 
 
 class _Stage(nn.ModuleList):
@@ -174,12 +176,12 @@ class FPN(nn.Module):
                 nn.init.zeros_(m.bias)
 
     def forward(self, feats):
-        last = self.inner_blocks[-1](feats[-1])
-        outs = [self.layer_blocks[-1](last)]
+        last = conv_bias_act(feats[-1], self.inner_blocks[-1][0])
+        outs = [conv_bias_act(last, self.layer_blocks[-1][0])]
         for i in range(len(feats) - 2, -1, -1):
-            lat = self.inner_blocks[i](feats[i])
+            lat = conv_bias_act(feats[i], self.inner_blocks[i][0])
             last = lat + F.interpolate(last, size=lat.shape[-2:], mode="nearest")
-            outs.insert(0, self.layer_blocks[i](last))
+            outs.insert(0, conv_bias_act(last, self.layer_blocks[i][0]))
         outs.append(F.max_pool2d(outs[-1], 1, 2, 0))
         return outs
 

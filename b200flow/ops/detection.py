@@ -76,6 +76,61 @@ def roi_align(feats_nhwc: list[torch.Tensor], scales: list[float], rois: torch.T
     return _RoIAlign.apply(rois, P, sampling, aligned, list(scales), *feats_nhwc)
 
 
+class _BiasAct(torch.autograd.Function):
+    """y <- act(y + bias[c] (+ residual)) in place on a channels-last activation (`b2f_bias_act_nhwc`).  `bias` is
+    either a constant (the shift of a folded frozen batch norm) or a trainable convolution bias, whose gradient is the
+    channel sum of the incoming gradient (`b2f_channel_sum_nhwc`)."""
+
+    @staticmethod
+    def forward(ctx, y, bias, residual, relu):
+        C = y.shape[1]
+        _lib.call("b2f_bias_act_nhwc", ptr(y), ptr(bias), ptr(residual), c_ll(y.numel()), c_int(C), c_int(int(relu)),
+                  stream_ptr())
+        ctx.mark_dirty(y)
+        ctx.relu, ctx.has_res, ctx.bias_dtype = relu, residual is not None, bias.dtype
+        if relu:
+            ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        if ctx.relu:
+            (out,) = ctx.saved_tensors
+            g = torch.ops.aten.threshold_backward(g, out, 0)
+        db = None
+        if ctx.needs_input_grad[1]:
+            g = g.contiguous(memory_format=torch.channels_last)
+            acc = torch.zeros(g.shape[1], dtype=torch.float32, device=g.device)
+            _lib.call("b2f_channel_sum_nhwc", ptr(g), ptr(acc), c_ll(g.numel()), c_int(g.shape[1]), stream_ptr())
+            db = acc.to(ctx.bias_dtype)
+        return g, db, (g if ctx.has_res else None), None
+
+
+def bias_act_(y: torch.Tensor, bias: torch.Tensor, residual: torch.Tensor | None = None, relu: bool = True):
+    """In place on the convolution output `y` [N, C, H, W]: y = act(y + bias.view(1, C, 1, 1) (+ residual))."""
+    C8 = y.shape[1] // 8 if y.dim() == 4 else 0
+    fast = (y.is_cuda and y.dtype == _lib.HALF and y.dim() == 4 and y.shape[1] % 8 == 0
+            and y.is_contiguous(memory_format=torch.channels_last) and bias.dtype == y.dtype and bias.is_contiguous()
+            and (not bias.requires_grad or (C8 <= 256 and 256 % C8 == 0))
+            and (residual is None or (residual.shape == y.shape and residual.dtype == y.dtype
+                                      and residual.is_contiguous(memory_format=torch.channels_last))))
+    if fast:
+        return _BiasAct.apply(y, bias, residual, relu)
+    y = y.add_(bias.view(1, -1, 1, 1).to(y.dtype))
+    if residual is not None:
+        y = y.add_(residual)
+    return torch.relu_(y) if relu else y
+
+
+def conv_bias_act(x: torch.Tensor, conv, relu: bool = False):
+    """`conv` (an nn.Conv2d with a bias) followed by an optional ReLU, with the bias and the activation in one in-place
+    pass over the output instead of cuDNN's separate broadcast add plus a ReLU kernel."""
+    if not x.is_cuda or conv.bias is None:
+        y = conv(x)
+        return torch.relu_(y) if relu else y
+    y = torch.nn.functional.conv2d(x, conv.weight, None, conv.stride, conv.padding, conv.dilation, conv.groups)
+    return bias_act_(y, conv.bias, None, relu)
+
 def box_decode(anchors: torch.Tensor, deltas: torch.Tensor, weights=(1.0, 1.0, 1.0, 1.0),
                img_w: float = 1e9, img_h: float = 1e9) -> torch.Tensor:
     anchors, deltas = anchors.float().contiguous(), deltas.float().contiguous()

@@ -139,6 +139,66 @@ roi_align_kernel(Pyramid pyr, const float* __restrict__ rois, int R, int P, int 
   }
 }
 
+// ---------------------------------------------------------------- conv epilogue for the folded-BN backbone
+// y = act(y + bias[c] (+ residual)) in place over an NHWC half-precision tensor, eight channels per thread.  cuDNN
+// leaves a convolution's bias to a separate broadcast add (an unvectorised kernel on channels-last data) and the
+// ReLU and the residual add to two more passes; this is all three in one pass over the activation.
+__global__ void __launch_bounds__(256)
+bias_act_nhwc_kernel(__nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ bias,
+                     const __nv_bfloat16* __restrict__ residual, long long n8, int C8, int relu) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8;
+       i += (long long)gridDim.x * blockDim.x) {
+    float v[8], b[8];
+    uint4* py = reinterpret_cast<uint4*>(y) + i;
+    unpack8(*py, v);
+    unpack8(__ldg(reinterpret_cast<const uint4*>(bias) + (int)(i % C8)), b);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] += b[j];
+    if (residual) {
+      unpack8(__ldg(reinterpret_cast<const uint4*>(residual) + i), b);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] += b[j];
+    }
+    if (relu) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
+    }
+    uint4 o;
+    o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
+    o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
+    *py = o;
+  }
+}
+
+// out[c] += sum over rows of g[row, c] for an NHWC half-precision gradient (the bias gradient of a convolution).
+// 256 threads = (256 / C8) row lanes x C8 channel groups of eight; fp32 partial sums in registers, one shared-memory
+// reduction per block, then one atomic per channel per block.
+__global__ void __launch_bounds__(256)
+channel_sum_nhwc_kernel(const __nv_bfloat16* __restrict__ g, float* __restrict__ out, long long rows, int C8) {
+  __shared__ float part[256 * 8];
+  const int c8 = threadIdx.x % C8, lane = threadIdx.x / C8, lanes = 256 / C8;
+  const long long per = (rows + gridDim.x - 1) / gridDim.x;
+  const long long r0 = (long long)blockIdx.x * per, r1 = r0 + per < rows ? r0 + per : rows;
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (long long r = r0 + lane; r < r1; r += lanes) {
+    float v[8];
+    unpack8(__ldg(reinterpret_cast<const uint4*>(g) + r * C8 + c8), v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] += v[j];
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) part[threadIdx.x * 8 + j] = acc[j];
+  __syncthreads();
+  if (lane == 0) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float t = 0.f;
+      for (int l = 0; l < lanes; ++l) t += part[(l * C8 + c8) * 8 + j];
+      atomicAdd(out + c8 * 8 + j, t);
+    }
+  }
+}
+
 // ---------------------------------------------------------------- K13 decode
 // boxes = decode(anchors, deltas) with weights (wx, wy, ww, wh), clipped to the image.
 __global__ void __launch_bounds__(256)
@@ -372,6 +432,30 @@ extern "C" int b2f_roi_align_bwd(const void* const* feats, float* const* grads, 
   if (int rc = fill_pyramid(&p, feats, grads, H, W, scales, levels, C)) return rc;
   roi_align_kernel<true><<<grid1d((long long)R * P * P * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
       p, rois, R, P, sampling, nullptr, (const __nv_bfloat16*)dout, aligned, levels == 1 ? 0 : -1);
+  B2F_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b2f_bias_act_nhwc(void* y, const void* bias, const void* residual, long long numel, int C,
+                                 int relu, void* stream) {
+  if (numel == 0) return 0;
+  B2F_REQUIRE(C > 0 && C % 8 == 0 && numel % C == 0, "bias_act_nhwc: channels must be a multiple of 8");
+  bias_act_nhwc_kernel<<<grid1d(numel / 8), 256, 0, (cudaStream_t)stream>>>(
+      (__nv_bfloat16*)y, (const __nv_bfloat16*)bias, (const __nv_bfloat16*)residual, numel / 8, C / 8, relu);
+  B2F_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// out: fp32 [C], zeroed by the caller.  C a multiple of 8 with 256 % (C / 8) == 0.
+extern "C" int b2f_channel_sum_nhwc(const void* g, float* out, long long numel, int C, void* stream) {
+  if (numel == 0) return 0;
+  B2F_REQUIRE(C > 0 && C % 8 == 0 && 256 % (C / 8) == 0 && numel % C == 0,
+              "channel_sum_nhwc: channels must be 8 x a power of two up to 2048");
+  const long long rows = numel / C;
+  long long blocks = (rows + 255) / 256;
+  const long long cap = (long long)sm_count() * 4;
+  if (blocks > cap) blocks = cap;
+  channel_sum_nhwc_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)g, out, rows, C / 8);
   B2F_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

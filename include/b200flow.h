@@ -223,6 +223,12 @@ int b2f_roi_align_fwd(const void* const* feats, const int* H, const int* W, cons
 int b2f_roi_align_bwd(const void* const* feats, float* const* grads, const int* H, const int* W,
                       const float* scales, int levels, int C, const float* rois, int R, int P,
                       int sampling, int aligned, const void* dout, void* stream);
+/* y = act(y + bias[c] (+ residual)) in place, NHWC half precision, C % 8 == 0: the epilogue of a convolution whose
+ * frozen batch norm was folded into the weights (tensorpack BACKBONE.NORM=FreezeBN). */
+int b2f_bias_act_nhwc(void* y, const void* bias, const void* residual, long long numel, int C, int relu,
+                      void* stream);
+/* out[c] += sum over N, H, W of g[n, h, w, c] (bias gradient); out fp32 [C] zeroed by the caller. */
+int b2f_channel_sum_nhwc(const void* g, float* out, long long numel, int C, void* stream);
 int b2f_box_decode(const float* anchors, const float* deltas, float* out, long long n, float wx,
                    float wy, float ww, float wh, float img_w, float img_h, void* stream);
 /* mask_scratch: u64 [total_boxes * ceil(max_seg / 64)] */

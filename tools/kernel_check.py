@@ -496,6 +496,41 @@ def group_detection():
     import torchvision
     from b200flow.ops import detection as Dt
     torch.manual_seed(6)
+    # --- conv epilogue of the folded-BN backbone: y = relu(y + bias (+ residual)) in place, with gradients
+    for (n, c, h, w), with_res, relu in [((2, 64, 50, 84), False, True), ((3, 256, 25, 42), True, True),
+                                         ((2, 128, 13, 21), False, False)]:
+        x0 = torch.randn(n, c, h, w, device=DEV).to(HALF).contiguous(memory_format=torch.channels_last)
+        bias = torch.randn(c, device=DEV).to(HALF)
+        res = torch.randn(n, c, h, w, device=DEV).to(HALF).contiguous(memory_format=torch.channels_last) if with_res else None
+        xa = x0.clone().requires_grad_()
+        ra = res.clone().requires_grad_() if with_res else None
+        ya = Dt.bias_act_(xa * 1.0, bias, ra, relu)                   # * 1.0: a non-leaf the kernel may overwrite
+        xb = x0.float().requires_grad_()
+        rb = res.float().requires_grad_() if with_res else None
+        yb = xb + bias.float().view(1, -1, 1, 1) + (rb if with_res else 0.0)
+        yb = torch.relu(yb) if relu else yb
+        g = torch.randn_like(yb)
+        ya.backward(g.to(HALF))
+        yb.backward(g)
+        tag = f"{c}x{h}x{w}_res{int(with_res)}_relu{int(relu)}"
+        report(f"bias_act_fwd_{tag}", ya.permute(0, 2, 3, 1).reshape(-1, c), yb.permute(0, 2, 3, 1).reshape(-1, c), 1e-2)
+        report(f"bias_act_dx_{tag}", xa.grad.permute(0, 2, 3, 1).reshape(-1, c), xb.grad.permute(0, 2, 3, 1).reshape(-1, c), 1e-2)
+        if with_res:
+            report(f"bias_act_dres_{tag}", ra.grad.permute(0, 2, 3, 1).reshape(-1, c), rb.grad.permute(0, 2, 3, 1).reshape(-1, c), 1e-2)
+    # trainable bias through conv_bias_act: output and all three gradients against nn.Conv2d + relu in fp32
+    conv = torch.nn.Conv2d(64, 256, 3, padding=1).to(DEV).to(HALF).to(memory_format=torch.channels_last)
+    ref = torch.nn.Conv2d(64, 256, 3, padding=1).to(DEV)
+    ref.load_state_dict({k: v.float() for k, v in conv.state_dict().items()})
+    x0 = torch.randn(2, 64, 40, 56, device=DEV).to(HALF).contiguous(memory_format=torch.channels_last)
+    xa, xb = x0.clone().requires_grad_(), x0.float().requires_grad_()
+    ya, yb = Dt.conv_bias_act(xa, conv, relu=True), torch.relu(ref(xb))
+    g = torch.randn_like(yb)
+    ya.backward(g.to(HALF))
+    yb.backward(g)
+    report("conv_bias_act_fwd", ya.permute(0, 2, 3, 1).reshape(-1, 256), yb.permute(0, 2, 3, 1).reshape(-1, 256), 2e-2)
+    report("conv_bias_act_dbias", conv.bias.grad[None], ref.bias.grad[None], 2e-2)
+    report("conv_bias_act_dw", conv.weight.grad.reshape(256, -1), ref.weight.grad.reshape(256, -1), 3e-2)
+    report("conv_bias_act_dx", xa.grad.permute(0, 2, 3, 1).reshape(-1, 64), xb.grad.permute(0, 2, 3, 1).reshape(-1, 64), 3e-2)
     # --- K12 RoIAlign fwd/bwd vs torchvision CPU (fp32), multilevel
     C = 64
     shapes = [(2, 200, 336), (2, 100, 168), (2, 50, 84), (2, 25, 42)]
