@@ -115,6 +115,31 @@ class P2P:
         self.prev, self.next = prev_rank, next_rank
         self.shape, self.dtype, self.device, self.group = tuple(shape), dtype, device, group
 
+        self._connected = False
+
+    def connect(self):
+        """Open both directions of every stage boundary before the schedule starts, one direction per call.  NCCL
+        connects a peer lazily inside the first group that names it; with a single micro-batch the first stage's first
+        group is "send forward + receive backward" while its neighbour's is "receive forward" alone, and that
+        asymmetric first contact fails inside NCCL's bootstrap exchange (2.28: "Message truncated").  After this the
+        schedule may mix directions freely."""
+        if self._connected or not dist.is_initialized():
+            return
+        self._connected = True
+        one = torch.zeros(1, dtype=self.dtype, device=self.device)
+        ops = []
+        if self.next is not None:
+            ops.append(dist.P2POp(dist.isend, one, self.next, self.group))
+        if self.prev is not None:
+            ops.append(dist.P2POp(dist.irecv, torch.empty_like(one), self.prev, self.group))
+        self._run(ops)
+        ops = []
+        if self.prev is not None:
+            ops.append(dist.P2POp(dist.isend, one, self.prev, self.group))
+        if self.next is not None:
+            ops.append(dist.P2POp(dist.irecv, torch.empty_like(one), self.next, self.group))
+        self._run(ops)
+
     def _buf(self):
         return torch.empty(self.shape, dtype=self.dtype, device=self.device)
 
@@ -126,7 +151,12 @@ class P2P:
 
     def exchange(self, send_fwd=None, send_bwd=None, recv_fwd=False, recv_bwd=False):
         """Post every requested send/recv as ONE group; returns (activation_in, grad_in)."""
+        self.connect()
         ops, act_in, grad_in = [], None, None
+        for t in (send_fwd, send_bwd):
+            if t is not None and (tuple(t.shape) != self.shape or t.dtype != self.dtype):
+                raise ValueError(f"pipeline boundary tensor {tuple(t.shape)} {t.dtype} does not match the agreed "
+                                 f"{self.shape} {self.dtype}")
         if send_fwd is not None and self.next is not None:
             ops.append(dist.P2POp(dist.isend, send_fwd.contiguous(), self.next, self.group))
         if send_bwd is not None and self.prev is not None:

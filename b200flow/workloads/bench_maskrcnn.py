@@ -27,7 +27,8 @@ def run_maskrcnn_bench(args, rank, world, dev, ClockSampler, emit=None):
     model = MaskRCNN(MaskRCNNConfig()).to(dev).to(torch.bfloat16).to(memory_format=torch.channels_last)
     ddp = DistributedDataParallel(model, fused=not args.no_fused) if world > 1 else None
     flat = ddp.flat if ddp is not None else FlatParams(model)
-    opt = FlatMomentumSGD(flat, lr=0.01 * world * batch / 8.0, momentum=0.9, weight_decay=1e-4)
+    peak_lr = 0.01 * world * batch / 8.0
+    opt = FlatMomentumSGD(flat, lr=peak_lr, momentum=0.9, weight_decay=1e-4)
     model.train()
     data = coco_like(10 ** 9, H, W, seed=1000 + rank, device="cpu")
 
@@ -51,6 +52,9 @@ def run_maskrcnn_bench(args, rank, world, dev, ClockSampler, emit=None):
         if src is host:
             im = im.to(dev, non_blocking=True)
             tg = [{k: v.to(dev, non_blocking=True) for k, v in t.items()} for t in tg]
+        # linear-scaling rule with a linear warm-up (tensorpack warms up as well): at 8 GPUs the full rate of 0.04
+        # from a cold start diverges on a randomly initialised backbone
+        opt.param_groups[0]["lr"] = peak_lr * min(1.0, (state["i"] + 1) / 100.0)
         opt.zero_grad()
         losses = model(im, tg)
         losses["total"].backward()
@@ -98,7 +102,8 @@ def run_maskrcnn_bench(args, rank, world, dev, ClockSampler, emit=None):
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "b200flow",
             "config": {"model": "maskrcnn-r50-fpn", "global_batch": gb, "image": [H, W],
                        "parallelism": f"dp{world}", "l2_policy": "activations per step >> 126 MB L2",
-                       "fused_collectives": not args.no_fused, "trunk_cuda_graph": graphed},
+                       "fused_collectives": not args.no_fused, "trunk_cuda_graph": graphed,
+                       "lr": f"{peak_lr:g} (0.01 x global batch / 8), linear warm-up over 100 steps"},
             "clocks": clocks.summary(),
             "e2e": {"value": gb * args.steps / (ms_e2e / 1e3), "unit": "images/s",
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},

@@ -523,7 +523,11 @@ def group_detection():
     ref.load_state_dict({k: v.float() for k, v in conv.state_dict().items()})
     x0 = torch.randn(2, 64, 40, 56, device=DEV).to(HALF).contiguous(memory_format=torch.channels_last)
     xa, xb = x0.clone().requires_grad_(), x0.float().requires_grad_()
-    ya, yb = Dt.conv_bias_act(xa, conv, relu=True), torch.relu(ref(xb))
+    # no ReLU here: a bf16 and an fp32 convolution disagree on the sign of outputs near zero, which flips mask bits and
+    # shows up as noise in every gradient; the ReLU backward is checked above on identical inputs
+    report("conv_bias_act_relu_fwd", Dt.conv_bias_act(x0, conv, relu=True).permute(0, 2, 3, 1).reshape(-1, 256),
+           torch.relu(ref(x0.float())).permute(0, 2, 3, 1).reshape(-1, 256), 2e-2)
+    ya, yb = Dt.conv_bias_act(xa, conv, relu=False), ref(xb)
     g = torch.randn_like(yb)
     ya.backward(g.to(HALF))
     yb.backward(g)
