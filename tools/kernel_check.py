@@ -488,6 +488,28 @@ def group_attn_perf():
             rec["sdpa_fwd_tflops"] = fl / t_ref / 1e9
         except Exception as e:  # noqa: BLE001
             rec["sdpa_error"] = repr(e)[:200]
+        # backward of the libraries this kernel replaces: SDPA (cuDNN / flash backend torch picks) and flash_attn 2.8
+        try:
+            qs, ks, vs = (t.transpose(1, 2).detach().clone().requires_grad_() for t in (q, k, v))
+            os_ = torch.nn.functional.scaled_dot_product_attention(qs, ks, vs, is_causal=causal)
+            gs = torch.randn_like(os_)
+            t_rb = timeit(lambda: torch.autograd.grad(os_, (qs, ks, vs), gs, retain_graph=True))
+            rec["sdpa_bwd_ms"] = t_rb
+            rec["sdpa_bwd_tflops"] = 2.5 * fl / t_rb / 1e9
+        except Exception as e:  # noqa: BLE001
+            rec["sdpa_bwd_error"] = repr(e)[:200]
+        try:
+            from flash_attn import flash_attn_func
+
+            qf, kf, vf = (t.detach().clone().requires_grad_() for t in (q, k, v))
+            t_ff = timeit(lambda: flash_attn_func(qf, kf, vf, causal=causal))
+            of = flash_attn_func(qf, kf, vf, causal=causal)
+            gf = torch.randn_like(of)
+            t_fb = timeit(lambda: torch.autograd.grad(of, (qf, kf, vf), gf, retain_graph=True))
+            rec.update(flash_attn_fwd_ms=t_ff, flash_attn_fwd_tflops=fl / t_ff / 1e9, flash_attn_bwd_ms=t_fb,
+                       flash_attn_bwd_tflops=2.5 * fl / t_fb / 1e9)
+        except Exception as e:  # noqa: BLE001
+            rec["flash_attn_error"] = repr(e)[:200]
         print(json.dumps(rec), flush=True)
         RESULTS.append({"name": rec["name"], "ok": True})
 
