@@ -79,7 +79,7 @@ def roi_align(feats_nhwc: list[torch.Tensor], scales: list[float], rois: torch.T
 class _BiasAct(torch.autograd.Function):
     """y <- act(y + bias[c] (+ residual)) in place on a channels-last activation (`b2f_bias_act_nhwc`).  `bias` is
     either a constant (the shift of a folded frozen batch norm) or a trainable convolution bias, whose gradient is the
-    channel sum of the incoming gradient (`b2f_channel_sum_nhwc`)."""
+    column sum of the incoming gradient over N, H, W (`ops.elementwise.colsum`)."""
 
     @staticmethod
     def forward(ctx, y, bias, residual, relu):
@@ -99,19 +99,18 @@ class _BiasAct(torch.autograd.Function):
             g = torch.ops.aten.threshold_backward(g, out, 0)
         db = None
         if ctx.needs_input_grad[1]:
+            from .elementwise import colsum
+
             g = g.contiguous(memory_format=torch.channels_last)
-            acc = torch.zeros(g.shape[1], dtype=torch.float32, device=g.device)
-            _lib.call("b2f_channel_sum_nhwc", ptr(g), ptr(acc), c_ll(g.numel()), c_int(g.shape[1]), stream_ptr())
-            db = acc.to(ctx.bias_dtype)
+            C = g.shape[1]
+            db = colsum(g.permute(0, 2, 3, 1).reshape(-1, C)).to(ctx.bias_dtype)      # NHWC memory as [N*H*W, C]
         return g, db, (g if ctx.has_res else None), None
 
 
 def bias_act_(y: torch.Tensor, bias: torch.Tensor, residual: torch.Tensor | None = None, relu: bool = True):
     """In place on the convolution output `y` [N, C, H, W]: y = act(y + bias.view(1, C, 1, 1) (+ residual))."""
-    C8 = y.shape[1] // 8 if y.dim() == 4 else 0
     fast = (y.is_cuda and y.dtype == _lib.HALF and y.dim() == 4 and y.shape[1] % 8 == 0
             and y.is_contiguous(memory_format=torch.channels_last) and bias.dtype == y.dtype and bias.is_contiguous()
-            and (not bias.requires_grad or (C8 <= 256 and 256 % C8 == 0))
             and (residual is None or (residual.shape == y.shape and residual.dtype == y.dtype
                                       and residual.is_contiguous(memory_format=torch.channels_last))))
     if fast:

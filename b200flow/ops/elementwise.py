@@ -7,6 +7,20 @@ from . import _lib
 from ._lib import c_float, c_int, c_ll, c_ull, ptr, stream_ptr
 
 
+def colsum(x: torch.Tensor) -> torch.Tensor:
+    """x.sum(0) of a half-precision [rows, C] matrix with fp32 accumulation (bias gradients): one pass at memory speed
+    (`b2f_colsum_partial`) plus a small deterministic reduction of the per-block partial rows.  Falls back to torch for
+    other dtypes / layouts / CPU."""
+    if not (x.is_cuda and x.dim() == 2 and x.dtype == _lib.HALF and x.is_contiguous() and x.shape[1] % 8 == 0
+            and x.shape[0] > 0):
+        return x.sum(0)
+    rows, C = x.shape
+    nb = _lib.cuda_lib().b2f_colsum_num_partials(c_ll(rows), c_int(C))
+    partial = torch.empty((nb, C), dtype=torch.float32, device=x.device)
+    _lib.call("b2f_colsum_partial", ptr(x), ptr(partial), c_ll(rows), c_int(C), stream_ptr())
+    return partial.sum(0).to(x.dtype)
+
+
 # ------------------------------------------------------------------ SwiGLU
 class _SwiGLU(torch.autograd.Function):
     @staticmethod

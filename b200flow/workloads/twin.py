@@ -302,7 +302,7 @@ def run_twin(args, rank, world, dev, ClockSampler):
         gen = torch.Generator().manual_seed(77 + rank)
 
         def make():
-            t = zipf_tokens(32000, (batch, seq + 1), generator=gen)
+            t = torch.randint(0, 32000, (batch, seq + 1), generator=gen)       # as bench.py's Llama arm
             return {"tokens": t[:, :-1].contiguous(), "labels": t[:, 1:].contiguous()}
 
         def loss_fn(mod, b):

@@ -242,12 +242,11 @@ def main():
         "fused_collectives": not args.no_fused,
         "pipeline": {"zero_bubble": not args.no_zero_bubble},
     }
-    # Linear warm-up of the rate, as the Megatron / DeepSpeed recipes of both models do (--lr-warmup-*): from a cold
-    # start at the full rate the loss first climbs for several steps (fused and NCCL arms, bf16 and fp8 experts alike:
-    # profiles/r2_call4_*, r2_call15_*), which says nothing about the kernels and makes the curves hard to read.
-    ds_config["scheduler"] = {"type": "WarmupLR", "params": {"warmup_min_lr": 0.0, "warmup_max_lr": 1.5e-4,
-                                                             "warmup_num_steps": 16 if is_moe else 8,
-                                                             "warmup_type": "linear"}}
+    if is_moe:
+        # the DeepSpeed-MoE recipes warm the rate up; from a cold start at the full rate the loss of this model
+        # first climbs for a dozen steps (bf16 and fp8 experts alike, profiles/r2_call4_*)
+        ds_config["scheduler"] = {"type": "WarmupLR", "params": {"warmup_min_lr": 0.0, "warmup_max_lr": 1.5e-4,
+                                                                 "warmup_num_steps": 16, "warmup_type": "linear"}}
     engine = initialize(cfg, ds_config, ps, device=dev)
     B, S = args.micro_batch, args.seq
     tokens_per_step = B * S * args.gas * dp
@@ -257,7 +256,13 @@ def main():
 
     g = torch.Generator().manual_seed(1234 + (ps.dp_rank if ps else 0))
     n_host = args.gas * 2
-    host = [zipf_tokens(cfg.vocab_size, (B, S + 1), generator=g).pin_memory() for _ in range(n_host)]
+    # MoE: Zipf-distributed tokens, so the router sees a skewed load and the loss has a unigram distribution to learn
+    # (11.4 -> 7.6 in 18 steps, profiles/r2_call15_*, r2_call19_20_*).  Dense Llama: uniform tokens over a fixed set of
+    # 2 x accumulation-steps micro-batches, which the 7B model memorises within a few steps at a constant rate (loss
+    # 11.2 -> 0.02); on Zipf tokens the first full-rate Adam steps of the 7B model overshoot instead (r2_call15, r2_call23).
+    draw = (lambda: zipf_tokens(cfg.vocab_size, (B, S + 1), generator=g)) if is_moe else \
+        (lambda: torch.randint(0, cfg.vocab_size, (B, S + 1), generator=g))
+    host = [draw().pin_memory() for _ in range(n_host)]
     dev_batches = [(h[:, :-1].to(dev), h[:, 1:].to(dev)) for h in host]
 
     def device_iter():

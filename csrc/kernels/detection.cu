@@ -170,31 +170,39 @@ bias_act_nhwc_kernel(__nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restr
   }
 }
 
-// out[c] += sum over rows of g[row, c] for an NHWC half-precision gradient (the bias gradient of a convolution).
-// 256 threads = (256 / C8) row lanes x C8 channel groups of eight; fp32 partial sums in registers, one shared-memory
-// reduction per block, then one atomic per channel per block.
+// Column sums of a half-precision [rows, C] matrix (bias gradients: of a linear layer, or of a convolution over an NHWC
+// gradient) as per-block partial sums: partial[blockIdx.x][c] = sum over this block's rows.  A block covers up to 256
+// groups of eight channels (blockIdx.y selects which) with 256 / groups row lanes; fp32 accumulation in registers, one
+// shared-memory reduction over the lanes, no atomics - the caller adds the few hundred partial rows, so the result
+// does not depend on scheduling.
 __global__ void __launch_bounds__(256)
-channel_sum_nhwc_kernel(const __nv_bfloat16* __restrict__ g, float* __restrict__ out, long long rows, int C8) {
+colsum_partial_kernel(const __nv_bfloat16* __restrict__ g, float* __restrict__ partial, long long rows, int C8) {
   __shared__ float part[256 * 8];
-  const int c8 = threadIdx.x % C8, lane = threadIdx.x / C8, lanes = 256 / C8;
+  const int g0 = blockIdx.y * 256;
+  const int G = C8 - g0 < 256 ? C8 - g0 : 256;
+  const int lanes = 256 / G;
+  const int c8 = threadIdx.x % G, lane = threadIdx.x / G;
   const long long per = (rows + gridDim.x - 1) / gridDim.x;
   const long long r0 = (long long)blockIdx.x * per, r1 = r0 + per < rows ? r0 + per : rows;
   float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  for (long long r = r0 + lane; r < r1; r += lanes) {
-    float v[8];
-    unpack8(__ldg(reinterpret_cast<const uint4*>(g) + r * C8 + c8), v);
+  if (lane < lanes) {
+    for (long long r = r0 + lane; r < r1; r += lanes) {
+      float v[8];
+      unpack8(__ldg(reinterpret_cast<const uint4*>(g) + r * C8 + g0 + c8), v);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] += v[j];
+      for (int j = 0; j < 8; ++j) acc[j] += v[j];
+    }
   }
 #pragma unroll
   for (int j = 0; j < 8; ++j) part[threadIdx.x * 8 + j] = acc[j];
   __syncthreads();
   if (lane == 0) {
+    float* dst = partial + (long long)blockIdx.x * C8 * 8 + (long long)(g0 + c8) * 8;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       float t = 0.f;
-      for (int l = 0; l < lanes; ++l) t += part[(l * C8 + c8) * 8 + j];
-      atomicAdd(out + c8 * 8 + j, t);
+      for (int l = 0; l < lanes; ++l) t += part[(l * G + c8) * 8 + j];
+      dst[j] = t;
     }
   }
 }
@@ -446,16 +454,21 @@ extern "C" int b2f_bias_act_nhwc(void* y, const void* bias, const void* residual
   return 0;
 }
 
-// out: fp32 [C], zeroed by the caller.  C a multiple of 8 with 256 % (C / 8) == 0.
-extern "C" int b2f_channel_sum_nhwc(const void* g, float* out, long long numel, int C, void* stream) {
-  if (numel == 0) return 0;
-  B2F_REQUIRE(C > 0 && C % 8 == 0 && 256 % (C / 8) == 0 && numel % C == 0,
-              "channel_sum_nhwc: channels must be 8 x a power of two up to 2048");
-  const long long rows = numel / C;
-  long long blocks = (rows + 255) / 256;
-  const long long cap = (long long)sm_count() * 4;
+// Number of partial rows b2f_colsum_partial writes for a matrix of `rows` rows and C columns.
+extern "C" int b2f_colsum_num_partials(long long rows, int C) {
+  const int ychunks = (C / 8 + 255) / 256;
+  long long blocks = (rows + 127) / 128;
+  long long cap = (long long)sm_count() * 4 / ychunks;
+  if (cap < 1) cap = 1;
   if (blocks > cap) blocks = cap;
-  channel_sum_nhwc_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)g, out, rows, C / 8);
+  return blocks < 1 ? 1 : (int)blocks;
+}
+
+// partial: fp32 [b2f_colsum_num_partials(rows, C), C]; every element is written.  C % 8 == 0.
+extern "C" int b2f_colsum_partial(const void* g, float* partial, long long rows, int C, void* stream) {
+  B2F_REQUIRE(C > 0 && C % 8 == 0 && rows >= 0, "colsum: columns must be a multiple of 8");
+  dim3 grid(b2f_colsum_num_partials(rows, C), (C / 8 + 255) / 256);
+  colsum_partial_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)g, partial, rows, C / 8);
   B2F_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -227,8 +227,10 @@ int b2f_roi_align_bwd(const void* const* feats, float* const* grads, const int* 
  * frozen batch norm was folded into the weights (tensorpack BACKBONE.NORM=FreezeBN). */
 int b2f_bias_act_nhwc(void* y, const void* bias, const void* residual, long long numel, int C, int relu,
                       void* stream);
-/* out[c] += sum over N, H, W of g[n, h, w, c] (bias gradient); out fp32 [C] zeroed by the caller. */
-int b2f_channel_sum_nhwc(const void* g, float* out, long long numel, int C, void* stream);
+/* Column sums of a half-precision [rows, C] matrix (bias gradient of a linear layer, or of a convolution over an NHWC
+ * gradient) as fp32 partial rows partial[b2f_colsum_num_partials(rows, C)][C]; the caller adds the partial rows. */
+int b2f_colsum_num_partials(long long rows, int C);
+int b2f_colsum_partial(const void* g, float* partial, long long rows, int C, void* stream);
 int b2f_box_decode(const float* anchors, const float* deltas, float* out, long long n, float wx,
                    float wy, float ww, float wh, float img_w, float img_h, void* stream);
 /* mask_scratch: u64 [total_boxes * ceil(max_seg / 64)] */

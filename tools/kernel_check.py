@@ -539,6 +539,14 @@ def group_detection():
         report(f"bias_act_dx_{tag}", xa.grad.permute(0, 2, 3, 1).reshape(-1, c), xb.grad.permute(0, 2, 3, 1).reshape(-1, c), 1e-2)
         if with_res:
             report(f"bias_act_dres_{tag}", ra.grad.permute(0, 2, 3, 1).reshape(-1, c), rb.grad.permute(0, 2, 3, 1).reshape(-1, c), 1e-2)
+    # column sums (bias gradients) against fp32
+    from b200flow.ops import elementwise as Ew
+    for rows, cols in [(32768, 1024), (4096, 3072), (1000, 4096), (7, 8), (5000, 264)]:
+        x = torch.randn(rows, cols, device=DEV).to(HALF)
+        report(f"colsum_{rows}x{cols}", Ew.colsum(x)[None], x.float().sum(0)[None], 1e-2)
+    x = torch.randn(32768, 1024, device=DEV).to(HALF)
+    ms_a, ms_b = timeit(lambda: Ew.colsum(x)), timeit(lambda: x.sum(0))
+    print(json.dumps({"name": "colsum_perf_32768x1024", "ms": ms_a, "torch_sum_ms": ms_b, "gbs": x.numel() * 2 / ms_a / 1e6}), flush=True)
     # trainable bias through conv_bias_act: output and all three gradients against nn.Conv2d + relu in fp32
     conv = torch.nn.Conv2d(64, 256, 3, padding=1).to(DEV).to(HALF).to(memory_format=torch.channels_last)
     ref = torch.nn.Conv2d(64, 256, 3, padding=1).to(DEV)
