@@ -8,9 +8,10 @@ from ._lib import c_float, c_int, c_ll, c_ull, ptr, stream_ptr
 
 
 def colsum(x: torch.Tensor) -> torch.Tensor:
-    """x.sum(0) of a half-precision [rows, C] matrix with fp32 accumulation (bias gradients): one pass at memory speed
-    (`b2f_colsum_partial`) plus a small deterministic reduction of the per-block partial rows.  Falls back to torch for
-    other dtypes / layouts / CPU."""
+    """x.sum(0) of a half-precision [rows, C] matrix with fp32 accumulation: one pass (`b2f_colsum_partial`) plus a small
+    deterministic reduction of the per-block partial rows.  Used for convolution bias gradients over NHWC memory, where
+    torch's reduction is 2-3x slower; for row-major linear-layer gradients torch's own sum is as fast (measured 49 vs
+    54 us at 32768 x 1024), so those keep `.sum(0)`.  Falls back to torch for other dtypes / layouts / CPU."""
     if not (x.is_cuda and x.dim() == 2 and x.dtype == _lib.HALF and x.is_contiguous() and x.shape[1] % 8 == 0
             and x.shape[0] > 0):
         return x.sum(0)

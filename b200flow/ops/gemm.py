@@ -21,12 +21,6 @@ EPI_GELU, EPI_OUT_F32, EPI_ACCUM, EPI_RELU, EPI_BIAS_ROW, EPI_DGELU = 1, 2, 4, 8
 GEMM_IMPL = os.environ.get("B2F_GEMM", "2cta")
 
 
-def _colsum(x):
-    from .elementwise import colsum      # bias gradient: one pass, fp32 accumulation
-
-    return colsum(x.reshape(-1, x.shape[-1]))
-
-
 def _entry(M: int, N: int) -> str:
     if GEMM_IMPL == "2cta" and M >= 256 and N >= 256:
         return "b2f_gemm_bf16_2cta"
@@ -163,7 +157,9 @@ class _LinearCPU(torch.autograd.Function):
             y = y + residual.reshape(-1, weight.shape[0])
         ctx.save_for_backward(x2, weight)
         ctx.has_bias, ctx.has_res, ctx.x_shape = bias is not None, residual is not None, x.shape
-        return y.reshape(*x.shape[:-1], weight.shape[0])
+        # 2-D input: hand out y itself, not a same-shape view of it - the vocab-parallel loss turns the logits into their
+        # gradient in place, which autograd refuses on a view created inside a custom Function
+        return y if x.dim() == 2 else y.reshape(*x.shape[:-1], weight.shape[0])
 
     @staticmethod
     def backward(ctx, dy):
@@ -171,7 +167,7 @@ class _LinearCPU(torch.autograd.Function):
         dy2 = dy.reshape(-1, dy.shape[-1])
         dx = (dy2 @ weight).reshape(ctx.x_shape) if ctx.needs_input_grad[0] else None
         dw = _wgrad(x2, dy2, weight)
-        return dx, dw, (_colsum(dy2) if ctx.has_bias else None), (dy if ctx.has_res else None)
+        return dx, dw, (dy2.sum(0) if ctx.has_bias else None), (dy if ctx.has_res else None)
 
 
 class _Linear(torch.autograd.Function):
@@ -194,7 +190,7 @@ class _Linear(torch.autograd.Function):
             dy2 = dy2.contiguous()
         dx = gemm(dy2, weight, b_mn_major=True).reshape(ctx.x_shape) if ctx.needs_input_grad[0] else None
         dw = _wgrad(x2, dy2, weight)
-        db = _colsum(dy2) if ctx.has_bias else None
+        db = dy2.sum(0) if ctx.has_bias else None
         return dx, dw, db, (dy if ctx.has_res else None)
 
 
@@ -230,7 +226,7 @@ class _LinearGelu(torch.autograd.Function):
         dpre = gelu_bwd_raw(pre, None, dy2)
         dx = gemm(dpre, weight, b_mn_major=True).reshape(ctx.x_shape)
         dw = _wgrad(x2, dpre, weight)
-        return dx, dw, _colsum(dpre)
+        return dx, dw, dpre.sum(0)
 
 
 class _MlpGelu(torch.autograd.Function):
@@ -256,10 +252,10 @@ class _MlpGelu(torch.autograd.Function):
             dy2 = dy2.contiguous()
         dpre = gemm(dy2, w2, b_mn_major=True, residual=pre, dgelu=True)
         dw2 = _wgrad(h, dy2, w2)
-        db2 = _colsum(dy2) if ctx.has_b[1] else None
+        db2 = dy2.sum(0) if ctx.has_b[1] else None
         dx = gemm(dpre, w1, b_mn_major=True).reshape(ctx.x_shape) if ctx.needs_input_grad[0] else None
         dw1 = _wgrad(x2, dpre, w1)
-        db1 = _colsum(dpre) if ctx.has_b[0] else None
+        db1 = dpre.sum(0) if ctx.has_b[0] else None
         return dx, dw1, db1, dw2, db2
 
 

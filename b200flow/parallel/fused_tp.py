@@ -22,12 +22,6 @@ from ..ops import gemm as G
 from ..ops._lib import c_int, c_ll, ptr, stream_ptr
 
 
-def _colsum(x):
-    from ..ops.elementwise import colsum      # bias gradient: one pass, fp32 accumulation
-
-    return colsum(x.reshape(-1, x.shape[-1]))
-
-
 class FusedTP:
     FLAG_WORDS = 1 << 16
 
@@ -166,7 +160,7 @@ class _FusedColumn(torch.autograd.Function):
         dy = dy.contiguous()
         dx = ctx.ftp.gemm_rs(dy, w, b_mn_major=True)          # dgrad fused with its reduce-scatter
         dw = G._wgrad(xg, dy, w)
-        return dx, dw, (_colsum(dy) if ctx.has_bias else None), None
+        return dx, dw, (dy.sum(0) if ctx.has_bias else None), None
 
 
 class _FusedRow(torch.autograd.Function):
@@ -184,7 +178,7 @@ class _FusedRow(torch.autograd.Function):
         dy = dy.contiguous()
         dx, dyg = ctx.ftp.ag_gemm(dy, w, b_mn_major=True)      # all-gather fused with dgrad
         dw = G._wgrad(x, dyg, w)
-        return dx, dw, (_colsum(dy) if ctx.has_bias else None), (dy if ctx.has_res else None), None
+        return dx, dw, (dy.sum(0) if ctx.has_bias else None), (dy if ctx.has_res else None), None
 
 
 class _FusedColumnAR(torch.autograd.Function):
@@ -203,7 +197,7 @@ class _FusedColumnAR(torch.autograd.Function):
         dy = dy.contiguous()
         dx = ctx.ftp.gemm_ar(dy, w, b_mn_major=True)
         dw = G._wgrad(x, dy, w)
-        return dx, dw, (_colsum(dy) if ctx.has_bias else None), None
+        return dx, dw, (dy.sum(0) if ctx.has_bias else None), None
 
 
 class _FusedRowAR(torch.autograd.Function):
@@ -223,4 +217,4 @@ class _FusedRowAR(torch.autograd.Function):
         dy = dy.contiguous()
         dx = G.gemm(dy, w, b_mn_major=True)
         dw = G._wgrad(x, dy, w)
-        return dx, dw, (_colsum(dy) if ctx.has_bias else None), (dy if ctx.has_res else None), None
+        return dx, dw, (dy.sum(0) if ctx.has_bias else None), (dy if ctx.has_res else None), None

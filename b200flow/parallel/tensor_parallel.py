@@ -38,12 +38,6 @@ _FUSED_AR = os.environ.get("B2F_FUSED_AR", "1") == "1"   # B2F_FUSED_AR=0: NCCL 
 # ---------------------------------------------------------------- primitives
 
 
-def _colsum(x):
-    from ..ops.elementwise import colsum      # bias gradient: one pass, fp32 accumulation
-
-    return colsum(x.reshape(-1, x.shape[-1]))
-
-
 def _mm(x, w, bias=None, residual=None):
     """x [M,K] · w[N,K]ᵀ (+bias) (+residual)."""
     if x.is_cuda:
@@ -99,7 +93,7 @@ class _ColumnSP(torch.autograd.Function):
         dxg = _mm_dgrad(dy, w)
         dx = ctx.tp.reduce_scatter_rows(dxg)
         dw = _mm_wgrad(xg, dy, w)
-        return dx, dw, (_colsum(dy) if ctx.has_bias else None), None
+        return dx, dw, (dy.sum(0) if ctx.has_bias else None), None
 
 
 class _RowSP(torch.autograd.Function):
@@ -121,7 +115,7 @@ class _RowSP(torch.autograd.Function):
         dyg = ctx.tp.all_gather_rows(dy.contiguous())
         dx = _mm_dgrad(dyg, w)
         dw = _mm_wgrad(x, dyg, w)
-        return dx, dw, (_colsum(dy) if ctx.has_bias else None), (dy if ctx.has_res else None), None
+        return dx, dw, (dy.sum(0) if ctx.has_bias else None), (dy if ctx.has_res else None), None
 
 
 class _CopyToTP(torch.autograd.Function):

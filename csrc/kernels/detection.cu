@@ -186,6 +186,7 @@ colsum_partial_kernel(const __nv_bfloat16* __restrict__ g, float* __restrict__ p
   const long long r0 = (long long)blockIdx.x * per, r1 = r0 + per < rows ? r0 + per : rows;
   float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (lane < lanes) {
+#pragma unroll 4
     for (long long r = r0 + lane; r < r1; r += lanes) {
       float v[8];
       unpack8(__ldg(reinterpret_cast<const uint4*>(g) + r * C8 + g0 + c8), v);

@@ -40,3 +40,13 @@ def test_tensor_parallel_without_sequence_parallel_uses_gemm_allreduce():
 
 def test_tp_pp_engines_and_moe_expert_parallel():
     _run(["tp", "pp", "moe_ep"])
+
+
+def test_fused_moe_k5_expert_parallel():
+    """K5 (dispatch + MX-fp8 GEMM 1, MX-fp8 GEMM 2 + combine) over two GPUs against the three-phase path."""
+    _run(["moe_k5"])
+
+
+def test_ulysses_sequence_parallel_through_the_engine():
+    """DeepSpeed-Ulysses (sequence <-> head all-to-all around the attention node) on GPUs against one GPU."""
+    _run(["ulysses"])
