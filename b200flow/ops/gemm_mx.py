@@ -5,6 +5,10 @@
 `tcgen05.cp`; `MxTensor` keeps values and scales together.  The MoE expert FFNs of BASELINE.json config 5 run their
 forward and dgrad GEMMs on this kernel (parallel/moe.py, csrc/comm/fused_moe.cu); wgrad stays bf16 with fp32
 accumulation from the dequantised operands, since the scale blocks run along the hidden dimension, not along tokens.
+
+Reference capability: the MoE expert FFNs of the pinned DeepSpeed 0.13.4 / Megatron-DeepSpeed a9856ce
+(containers/megatron-deepspeed/Dockerfile:12-13, `--num-experts` of the gpt2_345m examples) run on cuBLAS in fp16 / bf16;
+BASELINE.json config 5 asks for them in block-scaled fp8.
 """
 from __future__ import annotations
 

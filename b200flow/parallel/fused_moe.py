@@ -21,6 +21,11 @@ kernel of call e, which runs after that peer's UP kernel of call e has consumed 
 has at least launched call e, so when it writes parity (e+1) & 1 everyone is done reading the data of call e-1.  The
 counters of the other parity are cleared on the stream right before a call's kernels, i.e. before this rank's own
 tokens of the call leave, without which no peer can complete the call.
+
+Reference capability: DeepSpeed-MoE's `MOELayer` (einsum dispatch -> `all_to_all_single` -> experts -> `all_to_all_single`
+-> einsum combine) as pinned by containers/megatron-deepspeed/Dockerfile:12-13 and switched on by the `--num-experts /
+--moe-expert-parallel-size` flags of Megatron-DeepSpeed's `pretrain_gpt.py` (the entry point of
+examples/megatron-deepspeed/gpt2_345m/pretrain-ddp-zero1.yaml:74-85); SURVEY.md §2F "EP", §2H C13-C15, §8 K5.
 """
 from __future__ import annotations
 

@@ -1,5 +1,7 @@
 // b200flow K0 (block-scaled fp8) — MXFP8 quantiser / dequantiser and the plain block-scaled GEMM entry point.
-// See gemm_mx_core.cuh for the kernel body and the scale-factor layout.
+// See gemm_mx_core.cuh for the kernel body and the scale-factor layout.  Capability parity: the expert GEMMs of the
+// DeepSpeed-MoE / Megatron-DeepSpeed stack the reference pins (containers/megatron-deepspeed/Dockerfile:12-13), which
+// BASELINE.json config 5 runs in block-scaled fp8.
 #include "gemm_mx_core.cuh"
 #include "../common/host.h"
 #include "../../include/b200flow.h"
