@@ -75,7 +75,9 @@ def _script_lines(values: dict, workload_key: str, strict_exit: bool) -> list[st
     work = values.get(workload_key) or {}
     for item in list(work.get("command") or []) + list(work.get("args") or []):
         out.append(f"{item} \\")
-    out.append('&& echo "Training script done"')
+    # charts/machine-learning/data-prep/data-process/templates/data-process.yaml:38 says "Processing", the four
+    # training charts say "Training" (…/templates/train.yaml:38)
+    out.append('&& echo "Processing script done"' if workload_key == "process" else '&& echo "Training script done"')
     if strict_exit:
         out.append("B2F_STATUS=$?")
     out += [str(line) for line in (values.get("post_script") or [])]

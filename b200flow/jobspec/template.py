@@ -5,7 +5,10 @@ Supported (SURVEY.md §2B "Go-template features actually used"): `.Release.Name`
 `range`, pipelines `a | f`, string / int literals, and the functions `tpl`, `int`, `gt`,
 `ge`, `lt`, `le`, `eq`, `ne`, `and`, `or`, `not`, `add`, `sub`, `mul`, `div`, `required`,
 `default`, `quote`, `toString`, `date` (Go reference-time layouts) plus the control actions
-`if / else if / else / end`, `range / end`, and `{{-` / `-}}` whitespace trimming.
+`if / else if / else / end`, `range / end`, `with / end`, template variables (`$x := v`, `$x = v`,
+`range $v := ...`, `range $k, $v := ...`, `$x.field`, `$` for the root) and `{{-` / `-}}` whitespace
+trimming - enough to evaluate the reference's chart templates themselves, which `tests/test_chart_templates.py`
+does to hold `jobspec/render.py` against them.
 
 E.g. `"{{ mul .Values.resources.gpu_nodes .Values.resources.gpus_per_node }}"`
 (charts/machine-learning/training/mpijob-horovod-tensorflow-gpu/values.yaml:64-65) and
@@ -31,12 +34,14 @@ _ACTION = re.compile(r"\{\{(-?)(.*?)(-?)\}\}", re.S)
 
 @dataclass
 class _Node:
-    kind: str                      # text | expr | if | range
+    kind: str                      # text | expr | if | range | with | assign
     text: str = ""
     expr: str = ""
     branches: list = field(default_factory=list)   # if: [(cond_expr|None, [nodes])]
     body: list = field(default_factory=list)       # range body
     else_body: list = field(default_factory=list)
+    names: tuple = ()              # range: ($key, $value) or ($value,); assign: ($name,)
+    declare: bool = False          # assign: `:=` (new variable in this scope) vs `=` (nearest enclosing one)
 
 
 def _lex(src: str):
@@ -57,6 +62,10 @@ def _lex(src: str):
         if tok[0] == "action" and tok[2] and i + 1 < len(out):
             out[i + 1][1] = out[i + 1][1].lstrip()
     return [(t[0], t[1]) for t in out]
+
+
+_ASSIGN = re.compile(r"^(\$\w+)\s*(:=|=)\s*(.+)$", re.S)
+_RANGE_VARS = re.compile(r"^(\$\w+)\s*(?:,\s*(\$\w+)\s*)?:=\s*(.+)$", re.S)
 
 
 def _parse(tokens, i=0, stop=()):
@@ -90,8 +99,15 @@ def _parse(tokens, i=0, stop=()):
                 else:
                     cond = None
             nodes.append(node)
-        elif word == "range":
-            node = _Node("range", expr=val[5:].strip())
+        elif word in ("range", "with"):
+            rest = val[len(word):].strip()
+            node = _Node(word, expr=rest)
+            m = _RANGE_VARS.match(rest) if word == "range" else _ASSIGN.match(rest)
+            if m and word == "range":
+                node.names = tuple(n for n in (m.group(1), m.group(2)) if n)
+                node.expr = m.group(3).strip()
+            elif m:
+                node.names, node.expr = (m.group(1),), m.group(3).strip()
             node.body, i = _parse(tokens, i + 1, stop=("else", "end"))
             if i < len(tokens) and tokens[i][1].split(None, 1)[0] == "else":
                 node.else_body, i = _parse(tokens, i + 1, stop=("end",))
@@ -102,6 +118,10 @@ def _parse(tokens, i=0, stop=()):
         elif word in ("end", "else"):
             raise TemplateError(f"unexpected {{{{ {word} }}}}")
         elif val.startswith("/*"):
+            i += 1
+        elif _ASSIGN.match(val):
+            m = _ASSIGN.match(val)
+            nodes.append(_Node("assign", expr=m.group(3).strip(), names=(m.group(1),), declare=m.group(2) == ":="))
             i += 1
         else:
             nodes.append(_Node("expr", expr=val))
@@ -160,6 +180,7 @@ class Renderer:
     def __init__(self, context: dict):
         """context: {"Values": {...}, "Release": {...}, "Chart": {...}}"""
         self.ctx = context
+        self.scopes: list[dict] = [{}]      # template variables ($x := ...), innermost scope last
 
     # -- public ---------------------------------------------------------------
     def render(self, src: str, dot: Any = None) -> str:
@@ -177,19 +198,61 @@ class Renderer:
             elif n.kind == "expr":
                 v = self._eval(n.expr, dot)
                 out.append(self._fmt(v))
+            elif n.kind == "assign":
+                self._set_var(n.names[0], self._eval(n.expr, dot), n.declare)
             elif n.kind == "if":
                 for cond, body in n.branches:
                     if cond is None or _truthy(self._eval(cond, dot)):
-                        out.append(self._exec(body, dot))
+                        out.append(self._scoped(body, dot))
                         break
+            elif n.kind == "with":
+                v = self._eval(n.expr, dot)
+                if _truthy(v):
+                    out.append(self._scoped(n.body, v, {n.names[0]: v} if n.names else None))
+                else:
+                    out.append(self._scoped(n.else_body, dot))
             elif n.kind == "range":
                 seq = self._eval(n.expr, dot)
-                items = list(seq.values()) if isinstance(seq, dict) else list(seq or [])
-                if not items:
-                    out.append(self._exec(n.else_body, dot))
-                for item in items:
-                    out.append(self._exec(n.body, item))
+                if isinstance(seq, dict):       # Go ranges over maps in sorted key order
+                    pairs = [(k, seq[k]) for k in sorted(seq, key=str)]
+                elif isinstance(seq, int) and not isinstance(seq, bool):
+                    pairs = [(k, k) for k in range(seq)]
+                else:
+                    pairs = list(enumerate(seq or []))
+                if not pairs:
+                    out.append(self._scoped(n.else_body, dot))
+                for k, item in pairs:
+                    names = {}
+                    if len(n.names) == 2:
+                        names = {n.names[0]: k, n.names[1]: item}
+                    elif len(n.names) == 1:
+                        names = {n.names[0]: item}
+                    # with variables declared the dot stays what it was only in Go >= 1.x for `range $v :=`? No:
+                    # the dot is still set to the element, and the charts rely on `$` for the root inside such loops
+                    out.append(self._scoped(n.body, item, names))
         return "".join(out)
+
+    def _scoped(self, body, dot, names: dict | None = None) -> str:
+        self.scopes.append(dict(names or {}))
+        try:
+            return self._exec(body, dot)
+        finally:
+            self.scopes.pop()
+
+    def _set_var(self, name: str, value: Any, declare: bool) -> None:
+        if not declare:
+            for sc in reversed(self.scopes):
+                if name in sc:
+                    sc[name] = value
+                    return
+            raise TemplateError(f"assignment to undeclared variable {name}")
+        self.scopes[-1][name] = value
+
+    def _get_var(self, name: str) -> Any:
+        for sc in reversed(self.scopes):
+            if name in sc:
+                return sc[name]
+        raise TemplateError(f"undefined variable {name}")
 
     @staticmethod
     def _fmt(v: Any) -> str:
@@ -257,6 +320,14 @@ class Renderer:
             return dot, pos + 1
         if t == "$":
             return self.ctx, pos + 1
+        if re.fullmatch(r"\$\w+(\.\w+)*", t):           # $name or $name.field.sub
+            parts = t.split(".")
+            cur = self._get_var(parts[0])
+            for part in parts[1:]:
+                cur = cur.get(part) if isinstance(cur, dict) else getattr(cur, part, None)
+                if cur is None:
+                    break
+            return cur, pos + 1
         if t.startswith(".") or t.startswith("$."):
             root = self.ctx if (t.startswith("$.") or isinstance(dot, (str, int, float)) or dot is None) else dot
             path = t[2:] if t.startswith("$.") else t[1:]

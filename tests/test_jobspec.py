@@ -57,10 +57,11 @@ def test_reference_values_files_render(chart, rel, kind, nnodes, nproc, tmp_path
     assert (plan.kind, plan.nnodes, plan.nproc_per_node) == (kind, nnodes, nproc)
     lines = plan.script.splitlines()
     assert lines[0] == "#!/bin/bash"
-    assert '&& echo "Training script done"' in lines
+    done = '&& echo "Processing script done"' if kind == "pod" else '&& echo "Training script done"'
+    assert done in lines                                     # data-process.yaml:38 vs train.yaml:38
     assert plan.env["HOME"].endswith("/home/rel1")           # tpl of {{ .Release.Name }}
     if kind in ("static", "elastic", "pod", "rayjob"):
-        i = lines.index('&& echo "Training script done"')
+        i = lines.index(done)
         assert lines[i - 1].endswith("\\")                   # command/args joined by continuations
     if kind == "mpijob":
         assert plan.mpirun_np == 16 and plan.mpirun_args[3:5] == ["-np", "16"]
