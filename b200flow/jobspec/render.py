@@ -185,22 +185,36 @@ def render_job(chart_name: str, release: str, value_files=(), sets=(), root: str
                     "NCCL_SOCKET_IFNAME": str(m["nccl_socket_ifname"]), "NCCL_DEBUG": str(m["nccl_debug"]),
                     "TF_DEVICE_MIN_SYS_MEMORY_IN_MB": str(m["tf_device_min_sys_mem_mb"]),
                     "TF_ENABLE_AUTO_MIXED_PRECISION": str(m["tf_enable_auto_mixed_precision"])}
-        plan.mpirun_args = ["--output-filename", logroot, "--allow-run-as-root", "-np", str(m["gpus"]),
-                            "-bind-to", "none", "-map-by", "slot"]
+        optimized = "images_per_epoch" in m       # the -optimized chart (aws-samples fork of tensorpack's trainer)
+        # the launcher container's mpirun line, argument for argument (templates/maskrcnn.yaml:52-117 of both charts)
+        exports = ["HOROVOD_AUTOTUNE", "HOROVOD_HIERARCHICAL_ALLREDUCE=0", "HOROVOD_HIERARCHICAL_ALLGATHER=0",
+                   "HOROVOD_TORUS_ALLREDUCE=0", "HOROVOD_LOG_LEVEL", "NCCL_SOCKET_IFNAME", "NCCL_DEBUG",
+                   "TF_DEVICE_MIN_SYS_MEMORY_IN_MB", "TF_CPP_MIN_LOG_LEVEL", "TF_GPU_ALLOCATOR", "TF_AUTOTUNE_THRESHOLD",
+                   "TF_ENABLE_AUTO_MIXED_PRECISION", "TF_ENABLE_CUBLAS_TENSOR_OP_MATH_FP32",
+                   "TF_ENABLE_CUDNN_TENSOR_OP_MATH_FP32", "LD_LIBRARY_PATH", "PATH"]
+        plan.mpirun_args = (["--verbose"] if optimized else []) + [
+            "--output-filename", logroot, "--allow-run-as-root", "-np", str(m["gpus"]), "-bind-to", "none",
+            "-map-by", "slot", "-mca", "btl_tcp_if_exclude", "lo,docker0", "-mca", "oob_tcp_if_exclude", "lo,docker0",
+            "-mca", "plm_rsh_no_tree_spawn", "1"]
+        for e in exports:
+            plan.mpirun_args += ["-x", e]
+        plan.mpirun_args += ["-mca", "pml", "ob1", "-mca", "btl", "^openib", "--display-map", "--tag-output",
+                             "--timestamp-output"]
         cfg = [f"MODE_MASK={m['mode_mask']}", f"MODE_FPN={m['mode_fpn']}",
                f"DATA.BASEDIR=/{m['data_fs']}/{m['data_dir']}", f"DATA.TRAIN={m['data_train']}",
-               f"DATA.VAL={m['data_val']}", f"TRAIN.EVAL_PERIOD={m['eval_period_in_epochs']}"]
+               f"DATA.VAL={m['data_val']}"]
         cmd = ["python3", str(m["train_script"]), "--logdir", f"{logroot}/train_log/maskrcnn"]
-        if "images_per_epoch" in m:       # the -optimized chart (templates/maskrcnn.yaml:121-135)
+        weights = [f"TRAIN.BASE_LR={m['base_lr']}", f"BACKBONE.WEIGHTS=/{m['data_fs']}/{m['backbone_weights']}",
+                   f"BACKBONE.NORM={m['backbone_norm']}"]
+        if optimized:                     # templates/maskrcnn.yaml:121-135 of maskrcnn-optimized
             cmd += ["--images_per_epoch", str(m["images_per_epoch"])]
             cfg += [f"TRAIN.BATCH_SIZE_PER_GPU={m['batch_size_per_gpu']}",
-                    f"TRAIN.LR_EPOCH_SCHEDULE={m['lr_epoch_schedule']}",
-                    "PREPROC.PREDEFINED_PADDING=True"]
-        else:                             # tensorpack chart (templates/maskrcnn.yaml:119-132)
-            cfg += [f"TRAIN.STEPS_PER_EPOCH={m['steps_per_epoch']}", f"TRAIN.LR_SCHEDULE={m['lr_schedule']}"]
-        cfg += [f"TRAIN.BASE_LR={m['base_lr']}",
-                f"BACKBONE.WEIGHTS=/{m['data_fs']}/{m['backbone_weights']}",
-                f"BACKBONE.NORM={m['backbone_norm']}", "TRAINER=horovod"]
+                    f"TRAIN.EVAL_PERIOD={m['eval_period_in_epochs']}",
+                    f"TRAIN.LR_EPOCH_SCHEDULE={m['lr_epoch_schedule']}"] + weights + [
+                    "PREPROC.PREDEFINED_PADDING=True", "TRAINER=horovod"]
+        else:                             # tensorpack chart (templates/maskrcnn.yaml:119-132 of maskrcnn)
+            cfg += [f"TRAIN.EVAL_PERIOD={m['eval_period_in_epochs']}", f"TRAIN.STEPS_PER_EPOCH={m['steps_per_epoch']}",
+                    f"TRAIN.LR_SCHEDULE={m['lr_schedule']}"] + weights + ["TRAINER=horovod"]
         if m.get("extra_config"):
             cfg += str(m["extra_config"]).split()
         plan.launcher_command = cmd + ["--config"] + cfg
