@@ -141,14 +141,29 @@ def coco_like(num_images: int, height: int = 800, width: int = 1344, max_objects
         yield out
 
 
-def write_coco_tree(out: Path, num_train: int = 16, num_val: int = 4) -> None:
-    """Directory layout of the coco-data chart: train2017/ val2017/ annotations/ pretrained-models/."""
-    out = Path(out)
-    for split, n in (("train2017", num_train), ("val2017", num_val)):
-        (out / split).mkdir(parents=True, exist_ok=True)
+COCO_SPLITS = {"train2017": 16, "val2017": 4, "test2017": 4}
+STANDIN_KEY = "b200flow_offline_standin"
+
+
+def _coco_split(split: str):
+    """The synthetic samples of one COCO split; a function of the split name only, so images and annotations can be
+    written by different processes (the download chart unpacks them from different archives)."""
+    import zlib
+
+    return coco_like(COCO_SPLITS[split], 128, 160, seed=zlib.crc32(split.encode()) % 1000, mask=False)
+
+
+def write_coco_images(out: Path, split: str) -> None:
+    (out / split).mkdir(parents=True, exist_ok=True)
+    for i, s in enumerate(_coco_split(split)):
+        torch.save(s["image"].half(), out / split / f"{i:012d}.pt")
+
+
+def write_coco_annotations(out: Path, splits=("train2017", "val2017")) -> None:
+    (out / "annotations").mkdir(parents=True, exist_ok=True)
+    for split in splits:
         images, anns = [], []
-        for i, s in enumerate(coco_like(n, 128, 160, seed=hash(split) % 1000, mask=False)):
-            torch.save(s["image"].half(), out / split / f"{i:012d}.pt")
+        for i, s in enumerate(_coco_split(split)):
             images.append({"id": i, "file_name": f"{i:012d}.pt", "height": 128, "width": 160})
             for b, l in zip(s["boxes"].tolist(), s["labels"].tolist()):
                 cx, cy, rx, ry = (b[0] + b[2]) / 2, (b[1] + b[3]) / 2, (b[2] - b[0]) / 2, (b[3] - b[1]) / 2
@@ -157,28 +172,91 @@ def write_coco_tree(out: Path, num_train: int = 16, num_val: int = 4) -> None:
                 anns.append({"image_id": i, "bbox": [b[0], b[1], b[2] - b[0], b[3] - b[1]],
                              "category_id": l, "iscrowd": 0, "id": len(anns), "segmentation": [poly],
                              "area": math.pi * rx * ry})
-        (out / "annotations").mkdir(exist_ok=True)
         (out / "annotations" / f"instances_{split}.json").write_text(json.dumps(
             {"images": images, "annotations": anns,
              "categories": [{"id": c, "name": f"class{c}"} for c in range(1, 81)]}))
-    (out / "pretrained-models").mkdir(exist_ok=True)
-    np.savez(out / "pretrained-models" / "ImageNet-R50-AlignPadding.npz", synthetic=np.zeros(1))
+
+
+def write_backbone_placeholder(path: Path) -> None:
+    path.parent.mkdir(parents=True, exist_ok=True)
+    np.savez(path, synthetic=np.zeros(1))
+
+
+def write_coco_tree(out: Path, num_train: int = 16, num_val: int = 4) -> None:
+    """Directory layout of the coco-data chart: train2017/ val2017/ annotations/ pretrained-models/."""
+    out = Path(out)
+    for split in ("train2017", "val2017"):
+        write_coco_images(out, split)
+    write_coco_annotations(out)
+    write_backbone_placeholder(out / "pretrained-models" / "ImageNet-R50-AlignPadding.npz")
+
+
+def write_standin(url: str, dst: Path, docs: int = 2000) -> str:
+    """What the offline `wget` shim leaves in place of a download (launcher/offline.py): data files the workloads read
+    directly are generated at once (`.npz` backbone placeholder, `.jsonl` text corpus); an archive becomes a small marker
+    that the `unzip` shim expands with `unpack_standin`."""
+    dst = Path(dst)
+    dst.parent.mkdir(parents=True, exist_ok=True)
+    name = url.rstrip("/").rsplit("/", 1)[-1]
+    if name.endswith(".npz"):
+        write_backbone_placeholder(dst)
+        return "backbone placeholder"
+    if name.endswith(".jsonl"):
+        with open(dst, "w") as f:
+            for d in text_documents(docs):
+                f.write(json.dumps(d) + "\n")
+        return f"{docs} synthetic documents"
+    dst.write_text(json.dumps({STANDIN_KEY: url, "name": name}) + "\n")
+    return "archive marker"
+
+
+def read_standin(archive: Path) -> dict | None:
+    try:
+        with open(archive, "rb") as f:
+            head = f.read(4096)
+        d = json.loads(head.decode())
+        return d if isinstance(d, dict) and STANDIN_KEY in d else None
+    except (OSError, ValueError, UnicodeDecodeError):
+        return None
+
+
+def unpack_standin(marker: dict, dest: Path) -> str:
+    """Expand an archive marker into the tree the real archive holds (COCO 2017 zips)."""
+    dest = Path(dest)
+    name = marker["name"]
+    stem = name.removesuffix(".zip")
+    if stem in COCO_SPLITS:
+        write_coco_images(dest, stem)
+        return f"{COCO_SPLITS[stem]} synthetic images in {dest / stem}"
+    if stem.startswith("annotations_trainval"):
+        write_coco_annotations(dest)
+        return f"annotations in {dest / 'annotations'}"
+    raise SystemExit(f"[b200flow offline] no synthetic stand-in for archive {name}")
 
 
 def main(argv=None):
     ap = argparse.ArgumentParser()
-    ap.add_argument("kind", choices=["coco", "redpajama"])
+    ap.add_argument("kind", choices=["coco", "redpajama", "standin", "unpack"])
     ap.add_argument("--out", required=True)
     ap.add_argument("--docs", type=int, default=2000)
+    ap.add_argument("--url", default="")             # standin: what the download would have fetched
+    ap.add_argument("--archive", default="")         # unpack: a marker written by `standin`
     a = ap.parse_args(argv)
     out = Path(a.out)
+    if a.kind == "standin":
+        print(f"[b200flow offline] wget {a.url} -> {out}: {write_standin(a.url, out, a.docs)}")
+        return
+    if a.kind == "unpack":
+        marker = read_standin(Path(a.archive))
+        if marker is None:
+            raise SystemExit(f"{a.archive} is not an offline stand-in")
+        print(f"[b200flow offline] unzip {a.archive}: {unpack_standin(marker, out)}")
+        return
     out.mkdir(parents=True, exist_ok=True)
     if a.kind == "coco":
         write_coco_tree(out)
     else:
-        with open(out / "data.jsonl", "w") as f:
-            for d in text_documents(a.docs):
-                f.write(json.dumps(d) + "\n")
+        write_standin("book.jsonl", out / "data.jsonl", a.docs)
     print(f"[b200flow] synthetic {a.kind} data written to {out}")
 
 

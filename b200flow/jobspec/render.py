@@ -102,15 +102,33 @@ def _mounts(pvcs, root: Path) -> dict:
     return {str(p["mount_path"]): str(root / str(p["mount_path"]).strip("/")) for p in (pvcs or [])}
 
 
-def _data_script(kind: str, data_dir_expr: str) -> list[str]:
-    """coco-data / redpajama-data: idempotent populate of $DATA_DIR.  The reference downloads
-    (charts/machine-learning/data-prep/coco-data/templates/coco-data.yaml:13-35); there is no
-    network on the box, so the same layout is generated synthetically."""
-    return ["#!/bin/bash",
-            '[[ -d $DATA_DIR ]] && echo "$DATA_DIR already exists" && exit 0',
-            "mkdir -p $DATA_DIR",
-            'echo "Data dir: $DATA_DIR"',
-            f"python -m b200flow.data.synthetic {kind} --out $DATA_DIR"]
+# What the two download charts fetch (charts/machine-learning/data-prep/coco-data/templates/coco-data.yaml:19-35,
+# redpajama-data/templates/redpajama-data.yaml:15).  Offline the launcher's `wget` / `unzip` / `yum` shims stand in.
+COCO_HOST = "http://images.cocodataset.org"
+COCO_ARCHIVES = ("zips/train2017.zip", "zips/val2017.zip", "zips/test2017.zip",
+                 "annotations/annotations_trainval2017.zip")
+BACKBONE_HOST = "http://models.tensorpack.com/FasterRCNN"
+BACKBONES = ("ImageNet-R50-AlignPadding.npz", "ImageNet-R101-AlignPadding.npz")
+REDPAJAMA_BOOK = "https://data.together.xyz/redpajama-data-1T/v1.0.0/book/book.jsonl"
+
+
+def _data_script(kind: str) -> list[str]:
+    """The script of the coco-data / redpajama-data chart: install the tools, leave an existing $DATA_DIR alone,
+    download (and unpack) into it."""
+    tools = ("unzip", "wget") if kind == "coco" else ("wget",)
+    out = ["#!/bin/bash"] + [f"yum install -y {t}" for t in tools]
+    out += ['[[ -d $DATA_DIR ]] && echo "$DATA_DIR already exists" && exit 0', "mkdir -p $DATA_DIR",
+            'echo "Data dir: $DATA_DIR"']
+    if kind != "coco":
+        return out + [f"wget -O $DATA_DIR/data.jsonl {REDPAJAMA_BOOK}"]
+    out += ["DOWNLOAD_DIR=$DATA_DIR.$(cat /dev/urandom | tr -dc 'a-z0-9' | fold -w 16 | head -n 1)",
+            "mkdir -p $DOWNLOAD_DIR", 'echo "Download dir: $DOWNLOAD_DIR"']
+    for rel in COCO_ARCHIVES:
+        name = rel.rsplit("/", 1)[-1]
+        out += [f"wget -O $DOWNLOAD_DIR/{name} {COCO_HOST}/{rel}", f"unzip $DOWNLOAD_DIR/{name} -d $DATA_DIR"]
+    out.append("mkdir $DATA_DIR/pretrained-models")
+    out += [f"wget -O $DATA_DIR/pretrained-models/{b} {BACKBONE_HOST}/{b}" for b in BACKBONES]
+    return out + ["rm -rf $DOWNLOAD_DIR"]
 
 
 def render_job(chart_name: str, release: str, value_files=(), sets=(), root: str | Path = "/tmp/b200flow",
@@ -225,7 +243,7 @@ def render_job(chart_name: str, release: str, value_files=(), sets=(), root: str
         pvc = vals["pvc"]
         plan.mounts = _mounts(pvc, root)
         plan.env = {"DATA_DIR": f"{pvc['mount_path']}/{pvc['data_path']}"}
-        plan.script = "\n".join(_data_script("coco" if chart.name == "coco-data" else "redpajama", "")) + "\n"
+        plan.script = "\n".join(_data_script("coco" if chart.name == "coco-data" else "redpajama")) + "\n"
         return plan
 
     if chart.kind == "deployment":        # *-jupyter: inference + visualisation + TensorBoard

@@ -9,7 +9,11 @@ is no network, so the launcher prepends a directory of tiny executables to `PATH
   `pretrain_gpt.py`, `tools/preprocess_data.py`) into `<dir>`; `checkout` / `fetch` /
   `reset` inside such a tree succeed as no-ops; anything else goes to the real git.
 * `pip` / `pip3 install …` log and succeed (`offline: skip-pip`).
-* `wget` / `yum` / `apt-get` log and succeed without doing anything.
+* `yum` / `apt-get` log and succeed without doing anything.
+* `wget -O <file> <url>` leaves a synthetic stand-in for the download (`data/synthetic.py::write_standin`: a generated
+  text corpus for `.jsonl`, a placeholder for backbone `.npz` files, a small marker for archives) and `unzip <marker>
+  -d <dir>` expands a marker into the tree the real archive holds (COCO 2017 images / annotations); so the download
+  scripts of the `coco-data` and `redpajama-data` charts run unchanged.  Real archives still go to the real `unzip`.
 * absolute script paths baked into images (`/tensorpack/examples/FasterRCNN/train.py`,
   `/mask-rcnn-tensorflow/MaskRCNN/train.py`) are resolved by a `python3` shim.
 """
@@ -71,6 +75,40 @@ echo "[b200flow offline] skipped: {name} $*"
 exit 0
 '''
 
+_WGET = r'''#!{py}
+import sys
+sys.path.insert(0, {repo!r})
+args = sys.argv[1:]
+out, url, i = None, None, 0
+while i < len(args):
+    if args[i] in ("-O", "--output-document") and i + 1 < len(args):
+        out, i = args[i + 1], i + 2
+        continue
+    if not args[i].startswith("-"):
+        url = args[i]
+    i += 1
+if out is None or url is None:
+    print("[b200flow offline] skipped: wget " + " ".join(args))
+    sys.exit(0)
+from b200flow.data.synthetic import main
+main(["standin", "--url", url, "--out", out])
+'''
+
+_UNZIP = r'''#!{py}
+import os, subprocess, sys
+sys.path.insert(0, {repo!r})
+args = sys.argv[1:]
+files = [a for i, a in enumerate(args) if not a.startswith("-") and (i == 0 or args[i - 1] != "-d")]
+dest = args[args.index("-d") + 1] if "-d" in args and args.index("-d") + 1 < len(args) else "."
+from b200flow.data.synthetic import main, read_standin
+if files and read_standin(files[0]) is not None:
+    main(["unpack", "--archive", files[0], "--out", dest])
+    sys.exit(0)
+real = next((os.path.join(d, "unzip") for d in os.environ.get("PATH", "").split(os.pathsep)[1:]
+             if os.access(os.path.join(d, "unzip"), os.X_OK)), None)
+sys.exit(subprocess.call([real] + args) if real else 127)
+'''
+
 _PY = r'''#!{py}
 import os, sys
 sys.path.insert(0, {repo!r})
@@ -91,8 +129,10 @@ def write_shims(dirpath: Path) -> None:
     repo = str(Path(__file__).resolve().parent.parent.parent)
     py = sys.executable
     files = {"git": _GIT.format(py=py, repo=repo),
-             "python3": _PY.format(py=py, repo=repo)}
-    for name in ("pip", "pip3", "wget", "yum", "apt-get", "apt"):
+             "python3": _PY.format(py=py, repo=repo),
+             "wget": _WGET.format(py=py, repo=repo),
+             "unzip": _UNZIP.format(py=py, repo=repo)}
+    for name in ("pip", "pip3", "yum", "apt-get", "apt"):
         files[name] = _NOOP.format(name=name)
     for name, body in files.items():
         p = dirpath / name

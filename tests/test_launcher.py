@@ -114,7 +114,10 @@ def test_data_charts_run_offline_and_are_idempotent(tmp_root):
     rc, st = install("d-coco", "coco-data")
     assert rc == 0 and st["phase"] == "Succeeded" and st["kind"] == "pod"
     coco = tmp_root / "fsx/data/coco2017"
-    assert {"train2017", "val2017", "annotations", "pretrained-models"} <= {p.name for p in coco.iterdir()}
+    assert {"train2017", "val2017", "test2017", "annotations", "pretrained-models"} <= {p.name for p in coco.iterdir()}
+    assert {p.name for p in (coco / "pretrained-models").iterdir()} == {"ImageNet-R50-AlignPadding.npz",
+                                                                        "ImageNet-R101-AlignPadding.npz"}
+    assert not list(coco.parent.glob("coco2017.*"))           # the script removed its download directory
     marker = coco / "annotations" / "keep.me"
     marker.write_text("x")
     rc, st = install("d-coco", "coco-data")
