@@ -164,12 +164,17 @@ def attach_baseline(out: dict, base: dict | None, world: int) -> None:
                                 if base.get("impl") == "twin" else
                                 "same engine and GEMM kernels, NCCL collectives instead of the fused peer-memory kernels")}
     out["vs_baseline"] = out["value"] / base["value"] if base["value"] else None
-    a, b = out.get("loss_after_warmup"), base.get("loss_after_warmup")
-    if world > 1 and a is not None and b is not None and base.get("impl") != "twin":
-        rel = abs(a - b) / max(abs(b), 1e-6)
-        out["loss_parity"] = {"fused": a, "nccl": b, "rel_diff": rel, "ok": rel <= 1e-2}
+    ca, cb = out.get("loss_curve") or [], base.get("loss_curve") or []
+    if world > 1 and ca and cb and base.get("impl") != "twin":
+        # Same engine, seed and data in both arms: the curves may differ only by the summation order inside the
+        # collectives.  Compared over the first three optimizer steps - afterwards the 7B model is memorising the 32
+        # cached micro-batches (loss 11 -> 0.1 in three more steps) and amplifies rounding-level differences.
+        n = min(3, len(ca), len(cb))
+        rel = max(abs(x - y) / max(abs(y), 1e-6) for x, y in zip(ca[:n], cb[:n]))
+        out["loss_parity"] = {"steps_compared": n, "fused": ca[:n], "nccl": cb[:n], "max_rel_diff": rel,
+                              "ok": rel <= 1e-2}
         if rel > 1e-2:
-            print(f"WARNING: fused and NCCL loss after warm-up differ by {rel:.3e} (> 1e-2)", file=sys.stderr)
+            print(f"WARNING: fused and NCCL losses of the first {n} steps differ by {rel:.3e} (> 1e-2)", file=sys.stderr)
 
 
 def main():
