@@ -6,7 +6,7 @@
                  command: are the GPUs visible, are the shared mounts there and writable, do the native
                  libraries load, does a collective over all requested ranks return the right sum (NCCL on
                  GPUs with peer access reported per pair, gloo on CPU).
-* `stage-data` — `eks-cluster/utils/stage-data.yaml:1-50` copies `s3://$S3_BUCKET/$S3_PREFIX` to a directory
+* `stage-data` — `eks-cluster/utils/stage-data.yaml:1-46` copies `s3://$S3_BUCKET/$S3_PREFIX` to a directory
                  on the shared volume.  There is no object store on the box: the source is a local directory
                  (an `s3://bucket/prefix` source resolves under `$B2F_S3_ROOT/bucket/prefix`).
 * `attach`     — `eks-cluster/utils/attach-pvc.yaml:1-24` starts a pod with `/efs` and `/fsx` mounted to look
