@@ -105,3 +105,33 @@ def test_chart_defaults_and_special_charts(tmp_path):
         render_job("maskrcnn-jupyter", "j", [], root=tmp_path)
     j = render_job("maskrcnn-jupyter", "j", [], root=tmp_path, sets=["global.log_dir=logs/run1"])
     assert j.env["LOGDIR"] == "/fsx/logs/run1"
+
+
+def test_template_variables_with_and_keyed_range():
+    """The Go-template features the reference's chart templates use beyond the values files: variables with block
+    scope (`:=` declares, `=` assigns the enclosing one), `range $v :=` / `range $k, $v :=` (maps in sorted key order),
+    `with`, `$` for the root inside loops (charts/machine-learning/training/pytorchjob-distributed/templates/train.yaml:86-98,126-133)."""
+    from b200flow.jobspec.template import TemplateError, render
+
+    vals = {"pvc": [{"name": "efs"}, {"name": "fsx"}], "requests": {"nvidia.com/gpu": 4, "cpu": 2},
+            "tol": [{"key": "{{ .Values.k }}", "operator": "Exists"}], "k": "gpu", "empty": [], "opt": {"x": 1}}
+    # a counter declared outside the loop and advanced inside it (`$pv_index = add $pv_index 1`)
+    t = "{{- $i := 1 }}{{- range $pv := .Values.pvc }}[pv-{{ $i }}:{{ $pv.name }}]{{- $i = add $i 1 }}{{- end }} next={{ $i }}"
+    assert render(t, vals, "r") == "[pv-1:efs][pv-2:fsx] next=3"
+    # a declaration inside the block shadows and does not leak
+    t = "{{ $x := 1 }}{{ if true }}{{ $x := 2 }}{{ $x }}{{ end }}{{ $x }}"
+    assert render(t, vals, "r") == "21"
+    # maps iterate in sorted key order; key and value variables
+    t = "{{ range $k, $v := .Values.requests }}{{ $k }}={{ $v }};{{ end }}"
+    assert render(t, vals, "r") == "cpu=2;nvidia.com/gpu=4;"
+    # `$` is the root inside a loop whose dot is the element; tpl evaluates a value as a template
+    t = "{{ range $v := .Values.tol }}{{ tpl $v.key $ }}/{{ $.Release.Name }}/{{ $v.operator }}{{ end }}"
+    assert render(t, vals, "rel") == "gpu/rel/Exists"
+    # index variable over a list, else branch of an empty range, with / else
+    assert render("{{ range $i, $p := .Values.pvc }}{{ $i }}{{ $p.name }}{{ end }}", vals, "r") == "0efs1fsx"
+    assert render("{{ range .Values.empty }}x{{ else }}none{{ end }}", vals, "r") == "none"
+    assert render("{{ with .Values.opt }}{{ .x }}{{ else }}no{{ end }}|{{ with .Values.missing }}y{{ else }}no{{ end }}", vals, "r") == "1|no"
+    with pytest.raises(TemplateError):
+        render("{{ $undeclared = 1 }}", vals, "r")
+    with pytest.raises(TemplateError):
+        render("{{ $nope }}", vals, "r")
