@@ -142,7 +142,7 @@ def coco_like(num_images: int, height: int = 800, width: int = 1344, max_objects
 
 
 COCO_SPLITS = {"train2017": 16, "val2017": 4, "test2017": 4}
-STANDIN_KEY = "b200flow_offline_standin"
+from ..launcher.offline import STANDIN_KEY  # noqa: E402  (the marker the offline wget / unzip shims exchange)
 
 
 def _coco_split(split: str):

@@ -24,6 +24,7 @@ import sys
 from pathlib import Path
 
 WORKLOADS = Path(__file__).resolve().parent.parent / "workloads"
+STANDIN_KEY = "b200flow_offline_standin"      # first key of the JSON marker that stands in for a downloaded archive
 
 # upstream URL fragment -> local tree (relative to b200flow/workloads/trees)
 REPO_TREES = {
@@ -76,8 +77,7 @@ exit 0
 '''
 
 _WGET = r'''#!{py}
-import sys
-sys.path.insert(0, {repo!r})
+import json, os, sys
 args = sys.argv[1:]
 out, url, i = None, None, 0
 while i < len(args):
@@ -90,6 +90,14 @@ while i < len(args):
 if out is None or url is None:
     print("[b200flow offline] skipped: wget " + " ".join(args))
     sys.exit(0)
+name = url.rstrip("/").rsplit("/", 1)[-1]
+if name.endswith((".zip", ".tar", ".tar.gz", ".tgz")):      # an archive: a marker the unzip shim expands (no heavy imports)
+    os.makedirs(os.path.dirname(os.path.abspath(out)), exist_ok=True)
+    with open(out, "w") as f:
+        f.write(json.dumps({{{key!r}: url, "name": name}}) + "\n")
+    print(f"[b200flow offline] wget {{url}} -> {{out}}: archive marker")
+    sys.exit(0)
+sys.path.insert(0, {repo!r})
 from b200flow.data.synthetic import main
 main(["standin", "--url", url, "--out", out])
 '''
@@ -130,7 +138,7 @@ def write_shims(dirpath: Path) -> None:
     py = sys.executable
     files = {"git": _GIT.format(py=py, repo=repo),
              "python3": _PY.format(py=py, repo=repo),
-             "wget": _WGET.format(py=py, repo=repo),
+             "wget": _WGET.format(py=py, repo=repo, key=STANDIN_KEY),
              "unzip": _UNZIP.format(py=py, repo=repo)}
     for name in ("pip", "pip3", "yum", "apt-get", "apt"):
         files[name] = _NOOP.format(name=name)
