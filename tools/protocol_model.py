@@ -1,4 +1,4 @@
-"""Explicit-state models of the buffer-reuse protocols of the peer-memory kernels (K3, K4, K5), explored over EVERY
+"""Explicit-state models of the buffer-reuse protocols of the peer-memory kernels (K1, K3, K4, K5), explored over EVERY
 interleaving of the ranks' steps.
 
 The kernels reuse a fixed number of symmetric buffers across calls and never reset a flag: flags carry the call counter
@@ -39,6 +39,58 @@ def explore(initial, successors, is_final, limit: int = 2_000_000):
 
 def _set(tup, i, v):
     return tup[:i] + (v,) + tup[i + 1:]
+
+
+# ---------------------------------------------------------------------------------------------- K1: in-place all-reduce
+def k1_model(world: int = 2, calls: int = 3, end_barrier: bool = True):
+    """Per rank and call e (csrc/comm/collectives.cu::allreduce_f32_kernel, one block): the gradients of the call are in
+    the rank's symmetric buffer (one sub-slice per rank); barrier with flag value 2e-1 ("all gradients final"); the rank
+    reads sub-slice `me` of every rank, writes the average into sub-slice `me` of every rank; barrier with 2e ("all
+    slices landed"); then it reads its whole buffer.  One flag word per (rank, peer), never reset.
+    `end_barrier=False` is the negative control."""
+    W = world
+    # steps: 0 produce, 1 announce A, 2..W+1 wait A (each peer incl. self), W+2 reduce (read all), W+3 write all,
+    #        W+4 announce B, W+5..2W+4 wait B, 2W+5 consume
+    per_call = 2 * W + 6
+
+    def initial():
+        pcs = tuple((1, 0) for _ in range(W))
+        buf = tuple(tuple(None for _ in range(W)) for _ in range(W))         # buf[rank][sub-slice]
+        flag = tuple(tuple(0 for _ in range(W)) for _ in range(W))           # flag[at][from]
+        return (pcs, buf, flag)
+
+    def successors(state):
+        pcs, buf, flag = state
+        for r in range(W):
+            e, k = pcs[r]
+            if e > calls:
+                continue
+            nxt = (e, k + 1) if k + 1 < per_call else (e + 1, 0)
+            if k == 0:
+                yield (_set(pcs, r, nxt), _set(buf, r, tuple(("g", r, e) for _ in range(W))), flag)
+            elif k == 1 or k == W + 4:
+                val = 2 * e - 1 if k == 1 else 2 * e
+                yield (_set(pcs, r, nxt), buf, tuple(_set(flag[at], r, val) for at in range(W)))
+            elif 2 <= k <= W + 1:
+                if flag[r][k - 2] >= 2 * e - 1:
+                    yield (_set(pcs, r, nxt), buf, flag)
+            elif k == W + 2:
+                for p in range(W):
+                    if buf[p][r] != ("g", p, e):
+                        raise Violation(f"K1: rank {r} call {e} reduced {buf[p][r]} from rank {p}")
+                yield (_set(pcs, r, nxt), buf, flag)
+            elif k == W + 3:
+                yield (_set(pcs, r, nxt), tuple(_set(buf[p], r, ("avg", r, e)) for p in range(W)), flag)
+            elif W + 5 <= k <= 2 * W + 4:
+                if not end_barrier or flag[r][k - W - 5] >= 2 * e:
+                    yield (_set(pcs, r, nxt), buf, flag)
+            else:
+                for q in range(W):
+                    if buf[r][q] != ("avg", q, e):
+                        raise Violation(f"K1: rank {r} call {e} consumed {buf[r][q]} in sub-slice {q}")
+                yield (_set(pcs, r, nxt), buf, flag)
+
+    return initial(), successors, lambda s: all(e > calls for e, _ in s[0])
 
 
 # ---------------------------------------------------------------------------------------------- K3: all-gather -> GEMM
@@ -196,12 +248,12 @@ def k5_model(world: int = 2, calls: int = 3, buffers: int = 2, epoch_flags: bool
 
 
 def main():
-    for name, make in (("K3", k3_model), ("K4", k4_model), ("K5", k5_model)):
+    for name, make in (("K1", k1_model), ("K3", k3_model), ("K4", k4_model), ("K5", k5_model)):
         for world, calls in ((2, 4), (3, 3)):
             n = explore(*make(world, calls))
-            print(f"{name}: world {world}, {calls} calls, two buffers: {n} states, every read correct, no deadlock")
+            print(f"{name}: world {world}, {calls} calls, as built: {n} states, every read correct, no deadlock")
         try:
-            kw = {"slots": 1} if name == "K3" else ({"buffers": 1} if name == "K4" else {"epoch_flags": False})
+            kw = {"K1": {"end_barrier": False}, "K3": {"slots": 1}, "K4": {"buffers": 1}, "K5": {"epoch_flags": False}}[name]
             explore(*make(2, 3, **kw))
             print(f"{name}: negative control {kw} passed (unexpected)")
         except Violation as v:
