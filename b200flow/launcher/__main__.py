@@ -28,6 +28,12 @@ from . import runner as R
 
 def _common(p):
     p.add_argument("--root", default=os.environ.get("B2F_ROOT", "/tmp/b200flow"))
+    # accepted so that the README command lines of the reference work with `helm` / `kubectl` swapped for this CLI
+    # (`helm install --debug <release> ./charts/machine-learning/training/<chart>/ -f <values> -n <namespace>`,
+    # examples/accelerate/bert-glue-mrpc/README.md:23-25); there is one namespace here
+    p.add_argument("--debug", action="store_true", help="accepted for `helm install --debug`; prints the launch plan")
+    if not any(a.dest == "namespace" for a in p._actions):
+        p.add_argument("-n", "--namespace", default="local", help="accepted for helm / kubectl command lines; unused")
 
 
 def _install_detached(a, plan, argv) -> int:
@@ -134,6 +140,10 @@ def main(argv=None) -> int:
             print("---")
             print(script)
             return 0
+        if a.debug:
+            d = asdict(plan)
+            d.pop("script")
+            print(json.dumps(d, indent=1, default=str), file=sys.stderr)
         if a.no_wait:
             return _install_detached(a, plan, argv if argv is not None else sys.argv[1:])
         run = R.Runner(plan, a.root, offline=not a.online, fault=a.inject_fault,

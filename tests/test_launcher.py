@@ -304,3 +304,24 @@ def test_more_ranks_than_the_pods_gpu_limit_fails_before_spawning(tmp_root, monk
     assert not any("should-not-run" in v for v in logs.values())
     rc, logs, st = _run("pytorchjob-distributed", "lim2", vals, tmp_root, sets=[r"resources.limits.nvidia\.com/gpu=8"])
     assert st.get("message") is None and "should-not-run" in "".join(logs.values())
+
+
+def test_readme_command_lines_of_the_reference_work_with_the_cli_swapped_in(tmp_path):
+    """`helm install --debug <release> ./charts/machine-learning/training/<chart>/ -f <values> -n <namespace>`,
+    `helm uninstall <release> -n <namespace>`, `kubectl logs -f <pod>` (examples/accelerate/bert-glue-mrpc/README.md:23-34):
+    the same argument lists are accepted by `python -m b200flow.launcher`."""
+    import subprocess
+
+    repo = Path(__file__).resolve().parent.parent
+    vals = tmp_path / "v.yaml"
+    vals.write_text(json.dumps(_vals("echo hello-from-$HOSTNAME", resources={"nnodes": 1, "nproc_per_node": 1})))
+    run = lambda *a: subprocess.run([sys.executable, "-m", "b200flow.launcher", *a, "--root", str(tmp_path)],  # noqa: E731
+                                    cwd=repo, capture_output=True, text=True, timeout=300)
+    r = run("install", "--debug", "accel-bert", "./charts/machine-learning/training/pytorchjob-distributed/",
+            "-f", str(vals), "-n", "kubeflow-user-example-com")
+    assert r.returncode == 0 and json.loads(r.stdout.strip().splitlines()[-1])["phase"] == "Succeeded", r.stderr[-800:]
+    assert '"chart": "pytorchjob-distributed"' in r.stderr                 # --debug prints the plan
+    r = run("logs", "accel-bert", "-n", "kubeflow-user-example-com")
+    assert "hello-from-accel-bert-master-0" in r.stdout
+    r = run("uninstall", "accel-bert", "-n", "kubeflow-user-example-com")
+    assert r.returncode == 0 and "uninstalled" in r.stdout
