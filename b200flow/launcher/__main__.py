@@ -6,7 +6,7 @@
     status    <release> [--root DIR]
     logs      <release> [--root DIR] [--tail N] [-f]
     list      [--root DIR]                       (releases with chart, phase, restarts)
-    scale     <release> <replicas> [--root DIR]  (elastic releases: worker pods within min_replicas..max_replicas)
+    scale     <release> <replicas> | --replicas N [--root DIR]  (elastic releases: worker pods within min_replicas..max_replicas)
     smoke     [--gpus N] [--root DIR]            (GPU / mounts / native libraries / collective check)
     stage-data <src> <dst under /efs or /fsx> [--root DIR]
     attach    [release] [--root DIR]             (where /efs and /fsx live locally and what is in them)
@@ -92,7 +92,8 @@ def main(argv=None) -> int:
     _common(p)
     p = sub.add_parser("scale")
     p.add_argument("release")
-    p.add_argument("replicas", type=int)
+    p.add_argument("replicas_pos", type=int, nargs="?", default=None, metavar="replicas")
+    p.add_argument("--replicas", type=int, default=None, help="like `kubectl scale --replicas N`")
     _common(p)
     p = sub.add_parser("smoke")
     p.add_argument("--gpus", type=int, default=0)
@@ -117,8 +118,11 @@ def main(argv=None) -> int:
         print(json.dumps(rows, indent=1))
         return 0
     if a.cmd == "scale":
-        ok = R.scale(a.root, a.release, a.replicas)
-        print(f'release "{a.release}" ' + (f"scaling to {a.replicas}" if ok else "not found"))
+        n = a.replicas if a.replicas is not None else a.replicas_pos
+        if n is None:
+            ap.error("scale: give the number of replicas (positional or --replicas N)")
+        ok = R.scale(a.root, a.release, n)
+        print(f'release "{a.release}" ' + (f"scaling to {n}" if ok else "not found"))
         return 0 if ok else 1
     if a.cmd in ("smoke", "stage-data", "attach"):
         from . import tools as T
