@@ -164,16 +164,33 @@ def main(argv=None) -> int:
         print(json.dumps(R.status(a.root, a.release), indent=1))
         return 0
     if a.cmd == "logs":
-        for pod, txt in R.logs(a.root, a.release, a.tail).items():
+        # `kubectl logs -f pytorchjob-<release>-worker-0` names a pod: "<kind>-<release>-<role>-<n>" of the operators
+        # (examples/accelerate/bert-glue-mrpc/README.md:29); resolve it to the release and keep only that pod
+        only = None
+        if not R.logs(a.root, a.release):
+            import re
+            from pathlib import Path
+
+            m = re.match(r"^(?:pytorchjob|mpijob|rayjob|data-process|coco-data|redpajama-data)-(.+?)(?:-(master|worker|launcher|head)-(\d+))?$",
+                         a.release)
+            if m and (Path(a.root) / ".b200flow" / "releases" / m.group(1)).is_dir():
+                a.release = m.group(1)
+                only = f"{m.group(1)}-{m.group(2)}-{m.group(3)}" if m.group(2) else None
+        _logs = R.logs
+        if only is not None:
+            R_logs = lambda root, rel, tail=None: {k: v for k, v in _logs(root, rel, tail).items() if k.startswith(only)}  # noqa: E731
+        else:
+            R_logs = _logs
+        for pod, txt in R_logs(a.root, a.release, a.tail).items():
             print(f"==> {pod} <==")
             print(txt)
         if a.follow:          # `kubectl logs -f`: new lines of every pod until the release is no longer running
             import time
 
-            seen = {pod: len(txt) for pod, txt in R.logs(a.root, a.release).items()}
+            seen = {pod: len(txt) for pod, txt in R_logs(a.root, a.release).items()}
             while True:
                 running = R.status(a.root, a.release).get("phase") in ("Running", "Restarting")
-                for pod, txt in R.logs(a.root, a.release).items():
+                for pod, txt in R_logs(a.root, a.release).items():
                     if len(txt) > seen.get(pod, 0):
                         for line in txt[seen.get(pod, 0):].splitlines():
                             print(f"[{pod}] {line}", flush=True)

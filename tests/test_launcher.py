@@ -323,5 +323,7 @@ def test_readme_command_lines_of_the_reference_work_with_the_cli_swapped_in(tmp_
     assert '"chart": "pytorchjob-distributed"' in r.stderr                 # --debug prints the plan
     r = run("logs", "accel-bert", "-n", "kubeflow-user-example-com")
     assert "hello-from-accel-bert-master-0" in r.stdout
+    r = run("logs", "-f", "pytorchjob-accel-bert-master-0", "-n", "kubeflow-user-example-com")      # a pod name, as kubectl takes
+    assert "hello-from-accel-bert-master-0" in r.stdout and r.returncode == 0
     r = run("uninstall", "accel-bert", "-n", "kubeflow-user-example-com")
     assert r.returncode == 0 and "uninstalled" in r.stdout
