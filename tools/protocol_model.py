@@ -1,4 +1,4 @@
-"""Explicit-state models of the buffer-reuse protocols of the peer-memory kernels (K1, K3, K4, K5), explored over EVERY
+"""Explicit-state models of the buffer-reuse protocols of the peer-memory kernels (K1, K2, K3, K4, K5), explored over EVERY
 interleaving of the ranks' steps.
 
 The kernels reuse a fixed number of symmetric buffers across calls and never reset a flag: flags carry the call counter
@@ -89,6 +89,57 @@ def k1_model(world: int = 2, calls: int = 3, end_barrier: bool = True):
                     if buf[r][q] != ("avg", q, e):
                         raise Violation(f"K1: rank {r} call {e} consumed {buf[r][q]} in sub-slice {q}")
                 yield (_set(pcs, r, nxt), buf, flag)
+
+    return initial(), successors, lambda s: all(e > calls for e, _ in s[0])
+
+
+# ---------------------------------------------------------------------------------------------- K2: ZeRO-1 step
+def k2_model(world: int = 2, calls: int = 3, start_barrier: bool = True):
+    """Per rank and step e (csrc/comm/collectives.cu zero1_reduce / zero1_adam_gather, parallel/fused_dp.py):
+         forward + backward: read my copy of every parameter shard (must be the values of step e-1), write my gradients
+         barrier 2e-1 ("all gradients final" - also: everybody is done reading its parameters)
+         reduce: read gradient shard `me` from every rank
+         Adam on shard `me`, store the updated shard into every rank's parameter buffer
+         barrier 2e ("all shards landed" - also: everybody is done reading my gradients).
+       `start_barrier=False` is the negative control (a fast rank overwrites parameters a slow rank is still using)."""
+    W = world
+    per_call = 2 * W + 6        # 0 compute, 1 announce A, 2..W+1 wait A, W+2 reduce, W+3 write params, W+4 announce B, W+5..2W+4 wait B
+
+    def initial():
+        pcs = tuple((1, 0) for _ in range(W))
+        params = tuple(tuple(("p", q, 0) for q in range(W)) for _ in range(W))     # params[rank][shard]
+        grads = tuple(tuple(None for _ in range(W)) for _ in range(W))             # grads[rank][shard]
+        flag = tuple(tuple(0 for _ in range(W)) for _ in range(W))
+        return (pcs, params, grads, flag)
+
+    def successors(state):
+        pcs, params, grads, flag = state
+        for r in range(W):
+            e, k = pcs[r]
+            if e > calls:
+                continue
+            nxt = (e, k + 1) if k + 1 < per_call - 1 else (e + 1, 0)
+            if k == 0:
+                for q in range(W):
+                    if params[r][q] != ("p", q, e - 1):
+                        raise Violation(f"K2: rank {r} step {e} computed with parameter shard {params[r][q]}")
+                yield (_set(pcs, r, nxt), params, _set(grads, r, tuple(("g", r, e) for _ in range(W))), flag)
+            elif k == 1 or k == W + 4:
+                val = 2 * e - 1 if k == 1 else 2 * e
+                yield (_set(pcs, r, nxt), params, grads, tuple(_set(flag[at], r, val) for at in range(W)))
+            elif 2 <= k <= W + 1:
+                if not start_barrier or flag[r][k - 2] >= 2 * e - 1:
+                    yield (_set(pcs, r, nxt), params, grads, flag)
+            elif k == W + 2:
+                for p in range(W):
+                    if grads[p][r] != ("g", p, e):
+                        raise Violation(f"K2: rank {r} step {e} reduced gradient {grads[p][r]} of rank {p}")
+                yield (_set(pcs, r, nxt), params, grads, flag)
+            elif k == W + 3:
+                yield (_set(pcs, r, nxt), tuple(_set(params[p], r, ("p", r, e)) for p in range(W)), grads, flag)
+            else:
+                if flag[r][k - W - 5] >= 2 * e:
+                    yield (_set(pcs, r, nxt), params, grads, flag)
 
     return initial(), successors, lambda s: all(e > calls for e, _ in s[0])
 
@@ -248,12 +299,12 @@ def k5_model(world: int = 2, calls: int = 3, buffers: int = 2, epoch_flags: bool
 
 
 def main():
-    for name, make in (("K1", k1_model), ("K3", k3_model), ("K4", k4_model), ("K5", k5_model)):
+    for name, make in (("K1", k1_model), ("K2", k2_model), ("K3", k3_model), ("K4", k4_model), ("K5", k5_model)):
         for world, calls in ((2, 4), (3, 3)):
             n = explore(*make(world, calls))
             print(f"{name}: world {world}, {calls} calls, as built: {n} states, every read correct, no deadlock")
         try:
-            kw = {"K1": {"end_barrier": False}, "K3": {"slots": 1}, "K4": {"buffers": 1}, "K5": {"epoch_flags": False}}[name]
+            kw = {"K1": {"end_barrier": False}, "K2": {"start_barrier": False}, "K3": {"slots": 1}, "K4": {"buffers": 1}, "K5": {"epoch_flags": False}}[name]
             explore(*make(2, 3, **kw))
             print(f"{name}: negative control {kw} passed (unexpected)")
         except Violation as v:
